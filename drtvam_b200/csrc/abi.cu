@@ -1,0 +1,310 @@
+// C-ABI of the hot path (include/drtvam_b200.h): handle management, argument
+// validation, kernel-family selection, host-buffer convenience calls.
+#include <atomic>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <vector>
+
+#include "../../include/drtvam_b200.h"
+#include "kernels.h"
+
+namespace drtvam {
+
+static std::atomic<uint64_t> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+static thread_local char g_error[512] = "";
+
+static int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_error, sizeof(g_error), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define CUDA_TRY(expr)                                                                       \
+    do {                                                                                     \
+        cudaError_t _e = (expr);                                                             \
+        if (_e != cudaSuccess)                                                               \
+            return fail(DRTVAM_E_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), \
+                        __FILE__, __LINE__);                                                 \
+    } while (0)
+
+struct Scratch {
+    void* ptr = nullptr;
+    size_t bytes = 0;
+    cudaError_t reserve(size_t n) {
+        if (n <= bytes) return cudaSuccess;
+        if (ptr) cudaFree(ptr);
+        ptr = nullptr; bytes = 0;
+        cudaError_t e = cudaMalloc(&ptr, n);
+        if (e == cudaSuccess) bytes = n;
+        return e;
+    }
+    void release() { if (ptr) cudaFree(ptr); ptr = nullptr; bytes = 0; }
+};
+
+}  // namespace drtvam
+
+using namespace drtvam;
+
+struct DrtvamScene {
+    int device = 0;
+    SceneParams P{};
+    float print_time = 1.f;
+    float* motion_dev = nullptr;
+    bool force_general = false;
+    Scratch host_io[3];      // device staging for the *_host calls
+    unsigned long long* counter_dev = nullptr;
+};
+
+namespace {
+
+struct DeviceGuard {
+    int prev = 0;
+    bool ok;
+    explicit DeviceGuard(int dev) { ok = cudaGetDevice(&prev) == cudaSuccess && cudaSetDevice(dev) == cudaSuccess; }
+    ~DeviceGuard() { cudaSetDevice(prev); }
+};
+
+float ray_weight(const DrtvamScene* s, uint64_t n_active, uint32_t spp) {
+    // pixel_area * n_active / (n_active * spp) * print_time
+    // (projector.py:187,164-165; integrators/common.py:111)
+    const float area = s->P.pixel_x * s->P.pixel_y;
+    const float inv_pdf = area * static_cast<float>(n_active);
+    return inv_pdf / static_cast<float>(n_active * static_cast<uint64_t>(spp)) * s->print_time;
+}
+
+int check_call(const DrtvamScene* s, uint64_t n_active, uint32_t& spp) {
+    if (!s) return fail(DRTVAM_E_INVALID, "scene handle is NULL");
+    if (spp == 0) return fail(DRTVAM_E_INVALID, "spp must be >= 1");
+    if (s->P.regular_sampling) spp = 1;  // integrators/common.py:49-51
+    const unsigned __int128 lanes = static_cast<unsigned __int128>(n_active) * spp;
+    if (lanes > (static_cast<unsigned __int128>(1) << 32))
+        return fail(DRTVAM_E_TOO_MANY_RAYS,
+                    "The total number of Monte Carlo samples required by this rendering task (%llu) exceeds "
+                    "2^32 = 4294967296. Please use fewer samples per pixel or render using multiple passes.",
+                    static_cast<unsigned long long>(lanes));
+    return DRTVAM_OK;
+}
+
+size_t film_elems(const DrtvamScene* s) {
+    return static_cast<size_t>(s->P.res[0]) * s->P.res[1] * s->P.res[2] * (s->P.surface_aware ? 2 : 1);
+}
+
+}  // namespace
+
+extern "C" {
+
+int drtvam_abi_version(void) { return DRTVAM_ABI_VERSION; }
+const char* drtvam_last_error(void) { return g_error; }
+uint64_t drtvam_launch_count(void) { return g_launches.load(); }
+
+int drtvam_scene_create(const DrtvamSceneDesc* d, int device, DrtvamScene** out) {
+    if (!d || !out) return fail(DRTVAM_E_INVALID, "NULL argument");
+    *out = nullptr;
+    if (d->struct_size != sizeof(DrtvamSceneDesc) || d->abi_version != DRTVAM_ABI_VERSION)
+        return fail(DRTVAM_E_INVALID, "ABI mismatch: desc size %u (want %zu), version %u (want %d)", d->struct_size,
+                    sizeof(DrtvamSceneDesc), d->abi_version, DRTVAM_ABI_VERSION);
+    if (d->proj_kind < 0 || d->proj_kind > 2) return fail(DRTVAM_E_INVALID, "unknown projector kind %d", d->proj_kind);
+    if (d->n_patterns <= 0 || d->res_x <= 0 || d->res_y <= 0)
+        return fail(DRTVAM_E_INVALID, "projector size must be positive");
+    if (d->n_surf <= 0 || d->n_surf > DRTVAM_MAX_SURFACES)
+        return fail(DRTVAM_E_INVALID, "surface count %d outside [1, %d]", d->n_surf, DRTVAM_MAX_SURFACES);
+    if (!(d->sigma_t > 0.f)) return fail(DRTVAM_E_INVALID, "medium extinction must be positive");
+    if (d->albedo < 0.f || d->albedo > 1.f) return fail(DRTVAM_E_INVALID, "albedo outside [0, 1]");
+    if (d->sensor_kind != DRTVAM_SENSOR_DDA && d->sensor_kind != DRTVAM_SENSOR_RATIO)
+        return fail(DRTVAM_E_INVALID, "unsupported sensor kind %d", d->sensor_kind);
+    if (d->sensor_kind == DRTVAM_SENSOR_RATIO && !(d->majorant > 0.f))
+        return fail(DRTVAM_E_INVALID, "ratio sensor needs a positive majorant");
+    if (!d->motion_analytic && !d->motion_table_host)
+        return fail(DRTVAM_E_INVALID, "motion table missing");
+    if (d->sample_time && !d->motion_analytic)
+        return fail(DRTVAM_E_INVALID, "sample_time needs an analytic motion");
+    int medium_surfaces = 0;
+    for (int i = 0; i < d->n_surf; ++i) {
+        const DrtvamSurface& s = d->surf[i];
+        if (s.kind != DRTVAM_SURF_CYLINDER && s.kind != DRTVAM_SURF_BOX)
+            return fail(DRTVAM_E_INVALID, "surface %d: unknown kind %d", i, s.kind);
+        if (s.bsdf < 0 || s.bsdf > 2) return fail(DRTVAM_E_INVALID, "surface %d: unknown bsdf %d", i, s.bsdf);
+        if (s.bsdf == DRTVAM_BSDF_DIELECTRIC && !(s.eta > 0.f))
+            return fail(DRTVAM_E_INVALID, "surface %d: dielectric needs eta > 0", i);
+        medium_surfaces += (s.interior_medium != 0) + (s.exterior_medium != 0);
+    }
+    if (medium_surfaces == 0)
+        return fail(DRTVAM_E_INVALID, "No printing medium found in the scene");  // common.py:36-37
+    for (int a = 0; a < 3; ++a) {
+        if (d->res[a] <= 0) return fail(DRTVAM_E_INVALID, "film resolution must be positive");
+        if (!(d->bbox_max[a] > d->bbox_min[a])) return fail(DRTVAM_E_INVALID, "empty sensor bounding box");
+    }
+
+    int n_dev = 0;
+    CUDA_TRY(cudaGetDeviceCount(&n_dev));
+    if (device < 0 || device >= n_dev) return fail(DRTVAM_E_INVALID, "device %d not available (%d devices)", device, n_dev);
+    DeviceGuard guard(device);
+    if (!guard.ok) return fail(DRTVAM_E_CUDA, "cudaSetDevice(%d) failed", device);
+
+    DrtvamScene* s = new (std::nothrow) DrtvamScene();
+    if (!s) return fail(DRTVAM_E_INVALID, "out of host memory");
+    s->device = device;
+    SceneParams& P = s->P;
+    P.proj_kind = d->proj_kind; P.n_patterns = d->n_patterns; P.res_x = d->res_x; P.res_y = d->res_y;
+    P.pixel_x = d->pixel_x; P.pixel_y = d->pixel_y;
+    P.aperture_radius = d->aperture_radius; P.focus_distance = d->focus_distance;
+    P.motion_analytic = d->motion_analytic; P.clockwise = d->clockwise; P.distance = d->distance;
+    P.max_depth = d->max_depth; P.rr_depth = d->rr_depth; P.transmission_only = d->transmission_only;
+    P.regular_sampling = d->regular_sampling; P.sample_time = d->sample_time;
+    s->print_time = d->print_time;
+    P.sigma_t = d->sigma_t; P.albedo = d->albedo; P.phase_kind = d->phase_kind; P.hg_g = d->hg_g;
+    P.n_surf = d->n_surf;
+    for (int i = 0; i < d->n_surf; ++i) {
+        const DrtvamSurface& a = d->surf[i];
+        Surface& b = P.surf[i];
+        b.kind = a.kind; b.bsdf = a.bsdf; b.interior_medium = a.interior_medium; b.exterior_medium = a.exterior_medium;
+        b.radius = a.radius; b.z0 = a.z0; b.z1 = a.z1; b.hx = a.hx; b.hy = a.hy; b.hz = a.hz; b.eta = a.eta;
+    }
+    for (int a = 0; a < 3; ++a) { P.bmin[a] = d->bbox_min[a]; P.bmax[a] = d->bbox_max[a]; P.res[a] = d->res[a]; }
+    P.surface_aware = d->surface_aware; P.sensor_kind = d->sensor_kind; P.majorant = d->majorant;
+    P.motion_table = nullptr;
+    if (d->motion_table_host) {
+        const size_t bytes = sizeof(float) * 12 * static_cast<size_t>(d->n_patterns);
+        cudaError_t e = cudaMalloc(&s->motion_dev, bytes);
+        if (e == cudaSuccess) e = cudaMemcpy(s->motion_dev, d->motion_table_host, bytes, cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) {
+            drtvam_scene_destroy(s);
+            return fail(DRTVAM_E_CUDA, "motion table upload failed: %s", cudaGetErrorString(e));
+        }
+        P.motion_table = s->motion_dev;
+    }
+    cudaError_t e = cudaMalloc(&s->counter_dev, sizeof(unsigned long long));
+    if (e != cudaSuccess) {
+        drtvam_scene_destroy(s);
+        return fail(DRTVAM_E_CUDA, "counter allocation failed: %s", cudaGetErrorString(e));
+    }
+    *out = s;
+    return DRTVAM_OK;
+}
+
+void drtvam_scene_destroy(DrtvamScene* s) {
+    if (!s) return;
+    DeviceGuard guard(s->device);
+    if (s->motion_dev) cudaFree(s->motion_dev);
+    if (s->counter_dev) cudaFree(s->counter_dev);
+    for (auto& b : s->host_io) b.release();
+    delete s;
+}
+
+int drtvam_scene_set_depth(DrtvamScene* s, int32_t max_depth, int32_t rr_depth) {
+    if (!s) return fail(DRTVAM_E_INVALID, "scene handle is NULL");
+    s->P.max_depth = max_depth;
+    s->P.rr_depth = rr_depth;
+    return DRTVAM_OK;
+}
+
+int drtvam_scene_force_general(DrtvamScene* s, int32_t on) {
+    if (!s) return fail(DRTVAM_E_INVALID, "scene handle is NULL");
+    s->force_general = on != 0;
+    return DRTVAM_OK;
+}
+
+int drtvam_scene_plan(DrtvamScene* s, uint64_t, uint32_t) {
+    if (!s) return fail(DRTVAM_E_INVALID, "scene handle is NULL");
+    return 0;
+}
+
+int drtvam_forward(DrtvamScene* s, const float* active_data, const uint32_t* active_pixels, uint64_t n_active,
+                   uint32_t spp, uint32_t seed, float out_scale, float* dose, int32_t zero_first, void* stream) {
+    if (int rc = check_call(s, n_active, spp)) return rc;
+    if (!dose || (n_active && (!active_data || !active_pixels))) return fail(DRTVAM_E_INVALID, "NULL buffer");
+    DeviceGuard guard(s->device);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (zero_first) CUDA_TRY(cudaMemsetAsync(dose, 0, sizeof(float) * film_elems(s), st));
+    if (n_active == 0) return DRTVAM_OK;
+    const float w = ray_weight(s, n_active, spp) * out_scale;
+    CUDA_TRY(launch_forward_general(s->P, active_data, active_pixels, n_active * spp, spp, seed, w, dose, st));
+    return DRTVAM_OK;
+}
+
+int drtvam_adjoint(DrtvamScene* s, const float* dose_grad, const uint32_t* active_pixels, uint64_t n_active,
+                   uint32_t spp, uint32_t seed, float in_scale, float* pattern_grad, void* stream) {
+    if (int rc = check_call(s, n_active, spp)) return rc;
+    if (n_active == 0) return DRTVAM_OK;
+    if (!dose_grad || !active_pixels || !pattern_grad) return fail(DRTVAM_E_INVALID, "NULL buffer");
+    DeviceGuard guard(s->device);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const float w = ray_weight(s, n_active, spp) * in_scale;
+    CUDA_TRY(launch_adjoint_general(s->P, dose_grad, active_pixels, n_active * spp, spp, seed, w, pattern_grad, st));
+    return DRTVAM_OK;
+}
+
+int drtvam_raygen(DrtvamScene* s, const uint32_t* active_pixels, uint64_t n_active, uint32_t spp, uint32_t seed,
+                  float* rays_out, void* stream) {
+    if (int rc = check_call(s, n_active, spp)) return rc;
+    if (n_active == 0) return DRTVAM_OK;
+    if (!active_pixels || !rays_out) return fail(DRTVAM_E_INVALID, "NULL buffer");
+    DeviceGuard guard(s->device);
+    CUDA_TRY(launch_raygen(s->P, active_pixels, n_active * spp, spp, seed, rays_out,
+                           static_cast<cudaStream_t>(stream)));
+    return DRTVAM_OK;
+}
+
+int drtvam_count_visits(DrtvamScene* s, const uint32_t* active_pixels, uint64_t n_active, uint32_t spp,
+                        uint32_t seed, uint64_t* out_host) {
+    if (int rc = check_call(s, n_active, spp)) return rc;
+    if (!out_host) return fail(DRTVAM_E_INVALID, "NULL buffer");
+    *out_host = 0;
+    if (n_active == 0) return DRTVAM_OK;
+    DeviceGuard guard(s->device);
+    CUDA_TRY(cudaMemset(s->counter_dev, 0, sizeof(unsigned long long)));
+    CUDA_TRY(launch_count_general(s->P, active_pixels, n_active * spp, spp, seed, s->counter_dev, nullptr));
+    unsigned long long n = 0;
+    CUDA_TRY(cudaMemcpy(&n, s->counter_dev, sizeof(n), cudaMemcpyDeviceToHost));
+    *out_host = n;
+    return DRTVAM_OK;
+}
+
+int drtvam_forward_host(DrtvamScene* s, const float* active_data_host, const uint32_t* active_pixels_host,
+                        uint64_t n_active, uint32_t spp, uint32_t seed, float out_scale, float* dose_host) {
+    if (!s) return fail(DRTVAM_E_INVALID, "scene handle is NULL");
+    if (!dose_host || (n_active && (!active_data_host || !active_pixels_host)))
+        return fail(DRTVAM_E_INVALID, "NULL buffer");
+    DeviceGuard guard(s->device);
+    const size_t nb = sizeof(float) * n_active, fb = sizeof(float) * film_elems(s);
+    CUDA_TRY(s->host_io[0].reserve(nb ? nb : 4));
+    CUDA_TRY(s->host_io[1].reserve(nb ? nb : 4));
+    CUDA_TRY(s->host_io[2].reserve(fb));
+    CUDA_TRY(cudaMemcpyAsync(s->host_io[0].ptr, active_data_host, nb, cudaMemcpyHostToDevice, nullptr));
+    CUDA_TRY(cudaMemcpyAsync(s->host_io[1].ptr, active_pixels_host, nb, cudaMemcpyHostToDevice, nullptr));
+    if (int rc = drtvam_forward(s, static_cast<float*>(s->host_io[0].ptr), static_cast<uint32_t*>(s->host_io[1].ptr),
+                                n_active, spp, seed, out_scale, static_cast<float*>(s->host_io[2].ptr), 1, nullptr))
+        return rc;
+    CUDA_TRY(cudaMemcpyAsync(dose_host, s->host_io[2].ptr, fb, cudaMemcpyDeviceToHost, nullptr));
+    CUDA_TRY(cudaStreamSynchronize(nullptr));
+    return DRTVAM_OK;
+}
+
+int drtvam_adjoint_host(DrtvamScene* s, const float* dose_grad_host, const uint32_t* active_pixels_host,
+                        uint64_t n_active, uint32_t spp, uint32_t seed, float in_scale, float* pattern_grad_host) {
+    if (!s) return fail(DRTVAM_E_INVALID, "scene handle is NULL");
+    if (n_active == 0) return DRTVAM_OK;
+    if (!dose_grad_host || !active_pixels_host || !pattern_grad_host) return fail(DRTVAM_E_INVALID, "NULL buffer");
+    DeviceGuard guard(s->device);
+    const size_t nb = sizeof(float) * n_active, fb = sizeof(float) * film_elems(s);
+    CUDA_TRY(s->host_io[0].reserve(nb));
+    CUDA_TRY(s->host_io[1].reserve(nb));
+    CUDA_TRY(s->host_io[2].reserve(fb));
+    CUDA_TRY(cudaMemcpyAsync(s->host_io[2].ptr, dose_grad_host, fb, cudaMemcpyHostToDevice, nullptr));
+    CUDA_TRY(cudaMemcpyAsync(s->host_io[1].ptr, active_pixels_host, nb, cudaMemcpyHostToDevice, nullptr));
+    if (int rc = drtvam_adjoint(s, static_cast<float*>(s->host_io[2].ptr), static_cast<uint32_t*>(s->host_io[1].ptr),
+                                n_active, spp, seed, in_scale, static_cast<float*>(s->host_io[0].ptr), nullptr))
+        return rc;
+    CUDA_TRY(cudaMemcpyAsync(pattern_grad_host, s->host_io[0].ptr, nb, cudaMemcpyDeviceToHost, nullptr));
+    CUDA_TRY(cudaStreamSynchronize(nullptr));
+    return DRTVAM_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,49 @@
+// Device-side scene parameters for the Dr.TVAM hot path (sm_100a).
+// Filled by abi.cu from DrtvamSceneDesc (include/drtvam_b200.h).
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace drtvam {
+
+constexpr int kMaxSurfaces = 8;
+
+struct Surface {
+    int kind;             // 0 cylinder about z, 1 origin-centred box
+    int bsdf;             // 0 null, 1 dielectric, 2 absorber
+    int interior_medium;  // printing medium inside
+    int exterior_medium;  // printing medium outside
+    float radius, z0, z1;
+    float hx, hy, hz;
+    float eta;            // int_ior / ext_ior
+};
+
+struct SceneParams {
+    // projector
+    int proj_kind, n_patterns, res_x, res_y;
+    float pixel_x, pixel_y, aperture_radius, focus_distance;
+    // motion
+    int motion_analytic, clockwise;
+    float distance;
+    const float* motion_table;  // device, [n_patterns][12] row-major 3x4
+    // integrator
+    int max_depth, rr_depth, transmission_only, regular_sampling, sample_time;
+    // medium
+    float sigma_t, albedo;
+    int phase_kind;
+    float hg_g;
+    // surfaces
+    int n_surf;
+    Surface surf[kMaxSurfaces];
+    // sensor / film
+    float bmin[3], bmax[3];
+    int res[3];
+    int surface_aware, sensor_kind;
+    float majorant;
+};
+
+struct Ray {
+    float ox, oy, oz, dx, dy, dz;
+};
+
+}  // namespace drtvam

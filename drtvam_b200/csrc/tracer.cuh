@@ -1,0 +1,131 @@
+// The bounce loop of one lane: interfaces, free flight, deposit, phase sampling.
+// Reference: VolumeIntegrator.sample (integrators/volume.py:136-282).
+#pragma once
+#include "dda.cuh"
+#include "device_scene.cuh"
+#include "raygen.cuh"
+#include "rng.cuh"
+#include "surfaces.cuh"
+
+namespace drtvam {
+
+// Branchless orthonormal basis around n (Duff et al.), as Mitsuba's Frame3f.
+__device__ __forceinline__ void frame_from_normal(float nx, float ny, float nz, float s[3], float t[3]) {
+    const float sign = copysignf(1.f, nz);
+    const float a = -1.f / (sign + nz);
+    const float b = nx * ny * a;
+    s[0] = copysignf(nx * nx * a, nz) + 1.f;
+    s[1] = copysignf(b, nz);
+    s[2] = copysignf(nx, -nz);
+    t[0] = b;
+    t[1] = ny * ny * a + sign;
+    t[2] = -ny;
+}
+
+// Samples the phase function around the propagation direction (dx,dy,dz)
+// (volume.py:252-260).  HG follows Mitsuba's hg.cpp, Rayleigh rayleigh.cpp.
+__device__ __forceinline__ void sample_phase(const SceneParams& P, float u1, float u2, Ray& ray) {
+    float cos_theta;
+    if (P.phase_kind == 2) {
+        const float g = P.hg_g;
+        const float sq = (1.f - g * g) / (1.f - g + 2.f * g * u1);
+        cos_theta = (1.f + g * g - sq * sq) / (2.f * g);
+        if (fabsf(g) < 1e-7f) cos_theta = 1.f - 2.f * u1;
+        cos_theta = -cos_theta;  // expressed in the frame of wi = -d
+    } else if (P.phase_kind == 1) {
+        const float z = 2.f * (2.f * u1 - 1.f), tmp = sqrtf(z * z + 1.f);
+        cos_theta = cbrtf(z + tmp) + cbrtf(z - tmp);
+    } else {
+        cos_theta = 1.f - 2.f * u1;
+    }
+    const float sin_theta = sqrtf(fmaxf(1.f - cos_theta * cos_theta, 0.f));
+    float sp, cp;
+    sincosf(6.28318530717958647692f * u2, &sp, &cp);
+    const float wi[3] = {-ray.dx, -ray.dy, -ray.dz};
+    float s[3], t[3];
+    frame_from_normal(wi[0], wi[1], wi[2], s, t);
+    const float a = sin_theta * cp, b = sin_theta * sp;
+    ray.dx = s[0] * a + t[0] * b + wi[0] * cos_theta;
+    ray.dy = s[1] * a + t[1] * b + wi[1] * cos_theta;
+    ray.dz = s[2] * a + t[2] * b + wi[2] * cos_theta;
+}
+
+// Walks one lane through the scene.  Every medium segment is handed to the
+// sensor with the throughput at its origin.  kScatter is the scalar
+// `has_scattering` branch of volume.py:154-155,199.
+template <bool kScatter, class Sink>
+__device__ __forceinline__ void trace_lane(const SceneParams& P, Ray ray, Sampler& rng, Sink& sink) {
+    const float st = P.sigma_t;
+    const float ss = st * P.albedo;
+    const float absorb = (st - ss) / st;  // sigma_a / sigma_t
+    float attenuation = 1.f;
+    bool active = true, in_medium = false;
+    const bool inside_target = false;  // target mesh crossings: surface-aware meshes are a later row
+    uint32_t depth = 0;
+
+    while (active) {
+        // Russian roulette (volume.py:181-186); the sample is always consumed
+        const float q = fminf(0.99f, attenuation);
+        const bool rr = depth > static_cast<uint32_t>(P.rr_depth);
+        const float u_rr = rng.next();
+        active = (u_rr < q) || !rr;
+        if (rr) attenuation *= 1.f / q;
+        active = active && (attenuation != 0.f);
+        if (!active) break;
+
+        const SurfaceHit H = nearest_surface(P, ray);
+        if (H.shape < 0) break;  // volume.py:193
+
+        float weight = 1.f;
+        float t_coll = INFINITY;
+        bool reached_surface = in_medium;
+        if (kScatter) {
+            const float xi = rng.next();  // unmasked draw, volume.py:200
+            if (in_medium) {
+                t_coll = -logf(1.f - xi) / st;
+                reached_surface = H.t < t_coll;
+                if (reached_surface) t_coll = INFINITY;
+                const float tr = expf(-fminf(t_coll, H.t) * st);
+                const float pdf = reached_surface ? tr : tr * st;
+                weight *= tr * (pdf > 0.f ? 1.f / pdf : 0.f);
+            }
+        }
+        const bool deposit = in_medium;  // active_medium | reached_surface
+        const bool collide = in_medium && !reached_surface;
+
+        if (deposit) {
+            // both collision and surface lanes deposit along the whole [0, si.t] (volume.py:216)
+            if (P.sensor_kind == 1) ratio_segment(P, ray, H.t, attenuation * absorb, inside_target, rng, sink);
+            else dda_segment(P, ray, H.t, attenuation * absorb, inside_target, sink);
+        }
+
+        bool enters_medium = false;
+        if (!collide) {
+            // interface: BSDF sample + spawn (volume.py:228-247)
+            const float s1 = rng.next();
+            (void)rng.next();
+            (void)rng.next();
+            const bool allow_reflection = !P.transmission_only && depth != 0;
+            weight *= cross_interface(P, H, allow_reflection, s1, ray);
+            if (!kScatter && reached_surface) weight *= expf(-st * H.t);  // volume.py:263
+            const Surface& S = P.surf[H.shape];
+            const bool outward = (ray.dx * H.nx + ray.dy * H.ny + ray.dz * H.nz) > 0.f;
+            enters_medium = outward ? (S.exterior_medium != 0) : (S.interior_medium != 0);  // volume.py:268
+        } else {
+            // medium collision: albedo weight + phase sampling (volume.py:249-261)
+            weight *= ss;
+            (void)rng.next();
+            const float u1 = rng.next(), u2 = rng.next();
+            ray.ox = fmaf(ray.dx, t_coll, ray.ox);
+            ray.oy = fmaf(ray.dy, t_coll, ray.oy);
+            ray.oz = fmaf(ray.dz, t_coll, ray.oz);
+            sample_phase(P, u1, u2, ray);
+        }
+        attenuation *= weight;
+        in_medium = collide || enters_medium;
+        depth += 1;
+        active = depth < static_cast<uint32_t>(P.max_depth);
+    }
+}
+
+}  // namespace drtvam

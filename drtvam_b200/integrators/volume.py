@@ -1,0 +1,106 @@
+"""Volume integrator: the forward projection ``A p`` and its adjoint ``A^T g``.
+Mirrors ``src/drtvam/integrators/volume.py``: ``render`` (:18-56),
+``render_forward`` (:58-95), ``render_backward`` (:97-134).  The bounce loop
+``sample`` (:136-282) is ``csrc/tracer.cuh`` / ``csrc/planar_kernels.cu``.
+"""
+from __future__ import annotations
+
+import torch
+
+from .. import _lib
+from .common import TVAMIntegrator
+
+
+def _inv_volume(sensor, scene):
+    """(scalar, tensor-or-None): 1 / voxel volume, 0 where the volume is 0 (volume.py:41-42)."""
+    vol = sensor.compute_volume(scene)
+    if isinstance(vol, torch.Tensor):
+        inv = torch.where(vol != 0, 1.0 / vol, torch.zeros_like(vol))
+        return 1.0, inv
+    return (1.0 / vol if vol != 0 else 0.0), None
+
+
+def _sensor_of(scene, sensor):
+    if isinstance(sensor, int):
+        return scene.sensors()[sensor]
+    return sensor
+
+
+def _check_emitters(scene):
+    if len(scene.emitters()) == 0:
+        raise Exception("No projector found in the scene")
+    if len(scene.emitters()) > 1:
+        raise Exception("The scene contains more than one projector. Only one is supported")
+
+
+class VolumeIntegrator(TVAMIntegrator):
+    def to_string(self):
+        return ('VolumeIntegrator[\n'
+                f'    {self.print_time=},\n'
+                f'    {self.transmission_only=},\n'
+                f'    {self.sample_time=},\n'
+                f'    {self.max_depth=},\n'
+                f'    {self.rr_depth=},\n'
+                ']')
+
+    __repr__ = to_string
+
+    def _project(self, scene, sensor, seed, spp, active_data):
+        sensor = _sensor_of(scene, sensor)
+        projector = scene.emitters()[0]
+        spp, _ = self.prepare(projector, seed, spp)
+        handle = scene.handle(self, sensor)
+        inv_scalar, inv_tensor = _inv_volume(sensor, scene)
+        film = sensor.film()
+        film.data = torch.empty(film.shape, device=projector.active_data.device, dtype=torch.float32)
+        data = active_data.detach().to(torch.float32).contiguous()
+        pixels = projector.active_pixels
+        if data.numel() != pixels.numel():
+            raise ValueError(f"[{projector.__class__.__name__}] active_data and active_pixels must have the same length.")
+        lib = _lib.load()
+        _lib.check(lib.drtvam_forward(handle, data.data_ptr(), pixels.data_ptr(), data.numel(), spp,
+                                      seed & 0xFFFFFFFF, inv_scalar, film.data.data_ptr(), 1,
+                                      torch.cuda.current_stream(film.data.device).cuda_stream))
+        scene.reduce_dose(film.data)
+        out = film.data
+        if inv_tensor is not None:
+            out = out * inv_tensor
+        return out
+
+    def render(self, scene, sensor=0, seed: int = 0, spp: int = 0, develop: bool = True, evaluate: bool = True):
+        """Primal A p with p = projector.active_data; returns (resz, resy, resx, C)."""
+        _check_emitters(scene)
+        with torch.no_grad():
+            return self._project(scene, sensor, seed, spp, scene.emitters()[0].active_data)
+
+    def render_forward(self, scene, params=None, sensor=0, seed: int = 0, spp: int = 0, tangent=None):
+        """Forward-mode derivative: A is linear in the patterns, so the JVP is A
+        applied to the tangent (volume.py:58-95)."""
+        _check_emitters(scene)
+        if tangent is None:
+            raise ValueError("render_forward needs the tangent of projector.active_data")
+        with torch.no_grad():
+            return self._project(scene, sensor, seed, spp, tangent)
+
+    def render_backward(self, scene, params, grad_in, sensor=0, seed: int = 0, spp: int = 0):
+        """Adjoint A^T grad_in; returns d loss / d projector.active_data."""
+        _check_emitters(scene)
+        sensor = _sensor_of(scene, sensor)
+        projector = scene.emitters()[0]
+        spp, _ = self.prepare(projector, seed, spp)
+        handle = scene.handle(self, sensor)
+        inv_scalar, inv_tensor = _inv_volume(sensor, scene)
+        film = sensor.film()
+        g = grad_in.detach().to(torch.float32)
+        if tuple(g.shape) != tuple(film.shape):
+            g = g.reshape(film.shape)
+        if inv_tensor is not None:
+            g = g * inv_tensor
+        g = g.contiguous()
+        pixels = projector.active_pixels
+        out = torch.empty(pixels.numel(), device=g.device, dtype=torch.float32)
+        lib = _lib.load()
+        _lib.check(lib.drtvam_adjoint(handle, g.data_ptr(), pixels.data_ptr(), pixels.numel(), spp,
+                                      seed & 0xFFFFFFFF, inv_scalar, out.data_ptr(),
+                                      torch.cuda.current_stream(g.device).cuda_stream))
+        return out

@@ -1,0 +1,125 @@
+"""Objective functions on the dose volume.  Mirrors ``src/drtvam/loss.py``:
+``Loss.__call__`` shape handling and surface-aware weighting (:28-59),
+``L2Loss`` (:63-80), ``ThresholdedLoss`` (:82-132), registry (:135-138).
+torch elementwise + reductions; autograd supplies d loss / d dose.
+"""
+from __future__ import annotations
+
+import torch
+
+
+def relu(x):
+    return torch.clamp_min(x, 0)
+
+
+class Loss:
+    def __init__(self, props):
+        reduction = props.get('reduction', 'sum')
+        if reduction == 'sum':
+            self.reduction = torch.sum
+        elif reduction == 'mean':
+            self.reduction = torch.mean
+        else:
+            raise ValueError(f"Invalid reduction method: '{reduction}'.")
+        # sum of the (angle-sharded) pattern term over ranks; identity on one GPU
+        self.pattern_allsum = None
+
+    def eval_in(self, x):
+        raise NotImplementedError
+
+    def eval_out(self, x):
+        raise NotImplementedError
+
+    def eval_sparsity(self, patterns):
+        raise NotImplementedError
+
+    def eval(self, x, target, patterns):
+        raise NotImplementedError
+
+    def _reduce_patterns(self, lp):
+        if not isinstance(lp, torch.Tensor):
+            return lp
+        if self.pattern_allsum is None:
+            return self.reduction(lp)
+        if self.reduction is torch.mean:
+            n = self.pattern_allsum(torch.tensor(float(lp.numel()), device=lp.device))
+            return self.pattern_allsum(lp.sum()) / n
+        return self.pattern_allsum(lp.sum())
+
+    def __call__(self, x, target, patterns):
+        if x.shape != target.shape:
+            if x.dim() == target.dim() + 1 and x.shape[-1] == 1:
+                target = target[..., None]
+            else:
+                raise ValueError(f"Input and target shapes do not match: {tuple(x.shape)} != {tuple(target.shape)}")
+
+        if target.shape[-1] == 1:  # binary or grayscale target
+            loss, loss_patterns = self.eval(x, target, patterns)
+        elif target.shape[-1] == 2:  # surface-aware: fractional in/out sub-volumes
+            tot = target[..., 0] + target[..., 1]
+            w_in = target[..., 0] / tot
+            w_out = target[..., 1] / tot
+            loss = w_in * self.eval_in(x[..., 0]) + w_out * self.eval_out(x[..., 1])
+            loss_patterns = self.eval_sparsity(patterns)
+        else:
+            raise ValueError(f"[Loss] Received tensors of invalid shape: {tuple(target.shape)}. "
+                             "The last dimension should be either 1 or 2.")
+        # the two terms have different shapes, hence separate reductions
+        return self.reduction(loss) + self._reduce_patterns(loss_patterns)
+
+
+class L2Loss(Loss):
+    def __init__(self, props):
+        super().__init__(props)
+        self.M = props.get('M', 4)
+        self.weight_sparsity = props.get('weight_sparsity', 0)
+
+    def eval_in(self, x):
+        return torch.square(x - 1.)
+
+    def eval_out(self, x):
+        return torch.square(x)
+
+    def eval(self, x, target, patterns):
+        return torch.square(x - target), 0 * patterns
+
+    def eval_sparsity(self, patterns):
+        return patterns ** self.M * self.weight_sparsity
+
+
+class ThresholdedLoss(Loss):
+    """Thresholded loss following Wechsler et al. 2024:
+    w_obj relu(tu - x)^K + w_lim relu(x - 1)^K inside the object,
+    w_void relu(x - tl)^K outside, |p|^M w_sparsity on the patterns."""
+
+    def __init__(self, props):
+        super().__init__(props)
+        self.K = props.get('K', 2)
+        self.M = props.get('M', 4)
+        self.tl = props.get('tl', 0.9)
+        self.tu = props.get('tu', 0.95)
+        self.weight_object = props.get('weight_object', 1)
+        self.weight_void = props.get('weight_void', 1)
+        self.weight_limit = props.get('weight_limit', 1)
+        self.weight_sparsity = props.get('weight_sparsity', 0)
+        if self.tl >= self.tu:
+            raise ValueError(f"[ThresholdedLoss] Lower threshold ({self.tl}) must be smaller than upper threshold ({self.tu})")
+
+    def eval_in(self, x):
+        return self.weight_object * relu(self.tu - x) ** self.K + self.weight_limit * relu(x - 1.) ** self.K
+
+    def eval_out(self, x):
+        return self.weight_void * relu(x - self.tl) ** self.K
+
+    def eval_sparsity(self, patterns):
+        return torch.abs(patterns) ** self.M * self.weight_sparsity
+
+    def eval(self, x, target, patterns):
+        # target is a binary inside/outside mask
+        return torch.where(target > 0, self.eval_in(x), self.eval_out(x)), self.eval_sparsity(patterns)
+
+
+losses = {
+    'l2': L2Loss,
+    'threshold': ThresholdedLoss,
+}

@@ -1,0 +1,72 @@
+"""Angle sharding across GPUs (one process per GPU).
+
+``A = sum_k A_k`` over projection angles ``k``: rank ``r`` owns a contiguous
+range of angles, traces only those, and one ``all_reduce(SUM)`` of the dose
+volume follows each forward projection.  The adjoint needs no collective: the
+dose gradient is replicated and pattern gradients stay sharded.  L-BFGS dot
+products over the sharded pattern vectors become local dot + scalar
+all-reduce (``lbfgs.LinearLBFGS(dot=...)``).
+"""
+from __future__ import annotations
+
+import torch
+
+
+def angle_ranges(counts, world_size: int):
+    """Split angles [0, n) into `world_size` contiguous ranges balanced by the
+    number of active pixels per angle.  Returns a list of (k_lo, k_hi)."""
+    n = len(counts)
+    total = float(sum(counts))
+    bounds = [0]
+    acc = 0.0
+    k = 0
+    for r in range(1, world_size):
+        goal = total * r / world_size
+        while k < n and acc + counts[k] * 0.5 < goal:
+            acc += counts[k]
+            k += 1
+        bounds.append(k)
+    bounds.append(n)
+    return [(bounds[i], bounds[i + 1]) for i in range(world_size)]
+
+
+def shard_bounds(active_pixels: torch.Tensor, n_patterns: int, pixels_per_pattern: int, rank: int, world_size: int):
+    """Index range [lo, hi) of `active_pixels` (sorted by pattern) owned by `rank`."""
+    if world_size == 1:
+        return 0, int(active_pixels.numel())
+    k = (active_pixels.to(torch.int64) & 0xFFFFFFFF) // pixels_per_pattern
+    if k.numel() > 1 and bool((k[1:] < k[:-1]).any()):
+        raise ValueError("active_pixels must be sorted by pattern index to shard by angle")
+    counts = torch.bincount(k, minlength=n_patterns).tolist()
+    k_lo, k_hi = angle_ranges(counts, world_size)[rank]
+    lo = int(sum(counts[:k_lo]))
+    hi = int(sum(counts[:k_hi]))
+    return lo, hi
+
+
+def make_dot(group=None, world_size: int = 1):
+    """Dot product over angle-sharded vectors: local dot + scalar all-reduce."""
+    if world_size == 1:
+        return lambda a, b: torch.dot(a.reshape(-1), b.reshape(-1))
+    import torch.distributed as dist
+
+    def dot(a, b):
+        v = torch.dot(a.reshape(-1), b.reshape(-1))
+        dist.all_reduce(v, op=dist.ReduceOp.SUM, group=group)
+        return v
+
+    return dot
+
+
+def make_sum(group=None, world_size: int = 1):
+    """Sum of a scalar tensor over ranks (sparsity term of the loss)."""
+    if world_size == 1:
+        return lambda v: v
+    import torch.distributed as dist
+
+    def allsum(v):
+        v = v.clone()
+        dist.all_reduce(v, op=dist.ReduceOp.SUM, group=group)
+        return v
+
+    return allsum

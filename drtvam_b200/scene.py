@@ -1,0 +1,305 @@
+"""Scene container, parameter traversal and the differentiable ``render`` entry
+point -- the analogue of ``mi.load_dict`` / ``mi.traverse`` / ``mi.render`` as
+the reference uses them (``optimize.py:90-91,141,157-159,216,294,328``).
+
+``render`` wraps the C-ABI calls in a ``torch.autograd.Function`` whose forward
+is ``drtvam_forward`` and whose backward is ``drtvam_adjoint`` -- the
+counterpart of Mitsuba's ``_RenderOp``.
+
+Multi-GPU: when ``scene.shard(rank, world)`` has been called, the projector
+holds only this rank's projection angles, every forward projection is followed
+by one ``all_reduce(SUM)`` of the dose volume, and the adjoint stays local.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, List, Optional
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._scene import (PHASE_KINDS, PROJ_KINDS, SENSOR_KINDS, SceneDesc, SurfaceDesc, surface_from_shape_dict)
+from .integrators import integrators as _integrators
+from .motion import CircularMotion
+from .projector import TVAMProjector, projectors
+from .sensor import VolumetricSensor, sensors as _sensors
+
+
+def sample_tea_32(v0: int, v1: int, rounds: int = 4):
+    """Tiny Encryption Algorithm hash Mitsuba uses to derive seed_grad."""
+    s = 0
+    v0 &= 0xFFFFFFFF
+    v1 &= 0xFFFFFFFF
+    for _ in range(rounds):
+        s = (s + 0x9e3779b9) & 0xFFFFFFFF
+        v0 = (v0 + ((((v1 << 4) & 0xFFFFFFFF) + 0xa341316c) ^ ((v1 + s) & 0xFFFFFFFF) ^ ((v1 >> 5) + 0xc8013ea4))) & 0xFFFFFFFF
+        v1 = (v1 + ((((v0 << 4) & 0xFFFFFFFF) + 0xad90777d) ^ ((v0 + s) & 0xFFFFFFFF) ^ ((v0 >> 5) + 0x7e95761e))) & 0xFFFFFFFF
+    return v0, v1
+
+
+class Scene:
+    def __init__(self, projector: TVAMProjector, sensors: Dict[str, VolumetricSensor],
+                 surfaces: List[SurfaceDesc], medium: dict, target: Optional[dict] = None,
+                 integrator=None):
+        self.projector = projector
+        self._sensors = sensors
+        self.surfaces = surfaces
+        self.medium = medium
+        self.target = target
+        self.default_integrator = integrator
+        self._handles = {}
+        self._keepalive = {}
+        self.group = None      # torch.distributed process group when angle-sharded
+        self.world_size = 1
+        self.rank = 0
+        self.force_general = False
+
+    # -- Mitsuba-like accessors --------------------------------------------
+    def emitters(self):
+        return [self.projector]
+
+    def sensors(self):
+        return list(self._sensors.values())
+
+    def sensor(self, name):
+        return self._sensors[name]
+
+    def integrator(self):
+        return self.default_integrator
+
+    # -- lowering ----------------------------------------------------------
+    def describe(self, integrator, sensor) -> SceneDesc:
+        p = self.projector
+        d = SceneDesc()
+        d.proj_kind = PROJ_KINDS[p.kind]
+        d.n_patterns, d.res_x, d.res_y = p.n_patterns, p.res[0], p.res[1]
+        d.pixel_x, d.pixel_y = p.pixel_size
+        d.aperture_radius, d.focus_distance = float(p.aperture_radius), float(p.focus_distance)
+        circular = isinstance(p.motion, CircularMotion)
+        if integrator.sample_time:
+            if not circular:
+                raise NotImplementedError("sample_time needs an analytic motion; only 'circular' has a device evaluator")
+            d.motion_analytic = 1
+        if circular:
+            d.clockwise = int(bool(p.motion.clockwise))
+            d.distance = float(p.motion.distance)
+        d.motion_table = p.motion_table()
+        d.max_depth, d.rr_depth = int(integrator.max_depth), int(integrator.rr_depth)
+        d.transmission_only = int(bool(integrator.transmission_only))
+        d.regular_sampling = int(bool(integrator.regular_sampling))
+        d.sample_time = int(bool(integrator.sample_time))
+        d.print_time = float(integrator.print_time)
+        d.sigma_t = float(self.medium['sigma_t'])
+        d.albedo = float(self.medium.get('albedo', 0.0))
+        phase = self.medium.get('phase') or {'type': 'isotropic'}
+        if phase['type'] not in PHASE_KINDS:
+            raise NotImplementedError(f"phase function '{phase['type']}' has no kernel")
+        d.phase_kind = PHASE_KINDS[phase['type']]
+        d.hg_g = float(phase.get('g', 0.0))
+        d.surfaces = list(self.surfaces)
+        d.bbox_min = tuple(float(x) for x in sensor.bbox_min)
+        d.bbox_max = tuple(float(x) for x in sensor.bbox_max)
+        d.res = tuple(int(x) for x in sensor.resolution())
+        d.surface_aware = int(bool(sensor.film().surface_aware))
+        if sensor.kind not in SENSOR_KINDS:
+            raise NotImplementedError(f"sensor '{sensor.kind}' has no kernel")
+        d.sensor_kind = SENSOR_KINDS[sensor.kind]
+        d.majorant = float(getattr(sensor, 'majorant', 0.0))
+        return d
+
+    def handle(self, integrator, sensor):
+        """C handle for (integrator options, sensor); depth changes reuse it."""
+        key = (id(sensor), bool(integrator.transmission_only), bool(integrator.regular_sampling),
+               bool(integrator.sample_time), float(integrator.print_time))
+        lib = _lib.load()
+        h = self._handles.get(key)
+        if h is None:
+            desc = self.describe(integrator, sensor)
+            cdesc, keep = desc.to_c()
+            out = C.c_void_p()
+            dev = self.projector.active_data.device
+            if dev.type != 'cuda':
+                raise RuntimeError("drtvam_b200 has no CPU path: scene tensors must live on a CUDA device")
+            _lib.check(lib.drtvam_scene_create(C.byref(cdesc), dev.index or 0, C.byref(out)))
+            h = out.value
+            self._handles[key] = h
+            self._keepalive[key] = keep
+        _lib.check(lib.drtvam_scene_set_depth(h, int(integrator.max_depth), int(integrator.rr_depth)))
+        _lib.check(lib.drtvam_scene_force_general(h, int(self.force_general)))
+        return h
+
+    def close(self):
+        if self._handles:
+            lib = _lib.load()
+            for h in self._handles.values():
+                lib.drtvam_scene_destroy(h)
+        self._handles.clear()
+        self._keepalive.clear()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- multi-GPU ---------------------------------------------------------
+    def shard(self, rank: int, world_size: int, group=None):
+        """Keep only this rank's projection angles (contiguous range balanced
+        by active-pixel count)."""
+        from .parallel import shard_bounds
+        p = self.projector
+        lo, hi = shard_bounds(p.active_pixels, p.n_patterns, p.res[0] * p.res[1], rank, world_size)
+        p.active_pixels = p.active_pixels[lo:hi].contiguous()
+        p.active_data = p.active_data[lo:hi].contiguous()
+        self.rank, self.world_size, self.group = rank, world_size, group
+        return lo, hi
+
+    def reduce_dose(self, dose: torch.Tensor):
+        if self.world_size > 1:
+            import torch.distributed as dist
+            dist.all_reduce(dose, op=dist.ReduceOp.SUM, group=self.group)
+
+
+class Params(dict):
+    """What ``mi.traverse(scene)`` returns for this path: the keys the
+    reference touches (``projector.active_data`` differentiable,
+    ``projector.active_pixels``; optimize.py:141,157-159)."""
+
+    def __init__(self, scene: Scene):
+        super().__init__()
+        self.scene = scene
+        super().__setitem__('projector.active_data', scene.projector.active_data)
+        super().__setitem__('projector.active_pixels', scene.projector.active_pixels)
+
+    def update(self, values=None):
+        if values is not None:
+            for k, v in dict(values).items():
+                if k in self:
+                    self[k] = v
+        p = self.scene.projector
+        data = self['projector.active_data']
+        pixels = self['projector.active_pixels']
+        if not isinstance(data, torch.Tensor):
+            data = torch.as_tensor(np.asarray(data, np.float32))
+        if not isinstance(pixels, torch.Tensor):
+            pixels = torch.as_tensor(np.asarray(pixels, np.int64))
+        dev = p.active_data.device
+        p.active_data = data.to(dev, torch.float32).reshape(-1)
+        if pixels.dtype != torch.int32:
+            pixels = pixels.to(torch.int64).to(torch.int32)
+        p.active_pixels = pixels.to(dev).reshape(-1).contiguous()
+        super().__setitem__('projector.active_data', p.active_data)
+        super().__setitem__('projector.active_pixels', p.active_pixels)
+        p.parameters_changed()
+        return []
+
+
+def traverse(scene: Scene) -> Params:
+    return Params(scene)
+
+
+def load_dict(scene_dict: dict, device=None) -> Scene:
+    """Builds a Scene from the dict ``optimize.load_scene`` assembles
+    (optimize.py:61-77): one projector, ``sensor`` [+ ``final_sensor``], the
+    container shapes, ``printing_medium`` and (optionally) ``target``."""
+    if scene_dict.get('type', 'scene') != 'scene':
+        raise ValueError("load_dict expects a dict of type 'scene'")
+    projector = None
+    sensors: Dict[str, VolumetricSensor] = {}
+    surfaces: List[SurfaceDesc] = []
+    medium = None
+    target = None
+    integrator = None
+    for name, entry in scene_dict.items():
+        if not isinstance(entry, dict) and not isinstance(entry, (TVAMProjector, VolumetricSensor)):
+            continue
+        if isinstance(entry, TVAMProjector):
+            projector = entry
+            continue
+        if isinstance(entry, VolumetricSensor):
+            sensors[name] = entry
+            continue
+        t = entry.get('type')
+        if t in projectors:
+            if projector is not None:
+                raise Exception("The scene contains more than one projector. Only one is supported")
+            projector = projectors[t](dict(entry, device=device) if device is not None else entry)
+        elif t in _sensors:
+            props = dict(entry, id=name)
+            if device is not None:
+                props['device'] = device
+            sensors[name] = _sensors[t](props)
+        elif t == 'delta':
+            raise NotImplementedError("the delta-tracking sensor has no kernel yet")
+        elif t in _integrators:
+            integrator = _integrators[t](entry)
+        elif t == 'homogeneous':
+            if medium is not None and name != 'printing_medium':
+                raise ValueError("There is more than one medium in the scene. Only one is supported")
+            medium = entry
+        elif t in ('cylinder', 'cube'):
+            inline = entry.get('interior') if isinstance(entry.get('interior'), dict) else None
+            if inline is not None and inline.get('type') == 'homogeneous':
+                if medium is not None:
+                    raise ValueError("There is more than one medium in the scene. Only one is supported")
+                medium = inline
+            surfaces.append(surface_from_shape_dict(name, entry))
+        elif t in ('ply', 'obj'):
+            if name == 'target':
+                from .utils import load_mesh
+                from .transform import Transform4f
+                verts, tris = load_mesh(entry['filename'])
+                tw = entry.get('to_world')
+                if tw is not None:
+                    verts = Transform4f(tw) @ verts
+                target = dict(entry, vertices=np.asarray(verts, np.float64), triangles=tris)
+            else:
+                raise NotImplementedError(
+                    f"shape '{name}' is a triangle mesh; mesh vials / occluders need the BVH row (SURVEY.md 8(f))")
+        else:
+            raise NotImplementedError(f"scene entry '{name}' of type '{t}' is not supported")
+    if projector is None:
+        raise Exception("No projector found in the scene")
+    if medium is None:
+        raise ValueError("No printing medium found in the scene")
+    if not sensors:
+        raise ValueError("No sensor found in the scene")
+    return Scene(projector, sensors, surfaces, medium, target, integrator)
+
+
+class _RenderOp(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, active_data, scene, integrator, sensor, spp, spp_grad, seed, seed_grad):
+        ctx.args = (scene, integrator, sensor, spp_grad, seed_grad)
+        return integrator._project(scene, sensor, seed, spp, active_data)
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        scene, integrator, sensor, spp_grad, seed_grad = ctx.args
+        g = integrator.render_backward(scene, None, grad_out, sensor, seed_grad, spp_grad)
+        return g, None, None, None, None, None, None, None
+
+
+def render(scene: Scene, params: Optional[Params] = None, sensor=0, integrator=None,
+           seed: int = 0, seed_grad: int = 0, spp: int = 0, spp_grad: int = 0) -> torch.Tensor:
+    """Differentiable forward projection; same signature as ``mi.render``."""
+    if integrator is None:
+        integrator = scene.integrator()
+        if integrator is None:
+            raise ValueError("No integrator specified")
+    if isinstance(sensor, int):
+        sensor = scene.sensors()[sensor]
+    if spp_grad == 0:
+        spp_grad = spp
+    if seed_grad == 0:
+        # de-correlate primal and adjoint samples like mi.render (App. A.1)
+        seed_grad = sample_tea_32(seed, 1)[0]
+    data = params['projector.active_data'] if params is not None else scene.projector.active_data
+    if params is not None and data is not scene.projector.active_data:
+        params.update()
+        data = params['projector.active_data']
+    if torch.is_grad_enabled() and data.requires_grad:
+        return _RenderOp.apply(data, scene, integrator, sensor, spp, spp_grad, seed, seed_grad)
+    with torch.no_grad():
+        return integrator._project(scene, sensor, seed, spp, data)

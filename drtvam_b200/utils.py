@@ -1,0 +1,255 @@
+"""Reporting and one-shot helpers around the hot path.  Mirrors
+``src/drtvam/utils.py``: ``iou_loss`` (:8-11), ``reshape_grid`` (:13-27),
+``save_img`` / ``save_vol`` (:29-46, EXR via a minimal writer instead of
+``mi.Bitmap``), ``discretize`` (:83-128).  Mesh IO (binary/ascii PLY) stands in
+for Mitsuba's ``ply`` shape loader.
+"""
+from __future__ import annotations
+
+import os
+import struct
+
+import numpy as np
+import torch
+
+
+def iou_loss(pred, target, threshold=0.9):
+    obj_mask = target.reshape(-1) > 0.
+    thresholded = pred.reshape(-1) > threshold
+    return (thresholded & obj_mask).sum().to(torch.float32) / (thresholded | obj_mask).sum()
+
+
+def reshape_grid(array):
+    if len(array.shape) == 3:
+        n, h, w = array.shape
+        c = 1
+    elif len(array.shape) == 4:
+        n, h, w, c = array.shape
+    else:
+        raise ValueError(f"Invalid array shape: {array.shape}")
+    rows = int(np.ceil(np.sqrt(n)))
+    # pad so that the slices tile a square grid
+    array_new = np.zeros((rows ** 2, h, w, c))
+    array_new[:n] = np.asarray(array).reshape(n, h, w, c)
+    return array_new.reshape((rows, rows, h, w, c)).swapaxes(1, 2).reshape((rows * h, rows * w, c))
+
+
+def write_exr(path, img):
+    """Uncompressed scanline OpenEXR, float32 channels (Y, or R/G/B[/A])."""
+    img = np.asarray(img, np.float32)
+    if img.ndim == 2:
+        img = img[..., None]
+    h, w, c = img.shape
+    names = {1: ["Y"], 2: ["A", "Y"], 3: ["B", "G", "R"], 4: ["A", "B", "G", "R"]}[c]
+    order = {1: [0], 2: [1, 0], 3: [2, 1, 0], 4: [3, 2, 1, 0]}[c]
+
+    def attr(name, typ, data):
+        return name.encode() + b"\0" + typ.encode() + b"\0" + struct.pack("<i", len(data)) + data
+
+    chlist = b"".join(n.encode() + b"\0" + struct.pack("<iBBBBii", 2, 0, 0, 0, 0, 1, 1) for n in names) + b"\0"
+    box = struct.pack("<iiii", 0, 0, w - 1, h - 1)
+    header = (attr("channels", "chlist", chlist) + attr("compression", "compression", b"\0") +
+              attr("dataWindow", "box2i", box) + attr("displayWindow", "box2i", box) +
+              attr("lineOrder", "lineOrder", b"\0") + attr("pixelAspectRatio", "float", struct.pack("<f", 1.0)) +
+              attr("screenWindowCenter", "v2f", struct.pack("<ff", 0.0, 0.0)) +
+              attr("screenWindowWidth", "float", struct.pack("<f", 1.0)) + b"\0")
+    magic = struct.pack("<ii", 20000630, 2)
+    line_bytes = w * 4 * c
+    table_pos = len(magic) + len(header)
+    first = table_pos + 8 * h
+    offsets = [first + y * (8 + line_bytes) for y in range(h)]
+    os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
+    with open(path, "wb") as f:
+        f.write(magic)
+        f.write(header)
+        f.write(struct.pack(f"<{h}Q", *offsets))
+        for y in range(h):
+            f.write(struct.pack("<ii", y, line_bytes))
+            for ci in order:
+                f.write(np.ascontiguousarray(img[y, :, ci]).tobytes())
+
+
+def save_img(img, path):
+    if isinstance(img, torch.Tensor):
+        img = img.detach().cpu().numpy()
+    if img.ndim not in (2, 3):
+        raise ValueError("Invalid image shape")
+    write_exr(path, img)
+
+
+def save_vol(vol, path):
+    if isinstance(vol, torch.Tensor):
+        vol = vol.detach().cpu().numpy()
+    elif not isinstance(vol, np.ndarray):
+        raise ValueError(f"Invalid volume type: '{type(vol)}'")
+    write_exr(path, reshape_grid(vol))
+
+
+# ---------------------------------------------------------------------- meshes
+
+_PLY_TYPES = {"char": "i1", "uchar": "u1", "short": "i2", "ushort": "u2", "int": "i4", "uint": "u4",
+              "float": "f4", "double": "f8", "int8": "i1", "uint8": "u1", "int16": "i2", "uint16": "u2",
+              "int32": "i4", "uint32": "u4", "float32": "f4", "float64": "f8"}
+
+
+def load_ply(path):
+    """Returns (vertices [V,3] float64, triangles [F,3] int64); polygons are fan-triangulated."""
+    with open(path, "rb") as f:
+        raw = f.read()
+    end = raw.index(b"end_header") + len(b"end_header")
+    end = raw.index(b"\n", end) + 1
+    lines = raw[:end].decode("ascii", "replace").splitlines()
+    fmt = None
+    elements = []
+    for ln in lines:
+        tok = ln.split()
+        if not tok:
+            continue
+        if tok[0] == "format":
+            fmt = tok[1]
+        elif tok[0] == "element":
+            elements.append({"name": tok[1], "count": int(tok[2]), "props": []})
+        elif tok[0] == "property":
+            if tok[1] == "list":
+                elements[-1]["props"].append(("list", tok[2], tok[3], tok[4]))
+            else:
+                elements[-1]["props"].append(("scalar", tok[1], tok[2]))
+    body = raw[end:]
+    verts, faces = None, []
+    if fmt == "ascii":
+        toks = body.split()
+        pos = 0
+        for el in elements:
+            rows = []
+            for _ in range(el["count"]):
+                row = []
+                for p in el["props"]:
+                    if p[0] == "scalar":
+                        row.append(float(toks[pos])); pos += 1
+                    else:
+                        n = int(toks[pos]); pos += 1
+                        row.append([int(t) for t in toks[pos:pos + n]]); pos += n
+                rows.append(row)
+            if el["name"] == "vertex":
+                names = [p[2] for p in el["props"]]
+                ix = [names.index(a) for a in "xyz"]
+                verts = np.array([[r[i] for i in ix] for r in rows], np.float64)
+            elif el["name"] == "face":
+                faces = [r[0] for r in rows]
+    else:
+        endian = "<" if fmt == "binary_little_endian" else ">"
+        pos = 0
+        for el in elements:
+            if all(p[0] == "scalar" for p in el["props"]):
+                dt = np.dtype([(p[2], endian + _PLY_TYPES[p[1]]) for p in el["props"]])
+                arr = np.frombuffer(body, dt, el["count"], pos)
+                pos += dt.itemsize * el["count"]
+                if el["name"] == "vertex":
+                    verts = np.stack([arr["x"], arr["y"], arr["z"]], 1).astype(np.float64)
+            else:
+                for _ in range(el["count"]):
+                    for p in el["props"]:
+                        if p[0] == "scalar":
+                            pos += np.dtype(_PLY_TYPES[p[1]]).itemsize
+                        else:
+                            cdt = np.dtype(endian + _PLY_TYPES[p[1]])
+                            idt = np.dtype(endian + _PLY_TYPES[p[2]])
+                            n = int(np.frombuffer(body, cdt, 1, pos)[0]); pos += cdt.itemsize
+                            idx = np.frombuffer(body, idt, n, pos); pos += idt.itemsize * n
+                            if el["name"] == "face":
+                                faces.append(idx.tolist())
+    tris = []
+    for poly in faces:
+        for i in range(1, len(poly) - 1):
+            tris.append([poly[0], poly[i], poly[i + 1]])
+    return verts, np.asarray(tris, np.int64).reshape(-1, 3)
+
+
+def write_ply(path, verts, tris):
+    verts = np.asarray(verts, np.float32)
+    tris = np.asarray(tris, np.uint32)
+    os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
+    with open(path, "wb") as f:
+        f.write((f"ply\nformat binary_little_endian 1.0\nelement vertex {len(verts)}\n"
+                 "property float x\nproperty float y\nproperty float z\n"
+                 f"element face {len(tris)}\nproperty list uchar uint vertex_indices\nend_header\n").encode())
+        f.write(verts.astype("<f4").tobytes())
+        rec = np.empty(len(tris), np.dtype([("n", "u1"), ("i", "<u4", 3)]))
+        rec["n"] = 3
+        rec["i"] = tris
+        f.write(rec.tobytes())
+
+
+def load_mesh(path):
+    ext = os.path.splitext(path)[1][1:].lower()
+    if ext != "ply":
+        raise ValueError(f"Unsupported extension: '{ext}', only PLY meshes are supported.")
+    return load_ply(path)
+
+
+def _uniform_sphere(u1, u2):
+    z = 1.0 - 2.0 * u2
+    r = torch.sqrt(torch.clamp(1.0 - z * z, min=0.0))
+    phi = 2.0 * np.pi * u1
+    return torch.stack([r * torch.cos(phi), r * torch.sin(phi), z], -1)
+
+
+@torch.no_grad()
+def mesh_inside(points, dirs, verts, tris, chunk=1 << 16):
+    """Nearest-hit inside test of sensor.py:95-97 / utils.py:117-121: a point is
+    inside when the first triangle hit along `dirs` faces away (dot(n, d) > 0)."""
+    dev = points.device
+    v = torch.as_tensor(verts, dtype=torch.float32, device=dev)
+    t = torch.as_tensor(tris, dtype=torch.int64, device=dev)
+    p0, p1, p2 = v[t[:, 0]], v[t[:, 1]], v[t[:, 2]]
+    e1, e2 = p1 - p0, p2 - p0
+    n = torch.cross(e1, e2, dim=-1)
+    out = torch.zeros(points.shape[0], dtype=torch.bool, device=dev)
+    for lo in range(0, points.shape[0], chunk):
+        o = points[lo:lo + chunk, None, :]
+        d = dirs[lo:lo + chunk, None, :]
+        pvec = torch.cross(d, e2[None], dim=-1)
+        det = (e1[None] * pvec).sum(-1)
+        inv = 1.0 / det
+        tvec = o - p0[None]
+        u = (tvec * pvec).sum(-1) * inv
+        qvec = torch.cross(tvec, e1[None].expand_as(tvec), dim=-1)
+        w = (d * qvec).sum(-1) * inv
+        tt = (e2[None] * qvec).sum(-1) * inv
+        hit = (det.abs() > 1e-20) & (u >= 0) & (w >= 0) & (u + w <= 1) & (tt > 0)
+        tt = torch.where(hit, tt, torch.full_like(tt, float("inf")))
+        tmin, arg = tt.min(dim=1)
+        facing = (n[arg] * d[:, 0, :]).sum(-1) > 0
+        out[lo:lo + chunk] = torch.isfinite(tmin) & facing
+    return out
+
+
+@torch.no_grad()
+def discretize(scene, sensor=0, seed=0):
+    """Binary occupancy grid of the target mesh at the voxel centres: one ray in
+    a random direction per voxel, inside iff the first hit faces away
+    (utils.py:83-128).  Returns (resz, resy, resx, 1)."""
+    if isinstance(sensor, int):
+        sensor = scene.sensors()[sensor]
+    if scene.target is None:
+        raise ValueError("No target shape found in the scene")
+    verts, tris = scene.target["vertices"], scene.target["triangles"]
+    dev = scene.projector.active_data.device
+    rx, ry, rz = sensor.resolution()
+    vs = torch.as_tensor(sensor.voxel_size, dtype=torch.float32, device=dev)
+    bmin = torch.as_tensor(sensor.bbox_min, dtype=torch.float32, device=dev)
+    zz, yy, xx = torch.meshgrid(torch.arange(rz, device=dev), torch.arange(ry, device=dev),
+                                torch.arange(rx, device=dev), indexing="ij")
+    idx = torch.stack([xx, yy, zz], -1).reshape(-1, 3).to(torch.float32)
+    pos = bmin + (0.5 + idx) * vs
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    u = torch.rand(pos.shape[0], 2, generator=g).to(dev)
+    dirs = _uniform_sphere(u[:, 0], u[:, 1])
+    lo = torch.as_tensor(verts.min(0), dtype=torch.float32, device=dev)
+    hi = torch.as_tensor(verts.max(0), dtype=torch.float32, device=dev)
+    in_box = ((pos > lo) & (pos < hi)).all(-1)
+    inside = torch.zeros(pos.shape[0], dtype=torch.bool, device=dev)
+    sel = torch.nonzero(in_box).reshape(-1)
+    if sel.numel():
+        inside[sel] = mesh_inside(pos[sel], dirs[sel], verts, tris)
+    return inside.to(torch.float32).reshape(rz, ry, rx, 1)

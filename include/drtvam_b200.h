@@ -1,0 +1,164 @@
+/*
+ * drtvam_b200.h -- C-ABI of the B200-native Dr.TVAM hot path
+ * (forward projection A and its adjoint A^T).
+ *
+ * This is the drop-in boundary.  In the reference the path sits behind
+ * Mitsuba's Python plugin ABI and is reached through
+ *     vol = mi.render(scene, params, integrator, sensor, spp, spp_grad, seed)
+ *                                         (src/drtvam/optimize.py:216,294,328)
+ *     integrator.render_backward(scene, params, grad_in, sensor, seed, spp)
+ *                                         (src/drtvam/integrators/volume.py:97-134)
+ * which Dr.Jit turns into JIT megakernels.  There is no FFI in the reference;
+ * the entry points below are what a ctypes binding of that path binds
+ * (INTEGRATION.md shows the stub).  Each one cites the reference interface it
+ * replaces.
+ *
+ * Conventions
+ *  - return 0 on success, a negative DRTVAM_E_* otherwise; the message is
+ *    available through drtvam_last_error() (thread local).
+ *  - all data pointers are DEVICE pointers on the scene's device unless the
+ *    name says host; the library never allocates or frees caller-visible
+ *    buffers and never synchronises the stream it is given (the *_host
+ *    convenience calls are the exception: they copy and synchronise).
+ *  - `stream` is a cudaStream_t passed as void* (NULL = default stream).
+ *  - one handle per device; a handle is not thread safe.
+ *  - fp32 arithmetic throughout, like the reference's *_ad_mono variants.
+ */
+#ifndef DRTVAM_B200_H
+#define DRTVAM_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DRTVAM_ABI_VERSION 3
+#define DRTVAM_MAX_SURFACES 8
+
+#define DRTVAM_OK 0
+#define DRTVAM_E_INVALID -1      /* bad argument / unsupported configuration */
+#define DRTVAM_E_CUDA -2         /* CUDA runtime error */
+#define DRTVAM_E_TOO_MANY_RAYS -3 /* wavefront > 2^32, common.py:60-65 */
+
+/* surface kinds / bsdf kinds */
+#define DRTVAM_SURF_CYLINDER 0   /* open tube about the z axis: geometry.py:85-89,157-160 */
+#define DRTVAM_SURF_BOX 1        /* origin-centred axis-aligned box: geometry.py:198-208 */
+#define DRTVAM_BSDF_NULL 0       /* geometry.py:90 */
+#define DRTVAM_BSDF_DIELECTRIC 1 /* geometry.py:161-165,172-176,201-204,209-213 */
+#define DRTVAM_BSDF_ABSORBER 2   /* diffuse occluder, no transmission lobe: geometry.py:57-63 */
+
+#define DRTVAM_PROJ_COLLIMATED 0  /* projector.py:167-196 */
+#define DRTVAM_PROJ_TELECENTRIC 1 /* projector.py:199-237 */
+#define DRTVAM_PROJ_LENS 2        /* projector.py:241-296 */
+
+#define DRTVAM_PHASE_ISOTROPIC 0
+#define DRTVAM_PHASE_RAYLEIGH 1
+#define DRTVAM_PHASE_HG 2
+
+#define DRTVAM_SENSOR_DDA 0   /* sensor.py:297-440 */
+#define DRTVAM_SENSOR_RATIO 1 /* sensor.py:193-295 */
+
+typedef struct DrtvamSurface {
+    int32_t kind, bsdf;
+    int32_t interior_medium; /* shape 'interior' is the printing medium */
+    int32_t exterior_medium; /* shape 'exterior' is the printing medium */
+    float radius, z0, z1;    /* cylinder */
+    float hx, hy, hz;        /* box half extents */
+    float eta;               /* int_ior / ext_ior */
+    float _pad;
+} DrtvamSurface;
+
+/* Flat description of what mi.load_dict(scene_dict) builds for this path
+ * (optimize.py:61-73, geometry.py to_dict(), projector/sensor/film props). */
+typedef struct DrtvamSceneDesc {
+    uint32_t struct_size;    /* = sizeof(DrtvamSceneDesc), ABI check */
+    uint32_t abi_version;    /* = DRTVAM_ABI_VERSION */
+    /* projector (projector.py:41-296) */
+    int32_t proj_kind, n_patterns, res_x, res_y;
+    float pixel_x, pixel_y, aperture_radius, focus_distance;
+    /* motion (motion.py:19-36): analytic circular, or a HOST table of
+     * n_patterns row-major 3x4 to_world matrices ("arbitrary motion") */
+    int32_t motion_analytic, clockwise;
+    float distance;
+    float _pad0;
+    const float *motion_table_host;
+    /* integrator (integrators/common.py:10-22, optimize.py:121-128) */
+    int32_t max_depth, rr_depth, transmission_only, regular_sampling, sample_time;
+    float print_time;
+    /* medium (geometry.py:37-45) */
+    float sigma_t, albedo;
+    int32_t phase_kind;
+    float hg_g;
+    /* vial surfaces */
+    int32_t n_surf;
+    int32_t _pad1;
+    DrtvamSurface surf[DRTVAM_MAX_SURFACES];
+    /* sensor + film (sensor.py:11-19, film.py:9-21) */
+    float bbox_min[3], bbox_max[3];
+    int32_t res[3];          /* x, y, z as film.resolution() returns them */
+    int32_t surface_aware;
+    int32_t sensor_kind;
+    float majorant;
+} DrtvamSceneDesc;
+
+typedef struct DrtvamScene DrtvamScene;
+
+/* replaces mi.load_dict(scene_dict) for this path (optimize.py:90). */
+int drtvam_scene_create(const DrtvamSceneDesc *desc, int device, DrtvamScene **out);
+void drtvam_scene_destroy(DrtvamScene *scene);
+
+/* integrator.max_depth = ... (optimize.py:288-289) and the *_ref integrator
+ * (optimize.py:231-238) without rebuilding the scene. */
+int drtvam_scene_set_depth(DrtvamScene *scene, int32_t max_depth, int32_t rr_depth);
+
+/* Which kernel family a call will use for this scene and spp:
+ * 0 = general per-lane tracer, 1 = planar z-separable fast path. */
+int drtvam_scene_plan(DrtvamScene *scene, uint64_t n_active, uint32_t spp);
+/* Force the general tracer (1) or let the library choose (0). */
+int drtvam_scene_force_general(DrtvamScene *scene, int32_t on);
+
+/* A p : VolumeIntegrator.render (volume.py:18-56).  dose has
+ * res_z*res_y*res_x*C floats (C = 2 when surface_aware; film.py:17-21,
+ * flat index sensor.py:405-409) and receives film * out_scale, where the
+ * caller passes out_scale = 1/voxel_volume (volume.py:41-42,54).  active_data
+ * may be signed (lbfgs.py:240-248).  zero_first != 0 clears the film first
+ * (film.clear(), volume.py:33); otherwise the call accumulates. */
+int drtvam_forward(DrtvamScene *scene, const float *active_data, const uint32_t *active_pixels,
+                   uint64_t n_active, uint32_t spp, uint32_t seed, float out_scale,
+                   float *dose, int32_t zero_first, void *stream);
+
+/* A^T g : VolumeIntegrator.render_backward (volume.py:97-134).  dose_grad is
+ * grad_in; in_scale = 1/voxel_volume (volume.py:130).  Overwrites
+ * pattern_grad[n_active] with d loss / d active_data. */
+int drtvam_adjoint(DrtvamScene *scene, const float *dose_grad, const uint32_t *active_pixels,
+                   uint64_t n_active, uint32_t spp, uint32_t seed, float in_scale,
+                   float *pattern_grad, void *stream);
+
+/* TVAMIntegrator.sample_rays (common.py:70-116): rays_out[lanes][6] = o,d. */
+int drtvam_raygen(DrtvamScene *scene, const uint32_t *active_pixels, uint64_t n_active,
+                  uint32_t spp, uint32_t seed, float *rays_out, void *stream);
+
+/* Number of DDA trips (sensor.py:383) one forward pass makes; the unit of
+ * work of the roofline.  Synchronises and returns the count in *out_host. */
+int drtvam_count_visits(DrtvamScene *scene, const uint32_t *active_pixels, uint64_t n_active,
+                        uint32_t spp, uint32_t seed, uint64_t *out_host);
+
+/* HOST-buffer convenience calls: copy in, run, copy out, synchronise. */
+int drtvam_forward_host(DrtvamScene *scene, const float *active_data_host,
+                        const uint32_t *active_pixels_host, uint64_t n_active, uint32_t spp,
+                        uint32_t seed, float out_scale, float *dose_host);
+int drtvam_adjoint_host(DrtvamScene *scene, const float *dose_grad_host,
+                        const uint32_t *active_pixels_host, uint64_t n_active, uint32_t spp,
+                        uint32_t seed, float in_scale, float *pattern_grad_host);
+
+/* number of kernels this library has launched since load (bench gpu_launches) */
+uint64_t drtvam_launch_count(void);
+
+const char *drtvam_last_error(void);
+int drtvam_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DRTVAM_B200_H */
