@@ -1,0 +1,360 @@
+#!/usr/bin/env python
+"""Benchmark of the Dr.TVAM hot path on B200: rays/s and seconds per L-BFGS
+iteration on the synthetic Benchy-sized workload (BASELINE.json config 2:
+index-matched vial, 400x400 DMD, 400 angles, 400^3 dose grid, 1 spp).
+
+    python bench.py --gpus N --steps K --warmup W [--impl reference] [--workload C2]
+
+One "step" is the projection work of one L-BFGS iteration (optimize.py:294,308
+and lbfgs.py:248): forward A p, thresholded loss + its gradient, adjoint A^T g,
+forward A d (signed search direction) and one Armijo loss evaluation.  Prints
+ONE JSON line (see the contract in the task description).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="C2")
+    ap.add_argument("--n", type=int, default=0, help="override DMD/grid edge (default: full size)")
+    ap.add_argument("--jitter", action="store_true", help="regular_sampling=false (per-ray jitter, general tracer)")
+    ap.add_argument("--general", action="store_true", help="force the general per-lane tracer")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    return ap.parse_args()
+
+
+WORKLOAD_TEXT = {
+    "C1": "C1: index-matched vial r=5, collimated 128 angles x 128x128 DMD, 128^3 dda grid, 1 spp",
+    "C2": "C2: Benchy-sized synthetic target, index-matched vial r=7.5, collimated 400 angles x 400x400 DMD "
+          "(25 um), 400^3 dda grid, 1 spp",
+    "C3": "C3: as C2 with a cylindrical glass vial (refraction)",
+    "C4": "C4: as C2 with a square glass vial (refraction)",
+    "C5": "C5: as C3 with a Henyey-Greenstein scattering resin, 16 spp",
+}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows = []
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200", "-i", str(index)],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            parts = [p.strip() for p in r.split(",")]
+            if len(parts) < 6:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                mx = float(parts[1])
+            except ValueError:
+                continue
+            for n, v in zip(names, parts[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return json.load(f).get("hbm_gbs", 6650.0), "measured"
+    return 6650.0, "fallback"
+
+
+def oracle_sample(cfg, desc, seconds, threads=0):
+    """Times the CPU oracle (fp32 build, OpenMP over rays) on a bounded sample of
+    the workload: whole angles of the same scene, 3 passes each (A p, A^T g, A d)."""
+    import numpy as np
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle as orc
+    orc.build()
+    o = orc.Oracle(desc.as_dict(), "f32", threads=threads)
+    per_angle = desc.res_x * desc.res_y
+    rng = np.random.default_rng(0)
+    g = rng.standard_normal(desc.film_shape()).astype(np.float32)
+    n_angles, rays, t_used = 1, 0, 0.0
+    k0 = 0
+    while True:
+        ks = np.arange(k0, min(k0 + n_angles, desc.n_patterns))
+        if ks.size == 0:
+            break
+        pix = (ks[:, None] * per_angle + np.arange(per_angle)[None, :]).reshape(-1).astype(np.uint32)
+        p = rng.random(pix.size).astype(np.float32) + 0.01
+        d = (rng.random(pix.size).astype(np.float32) - 0.5)
+        t0 = time.perf_counter()
+        o.forward(p, pix)
+        o.adjoint(g, pix)
+        o.forward(d, pix)
+        t_used += time.perf_counter() - t0
+        rays += 3 * pix.size
+        k0 += ks.size
+        if t_used > seconds:
+            break
+        n_angles = min(n_angles * 2, 16)
+    return rays / t_used, rays, t_used, k0
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference" and rank != 0:
+        return 0
+
+    import numpy as np
+    import torch
+    from drtvam_b200.synthetic import make_config
+
+    workdir = os.path.join(tempfile.gettempdir(), f"drtvam_bench_{os.getuid()}_{rank}")
+    cfg = make_config(args.workload, workdir, n=args.n or None, regular_sampling=not args.jitter)
+    if args.workload == "C5":
+        cfg["regular_sampling"] = False
+    spp = int(cfg["spp"])
+    host_cores = os.cpu_count() or 1
+    workload = WORKLOAD_TEXT[args.workload] + (f" [edge overridden to {args.n}]" if args.n else "")
+    workload += ", regular_sampling=%s" % str(bool(cfg["regular_sampling"])).lower()
+
+    # ------------------------------------------------------------ reference arm (CPU)
+    if args.impl == "reference":
+        from drtvam_b200.integrators import VolumeIntegrator
+        from drtvam_b200.optimize import load_scene
+        from drtvam_b200.scene import load_dict
+        scene = load_dict(load_scene(cfg), device="cpu")
+        integ = VolumeIntegrator({"max_depth": cfg["max_depth"], "rr_depth": cfg["rr_depth"],
+                                  "regular_sampling": cfg["regular_sampling"], "print_time": 1.0})
+        desc = scene.describe(integ, scene.sensor("sensor"))
+        vals = []
+        per_step = max(2.0, min(20.0, 120.0 / max(1, args.steps + args.warmup)))
+        sample = ""
+        for i in range(args.warmup + args.steps):
+            rps, rays, t, n_ang = oracle_sample(cfg, desc, per_step)
+            if i >= args.warmup:
+                vals.append((rps, rays, t))
+            sample = f"{n_ang} of {desc.n_patterns} angles x {desc.res_x}x{desc.res_y} rays, 3 passes (A p, A^T g, A d)"
+        total_rays = sum(v[1] for v in vals)
+        total_t = sum(v[2] for v in vals)
+        value = total_rays / total_t
+        full_rays = 3 * desc.n_patterns * desc.res_x * desc.res_y * spp
+        line = {
+            "impl": "reference", "metric": "rays_per_s", "value": value, "unit": "rays/s", "n_gpus": 0,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": full_rays / value * 1e3,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": workload, "note": "reference's Dr.Jit LLVM path is unavailable on this box "
+                       "(mitsuba/drjit not installable); this is the CPU oracle port, fp32, OpenMP over rays; "
+                       "ms_per_step extrapolated from the bounded sample to the full step"},
+            "cpu_baseline": {"value": value, "unit": "rays/s", "cores": host_cores, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0,
+        }
+        print(json.dumps(line), flush=True)
+        return 0
+
+    # ------------------------------------------------------------ B200 arm
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the B200 arm has no CPU fallback (use --impl reference)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    import torch.distributed as dist
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    import drtvam_b200 as dv
+    from drtvam_b200 import _lib
+    from drtvam_b200.integrators import VolumeIntegrator
+    from drtvam_b200.loss import ThresholdedLoss
+    from drtvam_b200.optimize import load_scene
+    from drtvam_b200.utils import discretize
+
+    lib = _lib.load()
+    scene = dv.load_dict(load_scene(cfg), device=dev)
+    scene.force_general = bool(args.general)
+    integ = VolumeIntegrator({"max_depth": cfg["max_depth"], "rr_depth": cfg["rr_depth"],
+                              "regular_sampling": cfg["regular_sampling"], "print_time": 1.0})
+    sensor = scene.sensor("sensor")
+    desc_full = scene.describe(integ, sensor)
+    n_active_total = scene.projector.active_size()
+    target = discretize(scene, sensor=sensor)
+    if world > 1:
+        scene.shard(rank, world)
+    n_local = scene.projector.active_size()
+    pixels = scene.projector.active_pixels
+    loss_fn = ThresholdedLoss({})
+
+    gen = torch.Generator(device=dev).manual_seed(1234 + rank)
+    # dense, strictly non-zero inputs so that no ray is skipped
+    p_dev = (torch.rand(n_local, device=dev, generator=gen) * 2e-3 + 1e-4)
+    d_dev = (torch.rand(n_local, device=dev, generator=gen) - 0.5) * 1e-3
+    d_dev = torch.where(d_dev == 0, torch.full_like(d_dev, 1e-4), d_dev)
+    p_host = p_dev.cpu().pin_memory()
+    d_host = d_dev.cpu().pin_memory()
+    g_host = torch.empty(n_local, dtype=torch.float32).pin_memory()
+
+    fwd_events = []
+
+    def step(seed, p, d, record=False):
+        """One L-BFGS iteration's projections on device-resident inputs."""
+        p = p.detach().requires_grad_(True)
+        scene.projector.active_data = p
+        if record:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+        prm = dv.traverse(scene)
+        vol = dv.render(scene, prm, integrator=integ, sensor=sensor, spp=spp, seed=seed)
+        if record:
+            e1.record()
+            fwd_events.append((e0, e1))
+        loss = loss_fn(vol, target, p)
+        loss.backward()                                     # adjoint A^T g
+        with torch.no_grad():
+            scene.projector.active_data = d
+            dvol = dv.render(scene, None, integrator=integ, sensor=sensor, spp=spp, seed=seed)   # A d
+            f_new = loss_fn(vol.detach() + 1.0 * dvol, target, d)                                # Armijo trial
+        return loss.detach(), f_new, p.grad
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    for i in range(args.warmup):
+        step(i, p_dev, d_dev)
+    barrier()
+
+    clocks = ClockSampler(local_rank) if rank == 0 else None
+    launches0 = lib.drtvam_launch_count()
+    t0 = torch.cuda.Event(enable_timing=True)
+    t1 = torch.cuda.Event(enable_timing=True)
+    barrier()
+    t0.record()
+    for i in range(args.steps):
+        out = step(100 + i, p_dev, d_dev, record=True)
+    t1.record()
+    barrier()
+    ms = t0.elapsed_time(t1)
+    launches = lib.drtvam_launch_count() - launches0
+    clock_info = clocks.stop() if clocks else None
+
+    # end to end: host (pinned) inputs copied in and results copied out every step
+    barrier()
+    e0 = torch.cuda.Event(enable_timing=True)
+    e1 = torch.cuda.Event(enable_timing=True)
+    e0.record()
+    loss_host = 0.0
+    for i in range(args.steps):
+        p_in = p_host.to(dev, non_blocking=True)
+        d_in = d_host.to(dev, non_blocking=True)
+        loss, f_new, grad = step(100 + i, p_in, d_in)
+        g_host.copy_(grad, non_blocking=True)
+        loss_host = float(loss)                              # D2H of the scalar: syncs the step
+    e1.record()
+    barrier()
+    ms_e2e = e0.elapsed_time(e1)
+
+    times = torch.tensor([ms, ms_e2e], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(times, op=dist.ReduceOp.MAX)
+    ms, ms_e2e = times.tolist()
+
+    rays_per_step = 3 * n_active_total * spp
+    value = rays_per_step * args.steps / (ms * 1e-3)
+    e2e_value = rays_per_step * args.steps / (ms_e2e * 1e-3)
+
+    # roofline of the dominant kernel (forward dose scatter)
+    fwd_ms = sum(a.elapsed_time(b) for a, b in fwd_events) / max(1, len(fwd_events))
+    n_vis = _lib.C.c_uint64(0)
+    h = scene.handle(integ, sensor)
+    _lib.check(lib.drtvam_count_visits(h, pixels.data_ptr(), n_local, spp, 100, _lib.C.byref(n_vis)))
+    visits = int(n_vis.value)
+    peak, how = measured_peaks()
+    achieved = 4.0 * visits / (fwd_ms * 1e-3) * 1e-9
+    hbm_alg_bytes = 4.0 * n_local * 2 + 4.0 * int(np.prod(desc_full.film_shape()))
+    roofline = {
+        "bound": "hbm", "kernel": "forward dose scatter (A p)", "achieved": achieved, "peak": peak, "unit": "GB/s",
+        "frac": achieved / peak, "traffic": None, "peak_source": how,
+        "algorithmic_bytes_per_visit": 4, "visits_per_launch": visits, "kernel_ms": fwd_ms,
+        "hbm_algorithmic_gb": hbm_alg_bytes * 1e-9, "hbm_floor_frac": hbm_alg_bytes * 1e-9 / (fwd_ms * 1e-3) / peak,
+        "plan": int(lib.drtvam_scene_plan(h, n_local, spp)),
+    }
+
+    line = None
+    if rank == 0:
+        cpu_baseline = None
+        if not args.no_cpu_baseline and world == 1:
+            rps, rays, t, n_ang = oracle_sample(cfg, desc_full, args.cpu_seconds)
+            cpu_baseline = {"value": rps, "unit": "rays/s", "cores": host_cores, "kind": "port",
+                            "sample": f"{n_ang} of {desc_full.n_patterns} angles x {desc_full.res_x}x{desc_full.res_y} "
+                                      f"rays, 3 passes, {t:.1f} s of oracle (fp32, OpenMP) time"}
+        line = {
+            "metric": "rays_per_s", "value": value, "unit": "rays/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "sec_per_lbfgs_iter": ms / args.steps * 1e-3,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": workload, "rays_per_step": rays_per_step,
+                       "step": "A p + thresholded loss + A^T g + A d + 1 Armijo trial (one L-BFGS iteration's "
+                               "projections), dense non-zero patterns",
+                       "l2": "inputs (patterns 256 MB, dose 256 MB at C2) exceed the 126 MB L2",
+                       "parallelism": f"angle-sharded x{world}, 1 all_reduce(dose) per forward" if world > 1 else "1 GPU"},
+            "clocks": clock_info,
+            "e2e": {"value": e2e_value, "unit": "rays/s", "ms_per_step": ms_e2e / args.steps,
+                    "h2d_bytes_per_step": 8 * n_local, "d2h_bytes_per_step": 4 * n_local + 4},
+            "gpu_launches": int(launches),
+            "roofline": roofline,
+            "cpu_baseline": cpu_baseline,
+            "loss": loss_host,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,113 @@
+// Micro-benchmarks that measure the denominators MEASURED_PEAKS.json does not
+// have: fp32 reduction-atomic throughput into a > L2 array (REDG, scalar and
+// v4), and shared-memory accumulate throughput (native integer ATOMS, the
+// CAS-loop fp32 atomicAdd, and plain LDS+FADD+STS).  Bench-only library
+// (libdrtvam_microbench.so); not part of the product path.
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace {
+
+__device__ __forceinline__ uint32_t hash32(uint32_t x) {
+    x ^= x >> 16; x *= 0x7feb352dU; x ^= x >> 15; x *= 0x846ca68bU; x ^= x >> 16;
+    return x;
+}
+
+// pattern 0: a warp adds to 32 consecutive floats (one 128 B line)
+// pattern 1: a warp adds to 32 floats `stride` elements apart (one sector each)
+// pattern 2: every lane adds to an independent pseudo-random float
+__global__ void red_scalar_kernel(float* buf, uint32_t n_mask, int pattern, uint32_t stride, int iters) {
+    const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t warp = tid >> 5, lane = tid & 31;
+    uint32_t base = hash32(warp);
+    for (int i = 0; i < iters; ++i) {
+        base = hash32(base + i);
+        uint32_t idx;
+        if (pattern == 0) idx = (base & ~31u) + lane;
+        else if (pattern == 1) idx = base + lane * stride;
+        else idx = hash32(base ^ (lane * 0x9e3779b9u));
+        atomicAdd(buf + (idx & n_mask), 1.0f);
+    }
+}
+
+__global__ void red_v4_kernel(float* buf, uint32_t n_mask, int iters) {
+    const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t warp = tid >> 5, lane = tid & 31;
+    uint32_t base = hash32(warp);
+    for (int i = 0; i < iters; ++i) {
+        base = hash32(base + i);
+        const uint32_t idx = ((base & ~127u) + lane * 4) & n_mask;
+        asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(buf + idx), "f"(1.f), "f"(1.f), "f"(1.f),
+                     "f"(1.f)
+                     : "memory");
+    }
+}
+
+// mode 0: atomicAdd(int) ; 1: atomicAdd(float) (CAS loop) ; 2: LDS + FADD + STS (no atomicity)
+// addresses: each lane hits its own bank, a different row per iteration
+__global__ void smem_accumulate_kernel(float* out, int mode, int iters) {
+    extern __shared__ float tile[];
+    const int n = 12288;  // 48 KB
+    for (int i = threadIdx.x; i < n; i += blockDim.x) tile[i] = 0.f;
+    __syncthreads();
+    const uint32_t lane = threadIdx.x & 31;
+    uint32_t row = hash32(blockIdx.x * blockDim.x + threadIdx.x) >> 8;
+    int* itile = reinterpret_cast<int*>(tile);
+    for (int i = 0; i < iters; ++i) {
+        row = row * 1664525u + 1013904223u;
+        const uint32_t idx = (((row >> 10) % (n / 32)) * 32 + lane);
+        if (mode == 0) atomicAdd(itile + idx, 1);
+        else if (mode == 1) atomicAdd(tile + idx, 1.0f);
+        else tile[idx] += 1.0f;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) out[blockIdx.x] = tile[lane];
+}
+
+float time_launches(cudaEvent_t a, cudaEvent_t b) {
+    float ms = 0.f;
+    cudaEventSynchronize(b);
+    cudaEventElapsedTime(&ms, a, b);
+    return ms;
+}
+
+}  // namespace
+
+extern "C" {
+
+// Returns giga-adds per second (fp32 adds landed in memory), or < 0 on error.
+// buf must hold (n_mask + 1 + 32*stride) floats.
+double drtvam_mb_red(float* buf, uint32_t n_mask, int pattern, uint32_t stride, int iters, int blocks, int v4) {
+    cudaEvent_t a, b;
+    cudaEventCreate(&a); cudaEventCreate(&b);
+    const int threads = 256;
+    for (int rep = 0; rep < 2; ++rep) {
+        cudaEventRecord(a);
+        if (v4) red_v4_kernel<<<blocks, threads>>>(buf, n_mask, iters);
+        else red_scalar_kernel<<<blocks, threads>>>(buf, n_mask, pattern, stride, iters);
+        cudaEventRecord(b);
+    }
+    if (cudaGetLastError() != cudaSuccess) return -1.0;
+    const float ms = time_launches(a, b);
+    cudaEventDestroy(a); cudaEventDestroy(b);
+    const double adds = static_cast<double>(blocks) * threads * iters * (v4 ? 4 : 1);
+    return adds / (ms * 1e-3) * 1e-9;
+}
+
+// Returns giga-accumulates per second over the whole chip.
+double drtvam_mb_smem(float* out, int mode, int iters, int blocks) {
+    cudaEvent_t a, b;
+    cudaEventCreate(&a); cudaEventCreate(&b);
+    const int threads = 256;
+    for (int rep = 0; rep < 2; ++rep) {
+        cudaEventRecord(a);
+        smem_accumulate_kernel<<<blocks, threads, 49152>>>(out, mode, iters);
+        cudaEventRecord(b);
+    }
+    if (cudaGetLastError() != cudaSuccess) return -1.0;
+    const float ms = time_launches(a, b);
+    cudaEventDestroy(a); cudaEventDestroy(b);
+    return static_cast<double>(blocks) * threads * iters / (ms * 1e-3) * 1e-9;
+}
+
+}  // extern "C"

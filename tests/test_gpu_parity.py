@@ -1,0 +1,255 @@
+"""GPU parity tests: the CUDA path, called through the C-ABI, against the CPU
+oracle on the same seeded inputs.  Tolerance: 1e-4 relative L2 on dose volumes
+and pattern gradients for the deterministic 1-spp paths (BASELINE.json
+north_star); jittered runs use the same PCG32/TEA streams on both sides and
+are held to the same bound; scattering runs get a looser, stated bound because
+fp32 branch flips change individual random walks."""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+import oracle as orc
+from drtvam_b200 import _lib
+from helpers import build, pixels_np, random_inputs, rel_l2
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-4
+
+
+class Handle:
+    def __init__(self, desc, force_general=False):
+        self.lib = _lib.load()
+        cdesc, self.keep = desc.to_c()
+        h = C.c_void_p()
+        _lib.check(self.lib.drtvam_scene_create(C.byref(cdesc), 0, C.byref(h)))
+        self.h = h.value
+        _lib.check(self.lib.drtvam_scene_force_general(self.h, int(force_general)))
+        self.film_shape = desc.film_shape()
+
+    def forward(self, p, pix, spp=1, seed=0, scale=1.0):
+        p = torch.as_tensor(p, device="cuda")
+        pix = torch.as_tensor(pix.astype(np.int64), device="cuda").to(torch.int32)
+        film = torch.empty(self.film_shape, device="cuda", dtype=torch.float32)
+        _lib.check(self.lib.drtvam_forward(self.h, p.data_ptr(), pix.data_ptr(), p.numel(), spp, seed, scale,
+                                           film.data_ptr(), 1, None))
+        torch.cuda.synchronize()
+        return film.cpu().numpy()
+
+    def adjoint(self, g, pix, spp=1, seed=0, scale=1.0):
+        g = torch.as_tensor(g, device="cuda").contiguous()
+        pix = torch.as_tensor(pix.astype(np.int64), device="cuda").to(torch.int32)
+        out = torch.empty(pix.numel(), device="cuda", dtype=torch.float32)
+        _lib.check(self.lib.drtvam_adjoint(self.h, g.data_ptr(), pix.data_ptr(), pix.numel(), spp, seed, scale,
+                                           out.data_ptr(), None))
+        torch.cuda.synchronize()
+        return out.cpu().numpy()
+
+    def raygen(self, pix, spp=1, seed=0, regular=False):
+        pixt = torch.as_tensor(pix.astype(np.int64), device="cuda").to(torch.int32)
+        n = pix.size * (1 if regular else spp)
+        out = torch.empty((n, 6), device="cuda", dtype=torch.float32)
+        _lib.check(self.lib.drtvam_raygen(self.h, pixt.data_ptr(), pix.size, spp, seed, out.data_ptr(), None))
+        torch.cuda.synchronize()
+        return out.cpu().numpy()
+
+    def count(self, pix, spp=1, seed=0):
+        pixt = torch.as_tensor(pix.astype(np.int64), device="cuda").to(torch.int32)
+        n = C.c_uint64(0)
+        _lib.check(self.lib.drtvam_count_visits(self.h, pixt.data_ptr(), pix.size, spp, seed, C.byref(n)))
+        return int(n.value)
+
+    def __del__(self):
+        self.lib.drtvam_scene_destroy(self.h)
+
+
+@pytest.mark.parametrize("general", [True, False])
+@pytest.mark.parametrize("name", ["C1", "C2", "C3", "C4"])
+def test_forward_and_adjoint_match_oracle_regular(name, general, workdir):
+    scene, integ, sensor, d, _ = build(name, workdir, 48)
+    pix = pixels_np(scene)
+    p, g = random_inputs(d, pix.size, 3)
+    p = (p - 0.3).astype(np.float32)  # signed patterns (lbfgs.py:240-248)
+    o = orc.Oracle(d.as_dict(), "f64")
+    h = Handle(d, force_general=general)
+    assert rel_l2(h.forward(p, pix), o.forward(p, pix)) < TOL
+    assert rel_l2(h.adjoint(g, pix), o.adjoint(g, pix)) < TOL
+    assert h.count(pix) == o.last_visits or abs(h.count(pix) - o.last_visits) < 1e-3 * o.last_visits
+
+
+@pytest.mark.parametrize("name", ["C1", "C3", "C4"])
+def test_jittered_sampling_matches_oracle(name, workdir):
+    scene, integ, sensor, d, _ = build(name, workdir, 40, regular_sampling=False)
+    pix = pixels_np(scene)
+    p, g = random_inputs(d, pix.size, 4)
+    o = orc.Oracle(d.as_dict(), "f64")
+    h = Handle(d)
+    for spp, seed in ((1, 0), (4, 11)):
+        assert rel_l2(h.forward(p, pix, spp, seed), o.forward(p, pix, spp, seed)) < TOL
+        assert rel_l2(h.adjoint(g, pix, spp, seed), o.adjoint(g, pix, spp, seed)) < TOL
+    # non power-of-two spp takes the atomic reduction path
+    assert rel_l2(h.adjoint(g, pix, 3, 5), o.adjoint(g, pix, 3, 5)) < TOL
+
+
+def test_raygen_matches_oracle_all_projectors(workdir):
+    from drtvam_b200._scene import SceneDesc
+    scene, integ, sensor, d, _ = build("C1", workdir, 16, regular_sampling=False)
+    pix = pixels_np(scene)
+    for kind, extra in ((0, {}), (1, {"aperture_radius": 0.3, "focus_distance": 20.0}),
+                        (2, {"aperture_radius": 0.3, "focus_distance": 20.0})):
+        d.proj_kind = kind
+        for k, v in extra.items():
+            setattr(d, k, v)
+        a = Handle(d).raygen(pix, spp=2, seed=9)
+        b = orc.Oracle(d.as_dict(), "f32").raygen(pix, spp=2, seed=9)
+        np.testing.assert_allclose(a, b, rtol=0, atol=2e-5)
+
+
+def test_crop_bound_on_gpu():
+    """tests/test_projector.py:9-38 through the CUDA ray generator."""
+    from drtvam_b200._scene import SceneDesc, SurfaceDesc
+    from drtvam_b200.projector import CollimatedProjector
+    proj = CollimatedProjector({"n_patterns": 1, "resx": 20, "resy": 10, "cropx": 4, "cropy": 4,
+                                "crop_offset_x": 8, "crop_offset_y": 3, "pixel_size": 1.,
+                                "motion": "circular", "distance": 20, "device": "cuda"})
+    d = SceneDesc(proj_kind=0, n_patterns=1, res_x=20, res_y=10, pixel_x=1., pixel_y=1.,
+                  motion_table=proj.motion_table(), regular_sampling=0, sigma_t=1.0,
+                  surfaces=[SurfaceDesc(radius=1., z0=-1, z1=1, interior_medium=1)])
+    rays = Handle(d).raygen(pixels_np_from(proj), spp=128, seed=0)
+    o = rays[:, :3]
+    assert np.all((o[:, 1] > -2) & (o[:, 1] < 2) & (o[:, 2] > -2) & (o[:, 2] < 2))
+
+
+def pixels_np_from(proj):
+    return (proj.active_pixels.cpu().numpy().astype(np.int64) & 0xFFFFFFFF).astype(np.uint32)
+
+
+def test_scattering_matches_oracle(workdir):
+    """Henyey-Greenstein scattering resin (C5): same random streams on both
+    sides; fp32-vs-fp64 branch flips perturb a few walks, so the bound is 2e-3
+    relative L2 (and the totals agree to 1e-3)."""
+    scene, integ, sensor, d, _ = build("C5", workdir, 32, spp=4)
+    pix = pixels_np(scene)
+    p, g = random_inputs(d, pix.size, 5)
+    o = orc.Oracle(d.as_dict(), "f64")
+    h = Handle(d)
+    f_gpu, f_cpu = h.forward(p, pix, 4, 2), o.forward(p, pix, 4, 2)
+    assert rel_l2(f_gpu, f_cpu) < 2e-3
+    assert abs(f_gpu.sum() - f_cpu.sum()) < 1e-3 * f_cpu.sum()
+    assert rel_l2(h.adjoint(g, pix, 4, 2), o.adjoint(g, pix, 4, 2)) < 2e-3
+
+
+def test_fd_vs_adjoint_on_gpu(workdir):
+    """tests/test_integrators.py:69-110 on the CUDA path (scattering, glass
+    cylinder, sample_time, rr_depth 3): FD of mean(vol^2) vs reverse mode."""
+    from test_oracle import _motion_table
+    from drtvam_b200._scene import SceneDesc, SurfaceDesc
+    n_pat, n = 16, 32
+    d_ext, d_int = 16.77, 15.33
+    surfs = [SurfaceDesc(radius=0.5 * d_ext, z0=-10, z1=10, bsdf=1, eta=1.514 / 1.000277),
+             SurfaceDesc(radius=0.5 * d_int, z0=-10, z1=10, bsdf=1, eta=1.4849 / 1.514, interior_medium=1)]
+    d = SceneDesc(proj_kind=0, n_patterns=n_pat, res_x=n, res_y=n, pixel_x=d_ext / n, pixel_y=d_ext / n,
+                  motion_analytic=1, distance=1.5 * d_ext, motion_table=_motion_table(1.5 * d_ext, n_pat),
+                  max_depth=32, rr_depth=3, sample_time=1, regular_sampling=0,
+                  sigma_t=0.1, albedo=0.5, phase_kind=1, surfaces=surfs,
+                  bbox_min=(-d_ext / 2,) * 3, bbox_max=(d_ext / 2,) * 3, res=(n, n, n))
+    pix = np.arange(n_pat * n * n, dtype=np.uint32)
+    patterns = np.linspace(1, 10, pix.size).astype(np.float32)
+    h = Handle(d)
+    spp, eps = 16, 1e-3
+    inv_vol = float(1.0 / (d_ext / n) ** 3)
+
+    def loss(a):
+        vol = h.forward((patterns * a).astype(np.float32), pix, spp, 0, inv_vol).astype(np.float64)
+        return np.mean(vol ** 2), vol
+
+    fd = (loss(1 + eps)[0] - loss(1 - eps)[0]) / (2 * eps)
+    _, vol = loss(1.0)
+    g = h.adjoint((2 * vol / vol.size).astype(np.float32), pix, spp, 0, inv_vol)
+    ad = float(np.sum(g.astype(np.float64) * patterns))
+    assert abs((ad - fd) / fd) < 1e-3  # fp32 forward differences; the f64 oracle meets 2e-4
+
+
+def test_full_size_properties_c2(workdir):
+    """BASELINE config 2 at full size (400 angles x 400^2 DMD, 400^3 grid):
+    adjoint consistency <A p, g> = <p, A^T g>, linearity and sign symmetry."""
+    scene, integ, sensor, d, _ = build("C2", workdir, 400, device="cuda")
+    lib = _lib.load()
+    h = Handle(d)
+    n_active = scene.projector.active_pixels.numel()
+    gen = torch.Generator(device="cuda").manual_seed(0)
+    p = torch.rand(n_active, device="cuda", generator=gen)
+    q = torch.rand(n_active, device="cuda", generator=gen) - 0.5
+    g = torch.randn(d.film_shape(), device="cuda", generator=gen)
+    pix = scene.projector.active_pixels
+
+    def fwd(x):
+        film = torch.empty(d.film_shape(), device="cuda")
+        _lib.check(lib.drtvam_forward(h.h, x.data_ptr(), pix.data_ptr(), n_active, 1, 0, 1.0, film.data_ptr(), 1, None))
+        return film
+
+    def adj(x):
+        out = torch.empty(n_active, device="cuda")
+        _lib.check(lib.drtvam_adjoint(h.h, x.data_ptr(), pix.data_ptr(), n_active, 1, 0, 1.0, out.data_ptr(), None))
+        return out
+
+    Ap, Aq = fwd(p), fwd(q)
+    lhs = torch.sum(Ap.double() * g.double()).item()
+    rhs = torch.sum(adj(g).double() * p.double()).item()
+    assert abs(lhs - rhs) < 1e-4 * abs(lhs)
+    lin = fwd(p + 2 * q)
+    err = torch.linalg.norm((lin - (Ap + 2 * Aq)).double()) / torch.linalg.norm(lin.double())
+    assert err.item() < 1e-5
+    assert torch.linalg.norm((fwd(-p) + Ap).double()).item() < 1e-5 * torch.linalg.norm(Ap.double()).item()
+    assert Ap.min().item() >= 0.0
+
+
+def test_python_api_render_and_autograd(workdir):
+    """drtvam_b200.render + torch autograd against the oracle (the mi.render /
+    dr.backward pair of optimize.py:294,308)."""
+    import drtvam_b200 as dv
+    scene, integ, sensor, d, _ = build("C3", workdir, 32, device="cuda")
+    pix = pixels_np(scene)
+    p_np, g_np = random_inputs(d, pix.size, 6)
+    params = dv.traverse(scene)
+    p = torch.as_tensor(p_np, device="cuda").requires_grad_(True)
+    params["projector.active_data"] = p
+    params.update()
+    vol = dv.render(scene, params, integrator=integ, sensor=sensor, spp=1, seed=0)
+    assert tuple(vol.shape) == d.film_shape()
+    (vol * torch.as_tensor(g_np, device="cuda")).sum().backward()
+    o = orc.Oracle(d.as_dict(), "f64")
+    inv_vol = 1.0 / d.voxel_volume()
+    assert rel_l2(vol.detach().cpu().numpy(), o.forward(p_np, pix) * inv_vol) < TOL
+    assert rel_l2(p.grad.cpu().numpy(), o.adjoint(g_np.astype(np.float64) * inv_vol, pix)) < TOL
+
+
+def test_host_buffer_calls(workdir):
+    scene, integ, sensor, d, _ = build("C1", workdir, 24)
+    pix = pixels_np(scene)
+    p, g = random_inputs(d, pix.size, 7)
+    h = Handle(d)
+    film = np.empty(d.film_shape(), np.float32)
+    _lib.check(h.lib.drtvam_forward_host(h.h, p.ctypes.data, pix.ctypes.data, p.size, 1, 0, 1.0, film.ctypes.data))
+    assert rel_l2(film, h.forward(p, pix)) < 1e-6
+    out = np.empty(pix.size, np.float32)
+    g = np.ascontiguousarray(g)
+    _lib.check(h.lib.drtvam_adjoint_host(h.h, g.ctypes.data, pix.ctypes.data, pix.size, 1, 0, 1.0, out.ctypes.data))
+    assert rel_l2(out, h.adjoint(g, pix)) < 1e-6
+
+
+def test_error_paths():
+    from drtvam_b200._scene import SceneDesc, SurfaceDesc
+    lib = _lib.load()
+    d = SceneDesc(sigma_t=0.0, surfaces=[SurfaceDesc(radius=1, z0=-1, z1=1, interior_medium=1)],
+                  motion_table=np.eye(4)[None])
+    cdesc, keep = d.to_c()
+    h = C.c_void_p()
+    assert lib.drtvam_scene_create(C.byref(cdesc), 0, C.byref(h)) == -1
+    assert b"extinction" in lib.drtvam_last_error()
+    d = SceneDesc(sigma_t=1.0, surfaces=[SurfaceDesc(radius=1, z0=-1, z1=1)], motion_table=np.eye(4)[None])
+    cdesc, keep = d.to_c()
+    assert lib.drtvam_scene_create(C.byref(cdesc), 0, C.byref(h)) == -1
+    assert b"No printing medium" in lib.drtvam_last_error()
