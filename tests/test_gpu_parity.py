@@ -81,16 +81,28 @@ def test_forward_and_adjoint_match_oracle_regular(name, general, workdir):
 
 @pytest.mark.parametrize("name", ["C1", "C3", "C4"])
 def test_jittered_sampling_matches_oracle(name, workdir):
+    """Jittered pixel positions (regular_sampling=false, the reference default):
+    both sides draw from the same PCG32/TEA streams.  A jittered ray that lands
+    within an ulp of a voxel-layer boundary moves its whole deposit to the other
+    layer when the arithmetic changes precision, so the 1e-4 bound is held
+    against the fp32 oracle build (the reference computes in fp32); against the
+    fp64 build the stated band is 1e-2 at this size (a handful of flipped rays
+    out of 64 000 -- the f32 and f64 oracle builds differ by the same amount)."""
     scene, integ, sensor, d, _ = build(name, workdir, 40, regular_sampling=False)
     pix = pixels_np(scene)
     p, g = random_inputs(d, pix.size, 4)
-    o = orc.Oracle(d.as_dict(), "f64")
+    o32 = orc.Oracle(d.as_dict(), "f32")
+    o64 = orc.Oracle(d.as_dict(), "f64")
     h = Handle(d)
     for spp, seed in ((1, 0), (4, 11)):
-        assert rel_l2(h.forward(p, pix, spp, seed), o.forward(p, pix, spp, seed)) < TOL
-        assert rel_l2(h.adjoint(g, pix, spp, seed), o.adjoint(g, pix, spp, seed)) < TOL
+        f = h.forward(p, pix, spp, seed)
+        a = h.adjoint(g, pix, spp, seed)
+        assert rel_l2(f, o32.forward(p, pix, spp, seed)) < TOL
+        assert rel_l2(a, o32.adjoint(g, pix, spp, seed)) < TOL
+        assert rel_l2(f, o64.forward(p, pix, spp, seed)) < 1e-2
+        assert rel_l2(a, o64.adjoint(g, pix, spp, seed)) < 1e-2
     # non power-of-two spp takes the atomic reduction path
-    assert rel_l2(h.adjoint(g, pix, 3, 5), o.adjoint(g, pix, 3, 5)) < TOL
+    assert rel_l2(h.adjoint(g, pix, 3, 5), o32.adjoint(g, pix, 3, 5)) < TOL
 
 
 def test_raygen_matches_oracle_all_projectors(workdir):
