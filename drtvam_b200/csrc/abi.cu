@@ -58,6 +58,10 @@ struct DrtvamScene {
     float print_time = 1.f;
     float* motion_dev = nullptr;
     bool force_general = false;
+    std::vector<float> motion_host;  // copy of the motion table for the plan check
+    PlanarHost planar;
+    bool planar_tried = false;       // planar_build ran for the current depth setting
+    bool planar_ok = false;
     Scratch host_io[3];      // device staging for the *_host calls
     unsigned long long* counter_dev = nullptr;
 };
@@ -90,6 +94,60 @@ int check_call(const DrtvamScene* s, uint64_t n_active, uint32_t& spp) {
                     "2^32 = 4294967296. Please use fewer samples per pixel or render using multiple passes.",
                     static_cast<unsigned long long>(lanes));
     return DRTVAM_OK;
+}
+
+// Host-side eligibility of the planar z-separable plan (see planar.cuh): every
+// ray must have d_z = 0, one deterministic medium segment that depends only on
+// (angle, column), and the film must be the plain single-channel DDA film.
+bool planar_static_eligible(const DrtvamScene* s) {
+    const SceneParams& P = s->P;
+    if (P.proj_kind != DRTVAM_PROJ_COLLIMATED || !P.regular_sampling || P.sample_time) return false;
+    if (P.albedo != 0.f || P.sensor_kind != DRTVAM_SENSOR_DDA || P.surface_aware) return false;
+    if (!P.transmission_only) return false;
+    if (P.max_depth < 1 || P.max_depth - 1 > P.rr_depth) return false;  // Russian roulette never fires
+    if (!P.motion_analytic) {
+        // rotation about z: world z = const * local y, no z component in the beam direction
+        const size_t n = static_cast<size_t>(P.n_patterns);
+        if (s->motion_host.size() < 12 * n) return false;
+        const float* M = s->motion_host.data();
+        for (size_t k = 0; k < n; ++k) {
+            const float* R = M + 12 * k + 8;
+            if (R[0] != 0.f || R[2] != 0.f) return false;
+            if (fabsf(R[1] - M[9]) > 1e-6f || fabsf(R[3] - M[11]) > 1e-6f) return false;
+        }
+    }
+    float zmax = fmaxf(fabsf(P.bmin[2]), fabsf(P.bmax[2]));
+    for (int i = 0; i < P.n_surf; ++i) {
+        const Surface& S = P.surf[i];
+        if (S.kind == DRTVAM_SURF_CYLINDER) {
+            if (!(S.z0 < P.bmin[2] && S.z1 > P.bmax[2])) return false;
+            // spawn offset (1 + max|p|) eps must not depend on z
+            if (!(S.radius * 0.70710678f >= zmax)) return false;
+        } else {
+            if (!(S.hz > zmax && S.hx >= zmax && S.hy >= zmax)) return false;
+        }
+    }
+    return true;
+}
+
+int ensure_planar(DrtvamScene* s) {
+    if (s->planar_tried) return DRTVAM_OK;
+    s->planar_tried = true;
+    s->planar_ok = false;
+    if (!planar_static_eligible(s)) return DRTVAM_OK;
+    cudaError_t e = planar_build(s->P, s->planar);
+    if (e != cudaSuccess) {
+        planar_release(s->planar);
+        return fail(DRTVAM_E_CUDA, "planar plan build failed: %s", cudaGetErrorString(e));
+    }
+    s->planar_ok = s->planar.valid && s->planar.flags == 0 && s->planar.n_rows_in_sensor > 0;
+    return DRTVAM_OK;
+}
+
+bool use_planar(DrtvamScene* s, uint64_t n_active) {
+    if (s->force_general || !s->planar_ok || n_active == 0) return false;
+    const uint64_t hw = static_cast<uint64_t>(s->P.res_x) * s->P.res_y;
+    return n_active % hw == 0;
 }
 
 size_t film_elems(const DrtvamScene* s) {
@@ -179,6 +237,7 @@ int drtvam_scene_create(const DrtvamSceneDesc* d, int device, DrtvamScene** out)
             return fail(DRTVAM_E_CUDA, "motion table upload failed: %s", cudaGetErrorString(e));
         }
         P.motion_table = s->motion_dev;
+        s->motion_host.assign(d->motion_table_host, d->motion_table_host + 12 * static_cast<size_t>(d->n_patterns));
     }
     cudaError_t e = cudaMalloc(&s->counter_dev, sizeof(unsigned long long));
     if (e != cudaSuccess) {
@@ -194,12 +253,14 @@ void drtvam_scene_destroy(DrtvamScene* s) {
     DeviceGuard guard(s->device);
     if (s->motion_dev) cudaFree(s->motion_dev);
     if (s->counter_dev) cudaFree(s->counter_dev);
+    planar_release(s->planar);
     for (auto& b : s->host_io) b.release();
     delete s;
 }
 
 int drtvam_scene_set_depth(DrtvamScene* s, int32_t max_depth, int32_t rr_depth) {
     if (!s) return fail(DRTVAM_E_INVALID, "scene handle is NULL");
+    if (s->P.max_depth != max_depth || s->P.rr_depth != rr_depth) s->planar_tried = false;
     s->P.max_depth = max_depth;
     s->P.rr_depth = rr_depth;
     return DRTVAM_OK;
@@ -211,9 +272,11 @@ int drtvam_scene_force_general(DrtvamScene* s, int32_t on) {
     return DRTVAM_OK;
 }
 
-int drtvam_scene_plan(DrtvamScene* s, uint64_t, uint32_t) {
+int drtvam_scene_plan(DrtvamScene* s, uint64_t n_active, uint32_t) {
     if (!s) return fail(DRTVAM_E_INVALID, "scene handle is NULL");
-    return 0;
+    DeviceGuard guard(s->device);
+    if (int rc = ensure_planar(s)) return rc;
+    return use_planar(s, n_active) ? 1 : 0;
 }
 
 int drtvam_forward(DrtvamScene* s, const float* active_data, const uint32_t* active_pixels, uint64_t n_active,
@@ -225,6 +288,15 @@ int drtvam_forward(DrtvamScene* s, const float* active_data, const uint32_t* act
     if (zero_first) CUDA_TRY(cudaMemsetAsync(dose, 0, sizeof(float) * film_elems(s), st));
     if (n_active == 0) return DRTVAM_OK;
     const float w = ray_weight(s, n_active, spp) * out_scale;
+    if (int rc = ensure_planar(s)) return rc;
+    if (use_planar(s, n_active)) {
+        // the device decides: gate = 0 -> planar kernels, gate != 0 -> general tracer
+        CUDA_TRY(launch_planar_check(s->P, s->planar, active_pixels, n_active, st));
+        CUDA_TRY(launch_planar_forward(s->P, s->planar, active_data, active_pixels, n_active, w, dose, st));
+        CUDA_TRY(launch_forward_general(s->P, active_data, active_pixels, n_active * spp, spp, seed, w, dose, st,
+                                        s->planar.gate));
+        return DRTVAM_OK;
+    }
     CUDA_TRY(launch_forward_general(s->P, active_data, active_pixels, n_active * spp, spp, seed, w, dose, st));
     return DRTVAM_OK;
 }
@@ -237,6 +309,15 @@ int drtvam_adjoint(DrtvamScene* s, const float* dose_grad, const uint32_t* activ
     DeviceGuard guard(s->device);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const float w = ray_weight(s, n_active, spp) * in_scale;
+    if (int rc = ensure_planar(s)) return rc;
+    if (use_planar(s, n_active)) {
+        CUDA_TRY(cudaMemsetAsync(pattern_grad, 0, sizeof(float) * n_active, st));
+        CUDA_TRY(launch_planar_check(s->P, s->planar, active_pixels, n_active, st));
+        CUDA_TRY(launch_planar_adjoint(s->P, s->planar, dose_grad, active_pixels, n_active, w, pattern_grad, st));
+        CUDA_TRY(launch_adjoint_general(s->P, dose_grad, active_pixels, n_active * spp, spp, seed, w, pattern_grad, st,
+                                        s->planar.gate));
+        return DRTVAM_OK;
+    }
     CUDA_TRY(launch_adjoint_general(s->P, dose_grad, active_pixels, n_active * spp, spp, seed, w, pattern_grad, st));
     return DRTVAM_OK;
 }

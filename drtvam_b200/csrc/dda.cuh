@@ -11,6 +11,7 @@ namespace drtvam {
 
 // Primal sink: red.global.add.f32 into the film (no return value -> REDG).
 struct ScatterSink {
+    static constexpr bool kRecordOnly = false;
     float* film;
     float em;  // emitted radiance * ray weight
     float unused = 0.f;
@@ -19,6 +20,7 @@ struct ScatterSink {
 
 // Adjoint sink: gather dL and accumulate d/d(em).
 struct GatherSink {
+    static constexpr bool kRecordOnly = false;
     const float* dL;
     float acc = 0.f;
     __device__ __forceinline__ void visit(size_t idx, float w) { acc = fmaf(w, __ldg(dL + idx), acc); }
@@ -26,6 +28,7 @@ struct GatherSink {
 
 // Counting sink (roofline units).
 struct CountSink {
+    static constexpr bool kRecordOnly = false;
     unsigned long long n = 0;
     __device__ __forceinline__ void visit(size_t, float) { ++n; }
 };

@@ -16,9 +16,10 @@ template <bool kScatter>
 __global__ void __launch_bounds__(kThreads)
 forward_general_kernel(const __grid_constant__ SceneParams P, const float* __restrict__ active_data,
                        const uint32_t* __restrict__ active_pixels, uint64_t n_lanes, uint32_t spp, uint32_t seed,
-                       float ray_weight, float* __restrict__ film) {
+                       float ray_weight, float* __restrict__ film, const int* __restrict__ gate) {
     const uint64_t lane = static_cast<uint64_t>(blockIdx.x) * kThreads + threadIdx.x;
     if (lane >= n_lanes) return;
+    if (gate && *gate == 0) return;  // the planar fast path owns this call
     const uint64_t j = lane / spp;
     const float em = __ldg(active_data + j) * ray_weight;
     if (em == 0.f && !kScatter) return;  // a zero pixel deposits nothing
@@ -33,7 +34,8 @@ template <bool kScatter>
 __global__ void __launch_bounds__(kThreads)
 adjoint_general_kernel(const __grid_constant__ SceneParams P, const float* __restrict__ dL,
                        const uint32_t* __restrict__ active_pixels, uint64_t n_lanes, uint32_t spp, uint32_t seed,
-                       float ray_weight, float* __restrict__ grad) {
+                       float ray_weight, float* __restrict__ grad, const int* __restrict__ gate) {
+    if (gate && *gate == 0) return;  // the planar fast path owns this call
     const uint64_t lane = static_cast<uint64_t>(blockIdx.x) * kThreads + threadIdx.x;
     const bool live = lane < n_lanes;
     const uint64_t j = live ? lane / spp : 0;
@@ -94,21 +96,21 @@ inline unsigned grid_for(uint64_t n_lanes) { return static_cast<unsigned>((n_lan
 
 cudaError_t launch_forward_general(const SceneParams& P, const float* active_data, const uint32_t* active_pixels,
                                    uint64_t n_lanes, uint32_t spp, uint32_t seed, float ray_weight, float* film,
-                                   cudaStream_t stream) {
+                                   cudaStream_t stream, const int* gate) {
     if (n_lanes == 0) return cudaSuccess;
     if (P.albedo != 0.f)
         forward_general_kernel<true><<<grid_for(n_lanes), kThreads, 0, stream>>>(P, active_data, active_pixels,
-                                                                                  n_lanes, spp, seed, ray_weight, film);
+                                                                                  n_lanes, spp, seed, ray_weight, film, gate);
     else
         forward_general_kernel<false><<<grid_for(n_lanes), kThreads, 0, stream>>>(P, active_data, active_pixels,
-                                                                                   n_lanes, spp, seed, ray_weight, film);
+                                                                                   n_lanes, spp, seed, ray_weight, film, gate);
     count_launch();
     return cudaGetLastError();
 }
 
 cudaError_t launch_adjoint_general(const SceneParams& P, const float* dL, const uint32_t* active_pixels,
                                    uint64_t n_lanes, uint32_t spp, uint32_t seed, float ray_weight, float* grad,
-                                   cudaStream_t stream) {
+                                   cudaStream_t stream, const int* gate) {
     if (n_lanes == 0) return cudaSuccess;
     const bool pow2 = (spp & (spp - 1)) == 0 && spp <= 32;
     if (!pow2) {
@@ -117,10 +119,10 @@ cudaError_t launch_adjoint_general(const SceneParams& P, const float* dL, const 
     }
     if (P.albedo != 0.f)
         adjoint_general_kernel<true><<<grid_for(n_lanes), kThreads, 0, stream>>>(P, dL, active_pixels, n_lanes, spp,
-                                                                                  seed, ray_weight, grad);
+                                                                                  seed, ray_weight, grad, gate);
     else
         adjoint_general_kernel<false><<<grid_for(n_lanes), kThreads, 0, stream>>>(P, dL, active_pixels, n_lanes, spp,
-                                                                                   seed, ray_weight, grad);
+                                                                                   seed, ray_weight, grad, gate);
     count_launch();
     return cudaGetLastError();
 }

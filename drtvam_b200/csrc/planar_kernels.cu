@@ -1,0 +1,458 @@
+// Planar (z-separable) fast path of the forward projection and its adjoint.
+//
+// Forward: CTA = (tile of one z-layer, angle group).  The tile lives in shared
+// memory; every thread takes one (angle, column) ray whose medium segment
+// crosses the tile, clips it to the tile and marches a 2-D voxel DDA with
+// shared-memory atomics (tile privatisation); the tile is flushed once with
+// vectorised red.global.add.v4.f32.  Adjoint: same walk in gather form over a
+// staged tile of the dose gradient, one red.global per ray and tile.
+// Reference: DDAVolumetricSensor.accumulate (sensor.py:306-440), film.write
+// (film.py:40-41), VolumeIntegrator.render / render_backward
+// (integrators/volume.py:18-56, 97-134).
+#include <vector>
+
+#include "kernels.h"
+#include "planar.cuh"
+#include "tracer.cuh"
+
+namespace drtvam {
+
+namespace {
+
+constexpr int kPlanarThreads = 256;
+constexpr float kLog2e = 1.4426950408889634f;
+
+// Records the medium segments of one lane instead of depositing them.
+struct RecordSink {
+    static constexpr bool kRecordOnly = true;
+    Ray seg;
+    float tmax = 0.f, w0 = 0.f;
+    int count = 0;
+    __device__ __forceinline__ void record(const Ray& r, float maxt, float w) {
+        if (count == 0) { seg = r; tmax = maxt; w0 = w; }
+        ++count;
+    }
+    __device__ __forceinline__ void visit(size_t, float) {}
+};
+
+// Segment table: one thread per (angle, column), traced at row `row_ref`
+// through the general interface loop so both plans share the same arithmetic.
+__global__ void __launch_bounds__(kPlanarThreads)
+planar_segments_kernel(const __grid_constant__ SceneParams P, int row_ref, float4* __restrict__ seg_a,
+                       float2* __restrict__ seg_b, int* __restrict__ flags) {
+    const int i = blockIdx.x * kPlanarThreads + threadIdx.x;
+    const int n = P.n_patterns * P.res_x;
+    if (i >= n) return;
+    const int k = i / P.res_x, c = i - k * P.res_x;
+    const uint32_t pixel = (static_cast<uint32_t>(k) * P.res_y + row_ref) * P.res_x + c;
+    Sampler rng;
+    rng.seed(0u, static_cast<uint32_t>(i));  // never consumed for a deterministic configuration
+    const Ray ray = generate_ray(P, pixel, rng);
+    RecordSink sink;
+    sink.seg = ray;
+    trace_lane<false>(P, ray, rng, sink);
+    int f = 0;
+    if (sink.count > 1) f |= kPlanarFlagMultiSegment;
+    if (sink.count >= 1 && sink.seg.dz != 0.f) f |= kPlanarFlagNotPlanar;
+    if (ray.dz != 0.f) f |= kPlanarFlagNotPlanar;
+    if (f) atomicOr(flags, f);
+    const bool ok = sink.count >= 1 && sink.w0 != 0.f && sink.tmax > 0.f && isfinite(sink.tmax);
+    seg_a[i] = make_float4(sink.seg.ox, sink.seg.oy, sink.seg.dx, sink.seg.dy);
+    seg_b[i] = ok ? make_float2(sink.tmax, sink.w0) : make_float2(0.f, 0.f);
+}
+
+// Layer each DMD row deposits in (the z part of sensor.py:328-346), -1 = none.
+__global__ void planar_row_layer_kernel(const __grid_constant__ SceneParams P, int* __restrict__ row_layer) {
+    const int row = blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= P.res_y) return;
+    Sampler rng;
+    rng.seed(0u, 0u);
+    const Ray ray = generate_ray(P, static_cast<uint32_t>(row) * P.res_x, rng);
+    int layer = -1;
+    if (ray.oz > P.bmin[2] && ray.oz < P.bmax[2]) {
+        const float vs = (P.bmax[2] - P.bmin[2]) / static_cast<float>(P.res[2]);
+        layer = min(max(__float2int_rz((ray.oz - P.bmin[2]) / vs), 0), P.res[2] - 1);
+    }
+    row_layer[row] = layer;
+}
+
+// Clip of a 2-D segment against the voxel rectangle [x0, x0+w) x [y0, y0+h).
+__device__ __forceinline__ bool clip_to_tile(const SceneParams& P, const float4 a, float tmax, int x0, int y0, int w,
+                                             int h, float& t0, float& t1) {
+    const float vsx = (P.bmax[0] - P.bmin[0]) / static_cast<float>(P.res[0]);
+    const float vsy = (P.bmax[1] - P.bmin[1]) / static_cast<float>(P.res[1]);
+    const float xl = P.bmin[0] + static_cast<float>(x0) * vsx, xh = P.bmin[0] + static_cast<float>(x0 + w) * vsx;
+    const float yl = P.bmin[1] + static_cast<float>(y0) * vsy, yh = P.bmin[1] + static_cast<float>(y0 + h) * vsy;
+    float tn = 0.f, tf = tmax;
+    if (fabsf(a.z) > 1e-8f) {
+        const float ta = (xl - a.x) / a.z, tb = (xh - a.x) / a.z;
+        tn = fmaxf(tn, fminf(ta, tb));
+        tf = fminf(tf, fmaxf(ta, tb));
+    } else if (a.x < xl || a.x >= xh) {
+        return false;
+    }
+    if (fabsf(a.w) > 1e-8f) {
+        const float ta = (yl - a.y) / a.w, tb = (yh - a.y) / a.w;
+        tn = fmaxf(tn, fminf(ta, tb));
+        tf = fminf(tf, fmaxf(ta, tb));
+    } else if (a.y < yl || a.y >= yh) {
+        return false;
+    }
+    t0 = tn;
+    t1 = tf;
+    return tn < tf;
+}
+
+// Column range of every (tile, angle): one thread each, scanning the columns.
+__global__ void planar_ranges_kernel(const __grid_constant__ SceneParams P, const PlanarPlan L, int* __restrict__ clo,
+                                     int* __restrict__ cnt) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n_tiles = L.tiles_x * L.tiles_y;
+    if (i >= n_tiles * P.n_patterns) return;
+    const int tile = i / P.n_patterns, k = i - tile * P.n_patterns;
+    const int x0 = (tile % L.tiles_x) * L.tile_w, y0 = (tile / L.tiles_x) * L.tile_h;
+    const int w = min(L.tile_w, P.res[0] - x0), h = min(L.tile_h, P.res[1] - y0);
+    int lo = P.res_x, hi = -1;
+    for (int c = 0; c < P.res_x; ++c) {
+        const float2 b = L.seg_b[k * P.res_x + c];
+        if (b.y == 0.f) continue;
+        float t0, t1;
+        if (clip_to_tile(P, L.seg_a[k * P.res_x + c], b.x, x0, y0, w, h, t0, t1)) {
+            lo = min(lo, c);
+            hi = max(hi, c);
+        }
+    }
+    clo[i] = hi >= lo ? lo : 0;
+    cnt[i] = hi >= lo ? hi - lo + 1 : 0;
+}
+
+// gate[0] != 0  <=>  active_pixels is not `base + j` with whole patterns, i.e.
+// the planar kernels must stand down and the general tracer runs instead.
+__global__ void planar_check_pixels_kernel(const uint32_t* __restrict__ active_pixels, uint64_t n_active, uint32_t hw,
+                                           int* __restrict__ gate) {
+    const uint64_t j = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    const uint32_t base = __ldg(active_pixels);
+    bool bad = false;
+    if (j == 0) bad = (base % hw) != 0;
+    if (j < n_active) bad = bad || (__ldg(active_pixels + j) != base + static_cast<uint32_t>(j));
+    if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) atomicOr(gate, 1);
+}
+
+}  // namespace
+
+namespace {
+
+__device__ __forceinline__ float ex2_approx(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
+                 : "memory");
+}
+
+// 2-D DDA of one clipped segment inside a tile.  Times are carried as
+// u = sigma_t * log2(e) * t so that the transmittance is ex2(-u); the deposit
+// of a voxel is the telescoped difference  E(u_in) - E(u_out)  which equals
+// e^{-sigma_t t} (1 - e^{-sigma_t dt})  of sensor.py:400-404.
+// kAdjoint = false: atomicAdd(tile[v], em * dE);  true: returns sum tile[v] * dE.
+template <bool kAdjoint>
+__device__ __forceinline__ float march_tile(const SceneParams& P, float* __restrict__ tile, int pitch, const float4 a,
+                                            float t0, float t1, int x0, int y0, int w, int h, float em) {
+    const float sig = P.sigma_t * kLog2e;
+    const float vsx = (P.bmax[0] - P.bmin[0]) / static_cast<float>(P.res[0]);
+    const float vsy = (P.bmax[1] - P.bmin[1]) / static_cast<float>(P.res[1]);
+    // entry / exit voxel: truncation then clip (sensor.py:345-346), tile-local
+    const float gx = fmaf(a.z, t0, a.x), gy = fmaf(a.w, t0, a.y);
+    const float hx = fmaf(a.z, t1, a.x), hy = fmaf(a.w, t1, a.y);
+    const int ix = min(max(__float2int_rz((gx - P.bmin[0]) / vsx) - x0, 0), w - 1);
+    const int iy = min(max(__float2int_rz((gy - P.bmin[1]) / vsy) - y0, 0), h - 1);
+    const int jx = min(max(__float2int_rz((hx - P.bmin[0]) / vsx) - x0, 0), w - 1);
+    const int jy = min(max(__float2int_rz((hy - P.bmin[1]) / vsy) - y0, 0), h - 1);
+
+    float ux = INFINITY, uy = INFINITY, ax = 0.f, bx = 0.f, ay = 0.f, by = 0.f, fx = 0.f, fy = 0.f;
+    float sfx = 0.f, sfy = 0.f;
+    int sx = 0, sy = 0, nx = 0, ny = 0;
+    if (fabsf(a.z) > 1e-8f) {
+        const float inv = sig / a.z;
+        const bool pos = a.z > 0.f;
+        sx = pos ? 1 : -1;
+        sfx = pos ? 1.f : -1.f;
+        nx = max((jx - ix) * sx, 0);
+        fx = static_cast<float>(x0 + ix + (pos ? 1 : 0));  // index of the next x boundary
+        ax = vsx * inv;
+        bx = (P.bmin[0] - a.x) * inv;
+        if (nx > 0) ux = fmaf(fx, ax, bx);
+    }
+    if (fabsf(a.w) > 1e-8f) {
+        const float inv = sig / a.w;
+        const bool pos = a.w > 0.f;
+        sy = pos ? pitch : -pitch;
+        sfy = pos ? 1.f : -1.f;
+        ny = max((jy - iy) * (pos ? 1 : -1), 0);
+        fy = static_cast<float>(y0 + iy + (pos ? 1 : 0));
+        ay = vsy * inv;
+        by = (P.bmin[1] - a.y) * inv;
+        if (ny > 0) uy = fmaf(fy, ay, by);
+    }
+    int idx = (iy + 1) * pitch + ix + 1;  // one-voxel halo around the tile
+    float e_prev = ex2_approx(-sig * t0);
+    float acc = 0.f;
+    for (int n = nx + ny; n > 0; --n) {
+        const float e = ex2_approx(-fminf(ux, uy));
+        const float de = e_prev - e;
+        e_prev = e;
+        if (kAdjoint) acc = fmaf(tile[idx], de, acc);
+        else atomicAdd(tile + idx, em * de);
+        if (ux <= uy) {
+            fx += sfx;
+            ux = fmaf(fx, ax, bx);
+            idx += sx;
+        } else {
+            fy += sfy;
+            uy = fmaf(fy, ay, by);
+            idx += sy;
+        }
+    }
+    const float de = e_prev - ex2_approx(-sig * t1);
+    if (kAdjoint) acc = fmaf(tile[idx], de, acc);
+    else atomicAdd(tile + idx, em * de);
+    return acc;
+}
+
+// kAdjoint = false: in = active_data [n_active], out = film (accumulated with red.global)
+// kAdjoint = true : in = dL (film layout), out = pattern_grad [n_active] (pre-zeroed, red.global)
+template <bool kAdjoint>
+__global__ void __launch_bounds__(kPlanarThreads)
+planar_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ PlanarPlan L,
+              const float* __restrict__ in, float* __restrict__ out, const uint32_t* __restrict__ active_pixels,
+              uint64_t n_active, float ray_weight, const int* __restrict__ gate) {
+    extern __shared__ __align__(16) float smem[];
+    if (*gate != 0) return;
+    const int tile_id = blockIdx.x, layer = blockIdx.y, group = blockIdx.z;
+    const int rb = L.layer_row_begin[layer], re = L.layer_row_begin[layer + 1];
+    if (rb == re) return;
+
+    const int x0 = (tile_id % L.tiles_x) * L.tile_w, y0 = (tile_id / L.tiles_x) * L.tile_h;
+    const int w = min(L.tile_w, P.res[0] - x0), h = min(L.tile_h, P.res[1] - y0);
+    const int pitch = L.pitch;
+    float* tile = smem;
+    int* off = reinterpret_cast<int*>(smem + (L.tile_h + 2) * pitch);
+    int* clo = off + P.n_patterns + 1;
+
+    const uint32_t hw = static_cast<uint32_t>(P.res_x) * P.res_y;
+    const uint32_t base = __ldg(active_pixels);
+    const int k0 = base / hw, nk = static_cast<int>(n_active / hw);
+    const int ka = k0 + static_cast<int>(static_cast<long long>(nk) * group / L.groups);
+    const int kb = k0 + static_cast<int>(static_cast<long long>(nk) * (group + 1) / L.groups);
+
+    for (int i = threadIdx.x; i <= P.n_patterns; i += kPlanarThreads)
+        off[i] = L.tile_off[tile_id * (P.n_patterns + 1) + i];
+    for (int i = threadIdx.x; i < P.n_patterns; i += kPlanarThreads) clo[i] = L.tile_clo[tile_id * P.n_patterns + i];
+    const size_t layer_base = static_cast<size_t>(layer) * P.res[0] * P.res[1];
+    for (int i = threadIdx.x; i < (h + 2) * pitch; i += kPlanarThreads) {
+        float v = 0.f;
+        if (kAdjoint) {
+            const int yy = i / pitch - 1, xx = i - (yy + 1) * pitch - 1;
+            if (yy >= 0 && yy < h && xx >= 0 && xx < w)
+                v = __ldg(in + layer_base + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx));
+        }
+        tile[i] = v;
+    }
+    __syncthreads();
+
+    const int f_base = off[ka], total = off[kb] - f_base;
+    for (int ri = rb; ri < re; ++ri) {
+        const int row = L.layer_rows[ri];
+        int k = ka;
+        for (int f = threadIdx.x; f < total; f += kPlanarThreads) {
+            const int g = f + f_base;
+            while (off[k + 1] <= g) ++k;
+            const int c = clo[k] + (g - off[k]);
+            const int s = k * P.res_x + c;
+            const float2 b = __ldg(L.seg_b + s);
+            if (b.y == 0.f) continue;
+            const size_t j = (static_cast<size_t>(k - k0) * P.res_y + row) * P.res_x + c;
+            float em = 0.f;
+            if (!kAdjoint) {
+                em = __ldg(in + j) * (ray_weight * b.y);
+                if (em == 0.f) continue;
+            }
+            const float4 a = __ldg(L.seg_a + s);
+            float t0, t1;
+            if (!clip_to_tile(P, a, b.x, x0, y0, w, h, t0, t1)) continue;
+            const float acc = march_tile<kAdjoint>(P, tile, pitch, a, t0, t1, x0, y0, w, h, em);
+            if (kAdjoint && acc != 0.f) atomicAdd(out + j, acc * (ray_weight * b.y));
+        }
+    }
+    if (kAdjoint) return;
+    __syncthreads();
+
+    // flush: vectorised red.global.add when the tile rows are 16-byte aligned in the film
+    float* dst = out + layer_base;
+    if (((x0 | w | P.res[0]) & 3) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
+        const int w4 = w >> 2;
+        for (int i = threadIdx.x; i < h * w4; i += kPlanarThreads) {
+            const int yy = i / w4, xx = (i - yy * w4) << 2;
+            const float* t = tile + (yy + 1) * pitch + xx + 1;
+            red_add_v4(dst + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx), t[0], t[1], t[2], t[3]);
+        }
+    } else {
+        for (int i = threadIdx.x; i < h * w; i += kPlanarThreads) {
+            const int yy = i / w, xx = i - yy * w;
+            atomicAdd(dst + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx), tile[(yy + 1) * pitch + xx + 1]);
+        }
+    }
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------
+#define PL_TRY(expr)                        \
+    do {                                    \
+        cudaError_t _e = (expr);            \
+        if (_e != cudaSuccess) return _e;   \
+    } while (0)
+
+void planar_release(PlanarHost& H) {
+    void* ptrs[] = {H.seg_a, H.seg_b, H.layer_row_begin, H.layer_rows, H.tile_off, H.tile_clo, H.gate};
+    for (void* p : ptrs)
+        if (p) cudaFree(p);
+    H = PlanarHost();
+}
+
+// Builds the segment table, the layer -> rows CSR and the per-tile column
+// ranges.  Synchronous (runs once per scene and depth setting).
+cudaError_t planar_build(const SceneParams& P, PlanarHost& H) {
+    planar_release(H);
+    const int np = P.n_patterns, W = P.res_x, Hh = P.res_y;
+    const int rx = P.res[0], ry = P.res[1], rz = P.res[2];
+    constexpr int kMaxTile = 128;
+    PlanarPlan& L = H.plan;
+    L.tiles_x = (rx + kMaxTile - 1) / kMaxTile;
+    L.tiles_y = (ry + kMaxTile - 1) / kMaxTile;
+    L.tile_w = (((rx + L.tiles_x - 1) / L.tiles_x) + 3) & ~3;
+    L.tile_h = (ry + L.tiles_y - 1) / L.tiles_y;
+    L.tiles_x = (rx + L.tile_w - 1) / L.tile_w;
+    L.pitch = (L.tile_w + 2) | 1;
+    L.groups = 1;
+    const int n_tiles = L.tiles_x * L.tiles_y;
+    H.smem_bytes = sizeof(float) * static_cast<size_t>(L.tile_h + 2) * L.pitch + sizeof(int) * (2 * np + 1);
+
+    PL_TRY(cudaMalloc(&H.seg_a, sizeof(float4) * np * W));
+    PL_TRY(cudaMalloc(&H.seg_b, sizeof(float2) * np * W));
+    PL_TRY(cudaMalloc(&H.layer_row_begin, sizeof(int) * (rz + 1)));
+    PL_TRY(cudaMalloc(&H.layer_rows, sizeof(int) * Hh));
+    PL_TRY(cudaMalloc(&H.tile_off, sizeof(int) * n_tiles * (np + 1)));
+    PL_TRY(cudaMalloc(&H.tile_clo, sizeof(int) * n_tiles * np));
+    PL_TRY(cudaMalloc(&H.gate, sizeof(int) * 2));
+    PL_TRY(cudaMemset(H.gate, 0, sizeof(int) * 2));
+    L.seg_a = H.seg_a; L.seg_b = H.seg_b;
+    L.layer_row_begin = H.layer_row_begin; L.layer_rows = H.layer_rows;
+    L.tile_off = H.tile_off; L.tile_clo = H.tile_clo;
+
+    // rows -> layers
+    int* row_layer_dev = nullptr;
+    PL_TRY(cudaMalloc(&row_layer_dev, sizeof(int) * Hh));
+    planar_row_layer_kernel<<<(Hh + 127) / 128, 128>>>(P, row_layer_dev);
+    count_launch();
+    std::vector<int> row_layer(Hh);
+    cudaError_t e = cudaMemcpy(row_layer.data(), row_layer_dev, sizeof(int) * Hh, cudaMemcpyDeviceToHost);
+    cudaFree(row_layer_dev);
+    PL_TRY(e);
+    std::vector<int> begin(rz + 1, 0), rows;
+    int row_ref = -1;
+    for (int r = 0; r < Hh; ++r)
+        if (row_layer[r] >= 0) { ++begin[row_layer[r] + 1]; if (row_ref < 0) row_ref = r; }
+    for (int z = 0; z < rz; ++z) begin[z + 1] += begin[z];
+    rows.assign(Hh, 0);
+    {
+        std::vector<int> cur(begin.begin(), begin.end() - 1);
+        for (int r = 0; r < Hh; ++r)
+            if (row_layer[r] >= 0) rows[cur[row_layer[r]]++] = r;
+    }
+    H.n_rows_in_sensor = begin[rz];
+    PL_TRY(cudaMemcpy(H.layer_row_begin, begin.data(), sizeof(int) * (rz + 1), cudaMemcpyHostToDevice));
+    PL_TRY(cudaMemcpy(H.layer_rows, rows.data(), sizeof(int) * Hh, cudaMemcpyHostToDevice));
+    if (row_ref < 0) row_ref = Hh / 2;
+
+    // segment table (flags live in gate[1])
+    planar_segments_kernel<<<(np * W + kPlanarThreads - 1) / kPlanarThreads, kPlanarThreads>>>(P, row_ref, H.seg_a,
+                                                                                             H.seg_b, H.gate + 1);
+    count_launch();
+    PL_TRY(cudaGetLastError());
+    int flags = 0;
+    PL_TRY(cudaMemcpy(&flags, H.gate + 1, sizeof(int), cudaMemcpyDeviceToHost));
+    H.flags = flags;
+
+    // per-tile column ranges and their prefix sums
+    int* cnt_dev = nullptr;
+    PL_TRY(cudaMalloc(&cnt_dev, sizeof(int) * n_tiles * np));
+    planar_ranges_kernel<<<(n_tiles * np + 127) / 128, 128>>>(P, L, H.tile_clo, cnt_dev);
+    count_launch();
+    std::vector<int> cnt(static_cast<size_t>(n_tiles) * np), off(static_cast<size_t>(n_tiles) * (np + 1));
+    e = cudaMemcpy(cnt.data(), cnt_dev, sizeof(int) * cnt.size(), cudaMemcpyDeviceToHost);
+    cudaFree(cnt_dev);
+    PL_TRY(e);
+    for (int t = 0; t < n_tiles; ++t) {
+        int acc = 0;
+        for (int k = 0; k < np; ++k) { off[t * (np + 1) + k] = acc; acc += cnt[t * np + k]; }
+        off[t * (np + 1) + np] = acc;
+    }
+    PL_TRY(cudaMemcpy(H.tile_off, off.data(), sizeof(int) * off.size(), cudaMemcpyHostToDevice));
+
+    PL_TRY(cudaFuncSetAttribute(planar_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                static_cast<int>(H.smem_bytes)));
+    PL_TRY(cudaFuncSetAttribute(planar_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                static_cast<int>(H.smem_bytes)));
+    H.valid = true;
+    return cudaSuccess;
+}
+
+static int planar_groups(const SceneParams& P, const PlanarPlan& L, uint64_t n_active) {
+    const long long ctas = static_cast<long long>(L.tiles_x) * L.tiles_y * P.res[2];
+    const long long nk = static_cast<long long>(n_active / (static_cast<uint64_t>(P.res_x) * P.res_y));
+    long long g = (148 * 8 + ctas - 1) / ctas;
+    if (g > nk) g = nk;
+    if (g > 32) g = 32;
+    return g < 1 ? 1 : static_cast<int>(g);
+}
+
+cudaError_t launch_planar_check(const SceneParams& P, PlanarHost& H, const uint32_t* active_pixels, uint64_t n_active,
+                                cudaStream_t stream) {
+    PL_TRY(cudaMemsetAsync(H.gate, 0, sizeof(int), stream));
+    const uint32_t hw = static_cast<uint32_t>(P.res_x) * P.res_y;
+    planar_check_pixels_kernel<<<static_cast<unsigned>((n_active + 255) / 256), 256, 0, stream>>>(active_pixels,
+                                                                                                n_active, hw, H.gate);
+    count_launch();
+    return cudaGetLastError();
+}
+
+cudaError_t launch_planar_forward(const SceneParams& P, PlanarHost& H, const float* active_data,
+                                  const uint32_t* active_pixels, uint64_t n_active, float ray_weight, float* film,
+                                  cudaStream_t stream) {
+    PlanarPlan L = H.plan;
+    L.groups = planar_groups(P, L, n_active);
+    const dim3 grid(L.tiles_x * L.tiles_y, P.res[2], L.groups);
+    planar_kernel<false><<<grid, kPlanarThreads, H.smem_bytes, stream>>>(P, L, active_data, film, active_pixels,
+                                                                        n_active, ray_weight, H.gate);
+    count_launch();
+    return cudaGetLastError();
+}
+
+cudaError_t launch_planar_adjoint(const SceneParams& P, PlanarHost& H, const float* dL, const uint32_t* active_pixels,
+                                  uint64_t n_active, float ray_weight, float* grad, cudaStream_t stream) {
+    PlanarPlan L = H.plan;
+    L.groups = planar_groups(P, L, n_active);
+    const dim3 grid(L.tiles_x * L.tiles_y, P.res[2], L.groups);
+    planar_kernel<true><<<grid, kPlanarThreads, H.smem_bytes, stream>>>(P, L, dL, grad, active_pixels, n_active,
+                                                                       ray_weight, H.gate);
+    count_launch();
+    return cudaGetLastError();
+}
+
+}  // namespace drtvam

@@ -95,7 +95,8 @@ __device__ __forceinline__ void trace_lane(const SceneParams& P, Ray ray, Sample
 
         if (deposit) {
             // both collision and surface lanes deposit along the whole [0, si.t] (volume.py:216)
-            if (P.sensor_kind == 1) ratio_segment(P, ray, H.t, attenuation * absorb, inside_target, rng, sink);
+            if constexpr (Sink::kRecordOnly) sink.record(ray, H.t, attenuation * absorb);
+            else if (P.sensor_kind == 1) ratio_segment(P, ray, H.t, attenuation * absorb, inside_target, rng, sink);
             else dda_segment(P, ray, H.t, attenuation * absorb, inside_target, sink);
         }
 

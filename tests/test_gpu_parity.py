@@ -265,3 +265,91 @@ def test_error_paths():
     cdesc, keep = d.to_c()
     assert lib.drtvam_scene_create(C.byref(cdesc), 0, C.byref(h)) == -1
     assert b"No printing medium" in lib.drtvam_last_error()
+
+
+# ---------------------------------------------------------------------------
+# planar (z-separable, shared-memory tile) plan vs the general tracer
+# ---------------------------------------------------------------------------
+def _plan(h, n_active, spp=1):
+    return h.lib.drtvam_scene_plan(h.h, n_active, spp)
+
+
+@pytest.mark.parametrize("name", ["C1", "C2", "C3", "C4"])
+def test_planar_plan_selected_and_matches_general(name, workdir):
+    """The deterministic collimated configs take the planar plan; it must agree
+    with the general per-lane tracer (same arithmetic for the interfaces, a
+    re-associated DDA) far inside the 1e-4 bound, on a grid that is split into
+    several tiles (n = 160 > 128)."""
+    scene, integ, sensor, d, _ = build(name, workdir, 160, n_patterns=24)
+    pix = pixels_np(scene)
+    p, g = random_inputs(d, pix.size, 11)
+    p = (p - 0.4).astype(np.float32)
+    fast, slow = Handle(d), Handle(d, force_general=True)
+    assert _plan(fast, pix.size) == 1 and _plan(slow, pix.size) == 0
+    assert rel_l2(fast.forward(p, pix), slow.forward(p, pix)) < 2e-5
+    assert rel_l2(fast.adjoint(g, pix), slow.adjoint(g, pix)) < 2e-5
+
+
+def test_planar_rectangular_grid_and_scale(workdir):
+    """Grid != DMD resolution and not a multiple of 4 (scalar flush path),
+    several DMD rows per layer, out_scale and accumulate (zero_first = 0)."""
+    scene, integ, sensor, d, _ = build("C3", workdir, 96, n_patterns=16, grid=54)
+    pix = pixels_np(scene)
+    p, g = random_inputs(d, pix.size, 12)
+    o = orc.Oracle(d.as_dict(), "f64")
+    h = Handle(d)
+    assert _plan(h, pix.size) == 1
+    ref = o.forward(p, pix)
+    assert rel_l2(h.forward(p, pix, scale=3.0), 3.0 * ref) < TOL
+    assert rel_l2(h.adjoint(g, pix, scale=0.5), 0.5 * o.adjoint(g, pix)) < TOL
+    # accumulate into an existing film
+    pt = torch.as_tensor(p, device="cuda")
+    pixt = torch.as_tensor(pix.astype(np.int64), device="cuda").to(torch.int32)
+    film = torch.ones(d.film_shape(), device="cuda")
+    _lib.check(h.lib.drtvam_forward(h.h, pt.data_ptr(), pixt.data_ptr(), pt.numel(), 1, 0, 1.0, film.data_ptr(), 0, None))
+    assert rel_l2(film.cpu().numpy() - 1.0, ref) < TOL
+
+
+def test_planar_angle_shard_and_sparse_fallback(workdir):
+    """An angle shard (active_pixels = base + j) stays on the planar plan; a
+    sparse / permuted pixel list makes the device-side gate hand the call to the
+    general tracer.  Both must match the oracle."""
+    scene, integ, sensor, d, _ = build("C2", workdir, 64, n_patterns=12)
+    pix = pixels_np(scene)
+    hw = d.res_x * d.res_y
+    o = orc.Oracle(d.as_dict(), "f64")
+    h = Handle(d)
+    shard = pix[5 * hw:9 * hw]
+    p, g = random_inputs(d, shard.size, 13)
+    assert _plan(h, shard.size) == 1
+    assert rel_l2(h.forward(p, shard), o.forward(p, shard)) < TOL
+    assert rel_l2(h.adjoint(g, shard), o.adjoint(g, shard)) < TOL
+    rng = np.random.default_rng(0)
+    perm = rng.permutation(pix)[:4 * hw].astype(np.uint32)  # same length as a 4-angle shard, not affine
+    p2 = rng.random(perm.size).astype(np.float32)
+    assert rel_l2(h.forward(p2, perm), o.forward(p2, perm)) < TOL
+    assert rel_l2(h.adjoint(g, perm), o.adjoint(g, perm)) < TOL
+
+
+def test_planar_not_selected_for_stochastic_configs(workdir):
+    scene, integ, sensor, d, _ = build("C1", workdir, 32, regular_sampling=False)
+    assert _plan(Handle(d), 32 ** 3) == 0
+    scene, integ, sensor, d, _ = build("C5", workdir, 32, spp=2)
+    assert _plan(Handle(d), 32 ** 3) == 0
+
+
+def test_planar_progressive_depth(workdir):
+    """optimize.py:123,288-289: max_depth 3 for the first iterations, then the
+    configured depth; the segment table is rebuilt on drtvam_scene_set_depth."""
+    scene, integ, sensor, d, _ = build("C3", workdir, 48)
+    pix = pixels_np(scene)
+    p, _ = random_inputs(d, pix.size, 14)
+    h = Handle(d)
+    full = h.forward(p, pix)
+    _lib.check(h.lib.drtvam_scene_set_depth(h.h, 3, 6))
+    d.max_depth = 3
+    assert rel_l2(h.forward(p, pix), orc.Oracle(d.as_dict(), "f64").forward(p, pix)) < TOL
+    _lib.check(h.lib.drtvam_scene_set_depth(h.h, 2, 6))
+    assert np.abs(h.forward(p, pix)).max() == 0.0  # two interface events never reach the resin
+    _lib.check(h.lib.drtvam_scene_set_depth(h.h, 6, 6))
+    assert rel_l2(h.forward(p, pix), full) < 1e-6
