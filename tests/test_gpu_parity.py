@@ -86,8 +86,9 @@ def test_jittered_sampling_matches_oracle(name, workdir):
     within an ulp of a voxel-layer boundary moves its whole deposit to the other
     layer when the arithmetic changes precision, so the 1e-4 bound is held
     against the fp32 oracle build (the reference computes in fp32); against the
-    fp64 build the stated band is 1e-2 at this size (a handful of flipped rays
-    out of 64 000 -- the f32 and f64 oracle builds differ by the same amount)."""
+    fp64 build the stated band is 3e-2 at this size (a handful of flipped rays
+    out of 64 000 -- the f32 and f64 oracle builds differ by the same amount,
+    up to 1.9e-2 for the square vial's adjoint)."""
     scene, integ, sensor, d, _ = build(name, workdir, 40, regular_sampling=False)
     pix = pixels_np(scene)
     p, g = random_inputs(d, pix.size, 4)
@@ -99,8 +100,8 @@ def test_jittered_sampling_matches_oracle(name, workdir):
         a = h.adjoint(g, pix, spp, seed)
         assert rel_l2(f, o32.forward(p, pix, spp, seed)) < TOL
         assert rel_l2(a, o32.adjoint(g, pix, spp, seed)) < TOL
-        assert rel_l2(f, o64.forward(p, pix, spp, seed)) < 1e-2
-        assert rel_l2(a, o64.adjoint(g, pix, spp, seed)) < 1e-2
+        assert rel_l2(f, o64.forward(p, pix, spp, seed)) < 3e-2
+        assert rel_l2(a, o64.adjoint(g, pix, spp, seed)) < 3e-2
     # non power-of-two spp takes the atomic reduction path
     assert rel_l2(h.adjoint(g, pix, 3, 5), o32.adjoint(g, pix, 3, 5)) < TOL
 
