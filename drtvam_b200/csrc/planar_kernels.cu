@@ -9,6 +9,9 @@
 // Reference: DDAVolumetricSensor.accumulate (sensor.py:306-440), film.write
 // (film.py:40-41), VolumeIntegrator.render / render_backward
 // (integrators/volume.py:18-56, 97-134).
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
 #include <vector>
 
 #include "kernels.h"
@@ -138,6 +141,7 @@ __global__ void planar_check_pixels_kernel(const uint32_t* __restrict__ active_p
     if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) atomicOr(gate, 1);
 }
 
+
 }  // namespace
 
 namespace {
@@ -153,12 +157,18 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
                  : "memory");
 }
 
+// Kernel modes.  The forward tile accumulates with fp32 atomicAdd, which is an
+// LDS + ATOMS.CAST.SPIN loop on shared memory.  An int32 fixed-point tile with
+// native ATOMS.ADD.S32 was measured 2.4x slower on B200 (76.9 ms against
+// 31.5 ms per forward pass at C2, profiles/r01_notes.md) and was dropped.
+constexpr int kScatter = 0, kGather = 1;
+
 // 2-D DDA of one clipped segment inside a tile.  Times are carried as
 // u = sigma_t * log2(e) * t so that the transmittance is ex2(-u); the deposit
 // of a voxel is the telescoped difference  E(u_in) - E(u_out)  which equals
 // e^{-sigma_t t} (1 - e^{-sigma_t dt})  of sensor.py:400-404.
-// kAdjoint = false: atomicAdd(tile[v], em * dE);  true: returns sum tile[v] * dE.
-template <bool kAdjoint>
+// Scatter modes add em * dE to tile[v]; the gather mode returns sum tile[v] * dE.
+template <int kMode>
 __device__ __forceinline__ float march_tile(const SceneParams& P, float* __restrict__ tile, int pitch, const float4 a,
                                             float t0, float t1, int x0, int y0, int w, int h, float em) {
     const float sig = P.sigma_t * kLog2e;
@@ -178,9 +188,9 @@ __device__ __forceinline__ float march_tile(const SceneParams& P, float* __restr
     if (fabsf(a.z) > 1e-8f) {
         const float inv = sig / a.z;
         const bool pos = a.z > 0.f;
-        sx = pos ? 1 : -1;
+        sx = pos ? 4 : -4;  // byte strides
         sfx = pos ? 1.f : -1.f;
-        nx = max((jx - ix) * sx, 0);
+        nx = max(pos ? jx - ix : ix - jx, 0);
         fx = static_cast<float>(x0 + ix + (pos ? 1 : 0));  // index of the next x boundary
         ax = vsx * inv;
         bx = (P.bmin[0] - a.x) * inv;
@@ -189,42 +199,50 @@ __device__ __forceinline__ float march_tile(const SceneParams& P, float* __restr
     if (fabsf(a.w) > 1e-8f) {
         const float inv = sig / a.w;
         const bool pos = a.w > 0.f;
-        sy = pos ? pitch : -pitch;
+        sy = pos ? 4 * pitch : -4 * pitch;
         sfy = pos ? 1.f : -1.f;
-        ny = max((jy - iy) * (pos ? 1 : -1), 0);
+        ny = max(pos ? jy - iy : iy - jy, 0);
         fy = static_cast<float>(y0 + iy + (pos ? 1 : 0));
         ay = vsy * inv;
         by = (P.bmin[1] - a.y) * inv;
         if (ny > 0) uy = fmaf(fy, ay, by);
     }
-    int idx = (iy + 1) * pitch + ix + 1;  // one-voxel halo around the tile
+    // one-voxel halo around the tile; shared-window byte address
+    uint32_t addr = static_cast<uint32_t>(__cvta_generic_to_shared(tile)) + 4u * ((iy + 1) * pitch + ix + 1);
     float e_prev = ex2_approx(-sig * t0);
     float acc = 0.f;
+    auto deposit = [&](float de) {
+        if (kMode == kGather) {
+            float v;
+            asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+            acc = fmaf(v, de, acc);
+        } else {
+            float* ptr;
+            asm("cvta.shared.u64 %0, %1;" : "=l"(ptr) : "l"(static_cast<unsigned long long>(addr)));
+            atomicAdd(ptr, em * de);
+        }
+    };
     for (int n = nx + ny; n > 0; --n) {
         const float e = ex2_approx(-fminf(ux, uy));
-        const float de = e_prev - e;
+        deposit(e_prev - e);
         e_prev = e;
-        if (kAdjoint) acc = fmaf(tile[idx], de, acc);
-        else atomicAdd(tile + idx, em * de);
         if (ux <= uy) {
             fx += sfx;
             ux = fmaf(fx, ax, bx);
-            idx += sx;
+            addr += sx;
         } else {
             fy += sfy;
             uy = fmaf(fy, ay, by);
-            idx += sy;
+            addr += sy;
         }
     }
-    const float de = e_prev - ex2_approx(-sig * t1);
-    if (kAdjoint) acc = fmaf(tile[idx], de, acc);
-    else atomicAdd(tile + idx, em * de);
+    deposit(e_prev - ex2_approx(-sig * t1));
     return acc;
 }
 
-// kAdjoint = false: in = active_data [n_active], out = film (accumulated with red.global)
-// kAdjoint = true : in = dL (film layout), out = pattern_grad [n_active] (pre-zeroed, red.global)
-template <bool kAdjoint>
+// kScatter: in = active_data [n_active], out = film (accumulated with red.global)
+// kGather  : in = dL (film layout), out = pattern_grad [n_active] (pre-zeroed, red.global)
+template <int kMode>
 __global__ void __launch_bounds__(kPlanarThreads)
 planar_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ PlanarPlan L,
               const float* __restrict__ in, float* __restrict__ out, const uint32_t* __restrict__ active_pixels,
@@ -254,7 +272,7 @@ planar_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pla
     const size_t layer_base = static_cast<size_t>(layer) * P.res[0] * P.res[1];
     for (int i = threadIdx.x; i < (h + 2) * pitch; i += kPlanarThreads) {
         float v = 0.f;
-        if (kAdjoint) {
+        if (kMode == kGather) {
             const int yy = i / pitch - 1, xx = i - (yy + 1) * pitch - 1;
             if (yy >= 0 && yy < h && xx >= 0 && xx < w)
                 v = __ldg(in + layer_base + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx));
@@ -276,33 +294,37 @@ planar_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pla
             if (b.y == 0.f) continue;
             const size_t j = (static_cast<size_t>(k - k0) * P.res_y + row) * P.res_x + c;
             float em = 0.f;
-            if (!kAdjoint) {
+            if (kMode != kGather) {
                 em = __ldg(in + j) * (ray_weight * b.y);
                 if (em == 0.f) continue;
             }
             const float4 a = __ldg(L.seg_a + s);
             float t0, t1;
             if (!clip_to_tile(P, a, b.x, x0, y0, w, h, t0, t1)) continue;
-            const float acc = march_tile<kAdjoint>(P, tile, pitch, a, t0, t1, x0, y0, w, h, em);
-            if (kAdjoint && acc != 0.f) atomicAdd(out + j, acc * (ray_weight * b.y));
+            const float acc = march_tile<kMode>(P, tile, pitch, a, t0, t1, x0, y0, w, h, em);
+            if (kMode == kGather && acc != 0.f) atomicAdd(out + j, acc * (ray_weight * b.y));
         }
     }
-    if (kAdjoint) return;
+    if (kMode == kGather) return;
     __syncthreads();
 
     // flush: vectorised red.global.add when the tile rows are 16-byte aligned in the film
+    auto value = [&](int i) { return tile[i]; };
     float* dst = out + layer_base;
     if (((x0 | w | P.res[0]) & 3) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
         const int w4 = w >> 2;
         for (int i = threadIdx.x; i < h * w4; i += kPlanarThreads) {
             const int yy = i / w4, xx = (i - yy * w4) << 2;
-            const float* t = tile + (yy + 1) * pitch + xx + 1;
-            red_add_v4(dst + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx), t[0], t[1], t[2], t[3]);
+            const int t = (yy + 1) * pitch + xx + 1;
+            const float v0 = value(t), v1 = value(t + 1), v2 = value(t + 2), v3 = value(t + 3);
+            if (v0 != 0.f || v1 != 0.f || v2 != 0.f || v3 != 0.f)
+                red_add_v4(dst + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx), v0, v1, v2, v3);
         }
     } else {
         for (int i = threadIdx.x; i < h * w; i += kPlanarThreads) {
             const int yy = i / w, xx = i - yy * w;
-            atomicAdd(dst + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx), tile[(yy + 1) * pitch + xx + 1]);
+            const float v = value((yy + 1) * pitch + xx + 1);
+            if (v != 0.f) atomicAdd(dst + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx), v);
         }
     }
 }
@@ -405,9 +427,9 @@ cudaError_t planar_build(const SceneParams& P, PlanarHost& H) {
     }
     PL_TRY(cudaMemcpy(H.tile_off, off.data(), sizeof(int) * off.size(), cudaMemcpyHostToDevice));
 
-    PL_TRY(cudaFuncSetAttribute(planar_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    PL_TRY(cudaFuncSetAttribute(planar_kernel<kScatter>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 static_cast<int>(H.smem_bytes)));
-    PL_TRY(cudaFuncSetAttribute(planar_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    PL_TRY(cudaFuncSetAttribute(planar_kernel<kGather>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 static_cast<int>(H.smem_bytes)));
     H.valid = true;
     return cudaSuccess;
@@ -438,8 +460,8 @@ cudaError_t launch_planar_forward(const SceneParams& P, PlanarHost& H, const flo
     PlanarPlan L = H.plan;
     L.groups = planar_groups(P, L, n_active);
     const dim3 grid(L.tiles_x * L.tiles_y, P.res[2], L.groups);
-    planar_kernel<false><<<grid, kPlanarThreads, H.smem_bytes, stream>>>(P, L, active_data, film, active_pixels,
-                                                                        n_active, ray_weight, H.gate);
+    planar_kernel<kScatter><<<grid, kPlanarThreads, H.smem_bytes, stream>>>(P, L, active_data, film, active_pixels,
+                                                                           n_active, ray_weight, H.gate);
     count_launch();
     return cudaGetLastError();
 }
@@ -449,8 +471,8 @@ cudaError_t launch_planar_adjoint(const SceneParams& P, PlanarHost& H, const flo
     PlanarPlan L = H.plan;
     L.groups = planar_groups(P, L, n_active);
     const dim3 grid(L.tiles_x * L.tiles_y, P.res[2], L.groups);
-    planar_kernel<true><<<grid, kPlanarThreads, H.smem_bytes, stream>>>(P, L, dL, grad, active_pixels, n_active,
-                                                                       ray_weight, H.gate);
+    planar_kernel<kGather><<<grid, kPlanarThreads, H.smem_bytes, stream>>>(P, L, dL, grad, active_pixels, n_active,
+                                                                          ray_weight, H.gate);
     count_launch();
     return cudaGetLastError();
 }

@@ -11,12 +11,12 @@ namespace drtvam {
 
 // Branchless orthonormal basis around n (Duff et al.), as Mitsuba's Frame3f.
 __device__ __forceinline__ void frame_from_normal(float nx, float ny, float nz, float s[3], float t[3]) {
-    const float sign = copysignf(1.f, nz);
+    const float sign = nz >= 0.f ? 1.f : -1.f;
     const float a = -1.f / (sign + nz);
     const float b = nx * ny * a;
-    s[0] = copysignf(nx * nx * a, nz) + 1.f;
-    s[1] = copysignf(b, nz);
-    s[2] = copysignf(nx, -nz);
+    s[0] = nx * nx * a * sign + 1.f;  // mulsign(x, nz) = x * sign(nz)
+    s[1] = b * sign;
+    s[2] = -nx * sign;
     t[0] = b;
     t[1] = ny * ny * a + sign;
     t[2] = -ny;
