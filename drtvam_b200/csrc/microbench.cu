@@ -64,6 +64,62 @@ __global__ void smem_accumulate_kernel(float* out, int mode, int iters) {
     if (threadIdx.x == 0) out[blockIdx.x] = tile[lane];
 }
 
+
+// Refined shared-memory accumulate modes with cheap address generation (two
+// integer instructions per access), so that the shared-memory pipe and not
+// the issue slots bound the rate.  `share` lanes use the same address
+// (1 = conflict free, 2 = pairs of lanes collide, ...).
+// mode 0: red.shared.add.f32 (LDS + FADD + ATOMS.CAST.SPIN)
+// mode 1: red.shared.add.u32 (native ATOMS.ADD)
+// mode 2: 64-bit CAS loop adding a float2
+// mode 3: plain LDS + FADD + STS
+// mode 4: ld.shared only (gather)
+__global__ void smem_accumulate2_kernel(float* out, int mode, int iters, int share) {
+    extern __shared__ float tile[];
+    const int n = 12288;  // 48 KB
+    for (int i = threadIdx.x; i < n; i += blockDim.x) tile[i] = 0.f;
+    __syncthreads();
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t base = static_cast<uint32_t>(__cvta_generic_to_shared(tile));
+    uint32_t row = hash32(blockIdx.x * blockDim.x + (threadIdx.x >> 5)) & 127u;
+    const uint32_t col = lane / share;
+    float acc = 0.f;
+    if (mode == 2) {
+        for (int i = 0; i < iters; ++i) {
+            row = (row + 37u) & 127u;
+            const uint32_t a = base + 8u * (row * 32u + col);
+            unsigned long long old, assumed, upd;
+            asm volatile("ld.shared.b64 %0, [%1];" : "=l"(old) : "r"(a));
+            do {
+                assumed = old;
+                const float lo = __uint_as_float(static_cast<uint32_t>(assumed)) + 1.0f;
+                const float hi = __uint_as_float(static_cast<uint32_t>(assumed >> 32)) + 1.0f;
+                upd = (static_cast<unsigned long long>(__float_as_uint(hi)) << 32) | __float_as_uint(lo);
+                asm volatile("atom.shared.cas.b64 %0, [%1], %2, %3;" : "=l"(old) : "r"(a), "l"(assumed), "l"(upd) : "memory");
+            } while (old != assumed);
+        }
+    } else {
+        for (int i = 0; i < iters; ++i) {
+            row = (row + 37u) & 255u;
+            const uint32_t a = base + 4u * (row * 32u + col);
+            if (mode == 0) asm volatile("red.shared.add.f32 [%0], %1;" ::"r"(a), "f"(1.0f) : "memory");
+            else if (mode == 1) asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(a), "r"(1u) : "memory");
+            else if (mode == 3) {
+                float v;
+                asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
+                v += 1.0f;
+                asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v) : "memory");
+            } else {
+                float v;
+                asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
+                acc += v;
+            }
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) out[blockIdx.x] = tile[lane] + acc;
+}
+
 float time_launches(cudaEvent_t a, cudaEvent_t b) {
     float ms = 0.f;
     cudaEventSynchronize(b);
@@ -108,6 +164,22 @@ double drtvam_mb_smem(float* out, int mode, int iters, int blocks) {
     const float ms = time_launches(a, b);
     cudaEventDestroy(a); cudaEventDestroy(b);
     return static_cast<double>(blocks) * threads * iters / (ms * 1e-3) * 1e-9;
+}
+
+// Refined variant (cheap addressing); returns giga-accumulates per second
+// (mode 2 counts two fp32 adds per access).
+double drtvam_mb_smem2(float* out, int mode, int iters, int blocks, int threads, int share) {
+    cudaEvent_t a, b;
+    cudaEventCreate(&a); cudaEventCreate(&b);
+    for (int rep = 0; rep < 2; ++rep) {
+        cudaEventRecord(a);
+        smem_accumulate2_kernel<<<blocks, threads, 49152>>>(out, mode, iters, share);
+        cudaEventRecord(b);
+    }
+    if (cudaGetLastError() != cudaSuccess) return -1.0;
+    const float ms = time_launches(a, b);
+    cudaEventDestroy(a); cudaEventDestroy(b);
+    return static_cast<double>(blocks) * threads * iters * (mode == 2 ? 2 : 1) / (ms * 1e-3) * 1e-9;
 }
 
 }  // extern "C"

@@ -217,9 +217,8 @@ __device__ __forceinline__ float march_tile(const SceneParams& P, float* __restr
             asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
             acc = fmaf(v, de, acc);
         } else {
-            float* ptr;
-            asm("cvta.shared.u64 %0, %1;" : "=l"(ptr) : "l"(static_cast<unsigned long long>(addr)));
-            atomicAdd(ptr, em * de);
+            // explicit state space: LDS + FADD + ATOMS.CAST.SPIN, no generic-address detour
+            asm volatile("red.shared.add.f32 [%0], %1;" ::"r"(addr), "f"(em * de) : "memory");
         }
     };
     for (int n = nx + ny; n > 0; --n) {

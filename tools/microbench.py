@@ -38,6 +38,13 @@ def main():
     o = torch.zeros(blocks, device="cuda")
     for name, mode in (("atoms_int", 0), ("atoms_f32_cas", 1), ("lds_fadd_sts", 2)):
         out[f"smem_{name}_Gops"] = round(lib.drtvam_mb_smem(o.data_ptr(), mode, 4096, 148 * 4), 2)
+    lib.drtvam_mb_smem2.restype = C.c_double
+    lib.drtvam_mb_smem2.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]
+    for name, mode in (("red_f32", 0), ("red_u32", 1), ("cas64_f32x2", 2), ("lds_fadd_sts", 3), ("lds", 4)):
+        for share in (1, 2, 4):
+            for threads in (256, 1024):
+                g = lib.drtvam_mb_smem2(o.data_ptr(), mode, 8192, 148 * (4 if threads == 256 else 2), threads, share)
+                out[f"smem2_{name}_share{share}_t{threads}_Gops"] = round(g, 2)
     torch.cuda.synchronize()
     print(json.dumps(out))
 
