@@ -57,9 +57,10 @@ struct DrtvamScene {
     SceneParams P{};
     float print_time = 1.f;
     float* motion_dev = nullptr;
-    bool force_general = false;
+    int force_mode = 0;              // 0 auto, 1 general tracer, 2 planar v1 (per-ray tile DDA)
     std::vector<float> motion_host;  // copy of the motion table for the plan check
     PlanarHost planar;
+    PlanarZHost zplan;               // layer-parallel kernels on top of the planar tables
     bool planar_tried = false;       // planar_build ran for the current depth setting
     bool planar_ok = false;
     Scratch host_io[3];      // device staging for the *_host calls
@@ -101,7 +102,7 @@ int check_call(const DrtvamScene* s, uint64_t n_active, uint32_t& spp) {
 // (angle, column), and the film must be the plain single-channel DDA film.
 bool planar_static_eligible(const DrtvamScene* s) {
     const SceneParams& P = s->P;
-    if (P.proj_kind != DRTVAM_PROJ_COLLIMATED || !P.regular_sampling || P.sample_time) return false;
+    if (P.proj_kind != DRTVAM_PROJ_COLLIMATED || P.sample_time) return false;  // jitter keeps d_z = 0
     if (P.albedo != 0.f || P.sensor_kind != DRTVAM_SENSOR_DDA || P.surface_aware) return false;
     if (!P.transmission_only) return false;
     if (P.max_depth < 1 || P.max_depth - 1 > P.rr_depth) return false;  // Russian roulette never fires
@@ -141,11 +142,19 @@ int ensure_planar(DrtvamScene* s) {
         return fail(DRTVAM_E_CUDA, "planar plan build failed: %s", cudaGetErrorString(e));
     }
     s->planar_ok = s->planar.valid && s->planar.flags == 0 && s->planar.n_rows_in_sensor > 0;
+    planarz_release(s->zplan);
+    if (s->planar_ok && s->P.regular_sampling) {
+        e = planarz_build(s->P, s->planar, s->planar.row_layer, s->zplan);
+        if (e != cudaSuccess) {
+            planarz_release(s->zplan);
+            return fail(DRTVAM_E_CUDA, "layer-parallel plan build failed: %s", cudaGetErrorString(e));
+        }
+    }
     return DRTVAM_OK;
 }
 
 bool use_planar(DrtvamScene* s, uint64_t n_active) {
-    if (s->force_general || !s->planar_ok || n_active == 0) return false;
+    if (s->force_mode == 1 || !s->planar_ok || n_active == 0) return false;
     const uint64_t hw = static_cast<uint64_t>(s->P.res_x) * s->P.res_y;
     return n_active % hw == 0;
 }
@@ -254,6 +263,7 @@ void drtvam_scene_destroy(DrtvamScene* s) {
     if (s->motion_dev) cudaFree(s->motion_dev);
     if (s->counter_dev) cudaFree(s->counter_dev);
     planar_release(s->planar);
+    planarz_release(s->zplan);
     for (auto& b : s->host_io) b.release();
     delete s;
 }
@@ -268,7 +278,8 @@ int drtvam_scene_set_depth(DrtvamScene* s, int32_t max_depth, int32_t rr_depth) 
 
 int drtvam_scene_force_general(DrtvamScene* s, int32_t on) {
     if (!s) return fail(DRTVAM_E_INVALID, "scene handle is NULL");
-    s->force_general = on != 0;
+    if (on < 0 || on > 2) return fail(DRTVAM_E_INVALID, "force mode must be 0 (auto), 1 (general) or 2 (planar v1)");
+    s->force_mode = on;
     return DRTVAM_OK;
 }
 
@@ -276,7 +287,9 @@ int drtvam_scene_plan(DrtvamScene* s, uint64_t n_active, uint32_t) {
     if (!s) return fail(DRTVAM_E_INVALID, "scene handle is NULL");
     DeviceGuard guard(s->device);
     if (int rc = ensure_planar(s)) return rc;
-    return use_planar(s, n_active) ? 1 : 0;
+    if (!use_planar(s, n_active)) return 0;
+    if (!s->P.regular_sampling) return 3;
+    return (s->zplan.valid && s->force_mode != 2) ? 2 : 1;
 }
 
 int drtvam_forward(DrtvamScene* s, const float* active_data, const uint32_t* active_pixels, uint64_t n_active,
@@ -292,7 +305,16 @@ int drtvam_forward(DrtvamScene* s, const float* active_data, const uint32_t* act
     if (use_planar(s, n_active)) {
         // the device decides: gate = 0 -> planar kernels, gate != 0 -> general tracer
         CUDA_TRY(launch_planar_check(s->P, s->planar, active_pixels, n_active, st));
-        CUDA_TRY(launch_planar_forward(s->P, s->planar, active_data, active_pixels, n_active, w, dose, st));
+        if (!s->P.regular_sampling)
+            CUDA_TRY(launch_planar_lane_forward(s->P, s->planar, active_data, active_pixels, n_active, spp, seed, w, dose,
+                                                st));
+        else if (s->zplan.valid && s->force_mode != 2)
+            CUDA_TRY(launch_planarz_forward(s->P, s->zplan, s->planar.gate, active_data, active_pixels, n_active, w, dose,
+                                            st));
+        else
+            CUDA_TRY(launch_planar_forward(s->P, s->planar, active_data, active_pixels, n_active, w, dose, st));
+        if (s->P.regular_sampling)
+            CUDA_TRY(launch_planar_frozen(s->P, s->planar, 0, active_data, dose, active_pixels, n_active, w, st));
         CUDA_TRY(launch_forward_general(s->P, active_data, active_pixels, n_active * spp, spp, seed, w, dose, st,
                                         s->planar.gate));
         return DRTVAM_OK;
@@ -311,9 +333,20 @@ int drtvam_adjoint(DrtvamScene* s, const float* dose_grad, const uint32_t* activ
     const float w = ray_weight(s, n_active, spp) * in_scale;
     if (int rc = ensure_planar(s)) return rc;
     if (use_planar(s, n_active)) {
-        CUDA_TRY(cudaMemsetAsync(pattern_grad, 0, sizeof(float) * n_active, st));
         CUDA_TRY(launch_planar_check(s->P, s->planar, active_pixels, n_active, st));
-        CUDA_TRY(launch_planar_adjoint(s->P, s->planar, dose_grad, active_pixels, n_active, w, pattern_grad, st));
+        if (!s->P.regular_sampling) {
+            CUDA_TRY(cudaMemsetAsync(pattern_grad, 0, sizeof(float) * n_active, st));
+            CUDA_TRY(launch_planar_lane_adjoint(s->P, s->planar, dose_grad, active_pixels, n_active, spp, seed, w,
+                                                pattern_grad, st));
+        } else if (s->zplan.valid && s->force_mode != 2) {
+            CUDA_TRY(launch_planarz_adjoint(s->P, s->zplan, s->planar.gate, dose_grad, active_pixels, n_active, w,
+                                            pattern_grad, st));
+        } else {
+            CUDA_TRY(cudaMemsetAsync(pattern_grad, 0, sizeof(float) * n_active, st));
+            CUDA_TRY(launch_planar_adjoint(s->P, s->planar, dose_grad, active_pixels, n_active, w, pattern_grad, st));
+        }
+        if (s->P.regular_sampling)
+            CUDA_TRY(launch_planar_frozen(s->P, s->planar, 1, dose_grad, pattern_grad, active_pixels, n_active, w, st));
         CUDA_TRY(launch_adjoint_general(s->P, dose_grad, active_pixels, n_active * spp, spp, seed, w, pattern_grad, st,
                                         s->planar.gate));
         return DRTVAM_OK;

@@ -102,6 +102,52 @@ __device__ __forceinline__ void dda_segment(const SceneParams& P, const Ray& ray
     }
 }
 
+// The reference sets `dtmax[dtmax < 0] = inf` (sensor.py:359).  When fp32
+// rounding puts the segment start a hair on the far side of the boundary of
+// the voxel it was truncated into, that axis is frozen for the whole walk and
+// the ray deposits along a straight line of voxels.  dda_segment reproduces
+// this; the tiled planar kernels cannot, so they ask this predicate (same
+// arithmetic as the head of dda_segment) and leave such rays to dda_segment.
+__device__ __forceinline__ bool dda_has_frozen_axis(const SceneParams& P, const Ray& ray, float maxt) {
+    const float o[3] = {ray.ox, ray.oy, ray.oz};
+    const float d[3] = {ray.dx, ray.dy, ray.dz};
+    float t_near = -INFINITY, t_far = INFINITY;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        const float t0 = (P.bmin[a] - o[a]) / d[a];
+        const float t1 = (P.bmax[a] - o[a]) / d[a];
+        t_near = fmaxf(t_near, fminf(t0, t1));
+        t_far = fminf(t_far, fmaxf(t0, t1));
+    }
+    const float t_start = fmaxf(t_near, 0.f);
+    const float t_end = fminf(t_far, maxt);
+    if (!(isfinite(t_start) && isfinite(t_end) && t_start < t_end)) return false;
+    bool frozen = false;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        const float vs = (P.bmax[a] - P.bmin[a]) / static_cast<float>(P.res[a]);
+        const float gs = fmaf(d[a], t_start, o[a]);
+        const int stp = d[a] > 0.f ? 1 : -1;
+        const int cur = min(max(__float2int_rz((gs - P.bmin[a]) / vs), 0), P.res[a] - 1);
+        float boundary = P.bmin[a] + static_cast<float>(cur + stp) * vs;
+        if (d[a] < 0.f) boundary += vs;
+        if (fabsf(d[a]) > 1e-8f) {
+            // frozen axis, with a guard band: the decision is a knife edge of fp32 rounding that two
+            // compilations of this arithmetic can take differently, so everything within 1e-4 voxel of
+            // it goes to dda_segment as well (which then simply walks normally)
+            if ((boundary - gs) / d[a] < 0.f || fabsf(boundary - gs) < 1e-4f * vs) frozen = true;
+        }
+        if (a < 2 && fabsf(d[a]) > 1e-8f && fabsf(d[a]) < 1e-5f * fabsf(d[1 - a])) {
+            const float ge = fmaf(d[a], t_end, o[a]);
+            const float fs = (gs - P.bmin[a]) / vs, fe = (ge - P.bmin[a]) / vs;
+            const int endv = min(max(__float2int_rz(fe), 0), P.res[a] - 1);
+            const bool near_edge = fabsf(fs - rintf(fs)) < 1e-3f || fabsf(fe - rintf(fe)) < 1e-3f;
+            if (endv != cur || near_edge) frozen = true;
+        }
+    }
+    return frozen;
+}
+
 // Ratio-tracking estimator (sensor.py:243-293): exponential steps with the
 // majorant, one deposit per tentative collision.
 template <class Sink>

@@ -113,7 +113,7 @@ cudaError_t launch_adjoint_general(const SceneParams& P, const float* dL, const 
                                    cudaStream_t stream, const int* gate) {
     if (n_lanes == 0) return cudaSuccess;
     const bool pow2 = (spp & (spp - 1)) == 0 && spp <= 32;
-    if (!pow2) {
+    if (!pow2 && gate == nullptr) {  // a gated call hands in a zeroed gradient (abi.cu)
         cudaError_t e = cudaMemsetAsync(grad, 0, sizeof(float) * (n_lanes / spp), stream);
         if (e != cudaSuccess) return e;
     }

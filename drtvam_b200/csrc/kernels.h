@@ -1,6 +1,7 @@
 // Host-side launch interface of the kernel translation units.
 #pragma once
 #include <cstdint>
+#include <vector>
 #include <cuda_runtime.h>
 #include "device_scene.cuh"
 #include "planar.cuh"
@@ -35,8 +36,18 @@ struct PlanarHost {
     int* tile_off = nullptr;
     int* tile_clo = nullptr;
     int* gate = nullptr;  // [0] per-call pixel-layout gate, [1] build flags
+    // jittered passes
+    int* jlayer_row_begin = nullptr;
+    int* jlayer_rows = nullptr;
+    int* jtile_off = nullptr;
+    int* jtile_clo = nullptr;
+    int* frozen_list = nullptr;    // (angle, column) rays with a frozen DDA axis (sensor.py:359), walked generally
+    int n_frozen = 0;
+    void* lane_scratch = nullptr;  // per-lane segment table of the current angle chunk
+    size_t lane_scratch_bytes = 0;
     PlanarPlan plan{};
     size_t smem_bytes = 0;
+    std::vector<int> row_layer;  // host copy: film layer of every DMD row, -1 = outside the sensor
 };
 cudaError_t planar_build(const SceneParams& P, PlanarHost& H);
 void planar_release(PlanarHost& H);
@@ -47,5 +58,44 @@ cudaError_t launch_planar_forward(const SceneParams& P, PlanarHost& H, const flo
                                   cudaStream_t stream);
 cudaError_t launch_planar_adjoint(const SceneParams& P, PlanarHost& H, const float* dL, const uint32_t* active_pixels,
                                   uint64_t n_active, float ray_weight, float* grad, cudaStream_t stream);
+
+// per-(tile, angle) first crossing column and prefix sums of the crossing-column counts
+cudaError_t planar_tile_ranges(const SceneParams& P, const float4* seg_a, const float2* seg_b, int tiles_x, int tiles_y,
+                               int tile_w, int tile_h, int* tile_off_dev, int* tile_clo_dev, float margin = 0.f);
+// mode 0: deposit the frozen-axis rays into the film; mode 1: write their pattern gradients
+cudaError_t launch_planar_frozen(const SceneParams& P, PlanarHost& H, int mode, const float* in, float* out,
+                                 const uint32_t* active_pixels, uint64_t n_active, float ray_weight,
+                                 cudaStream_t stream);
+// jittered planar passes (per-lane segment table)
+cudaError_t launch_planar_lane_forward(const SceneParams& P, PlanarHost& H, const float* active_data,
+                                       const uint32_t* active_pixels, uint64_t n_active, uint32_t spp, uint32_t seed,
+                                       float ray_weight, float* film, cudaStream_t stream);
+cudaError_t launch_planar_lane_adjoint(const SceneParams& P, PlanarHost& H, const float* dL,
+                                       const uint32_t* active_pixels, uint64_t n_active, uint32_t spp, uint32_t seed,
+                                       float ray_weight, float* grad, cudaStream_t stream);
+
+// layer-parallel planar kernels (planarz_kernels.cu), the deterministic fast path
+struct PlanarZHost {
+    bool valid = false;
+    PlanarZPlan plan{};
+    int* tile_off = nullptr;
+    int* tile_clo = nullptr;
+    int* zl = nullptr;
+    int* a_row_begin = nullptr;
+    int* a_rows = nullptr;
+    int* row_a = nullptr;
+    float* scratch = nullptr;  // [angles][columns][active layers] repack of patterns / gradients
+    size_t scratch_bytes = 0;
+    size_t smem_bytes = 0;
+};
+cudaError_t planarz_build(const SceneParams& P, const PlanarHost& base, const std::vector<int>& row_layer,
+                          PlanarZHost& H);
+void planarz_release(PlanarZHost& H);
+cudaError_t launch_planarz_forward(const SceneParams& P, PlanarZHost& H, const int* gate, const float* active_data,
+                                   const uint32_t* active_pixels, uint64_t n_active, float ray_weight, float* film,
+                                   cudaStream_t stream);
+cudaError_t launch_planarz_adjoint(const SceneParams& P, PlanarZHost& H, const int* gate, const float* dL,
+                                   const uint32_t* active_pixels, uint64_t n_active, float ray_weight, float* grad,
+                                   cudaStream_t stream);
 
 }  // namespace drtvam

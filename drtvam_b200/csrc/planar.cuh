@@ -23,11 +23,80 @@ struct PlanarPlan {
     const int* layer_rows;       // DMD rows sorted by the layer they deposit in
     const int* tile_off;         // [n_tiles][n_patterns + 1] prefix of per-angle column counts
     const int* tile_clo;         // [n_tiles][n_patterns] first column crossing the tile
+    // jittered passes: conservative variants (a jittered ray of column c lies within half a pixel of
+    // the centre ray of c; a DMD row can reach the layers next to the one its centre is in)
+    const int* jlayer_row_begin;
+    const int* jlayer_rows;
+    const int* jtile_off;
+    const int* jtile_clo;
     int tiles_x, tiles_y, tile_w, tile_h, pitch, groups;
 };
 
 // flags written by the table builder
 constexpr int kPlanarFlagMultiSegment = 1;  // a ray had more than one medium segment
 constexpr int kPlanarFlagNotPlanar = 2;     // a segment had d_z != 0
+
+// Layer-parallel ("z-lane") plan: a warp marches ONE (angle, column) ray and
+// its 32 lanes deposit into 32 different z-layers at the same (x, y), so the
+// traversal is warp-uniform, shared-memory banks never conflict and the
+// pattern / gradient values are read and written as 128-byte lines from a
+// [angle][column][active layer] repack of active_data.
+struct PlanarZPlan {
+    const float4* seg_a;     // shared with PlanarPlan
+    const float2* seg_b;
+    const int* tile_off;     // [n_tiles][n_patterns + 1] prefix of per-angle column counts
+    const int* tile_clo;     // [n_tiles][n_patterns]
+    const int* zl;           // [nz_pad] film layer of active layer a (-1 = padding)
+    const int* a_row_begin;  // [nz + 1] CSR over a_rows: DMD rows that deposit in active layer a
+    const int* a_rows;
+    const int* row_a;        // [res_y] active layer of DMD row r, -1 = outside the sensor
+    int tiles_x, tiles_y, tile_w, tile_h;
+    int nz, nz_pad;          // active layers, padded to a multiple of 32 * layers-per-lane
+    int lanes_l;             // layers per lane (1, 2 or 4)
+    int groups;
+};
+
+#ifdef __CUDACC__
+__device__ __forceinline__ float ex2_approx(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
+                 : "memory");
+}
+
+// Clip of a 2-D segment against the voxel rectangle [x0, x0+w) x [y0, y0+h).
+template <class Params>
+__device__ __forceinline__ bool clip_to_tile(const Params& P, const float4 a, float tmax, int x0, int y0, int w,
+                                             int h, float& t0, float& t1, float margin = 0.f) {
+    const float vsx = (P.bmax[0] - P.bmin[0]) / static_cast<float>(P.res[0]);
+    const float vsy = (P.bmax[1] - P.bmin[1]) / static_cast<float>(P.res[1]);
+    const float xl = P.bmin[0] + static_cast<float>(x0) * vsx - margin;
+    const float xh = P.bmin[0] + static_cast<float>(x0 + w) * vsx + margin;
+    const float yl = P.bmin[1] + static_cast<float>(y0) * vsy - margin;
+    const float yh = P.bmin[1] + static_cast<float>(y0 + h) * vsy + margin;
+    float tn = 0.f, tf = tmax;
+    if (fabsf(a.z) > 1e-8f) {
+        const float ta = (xl - a.x) / a.z, tb = (xh - a.x) / a.z;
+        tn = fmaxf(tn, fminf(ta, tb));
+        tf = fminf(tf, fmaxf(ta, tb));
+    } else if (a.x < xl || a.x >= xh) {
+        return false;
+    }
+    if (fabsf(a.w) > 1e-8f) {
+        const float ta = (yl - a.y) / a.w, tb = (yh - a.y) / a.w;
+        tn = fmaxf(tn, fminf(ta, tb));
+        tf = fminf(tf, fmaxf(ta, tb));
+    } else if (a.y < yl || a.y >= yh) {
+        return false;
+    }
+    t0 = tn;
+    t1 = tf;
+    return tn < tf;
+}
+#endif
 
 }  // namespace drtvam

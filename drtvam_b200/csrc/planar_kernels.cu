@@ -42,7 +42,8 @@ struct RecordSink {
 // through the general interface loop so both plans share the same arithmetic.
 __global__ void __launch_bounds__(kPlanarThreads)
 planar_segments_kernel(const __grid_constant__ SceneParams P, int row_ref, float4* __restrict__ seg_a,
-                       float2* __restrict__ seg_b, int* __restrict__ flags) {
+                       float2* __restrict__ seg_b, int* __restrict__ flags, int* __restrict__ frozen_list,
+                       int* __restrict__ frozen_count) {
     const int i = blockIdx.x * kPlanarThreads + threadIdx.x;
     const int n = P.n_patterns * P.res_x;
     if (i >= n) return;
@@ -59,13 +60,19 @@ planar_segments_kernel(const __grid_constant__ SceneParams P, int row_ref, float
     if (sink.count >= 1 && sink.seg.dz != 0.f) f |= kPlanarFlagNotPlanar;
     if (ray.dz != 0.f) f |= kPlanarFlagNotPlanar;
     if (f) atomicOr(flags, f);
-    const bool ok = sink.count >= 1 && sink.w0 != 0.f && sink.tmax > 0.f && isfinite(sink.tmax);
+    bool ok = sink.count >= 1 && sink.w0 != 0.f && sink.tmax > 0.f && isfinite(sink.tmax);
+    if (ok && dda_has_frozen_axis(P, sink.seg, sink.tmax)) {
+        // sensor.py:359 quirk: this (angle, column) is walked by dda_segment in planar_frozen_kernel
+        frozen_list[atomicAdd(frozen_count, 1)] = i;
+        ok = false;
+    }
     seg_a[i] = make_float4(sink.seg.ox, sink.seg.oy, sink.seg.dx, sink.seg.dy);
     seg_b[i] = ok ? make_float2(sink.tmax, sink.w0) : make_float2(0.f, 0.f);
 }
 
 // Layer each DMD row deposits in (the z part of sensor.py:328-346), -1 = none.
-__global__ void planar_row_layer_kernel(const __grid_constant__ SceneParams P, int* __restrict__ row_layer) {
+__global__ void planar_row_layer_kernel(const __grid_constant__ SceneParams P, int* __restrict__ row_layer,
+                                        float* __restrict__ row_z) {
     const int row = blockIdx.x * blockDim.x + threadIdx.x;
     if (row >= P.res_y) return;
     Sampler rng;
@@ -77,38 +84,12 @@ __global__ void planar_row_layer_kernel(const __grid_constant__ SceneParams P, i
         layer = min(max(__float2int_rz((ray.oz - P.bmin[2]) / vs), 0), P.res[2] - 1);
     }
     row_layer[row] = layer;
-}
-
-// Clip of a 2-D segment against the voxel rectangle [x0, x0+w) x [y0, y0+h).
-__device__ __forceinline__ bool clip_to_tile(const SceneParams& P, const float4 a, float tmax, int x0, int y0, int w,
-                                             int h, float& t0, float& t1) {
-    const float vsx = (P.bmax[0] - P.bmin[0]) / static_cast<float>(P.res[0]);
-    const float vsy = (P.bmax[1] - P.bmin[1]) / static_cast<float>(P.res[1]);
-    const float xl = P.bmin[0] + static_cast<float>(x0) * vsx, xh = P.bmin[0] + static_cast<float>(x0 + w) * vsx;
-    const float yl = P.bmin[1] + static_cast<float>(y0) * vsy, yh = P.bmin[1] + static_cast<float>(y0 + h) * vsy;
-    float tn = 0.f, tf = tmax;
-    if (fabsf(a.z) > 1e-8f) {
-        const float ta = (xl - a.x) / a.z, tb = (xh - a.x) / a.z;
-        tn = fmaxf(tn, fminf(ta, tb));
-        tf = fminf(tf, fmaxf(ta, tb));
-    } else if (a.x < xl || a.x >= xh) {
-        return false;
-    }
-    if (fabsf(a.w) > 1e-8f) {
-        const float ta = (yl - a.y) / a.w, tb = (yh - a.y) / a.w;
-        tn = fmaxf(tn, fminf(ta, tb));
-        tf = fminf(tf, fmaxf(ta, tb));
-    } else if (a.y < yl || a.y >= yh) {
-        return false;
-    }
-    t0 = tn;
-    t1 = tf;
-    return tn < tf;
+    row_z[row] = ray.oz;
 }
 
 // Column range of every (tile, angle): one thread each, scanning the columns.
 __global__ void planar_ranges_kernel(const __grid_constant__ SceneParams P, const PlanarPlan L, int* __restrict__ clo,
-                                     int* __restrict__ cnt) {
+                                     int* __restrict__ cnt, float margin) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int n_tiles = L.tiles_x * L.tiles_y;
     if (i >= n_tiles * P.n_patterns) return;
@@ -120,10 +101,14 @@ __global__ void planar_ranges_kernel(const __grid_constant__ SceneParams P, cons
         const float2 b = L.seg_b[k * P.res_x + c];
         if (b.y == 0.f) continue;
         float t0, t1;
-        if (clip_to_tile(P, L.seg_a[k * P.res_x + c], b.x, x0, y0, w, h, t0, t1)) {
+        if (clip_to_tile(P, L.seg_a[k * P.res_x + c], b.x, x0, y0, w, h, t0, t1, margin)) {
             lo = min(lo, c);
             hi = max(hi, c);
         }
+    }
+    if (margin > 0.f && hi >= lo) {  // jittered rays of the neighbouring columns may cross too
+        lo = max(lo - 1, 0);
+        hi = min(hi + 1, P.res_x - 1);
     }
     clo[i] = hi >= lo ? lo : 0;
     cnt[i] = hi >= lo ? hi - lo + 1 : 0;
@@ -142,20 +127,42 @@ __global__ void planar_check_pixels_kernel(const uint32_t* __restrict__ active_p
 }
 
 
+
+// Rays of the deterministic table whose walk has a frozen axis (sensor.py:359):
+// one thread per (listed (angle, column), DMD row), general walk.
+// kMode 0: in = active_data, out = film.  kMode 1: in = dL, out = pattern_grad (written, not added).
+template <int kMode>
+__global__ void __launch_bounds__(kPlanarThreads)
+planar_frozen_kernel(const __grid_constant__ SceneParams P, const int* __restrict__ frozen_list, int n_frozen,
+                     const float* __restrict__ in, float* __restrict__ out, const uint32_t* __restrict__ active_pixels,
+                     uint64_t n_active, float ray_weight, const int* __restrict__ gate) {
+    if (*gate != 0) return;
+    const int i = blockIdx.x * kPlanarThreads + threadIdx.x;
+    if (i >= n_frozen * P.res_y) return;
+    const int e = __ldg(frozen_list + i / P.res_y), row = i % P.res_y;
+    const int k = e / P.res_x, c = e - k * P.res_x;
+    const uint32_t hw = static_cast<uint32_t>(P.res_x) * P.res_y;
+    const int k0 = __ldg(active_pixels) / hw, nk = static_cast<int>(n_active / hw);
+    if (k < k0 || k >= k0 + nk) return;
+    const size_t j = (static_cast<size_t>(k - k0) * P.res_y + row) * P.res_x + c;
+    Sampler rng;
+    rng.seed(0u, 0u);  // never consumed: deterministic configuration
+    const Ray ray = generate_ray(P, __ldg(active_pixels + j), rng);
+    if (kMode == 1) {
+        GatherSink g{in};
+        trace_lane<false>(P, ray, rng, g);
+        out[j] = g.acc * ray_weight;
+    } else {
+        const float em = __ldg(in + j) * ray_weight;
+        if (em == 0.f) return;
+        ScatterSink sc{out, em};
+        trace_lane<false>(P, ray, rng, sc);
+    }
+}
+
 }  // namespace
 
 namespace {
-
-__device__ __forceinline__ float ex2_approx(float x) {
-    float y;
-    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-    return y;
-}
-
-__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
-    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
-                 : "memory");
-}
 
 // Kernel modes.  The forward tile accumulates with fp32 atomicAdd, which is an
 // LDS + ATOMS.CAST.SPIN loop on shared memory.  An int32 fixed-point tile with
@@ -183,29 +190,29 @@ __device__ __forceinline__ float march_tile(const SceneParams& P, float* __restr
     const int jy = min(max(__float2int_rz((hy - P.bmin[1]) / vsy) - y0, 0), h - 1);
 
     float ux = INFINITY, uy = INFINITY, ax = 0.f, bx = 0.f, ay = 0.f, by = 0.f, fx = 0.f, fy = 0.f;
-    float sfx = 0.f, sfy = 0.f;
     int sx = 0, sy = 0, nx = 0, ny = 0;
     if (fabsf(a.z) > 1e-8f) {
         const float inv = sig / a.z;
         const bool pos = a.z > 0.f;
         sx = pos ? 4 : -4;  // byte strides
-        sfx = pos ? 1.f : -1.f;
         nx = max(pos ? jx - ix : ix - jx, 0);
-        fx = static_cast<float>(x0 + ix + (pos ? 1 : 0));  // index of the next x boundary
-        ax = vsx * inv;
-        bx = (P.bmin[0] - a.x) * inv;
-        if (nx > 0) ux = fmaf(fx, ax, bx);
+        // boundary times relative to the tile entry: u = u(t0) + (boundary - g) * sig / d keeps the
+        // cancellation in (boundary - g), a difference of nearby positions; later boundaries are
+        // fx whole voxels further (fx counts the steps taken)
+        ax = fabsf(vsx * inv);
+        bx = fmaf(fmaf(static_cast<float>(x0 + ix + (pos ? 1 : 0)), vsx, P.bmin[0]) - gx, inv, sig * t0);
+        fx = 0.f;
+        if (nx > 0) ux = bx;
     }
     if (fabsf(a.w) > 1e-8f) {
         const float inv = sig / a.w;
         const bool pos = a.w > 0.f;
         sy = pos ? 4 * pitch : -4 * pitch;
-        sfy = pos ? 1.f : -1.f;
         ny = max(pos ? jy - iy : iy - jy, 0);
-        fy = static_cast<float>(y0 + iy + (pos ? 1 : 0));
-        ay = vsy * inv;
-        by = (P.bmin[1] - a.y) * inv;
-        if (ny > 0) uy = fmaf(fy, ay, by);
+        ay = fabsf(vsy * inv);
+        by = fmaf(fmaf(static_cast<float>(y0 + iy + (pos ? 1 : 0)), vsy, P.bmin[1]) - gy, inv, sig * t0);
+        fy = 0.f;
+        if (ny > 0) uy = by;
     }
     // one-voxel halo around the tile; shared-window byte address
     uint32_t addr = static_cast<uint32_t>(__cvta_generic_to_shared(tile)) + 4u * ((iy + 1) * pitch + ix + 1);
@@ -226,11 +233,11 @@ __device__ __forceinline__ float march_tile(const SceneParams& P, float* __restr
         deposit(e_prev - e);
         e_prev = e;
         if (ux <= uy) {
-            fx += sfx;
+            fx += 1.f;
             ux = fmaf(fx, ax, bx);
             addr += sx;
         } else {
-            fy += sfy;
+            fy += 1.f;
             uy = fmaf(fy, ay, by);
             addr += sy;
         }
@@ -328,6 +335,156 @@ planar_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pla
     }
 }
 
+
+// ---------------------------------------------------------------------------
+// Jittered planar pass (regular_sampling = false, the reference default): rays
+// of a planar scene still have d_z = 0 and stay in one layer, but each lane has
+// its own pixel jitter (integrators/common.py:92-95), so the segment table is
+// per lane.  A pre-pass traces the interfaces of every lane once and writes
+// (layer, segment); lanes whose path is not one planar segment are deposited
+// right there by the general walk.  The tile kernel then marches the lanes of
+// its layer exactly like the deterministic per-ray kernel.
+// ---------------------------------------------------------------------------
+struct LaneTable {
+    float4* a;   // ox, oy, dx, dy
+    float2* b;   // tmax, w0
+    int* layer;  // film layer, -1 = nothing to march (miss, outside, or already deposited)
+};
+
+template <int kMode>
+__global__ void __launch_bounds__(kPlanarThreads)
+planar_lane_table_kernel(const __grid_constant__ SceneParams P, const float* __restrict__ in, float* __restrict__ out,
+                         const uint32_t* __restrict__ active_pixels, uint64_t lane0, uint64_t n_lanes, uint32_t spp,
+                         uint32_t seed, float ray_weight, LaneTable T, const int* __restrict__ gate) {
+    if (*gate != 0) return;
+    const uint64_t i = static_cast<uint64_t>(blockIdx.x) * kPlanarThreads + threadIdx.x;
+    if (i >= n_lanes) return;
+    const uint64_t lane = lane0 + i;
+    const uint64_t j = lane / spp;
+    const uint32_t pixel = __ldg(active_pixels + j);
+    Sampler rng;
+    rng.seed(seed, static_cast<uint32_t>(lane));
+    const Ray ray = generate_ray(P, pixel, rng);
+    RecordSink sink;
+    sink.seg = ray;
+    trace_lane<false>(P, ray, rng, sink);
+    const bool odd = sink.count > 1 || ray.dz != 0.f || (sink.count == 1 && sink.seg.dz != 0.f) ||
+                     (sink.count == 1 && dda_has_frozen_axis(P, sink.seg, sink.tmax));
+    int layer = -1;
+    if (odd) {
+        // not a single planar segment (e.g. a square-vial corner): general walk, deposited here
+        Sampler rng2;
+        rng2.seed(seed, static_cast<uint32_t>(lane));
+        const Ray ray2 = generate_ray(P, pixel, rng2);
+        if (kMode == kGather) {
+            GatherSink g{in};
+            trace_lane<false>(P, ray2, rng2, g);
+            if (g.acc != 0.f) atomicAdd(out + j, g.acc * ray_weight);
+        } else {
+            const float em = __ldg(in + j) * ray_weight;
+            if (em != 0.f) {
+                ScatterSink sc{out, em};
+                trace_lane<false>(P, ray2, rng2, sc);
+            }
+        }
+    } else if (sink.count == 1 && sink.w0 != 0.f && sink.tmax > 0.f && isfinite(sink.tmax)) {
+        const float z = sink.seg.oz;
+        if (z > P.bmin[2] && z < P.bmax[2]) {
+            const float vs = (P.bmax[2] - P.bmin[2]) / static_cast<float>(P.res[2]);
+            layer = min(max(__float2int_rz((z - P.bmin[2]) / vs), 0), P.res[2] - 1);
+        }
+    }
+    T.a[i] = make_float4(sink.seg.ox, sink.seg.oy, sink.seg.dx, sink.seg.dy);
+    T.b[i] = make_float2(sink.tmax, sink.w0);
+    T.layer[i] = layer;
+}
+
+// kScatter: in = active_data, out = film.  kGather: in = dL, out = pattern_grad (pre-zeroed).
+// Angles [kc, kc + nkc) of the call (relative to its first angle) are in the lane table.
+template <int kMode>
+__global__ void __launch_bounds__(kPlanarThreads)
+planar_lane_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ PlanarPlan L, LaneTable T,
+                   const float* __restrict__ in, float* __restrict__ out, const uint32_t* __restrict__ active_pixels,
+                   int kc, int nkc, uint32_t spp, float ray_weight, const int* __restrict__ gate) {
+    extern __shared__ __align__(16) float smem[];
+    if (*gate != 0) return;
+    const int tile_id = blockIdx.x, layer = blockIdx.y, group = blockIdx.z;
+    const int rb = L.jlayer_row_begin[layer], re = L.jlayer_row_begin[layer + 1];
+    if (rb == re) return;
+
+    const int x0 = (tile_id % L.tiles_x) * L.tile_w, y0 = (tile_id / L.tiles_x) * L.tile_h;
+    const int w = min(L.tile_w, P.res[0] - x0), h = min(L.tile_h, P.res[1] - y0);
+    const int pitch = L.pitch;
+    float* tile = smem;
+    const int* __restrict__ off = L.jtile_off + static_cast<size_t>(tile_id) * (P.n_patterns + 1);
+    const int* __restrict__ clo = L.jtile_clo + static_cast<size_t>(tile_id) * P.n_patterns;
+
+    const uint32_t hw = static_cast<uint32_t>(P.res_x) * P.res_y;
+    const int k0 = __ldg(active_pixels) / hw;
+    const int kfirst = k0 + kc;  // first angle held by the lane table
+    const int ka = kfirst + static_cast<int>(static_cast<long long>(nkc) * group / L.groups);
+    const int kb = kfirst + static_cast<int>(static_cast<long long>(nkc) * (group + 1) / L.groups);
+
+    const size_t layer_base = static_cast<size_t>(layer) * P.res[0] * P.res[1];
+    for (int i = threadIdx.x; i < (h + 2) * pitch; i += kPlanarThreads) {
+        float v = 0.f;
+        if (kMode == kGather) {
+            const int yy = i / pitch - 1, xx = i - (yy + 1) * pitch - 1;
+            if (yy >= 0 && yy < h && xx >= 0 && xx < w)
+                v = __ldg(in + layer_base + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx));
+        }
+        tile[i] = v;
+    }
+    __syncthreads();
+
+    const int f_base = __ldg(off + ka);
+    const long long total = static_cast<long long>(__ldg(off + kb) - f_base) * spp;
+    for (int ri = rb; ri < re; ++ri) {
+        const int row = L.jlayer_rows[ri];
+        int k = ka;
+        for (long long f = threadIdx.x; f < total; f += kPlanarThreads) {
+            const int g = static_cast<int>(f / spp) + f_base;
+            const int smp = static_cast<int>(f - static_cast<long long>(g - f_base) * spp);
+            while (__ldg(off + k + 1) <= g) ++k;
+            const int c = __ldg(clo + k) + (g - __ldg(off + k));
+            const size_t idx = ((static_cast<size_t>(k - kfirst) * P.res_y + row) * P.res_x + c) * spp + smp;
+            if (__ldg(T.layer + idx) != layer) continue;
+            const float2 b = __ldg(T.b + idx);
+            const size_t j = (static_cast<size_t>(k - k0) * P.res_y + row) * P.res_x + c;
+            float em = 0.f;
+            if (kMode != kGather) {
+                em = __ldg(in + j) * (ray_weight * b.y);
+                if (em == 0.f) continue;
+            }
+            const float4 a = __ldg(T.a + idx);
+            float t0, t1;
+            if (!clip_to_tile(P, a, b.x, x0, y0, w, h, t0, t1)) continue;
+            const float acc = march_tile<kMode>(P, tile, pitch, a, t0, t1, x0, y0, w, h, em);
+            if (kMode == kGather && acc != 0.f) atomicAdd(out + j, acc * (ray_weight * b.y));
+        }
+    }
+    if (kMode == kGather) return;
+    __syncthreads();
+
+    float* dst = out + layer_base;
+    if (((x0 | w | P.res[0]) & 3) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
+        const int w4 = w >> 2;
+        for (int i = threadIdx.x; i < h * w4; i += kPlanarThreads) {
+            const int yy = i / w4, xx = (i - yy * w4) << 2;
+            const int t = (yy + 1) * pitch + xx + 1;
+            const float v0 = tile[t], v1 = tile[t + 1], v2 = tile[t + 2], v3 = tile[t + 3];
+            if (v0 != 0.f || v1 != 0.f || v2 != 0.f || v3 != 0.f)
+                red_add_v4(dst + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx), v0, v1, v2, v3);
+        }
+    } else {
+        for (int i = threadIdx.x; i < h * w; i += kPlanarThreads) {
+            const int yy = i / w, xx = i - yy * w;
+            const float v = tile[(yy + 1) * pitch + xx + 1];
+            if (v != 0.f) atomicAdd(dst + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx), v);
+        }
+    }
+}
+
 }  // namespace
 
 // ---------------------------------------------------------------------------
@@ -340,10 +497,33 @@ planar_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pla
     } while (0)
 
 void planar_release(PlanarHost& H) {
-    void* ptrs[] = {H.seg_a, H.seg_b, H.layer_row_begin, H.layer_rows, H.tile_off, H.tile_clo, H.gate};
+    void* ptrs[] = {H.seg_a, H.seg_b, H.layer_row_begin, H.layer_rows, H.tile_off, H.tile_clo, H.gate,
+                    H.jlayer_row_begin, H.jlayer_rows, H.jtile_off, H.jtile_clo, H.lane_scratch, H.frozen_list};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     H = PlanarHost();
+}
+
+cudaError_t planar_tile_ranges(const SceneParams& P, const float4* seg_a, const float2* seg_b, int tiles_x, int tiles_y,
+                               int tile_w, int tile_h, int* tile_off_dev, int* tile_clo_dev, float margin) {
+    const int np = P.n_patterns, n_tiles = tiles_x * tiles_y;
+    PlanarPlan L{};
+    L.seg_a = seg_a; L.seg_b = seg_b;
+    L.tiles_x = tiles_x; L.tiles_y = tiles_y; L.tile_w = tile_w; L.tile_h = tile_h;
+    int* cnt_dev = nullptr;
+    PL_TRY(cudaMalloc(&cnt_dev, sizeof(int) * n_tiles * np));
+    planar_ranges_kernel<<<(n_tiles * np + 127) / 128, 128>>>(P, L, tile_clo_dev, cnt_dev, margin);
+    count_launch();
+    std::vector<int> cnt(static_cast<size_t>(n_tiles) * np), off(static_cast<size_t>(n_tiles) * (np + 1));
+    cudaError_t e = cudaMemcpy(cnt.data(), cnt_dev, sizeof(int) * cnt.size(), cudaMemcpyDeviceToHost);
+    cudaFree(cnt_dev);
+    PL_TRY(e);
+    for (int t = 0; t < n_tiles; ++t) {
+        int acc = 0;
+        for (int k = 0; k < np; ++k) { off[t * (np + 1) + k] = acc; acc += cnt[t * np + k]; }
+        off[t * (np + 1) + np] = acc;
+    }
+    return cudaMemcpy(tile_off_dev, off.data(), sizeof(int) * off.size(), cudaMemcpyHostToDevice);
 }
 
 // Builds the segment table, the layer -> rows CSR and the per-tile column
@@ -370,20 +550,29 @@ cudaError_t planar_build(const SceneParams& P, PlanarHost& H) {
     PL_TRY(cudaMalloc(&H.layer_rows, sizeof(int) * Hh));
     PL_TRY(cudaMalloc(&H.tile_off, sizeof(int) * n_tiles * (np + 1)));
     PL_TRY(cudaMalloc(&H.tile_clo, sizeof(int) * n_tiles * np));
-    PL_TRY(cudaMalloc(&H.gate, sizeof(int) * 2));
-    PL_TRY(cudaMemset(H.gate, 0, sizeof(int) * 2));
+    PL_TRY(cudaMalloc(&H.gate, sizeof(int) * 4));
+    PL_TRY(cudaMemset(H.gate, 0, sizeof(int) * 4));
+    PL_TRY(cudaMalloc(&H.frozen_list, sizeof(int) * np * W));
     L.seg_a = H.seg_a; L.seg_b = H.seg_b;
     L.layer_row_begin = H.layer_row_begin; L.layer_rows = H.layer_rows;
     L.tile_off = H.tile_off; L.tile_clo = H.tile_clo;
 
     // rows -> layers
     int* row_layer_dev = nullptr;
+    float* row_z_dev = nullptr;
     PL_TRY(cudaMalloc(&row_layer_dev, sizeof(int) * Hh));
-    planar_row_layer_kernel<<<(Hh + 127) / 128, 128>>>(P, row_layer_dev);
+    PL_TRY(cudaMalloc(&row_z_dev, sizeof(float) * Hh));
+    // the tables describe the pixel-centre rays, also when the passes themselves are jittered
+    SceneParams R = P;
+    R.regular_sampling = 1;
+    planar_row_layer_kernel<<<(Hh + 127) / 128, 128>>>(R, row_layer_dev, row_z_dev);
     count_launch();
     std::vector<int> row_layer(Hh);
+    std::vector<float> row_z(Hh);
     cudaError_t e = cudaMemcpy(row_layer.data(), row_layer_dev, sizeof(int) * Hh, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) e = cudaMemcpy(row_z.data(), row_z_dev, sizeof(float) * Hh, cudaMemcpyDeviceToHost);
     cudaFree(row_layer_dev);
+    cudaFree(row_z_dev);
     PL_TRY(e);
     std::vector<int> begin(rz + 1, 0), rows;
     int row_ref = -1;
@@ -402,29 +591,57 @@ cudaError_t planar_build(const SceneParams& P, PlanarHost& H) {
     if (row_ref < 0) row_ref = Hh / 2;
 
     // segment table (flags live in gate[1])
-    planar_segments_kernel<<<(np * W + kPlanarThreads - 1) / kPlanarThreads, kPlanarThreads>>>(P, row_ref, H.seg_a,
-                                                                                             H.seg_b, H.gate + 1);
+    planar_segments_kernel<<<(np * W + kPlanarThreads - 1) / kPlanarThreads, kPlanarThreads>>>(R, row_ref, H.seg_a,
+                                                                                             H.seg_b, H.gate + 1,
+                                                                                             H.frozen_list, H.gate + 2);
     count_launch();
     PL_TRY(cudaGetLastError());
     int flags = 0;
     PL_TRY(cudaMemcpy(&flags, H.gate + 1, sizeof(int), cudaMemcpyDeviceToHost));
     H.flags = flags;
+    PL_TRY(cudaMemcpy(&H.n_frozen, H.gate + 2, sizeof(int), cudaMemcpyDeviceToHost));
 
-    // per-tile column ranges and their prefix sums
-    int* cnt_dev = nullptr;
-    PL_TRY(cudaMalloc(&cnt_dev, sizeof(int) * n_tiles * np));
-    planar_ranges_kernel<<<(n_tiles * np + 127) / 128, 128>>>(P, L, H.tile_clo, cnt_dev);
-    count_launch();
-    std::vector<int> cnt(static_cast<size_t>(n_tiles) * np), off(static_cast<size_t>(n_tiles) * (np + 1));
-    e = cudaMemcpy(cnt.data(), cnt_dev, sizeof(int) * cnt.size(), cudaMemcpyDeviceToHost);
-    cudaFree(cnt_dev);
-    PL_TRY(e);
-    for (int t = 0; t < n_tiles; ++t) {
-        int acc = 0;
-        for (int k = 0; k < np; ++k) { off[t * (np + 1) + k] = acc; acc += cnt[t * np + k]; }
-        off[t * (np + 1) + np] = acc;
+    PL_TRY(planar_tile_ranges(P, H.seg_a, H.seg_b, L.tiles_x, L.tiles_y, L.tile_w, L.tile_h, H.tile_off, H.tile_clo));
+    H.row_layer = row_layer;
+
+    // jittered passes: a row's samples span [row, row + 1] pixels in z, which can reach the
+    // neighbouring layers; the lane table holds the exact layer of every lane
+    {
+        const float vs = (P.bmax[2] - P.bmin[2]) / static_cast<float>(rz);
+        const float dz = Hh > 1 ? std::fabs(row_z[1] - row_z[0]) : P.pixel_y;
+        const float slack = 1e-3f * vs;
+        std::vector<std::vector<int>> rows_of(rz);
+        for (int r = 0; r < Hh; ++r) {
+            const float zlo = row_z[r] - 0.5f * dz - slack, zhi = row_z[r] + 0.5f * dz + slack;
+            if (zhi <= P.bmin[2] || zlo >= P.bmax[2]) continue;
+            int la = static_cast<int>(std::floor((zlo - P.bmin[2]) / vs));
+            int lb = static_cast<int>(std::floor((zhi - P.bmin[2]) / vs));
+            la = std::max(la, 0);
+            lb = std::min(lb, rz - 1);
+            for (int z = la; z <= lb; ++z) rows_of[z].push_back(r);
+        }
+        std::vector<int> jbegin(rz + 1, 0), jrows;
+        for (int z = 0; z < rz; ++z) {
+            jrows.insert(jrows.end(), rows_of[z].begin(), rows_of[z].end());
+            jbegin[z + 1] = static_cast<int>(jrows.size());
+        }
+        if (jrows.empty()) jrows.push_back(0);
+        PL_TRY(cudaMalloc(&H.jlayer_row_begin, sizeof(int) * (rz + 1)));
+        PL_TRY(cudaMalloc(&H.jlayer_rows, sizeof(int) * jrows.size()));
+        PL_TRY(cudaMemcpy(H.jlayer_row_begin, jbegin.data(), sizeof(int) * (rz + 1), cudaMemcpyHostToDevice));
+        PL_TRY(cudaMemcpy(H.jlayer_rows, jrows.data(), sizeof(int) * jrows.size(), cudaMemcpyHostToDevice));
+        PL_TRY(cudaMalloc(&H.jtile_off, sizeof(int) * n_tiles * (np + 1)));
+        PL_TRY(cudaMalloc(&H.jtile_clo, sizeof(int) * n_tiles * np));
+        const float margin = 1.5f * std::fmax(P.pixel_x, P.pixel_y);
+        PL_TRY(planar_tile_ranges(P, H.seg_a, H.seg_b, L.tiles_x, L.tiles_y, L.tile_w, L.tile_h, H.jtile_off,
+                                  H.jtile_clo, margin));
+        L.jlayer_row_begin = H.jlayer_row_begin; L.jlayer_rows = H.jlayer_rows;
+        L.jtile_off = H.jtile_off; L.jtile_clo = H.jtile_clo;
     }
-    PL_TRY(cudaMemcpy(H.tile_off, off.data(), sizeof(int) * off.size(), cudaMemcpyHostToDevice));
+    PL_TRY(cudaFuncSetAttribute(planar_lane_kernel<kScatter>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                static_cast<int>(H.smem_bytes)));
+    PL_TRY(cudaFuncSetAttribute(planar_lane_kernel<kGather>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                static_cast<int>(H.smem_bytes)));
 
     PL_TRY(cudaFuncSetAttribute(planar_kernel<kScatter>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 static_cast<int>(H.smem_bytes)));
@@ -474,6 +691,85 @@ cudaError_t launch_planar_adjoint(const SceneParams& P, PlanarHost& H, const flo
                                                                           ray_weight, H.gate);
     count_launch();
     return cudaGetLastError();
+}
+
+cudaError_t launch_planar_frozen(const SceneParams& P, PlanarHost& H, int mode, const float* in, float* out,
+                                 const uint32_t* active_pixels, uint64_t n_active, float ray_weight,
+                                 cudaStream_t stream) {
+    if (H.n_frozen <= 0) return cudaSuccess;
+    const unsigned blocks = static_cast<unsigned>((static_cast<size_t>(H.n_frozen) * P.res_y + kPlanarThreads - 1) /
+                                                  kPlanarThreads);
+    if (mode == 1)
+        planar_frozen_kernel<1><<<blocks, kPlanarThreads, 0, stream>>>(P, H.frozen_list, H.n_frozen, in, out,
+                                                                       active_pixels, n_active, ray_weight, H.gate);
+    else
+        planar_frozen_kernel<0><<<blocks, kPlanarThreads, 0, stream>>>(P, H.frozen_list, H.n_frozen, in, out,
+                                                                       active_pixels, n_active, ray_weight, H.gate);
+    count_launch();
+    return cudaGetLastError();
+}
+
+// Angles per chunk of the per-lane table (28 bytes per lane, at most ~3 GB of scratch).
+static int lane_chunk_angles(const SceneParams& P, uint32_t spp, int nk) {
+    const double per_angle = 28.0 * P.res_x * P.res_y * spp;
+    long long n = static_cast<long long>(3.0e9 / per_angle);
+    if (n < 1) n = 1;
+    return static_cast<int>(n < nk ? n : nk);
+}
+
+template <int kMode>
+static cudaError_t planar_lane_pass(const SceneParams& P, PlanarHost& H, const float* in, float* out,
+                                    const uint32_t* active_pixels, uint64_t n_active, uint32_t spp, uint32_t seed,
+                                    float ray_weight, cudaStream_t stream) {
+    const uint64_t hw = static_cast<uint64_t>(P.res_x) * P.res_y;
+    const int nk = static_cast<int>(n_active / hw);
+    const int chunk = lane_chunk_angles(P, spp, nk);
+    const size_t lanes_max = static_cast<size_t>(chunk) * hw * spp;
+    const size_t a_bytes = (sizeof(float4) * lanes_max + 255) & ~static_cast<size_t>(255);
+    const size_t b_bytes = (sizeof(float2) * lanes_max + 255) & ~static_cast<size_t>(255);
+    const size_t bytes = a_bytes + b_bytes + sizeof(int) * lanes_max;
+    if (bytes > H.lane_scratch_bytes) {
+        if (H.lane_scratch) cudaFree(H.lane_scratch);
+        H.lane_scratch = nullptr;
+        H.lane_scratch_bytes = 0;
+        PL_TRY(cudaMalloc(&H.lane_scratch, bytes));
+        H.lane_scratch_bytes = bytes;
+    }
+    LaneTable T;
+    char* base = static_cast<char*>(H.lane_scratch);
+    T.a = reinterpret_cast<float4*>(base);
+    T.b = reinterpret_cast<float2*>(base + a_bytes);
+    T.layer = reinterpret_cast<int*>(base + a_bytes + b_bytes);
+    for (int kc = 0; kc < nk; kc += chunk) {
+        const int nkc = (nk - kc) < chunk ? (nk - kc) : chunk;
+        const uint64_t lane0 = static_cast<uint64_t>(kc) * hw * spp, n_lanes = static_cast<uint64_t>(nkc) * hw * spp;
+        planar_lane_table_kernel<kMode><<<static_cast<unsigned>((n_lanes + kPlanarThreads - 1) / kPlanarThreads),
+                                          kPlanarThreads, 0, stream>>>(P, in, out, active_pixels, lane0, n_lanes, spp,
+                                                                        seed, ray_weight, T, H.gate);
+        count_launch();
+        PL_TRY(cudaGetLastError());
+        PlanarPlan L = H.plan;
+        L.groups = planar_groups(P, L, static_cast<uint64_t>(nkc) * hw);
+        const dim3 grid(L.tiles_x * L.tiles_y, P.res[2], L.groups);
+        const size_t smem = sizeof(float) * static_cast<size_t>(L.tile_h + 2) * L.pitch;
+        planar_lane_kernel<kMode><<<grid, kPlanarThreads, smem, stream>>>(P, L, T, in, out, active_pixels, kc, nkc, spp,
+                                                                          ray_weight, H.gate);
+        count_launch();
+        PL_TRY(cudaGetLastError());
+    }
+    return cudaSuccess;
+}
+
+cudaError_t launch_planar_lane_forward(const SceneParams& P, PlanarHost& H, const float* active_data,
+                                       const uint32_t* active_pixels, uint64_t n_active, uint32_t spp, uint32_t seed,
+                                       float ray_weight, float* film, cudaStream_t stream) {
+    return planar_lane_pass<kScatter>(P, H, active_data, film, active_pixels, n_active, spp, seed, ray_weight, stream);
+}
+
+cudaError_t launch_planar_lane_adjoint(const SceneParams& P, PlanarHost& H, const float* dL,
+                                       const uint32_t* active_pixels, uint64_t n_active, uint32_t spp, uint32_t seed,
+                                       float ray_weight, float* grad, cudaStream_t stream) {
+    return planar_lane_pass<kGather>(P, H, dL, grad, active_pixels, n_active, spp, seed, ray_weight, stream);
 }
 
 }  // namespace drtvam

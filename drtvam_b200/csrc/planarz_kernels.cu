@@ -1,0 +1,429 @@
+// Layer-parallel ("z-lane") planar kernels: the fast path of the deterministic
+// (regular_sampling) forward projection and adjoint.
+//
+// In a planar scene (planar.cuh) the medium segment of a ray depends only on
+// (angle, DMD column); all DMD rows share it and differ only in the z-layer
+// they deposit in.  So a WARP marches ONE (angle, column) segment through a
+// small xy-tile and its 32 lanes are 32 different z-layers (times kL layers per
+// lane in registers):
+//   - the 2-D voxel DDA is warp-uniform: no divergence, one traversal is
+//     amortised over 32 * kL rays;
+//   - the shared tile is laid out [kL][y][x][33] floats, lane = innermost index,
+//     so every shared access of a warp touches 32 distinct banks;
+//   - pattern values / pattern gradients are read / written as 128-byte lines
+//     from a [angle][column][active layer] repack of active_data.
+// Forward: red.shared.add.f32 into the tile, one red.global.add.v4.f32 flush.
+// Adjoint: the tile holds the dose gradient, plain ld.shared gathers, one
+// coalesced red.global per (ray, tile) into the repacked gradient.
+// Reference: DDAVolumetricSensor.accumulate (sensor.py:306-440), film.write
+// (film.py:40-41), VolumeIntegrator.render / render_backward
+// (integrators/volume.py:18-56, 97-134).
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
+#include <vector>
+
+#include "kernels.h"
+#include "planar.cuh"
+
+namespace drtvam {
+
+namespace {
+
+constexpr int kZThreads = 1024;
+constexpr int kZWarps = kZThreads / 32;
+constexpr int kZLaneStride = 33;  // floats per voxel: 32 lanes + 1 pad (conflict-free flush)
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr int kScatter = 0, kGather = 1;
+
+// active_data [kk][row][col]  ->  pT [kk][col][a]  (sum over the rows of layer a)
+__global__ void __launch_bounds__(256)
+zpack_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ PlanarZPlan Z,
+             const float* __restrict__ active_data, float* __restrict__ pT, int nk, const int* __restrict__ gate) {
+    __shared__ float tr[32][33];
+    if (*gate != 0) return;
+    const int kk = blockIdx.z;
+    const int c0 = blockIdx.x * 32, a0 = blockIdx.y * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+    for (int j = ty; j < 32; j += 8) {
+        const int a = a0 + j, c = c0 + tx;
+        float v = 0.f;
+        if (a < Z.nz && c < P.res_x) {
+            const int rb = __ldg(Z.a_row_begin + a), re = __ldg(Z.a_row_begin + a + 1);
+            for (int ri = rb; ri < re; ++ri) {
+                const int r = __ldg(Z.a_rows + ri);
+                v += __ldg(active_data + (static_cast<size_t>(kk) * P.res_y + r) * P.res_x + c);
+            }
+        }
+        tr[j][tx] = v;
+    }
+    __syncthreads();
+    for (int j = ty; j < 32; j += 8) {
+        const int c = c0 + j, a = a0 + tx;
+        if (c < P.res_x && a < Z.nz_pad)
+            pT[(static_cast<size_t>(kk) * P.res_x + c) * Z.nz_pad + a] = tr[tx][j];
+    }
+    (void)nk;
+}
+
+// gT [kk][col][a]  ->  pattern_grad [kk][row][col]  (every row of a layer gets the layer's value)
+__global__ void __launch_bounds__(256)
+zunpack_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ PlanarZPlan Z,
+               const float* __restrict__ gT, float* __restrict__ grad, const int* __restrict__ gate) {
+    __shared__ float tr[32][33];
+    if (*gate != 0) return;
+    const int kk = blockIdx.z;
+    const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    for (int j = ty; j < 32; j += 8) {
+        const int c = c0 + j, r = r0 + tx;
+        float v = 0.f;
+        if (c < P.res_x && r < P.res_y) {
+            const int a = __ldg(Z.row_a + r);
+            if (a >= 0) v = __ldg(gT + (static_cast<size_t>(kk) * P.res_x + c) * Z.nz_pad + a);
+        }
+        tr[j][tx] = v;
+    }
+    __syncthreads();
+    for (int j = ty; j < 32; j += 8) {
+        const int r = r0 + j, c = c0 + tx;
+        if (r < P.res_y && c < P.res_x) grad[(static_cast<size_t>(kk) * P.res_y + r) * P.res_x + c] = tr[tx][j];
+    }
+}
+
+// kScatter: in = pT, out = film (red.global flush).  kGather: in = dL (film layout), out = gT.
+template <int kMode, int kL>
+__global__ void __launch_bounds__(kZThreads, 1)
+planarz_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ PlanarZPlan Z,
+               const float* __restrict__ in, float* __restrict__ out, const uint32_t* __restrict__ active_pixels,
+               uint64_t n_active, float ray_weight, const int* __restrict__ gate) {
+    extern __shared__ __align__(16) float tile[];
+    if (*gate != 0) return;
+    const int tile_id = blockIdx.x, zb = blockIdx.y, group = blockIdx.z;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int x0 = (tile_id % Z.tiles_x) * Z.tile_w, y0 = (tile_id / Z.tiles_x) * Z.tile_h;
+    const int w = min(Z.tile_w, P.res[0] - x0), h = min(Z.tile_h, P.res[1] - y0);
+    const int tw = Z.tile_w;
+    const int plane = Z.tile_h * tw * kZLaneStride;  // floats per lane-layer slab
+    const int a_base = zb * (32 * kL);
+    const size_t layer_elems = static_cast<size_t>(P.res[0]) * P.res[1];
+
+    // ---- stage the tile
+    if (kMode == kScatter) {
+        for (int i = threadIdx.x; i < kL * plane; i += kZThreads) tile[i] = 0.f;
+    } else {
+        const int per_layer = h * w;
+        for (int i = threadIdx.x; i < kL * 32 * per_layer; i += kZThreads) {
+            const int al = i / per_layer, rem = i - al * per_layer;
+            const int yy = rem / w, xx = rem - yy * w;
+            const int z = __ldg(Z.zl + a_base + al);
+            float v = 0.f;
+            if (z >= 0) v = __ldg(in + z * layer_elems + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx));
+            tile[(al >> 5) * plane + (yy * tw + xx) * kZLaneStride + (al & 31)] = v;
+        }
+    }
+    __syncthreads();
+
+    const uint32_t hw = static_cast<uint32_t>(P.res_x) * P.res_y;
+    const uint32_t base = __ldg(active_pixels);
+    const int k0 = base / hw, nk = static_cast<int>(n_active / hw);
+    const int ka = k0 + static_cast<int>(static_cast<long long>(nk) * group / Z.groups);
+    const int kb = k0 + static_cast<int>(static_cast<long long>(nk) * (group + 1) / Z.groups);
+    const int* __restrict__ off = Z.tile_off + static_cast<size_t>(tile_id) * (P.n_patterns + 1);
+    const int* __restrict__ clo = Z.tile_clo + static_cast<size_t>(tile_id) * P.n_patterns;
+
+    const float sig = P.sigma_t * kLog2e;
+    const float vsx = (P.bmax[0] - P.bmin[0]) / static_cast<float>(P.res[0]);
+    const float vsy = (P.bmax[1] - P.bmin[1]) / static_cast<float>(P.res[1]);
+    const uint32_t tile_s = static_cast<uint32_t>(__cvta_generic_to_shared(tile)) + 4u * lane;
+    const uint32_t plane_b = 4u * plane;
+    const int sxb = 4 * kZLaneStride, syb = 4 * kZLaneStride * tw;
+
+    const int f_base = __ldg(off + ka), total = __ldg(off + kb) - f_base;
+    int k = ka;
+    for (int f = warp; f < total; f += kZWarps) {
+        const int g = f + f_base;
+        while (__ldg(off + k + 1) <= g) ++k;
+        const int c = __ldg(clo + k) + (g - __ldg(off + k));
+        const int s = k * P.res_x + c;
+        const float2 b = __ldg(Z.seg_b + s);
+        if (b.y == 0.f) continue;
+        const float4 a = __ldg(Z.seg_a + s);
+        float t0, t1;
+        if (!clip_to_tile(P, a, b.x, x0, y0, w, h, t0, t1)) continue;
+
+        const float wray = ray_weight * b.y;
+        const size_t tbase = (static_cast<size_t>(k - k0) * P.res_x + c) * Z.nz_pad + a_base + lane;
+        float em[kL], acc[kL];
+#pragma unroll
+        for (int m = 0; m < kL; ++m) { em[m] = 0.f; acc[m] = 0.f; }
+        if (kMode == kScatter) {
+            bool any = false;
+#pragma unroll
+            for (int m = 0; m < kL; ++m) {
+                em[m] = __ldg(in + tbase + 32 * m) * wray;
+                any = any || (em[m] != 0.f);
+            }
+            if (!__any_sync(0xffffffffu, any)) continue;  // dark ray in all of this block's layers
+        }
+
+        // ---- warp-uniform 2-D DDA inside the tile (sensor.py:345-438 restricted to z = const)
+        const float gx = fmaf(a.z, t0, a.x), gy = fmaf(a.w, t0, a.y);
+        const float hx = fmaf(a.z, t1, a.x), hy = fmaf(a.w, t1, a.y);
+        const int ix = min(max(__float2int_rz((gx - P.bmin[0]) / vsx) - x0, 0), w - 1);
+        const int iy = min(max(__float2int_rz((gy - P.bmin[1]) / vsy) - y0, 0), h - 1);
+        const int jx = min(max(__float2int_rz((hx - P.bmin[0]) / vsx) - x0, 0), w - 1);
+        const int jy = min(max(__float2int_rz((hy - P.bmin[1]) / vsy) - y0, 0), h - 1);
+        float ux = INFINITY, uy = INFINITY, ax = 0.f, bx = 0.f, ay = 0.f, by = 0.f, fx = 0.f, fy = 0.f;
+        int sx = 0, sy = 0, nx = 0, ny = 0;
+        if (fabsf(a.z) > 1e-8f) {
+            const float inv = sig / a.z;
+            const bool pos = a.z > 0.f;
+            sx = pos ? sxb : -sxb;
+            nx = max(pos ? jx - ix : ix - jx, 0);
+            // boundary times relative to the tile entry (see march_tile in planar_kernels.cu)
+            ax = fabsf(vsx * inv);
+            bx = fmaf(fmaf(static_cast<float>(x0 + ix + (pos ? 1 : 0)), vsx, P.bmin[0]) - gx, inv, sig * t0);
+            fx = 0.f;
+            if (nx > 0) ux = bx;
+        }
+        if (fabsf(a.w) > 1e-8f) {
+            const float inv = sig / a.w;
+            const bool pos = a.w > 0.f;
+            sy = pos ? syb : -syb;
+            ny = max(pos ? jy - iy : iy - jy, 0);
+            ay = fabsf(vsy * inv);
+            by = fmaf(fmaf(static_cast<float>(y0 + iy + (pos ? 1 : 0)), vsy, P.bmin[1]) - gy, inv, sig * t0);
+            fy = 0.f;
+            if (ny > 0) uy = by;
+        }
+        uint32_t addr = tile_s + static_cast<uint32_t>((iy * tw + ix) * (4 * kZLaneStride));
+        float e_prev = ex2_approx(-sig * t0);
+        auto deposit = [&](float de) {
+#pragma unroll
+            for (int m = 0; m < kL; ++m) {
+                if (kMode == kGather) {
+                    float v;
+                    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr + m * plane_b));
+                    acc[m] = fmaf(v, de, acc[m]);
+                } else {
+                    asm volatile("red.shared.add.f32 [%0], %1;" ::"r"(addr + m * plane_b), "f"(em[m] * de) : "memory");
+                }
+            }
+        };
+        for (int n = nx + ny; n > 0; --n) {
+            const bool stepx = ux <= uy;
+            const float e = ex2_approx(-(stepx ? ux : uy));
+            deposit(e_prev - e);
+            e_prev = e;
+            if (stepx) {
+                addr += sx;
+                fx += 1.f;
+                ux = (--nx > 0) ? fmaf(fx, ax, bx) : INFINITY;
+            } else {
+                addr += sy;
+                fy += 1.f;
+                uy = (--ny > 0) ? fmaf(fy, ay, by) : INFINITY;
+            }
+        }
+        deposit(e_prev - ex2_approx(-sig * t1));
+
+        if (kMode == kGather) {
+#pragma unroll
+            for (int m = 0; m < kL; ++m)
+                if (acc[m] != 0.f) atomicAdd(out + tbase + 32 * m, acc[m] * wray);
+        }
+    }
+    if (kMode == kGather) return;
+    __syncthreads();
+
+    // ---- flush: one red.global per voxel (v4 when the rows are 16-byte aligned in the film)
+    const bool vec = ((x0 | w | P.res[0]) & 3) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0;
+    if (vec) {
+        const int w4 = w >> 2, per_layer = h * w4;
+        for (int i = threadIdx.x; i < kL * 32 * per_layer; i += kZThreads) {
+            const int al = i / per_layer, rem = i - al * per_layer;
+            const int yy = rem / w4, xx = (rem - yy * w4) << 2;
+            const int z = __ldg(Z.zl + a_base + al);
+            if (z < 0) continue;
+            const float* src = tile + (al >> 5) * plane + (yy * tw + xx) * kZLaneStride + (al & 31);
+            const float v0 = src[0], v1 = src[kZLaneStride], v2 = src[2 * kZLaneStride], v3 = src[3 * kZLaneStride];
+            if (v0 != 0.f || v1 != 0.f || v2 != 0.f || v3 != 0.f)
+                red_add_v4(out + z * layer_elems + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx), v0, v1, v2, v3);
+        }
+    } else {
+        const int per_layer = h * w;
+        for (int i = threadIdx.x; i < kL * 32 * per_layer; i += kZThreads) {
+            const int al = i / per_layer, rem = i - al * per_layer;
+            const int yy = rem / w, xx = rem - yy * w;
+            const int z = __ldg(Z.zl + a_base + al);
+            if (z < 0) continue;
+            const float v = tile[(al >> 5) * plane + (yy * tw + xx) * kZLaneStride + (al & 31)];
+            if (v != 0.f) atomicAdd(out + z * layer_elems + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx), v);
+        }
+    }
+}
+
+}  // namespace
+
+#define PZ_TRY(expr)                      \
+    do {                                  \
+        cudaError_t _e = (expr);          \
+        if (_e != cudaSuccess) return _e; \
+    } while (0)
+
+void planarz_release(PlanarZHost& H) {
+    void* ptrs[] = {H.tile_off, H.tile_clo, H.zl, H.a_row_begin, H.a_rows, H.row_a, H.scratch};
+    for (void* p : ptrs)
+        if (p) cudaFree(p);
+    H = PlanarZHost();
+}
+
+// Tile geometry for kL layers per lane: the largest xy tile whose
+// [kL][h][w][33] float slab fits the 227 KB of opt-in shared memory.
+static void z_tile_dims(int rx, int ry, int kL, int& tw, int& th) {
+    const int max_floats = (227 * 1024) / 4;
+    const int area = max_floats / (kZLaneStride * kL);
+    int side = static_cast<int>(std::floor(std::sqrt(static_cast<double>(area))));
+    int tw_max = std::max(4, side & ~3);
+    int tiles_x = (rx + tw_max - 1) / tw_max;
+    tw = (((rx + tiles_x - 1) / tiles_x) + 3) & ~3;
+    int th_max = std::max(1, area / tw);
+    int tiles_y = (ry + th_max - 1) / th_max;
+    th = (ry + tiles_y - 1) / tiles_y;
+}
+
+cudaError_t planarz_build(const SceneParams& P, const PlanarHost& base, const std::vector<int>& row_layer,
+                          PlanarZHost& H) {
+    planarz_release(H);
+    int kL = 2;
+    if (const char* env = std::getenv("DRTVAM_Z_LAYERS")) {
+        const int v = std::atoi(env);
+        if (v == 1 || v == 2 || v == 4) kL = v;
+    }
+    const int rz = P.res[2], Hh = P.res_y, np = P.n_patterns;
+    // active layers and their rows
+    std::vector<int> layer_a(rz, -1), zl, a_row_begin(1, 0), a_rows, row_a(Hh, -1);
+    std::vector<std::vector<int>> rows_of(rz);
+    for (int r = 0; r < Hh; ++r)
+        if (row_layer[r] >= 0) rows_of[row_layer[r]].push_back(r);
+    for (int z = 0; z < rz; ++z) {
+        if (rows_of[z].empty()) continue;
+        layer_a[z] = static_cast<int>(zl.size());
+        zl.push_back(z);
+        for (int r : rows_of[z]) { a_rows.push_back(r); row_a[r] = layer_a[z]; }
+        a_row_begin.push_back(static_cast<int>(a_rows.size()));
+    }
+    const int nz = static_cast<int>(zl.size());
+    if (nz == 0) return cudaSuccess;  // nothing deposits: leave the plan invalid
+    // small problems: fewer layers per lane keeps more CTAs in flight
+    while (kL > 1 && nz <= 32 * (kL / 2)) kL /= 2;
+    const int block = 32 * kL;
+    const int nz_pad = (nz + block - 1) / block * block;
+    zl.resize(nz_pad, -1);
+    if (a_rows.empty()) a_rows.push_back(0);
+
+    PlanarZPlan& Z = H.plan;
+    Z.seg_a = base.seg_a;
+    Z.seg_b = base.seg_b;
+    z_tile_dims(P.res[0], P.res[1], kL, Z.tile_w, Z.tile_h);
+    Z.tiles_x = (P.res[0] + Z.tile_w - 1) / Z.tile_w;
+    Z.tiles_y = (P.res[1] + Z.tile_h - 1) / Z.tile_h;
+    Z.nz = nz;
+    Z.nz_pad = nz_pad;
+    Z.lanes_l = kL;
+    Z.groups = 1;
+    const int n_tiles = Z.tiles_x * Z.tiles_y;
+    H.smem_bytes = sizeof(float) * static_cast<size_t>(kL) * Z.tile_h * Z.tile_w * kZLaneStride;
+
+    PZ_TRY(cudaMalloc(&H.tile_off, sizeof(int) * n_tiles * (np + 1)));
+    PZ_TRY(cudaMalloc(&H.tile_clo, sizeof(int) * n_tiles * np));
+    PZ_TRY(cudaMalloc(&H.zl, sizeof(int) * nz_pad));
+    PZ_TRY(cudaMalloc(&H.a_row_begin, sizeof(int) * (nz + 1)));
+    PZ_TRY(cudaMalloc(&H.a_rows, sizeof(int) * a_rows.size()));
+    PZ_TRY(cudaMalloc(&H.row_a, sizeof(int) * Hh));
+    PZ_TRY(cudaMemcpy(H.zl, zl.data(), sizeof(int) * nz_pad, cudaMemcpyHostToDevice));
+    PZ_TRY(cudaMemcpy(H.a_row_begin, a_row_begin.data(), sizeof(int) * (nz + 1), cudaMemcpyHostToDevice));
+    PZ_TRY(cudaMemcpy(H.a_rows, a_rows.data(), sizeof(int) * a_rows.size(), cudaMemcpyHostToDevice));
+    PZ_TRY(cudaMemcpy(H.row_a, row_a.data(), sizeof(int) * Hh, cudaMemcpyHostToDevice));
+    PZ_TRY(planar_tile_ranges(P, base.seg_a, base.seg_b, Z.tiles_x, Z.tiles_y, Z.tile_w, Z.tile_h, H.tile_off,
+                              H.tile_clo));
+    Z.tile_off = H.tile_off; Z.tile_clo = H.tile_clo; Z.zl = H.zl;
+    Z.a_row_begin = H.a_row_begin; Z.a_rows = H.a_rows; Z.row_a = H.row_a;
+
+    const int smem = static_cast<int>(H.smem_bytes);
+#define PZ_ATTR(MODE, LL) \
+    PZ_TRY(cudaFuncSetAttribute(planarz_kernel<MODE, LL>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem))
+    if (kL == 1) { PZ_ATTR(kScatter, 1); PZ_ATTR(kGather, 1); }
+    else if (kL == 2) { PZ_ATTR(kScatter, 2); PZ_ATTR(kGather, 2); }
+    else { PZ_ATTR(kScatter, 4); PZ_ATTR(kGather, 4); }
+#undef PZ_ATTR
+    H.valid = true;
+    return cudaSuccess;
+}
+
+static cudaError_t z_scratch(PlanarZHost& H, size_t bytes) {
+    if (bytes <= H.scratch_bytes) return cudaSuccess;
+    if (H.scratch) cudaFree(H.scratch);
+    H.scratch = nullptr;
+    H.scratch_bytes = 0;
+    PZ_TRY(cudaMalloc(&H.scratch, bytes));
+    H.scratch_bytes = bytes;
+    return cudaSuccess;
+}
+
+static int z_groups(const SceneParams& P, const PlanarZPlan& Z, int nk) {
+    const long long ctas = static_cast<long long>(Z.tiles_x) * Z.tiles_y * (Z.nz_pad / (32 * Z.lanes_l));
+    long long g = (148 * 2 + ctas - 1) / ctas;
+    g = std::min<long long>(g, std::max(1, nk / 8));
+    g = std::min<long long>(g, 64);
+    (void)P;
+    return g < 1 ? 1 : static_cast<int>(g);
+}
+
+template <int kMode>
+static cudaError_t z_launch(const SceneParams& P, const PlanarZPlan& Z, size_t smem, const float* in, float* out,
+                            const uint32_t* active_pixels, uint64_t n_active, float w, const int* gate,
+                            cudaStream_t stream) {
+    const dim3 grid(Z.tiles_x * Z.tiles_y, Z.nz_pad / (32 * Z.lanes_l), Z.groups);
+    if (Z.lanes_l == 1)
+        planarz_kernel<kMode, 1><<<grid, kZThreads, smem, stream>>>(P, Z, in, out, active_pixels, n_active, w, gate);
+    else if (Z.lanes_l == 2)
+        planarz_kernel<kMode, 2><<<grid, kZThreads, smem, stream>>>(P, Z, in, out, active_pixels, n_active, w, gate);
+    else
+        planarz_kernel<kMode, 4><<<grid, kZThreads, smem, stream>>>(P, Z, in, out, active_pixels, n_active, w, gate);
+    count_launch();
+    return cudaGetLastError();
+}
+
+cudaError_t launch_planarz_forward(const SceneParams& P, PlanarZHost& H, const int* gate, const float* active_data,
+                                   const uint32_t* active_pixels, uint64_t n_active, float ray_weight, float* film,
+                                   cudaStream_t stream) {
+    const int nk = static_cast<int>(n_active / (static_cast<uint64_t>(P.res_x) * P.res_y));
+    PlanarZPlan Z = H.plan;
+    Z.groups = z_groups(P, Z, nk);
+    PZ_TRY(z_scratch(H, sizeof(float) * static_cast<size_t>(nk) * P.res_x * Z.nz_pad));
+    const dim3 pgrid((P.res_x + 31) / 32, Z.nz_pad / 32, nk);
+    zpack_kernel<<<pgrid, 256, 0, stream>>>(P, Z, active_data, H.scratch, nk, gate);
+    count_launch();
+    PZ_TRY(cudaGetLastError());
+    return z_launch<kScatter>(P, Z, H.smem_bytes, H.scratch, film, active_pixels, n_active, ray_weight, gate, stream);
+}
+
+cudaError_t launch_planarz_adjoint(const SceneParams& P, PlanarZHost& H, const int* gate, const float* dL,
+                                   const uint32_t* active_pixels, uint64_t n_active, float ray_weight, float* grad,
+                                   cudaStream_t stream) {
+    const int nk = static_cast<int>(n_active / (static_cast<uint64_t>(P.res_x) * P.res_y));
+    PlanarZPlan Z = H.plan;
+    Z.groups = z_groups(P, Z, nk);
+    const size_t bytes = sizeof(float) * static_cast<size_t>(nk) * P.res_x * Z.nz_pad;
+    PZ_TRY(z_scratch(H, bytes));
+    PZ_TRY(cudaMemsetAsync(H.scratch, 0, bytes, stream));
+    PZ_TRY(z_launch<kGather>(P, Z, H.smem_bytes, dL, H.scratch, active_pixels, n_active, ray_weight, gate, stream));
+    const dim3 ugrid((P.res_x + 31) / 32, (P.res_y + 31) / 32, nk);
+    zunpack_kernel<<<ugrid, 256, 0, stream>>>(P, Z, H.scratch, grad, gate);
+    count_launch();
+    return cudaGetLastError();
+}
+
+}  // namespace drtvam

@@ -113,9 +113,12 @@ void drtvam_scene_destroy(DrtvamScene *scene);
 int drtvam_scene_set_depth(DrtvamScene *scene, int32_t max_depth, int32_t rr_depth);
 
 /* Which kernel family a call will use for this scene and spp:
- * 0 = general per-lane tracer, 1 = planar z-separable fast path. */
+ * 0 = general per-lane tracer, 1 = planar per-ray tile DDA,
+ * 2 = planar layer-parallel kernels (deterministic fast path),
+ * 3 = planar per-lane table kernels (jittered sampling). */
 int drtvam_scene_plan(DrtvamScene *scene, uint64_t n_active, uint32_t spp);
-/* Force the general tracer (1) or let the library choose (0). */
+/* 0 = let the library choose, 1 = force the general tracer, 2 = force the
+ * planar per-ray tile DDA where the scene is planar (A/B tests). */
 int drtvam_scene_force_general(DrtvamScene *scene, int32_t on);
 
 /* A p : VolumeIntegrator.render (volume.py:18-56).  dose has

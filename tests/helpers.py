@@ -36,3 +36,24 @@ def random_inputs(desc, n_active, seed=0):
 
 def pixels_np(scene):
     return (scene.projector.active_pixels.cpu().numpy().astype(np.int64) & 0xFFFFFFFF).astype(np.uint32)
+
+
+def rel_l2_trimmed(a, b, outlier_frac=1e-4):
+    """Relative L2 after discarding the `outlier_frac` largest |a - b| entries.
+
+    Used for JITTERED comparisons only.  A jittered ray that starts within an
+    ulp of a voxel boundary is a knife edge of fp32 rounding: which voxel it is
+    truncated into, and whether the reference's `dtmax < 0 -> inf` rule
+    (sensor.py:359) freezes an axis, can differ between two compilations of the
+    same arithmetic (CUDA kernels with different inlining contexts, gcc for the
+    oracle).  One such ray out of 10^5 moves the plain relative L2 to ~1e-3
+    while every other ray agrees to 1e-6, so the comparison allows 1e-4 of the
+    entries (a handful of rays) to disagree and holds the rest to the bound."""
+    a = np.asarray(a, np.float64).ravel()
+    b = np.asarray(b, np.float64).ravel()
+    diff = np.abs(a - b)
+    k = int(np.ceil(outlier_frac * diff.size))
+    if k > 0:
+        keep = np.argpartition(diff, diff.size - k)[:diff.size - k]
+        return float(np.linalg.norm(diff[keep]) / max(np.linalg.norm(b[keep]), 1e-300))
+    return float(np.linalg.norm(diff) / max(np.linalg.norm(b), 1e-300))
