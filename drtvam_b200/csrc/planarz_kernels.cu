@@ -8,8 +8,11 @@
 // lane in registers):
 //   - the 2-D voxel DDA is warp-uniform: no divergence, one traversal is
 //     amortised over 32 * kL rays;
-//   - the shared tile is laid out [kL][y][x][33] floats, lane = innermost index,
-//     so every shared access of a warp touches 32 distinct banks;
+//   - the shared tile is laid out [y][x][33 lanes][kL] floats, so a lane's kL
+//     layers are one 4 / 8 / 16-byte word and every shared access of a warp is
+//     a run of consecutive words (no bank conflicts); the forward accumulates
+//     with ONE compare-and-swap per lane and voxel (red.shared.add.f32,
+//     atom.shared.cas.b64 or atom.shared.cas.b128 for kL = 1, 2, 4);
 //   - pattern values / pattern gradients are read / written as 128-byte lines
 //     from a [angle][column][active layer] repack of active_data.
 // Forward: red.shared.add.f32 into the tile, one red.global.add.v4.f32 flush.
@@ -91,6 +94,76 @@ zunpack_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
     }
 }
 
+// tile[addr .. addr + kL) += em[0..kL) * de, atomically with respect to the other warps of the CTA.
+template <int kL>
+__device__ __forceinline__ void z_scatter(uint32_t addr, const float (&em)[kL], float de) {
+    if constexpr (kL == 1) {
+        asm volatile("red.shared.add.f32 [%0], %1;" ::"r"(addr), "f"(em[0] * de) : "memory");
+    } else if constexpr (kL == 2) {
+        float o0, o1;
+        asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(o0), "=f"(o1) : "r"(addr));
+        bool again;
+        do {
+            const float n0 = fmaf(em[0], de, o0), n1 = fmaf(em[1], de, o1);
+            float r0, r1;
+            asm volatile(
+                "{\n\t.reg .b64 c, u, r;\n\t"
+                "mov.b64 c, {%2, %3};\n\t"
+                "mov.b64 u, {%4, %5};\n\t"
+                "atom.shared.cas.b64 r, [%6], c, u;\n\t"
+                "mov.b64 {%0, %1}, r;\n\t}"
+                : "=f"(r0), "=f"(r1)
+                : "f"(o0), "f"(o1), "f"(n0), "f"(n1), "r"(addr)
+                : "memory");
+            again = (__float_as_uint(r0) != __float_as_uint(o0)) | (__float_as_uint(r1) != __float_as_uint(o1));
+            o0 = r0; o1 = r1;
+        } while (again);
+    } else {
+        float o0, o1, o2, o3;
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(o0), "=f"(o1), "=f"(o2), "=f"(o3) : "r"(addr));
+        bool again;
+        do {
+            const float n0 = fmaf(em[0], de, o0), n1 = fmaf(em[1], de, o1);
+            const float n2 = fmaf(em[2], de, o2), n3 = fmaf(em[3], de, o3);
+            float r0, r1, r2, r3;
+            asm volatile(
+                "{\n\t.reg .b128 c, u, r;\n\t"
+                "mov.b128 c, {%4, %5, %6, %7};\n\t"
+                "mov.b128 u, {%8, %9, %10, %11};\n\t"
+                "atom.shared.cas.b128 r, [%12], c, u;\n\t"
+                "mov.b128 {%0, %1, %2, %3}, r;\n\t}"
+                : "=f"(r0), "=f"(r1), "=f"(r2), "=f"(r3)
+                : "f"(o0), "f"(o1), "f"(o2), "f"(o3), "f"(n0), "f"(n1), "f"(n2), "f"(n3), "r"(addr)
+                : "memory");
+            again = (__float_as_uint(r0) != __float_as_uint(o0)) | (__float_as_uint(r1) != __float_as_uint(o1)) |
+                    (__float_as_uint(r2) != __float_as_uint(o2)) | (__float_as_uint(r3) != __float_as_uint(o3));
+            o0 = r0; o1 = r1; o2 = r2; o3 = r3;
+        } while (again);
+    }
+}
+
+// acc[0..kL) += tile[addr .. addr + kL) * de
+template <int kL>
+__device__ __forceinline__ void z_gather(uint32_t addr, float (&acc)[kL], float de) {
+    if constexpr (kL == 1) {
+        float v;
+        asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+        acc[0] = fmaf(v, de, acc[0]);
+    } else if constexpr (kL == 2) {
+        float v0, v1;
+        asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v0), "=f"(v1) : "r"(addr));
+        acc[0] = fmaf(v0, de, acc[0]);
+        acc[1] = fmaf(v1, de, acc[1]);
+    } else {
+        float v0, v1, v2, v3;
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v0), "=f"(v1), "=f"(v2), "=f"(v3) : "r"(addr));
+        acc[0] = fmaf(v0, de, acc[0]);
+        acc[1] = fmaf(v1, de, acc[1]);
+        acc[2] = fmaf(v2, de, acc[2]);
+        acc[3] = fmaf(v3, de, acc[3]);
+    }
+}
+
 // kScatter: in = pT, out = film (red.global flush).  kGather: in = dL (film layout), out = gT.
 template <int kMode, int kL>
 __global__ void __launch_bounds__(kZThreads, 1)
@@ -104,13 +177,14 @@ planarz_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
     const int x0 = (tile_id % Z.tiles_x) * Z.tile_w, y0 = (tile_id / Z.tiles_x) * Z.tile_h;
     const int w = min(Z.tile_w, P.res[0] - x0), h = min(Z.tile_h, P.res[1] - y0);
     const int tw = Z.tile_w;
-    const int plane = Z.tile_h * tw * kZLaneStride;  // floats per lane-layer slab
+    constexpr int kVox = kZLaneStride * kL;           // floats per voxel: [33 lanes][kL layers]
+    const int tile_floats = Z.tile_h * tw * kVox;
     const int a_base = zb * (32 * kL);
     const size_t layer_elems = static_cast<size_t>(P.res[0]) * P.res[1];
 
     // ---- stage the tile
     if (kMode == kScatter) {
-        for (int i = threadIdx.x; i < kL * plane; i += kZThreads) tile[i] = 0.f;
+        for (int i = threadIdx.x; i < tile_floats; i += kZThreads) tile[i] = 0.f;
     } else {
         const int per_layer = h * w;
         for (int i = threadIdx.x; i < kL * 32 * per_layer; i += kZThreads) {
@@ -119,7 +193,7 @@ planarz_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
             const int z = __ldg(Z.zl + a_base + al);
             float v = 0.f;
             if (z >= 0) v = __ldg(in + z * layer_elems + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx));
-            tile[(al >> 5) * plane + (yy * tw + xx) * kZLaneStride + (al & 31)] = v;
+            tile[(yy * tw + xx) * kVox + (al & 31) * kL + (al >> 5)] = v;
         }
     }
     __syncthreads();
@@ -135,9 +209,12 @@ planarz_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
     const float sig = P.sigma_t * kLog2e;
     const float vsx = (P.bmax[0] - P.bmin[0]) / static_cast<float>(P.res[0]);
     const float vsy = (P.bmax[1] - P.bmin[1]) / static_cast<float>(P.res[1]);
-    const uint32_t tile_s = static_cast<uint32_t>(__cvta_generic_to_shared(tile)) + 4u * lane;
-    const uint32_t plane_b = 4u * plane;
-    const int sxb = 4 * kZLaneStride, syb = 4 * kZLaneStride * tw;
+    const float inv_vsx = 1.f / vsx, inv_vsy = 1.f / vsy;
+    // tile rectangle in world units (CTA-uniform)
+    const float xl = P.bmin[0] + static_cast<float>(x0) * vsx, xh = P.bmin[0] + static_cast<float>(x0 + w) * vsx;
+    const float yl = P.bmin[1] + static_cast<float>(y0) * vsy, yh = P.bmin[1] + static_cast<float>(y0 + h) * vsy;
+    const uint32_t tile_s = static_cast<uint32_t>(__cvta_generic_to_shared(tile)) + 4u * kL * lane;
+    const int sxb = 4 * kVox, syb = 4 * kVox * tw;
 
     const int f_base = __ldg(off + ka), total = __ldg(off + kb) - f_base;
     int k = ka;
@@ -149,8 +226,27 @@ planarz_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
         const float2 b = __ldg(Z.seg_b + s);
         if (b.y == 0.f) continue;
         const float4 a = __ldg(Z.seg_a + s);
-        float t0, t1;
-        if (!clip_to_tile(P, a, b.x, x0, y0, w, h, t0, t1)) continue;
+
+        // ---- clip to the tile (warp-uniform; reciprocals instead of the divisions of clip_to_tile:
+        //      a segment that only grazes the tile may be dropped or kept, its length is ~0 either way)
+        const bool vx = fabsf(a.z) > 1e-8f, vy = fabsf(a.w) > 1e-8f;
+        const float rdx = vx ? rcp_approx(a.z) : 0.f, rdy = vy ? rcp_approx(a.w) : 0.f;
+        float t0 = 0.f, t1 = b.x;
+        if (vx) {
+            const float ta = (xl - a.x) * rdx, tb = (xh - a.x) * rdx;
+            t0 = fmaxf(t0, fminf(ta, tb));
+            t1 = fminf(t1, fmaxf(ta, tb));
+        } else if (a.x < xl || a.x >= xh) {
+            continue;
+        }
+        if (vy) {
+            const float ta = (yl - a.y) * rdy, tb = (yh - a.y) * rdy;
+            t0 = fmaxf(t0, fminf(ta, tb));
+            t1 = fminf(t1, fmaxf(ta, tb));
+        } else if (a.y < yl || a.y >= yh) {
+            continue;
+        }
+        if (!(t0 < t1)) continue;
 
         const float wray = ray_weight * b.y;
         const size_t tbase = (static_cast<size_t>(k - k0) * P.res_x + c) * Z.nz_pad + a_base + lane;
@@ -167,63 +263,61 @@ planarz_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
             if (!__any_sync(0xffffffffu, any)) continue;  // dark ray in all of this block's layers
         }
 
-        // ---- warp-uniform 2-D DDA inside the tile (sensor.py:345-438 restricted to z = const)
+        // ---- warp-uniform 2-D DDA inside the tile (sensor.py:345-438 restricted to z = const);
+        //      entry / exit voxel by truncation then clip, in tile-local voxel units
         const float gx = fmaf(a.z, t0, a.x), gy = fmaf(a.w, t0, a.y);
         const float hx = fmaf(a.z, t1, a.x), hy = fmaf(a.w, t1, a.y);
-        const int ix = min(max(__float2int_rz((gx - P.bmin[0]) / vsx) - x0, 0), w - 1);
-        const int iy = min(max(__float2int_rz((gy - P.bmin[1]) / vsy) - y0, 0), h - 1);
-        const int jx = min(max(__float2int_rz((hx - P.bmin[0]) / vsx) - x0, 0), w - 1);
-        const int jy = min(max(__float2int_rz((hy - P.bmin[1]) / vsy) - y0, 0), h - 1);
+        const int ix = min(max(__float2int_rz((gx - xl) * inv_vsx), 0), w - 1);
+        const int iy = min(max(__float2int_rz((gy - yl) * inv_vsy), 0), h - 1);
+        const int jx = min(max(__float2int_rz((hx - xl) * inv_vsx), 0), w - 1);
+        const int jy = min(max(__float2int_rz((hy - yl) * inv_vsy), 0), h - 1);
+        const float u0 = sig * t0;
         float ux = INFINITY, uy = INFINITY, ax = 0.f, bx = 0.f, ay = 0.f, by = 0.f, fx = 0.f, fy = 0.f;
         int sx = 0, sy = 0, nx = 0, ny = 0;
-        if (fabsf(a.z) > 1e-8f) {
-            const float inv = sig / a.z;
+        if (vx) {
+            const float inv = sig * rdx;
             const bool pos = a.z > 0.f;
             sx = pos ? sxb : -sxb;
             nx = max(pos ? jx - ix : ix - jx, 0);
-            // boundary times relative to the tile entry (see march_tile in planar_kernels.cu)
+            // boundary times relative to the tile entry: u = u(t0) + (boundary - g) * sig / d keeps the
+            // cancellation in (boundary - g); later boundaries are fx whole voxels further
             ax = fabsf(vsx * inv);
-            bx = fmaf(fmaf(static_cast<float>(x0 + ix + (pos ? 1 : 0)), vsx, P.bmin[0]) - gx, inv, sig * t0);
-            fx = 0.f;
+            bx = fmaf(fmaf(static_cast<float>(ix + (pos ? 1 : 0)), vsx, xl) - gx, inv, u0);
             if (nx > 0) ux = bx;
         }
-        if (fabsf(a.w) > 1e-8f) {
-            const float inv = sig / a.w;
+        if (vy) {
+            const float inv = sig * rdy;
             const bool pos = a.w > 0.f;
             sy = pos ? syb : -syb;
             ny = max(pos ? jy - iy : iy - jy, 0);
             ay = fabsf(vsy * inv);
-            by = fmaf(fmaf(static_cast<float>(y0 + iy + (pos ? 1 : 0)), vsy, P.bmin[1]) - gy, inv, sig * t0);
-            fy = 0.f;
+            by = fmaf(fmaf(static_cast<float>(iy + (pos ? 1 : 0)), vsy, yl) - gy, inv, u0);
             if (ny > 0) uy = by;
         }
-        uint32_t addr = tile_s + static_cast<uint32_t>((iy * tw + ix) * (4 * kZLaneStride));
-        float e_prev = ex2_approx(-sig * t0);
+        uint32_t addr = tile_s + static_cast<uint32_t>((iy * tw + ix) * (4 * kVox));
+        float e_prev = ex2_approx(-u0);
         auto deposit = [&](float de) {
-#pragma unroll
-            for (int m = 0; m < kL; ++m) {
-                if (kMode == kGather) {
-                    float v;
-                    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr + m * plane_b));
-                    acc[m] = fmaf(v, de, acc[m]);
-                } else {
-                    asm volatile("red.shared.add.f32 [%0], %1;" ::"r"(addr + m * plane_b), "f"(em[m] * de) : "memory");
-                }
-            }
+            if (kMode == kGather) z_gather<kL>(addr, acc, de);
+            else z_scatter<kL>(addr, em, de);
         };
+        // every branch below is warp-uniform: all lanes walk the same (angle, column) segment
         for (int n = nx + ny; n > 0; --n) {
-            const bool stepx = ux <= uy;
-            const float e = ex2_approx(-(stepx ? ux : uy));
-            deposit(e_prev - e);
-            e_prev = e;
-            if (stepx) {
+            if (ux <= uy) {
+                const float e = ex2_approx(-ux);
+                deposit(e_prev - e);
+                e_prev = e;
                 addr += sx;
                 fx += 1.f;
-                ux = (--nx > 0) ? fmaf(fx, ax, bx) : INFINITY;
+                ux = fmaf(fx, ax, bx);
+                if (--nx == 0) ux = INFINITY;
             } else {
+                const float e = ex2_approx(-uy);
+                deposit(e_prev - e);
+                e_prev = e;
                 addr += sy;
                 fy += 1.f;
-                uy = (--ny > 0) ? fmaf(fy, ay, by) : INFINITY;
+                uy = fmaf(fy, ay, by);
+                if (--ny == 0) uy = INFINITY;
             }
         }
         deposit(e_prev - ex2_approx(-sig * t1));
@@ -246,8 +340,8 @@ planarz_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
             const int yy = rem / w4, xx = (rem - yy * w4) << 2;
             const int z = __ldg(Z.zl + a_base + al);
             if (z < 0) continue;
-            const float* src = tile + (al >> 5) * plane + (yy * tw + xx) * kZLaneStride + (al & 31);
-            const float v0 = src[0], v1 = src[kZLaneStride], v2 = src[2 * kZLaneStride], v3 = src[3 * kZLaneStride];
+            const float* src = tile + (yy * tw + xx) * kVox + (al & 31) * kL + (al >> 5);
+            const float v0 = src[0], v1 = src[kVox], v2 = src[2 * kVox], v3 = src[3 * kVox];
             if (v0 != 0.f || v1 != 0.f || v2 != 0.f || v3 != 0.f)
                 red_add_v4(out + z * layer_elems + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx), v0, v1, v2, v3);
         }
@@ -258,7 +352,7 @@ planarz_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
             const int yy = rem / w, xx = rem - yy * w;
             const int z = __ldg(Z.zl + a_base + al);
             if (z < 0) continue;
-            const float v = tile[(al >> 5) * plane + (yy * tw + xx) * kZLaneStride + (al & 31)];
+            const float v = tile[(yy * tw + xx) * kVox + (al & 31) * kL + (al >> 5)];
             if (v != 0.f) atomicAdd(out + z * layer_elems + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx), v);
         }
     }
@@ -296,7 +390,7 @@ static void z_tile_dims(int rx, int ry, int kL, int& tw, int& th) {
 cudaError_t planarz_build(const SceneParams& P, const PlanarHost& base, const std::vector<int>& row_layer,
                           PlanarZHost& H) {
     planarz_release(H);
-    int kL = 2;
+    int kL = 4;
     if (const char* env = std::getenv("DRTVAM_Z_LAYERS")) {
         const int v = std::atoi(env);
         if (v == 1 || v == 2 || v == 4) kL = v;
