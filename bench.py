@@ -236,20 +236,13 @@ def main():
     d_host = d_dev.cpu().pin_memory()
     g_host = torch.empty(n_local, dtype=torch.float32).pin_memory()
 
-    fwd_events = []
-
     def step(seed, p, d, record=False):
         """One L-BFGS iteration's projections on device-resident inputs."""
         p = p.detach().requires_grad_(True)
         scene.projector.active_data = p
-        if record:
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
+        integ.events = pass_events if record else None
         prm = dv.traverse(scene)
         vol = dv.render(scene, prm, integrator=integ, sensor=sensor, spp=spp, seed=seed)
-        if record:
-            e1.record()
-            fwd_events.append((e0, e1))
         loss = loss_fn(vol, target, p)
         loss.backward()                                     # adjoint A^T g
         with torch.no_grad():
@@ -257,6 +250,8 @@ def main():
             dvol = dv.render(scene, None, integrator=integ, sensor=sensor, spp=spp, seed=seed)   # A d
             f_new = loss_fn(vol.detach() + 1.0 * dvol, target, d)                                # Armijo trial
         return loss.detach(), f_new, p.grad
+
+    pass_events = {}
 
     def barrier():
         if world > 1:
@@ -309,7 +304,10 @@ def main():
     e2e_value = rays_per_step * args.steps / (ms_e2e * 1e-3)
 
     # roofline of the dominant kernel (forward dose scatter)
-    fwd_ms = sum(a.elapsed_time(b) for a, b in fwd_events) / max(1, len(fwd_events))
+    def mean_ms(name):
+        ev = pass_events.get(name, [])
+        return sum(a.elapsed_time(b) for a, b in ev) / max(1, len(ev))
+    fwd_ms, adj_ms, ar_ms = mean_ms("forward"), mean_ms("adjoint"), mean_ms("allreduce")
     n_vis = _lib.C.c_uint64(0)
     h = scene.handle(integ, sensor)
     _lib.check(lib.drtvam_count_visits(h, pixels.data_ptr(), n_local, spp, 100, _lib.C.byref(n_vis)))
@@ -321,6 +319,8 @@ def main():
         "bound": "hbm", "kernel": "forward dose scatter (A p)", "achieved": achieved, "peak": peak, "unit": "GB/s",
         "frac": achieved / peak, "traffic": None, "peak_source": how,
         "algorithmic_bytes_per_visit": 4, "visits_per_launch": visits, "kernel_ms": fwd_ms,
+        "adjoint_ms": adj_ms, "adjoint_achieved": 4.0 * visits / (adj_ms * 1e-3) * 1e-9 if adj_ms else None,
+        "allreduce_ms": ar_ms,
         "hbm_algorithmic_gb": hbm_alg_bytes * 1e-9, "hbm_floor_frac": hbm_alg_bytes * 1e-9 / (fwd_ms * 1e-3) / peak,
         "plan": int(lib.drtvam_scene_plan(h, n_local, spp)),
     }

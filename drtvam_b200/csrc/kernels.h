@@ -75,18 +75,26 @@ cudaError_t launch_planar_lane_adjoint(const SceneParams& P, PlanarHost& H, cons
                                        float ray_weight, float* grad, cudaStream_t stream);
 
 // layer-parallel planar kernels (planarz_kernels.cu), the deterministic fast path
-struct PlanarZHost {
-    bool valid = false;
+struct PlanarZSub {      // a run of z-blocks that all hold 32 * lanes_l active layers
     PlanarZPlan plan{};
     int* tile_off = nullptr;
     int* tile_clo = nullptr;
+    int* tile_ebase = nullptr;
+    float4* entries = nullptr;
+    size_t smem_bytes = 0;
+    int n_blocks = 0;
+};
+struct PlanarZHost {
+    bool valid = false;
+    int n_sub = 0;
+    PlanarZSub sub[3];       // e.g. 400 layers = 3 blocks of 128 (4 per lane) + 1 block of 32 (1 per lane)
+    int nz = 0, nz_pad = 0;
     int* zl = nullptr;
     int* a_row_begin = nullptr;
     int* a_rows = nullptr;
     int* row_a = nullptr;
     float* scratch = nullptr;  // [angles][columns][active layers] repack of patterns / gradients
     size_t scratch_bytes = 0;
-    size_t smem_bytes = 0;
 };
 cudaError_t planarz_build(const SceneParams& P, const PlanarHost& base, const std::vector<int>& row_layer,
                           PlanarZHost& H);

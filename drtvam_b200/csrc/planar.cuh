@@ -46,13 +46,16 @@ struct PlanarZPlan {
     const float2* seg_b;
     const int* tile_off;     // [n_tiles][n_patterns + 1] prefix of per-angle column counts
     const int* tile_clo;     // [n_tiles][n_patterns]
+    const int* tile_ebase;   // [n_tiles + 1] first walk entry of every tile
+    const float4* entries;   // 2 x float4 per (tile, angle, column): the clipped walk, ready to march
     const int* zl;           // [nz_pad] film layer of active layer a (-1 = padding)
     const int* a_row_begin;  // [nz + 1] CSR over a_rows: DMD rows that deposit in active layer a
     const int* a_rows;
     const int* row_a;        // [res_y] active layer of DMD row r, -1 = outside the sensor
     int tiles_x, tiles_y, tile_w, tile_h;
-    int nz, nz_pad;          // active layers, padded to a multiple of 32 * layers-per-lane
-    int lanes_l;             // layers per lane (1, 2 or 4)
+    int nz, nz_pad;          // active layers, padded to a multiple of 32
+    int lanes_l;             // layers per lane of this sub-plan (1, 2 or 4)
+    int a_begin;             // first active layer of this sub-plan
     int groups;
 };
 

@@ -164,6 +164,83 @@ __device__ __forceinline__ void z_gather(uint32_t addr, float (&acc)[kL], float 
     }
 }
 
+// ---------------------------------------------------------------------------
+// Walk entries.  The clipped 2-D walk of a (tile, angle, column) triple depends
+// only on the scene, not on the patterns, so it is computed once per scene
+// (and depth setting) and every pass of every z-block just reads it:
+//   e[0] = { u0, u1, ux, uy }   u = sigma_t log2(e) t at tile entry / exit and
+//                               at the first x / y voxel boundary (inf = none)
+//   e[1] = { ax, ay, w0, bits } boundary-to-boundary increments of u, the
+//                               throughput at the segment origin, and
+//                               ix | iy<<7 | nx<<14 | ny<<21 | xneg<<28 | yneg<<29 | valid<<30
+// Times are taken relative to the tile entry, u = u(t0) + (boundary - g) sig / d,
+// so the cancellation sits in (boundary - g), a difference of nearby positions.
+// ---------------------------------------------------------------------------
+constexpr unsigned kEntryValid = 1u << 30;
+
+__global__ void __launch_bounds__(256)
+zsetup_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ PlanarZPlan Z, float4* __restrict__ entries,
+              int total) {
+    const int e = blockIdx.x * 256 + threadIdx.x;
+    if (e >= total) return;
+    const int n_tiles = Z.tiles_x * Z.tiles_y;
+    int lo = 0, hi = n_tiles;  // last tile with ebase <= e
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (__ldg(Z.tile_ebase + mid) <= e) lo = mid; else hi = mid;
+    }
+    const int tile_id = lo, g = e - __ldg(Z.tile_ebase + tile_id);
+    const int* off = Z.tile_off + static_cast<size_t>(tile_id) * (P.n_patterns + 1);
+    lo = 0; hi = P.n_patterns;  // last angle with off <= g
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (__ldg(off + mid) <= g) lo = mid; else hi = mid;
+    }
+    const int k = lo, c = __ldg(Z.tile_clo + static_cast<size_t>(tile_id) * P.n_patterns + k) + (g - __ldg(off + k));
+    const int x0 = (tile_id % Z.tiles_x) * Z.tile_w, y0 = (tile_id / Z.tiles_x) * Z.tile_h;
+    const int w = min(Z.tile_w, P.res[0] - x0), h = min(Z.tile_h, P.res[1] - y0);
+    float4 e0 = make_float4(0.f, 0.f, INFINITY, INFINITY), e1 = make_float4(0.f, 0.f, 0.f, __uint_as_float(0u));
+    const int s = k * P.res_x + c;
+    const float2 b = Z.seg_b[s];
+    const float4 a = Z.seg_a[s];
+    float t0, t1;
+    if (b.y != 0.f && clip_to_tile(P, a, b.x, x0, y0, w, h, t0, t1)) {
+        const float sig = P.sigma_t * kLog2e;
+        const float vsx = (P.bmax[0] - P.bmin[0]) / static_cast<float>(P.res[0]);
+        const float vsy = (P.bmax[1] - P.bmin[1]) / static_cast<float>(P.res[1]);
+        // entry / exit voxel: truncation then clip (sensor.py:345-346), tile-local
+        const float gx = fmaf(a.z, t0, a.x), gy = fmaf(a.w, t0, a.y);
+        const float hx = fmaf(a.z, t1, a.x), hy = fmaf(a.w, t1, a.y);
+        const int ix = min(max(__float2int_rz((gx - P.bmin[0]) / vsx) - x0, 0), w - 1);
+        const int iy = min(max(__float2int_rz((gy - P.bmin[1]) / vsy) - y0, 0), h - 1);
+        const int jx = min(max(__float2int_rz((hx - P.bmin[0]) / vsx) - x0, 0), w - 1);
+        const int jy = min(max(__float2int_rz((hy - P.bmin[1]) / vsy) - y0, 0), h - 1);
+        const float u0 = sig * t0;
+        unsigned bits = kEntryValid | static_cast<unsigned>(ix) | (static_cast<unsigned>(iy) << 7);
+        float ux = INFINITY, uy = INFINITY, ax = 0.f, ay = 0.f;
+        if (fabsf(a.z) > 1e-8f) {
+            const float inv = sig / a.z;
+            const bool pos = a.z > 0.f;
+            const int nx = max(pos ? jx - ix : ix - jx, 0);
+            ax = fabsf(vsx * inv);
+            if (nx > 0) ux = fmaf(fmaf(static_cast<float>(x0 + ix + (pos ? 1 : 0)), vsx, P.bmin[0]) - gx, inv, u0);
+            bits |= (static_cast<unsigned>(nx) << 14) | (pos ? 0u : (1u << 28));
+        }
+        if (fabsf(a.w) > 1e-8f) {
+            const float inv = sig / a.w;
+            const bool pos = a.w > 0.f;
+            const int ny = max(pos ? jy - iy : iy - jy, 0);
+            ay = fabsf(vsy * inv);
+            if (ny > 0) uy = fmaf(fmaf(static_cast<float>(y0 + iy + (pos ? 1 : 0)), vsy, P.bmin[1]) - gy, inv, u0);
+            bits |= (static_cast<unsigned>(ny) << 21) | (pos ? 0u : (1u << 29));
+        }
+        e0 = make_float4(u0, sig * t1, ux, uy);
+        e1 = make_float4(ax, ay, b.y, __uint_as_float(bits));
+    }
+    entries[2 * static_cast<size_t>(e)] = e0;
+    entries[2 * static_cast<size_t>(e) + 1] = e1;
+}
+
 // kScatter: in = pT, out = film (red.global flush).  kGather: in = dL (film layout), out = gT.
 template <int kMode, int kL>
 __global__ void __launch_bounds__(kZThreads, 1)
@@ -177,9 +254,9 @@ planarz_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
     const int x0 = (tile_id % Z.tiles_x) * Z.tile_w, y0 = (tile_id / Z.tiles_x) * Z.tile_h;
     const int w = min(Z.tile_w, P.res[0] - x0), h = min(Z.tile_h, P.res[1] - y0);
     const int tw = Z.tile_w;
-    constexpr int kVox = kZLaneStride * kL;           // floats per voxel: [33 lanes][kL layers]
+    constexpr int kVox = kZLaneStride * kL;  // floats per voxel: [33 lanes][kL layers]
     const int tile_floats = Z.tile_h * tw * kVox;
-    const int a_base = zb * (32 * kL);
+    const int a_base = Z.a_begin + zb * (32 * kL);
     const size_t layer_elems = static_cast<size_t>(P.res[0]) * P.res[1];
 
     // ---- stage the tile
@@ -205,14 +282,8 @@ planarz_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
     const int kb = k0 + static_cast<int>(static_cast<long long>(nk) * (group + 1) / Z.groups);
     const int* __restrict__ off = Z.tile_off + static_cast<size_t>(tile_id) * (P.n_patterns + 1);
     const int* __restrict__ clo = Z.tile_clo + static_cast<size_t>(tile_id) * P.n_patterns;
+    const float4* __restrict__ entries = Z.entries + 2 * static_cast<size_t>(__ldg(Z.tile_ebase + tile_id));
 
-    const float sig = P.sigma_t * kLog2e;
-    const float vsx = (P.bmax[0] - P.bmin[0]) / static_cast<float>(P.res[0]);
-    const float vsy = (P.bmax[1] - P.bmin[1]) / static_cast<float>(P.res[1]);
-    const float inv_vsx = 1.f / vsx, inv_vsy = 1.f / vsy;
-    // tile rectangle in world units (CTA-uniform)
-    const float xl = P.bmin[0] + static_cast<float>(x0) * vsx, xh = P.bmin[0] + static_cast<float>(x0 + w) * vsx;
-    const float yl = P.bmin[1] + static_cast<float>(y0) * vsy, yh = P.bmin[1] + static_cast<float>(y0 + h) * vsy;
     const uint32_t tile_s = static_cast<uint32_t>(__cvta_generic_to_shared(tile)) + 4u * kL * lane;
     const int sxb = 4 * kVox, syb = 4 * kVox * tw;
 
@@ -220,35 +291,14 @@ planarz_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
     int k = ka;
     for (int f = warp; f < total; f += kZWarps) {
         const int g = f + f_base;
+        const float4 e1 = __ldg(entries + 2 * static_cast<size_t>(g) + 1);
+        const unsigned bits = __float_as_uint(e1.w);
+        if (!(bits & kEntryValid)) continue;
+        const float4 e0 = __ldg(entries + 2 * static_cast<size_t>(g));
         while (__ldg(off + k + 1) <= g) ++k;
         const int c = __ldg(clo + k) + (g - __ldg(off + k));
-        const int s = k * P.res_x + c;
-        const float2 b = __ldg(Z.seg_b + s);
-        if (b.y == 0.f) continue;
-        const float4 a = __ldg(Z.seg_a + s);
 
-        // ---- clip to the tile (warp-uniform; reciprocals instead of the divisions of clip_to_tile:
-        //      a segment that only grazes the tile may be dropped or kept, its length is ~0 either way)
-        const bool vx = fabsf(a.z) > 1e-8f, vy = fabsf(a.w) > 1e-8f;
-        const float rdx = vx ? rcp_approx(a.z) : 0.f, rdy = vy ? rcp_approx(a.w) : 0.f;
-        float t0 = 0.f, t1 = b.x;
-        if (vx) {
-            const float ta = (xl - a.x) * rdx, tb = (xh - a.x) * rdx;
-            t0 = fmaxf(t0, fminf(ta, tb));
-            t1 = fminf(t1, fmaxf(ta, tb));
-        } else if (a.x < xl || a.x >= xh) {
-            continue;
-        }
-        if (vy) {
-            const float ta = (yl - a.y) * rdy, tb = (yh - a.y) * rdy;
-            t0 = fmaxf(t0, fminf(ta, tb));
-            t1 = fminf(t1, fmaxf(ta, tb));
-        } else if (a.y < yl || a.y >= yh) {
-            continue;
-        }
-        if (!(t0 < t1)) continue;
-
-        const float wray = ray_weight * b.y;
+        const float wray = ray_weight * e1.z;
         const size_t tbase = (static_cast<size_t>(k - k0) * P.res_x + c) * Z.nz_pad + a_base + lane;
         float em[kL], acc[kL];
 #pragma unroll
@@ -263,39 +313,15 @@ planarz_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
             if (!__any_sync(0xffffffffu, any)) continue;  // dark ray in all of this block's layers
         }
 
-        // ---- warp-uniform 2-D DDA inside the tile (sensor.py:345-438 restricted to z = const);
-        //      entry / exit voxel by truncation then clip, in tile-local voxel units
-        const float gx = fmaf(a.z, t0, a.x), gy = fmaf(a.w, t0, a.y);
-        const float hx = fmaf(a.z, t1, a.x), hy = fmaf(a.w, t1, a.y);
-        const int ix = min(max(__float2int_rz((gx - xl) * inv_vsx), 0), w - 1);
-        const int iy = min(max(__float2int_rz((gy - yl) * inv_vsy), 0), h - 1);
-        const int jx = min(max(__float2int_rz((hx - xl) * inv_vsx), 0), w - 1);
-        const int jy = min(max(__float2int_rz((hy - yl) * inv_vsy), 0), h - 1);
-        const float u0 = sig * t0;
-        float ux = INFINITY, uy = INFINITY, ax = 0.f, bx = 0.f, ay = 0.f, by = 0.f, fx = 0.f, fy = 0.f;
-        int sx = 0, sy = 0, nx = 0, ny = 0;
-        if (vx) {
-            const float inv = sig * rdx;
-            const bool pos = a.z > 0.f;
-            sx = pos ? sxb : -sxb;
-            nx = max(pos ? jx - ix : ix - jx, 0);
-            // boundary times relative to the tile entry: u = u(t0) + (boundary - g) * sig / d keeps the
-            // cancellation in (boundary - g); later boundaries are fx whole voxels further
-            ax = fabsf(vsx * inv);
-            bx = fmaf(fmaf(static_cast<float>(ix + (pos ? 1 : 0)), vsx, xl) - gx, inv, u0);
-            if (nx > 0) ux = bx;
-        }
-        if (vy) {
-            const float inv = sig * rdy;
-            const bool pos = a.w > 0.f;
-            sy = pos ? syb : -syb;
-            ny = max(pos ? jy - iy : iy - jy, 0);
-            ay = fabsf(vsy * inv);
-            by = fmaf(fmaf(static_cast<float>(iy + (pos ? 1 : 0)), vsy, yl) - gy, inv, u0);
-            if (ny > 0) uy = by;
-        }
+        // ---- warp-uniform 2-D DDA inside the tile (sensor.py:345-438 restricted to z = const)
+        const int ix = bits & 127, iy = (bits >> 7) & 127;
+        int nx = (bits >> 14) & 127, ny = (bits >> 21) & 127;
+        const int sx = (bits & (1u << 28)) ? -sxb : sxb, sy = (bits & (1u << 29)) ? -syb : syb;
+        float ux = e0.z, uy = e0.w;
+        const float ax = e1.x, ay = e1.y, bx = e0.z, by = e0.w;
+        float fx = 0.f, fy = 0.f;
         uint32_t addr = tile_s + static_cast<uint32_t>((iy * tw + ix) * (4 * kVox));
-        float e_prev = ex2_approx(-u0);
+        float e_prev = ex2_approx(-e0.x);
         auto deposit = [&](float de) {
             if (kMode == kGather) z_gather<kL>(addr, acc, de);
             else z_scatter<kL>(addr, em, de);
@@ -320,7 +346,7 @@ planarz_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
                 if (--ny == 0) uy = INFINITY;
             }
         }
-        deposit(e_prev - ex2_approx(-sig * t1));
+        deposit(e_prev - ex2_approx(-e0.y));
 
         if (kMode == kGather) {
 #pragma unroll
@@ -367,14 +393,19 @@ planarz_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
     } while (0)
 
 void planarz_release(PlanarZHost& H) {
-    void* ptrs[] = {H.tile_off, H.tile_clo, H.zl, H.a_row_begin, H.a_rows, H.row_a, H.scratch};
+    for (PlanarZSub& S : H.sub) {
+        void* ptrs[] = {S.tile_off, S.tile_clo, S.tile_ebase, S.entries};
+        for (void* p : ptrs)
+            if (p) cudaFree(p);
+    }
+    void* ptrs[] = {H.zl, H.a_row_begin, H.a_rows, H.row_a, H.scratch};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     H = PlanarZHost();
 }
 
 // Tile geometry for kL layers per lane: the largest xy tile whose
-// [kL][h][w][33] float slab fits the 227 KB of opt-in shared memory.
+// [h][w][33][kL] float slab fits the 227 KB of opt-in shared memory.
 static void z_tile_dims(int rx, int ry, int kL, int& tw, int& th) {
     const int max_floats = (227 * 1024) / 4;
     const int area = max_floats / (kZLaneStride * kL);
@@ -387,71 +418,104 @@ static void z_tile_dims(int rx, int ry, int kL, int& tw, int& th) {
     th = (ry + tiles_y - 1) / tiles_y;
 }
 
-cudaError_t planarz_build(const SceneParams& P, const PlanarHost& base, const std::vector<int>& row_layer,
-                          PlanarZHost& H) {
-    planarz_release(H);
-    int kL = 4;
-    if (const char* env = std::getenv("DRTVAM_Z_LAYERS")) {
-        const int v = std::atoi(env);
-        if (v == 1 || v == 2 || v == 4) kL = v;
-    }
-    const int rz = P.res[2], Hh = P.res_y, np = P.n_patterns;
-    // active layers and their rows
-    std::vector<int> layer_a(rz, -1), zl, a_row_begin(1, 0), a_rows, row_a(Hh, -1);
-    std::vector<std::vector<int>> rows_of(rz);
-    for (int r = 0; r < Hh; ++r)
-        if (row_layer[r] >= 0) rows_of[row_layer[r]].push_back(r);
-    for (int z = 0; z < rz; ++z) {
-        if (rows_of[z].empty()) continue;
-        layer_a[z] = static_cast<int>(zl.size());
-        zl.push_back(z);
-        for (int r : rows_of[z]) { a_rows.push_back(r); row_a[r] = layer_a[z]; }
-        a_row_begin.push_back(static_cast<int>(a_rows.size()));
-    }
-    const int nz = static_cast<int>(zl.size());
-    if (nz == 0) return cudaSuccess;  // nothing deposits: leave the plan invalid
-    // small problems: fewer layers per lane keeps more CTAs in flight
-    while (kL > 1 && nz <= 32 * (kL / 2)) kL /= 2;
-    const int block = 32 * kL;
-    const int nz_pad = (nz + block - 1) / block * block;
-    zl.resize(nz_pad, -1);
-    if (a_rows.empty()) a_rows.push_back(0);
+template <int kL>
+static cudaError_t z_set_smem(size_t bytes) {
+    PZ_TRY(cudaFuncSetAttribute(planarz_kernel<kScatter, kL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                static_cast<int>(bytes)));
+    return cudaFuncSetAttribute(planarz_kernel<kGather, kL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                static_cast<int>(bytes));
+}
 
-    PlanarZPlan& Z = H.plan;
+static cudaError_t z_build_sub(const SceneParams& P, const PlanarHost& base, const PlanarZHost& H, int kL, int a_begin,
+                               int n_blocks, PlanarZSub& S) {
+    const int np = P.n_patterns;
+    PlanarZPlan& Z = S.plan;
     Z.seg_a = base.seg_a;
     Z.seg_b = base.seg_b;
     z_tile_dims(P.res[0], P.res[1], kL, Z.tile_w, Z.tile_h);
     Z.tiles_x = (P.res[0] + Z.tile_w - 1) / Z.tile_w;
     Z.tiles_y = (P.res[1] + Z.tile_h - 1) / Z.tile_h;
-    Z.nz = nz;
-    Z.nz_pad = nz_pad;
+    Z.nz = H.nz;
+    Z.nz_pad = H.nz_pad;
     Z.lanes_l = kL;
+    Z.a_begin = a_begin;
     Z.groups = 1;
+    Z.zl = H.zl; Z.a_row_begin = H.a_row_begin; Z.a_rows = H.a_rows; Z.row_a = H.row_a;
+    S.n_blocks = n_blocks;
     const int n_tiles = Z.tiles_x * Z.tiles_y;
-    H.smem_bytes = sizeof(float) * static_cast<size_t>(kL) * Z.tile_h * Z.tile_w * kZLaneStride;
+    S.smem_bytes = sizeof(float) * static_cast<size_t>(kL) * Z.tile_h * Z.tile_w * kZLaneStride;
+    PZ_TRY(cudaMalloc(&S.tile_off, sizeof(int) * n_tiles * (np + 1)));
+    PZ_TRY(cudaMalloc(&S.tile_clo, sizeof(int) * n_tiles * np));
+    PZ_TRY(cudaMalloc(&S.tile_ebase, sizeof(int) * (n_tiles + 1)));
+    PZ_TRY(planar_tile_ranges(P, base.seg_a, base.seg_b, Z.tiles_x, Z.tiles_y, Z.tile_w, Z.tile_h, S.tile_off,
+                              S.tile_clo));
+    // entry base of every tile = prefix of the per-tile totals (last element of each tile's prefix row)
+    std::vector<int> last(n_tiles), ebase(n_tiles + 1, 0);
+    PZ_TRY(cudaMemcpy2D(last.data(), sizeof(int), S.tile_off + np, sizeof(int) * (np + 1), sizeof(int), n_tiles,
+                        cudaMemcpyDeviceToHost));
+    long long total = 0;
+    for (int t = 0; t < n_tiles; ++t) { ebase[t] = static_cast<int>(total); total += last[t]; }
+    if (total >= (1ll << 30)) return cudaErrorInvalidValue;
+    ebase[n_tiles] = static_cast<int>(total);
+    PZ_TRY(cudaMemcpy(S.tile_ebase, ebase.data(), sizeof(int) * (n_tiles + 1), cudaMemcpyHostToDevice));
+    PZ_TRY(cudaMalloc(&S.entries, sizeof(float4) * 2 * static_cast<size_t>(std::max<long long>(total, 1))));
+    Z.tile_off = S.tile_off; Z.tile_clo = S.tile_clo; Z.tile_ebase = S.tile_ebase; Z.entries = S.entries;
+    if (total > 0) {
+        zsetup_kernel<<<static_cast<unsigned>((total + 255) / 256), 256>>>(P, Z, S.entries, static_cast<int>(total));
+        count_launch();
+        PZ_TRY(cudaGetLastError());
+    }
+    if (kL == 1) return z_set_smem<1>(S.smem_bytes);
+    if (kL == 2) return z_set_smem<2>(S.smem_bytes);
+    return z_set_smem<4>(S.smem_bytes);
+}
 
-    PZ_TRY(cudaMalloc(&H.tile_off, sizeof(int) * n_tiles * (np + 1)));
-    PZ_TRY(cudaMalloc(&H.tile_clo, sizeof(int) * n_tiles * np));
-    PZ_TRY(cudaMalloc(&H.zl, sizeof(int) * nz_pad));
+cudaError_t planarz_build(const SceneParams& P, const PlanarHost& base, const std::vector<int>& row_layer,
+                          PlanarZHost& H) {
+    planarz_release(H);
+    int max_l = 4;
+    if (const char* env = std::getenv("DRTVAM_Z_LAYERS")) {
+        const int v = std::atoi(env);
+        if (v == 1 || v == 2 || v == 4) max_l = v;
+    }
+    const int rz = P.res[2], Hh = P.res_y;
+    // active layers and their rows
+    std::vector<int> zl, a_row_begin(1, 0), a_rows, row_a(Hh, -1);
+    std::vector<std::vector<int>> rows_of(rz);
+    for (int r = 0; r < Hh; ++r)
+        if (row_layer[r] >= 0) rows_of[row_layer[r]].push_back(r);
+    for (int z = 0; z < rz; ++z) {
+        if (rows_of[z].empty()) continue;
+        for (int r : rows_of[z]) { a_rows.push_back(r); row_a[r] = static_cast<int>(zl.size()); }
+        zl.push_back(z);
+        a_row_begin.push_back(static_cast<int>(a_rows.size()));
+    }
+    const int nz = static_cast<int>(zl.size());
+    if (nz == 0) return cudaSuccess;  // nothing deposits: leave the plan invalid
+    const int units = (nz + 31) / 32;  // warps' worth of layers
+    H.nz = nz;
+    H.nz_pad = units * 32;
+    zl.resize(H.nz_pad, -1);
+    if (a_rows.empty()) a_rows.push_back(0);
+    PZ_TRY(cudaMalloc(&H.zl, sizeof(int) * H.nz_pad));
     PZ_TRY(cudaMalloc(&H.a_row_begin, sizeof(int) * (nz + 1)));
     PZ_TRY(cudaMalloc(&H.a_rows, sizeof(int) * a_rows.size()));
     PZ_TRY(cudaMalloc(&H.row_a, sizeof(int) * Hh));
-    PZ_TRY(cudaMemcpy(H.zl, zl.data(), sizeof(int) * nz_pad, cudaMemcpyHostToDevice));
+    PZ_TRY(cudaMemcpy(H.zl, zl.data(), sizeof(int) * H.nz_pad, cudaMemcpyHostToDevice));
     PZ_TRY(cudaMemcpy(H.a_row_begin, a_row_begin.data(), sizeof(int) * (nz + 1), cudaMemcpyHostToDevice));
     PZ_TRY(cudaMemcpy(H.a_rows, a_rows.data(), sizeof(int) * a_rows.size(), cudaMemcpyHostToDevice));
     PZ_TRY(cudaMemcpy(H.row_a, row_a.data(), sizeof(int) * Hh, cudaMemcpyHostToDevice));
-    PZ_TRY(planar_tile_ranges(P, base.seg_a, base.seg_b, Z.tiles_x, Z.tiles_y, Z.tile_w, Z.tile_h, H.tile_off,
-                              H.tile_clo));
-    Z.tile_off = H.tile_off; Z.tile_clo = H.tile_clo; Z.zl = H.zl;
-    Z.a_row_begin = H.a_row_begin; Z.a_rows = H.a_rows; Z.row_a = H.row_a;
 
-    const int smem = static_cast<int>(H.smem_bytes);
-#define PZ_ATTR(MODE, LL) \
-    PZ_TRY(cudaFuncSetAttribute(planarz_kernel<MODE, LL>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem))
-    if (kL == 1) { PZ_ATTR(kScatter, 1); PZ_ATTR(kGather, 1); }
-    else if (kL == 2) { PZ_ATTR(kScatter, 2); PZ_ATTR(kGather, 2); }
-    else { PZ_ATTR(kScatter, 4); PZ_ATTR(kGather, 4); }
-#undef PZ_ATTR
+    // split the layer units into runs of blocks with 4, 2 and 1 layers per lane (no padded blocks)
+    int done = 0;
+    for (int kL = max_l; kL >= 1 && done < units; kL >>= 1) {
+        const int n_blocks = (units - done) / kL;
+        if (n_blocks == 0) continue;
+        PZ_TRY(z_build_sub(P, base, H, kL, done * 32, n_blocks, H.sub[H.n_sub]));
+        ++H.n_sub;
+        done += n_blocks * kL;
+    }
+    PZ_TRY(cudaDeviceSynchronize());
     H.valid = true;
     return cudaSuccess;
 }
@@ -466,56 +530,65 @@ static cudaError_t z_scratch(PlanarZHost& H, size_t bytes) {
     return cudaSuccess;
 }
 
-static int z_groups(const SceneParams& P, const PlanarZPlan& Z, int nk) {
-    const long long ctas = static_cast<long long>(Z.tiles_x) * Z.tiles_y * (Z.nz_pad / (32 * Z.lanes_l));
-    long long g = (148 * 2 + ctas - 1) / ctas;
+static int z_groups(const PlanarZHost& H, int nk) {
+    long long ctas = 0;
+    for (int i = 0; i < H.n_sub; ++i)
+        ctas += static_cast<long long>(H.sub[i].plan.tiles_x) * H.sub[i].plan.tiles_y * H.sub[i].n_blocks;
+    long long g = (148 * 2 + ctas - 1) / std::max<long long>(ctas, 1);
     g = std::min<long long>(g, std::max(1, nk / 8));
     g = std::min<long long>(g, 64);
-    (void)P;
     return g < 1 ? 1 : static_cast<int>(g);
 }
 
 template <int kMode>
-static cudaError_t z_launch(const SceneParams& P, const PlanarZPlan& Z, size_t smem, const float* in, float* out,
+static cudaError_t z_launch(const SceneParams& P, PlanarZHost& H, const float* in, float* out,
                             const uint32_t* active_pixels, uint64_t n_active, float w, const int* gate,
                             cudaStream_t stream) {
-    const dim3 grid(Z.tiles_x * Z.tiles_y, Z.nz_pad / (32 * Z.lanes_l), Z.groups);
-    if (Z.lanes_l == 1)
-        planarz_kernel<kMode, 1><<<grid, kZThreads, smem, stream>>>(P, Z, in, out, active_pixels, n_active, w, gate);
-    else if (Z.lanes_l == 2)
-        planarz_kernel<kMode, 2><<<grid, kZThreads, smem, stream>>>(P, Z, in, out, active_pixels, n_active, w, gate);
-    else
-        planarz_kernel<kMode, 4><<<grid, kZThreads, smem, stream>>>(P, Z, in, out, active_pixels, n_active, w, gate);
-    count_launch();
-    return cudaGetLastError();
+    const int nk = static_cast<int>(n_active / (static_cast<uint64_t>(P.res_x) * P.res_y));
+    const int groups = z_groups(H, nk);
+    for (int i = 0; i < H.n_sub; ++i) {
+        const PlanarZSub& S = H.sub[i];
+        PlanarZPlan Z = S.plan;
+        Z.groups = groups;
+        const dim3 grid(Z.tiles_x * Z.tiles_y, S.n_blocks, groups);
+        if (Z.lanes_l == 1)
+            planarz_kernel<kMode, 1><<<grid, kZThreads, S.smem_bytes, stream>>>(P, Z, in, out, active_pixels, n_active,
+                                                                               w, gate);
+        else if (Z.lanes_l == 2)
+            planarz_kernel<kMode, 2><<<grid, kZThreads, S.smem_bytes, stream>>>(P, Z, in, out, active_pixels, n_active,
+                                                                               w, gate);
+        else
+            planarz_kernel<kMode, 4><<<grid, kZThreads, S.smem_bytes, stream>>>(P, Z, in, out, active_pixels, n_active,
+                                                                               w, gate);
+        count_launch();
+        PZ_TRY(cudaGetLastError());
+    }
+    return cudaSuccess;
 }
 
 cudaError_t launch_planarz_forward(const SceneParams& P, PlanarZHost& H, const int* gate, const float* active_data,
                                    const uint32_t* active_pixels, uint64_t n_active, float ray_weight, float* film,
                                    cudaStream_t stream) {
     const int nk = static_cast<int>(n_active / (static_cast<uint64_t>(P.res_x) * P.res_y));
-    PlanarZPlan Z = H.plan;
-    Z.groups = z_groups(P, Z, nk);
-    PZ_TRY(z_scratch(H, sizeof(float) * static_cast<size_t>(nk) * P.res_x * Z.nz_pad));
-    const dim3 pgrid((P.res_x + 31) / 32, Z.nz_pad / 32, nk);
-    zpack_kernel<<<pgrid, 256, 0, stream>>>(P, Z, active_data, H.scratch, nk, gate);
+    const PlanarZPlan& Z0 = H.sub[0].plan;
+    PZ_TRY(z_scratch(H, sizeof(float) * static_cast<size_t>(nk) * P.res_x * H.nz_pad));
+    const dim3 pgrid((P.res_x + 31) / 32, H.nz_pad / 32, nk);
+    zpack_kernel<<<pgrid, 256, 0, stream>>>(P, Z0, active_data, H.scratch, nk, gate);
     count_launch();
     PZ_TRY(cudaGetLastError());
-    return z_launch<kScatter>(P, Z, H.smem_bytes, H.scratch, film, active_pixels, n_active, ray_weight, gate, stream);
+    return z_launch<kScatter>(P, H, H.scratch, film, active_pixels, n_active, ray_weight, gate, stream);
 }
 
 cudaError_t launch_planarz_adjoint(const SceneParams& P, PlanarZHost& H, const int* gate, const float* dL,
                                    const uint32_t* active_pixels, uint64_t n_active, float ray_weight, float* grad,
                                    cudaStream_t stream) {
     const int nk = static_cast<int>(n_active / (static_cast<uint64_t>(P.res_x) * P.res_y));
-    PlanarZPlan Z = H.plan;
-    Z.groups = z_groups(P, Z, nk);
-    const size_t bytes = sizeof(float) * static_cast<size_t>(nk) * P.res_x * Z.nz_pad;
+    const size_t bytes = sizeof(float) * static_cast<size_t>(nk) * P.res_x * H.nz_pad;
     PZ_TRY(z_scratch(H, bytes));
     PZ_TRY(cudaMemsetAsync(H.scratch, 0, bytes, stream));
-    PZ_TRY(z_launch<kGather>(P, Z, H.smem_bytes, dL, H.scratch, active_pixels, n_active, ray_weight, gate, stream));
+    PZ_TRY(z_launch<kGather>(P, H, dL, H.scratch, active_pixels, n_active, ray_weight, gate, stream));
     const dim3 ugrid((P.res_x + 31) / 32, (P.res_y + 31) / 32, nk);
-    zunpack_kernel<<<ugrid, 256, 0, stream>>>(P, Z, H.scratch, grad, gate);
+    zunpack_kernel<<<ugrid, 256, 0, stream>>>(P, H.sub[0].plan, H.scratch, grad, gate);
     count_launch();
     return cudaGetLastError();
 }

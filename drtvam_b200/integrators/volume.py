@@ -45,6 +45,19 @@ class VolumeIntegrator(TVAMIntegrator):
 
     __repr__ = to_string
 
+    # CUDA-event timing of the C-ABI calls (the analogue of the reference's
+    # KernelHistory timing, optimize.py:291,306,323): set `integrator.events = {}`
+    # to collect {'forward' | 'adjoint' | 'allreduce': [(start, end), ...]}.
+    events = None
+
+    def _event_pair(self, name):
+        if self.events is None:
+            return None
+        pair = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+        pair[0].record()
+        self.events.setdefault(name, []).append(pair)
+        return pair
+
     def _project(self, scene, sensor, seed, spp, active_data):
         sensor = _sensor_of(scene, sensor)
         projector = scene.emitters()[0]
@@ -58,10 +71,16 @@ class VolumeIntegrator(TVAMIntegrator):
         if data.numel() != pixels.numel():
             raise ValueError(f"[{projector.__class__.__name__}] active_data and active_pixels must have the same length.")
         lib = _lib.load()
+        ev = self._event_pair('forward')
         _lib.check(lib.drtvam_forward(handle, data.data_ptr(), pixels.data_ptr(), data.numel(), spp,
                                       seed & 0xFFFFFFFF, inv_scalar, film.data.data_ptr(), 1,
                                       torch.cuda.current_stream(film.data.device).cuda_stream))
+        if ev is not None:
+            ev[1].record()
+        ev = self._event_pair('allreduce') if scene.world_size > 1 else None
         scene.reduce_dose(film.data)
+        if ev is not None:
+            ev[1].record()
         out = film.data
         if inv_tensor is not None:
             out = out * inv_tensor
@@ -100,7 +119,10 @@ class VolumeIntegrator(TVAMIntegrator):
         pixels = projector.active_pixels
         out = torch.empty(pixels.numel(), device=g.device, dtype=torch.float32)
         lib = _lib.load()
+        ev = self._event_pair('adjoint')
         _lib.check(lib.drtvam_adjoint(handle, g.data_ptr(), pixels.data_ptr(), pixels.numel(), spp,
                                       seed & 0xFFFFFFFF, inv_scalar, out.data_ptr(),
                                       torch.cuda.current_stream(g.device).cuda_stream))
+        if ev is not None:
+            ev[1].record()
         return out
