@@ -208,7 +208,7 @@ def main():
     import drtvam_b200 as dv
     from drtvam_b200 import _lib
     from drtvam_b200.integrators import VolumeIntegrator
-    from drtvam_b200.loss import ThresholdedLoss
+    from drtvam_b200.loss import LazyAxpy, ThresholdedLoss
     from drtvam_b200.optimize import load_scene
     from drtvam_b200.utils import discretize
 
@@ -248,7 +248,7 @@ def main():
         with torch.no_grad():
             scene.projector.active_data = d
             dvol = dv.render(scene, None, integrator=integ, sensor=sensor, spp=spp, seed=seed)   # A d
-            f_new = loss_fn(vol.detach() + 1.0 * dvol, target, d)                                # Armijo trial
+            f_new = loss_fn(LazyAxpy(vol.detach(), dvol, 1.0), target, d)                        # Armijo trial
         return loss.detach(), f_new, p.grad
 
     pass_events = {}

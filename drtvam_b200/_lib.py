@@ -11,7 +11,7 @@ import os
 from . import build as _build
 
 MAX_SURFACES = 8
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 
 class DrtvamSurface(C.Structure):
@@ -61,6 +61,8 @@ SYMBOLS = {
     "drtvam_count_visits": (C.c_int, [_vp, _vp, _u64, _u32, _u32, C.POINTER(_u64)]),
     "drtvam_forward_host": (C.c_int, [_vp, _vp, _vp, _u64, _u32, _u32, _f32, _vp]),
     "drtvam_adjoint_host": (C.c_int, [_vp, _vp, _vp, _u64, _u32, _u32, _f32, _vp]),
+    "drtvam_thresholded_loss": (C.c_int, [C.c_int, _vp, _vp, _f32, _vp, _u64, _f32, _f32, _f32, _f32, _f32, _i32, _f32,
+                                          _vp, _vp, _vp]),
     "drtvam_launch_count": (_u64, []),
     "drtvam_last_error": (C.c_char_p, []),
     "drtvam_abi_version": (C.c_int, []),

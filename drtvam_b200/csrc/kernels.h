@@ -106,4 +106,9 @@ cudaError_t launch_planarz_adjoint(const SceneParams& P, PlanarZHost& H, const i
                                    const uint32_t* active_pixels, uint64_t n_active, float ray_weight, float* grad,
                                    cudaStream_t stream);
 
+// fused thresholded loss + gradient on the dose volume (loss_kernels.cu)
+cudaError_t launch_thresholded_loss(const float* x, const float* x_b, float alpha, const float* target, size_t n,
+                                    float tl, float tu, float w_obj, float w_void, float w_lim, int K, float grad_scale,
+                                    float* grad, double* loss_out, cudaStream_t stream);
+
 }  // namespace drtvam

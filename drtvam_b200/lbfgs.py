@@ -9,6 +9,8 @@ from __future__ import annotations
 
 import torch
 
+from .loss import LazyAxpy
+
 
 class Optimizer:
     """Dict-like holder of optimised variables (the role of ``mi.ad.Optimizer``)."""
@@ -118,7 +120,9 @@ class LinearLBFGS(Optimizer):
             for _ in range(self.search_it):
                 trials += 1
                 # note: the pattern term sees the *direction*, as in lbfgs.py:260
-                f_new = self.loss_fn(vol + alpha * dvol, params['projector.active_data']
+                y_trial = LazyAxpy(vol, dvol, alpha) if getattr(self.loss_fn, 'accepts_lazy', False) \
+                    else vol + alpha * dvol
+                f_new = self.loss_fn(y_trial, params['projector.active_data']
                                      if 'projector.active_data' in params else next(iter(params.values())))
                 if bool((f_new <= loss + c1 * alpha * g_dot_z).all()):
                     break

@@ -12,6 +12,57 @@ def relu(x):
     return torch.clamp_min(x, 0)
 
 
+class LazyAxpy:
+    """`x + alpha * dx` that has not been formed yet.  LinearLBFGS hands it to a
+    loss that declares `accepts_lazy` for the Armijo trials (lbfgs.py:258), so
+    the fused CUDA loss can read both volumes once instead of materialising
+    their sum; any other loss gets `materialize()`."""
+
+    def __init__(self, x, dx, alpha):
+        self.x, self.dx, self.alpha = x, dx, float(alpha)
+
+    @property
+    def shape(self):
+        return self.x.shape
+
+    def dim(self):
+        return self.x.dim()
+
+    def materialize(self):
+        return self.x + self.alpha * self.dx
+
+
+class _FusedThresholded(torch.autograd.Function):
+    """ThresholdedLoss on a CUDA dose volume through drtvam_thresholded_loss
+    (csrc/loss_kernels.cu): loss and d loss / d dose in one pass."""
+
+    @staticmethod
+    def forward(ctx, x, dx, alpha, target, loss):
+        from . import _lib
+        lib = _lib.load()
+        n = x.numel()
+        need_grad = x.requires_grad and torch.is_grad_enabled()
+        ctx.has_grad = bool(x.requires_grad)
+        grad = torch.empty_like(x) if x.requires_grad else None
+        out = torch.empty(1, device=x.device, dtype=torch.float64)
+        mean = loss.reduction is torch.mean
+        _lib.check(lib.drtvam_thresholded_loss(
+            x.device.index or 0, x.data_ptr(), dx.data_ptr() if dx is not None else None, float(alpha),
+            target.data_ptr(), n, float(loss.tl), float(loss.tu), float(loss.weight_object), float(loss.weight_void),
+            float(loss.weight_limit), int(loss.K), (1.0 / n) if mean else 1.0,
+            grad.data_ptr() if grad is not None else None, out.data_ptr(),
+            torch.cuda.current_stream(x.device).cuda_stream))
+        ctx.grad = grad
+        del need_grad
+        res = out[0] / n if mean else out[0]
+        return res.to(torch.float32)
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        g = ctx.grad * grad_out if ctx.grad is not None else None
+        return g, None, None, None, None
+
+
 class Loss:
     def __init__(self, props):
         reduction = props.get('reduction', 'sum')
@@ -46,7 +97,11 @@ class Loss:
             return self.pattern_allsum(lp.sum()) / n
         return self.pattern_allsum(lp.sum())
 
+    accepts_lazy = True
+
     def __call__(self, x, target, patterns):
+        if isinstance(x, LazyAxpy):
+            x = x.materialize()
         if x.shape != target.shape:
             if x.dim() == target.dim() + 1 and x.shape[-1] == 1:
                 target = target[..., None]
@@ -117,6 +172,30 @@ class ThresholdedLoss(Loss):
     def eval(self, x, target, patterns):
         # target is a binary inside/outside mask
         return torch.where(target > 0, self.eval_in(x), self.eval_out(x)), self.eval_sparsity(patterns)
+
+    accepts_lazy = True
+
+    def _fusable(self, x, target):
+        if not (isinstance(x, torch.Tensor) and x.is_cuda and x.dtype == torch.float32 and x.is_contiguous()):
+            return False
+        if not (isinstance(target, torch.Tensor) and target.is_cuda and target.dtype == torch.float32
+                and target.is_contiguous() and target.numel() == x.numel()):
+            return False
+        if x.shape != target.shape and not (x.dim() == target.dim() + 1 and x.shape[-1] == 1):
+            return False
+        if target.shape == x.shape and x.shape[-1] == 2 and x.dim() == 4:
+            return False  # surface-aware two-channel volumes take the generic path
+        return float(self.K).is_integer() and 1 <= int(self.K) <= 8
+
+    def __call__(self, x, target, patterns):
+        lazy = isinstance(x, LazyAxpy)
+        base = x.x if lazy else x
+        if not self._fusable(base, target) or (lazy and not self._fusable(x.dx, target)):
+            return super().__call__(x.materialize() if lazy else x, target, patterns)
+        loss = _FusedThresholded.apply(base, x.dx if lazy else None, x.alpha if lazy else 0.0, target, self)
+        if self.weight_sparsity != 0:
+            loss = loss + self._reduce_patterns(self.eval_sparsity(patterns))
+        return loss
 
 
 losses = {

@@ -160,6 +160,7 @@ def optimize(config, patterns_fwd=None, progress=True):
 
     def loss_fn2(y, patterns):
         return loss_fn(y, target, patterns)
+    loss_fn2.accepts_lazy = getattr(loss_fn, 'accepts_lazy', False)
 
     opt = LinearLBFGS(loss_fn=loss_fn2, render_fn=render_fn, dot=parallel.make_dot(None, world), **opt_cfg)
     opt[patterns_key] = params[patterns_key]

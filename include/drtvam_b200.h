@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define DRTVAM_ABI_VERSION 3
+#define DRTVAM_ABI_VERSION 4
 #define DRTVAM_MAX_SURFACES 8
 
 #define DRTVAM_OK 0
@@ -154,6 +154,17 @@ int drtvam_forward_host(DrtvamScene *scene, const float *active_data_host,
 int drtvam_adjoint_host(DrtvamScene *scene, const float *dose_grad_host,
                         const uint32_t *active_pixels_host, uint64_t n_active, uint32_t spp,
                         uint32_t seed, float in_scale, float *pattern_grad_host);
+
+/* Caller of the path (next row): ThresholdedLoss on the
+ * dose volume, loss.py:102-132 with Loss.__call__'s reduction (loss.py:58-59),
+ * binary target (target > 0 = inside).  Evaluates at dose + alpha * dose_b
+ * when dose_b != NULL (the Armijo trial of lbfgs.py:258).  *loss_out (device
+ * double) receives the SUM over voxels; grad (may be NULL) receives
+ * grad_scale * d sum / d dose (grad_scale = 1/N for reduction 'mean'). */
+int drtvam_thresholded_loss(int device, const float *dose, const float *dose_b, float alpha, const float *target,
+                            uint64_t n, float tl, float tu, float weight_object, float weight_void,
+                            float weight_limit, int32_t K, float grad_scale, float *grad, double *loss_out,
+                            void *stream);
 
 /* number of kernels this library has launched since load (bench gpu_launches) */
 uint64_t drtvam_launch_count(void);

@@ -447,3 +447,40 @@ def test_layer_parallel_kernels_all_register_blockings(layers, workdir, monkeypa
     assert _plan(h, pix.size) == 2
     assert rel_l2(h.forward(p, pix), o.forward(p, pix)) < TOL
     assert rel_l2(h.adjoint(g, pix), o.adjoint(g, pix)) < TOL
+
+
+# ---------------------------------------------------------------------------
+# fused thresholded loss (csrc/loss_kernels.cu) vs the elementwise torch form
+# ---------------------------------------------------------------------------
+@pytest.mark.parametrize("reduction", ["sum", "mean"])
+@pytest.mark.parametrize("K", [1, 2, 3])
+def test_fused_thresholded_loss_matches_torch(K, reduction):
+    """loss.py:102-132: value and d loss / d dose of the fused CUDA loss against
+    the reference's formula evaluated with torch ops (fp64), incl. the lazy
+    `vol + alpha dvol` form used by the Armijo trials (lbfgs.py:258)."""
+    from drtvam_b200.loss import LazyAxpy, ThresholdedLoss
+    g = torch.Generator(device="cuda").manual_seed(5)
+    shape = (37, 41, 43, 1)  # odd sizes: exercises the scalar tail
+    x = (torch.rand(shape, device="cuda", generator=g) * 1.6).requires_grad_(True)
+    dx = torch.randn(shape, device="cuda", generator=g) * 0.1
+    target = (torch.rand(shape[:-1], device="cuda", generator=g) > 0.6).float()
+    props = {"K": K, "tl": 0.85, "tu": 0.93, "weight_object": 1.5, "weight_void": 0.7, "weight_limit": 2.0,
+             "reduction": reduction}
+    fused = ThresholdedLoss(props)
+    loss = fused(x, target, torch.zeros(3, device="cuda"))
+    loss.backward()
+    # reference formula in fp64
+    xd = x.detach().double().requires_grad_(True)
+    t = target[..., None].double()
+    inside = props["weight_object"] * torch.clamp_min(props["tu"] - xd, 0) ** K + \
+        props["weight_limit"] * torch.clamp_min(xd - 1.0, 0) ** K
+    outside = props["weight_void"] * torch.clamp_min(xd - props["tl"], 0) ** K
+    ref = torch.where(t > 0, inside, outside)
+    ref = ref.sum() if reduction == "sum" else ref.mean()
+    ref.backward()
+    assert abs(float(loss) - float(ref)) < 2e-6 * abs(float(ref))
+    assert rel_l2(x.grad.cpu().numpy(), xd.grad.cpu().numpy()) < 1e-6
+    with torch.no_grad():
+        lazy = fused(LazyAxpy(x.detach(), dx, 0.5), target, torch.zeros(3, device="cuda"))
+        generic = super(ThresholdedLoss, fused).__call__(x.detach() + 0.5 * dx, target, torch.zeros(3, device="cuda"))
+    assert abs(float(lazy) - float(generic)) < 1e-5 * abs(float(generic))
