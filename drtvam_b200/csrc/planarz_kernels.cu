@@ -164,6 +164,49 @@ __device__ __forceinline__ void z_gather(uint32_t addr, float (&acc)[kL], float 
     }
 }
 
+// Two deposits in flight: the loads and the compare-and-swaps of two consecutive voxels of the
+// walk are issued back to back, so the shared-memory latency of one hides behind the other (a warp
+// never visits the same voxel twice in a row, so the two never alias within the warp).
+template <int kL>
+__device__ __forceinline__ void z_scatter2(uint32_t addr_a, float de_a, uint32_t addr_b, float de_b,
+                                           const float (&em)[kL]) {
+    if constexpr (kL == 4) {
+        float a0, a1, a2, a3, b0, b1, b2, b3;
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(a0), "=f"(a1), "=f"(a2), "=f"(a3) : "r"(addr_a));
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(b0), "=f"(b1), "=f"(b2), "=f"(b3) : "r"(addr_b));
+        float ra0, ra1, ra2, ra3, rb0, rb1, rb2, rb3;
+        asm volatile(
+            "{\n\t.reg .b128 c, u, r;\n\t"
+            "mov.b128 c, {%4, %5, %6, %7};\n\t"
+            "mov.b128 u, {%8, %9, %10, %11};\n\t"
+            "atom.shared.cas.b128 r, [%12], c, u;\n\t"
+            "mov.b128 {%0, %1, %2, %3}, r;\n\t}"
+            : "=f"(ra0), "=f"(ra1), "=f"(ra2), "=f"(ra3)
+            : "f"(a0), "f"(a1), "f"(a2), "f"(a3), "f"(fmaf(em[0], de_a, a0)), "f"(fmaf(em[1], de_a, a1)),
+              "f"(fmaf(em[2], de_a, a2)), "f"(fmaf(em[3], de_a, a3)), "r"(addr_a)
+            : "memory");
+        asm volatile(
+            "{\n\t.reg .b128 c, u, r;\n\t"
+            "mov.b128 c, {%4, %5, %6, %7};\n\t"
+            "mov.b128 u, {%8, %9, %10, %11};\n\t"
+            "atom.shared.cas.b128 r, [%12], c, u;\n\t"
+            "mov.b128 {%0, %1, %2, %3}, r;\n\t}"
+            : "=f"(rb0), "=f"(rb1), "=f"(rb2), "=f"(rb3)
+            : "f"(b0), "f"(b1), "f"(b2), "f"(b3), "f"(fmaf(em[0], de_b, b0)), "f"(fmaf(em[1], de_b, b1)),
+              "f"(fmaf(em[2], de_b, b2)), "f"(fmaf(em[3], de_b, b3)), "r"(addr_b)
+            : "memory");
+        const bool fail_a = (__float_as_uint(ra0) != __float_as_uint(a0)) | (__float_as_uint(ra1) != __float_as_uint(a1)) |
+                            (__float_as_uint(ra2) != __float_as_uint(a2)) | (__float_as_uint(ra3) != __float_as_uint(a3));
+        const bool fail_b = (__float_as_uint(rb0) != __float_as_uint(b0)) | (__float_as_uint(rb1) != __float_as_uint(b1)) |
+                            (__float_as_uint(rb2) != __float_as_uint(b2)) | (__float_as_uint(rb3) != __float_as_uint(b3));
+        if (fail_a) z_scatter<kL>(addr_a, em, de_a);  // another warp got in between: the plain retry loop
+        if (fail_b) z_scatter<kL>(addr_b, em, de_b);
+    } else {
+        z_scatter<kL>(addr_a, em, de_a);
+        z_scatter<kL>(addr_b, em, de_b);
+    }
+}
+
 // ---------------------------------------------------------------------------
 // Walk entries.  The clipped 2-D walk of a (tile, angle, column) triple depends
 // only on the scene, not on the patterns, so it is computed once per scene
@@ -322,31 +365,71 @@ planarz_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
         float fx = 0.f, fy = 0.f;
         uint32_t addr = tile_s + static_cast<uint32_t>((iy * tw + ix) * (4 * kVox));
         float e_prev = ex2_approx(-e0.x);
-        auto deposit = [&](float de) {
-            if (kMode == kGather) z_gather<kL>(addr, acc, de);
-            else z_scatter<kL>(addr, em, de);
+        // every branch below is warp-uniform: all lanes walk the same (angle, column) segment.
+        // `next` yields the voxel address and the deposit E(u_in) - E(u_out) of the current voxel
+        // and steps to the neighbour across the nearer boundary (the last voxel ends at u1).
+        int n = nx + ny;
+        auto next = [&](uint32_t& a_out, float& de_out) {
+            a_out = addr;
+            float u_out = e0.y;
+            if (n > 0) {
+                if (ux <= uy) {
+                    u_out = ux;
+                    addr += sx;
+                    fx += 1.f;
+                    ux = fmaf(fx, ax, bx);
+                    if (--nx == 0) ux = INFINITY;
+                } else {
+                    u_out = uy;
+                    addr += sy;
+                    fy += 1.f;
+                    uy = fmaf(fy, ay, by);
+                    if (--ny == 0) uy = INFINITY;
+                }
+            }
+            --n;
+            const float e = ex2_approx(-u_out);
+            de_out = e_prev - e;
+            e_prev = e;
         };
-        // every branch below is warp-uniform: all lanes walk the same (angle, column) segment
-        for (int n = nx + ny; n > 0; --n) {
-            if (ux <= uy) {
-                const float e = ex2_approx(-ux);
-                deposit(e_prev - e);
-                e_prev = e;
-                addr += sx;
-                fx += 1.f;
-                ux = fmaf(fx, ax, bx);
-                if (--nx == 0) ux = INFINITY;
-            } else {
-                const float e = ex2_approx(-uy);
-                deposit(e_prev - e);
-                e_prev = e;
-                addr += sy;
-                fy += 1.f;
-                uy = fmaf(fy, ay, by);
-                if (--ny == 0) uy = INFINITY;
+        if (kMode == kGather) {
+            // plain loads: the compiler already overlaps them, keep the loop minimal
+            for (; n > 0; --n) {
+                if (ux <= uy) {
+                    const float e = ex2_approx(-ux);
+                    z_gather<kL>(addr, acc, e_prev - e);
+                    e_prev = e;
+                    addr += sx;
+                    fx += 1.f;
+                    ux = fmaf(fx, ax, bx);
+                    if (--nx == 0) ux = INFINITY;
+                } else {
+                    const float e = ex2_approx(-uy);
+                    z_gather<kL>(addr, acc, e_prev - e);
+                    e_prev = e;
+                    addr += sy;
+                    fy += 1.f;
+                    uy = fmaf(fy, ay, by);
+                    if (--ny == 0) uy = INFINITY;
+                }
+            }
+            z_gather<kL>(addr, acc, e_prev - ex2_approx(-e0.y));
+        } else {
+            int deposits = n + 1;
+            for (; deposits >= 2; deposits -= 2) {
+                uint32_t a_a, a_b;
+                float de_a, de_b;
+                next(a_a, de_a);
+                next(a_b, de_b);
+                z_scatter2<kL>(a_a, de_a, a_b, de_b, em);
+            }
+            if (deposits) {
+                uint32_t a_a;
+                float de_a;
+                next(a_a, de_a);
+                z_scatter<kL>(a_a, em, de_a);
             }
         }
-        deposit(e_prev - ex2_approx(-e0.y));
 
         if (kMode == kGather) {
 #pragma unroll
@@ -530,10 +613,9 @@ static cudaError_t z_scratch(PlanarZHost& H, size_t bytes) {
     return cudaSuccess;
 }
 
-static int z_groups(const PlanarZHost& H, int nk) {
-    long long ctas = 0;
-    for (int i = 0; i < H.n_sub; ++i)
-        ctas += static_cast<long long>(H.sub[i].plan.tiles_x) * H.sub[i].plan.tiles_y * H.sub[i].n_blocks;
+// Angle groups of one sub-plan: enough CTAs for two waves of the 148 SMs.
+static int z_groups(const PlanarZSub& S, int nk) {
+    const long long ctas = static_cast<long long>(S.plan.tiles_x) * S.plan.tiles_y * S.n_blocks;
     long long g = (148 * 2 + ctas - 1) / std::max<long long>(ctas, 1);
     g = std::min<long long>(g, std::max(1, nk / 8));
     g = std::min<long long>(g, 64);
@@ -545,10 +627,10 @@ static cudaError_t z_launch(const SceneParams& P, PlanarZHost& H, const float* i
                             const uint32_t* active_pixels, uint64_t n_active, float w, const int* gate,
                             cudaStream_t stream) {
     const int nk = static_cast<int>(n_active / (static_cast<uint64_t>(P.res_x) * P.res_y));
-    const int groups = z_groups(H, nk);
     for (int i = 0; i < H.n_sub; ++i) {
         const PlanarZSub& S = H.sub[i];
         PlanarZPlan Z = S.plan;
+        const int groups = z_groups(S, nk);
         Z.groups = groups;
         const dim3 grid(Z.tiles_x * Z.tiles_y, S.n_blocks, groups);
         if (Z.lanes_l == 1)
