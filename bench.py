@@ -35,6 +35,8 @@ def parse_args():
     ap.add_argument("--n", type=int, default=0, help="override DMD/grid edge (default: full size)")
     ap.add_argument("--jitter", action="store_true", help="regular_sampling=false (per-ray jitter, general tracer)")
     ap.add_argument("--general", action="store_true", help="force the general per-lane tracer")
+    ap.add_argument("--surface-aware", action="store_true",
+                    help="surface-aware discretization (two-channel film + target-mesh crossings; BASELINE config 4)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     return ap.parse_args()
@@ -152,13 +154,16 @@ def main():
     from drtvam_b200.synthetic import make_config
 
     workdir = os.path.join(tempfile.gettempdir(), f"drtvam_bench_{os.getuid()}_{rank}")
-    cfg = make_config(args.workload, workdir, n=args.n or None, regular_sampling=not args.jitter)
+    cfg = make_config(args.workload, workdir, n=args.n or None, regular_sampling=not args.jitter,
+                      surface_aware=args.surface_aware)
     if args.workload == "C5":
         cfg["regular_sampling"] = False
     spp = int(cfg["spp"])
     host_cores = os.cpu_count() or 1
     workload = WORKLOAD_TEXT[args.workload] + (f" [edge overridden to {args.n}]" if args.n else "")
     workload += ", regular_sampling=%s" % str(bool(cfg["regular_sampling"])).lower()
+    if args.surface_aware:
+        workload += ", surface-aware discretization (2-channel film, target mesh traced)"
 
     # ------------------------------------------------------------ reference arm (CPU)
     if args.impl == "reference":
@@ -220,7 +225,10 @@ def main():
     sensor = scene.sensor("sensor")
     desc_full = scene.describe(integ, sensor)
     n_active_total = scene.projector.active_size()
-    target = discretize(scene, sensor=sensor)
+    if sensor.film().surface_aware:
+        target = sensor.compute_volume(scene)     # sensor.py:47-110, once per run (optimize.py:131-134)
+    else:
+        target = discretize(scene, sensor=sensor)
     if world > 1:
         scene.shard(rank, world)
     n_local = scene.projector.active_size()

@@ -11,7 +11,7 @@ import os
 from . import build as _build
 
 MAX_SURFACES = 8
-ABI_VERSION = 4
+ABI_VERSION = 5
 
 
 class DrtvamSurface(C.Structure):
@@ -53,6 +53,9 @@ SYMBOLS = {
     "drtvam_scene_create": (C.c_int, [C.POINTER(DrtvamSceneDesc), C.c_int, C.POINTER(_vp)]),
     "drtvam_scene_destroy": (None, [_vp]),
     "drtvam_scene_set_depth": (C.c_int, [_vp, _i32, _i32]),
+    "drtvam_scene_set_target": (C.c_int, [_vp, _vp, _u32]),
+    "drtvam_compute_volume": (C.c_int, [_vp, _u32, _vp, _vp]),
+    "drtvam_scene_set_inv_volume": (C.c_int, [_vp, _vp]),
     "drtvam_scene_plan": (C.c_int, [_vp, _u64, _u32]),
     "drtvam_scene_force_general": (C.c_int, [_vp, _i32]),
     "drtvam_forward": (C.c_int, [_vp, _vp, _vp, _u64, _u32, _u32, _f32, _vp, _i32, _vp]),

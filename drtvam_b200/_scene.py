@@ -93,6 +93,9 @@ class SceneDesc:
     surface_aware: int = 0
     sensor_kind: int = 0
     majorant: float = 0.0
+    # [n_tri, 3, 3] world-space target mesh of a surface-aware run (uploaded with
+    # drtvam_scene_set_target, not part of the C struct), else None
+    target_triangles: object = None
 
     def film_shape(self):
         rx, ry, rz = self.res
@@ -105,7 +108,10 @@ class SceneDesc:
         return float(np.prod(vs, dtype=np.float32))
 
     def as_dict(self) -> dict:
+        tri, self.target_triangles = self.target_triangles, None
         d = asdict(self)
+        self.target_triangles = tri
+        d["target_triangles"] = tri
         d["surfaces"] = [asdict(s) for s in self.surfaces]
         return d
 

@@ -26,7 +26,8 @@ NVCC_FLAGS = [
     "-Xptxas", "-v",
 ]
 
-LIB_SOURCES = ["abi.cu", "general_kernels.cu", "planar_kernels.cu", "planarz_kernels.cu", "loss_kernels.cu"]
+LIB_SOURCES = ["abi.cu", "general_kernels.cu", "planar_kernels.cu", "planarz_kernels.cu", "loss_kernels.cu",
+               "mesh_kernels.cu"]
 MICRO_SOURCES = ["microbench.cu"]
 
 

@@ -63,6 +63,9 @@ struct DrtvamScene {
     PlanarZHost zplan;               // layer-parallel kernels on top of the planar tables
     bool planar_tried = false;       // planar_build ran for the current depth setting
     bool planar_ok = false;
+    MeshHost target;                 // target mesh (surface-aware runs only)
+    const float* inv_volume = nullptr;  // caller-owned [film_elems] 1/sub-voxel volume (volume.py:41-42), or NULL
+    Scratch dl_scaled;               // grad_in * inv_vol of the adjoint
     Scratch host_io[3];      // device staging for the *_host calls
     unsigned long long* counter_dev = nullptr;
 };
@@ -103,7 +106,7 @@ int check_call(const DrtvamScene* s, uint64_t n_active, uint32_t& spp) {
 bool planar_static_eligible(const DrtvamScene* s) {
     const SceneParams& P = s->P;
     if (P.proj_kind != DRTVAM_PROJ_COLLIMATED || P.sample_time) return false;  // jitter keeps d_z = 0
-    if (P.albedo != 0.f || P.sensor_kind != DRTVAM_SENSOR_DDA || P.surface_aware) return false;
+    if (P.albedo != 0.f || P.sensor_kind != DRTVAM_SENSOR_DDA || P.surface_aware || P.target.n_tri > 0) return false;
     if (!P.transmission_only) return false;
     if (P.max_depth < 1 || P.max_depth - 1 > P.rr_depth) return false;  // Russian roulette never fires
     if (!P.motion_analytic) {
@@ -209,6 +212,9 @@ int drtvam_scene_create(const DrtvamSceneDesc* d, int device, DrtvamScene** out)
         if (!(d->bbox_max[a] > d->bbox_min[a])) return fail(DRTVAM_E_INVALID, "empty sensor bounding box");
     }
 
+    if (static_cast<unsigned long long>(d->res[0]) * d->res[1] * d->res[2] * (d->surface_aware ? 2 : 1) >= (1ull << 31))
+        return fail(DRTVAM_E_INVALID, "film of 2^31 elements or more is not supported (32-bit voxel index)");
+
     int n_dev = 0;
     CUDA_TRY(cudaGetDeviceCount(&n_dev));
     if (device < 0 || device >= n_dev) return fail(DRTVAM_E_INVALID, "device %d not available (%d devices)", device, n_dev);
@@ -264,6 +270,8 @@ void drtvam_scene_destroy(DrtvamScene* s) {
     if (s->counter_dev) cudaFree(s->counter_dev);
     planar_release(s->planar);
     planarz_release(s->zplan);
+    mesh_release(s->target);
+    s->dl_scaled.release();
     for (auto& b : s->host_io) b.release();
     delete s;
 }
@@ -280,6 +288,33 @@ int drtvam_scene_force_general(DrtvamScene* s, int32_t on) {
     if (!s) return fail(DRTVAM_E_INVALID, "scene handle is NULL");
     if (on < 0 || on > 2) return fail(DRTVAM_E_INVALID, "force mode must be 0 (auto), 1 (general) or 2 (planar v1)");
     s->force_mode = on;
+    return DRTVAM_OK;
+}
+
+int drtvam_scene_set_target(DrtvamScene* s, const float* triangles_host, uint32_t n_triangles) {
+    if (!s) return fail(DRTVAM_E_INVALID, "scene handle is NULL");
+    if (n_triangles && !triangles_host) return fail(DRTVAM_E_INVALID, "NULL triangle buffer");
+    if (n_triangles > (1u << 28)) return fail(DRTVAM_E_INVALID, "too many triangles");
+    DeviceGuard guard(s->device);
+    CUDA_TRY(cudaDeviceSynchronize());
+    CUDA_TRY(mesh_build(triangles_host, n_triangles, s->target));
+    s->P.target = s->target.view;
+    s->planar_tried = false;
+    return DRTVAM_OK;
+}
+
+int drtvam_scene_set_inv_volume(DrtvamScene* s, const float* inv_volume) {
+    if (!s) return fail(DRTVAM_E_INVALID, "scene handle is NULL");
+    s->inv_volume = inv_volume;
+    return DRTVAM_OK;
+}
+
+int drtvam_compute_volume(DrtvamScene* s, uint32_t sample_count, float* volumes, void* stream) {
+    if (!s) return fail(DRTVAM_E_INVALID, "scene handle is NULL");
+    if (!volumes || sample_count == 0) return fail(DRTVAM_E_INVALID, "NULL buffer or zero sample count");
+    if (s->P.target.n_tri <= 0) return fail(DRTVAM_E_INVALID, "No target shape found in the scene");  // sensor.py:62-63
+    DeviceGuard guard(s->device);
+    CUDA_TRY(launch_compute_volume(s->P, sample_count, volumes, static_cast<cudaStream_t>(stream)));
     return DRTVAM_OK;
 }
 
@@ -302,6 +337,8 @@ int drtvam_forward(DrtvamScene* s, const float* active_data, const uint32_t* act
     if (n_active == 0) return DRTVAM_OK;
     const float w = ray_weight(s, n_active, spp) * out_scale;
     if (int rc = ensure_planar(s)) return rc;
+    if (s->inv_volume && !zero_first)
+        return fail(DRTVAM_E_INVALID, "an accumulating forward call cannot apply the per-voxel inverse volume");
     if (use_planar(s, n_active)) {
         // the device decides: gate = 0 -> planar kernels, gate != 0 -> general tracer
         CUDA_TRY(launch_planar_check(s->P, s->planar, active_pixels, n_active, st));
@@ -317,9 +354,11 @@ int drtvam_forward(DrtvamScene* s, const float* active_data, const uint32_t* act
             CUDA_TRY(launch_planar_frozen(s->P, s->planar, 0, active_data, dose, active_pixels, n_active, w, st));
         CUDA_TRY(launch_forward_general(s->P, active_data, active_pixels, n_active * spp, spp, seed, w, dose, st,
                                         s->planar.gate));
+        if (s->inv_volume) CUDA_TRY(launch_mul_inplace(dose, s->inv_volume, film_elems(s), st));  // volume.py:54
         return DRTVAM_OK;
     }
     CUDA_TRY(launch_forward_general(s->P, active_data, active_pixels, n_active * spp, spp, seed, w, dose, st));
+    if (s->inv_volume) CUDA_TRY(launch_mul_inplace(dose, s->inv_volume, film_elems(s), st));  // volume.py:54
     return DRTVAM_OK;
 }
 
@@ -332,6 +371,11 @@ int drtvam_adjoint(DrtvamScene* s, const float* dose_grad, const uint32_t* activ
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const float w = ray_weight(s, n_active, spp) * in_scale;
     if (int rc = ensure_planar(s)) return rc;
+    if (s->inv_volume) {  // volume.py:130: dL = grad_in * inv_vol
+        CUDA_TRY(s->dl_scaled.reserve(sizeof(float) * film_elems(s)));
+        CUDA_TRY(launch_mul(dose_grad, s->inv_volume, static_cast<float*>(s->dl_scaled.ptr), film_elems(s), st));
+        dose_grad = static_cast<const float*>(s->dl_scaled.ptr);
+    }
     if (use_planar(s, n_active)) {
         CUDA_TRY(launch_planar_check(s->P, s->planar, active_pixels, n_active, st));
         if (!s->P.regular_sampling) {

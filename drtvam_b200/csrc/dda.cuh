@@ -9,6 +9,12 @@
 
 namespace drtvam {
 
+__device__ __forceinline__ float ex2_approx_dda(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
 // Primal sink: red.global.add.f32 into the film (no return value -> REDG).
 struct ScatterSink {
     static constexpr bool kRecordOnly = false;
@@ -33,73 +39,113 @@ struct CountSink {
     __device__ __forceinline__ void visit(size_t, float) { ++n; }
 };
 
-// Amanatides-Woo walk over [0, maxt] of `ray`, clipped to the sensor box.
-// `w0` is the throughput at the segment origin times sigma_a / sigma_t.
+// Amanatides-Woo walk over [0, maxt] of `ray`, clipped to the sensor box, as a
+// resumable state: begin() clips and sets up, step() deposits one voxel.  The
+// general tracer interleaves the steps of the 32 lanes of a warp whatever
+// segment each of them is on (general_kernels.cu).
+//
+// Same walk as sensor.py:328-438, arranged for the issue slots of one thread:
+//  - optical depth u = sigma_t log2(e) t, so the deposit of a voxel is
+//    w0 (2^-u_in - 2^-u_out): one ex2.approx per visit, the previous one is carried;
+//  - boundary times are absolute, u_b = b0 + count * du (no accumulated rounding);
+//  - the flat film index is stepped by +-stride of the axis that was crossed;
+//  - an axis takes as many steps as separate the start voxel from the end voxel (sensor.py:427)
+//    and the walk ends at the segment end u_end.
+// An axis whose first boundary time is negative never steps, as sensor.py:359 has it.
+struct DdaWalk {
+    int idx, sx, sy, sz;               // film index (32 bit) and the signed strides of the three axes
+    float ux, uy, uz;                  // next boundary of every axis (inf = none left)
+    float fx, fy, fz, lx, ly, lz;      // steps taken / allowed
+    float bx, by, bz, dx, dy, dz;      // first boundary and boundary spacing
+    float u_end, e_prev, w0;
+
+    // `w0_` is the throughput at the segment origin times sigma_a / sigma_t.  False: no overlap.
+    __device__ __forceinline__ bool begin(const SceneParams& P, const Ray& ray, float maxt, float w0_,
+                                          bool inside_target) {
+        const float o[3] = {ray.ox, ray.oy, ray.oz};
+        const float d[3] = {ray.dx, ray.dy, ray.dz};
+        // slab clip (sensor.py:328-337)
+        float t_near = -INFINITY, t_far = INFINITY;
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            const float t0 = (P.bmin[a] - o[a]) / d[a];
+            const float t1 = (P.bmax[a] - o[a]) / d[a];
+            t_near = fmaxf(t_near, fminf(t0, t1));
+            t_far = fminf(t_far, fmaxf(t0, t1));
+        }
+        const float t_start = fmaxf(t_near, 0.f);
+        const float t_end = fminf(t_far, maxt);
+        if (!(isfinite(t_start) && isfinite(t_end) && t_start < t_end)) return false;
+
+        const float sig = P.sigma_t * 1.4426950408889634f;
+        const float u_start = sig * t_start;
+        u_end = sig * t_end;
+        int cur[3], stp[3];
+        float b0[3], du[3], lim[3];
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            const float vs = (P.bmax[a] - P.bmin[a]) / static_cast<float>(P.res[a]);
+            const float gs = fmaf(d[a], t_start, o[a]);
+            const float ge = fmaf(d[a], t_end, o[a]);
+            stp[a] = d[a] > 0.f ? 1 : -1;
+            // truncation toward zero then clip (sensor.py:345-346)
+            cur[a] = min(max(__float2int_rz((gs - P.bmin[a]) / vs), 0), P.res[a] - 1);
+            const int endv = min(max(__float2int_rz((ge - P.bmin[a]) / vs), 0), P.res[a] - 1);
+            float boundary = P.bmin[a] + static_cast<float>(cur[a] + stp[a]) * vs;
+            if (d[a] < 0.f) boundary += vs;
+            const bool valid = fabsf(d[a]) > 1e-8f;
+            float first = valid ? (boundary - gs) / d[a] : INFINITY;
+            if (first < 0.f) first = INFINITY;  // sensor.py:359: this axis never steps
+            const int n = (first < INFINITY) ? max(stp[a] > 0 ? endv - cur[a] : cur[a] - endv, 0) : 0;
+            lim[a] = static_cast<float>(n);
+            b0[a] = n > 0 ? fmaf(sig, first, u_start) : INFINITY;
+            du[a] = valid ? fabsf(sig * vs / d[a]) : 0.f;
+        }
+        // 32-bit film index: drtvam_scene_create rejects films of 2^31 elements or more
+        const int C = P.surface_aware ? 2 : 1;
+        sx = C * stp[0]; sy = C * stp[1] * P.res[0]; sz = C * stp[2] * P.res[0] * P.res[1];
+        idx = C * (cur[0] + cur[1] * P.res[0] + cur[2] * P.res[0] * P.res[1]) +
+              ((P.surface_aware && !inside_target) ? 1 : 0);
+        bx = b0[0]; by = b0[1]; bz = b0[2];
+        ux = bx; uy = by; uz = bz;
+        dx = du[0]; dy = du[1]; dz = du[2];
+        lx = lim[0]; ly = lim[1]; lz = lim[2];
+        fx = fy = fz = 0.f;
+        e_prev = ex2_approx_dda(-u_start);
+        w0 = w0_;
+        return true;
+    }
+
+    // Deposits the current voxel and moves to the next one.  False: that was the last voxel.
+    template <class Sink>
+    __device__ __forceinline__ bool step(Sink& sink) {
+        const float un = fminf(fminf(ux, uy), uz);
+        const bool more = un < u_end;  // false also when every axis has used up its steps (all inf)
+        const float e = ex2_approx_dda(-(more ? un : u_end));
+        sink.visit(static_cast<size_t>(static_cast<unsigned>(idx)), w0 * (e_prev - e));
+        e_prev = e;
+        // branch-free choice of the axis that was crossed (lanes of a warp cross different axes)
+        const bool px = ux == un;
+        const bool py = !px && (uy == un);
+        const bool pz = !px && !py;
+        idx += more ? (px ? sx : (py ? sy : sz)) : 0;
+        const float fxn = fx + 1.f, fyn = fy + 1.f, fzn = fz + 1.f;
+        const float uxn = fxn < lx ? fmaf(fxn, dx, bx) : INFINITY;
+        const float uyn = fyn < ly ? fmaf(fyn, dy, by) : INFINITY;
+        const float uzn = fzn < lz ? fmaf(fzn, dz, bz) : INFINITY;
+        fx = px ? fxn : fx; ux = px ? uxn : ux;
+        fy = py ? fyn : fy; uy = py ? uyn : uy;
+        fz = pz ? fzn : fz; uz = pz ? uzn : uz;
+        return more;
+    }
+};
+
 template <class Sink>
 __device__ __forceinline__ void dda_segment(const SceneParams& P, const Ray& ray, float maxt, float w0,
                                             bool inside_target, Sink& sink) {
-    const float o[3] = {ray.ox, ray.oy, ray.oz};
-    const float d[3] = {ray.dx, ray.dy, ray.dz};
-
-    // slab clip (sensor.py:328-337)
-    float t_near = -INFINITY, t_far = INFINITY;
-#pragma unroll
-    for (int a = 0; a < 3; ++a) {
-        const float t0 = (P.bmin[a] - o[a]) / d[a];
-        const float t1 = (P.bmax[a] - o[a]) / d[a];
-        t_near = fmaxf(t_near, fminf(t0, t1));
-        t_far = fminf(t_far, fmaxf(t0, t1));
-    }
-    const float t_start = fmaxf(t_near, 0.f);
-    const float t_end = fminf(t_far, maxt);
-    if (!(isfinite(t_start) && isfinite(t_end) && t_start < t_end)) return;
-
-    int cur[3], endv[3], stp[3];
-    float dtmax[3], tstep[3];
-#pragma unroll
-    for (int a = 0; a < 3; ++a) {
-        const float vs = (P.bmax[a] - P.bmin[a]) / static_cast<float>(P.res[a]);
-        const float gs = fmaf(d[a], t_start, o[a]);
-        const float ge = fmaf(d[a], t_end, o[a]);
-        stp[a] = d[a] > 0.f ? 1 : -1;
-        // truncation toward zero then clip (sensor.py:345-346)
-        cur[a] = min(max(__float2int_rz((gs - P.bmin[a]) / vs), 0), P.res[a] - 1);
-        endv[a] = min(max(__float2int_rz((ge - P.bmin[a]) / vs), 0), P.res[a] - 1);
-        float boundary = P.bmin[a] + static_cast<float>(cur[a] + stp[a]) * vs;
-        if (d[a] < 0.f) boundary += vs;
-        const bool valid = fabsf(d[a]) > 1e-8f;
-        float first = valid ? (boundary - gs) / d[a] : INFINITY;
-        if (first < 0.f) first = INFINITY;  // sensor.py:359
-        dtmax[a] = first;
-        tstep[a] = valid ? vs / d[a] * static_cast<float>(stp[a]) : INFINITY;
-    }
-
-    const float st = P.sigma_t;
-    float t = t_start;
-    float remaining = t_end - t_start;
-    const int rx = P.res[0], rxy = P.res[0] * P.res[1];
-    bool active = true;
-    while (active) {
-        const float dt = fminf(fminf(fminf(dtmax[0], dtmax[1]), dtmax[2]), remaining);
-        remaining -= dt;
-        const float w = w0 * expf(-st * t) * (1.f - expf(-st * fmaxf(dt, 0.f)));
-        const size_t flat = static_cast<size_t>(cur[0]) + static_cast<size_t>(cur[1]) * rx +
-                            static_cast<size_t>(cur[2]) * rxy;
-        const size_t idx = P.surface_aware ? (2 * flat + (inside_target ? 0 : 1)) : flat;
-        sink.visit(idx, w);
-
-        active = (endv[0] != cur[0] || endv[1] != cur[1] || endv[2] != cur[2]) && (remaining > 1e-6f);
-        bool in_grid = true;
-#pragma unroll
-        for (int a = 0; a < 3; ++a) {
-            const bool hit = dtmax[a] == dt;
-            dtmax[a] = hit ? tstep[a] : dtmax[a] - dt;
-            if (active && hit) cur[a] += stp[a];
-            in_grid = in_grid && cur[a] >= 0 && cur[a] < P.res[a];
-        }
-        active = active && in_grid;
-        t += dt;
-    }
+    DdaWalk W;
+    if (!W.begin(P, ray, maxt, w0, inside_target)) return;
+    while (W.step(sink)) {}
 }
 
 // The reference sets `dtmax[dtmax < 0] = inf` (sensor.py:359).  When fp32
@@ -156,7 +202,7 @@ __device__ __forceinline__ void ratio_segment(const SceneParams& P, const Ray& r
     const float st = P.sigma_t, mu = P.majorant;
     const float base = w0 * st / mu;
     const float ratio = 1.f - st / mu;
-    float t = 0.f, k = 0.f;
+    float t = 0.f, wk = base;  // base * ratio^k as a running product
     for (;;) {
         t += -logf(1.f - rng.next()) / mu;
         if (!(t < maxt)) break;
@@ -173,9 +219,9 @@ __device__ __forceinline__ void ratio_segment(const SceneParams& P, const Ray& r
             const size_t flat = static_cast<size_t>(v[0]) + static_cast<size_t>(v[1]) * P.res[0] +
                                 static_cast<size_t>(v[2]) * P.res[0] * P.res[1];
             const size_t idx = P.surface_aware ? (2 * flat + (inside_target ? 0 : 1)) : flat;
-            sink.visit(idx, base * powf(ratio, k));
+            sink.visit(idx, wk);
         }
-        k += 1.f;
+        wk *= ratio;
     }
 }
 

@@ -4,6 +4,8 @@
 #include <cstdint>
 #include <cuda_runtime.h>
 
+#include "mesh.cuh"
+
 namespace drtvam {
 
 constexpr int kMaxSurfaces = 8;
@@ -40,6 +42,9 @@ struct SceneParams {
     int res[3];
     int surface_aware, sensor_kind;
     float majorant;
+    // target mesh; n_tri = 0 unless the run is surface-aware (otherwise the reference moves the mesh
+    // 1e5 away, optimize.py:188-191, and no ray meets it)
+    MeshView target;
 };
 
 struct Ray {

@@ -106,6 +106,19 @@ cudaError_t launch_planarz_adjoint(const SceneParams& P, PlanarZHost& H, const i
                                    const uint32_t* active_pixels, uint64_t n_active, float ray_weight, float* grad,
                                    cudaStream_t stream);
 
+// target mesh + surface-aware sub-voxel volumes (mesh_kernels.cu)
+struct MeshHost {
+    BvhNode* nodes = nullptr;
+    float4* tri = nullptr;
+    MeshView view{};
+};
+cudaError_t mesh_build(const float* tri_host, uint32_t n_tri, MeshHost& H);
+void mesh_release(MeshHost& H);
+// sensor.py:47-110; synchronises the stream (one-off set-up work)
+cudaError_t launch_compute_volume(const SceneParams& P, uint32_t sample_count, float* volumes, cudaStream_t stream);
+cudaError_t launch_mul_inplace(float* a, const float* b, size_t n, cudaStream_t stream);
+cudaError_t launch_mul(const float* a, const float* b, float* out, size_t n, cudaStream_t stream);
+
 // fused thresholded loss + gradient on the dose volume (loss_kernels.cu)
 cudaError_t launch_thresholded_loss(const float* x, const float* x_b, float alpha, const float* target, size_t n,
                                     float tl, float tu, float w_obj, float w_void, float w_lim, int K, float grad_scale,

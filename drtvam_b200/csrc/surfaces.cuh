@@ -170,4 +170,14 @@ __device__ __forceinline__ float cross_interface(const SceneParams& P, const Sur
     return weight;
 }
 
+// Null-BSDF crossing (the target mesh): direction unchanged, origin re-spawned past the surface.
+__device__ __forceinline__ void spawn_through(const SurfaceHit& H, Ray& ray) {
+    const float m = fmaxf(fmaxf(fabsf(H.px), fabsf(H.py)), fabsf(H.pz));
+    float mag = (1.f + m) * (1500.0f * 5.9604644775390625e-8f);
+    if (H.nx * ray.dx + H.ny * ray.dy + H.nz * ray.dz < 0.f) mag = -mag;
+    ray.ox = fmaf(H.nx, mag, H.px);
+    ray.oy = fmaf(H.ny, mag, H.py);
+    ray.oz = fmaf(H.nz, mag, H.pz);
+}
+
 }  // namespace drtvam

@@ -60,7 +60,7 @@ __device__ __forceinline__ void trace_lane(const SceneParams& P, Ray ray, Sample
     const float absorb = (st - ss) / st;  // sigma_a / sigma_t
     float attenuation = 1.f;
     bool active = true, in_medium = false;
-    const bool inside_target = false;  // target mesh crossings: surface-aware meshes are a later row
+    bool inside_target = false;  // every ray starts outside the target (volume.py:173-174)
     uint32_t depth = 0;
 
     while (active) {
@@ -73,7 +73,18 @@ __device__ __forceinline__ void trace_lane(const SceneParams& P, Ray ray, Sample
         active = active && (attenuation != 0.f);
         if (!active) break;
 
-        const SurfaceHit H = nearest_surface(P, ray);
+        SurfaceHit H = nearest_surface(P, ray);
+        bool hit_target = false;  // volume.py:196
+        if (P.target.n_tri > 0) {
+            float nx, ny, nz;
+            const float t = mesh_nearest(P.target, ray.ox, ray.oy, ray.oz, ray.dx, ray.dy, ray.dz, H.t, nx, ny, nz);
+            if (t < H.t) {
+                hit_target = true;
+                H.t = t; H.shape = kMaxSurfaces;
+                H.nx = nx; H.ny = ny; H.nz = nz;
+                H.px = fmaf(ray.dx, t, ray.ox); H.py = fmaf(ray.dy, t, ray.oy); H.pz = fmaf(ray.dz, t, ray.oz);
+            }
+        }
         if (H.shape < 0) break;  // volume.py:193
 
         float weight = 1.f;
@@ -100,18 +111,26 @@ __device__ __forceinline__ void trace_lane(const SceneParams& P, Ray ray, Sample
             else dda_segment(P, ray, H.t, attenuation * absorb, inside_target, sink);
         }
 
+        inside_target = inside_target != hit_target;  // volume.py:219
+
         bool enters_medium = false;
         if (!collide) {
             // interface: BSDF sample + spawn (volume.py:228-247)
             const float s1 = rng.next();
             (void)rng.next();
             (void)rng.next();
-            const bool allow_reflection = !P.transmission_only && depth != 0;
-            weight *= cross_interface(P, H, allow_reflection, s1, ray);
+            if (hit_target) {
+                // null BSDF (optimize.py:70-72): straight through, weight 1; the ray stays in the medium
+                spawn_through(H, ray);
+                enters_medium = true;  // volume.py:268
+            } else {
+                const bool allow_reflection = !P.transmission_only && depth != 0;
+                weight *= cross_interface(P, H, allow_reflection, s1, ray);
+                const Surface& S = P.surf[H.shape];
+                const bool outward = (ray.dx * H.nx + ray.dy * H.ny + ray.dz * H.nz) > 0.f;
+                enters_medium = outward ? (S.exterior_medium != 0) : (S.interior_medium != 0);  // volume.py:268
+            }
             if (!kScatter && reached_surface) weight *= expf(-st * H.t);  // volume.py:263
-            const Surface& S = P.surf[H.shape];
-            const bool outward = (ray.dx * H.nx + ray.dy * H.ny + ray.dz * H.nz) > 0.f;
-            enters_medium = outward ? (S.exterior_medium != 0) : (S.interior_medium != 0);  // volume.py:268
         } else {
             // medium collision: albedo weight + phase sampling (volume.py:249-261)
             weight *= ss;
@@ -124,7 +143,7 @@ __device__ __forceinline__ void trace_lane(const SceneParams& P, Ray ray, Sample
         }
         attenuation *= weight;
         in_medium = collide || enters_medium;
-        depth += 1;
+        if (!hit_target) depth += 1;  // volume.py:271
         active = depth < static_cast<uint32_t>(P.max_depth);
     }
 }

@@ -15,8 +15,11 @@ def _inv_volume(sensor, scene):
     """(scalar, tensor-or-None): 1 / voxel volume, 0 where the volume is 0 (volume.py:41-42)."""
     vol = sensor.compute_volume(scene)
     if isinstance(vol, torch.Tensor):
-        inv = torch.where(vol != 0, 1.0 / vol, torch.zeros_like(vol))
-        return 1.0, inv
+        cached = getattr(sensor, '_inv_volumes', None)
+        if cached is None or cached[0] is not vol:
+            cached = (vol, torch.where(vol != 0, 1.0 / vol, torch.zeros_like(vol)).contiguous())
+            sensor._inv_volumes = cached
+        return 1.0, cached[1]
     return (1.0 / vol if vol != 0 else 0.0), None
 
 
@@ -72,19 +75,21 @@ class VolumeIntegrator(TVAMIntegrator):
             raise ValueError(f"[{projector.__class__.__name__}] active_data and active_pixels must have the same length.")
         lib = _lib.load()
         ev = self._event_pair('forward')
-        _lib.check(lib.drtvam_forward(handle, data.data_ptr(), pixels.data_ptr(), data.numel(), spp,
-                                      seed & 0xFFFFFFFF, inv_scalar, film.data.data_ptr(), 1,
-                                      torch.cuda.current_stream(film.data.device).cuda_stream))
+        # per-voxel 1 / sub-voxel volume of a surface-aware film: applied by the library (volume.py:54)
+        _lib.check(lib.drtvam_scene_set_inv_volume(handle, inv_tensor.data_ptr() if inv_tensor is not None else None))
+        try:
+            _lib.check(lib.drtvam_forward(handle, data.data_ptr(), pixels.data_ptr(), data.numel(), spp,
+                                          seed & 0xFFFFFFFF, inv_scalar, film.data.data_ptr(), 1,
+                                          torch.cuda.current_stream(film.data.device).cuda_stream))
+        finally:
+            lib.drtvam_scene_set_inv_volume(handle, None)
         if ev is not None:
             ev[1].record()
         ev = self._event_pair('allreduce') if scene.world_size > 1 else None
         scene.reduce_dose(film.data)
         if ev is not None:
             ev[1].record()
-        out = film.data
-        if inv_tensor is not None:
-            out = out * inv_tensor
-        return out
+        return film.data
 
     def render(self, scene, sensor=0, seed: int = 0, spp: int = 0, develop: bool = True, evaluate: bool = True):
         """Primal A p with p = projector.active_data; returns (resz, resy, resx, C)."""
@@ -113,16 +118,18 @@ class VolumeIntegrator(TVAMIntegrator):
         g = grad_in.detach().to(torch.float32)
         if tuple(g.shape) != tuple(film.shape):
             g = g.reshape(film.shape)
-        if inv_tensor is not None:
-            g = g * inv_tensor
         g = g.contiguous()
         pixels = projector.active_pixels
         out = torch.empty(pixels.numel(), device=g.device, dtype=torch.float32)
         lib = _lib.load()
         ev = self._event_pair('adjoint')
-        _lib.check(lib.drtvam_adjoint(handle, g.data_ptr(), pixels.data_ptr(), pixels.numel(), spp,
-                                      seed & 0xFFFFFFFF, inv_scalar, out.data_ptr(),
-                                      torch.cuda.current_stream(g.device).cuda_stream))
+        _lib.check(lib.drtvam_scene_set_inv_volume(handle, inv_tensor.data_ptr() if inv_tensor is not None else None))
+        try:
+            _lib.check(lib.drtvam_adjoint(handle, g.data_ptr(), pixels.data_ptr(), pixels.numel(), spp,
+                                          seed & 0xFFFFFFFF, inv_scalar, out.data_ptr(),
+                                          torch.cuda.current_stream(g.device).cuda_stream))
+        finally:
+            lib.drtvam_scene_set_inv_volume(handle, None)
         if ev is not None:
             ev[1].record()
         return out

@@ -47,6 +47,10 @@ class Scene:
         self.surfaces = surfaces
         self.medium = medium
         self.target = target
+        # The reference keeps the target mesh in the ray-traced scene only for surface-aware runs
+        # and otherwise moves it 1e5 away (optimize.py:188-191), so its crossings only exist then.
+        main = sensors.get('sensor') or next(iter(sensors.values()))
+        self.target_active = bool(target is not None and main.film().surface_aware)
         self.default_integrator = integrator
         self._handles = {}
         self._keepalive = {}
@@ -106,7 +110,16 @@ class Scene:
             raise NotImplementedError(f"sensor '{sensor.kind}' has no kernel")
         d.sensor_kind = SENSOR_KINDS[sensor.kind]
         d.majorant = float(getattr(sensor, 'majorant', 0.0))
+        d.target_triangles = self.target_triangles()
         return d
+
+    def target_triangles(self):
+        """[n_tri, 3, 3] float32 world-space vertices of the target while it is part of the traced
+        scene (surface-aware runs), else None."""
+        if not self.target_active:
+            return None
+        t = self.target
+        return np.ascontiguousarray(np.asarray(t['vertices'], np.float64)[np.asarray(t['triangles'])].astype(np.float32))
 
     def handle(self, integrator, sensor):
         """C handle for (integrator options, sensor); depth changes reuse it."""
@@ -123,11 +136,23 @@ class Scene:
                 raise RuntimeError("drtvam_b200 has no CPU path: scene tensors must live on a CUDA device")
             _lib.check(lib.drtvam_scene_create(C.byref(cdesc), dev.index or 0, C.byref(out)))
             h = out.value
+            if desc.target_triangles is not None:
+                tri = desc.target_triangles
+                _lib.check(lib.drtvam_scene_set_target(h, tri.ctypes.data, tri.shape[0]))
             self._handles[key] = h
             self._keepalive[key] = keep
         _lib.check(lib.drtvam_scene_set_depth(h, int(integrator.max_depth), int(integrator.rr_depth)))
         _lib.check(lib.drtvam_scene_force_general(h, int(self.force_general)))
         return h
+
+    def geometry_integrator(self):
+        """Integrator options for calls that only need the geometry (compute_volume)."""
+        if self.default_integrator is not None:
+            return self.default_integrator
+        from .integrators import VolumeIntegrator
+        if getattr(self, '_geom_integrator', None) is None:
+            self._geom_integrator = VolumeIntegrator({})
+        return self._geom_integrator
 
     def close(self):
         if self._handles:

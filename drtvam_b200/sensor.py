@@ -4,7 +4,8 @@
 
 ``accumulate`` -- the voxel walk itself -- is the CUDA hot loop
 (``csrc/dda.cuh``, ``csrc/planar_kernels.cu``); these classes carry the
-geometry.  The delta-tracking sensor (:112-191) is not built yet.
+geometry.  The delta-tracking sensor (:112-191) is not built yet.  The surface-aware
+sub-voxel volumes (:53-110) are ``drtvam_compute_volume`` (``csrc/mesh_kernels.cu``).
 """
 from __future__ import annotations
 
@@ -49,9 +50,20 @@ class VolumetricSensor:
             return float(np.prod(self.voxel_size, dtype=np.float32))
         if self.volumes is not None:
             return self.volumes
-        raise NotImplementedError(
-            "surface-aware sub-voxel volumes need the target-mesh inside test (SURVEY.md section 8(f) row 1), "
-            "which is not built yet; assign sensor.volumes explicitly")
+        if scene is None or getattr(scene, 'target', None) is None:
+            raise ValueError("No target shape found in the scene")
+        import torch
+
+        from . import _lib
+        lib = _lib.load()
+        handle = scene.handle(scene.geometry_integrator(), self)
+        dev = scene.projector.active_data.device
+        rx, ry, rz = self.resolution()
+        vol = torch.empty((rz, ry, rx, 2), device=dev, dtype=torch.float32)
+        _lib.check(lib.drtvam_compute_volume(handle, int(sample_count), vol.data_ptr(),
+                                             torch.cuda.current_stream(dev).cuda_stream))
+        self.volumes = vol
+        return self.volumes
 
     def to_string(self):
         return (f'{self.__class__.__name__}[\n'

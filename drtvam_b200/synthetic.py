@@ -101,7 +101,7 @@ MEDIUM_ABSORPTIVE = {"ior": 1.347, "phase": {"type": "rayleigh"}, "extinction": 
 
 
 def make_config(name: str, workdir: str, n=None, n_patterns=None, spp=None, regular_sampling=True,
-                n_steps=None, grid=None):
+                n_steps=None, grid=None, surface_aware=False):
     """Config dict for synthetic config `name` in {C1..C5}; `n` overrides the
     DMD / grid edge (default: the full-size value), `n_patterns` the angle count."""
     name = name.upper()
@@ -145,4 +145,10 @@ def make_config(name: str, workdir: str, n=None, n_patterns=None, spp=None, regu
                        "medium": dict(MEDIUM_ABSORPTIVE)}
     if spp is not None:
         cfg["spp"] = spp
+    if surface_aware:
+        # surface-aware discretization (film.py:22, sensor.py:53-110) needs a plain final_sensor
+        # for the final render (optimize.py:113-116)
+        import copy
+        cfg["final_sensor"] = copy.deepcopy(cfg["sensor"])
+        cfg["sensor"]["film"]["surface_aware"] = True
     return cfg

@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define DRTVAM_ABI_VERSION 4
+#define DRTVAM_ABI_VERSION 5
 #define DRTVAM_MAX_SURFACES 8
 
 #define DRTVAM_OK 0
@@ -111,6 +111,27 @@ void drtvam_scene_destroy(DrtvamScene *scene);
 /* integrator.max_depth = ... (optimize.py:288-289) and the *_ref integrator
  * (optimize.py:231-238) without rebuilding the scene. */
 int drtvam_scene_set_depth(DrtvamScene *scene, int32_t max_depth, int32_t rr_depth);
+
+/* Target mesh of a surface-aware run: the shape 'target' of optimize.py:66-73
+ * (null BSDF), n_triangles x 9 floats (three world-space vertices each) in HOST
+ * memory.  Its crossings flip the inside/outside flag that selects the film
+ * channel (volume.py:196,219; sensor.py:407-408) and do not count as bounces
+ * (volume.py:271).  Only pass it while film.surface_aware is on: otherwise the
+ * reference moves the mesh 1e5 away (optimize.py:188-191).  n_triangles = 0
+ * removes it.  Builds the BVH; synchronises the device. */
+int drtvam_scene_set_target(DrtvamScene *scene, const float *triangles_host, uint32_t n_triangles);
+
+/* VolumetricSensor.compute_volume, surface-aware branch (sensor.py:53-110):
+ * volumes[res_z][res_y][res_x][2] = (inside, outside) sub-voxel volumes by
+ * Monte Carlo with sample_count rays per voxel (reference default 2^14),
+ * per-voxel PCG32 streams seeded as sensor.py:83-84.  Synchronises. */
+int drtvam_compute_volume(DrtvamScene *scene, uint32_t sample_count, float *volumes, void *stream);
+
+/* inv_vol of volume.py:41-42,54,130 when it is a tensor (surface-aware): a
+ * caller-owned DEVICE array of film size that drtvam_forward multiplies the
+ * film by and drtvam_adjoint multiplies dose_grad by.  NULL (default) = the
+ * scalar out_scale / in_scale only. */
+int drtvam_scene_set_inv_volume(DrtvamScene *scene, const float *inv_volume);
 
 /* Which kernel family a call will use for this scene and spp:
  * 0 = general per-lane tracer, 1 = planar per-ray tile DDA,

@@ -79,7 +79,15 @@ typedef struct {
     int32_t surface_aware;   /* 2-channel film */
     int32_t sensor_kind;     /* 0 dda, 1 ratio, 2 delta */
     double majorant;
+    /* target mesh (optimize.py:66-73: shape 'target', null BSDF), world space, 9 doubles per
+     * triangle.  Only present while the run is surface-aware: otherwise optimize.py:188-191 moves it
+     * 1e5 away and no ray meets it. */
+    int32_t n_tri;
+    int32_t _pad_tri;
+    const double *tri;
 } OrcScene;
+
+#define ORC_SHAPE_TARGET 1000
 
 /* ------------------------------------------------------------------ RNG */
 /* Mitsuba independent sampler: one PCG32 per lane seeded through TEA
@@ -291,7 +299,40 @@ static real isect_box(const OrcSurface *b, Ray r, V3 *n) {
     return RINF;
 }
 
-/* scene.ray_intersect (volume.py:191): nearest hit over the vial surfaces. */
+/* Mitsuba Mesh::ray_intersect_triangle (Moeller-Trumbore): returns t or inf, and the unnormalised
+ * geometric normal e1 x e2. */
+static real isect_triangle(const double *T, Ray r, V3 *ng) {
+    V3 p0 = v3((real)T[0], (real)T[1], (real)T[2]);
+    V3 e1 = vsub(v3((real)T[3], (real)T[4], (real)T[5]), p0);
+    V3 e2 = vsub(v3((real)T[6], (real)T[7], (real)T[8]), p0);
+    V3 pvec = vcross(r.d, e2);
+    real det = vdot(e1, pvec);
+    if (det == 0) return RINF;
+    real inv_det = 1 / det;
+    V3 tvec = vsub(r.o, p0);
+    real u = vdot(tvec, pvec) * inv_det;
+    if (!(u >= 0 && u <= 1)) return RINF;
+    V3 qvec = vcross(tvec, e1);
+    real v = vdot(r.d, qvec) * inv_det;
+    if (!(v >= 0 && u + v <= 1)) return RINF;
+    real t = vdot(e2, qvec) * inv_det;
+    if (!(t >= 0)) return RINF;
+    *ng = vcross(e1, e2);
+    return t;
+}
+
+/* nearest hit on the target mesh alone (sensor.py:66-69 target_scene, and part of the full scene) */
+static real mesh_intersect(const OrcScene *s, Ray r, V3 *n) {
+    real best = RINF;
+    for (int i = 0; i < s->n_tri; ++i) {
+        V3 ng; real t = isect_triangle(s->tri + 9 * (size_t)i, r, &ng);
+        if (t < best) { best = t; *n = ng; }
+    }
+    if (best < RINF) *n = vnorm(*n);
+    return best;
+}
+
+/* scene.ray_intersect (volume.py:191): nearest hit over the vial surfaces and the target mesh. */
 static Hit scene_intersect(const OrcScene *s, Ray r) {
     Hit h; h.valid = 0; h.shape = -1; h.t = RINF; h.p = v3(0, 0, 0); h.n = v3(0, 0, 1);
     for (int i = 0; i < s->n_surf; ++i) {
@@ -299,6 +340,10 @@ static Hit scene_intersect(const OrcScene *s, Ray r) {
         V3 n = v3(0, 0, 1); real t;
         if (sf->kind == 0) t = isect_cylinder(sf, r); else t = isect_box(sf, r, &n);
         if (t < h.t) { h.t = t; h.shape = i; h.valid = 1; if (sf->kind == 1) h.n = n; }
+    }
+    if (s->n_tri > 0) {
+        V3 n = v3(0, 0, 1); real t = mesh_intersect(s, r, &n);
+        if (t < h.t) { h.t = t; h.shape = ORC_SHAPE_TARGET; h.valid = 1; h.n = n; h.p = vadd(r.o, vscale(r.d, t)); return h; }
     }
     if (h.valid) {
         h.p = vadd(r.o, vscale(r.d, h.t));
@@ -497,7 +542,7 @@ static real trace_lane(Acc *A, Ray ray, real Le, Pcg32 *rng) {
         if (active) si = scene_intersect(s, ray);
         active = active && si.valid;
         active_medium = active_medium && active;
-        int hit_target = 0; /* target mesh is not part of the closed-form scene (optimize.py:189-191) */
+        int hit_target = active && si.shape == ORC_SHAPE_TARGET; /* volume.py:196 */
 
         real weight = 1, mei_t = RINF;
         int reached_surface;
@@ -528,9 +573,9 @@ static real trace_lane(Acc *A, Ray ray, real Le, Pcg32 *rng) {
         Ray new_ray = ray;
         if (active_surface) {
             real s1 = next_1d(rng); (void)next_1d(rng); (void)next_1d(rng);
-            const OrcSurface *sf = &s->surf[si.shape];
+            const OrcSurface *sf = hit_target ? NULL : &s->surf[si.shape];
             V3 wo; real bw;
-            if (sf->bsdf == 0) { wo = ray.d; bw = 1; }
+            if (hit_target || sf->bsdf == 0) { wo = ray.d; bw = 1; } /* null BSDF: optimize.py:70-72 */
             else if (sf->bsdf == 2) { wo = ray.d; bw = 0; }
             else {
                 real cos_i = -vdot(si.n, ray.d), cos_t, eta_it, eta_ti;
@@ -585,10 +630,13 @@ static real trace_lane(Acc *A, Ray ray, real Le, Pcg32 *rng) {
         if (active) attenuation *= weight;
         ray = new_ray;
         if (active_surface) {
-            const OrcSurface *sf = &s->surf[si.shape];
-            int transition = sf->interior_medium || sf->exterior_medium;
-            int target_is_medium = vdot(ray.d, si.n) > 0 ? sf->exterior_medium : sf->interior_medium;
-            if (hit_target || (transition && target_is_medium)) active_medium = 1;
+            if (hit_target) active_medium = 1; /* volume.py:268 */
+            else {
+                const OrcSurface *sf = &s->surf[si.shape];
+                int transition = sf->interior_medium || sf->exterior_medium;
+                int target_is_medium = vdot(ray.d, si.n) > 0 ? sf->exterior_medium : sf->interior_medium;
+                if (transition && target_is_medium) active_medium = 1;
+            }
         }
         active = active && (active_surface || active_medium);
         if (active && !hit_target) depth += 1;
@@ -663,6 +711,60 @@ int orc_raygen(const OrcScene *s, const uint32_t *active_pixels, uint64_t n_acti
         Ray r = gen_ray(s, active_pixels[lane / spp], &rng);
         real *o = out + 6 * lane;
         o[0] = r.o.x; o[1] = r.o.y; o[2] = r.o.z; o[3] = r.d.x; o[4] = r.d.y; o[5] = r.d.z;
+    }
+    return 0;
+}
+
+/* sensor.py:47-110 VolumetricSensor.compute_volume, surface-aware branch: per voxel, `sample_count`
+ * random rays from random points of the voxel; a point is inside when the first hit on the target
+ * is a back face.  volumes = [rz][ry][rx][2] (in, out) in units of volume. */
+int orc_compute_volume(const OrcScene *s, uint32_t sample_count, real *volumes, int n_threads) {
+    if (s->n_tri <= 0) return -1;
+    real mbmin[3] = {RINF, RINF, RINF}, mbmax[3] = {-RINF, -RINF, -RINF};
+    for (int i = 0; i < s->n_tri * 3; ++i)
+        for (int a = 0; a < 3; ++a) {
+            real v = (real)s->tri[3 * (size_t)i + a];
+            if (v < mbmin[a]) mbmin[a] = v;
+            if (v > mbmax[a]) mbmax[a] = v;
+        }
+    real bmin[3], vs[3];
+    for (int a = 0; a < 3; ++a) {
+        bmin[a] = (real)s->bbox_min[a];
+        vs[a] = ((real)s->bbox_max[a] - (real)s->bbox_min[a]) / (real)s->res[a];
+    }
+    real voxel_vol = vs[0] * vs[1] * vs[2];
+    int64_t n_vox = (int64_t)s->res[0] * s->res[1] * s->res[2];
+#ifdef _OPENMP
+    if (n_threads > 0) omp_set_num_threads(n_threads);
+#pragma omp parallel for schedule(dynamic, 256)
+#endif
+    for (int64_t idx = 0; idx < n_vox; ++idx) {
+        int x = (int)(idx % s->res[0]), y = (int)((idx / s->res[0]) % s->res[1]), z = (int)(idx / ((int64_t)s->res[0] * s->res[1]));
+        Pcg32 rng; sampler_seed(&rng, 0u, (uint32_t)idx); /* sensor.py:83-84 */
+        uint32_t cin = 0, cout = 0;
+        for (uint32_t d = 0; d < sample_count; ++d) {
+            real o0 = next_1d(&rng), o1 = next_1d(&rng), o2 = next_1d(&rng);
+            real u0 = next_1d(&rng), u1 = next_1d(&rng);
+            Ray r;
+            r.o = v3(bmin[0] + vs[0] * ((real)x + o0), bmin[1] + vs[1] * ((real)y + o1), bmin[2] + vs[2] * ((real)z + o2));
+            /* warp::square_to_uniform_sphere */
+            real cz = 1 - 2 * u1, rr = safe_sqrt(1 - cz * cz);
+            const real pi = (real)3.14159265358979323846;
+            real phi = 2 * pi * u0;
+            real sp = sizeof(real) == 4 ? (real)sinf((float)phi) : (real)sin((double)phi);
+            real cp = sizeof(real) == 4 ? (real)cosf((float)phi) : (real)cos((double)phi);
+            r.d = v3(rr * cp, rr * sp, cz);
+            int in_bbox = r.o.x > mbmin[0] && r.o.x < mbmax[0] && r.o.y > mbmin[1] && r.o.y < mbmax[1] &&
+                          r.o.z > mbmin[2] && r.o.z < mbmax[2];
+            int inside = 0;
+            if (in_bbox) {
+                V3 n; real t = mesh_intersect(s, r, &n);
+                inside = t < RINF && vdot(r.d, n) > 0;
+            }
+            if (inside) ++cin; else ++cout;
+        }
+        volumes[2 * idx] = (real)cin * voxel_vol / (real)sample_count;
+        volumes[2 * idx + 1] = (real)cout * voxel_vol / (real)sample_count;
     }
     return 0;
 }

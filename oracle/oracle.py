@@ -37,6 +37,7 @@ class OrcScene(C.Structure):
         ("n_surf", C.c_int32), ("surf", OrcSurface * MAX_SURF),
         ("bbox_min", C.c_double * 3), ("bbox_max", C.c_double * 3), ("res", C.c_int32 * 3),
         ("surface_aware", C.c_int32), ("sensor_kind", C.c_int32), ("majorant", C.c_double),
+        ("n_tri", C.c_int32), ("_pad_tri", C.c_int32), ("tri", C.POINTER(C.c_double)),
     ]
 
 
@@ -69,6 +70,8 @@ def _lib(precision: str):
                                     C.c_void_p, C.c_int]
         lib.orc_raygen.restype = C.c_int
         lib.orc_raygen.argtypes = [C.POINTER(OrcScene), C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_void_p]
+        lib.orc_compute_volume.restype = C.c_int
+        lib.orc_compute_volume.argtypes = [C.POINTER(OrcScene), C.c_uint32, C.c_void_p, C.c_int]
         lib.orc_rng_stream.restype = C.c_int
         lib.orc_rng_stream.argtypes = [C.c_uint32, C.c_uint32, C.c_int, C.c_void_p]
         assert lib.orc_sizeof_real() == C.sizeof(real)
@@ -103,6 +106,12 @@ class Oracle:
             s.bbox_min[a] = desc["bbox_min"][a]
             s.bbox_max[a] = desc["bbox_max"][a]
             s.res[a] = int(desc["res"][a])
+        # target mesh: [n_tri][3][3] world-space vertices (only passed for surface-aware runs)
+        self._tri = None
+        if desc.get("target_triangles") is not None:
+            self._tri = np.ascontiguousarray(np.asarray(desc["target_triangles"], np.float64).reshape(-1, 9))
+            s.n_tri = self._tri.shape[0]
+            s.tri = self._tri.ctypes.data_as(C.POINTER(C.c_double))
         self.scene = s
         rx, ry, rz = (int(v) for v in desc["res"])
         self.film_shape = (rz, ry, rx, 2 if desc["surface_aware"] else 1)
@@ -129,6 +138,14 @@ class Oracle:
         rc = self.lib.orc_adjoint(C.byref(self.scene), g.ctypes.data, pix.ctypes.data, pix.size, spp, seed,
                                   out.ctypes.data, self.threads)
         assert rc == 0
+        return out
+
+    def compute_volume(self, sample_count=2 ** 14):
+        """Surface-aware sub-voxel volumes (sensor.py:47-110), shape (rz, ry, rx, 2) = (in, out)."""
+        rz, ry, rx, _ = self.film_shape
+        out = np.zeros((rz, ry, rx, 2), self.real)
+        rc = self.lib.orc_compute_volume(C.byref(self.scene), int(sample_count), out.ctypes.data, self.threads)
+        assert rc == 0, "compute_volume needs a target mesh"
         return out
 
     def raygen(self, active_pixels, spp=1, seed=0):
