@@ -32,6 +32,25 @@ struct GatherSink {
     __device__ __forceinline__ void visit(size_t idx, float w) { acc = fmaf(w, __ldg(dL + idx), acc); }
 };
 
+// Adjoint sink of the persistent tracer: the product of a visit is formed one visit later, so the
+// thread does not wait for its own gather before it computes the next voxel step.
+struct PipelinedGatherSink {
+    static constexpr bool kRecordOnly = false;
+    const float* dL;
+    float acc = 0.f, w_prev = 0.f, v_prev = 0.f;
+    __device__ __forceinline__ void visit(size_t idx, float w) {
+        acc = fmaf(w_prev, v_prev, acc);
+        v_prev = __ldg(dL + idx);
+        w_prev = w;
+    }
+    __device__ __forceinline__ float finish() {
+        acc = fmaf(w_prev, v_prev, acc);
+        const float r = acc;
+        acc = w_prev = v_prev = 0.f;
+        return r;
+    }
+};
+
 // Counting sink (roofline units).
 struct CountSink {
     static constexpr bool kRecordOnly = false;
@@ -128,7 +147,11 @@ struct DdaWalk {
         const bool px = ux == un;
         const bool py = !px && (uy == un);
         const bool pz = !px && !py;
-        idx += more ? (px ? sx : (py ? sy : sz)) : 0;
+        // (written as two selects: nvcc 12.9 drops the y stride from `px ? sx : (py ? sy : sz)`)
+        int stride = sz;
+        stride = py ? sy : stride;
+        stride = px ? sx : stride;
+        idx += more ? stride : 0;
         const float fxn = fx + 1.f, fyn = fy + 1.f, fzn = fz + 1.f;
         const float uxn = fxn < lx ? fmaf(fxn, dx, bx) : INFINITY;
         const float uyn = fyn < ly ? fmaf(fyn, dy, by) : INFINITY;

@@ -1,8 +1,26 @@
-// General per-lane tracer kernels: one thread per (active pixel, sample).
+// General per-lane tracer kernels: one lane per (active pixel, sample).
 // Handles every configuration of the path (jittered sampling, aperture
-// projectors, scattering, reflections, any vial built from cylinders/boxes).
+// projectors, scattering, reflections, any vial built from cylinders/boxes,
+// the target mesh of surface-aware runs).
+//
+// The production kernels are the nested ones (forward_general_kernel, adjoint_general_kernel).
+// general_persistent_kernel is the experimental alternative: a warp owns a chunk of
+// consecutive lanes and runs a small state machine per thread
+//     {no ray} -> ray generation -> {needs a bounce} -> bounce_once -> {walking} -> ... -> retire
+// so that the 32 threads spend their issue slots on voxel steps whatever
+// segment each of them is on.  With the naive nesting (a DDA loop inside the
+// bounce loop, forward_general_kernel below) ncu shows 7.2 of 32 threads active
+// per instruction on the scattering configuration (profiles/r01d_*): every lane
+// waits for the longest segment of every bounce and for the deepest path of
+// the warp.  Bounces are expensive and rare (one per ~450 voxel steps), so they
+// are batched: the warp only runs the bounce code when at least kSetupMin
+// lanes wait for it, nobody is walking, or the waiting lanes have sat out
+// kMaxWait bursts.
 // Reference: VolumeIntegrator.render / render_backward
 // (integrators/volume.py:18-56, 97-134).
+#include <cstdlib>
+#include <cstring>
+
 #include "kernels.h"
 #include "tracer.cuh"
 
@@ -44,9 +62,9 @@ adjoint_general_kernel(const __grid_constant__ SceneParams P, const float* __res
         Sampler rng;
         rng.seed(seed, static_cast<uint32_t>(lane));
         const Ray ray = generate_ray(P, __ldg(active_pixels + j), rng);
-        GatherSink sink{dL};
+        PipelinedGatherSink sink{dL};
         trace_lane<kScatter>(P, ray, rng, sink);
-        g = sink.acc * ray_weight;
+        g = sink.finish() * ray_weight;
     }
     // sum over the spp lanes of one pixel (the dr.repeat of common.py:82)
     if (spp == 1) {
@@ -90,6 +108,159 @@ count_general_kernel(const __grid_constant__ SceneParams P, const uint32_t* __re
     if ((threadIdx.x & 31) == 0 && n) atomicAdd(total, n);
 }
 
+constexpr int kChunk = 512;     // consecutive lanes (rays) owned by one warp
+struct PersistTuning {
+    int burst;       // voxel steps between two looks at the lane states
+    int setup_min;   // lanes that must wait for a bounce before the warp runs one ...
+    int max_wait;    // ... unless they have waited this many bursts
+};
+
+// kMode 0: in = active_data, out = film (red.global).  kMode 1: in = dL, out = pattern gradient.
+template <bool kScatter, int kMode, int kMinBlocks>
+__global__ void __launch_bounds__(kThreads, kMinBlocks)
+general_persistent_kernel(const __grid_constant__ SceneParams P, const float* __restrict__ in,
+                          const uint32_t* __restrict__ active_pixels, uint64_t n_lanes, uint32_t spp, uint32_t seed,
+                          float ray_weight, float* __restrict__ out, const int* __restrict__ gate,
+                          const PersistTuning tune) {
+    const int kBurst = tune.burst, kSetupMin = tune.setup_min, kMaxWait = tune.max_wait;
+    if (gate && *gate == 0) return;  // the planar fast path owns this call
+    constexpr unsigned kFull = 0xffffffffu;
+    const unsigned lane_id = threadIdx.x & 31;
+    const uint64_t warp_global = (static_cast<uint64_t>(blockIdx.x) * kThreads + threadIdx.x) >> 5;
+    uint64_t next = warp_global * kChunk;
+    if (next >= n_lanes) return;
+    const uint64_t chunk_end = min(next + static_cast<uint64_t>(kChunk), n_lanes);
+
+    TraceState T;
+    Sampler rng;
+    DdaWalk W;
+    bool has_ray = false, walking = false, ray_done = false;
+    uint64_t item = 0;
+    float em = 0.f;
+    PipelinedGatherSink gsink{in};
+    int waited = 0;
+
+    for (;;) {
+        const bool need = !walking && (has_ray || next < chunk_end);
+        const unsigned nm = __ballot_sync(kFull, need), km = __ballot_sync(kFull, walking);
+        if (nm == 0 && km == 0) break;
+        if (nm != 0 && (km == 0 || __popc(nm) >= kSetupMin || waited >= kMaxWait)) {
+            waited = 0;
+            // ---- hand out the next lanes of the chunk to the threads without a ray
+            for (int attempt = 0; attempt < 4; ++attempt) {
+                const bool want = need && !has_ray;
+                const unsigned wm = __ballot_sync(kFull, want);
+                if (wm == 0 || next >= chunk_end) break;
+                const uint64_t mine = next + __popc(wm & ((1u << lane_id) - 1u));
+                next += __popc(wm);
+                if (want && mine < chunk_end) {
+                    const uint64_t j = mine / spp;
+                    bool take = true;
+                    if (kMode == 0) {
+                        em = __ldg(in + j) * ray_weight;
+                        take = em != 0.f;  // a zero pixel deposits nothing
+                    }
+                    if (take) {
+                        item = mine;
+                        rng.seed(seed, static_cast<uint32_t>(mine));
+                        T = TraceState();
+                        T.ray = generate_ray(P, __ldg(active_pixels + j), rng);
+                        has_ray = true;
+                        ray_done = false;
+                    }
+                }
+            }
+            // ---- one or more bounces, until a segment has been set up or the ray is over
+            if (need && has_ray) {
+                bool alive = true, begun = false;
+                do {
+                    alive = bounce_once<kScatter>(P, T, rng, [&](const Ray& r, float maxt, float w0, bool inside) {
+                        if (P.sensor_kind == 1) {  // ratio tracking draws from the lane's stream: not deferred
+                            if (kMode == 0) {
+                                ScatterSink sink{out, em};
+                                ratio_segment(P, r, maxt, w0, inside, rng, sink);
+                            } else {
+                                ratio_segment(P, r, maxt, w0, inside, rng, gsink);
+                            }
+                        } else {
+                            begun = W.begin(P, r, maxt, w0, inside);
+                        }
+                    });
+                } while (alive && !begun);
+                walking = begun;
+                ray_done = !alive;
+            }
+        } else if (nm != 0) {
+            ++waited;
+        }
+        // ---- a burst of voxel steps
+        if (kMode == 0) {
+            ScatterSink sink{out, em};
+#pragma unroll 1
+            for (int i = 0; i < kBurst; ++i) {
+                if (walking) walking = W.step(sink);
+            }
+        } else {
+#pragma unroll 1
+            for (int i = 0; i < kBurst; ++i) {
+                if (walking) walking = W.step(gsink);
+            }
+        }
+        // ---- retire the lanes whose ray is over and whose last segment has been walked
+        if (has_ray && !walking && ray_done) {
+            if (kMode == 1) {
+                const float g = gsink.finish() * ray_weight;
+                if (spp == 1) out[item] = g;
+                else atomicAdd(out + item / spp, g);  // the dr.repeat of common.py:82; zeroed by the host
+            }
+            has_ray = false;
+            ray_done = false;
+        }
+    }
+}
+
+// The persistent kernel is opt-in (DRTVAM_GENERAL_KERNELS=persistent): on B200 it is not yet faster
+// than the nested kernels (profiles/r01_general_tracer_sweep.txt), see DESIGN.md section 5.
+inline bool use_simple_kernels() {
+    static const bool simple = [] {
+        const char* e = std::getenv("DRTVAM_GENERAL_KERNELS");
+        return !(e != nullptr && std::strcmp(e, "persistent") == 0);
+    }();
+    return simple;
+}
+
+inline int env_int(const char* name, int fallback) {
+    const char* e = std::getenv(name);
+    return e ? std::atoi(e) : fallback;
+}
+
+template <bool kScatter, int kMode>
+cudaError_t launch_persistent(const SceneParams& P, const float* in, const uint32_t* active_pixels, uint64_t n_lanes,
+                              uint32_t spp, uint32_t seed, float ray_weight, float* out, cudaStream_t stream,
+                              const int* gate) {
+    static const int blocks = env_int("DRTVAM_PERSIST_BLOCKS", 2);
+    static const PersistTuning tune{env_int("DRTVAM_PERSIST_BURST", 16), env_int("DRTVAM_PERSIST_SETUP_MIN", 8),
+                                    env_int("DRTVAM_PERSIST_MAX_WAIT", 3)};
+    const uint64_t warps = (n_lanes + kChunk - 1) / kChunk;
+    const unsigned grid = static_cast<unsigned>((warps * 32 + kThreads - 1) / kThreads);
+    if (blocks >= 4)
+        general_persistent_kernel<kScatter, kMode, 4><<<grid, kThreads, 0, stream>>>(P, in, active_pixels, n_lanes, spp,
+                                                                                    seed, ray_weight, out, gate, tune);
+    else if (blocks == 3)
+        general_persistent_kernel<kScatter, kMode, 3><<<grid, kThreads, 0, stream>>>(P, in, active_pixels, n_lanes, spp,
+                                                                                    seed, ray_weight, out, gate, tune);
+    else
+        general_persistent_kernel<kScatter, kMode, 2><<<grid, kThreads, 0, stream>>>(P, in, active_pixels, n_lanes, spp,
+                                                                                    seed, ray_weight, out, gate, tune);
+    count_launch();
+    return cudaGetLastError();
+}
+
+inline unsigned grid_persistent(uint64_t n_lanes) {
+    const uint64_t warps = (n_lanes + kChunk - 1) / kChunk;
+    return static_cast<unsigned>((warps * 32 + kThreads - 1) / kThreads);
+}
+
 inline unsigned grid_for(uint64_t n_lanes) { return static_cast<unsigned>((n_lanes + kThreads - 1) / kThreads); }
 
 }  // namespace
@@ -98,6 +269,13 @@ cudaError_t launch_forward_general(const SceneParams& P, const float* active_dat
                                    uint64_t n_lanes, uint32_t spp, uint32_t seed, float ray_weight, float* film,
                                    cudaStream_t stream, const int* gate) {
     if (n_lanes == 0) return cudaSuccess;
+    if (!use_simple_kernels()) {
+        if (P.albedo != 0.f)
+            return launch_persistent<true, 0>(P, active_data, active_pixels, n_lanes, spp, seed, ray_weight, film, stream,
+                                              gate);
+        return launch_persistent<false, 0>(P, active_data, active_pixels, n_lanes, spp, seed, ray_weight, film, stream,
+                                           gate);
+    }
     if (P.albedo != 0.f)
         forward_general_kernel<true><<<grid_for(n_lanes), kThreads, 0, stream>>>(P, active_data, active_pixels,
                                                                                   n_lanes, spp, seed, ray_weight, film, gate);
@@ -112,10 +290,18 @@ cudaError_t launch_adjoint_general(const SceneParams& P, const float* dL, const 
                                    uint64_t n_lanes, uint32_t spp, uint32_t seed, float ray_weight, float* grad,
                                    cudaStream_t stream, const int* gate) {
     if (n_lanes == 0) return cudaSuccess;
+    const bool simple = use_simple_kernels();
     const bool pow2 = (spp & (spp - 1)) == 0 && spp <= 32;
-    if (!pow2 && gate == nullptr) {  // a gated call hands in a zeroed gradient (abi.cu)
+    // lanes of one pixel are summed with atomics (always in the persistent kernel, for odd spp in the
+    // simple one); a gated call hands in a zeroed gradient (abi.cu)
+    if (((simple && !pow2) || (!simple && spp > 1)) && gate == nullptr) {
         cudaError_t e = cudaMemsetAsync(grad, 0, sizeof(float) * (n_lanes / spp), stream);
         if (e != cudaSuccess) return e;
+    }
+    if (!simple) {
+        if (P.albedo != 0.f)
+            return launch_persistent<true, 1>(P, dL, active_pixels, n_lanes, spp, seed, ray_weight, grad, stream, gate);
+        return launch_persistent<false, 1>(P, dL, active_pixels, n_lanes, spp, seed, ray_weight, grad, stream, gate);
     }
     if (P.albedo != 0.f)
         adjoint_general_kernel<true><<<grid_for(n_lanes), kThreads, 0, stream>>>(P, dL, active_pixels, n_lanes, spp,
