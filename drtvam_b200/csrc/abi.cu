@@ -61,6 +61,7 @@ struct DrtvamScene {
     std::vector<float> motion_host;  // copy of the motion table for the plan check
     PlanarHost planar;
     PlanarZHost zplan;               // layer-parallel kernels on top of the planar tables
+    PlanarGHost gplan;               // patch-gather forward on top of the layer-parallel plan
     bool planar_tried = false;       // planar_build ran for the current depth setting
     bool planar_ok = false;
     MeshHost target;                 // target mesh (surface-aware runs only)
@@ -146,11 +147,17 @@ int ensure_planar(DrtvamScene* s) {
     }
     s->planar_ok = s->planar.valid && s->planar.flags == 0 && s->planar.n_rows_in_sensor > 0;
     planarz_release(s->zplan);
+    planarg_release(s->gplan);
     if (s->planar_ok && s->P.regular_sampling) {
         e = planarz_build(s->P, s->planar, s->planar.row_layer, s->zplan);
         if (e != cudaSuccess) {
             planarz_release(s->zplan);
             return fail(DRTVAM_E_CUDA, "layer-parallel plan build failed: %s", cudaGetErrorString(e));
+        }
+        e = planarg_build(s->P, s->planar, s->zplan, s->gplan);
+        if (e != cudaSuccess) {  // e.g. out of memory: the scatter kernel serves the forward pass
+            cudaGetLastError();
+            planarg_release(s->gplan);
         }
     }
     return DRTVAM_OK;
@@ -270,6 +277,7 @@ void drtvam_scene_destroy(DrtvamScene* s) {
     if (s->counter_dev) cudaFree(s->counter_dev);
     planar_release(s->planar);
     planarz_release(s->zplan);
+    planarg_release(s->gplan);
     mesh_release(s->target);
     s->dl_scaled.release();
     for (auto& b : s->host_io) b.release();
@@ -345,6 +353,9 @@ int drtvam_forward(DrtvamScene* s, const float* active_data, const uint32_t* act
         if (!s->P.regular_sampling)
             CUDA_TRY(launch_planar_lane_forward(s->P, s->planar, active_data, active_pixels, n_active, spp, seed, w, dose,
                                                 st));
+        else if (s->zplan.valid && s->gplan.valid && s->force_mode != 2)
+            CUDA_TRY(launch_planarg_forward(s->P, s->zplan, s->gplan, s->planar.gate, active_data, active_pixels,
+                                            n_active, w, dose, st));
         else if (s->zplan.valid && s->force_mode != 2)
             CUDA_TRY(launch_planarz_forward(s->P, s->zplan, s->planar.gate, active_data, active_pixels, n_active, w, dose,
                                             st));

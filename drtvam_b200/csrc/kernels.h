@@ -96,8 +96,25 @@ struct PlanarZHost {
     float* scratch = nullptr;  // [angles][columns][active layers] repack of patterns / gradients
     size_t scratch_bytes = 0;
 };
+// patch-gather forward (planarz_kernels.cu): per (4x4 voxel patch, angle, column) a dense block of
+// 16 deposit coefficients, so that the forward pass keeps its accumulators in registers
+struct PlanarGHost {
+    bool valid = false;
+    PlanarZPlan plan{};        // 4x4 tiles; entries unused
+    int* tile_off = nullptr;
+    int* tile_clo = nullptr;
+    int* tile_ebase = nullptr;
+    float4* coef = nullptr;    // [pairs][4] float4 = 16 coefficients, voxel (yy, xx) at 4 * yy + xx
+    int* ray = nullptr;        // [pairs] k * res_x + c
+    long long pairs = 0;
+};
 cudaError_t planarz_build(const SceneParams& P, const PlanarHost& base, const std::vector<int>& row_layer,
                           PlanarZHost& H);
+cudaError_t planarg_build(const SceneParams& P, const PlanarHost& base, const PlanarZHost& Zh, PlanarGHost& G);
+void planarg_release(PlanarGHost& G);
+cudaError_t launch_planarg_forward(const SceneParams& P, PlanarZHost& H, PlanarGHost& G, const int* gate,
+                                   const float* active_data, const uint32_t* active_pixels, uint64_t n_active,
+                                   float ray_weight, float* film, cudaStream_t stream);
 void planarz_release(PlanarZHost& H);
 cudaError_t launch_planarz_forward(const SceneParams& P, PlanarZHost& H, const int* gate, const float* active_data,
                                    const uint32_t* active_pixels, uint64_t n_active, float ray_weight, float* film,

@@ -22,8 +22,10 @@
 // (film.py:40-41), VolumeIntegrator.render / render_backward
 // (integrators/volume.py:18-56, 97-134).
 #include <algorithm>
+#include <climits>
 #include <cmath>
 #include <cstdlib>
+#include <cstring>
 #include <vector>
 
 #include "kernels.h"
@@ -221,31 +223,15 @@ __device__ __forceinline__ void z_scatter2(uint32_t addr_a, float de_a, uint32_t
 // ---------------------------------------------------------------------------
 constexpr unsigned kEntryValid = 1u << 30;
 
-__global__ void __launch_bounds__(256)
-zsetup_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ PlanarZPlan Z, float4* __restrict__ entries,
-              int total) {
-    const int e = blockIdx.x * 256 + threadIdx.x;
-    if (e >= total) return;
-    const int n_tiles = Z.tiles_x * Z.tiles_y;
-    int lo = 0, hi = n_tiles;  // last tile with ebase <= e
-    while (hi - lo > 1) {
-        const int mid = (lo + hi) >> 1;
-        if (__ldg(Z.tile_ebase + mid) <= e) lo = mid; else hi = mid;
-    }
-    const int tile_id = lo, g = e - __ldg(Z.tile_ebase + tile_id);
-    const int* off = Z.tile_off + static_cast<size_t>(tile_id) * (P.n_patterns + 1);
-    lo = 0; hi = P.n_patterns;  // last angle with off <= g
-    while (hi - lo > 1) {
-        const int mid = (lo + hi) >> 1;
-        if (__ldg(off + mid) <= g) lo = mid; else hi = mid;
-    }
-    const int k = lo, c = __ldg(Z.tile_clo + static_cast<size_t>(tile_id) * P.n_patterns + k) + (g - __ldg(off + k));
-    const int x0 = (tile_id % Z.tiles_x) * Z.tile_w, y0 = (tile_id / Z.tiles_x) * Z.tile_h;
-    const int w = min(Z.tile_w, P.res[0] - x0), h = min(Z.tile_h, P.res[1] - y0);
-    float4 e0 = make_float4(0.f, 0.f, INFINITY, INFINITY), e1 = make_float4(0.f, 0.f, 0.f, __uint_as_float(0u));
+// The walk entry of one (angle k, column c) segment clipped to the tile [x0, x0+w) x [y0, y0+h).
+__device__ __forceinline__ void make_entry(const SceneParams& P, const float4* __restrict__ seg_a,
+                                           const float2* __restrict__ seg_b, int k, int c, int x0, int y0, int w, int h,
+                                           float4& e0, float4& e1) {
+    e0 = make_float4(0.f, 0.f, INFINITY, INFINITY);
+    e1 = make_float4(0.f, 0.f, 0.f, __uint_as_float(0u));
     const int s = k * P.res_x + c;
-    const float2 b = Z.seg_b[s];
-    const float4 a = Z.seg_a[s];
+    const float2 b = seg_b[s];
+    const float4 a = seg_a[s];
     float t0, t1;
     if (b.y != 0.f && clip_to_tile(P, a, b.x, x0, y0, w, h, t0, t1)) {
         const float sig = P.sigma_t * kLog2e;
@@ -280,6 +266,40 @@ zsetup_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pla
         e0 = make_float4(u0, sig * t1, ux, uy);
         e1 = make_float4(ax, ay, b.y, __uint_as_float(bits));
     }
+}
+
+// (tile, angle, column) of walk entry e of a plan (binary searches in the prefix tables)
+__device__ __forceinline__ void locate_entry(const SceneParams& P, const PlanarZPlan& Z, int e, int& tile_id, int& k,
+                                             int& c) {
+    const int n_tiles = Z.tiles_x * Z.tiles_y;
+    int lo = 0, hi = n_tiles;  // last tile with ebase <= e
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (__ldg(Z.tile_ebase + mid) <= e) lo = mid; else hi = mid;
+    }
+    tile_id = lo;
+    const int g = e - __ldg(Z.tile_ebase + tile_id);
+    const int* off = Z.tile_off + static_cast<size_t>(tile_id) * (P.n_patterns + 1);
+    lo = 0; hi = P.n_patterns;  // last angle with off <= g
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (__ldg(off + mid) <= g) lo = mid; else hi = mid;
+    }
+    k = lo;
+    c = __ldg(Z.tile_clo + static_cast<size_t>(tile_id) * P.n_patterns + k) + (g - __ldg(off + k));
+}
+
+__global__ void __launch_bounds__(256)
+zsetup_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ PlanarZPlan Z, float4* __restrict__ entries,
+              int total) {
+    const int e = blockIdx.x * 256 + threadIdx.x;
+    if (e >= total) return;
+    int tile_id, k, c;
+    locate_entry(P, Z, e, tile_id, k, c);
+    const int x0 = (tile_id % Z.tiles_x) * Z.tile_w, y0 = (tile_id / Z.tiles_x) * Z.tile_h;
+    const int w = min(Z.tile_w, P.res[0] - x0), h = min(Z.tile_h, P.res[1] - y0);
+    float4 e0, e1;
+    make_entry(P, Z.seg_a, Z.seg_b, k, c, x0, y0, w, h, e0, e1);
     entries[2 * static_cast<size_t>(e)] = e0;
     entries[2 * static_cast<size_t>(e) + 1] = e1;
 }
@@ -463,6 +483,275 @@ planarz_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
             if (z < 0) continue;
             const float v = tile[(yy * tw + xx) * kVox + (al & 31) * kL + (al >> 5)];
             if (v != 0.f) atomicAdd(out + z * layer_elems + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx), v);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
+// Patch-gather forward.  The scatter kernel above spends its time on the
+// read-modify-write of the shared tile (12 shared wavefronts and ~50 issue slots
+// per 128 visits, profiles/r01a_planarz_ncu_details.txt).  Here a warp OWNS a
+// 4x4 patch of voxels (lanes = z-layers, kL layers per lane) and keeps its
+// 16 * kL accumulators in registers for the whole pass; for every (angle,
+// column) segment that crosses the patch it reads a dense block of 16
+// precomputed deposit coefficients (warp-uniform 128-bit loads; a segment
+// visits 3 of the 16 voxels on average, the others are zero) and the kL pattern
+// values of its layers, and issues 16 * kL FMAs.  No atomics, no shared memory,
+// and the result is deterministic.  The coefficients come from the same clipped
+// walk as the scatter kernel (make_entry + the walk below).
+// ---------------------------------------------------------------------------
+constexpr int kPatch = 4;
+
+// Marches the clipped walk of entry (e0, e1) and calls visit(yy * tw + xx, de) for every voxel, with
+// de = 2^-u_in - 2^-u_out (the arithmetic of the `next` lambda of planarz_kernel).
+template <class Visit>
+__device__ __forceinline__ void walk_entry(const float4 e0, const float4 e1, int tw, Visit&& visit) {
+    const unsigned bits = __float_as_uint(e1.w);
+    if (!(bits & kEntryValid)) return;
+    const int ix = bits & 127, iy = (bits >> 7) & 127;
+    int nx = (bits >> 14) & 127, ny = (bits >> 21) & 127;
+    const int sx = (bits & (1u << 28)) ? -1 : 1, sy = (bits & (1u << 29)) ? -tw : tw;
+    float ux = e0.z, uy = e0.w;
+    const float ax = e1.x, ay = e1.y, bx = e0.z, by = e0.w;
+    float fx = 0.f, fy = 0.f;
+    int v = iy * tw + ix;
+    float e_prev = ex2_approx(-e0.x);
+    for (int n = nx + ny; n >= 0; --n) {
+        float u_out = e0.y;
+        const int v_here = v;
+        if (n > 0) {
+            if (ux <= uy) {
+                u_out = ux; v += sx; fx += 1.f;
+                ux = fmaf(fx, ax, bx);
+                if (--nx == 0) ux = INFINITY;
+            } else {
+                u_out = uy; v += sy; fy += 1.f;
+                uy = fmaf(fy, ay, by);
+                if (--ny == 0) uy = INFINITY;
+            }
+        }
+        const float e = ex2_approx(-u_out);
+        visit(v_here, e_prev - e);
+        e_prev = e;
+    }
+}
+
+// coef[g][16] and ray[g] of every (patch, angle, column) pair g
+__global__ void __launch_bounds__(256)
+gsetup_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ PlanarZPlan Z, float4* __restrict__ coef,
+              int* __restrict__ ray, int total) {
+    const int g = blockIdx.x * 256 + threadIdx.x;
+    if (g >= total) return;
+    int tile_id, k, c;
+    locate_entry(P, Z, g, tile_id, k, c);
+    const int x0 = (tile_id % Z.tiles_x) * kPatch, y0 = (tile_id / Z.tiles_x) * kPatch;
+    const int w = min(kPatch, P.res[0] - x0), h = min(kPatch, P.res[1] - y0);
+    float4 e0, e1;
+    make_entry(P, Z.seg_a, Z.seg_b, k, c, x0, y0, w, h, e0, e1);
+    float cf[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) cf[i] = 0.f;
+    const float w0 = e1.z;  // throughput at the segment origin times sigma_a / sigma_t
+    walk_entry(e0, e1, kPatch, [&](int v, float de) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+            if (i == v) cf[i] += w0 * de;
+    });
+    float4* o = coef + 4 * static_cast<size_t>(g);
+    o[0] = make_float4(cf[0], cf[1], cf[2], cf[3]);
+    o[1] = make_float4(cf[4], cf[5], cf[6], cf[7]);
+    o[2] = make_float4(cf[8], cf[9], cf[10], cf[11]);
+    o[3] = make_float4(cf[12], cf[13], cf[14], cf[15]);
+    ray[g] = k * P.res_x + c;
+}
+
+constexpr int kGWarpsX = 4, kGWarpsY = 2;  // patches per CTA: a 16 x 8 voxel region, one warp per patch
+
+// in = pT [angle][column][layer], out = film.  grid = (regions, z-blocks of this sub-plan).
+template <int kL>
+__global__ void __launch_bounds__(32 * kGWarpsX * kGWarpsY)
+planarg_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ PlanarZPlan Z,
+               const float4* __restrict__ coef, const int* __restrict__ ray, const float* __restrict__ in,
+               float* __restrict__ out, const uint32_t* __restrict__ active_pixels, uint64_t n_active, float ray_weight,
+               const int* __restrict__ gate, int a_begin) {
+    if (*gate != 0) return;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int regions_x = (Z.tiles_x + kGWarpsX - 1) / kGWarpsX;
+    const int px = (blockIdx.x % regions_x) * kGWarpsX + (warp % kGWarpsX);
+    const int py = (blockIdx.x / regions_x) * kGWarpsY + (warp / kGWarpsX);
+    if (px >= Z.tiles_x || py >= Z.tiles_y) return;
+    const int tile_id = py * Z.tiles_x + px;
+    const int a_base = a_begin + blockIdx.y * (32 * kL);
+
+    const uint32_t hw = static_cast<uint32_t>(P.res_x) * P.res_y;
+    const int k0 = __ldg(active_pixels) / hw, nk = static_cast<int>(n_active / hw);
+    const int* __restrict__ off = Z.tile_off + static_cast<size_t>(tile_id) * (P.n_patterns + 1);
+    const int ebase = __ldg(Z.tile_ebase + tile_id);
+    const int g0 = ebase + __ldg(off + k0), g1 = ebase + __ldg(off + k0 + nk);
+    // pattern values of this lane's layers for ray r: xb[r * nz_pad + 32 m]
+    const float* __restrict__ xb = in + a_base + lane - static_cast<long long>(k0) * P.res_x * Z.nz_pad;
+
+    float acc[16][kL];
+#pragma unroll
+    for (int i = 0; i < 16; ++i)
+#pragma unroll
+        for (int m = 0; m < kL; ++m) acc[i][m] = 0.f;
+
+    float xn[kL];
+    float4 cn[4];
+    auto fetch = [&](int g) {
+        const int r = __ldg(ray + g);
+        const float* x = xb + static_cast<size_t>(r) * Z.nz_pad;
+#pragma unroll
+        for (int m = 0; m < kL; ++m) xn[m] = __ldg(x + 32 * m);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) cn[q] = __ldg(coef + 4 * static_cast<size_t>(g) + q);
+    };
+    if (g0 < g1) fetch(g0);
+    for (int g = g0; g < g1; ++g) {
+        float x[kL];
+        float c[16];
+        bool any = false;
+#pragma unroll
+        for (int m = 0; m < kL; ++m) { x[m] = xn[m]; any = any || (x[m] != 0.f); }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) { c[4 * q] = cn[q].x; c[4 * q + 1] = cn[q].y; c[4 * q + 2] = cn[q].z; c[4 * q + 3] = cn[q].w; }
+        if (g + 1 < g1) fetch(g + 1);  // the loads of the next pair fly during this pair's FMAs
+        if (!__any_sync(0xffffffffu, any)) continue;  // dark in all of this block's layers
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+#pragma unroll
+            for (int m = 0; m < kL; ++m) acc[i][m] = fmaf(c[i], x[m], acc[i][m]);
+    }
+
+    // the warp is the only writer of its (patch, layers) in this launch: plain read-add-write
+    const int x0 = px * kPatch, y0 = py * kPatch;
+    const size_t layer_elems = static_cast<size_t>(P.res[0]) * P.res[1];
+#pragma unroll
+    for (int m = 0; m < kL; ++m) {
+        const int z = __ldg(Z.zl + a_base + lane + 32 * m);
+        if (z < 0) continue;
+        float* o = out + z * layer_elems;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const int xx = x0 + (i & 3), yy = y0 + (i >> 2);
+            if (xx < P.res[0] && yy < P.res[1] && acc[i][m] != 0.f)
+                o[static_cast<size_t>(yy) * P.res[0] + xx] += acc[i][m] * ray_weight;
+        }
+    }
+}
+
+// ---- the same pass for 128-layer blocks with the operand streams staged by cp.async ------------
+// ncu of planarg_kernel<4> (profiles/r01l_*): 42 % issue activity, long-scoreboard stalls, 16
+// resident warps per SM: the warp waits for its own global loads.  Here the two streams a warp
+// consumes - 64 B of coefficients per pair (contiguous in g) and the 512 B pattern line of the
+// pair's ray (lane l holds layers 4l .. 4l+3) - are copied to shared memory one chunk of kGChunk
+// pairs ahead with cp.async, so the FMA loop only ever reads shared memory.
+constexpr int kGChunk = 8;
+constexpr int kGBufFloats = kGChunk * 128 + kGChunk * 16;  // x lines + coefficient blocks of one chunk
+constexpr size_t kG4SmemBytes = sizeof(float) * 2 * kGBufFloats * kGWarpsX * kGWarpsY;
+
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(static_cast<uint32_t>(__cvta_generic_to_shared(smem))),
+                 "l"(gmem)
+                 : "memory");
+}
+
+__global__ void __launch_bounds__(32 * kGWarpsX * kGWarpsY)
+planarg4_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ PlanarZPlan Z,
+                const float4* __restrict__ coef, const int* __restrict__ ray, const float* __restrict__ in,
+                float* __restrict__ out, const uint32_t* __restrict__ active_pixels, uint64_t n_active, float ray_weight,
+                const int* __restrict__ gate, int a_begin) {
+    extern __shared__ __align__(16) float g4_smem[];
+    if (*gate != 0) return;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int regions_x = (Z.tiles_x + kGWarpsX - 1) / kGWarpsX;
+    const int px = (blockIdx.x % regions_x) * kGWarpsX + (warp % kGWarpsX);
+    const int py = (blockIdx.x / regions_x) * kGWarpsY + (warp / kGWarpsX);
+    if (px >= Z.tiles_x || py >= Z.tiles_y) return;
+    const int tile_id = py * Z.tiles_x + px;
+    const int a_base = a_begin + blockIdx.y * 128;
+    float* buf = g4_smem + warp * (2 * kGBufFloats);
+
+    const uint32_t hw = static_cast<uint32_t>(P.res_x) * P.res_y;
+    const int k0 = __ldg(active_pixels) / hw, nk = static_cast<int>(n_active / hw);
+    const int* __restrict__ off = Z.tile_off + static_cast<size_t>(tile_id) * (P.n_patterns + 1);
+    const int ebase = __ldg(Z.tile_ebase + tile_id);
+    const int g0 = ebase + __ldg(off + k0), g1 = ebase + __ldg(off + k0 + nk);
+    const float* __restrict__ xb = in + a_base + 4 * lane - static_cast<long long>(k0) * P.res_x * Z.nz_pad;
+    const int n_chunks = (g1 - g0 + kGChunk - 1) / kGChunk;
+
+    float acc[16][4];
+#pragma unroll
+    for (int i = 0; i < 16; ++i)
+#pragma unroll
+        for (int m = 0; m < 4; ++m) acc[i][m] = 0.f;
+
+    // ray index of pair (lane % kGChunk) of a chunk, loaded one chunk before it is needed
+    auto load_rays = [&](int c) {
+        const int g = g0 + c * kGChunk + (lane & (kGChunk - 1));
+        return (c < n_chunks && g < g1) ? __ldg(ray + g) : -1;
+    };
+    auto issue = [&](int c, int rl) {
+        float* b = buf + (c & 1) * kGBufFloats;
+        const int g = g0 + c * kGChunk;
+#pragma unroll
+        for (int j = 0; j < kGChunk; ++j) {
+            const int r = __shfl_sync(0xffffffffu, rl, j);
+            if (r >= 0) cp_async16(b + j * 128 + 4 * lane, xb + static_cast<size_t>(r) * Z.nz_pad);
+        }
+        // 8 pairs x 4 float4 of coefficients = one 16-byte copy per lane
+        if (g + (lane >> 2) < g1) cp_async16(b + kGChunk * 128 + 4 * lane, coef + 4 * static_cast<size_t>(g) + lane);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+
+    int rl_next = load_rays(0);
+    if (n_chunks > 0) issue(0, rl_next);
+    rl_next = load_rays(1);
+    for (int c = 0; c < n_chunks; ++c) {
+        if (c + 1 < n_chunks) {
+            issue(c + 1, rl_next);
+            rl_next = load_rays(c + 2);
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+        } else {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+        }
+        __syncwarp();
+        const float* b = buf + (c & 1) * kGBufFloats;
+        const int n_here = min(kGChunk, g1 - (g0 + c * kGChunk));
+        for (int j = 0; j < n_here; ++j) {
+            const float4 x = *reinterpret_cast<const float4*>(b + j * 128 + 4 * lane);
+            const bool any = x.x != 0.f || x.y != 0.f || x.z != 0.f || x.w != 0.f;
+            if (!__any_sync(0xffffffffu, any)) continue;  // dark in all of this block's layers
+            const float4* cj = reinterpret_cast<const float4*>(b + kGChunk * 128 + 16 * j);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const float4 cq = cj[q];  // warp-uniform address: one shared wavefront
+                const float cs[4] = {cq.x, cq.y, cq.z, cq.w};
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    acc[4 * q + t][0] = fmaf(cs[t], x.x, acc[4 * q + t][0]);
+                    acc[4 * q + t][1] = fmaf(cs[t], x.y, acc[4 * q + t][1]);
+                    acc[4 * q + t][2] = fmaf(cs[t], x.z, acc[4 * q + t][2]);
+                    acc[4 * q + t][3] = fmaf(cs[t], x.w, acc[4 * q + t][3]);
+                }
+            }
+        }
+        __syncwarp();  // the buffer is refilled by the issue of the next iteration
+    }
+
+    const int x0 = px * kPatch, y0 = py * kPatch;
+    const size_t layer_elems = static_cast<size_t>(P.res[0]) * P.res[1];
+#pragma unroll
+    for (int m = 0; m < 4; ++m) {
+        const int z = __ldg(Z.zl + a_base + 4 * lane + m);
+        if (z < 0) continue;
+        float* o = out + z * layer_elems;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const int xx = x0 + (i & 3), yy = y0 + (i >> 2);
+            if (xx < P.res[0] && yy < P.res[1] && acc[i][m] != 0.f)
+                o[static_cast<size_t>(yy) * P.res[0] + xx] += acc[i][m] * ray_weight;
         }
     }
 }
@@ -673,6 +962,106 @@ cudaError_t launch_planarz_adjoint(const SceneParams& P, PlanarZHost& H, const i
     zunpack_kernel<<<ugrid, 256, 0, stream>>>(P, H.sub[0].plan, H.scratch, grad, gate);
     count_launch();
     return cudaGetLastError();
+}
+
+void planarg_release(PlanarGHost& G) {
+    void* ptrs[] = {G.tile_off, G.tile_clo, G.tile_ebase, G.coef, G.ray};
+    for (void* p : ptrs)
+        if (p) cudaFree(p);
+    G = PlanarGHost();
+}
+
+// Builds the coefficient blocks of the patch-gather forward.  Leaves G.valid = false (no error) when
+// the tables would not fit comfortably: the scatter kernel then serves the forward pass.
+cudaError_t planarg_build(const SceneParams& P, const PlanarHost& base, const PlanarZHost& Zh, PlanarGHost& G) {
+    planarg_release(G);
+    if (const char* env = std::getenv("DRTVAM_PLANAR_FORWARD"))
+        if (std::strcmp(env, "scatter") == 0) return cudaSuccess;
+    if (!Zh.valid) return cudaSuccess;
+    const int np = P.n_patterns;
+    PlanarZPlan& Z = G.plan;
+    Z = Zh.sub[0].plan;
+    Z.seg_a = base.seg_a;
+    Z.seg_b = base.seg_b;
+    Z.tile_w = Z.tile_h = kPatch;
+    Z.tiles_x = (P.res[0] + kPatch - 1) / kPatch;
+    Z.tiles_y = (P.res[1] + kPatch - 1) / kPatch;
+    Z.entries = nullptr;
+    const int n_tiles = Z.tiles_x * Z.tiles_y;
+    if (static_cast<long long>(n_tiles) * (np + 1) >= (1ll << 29)) return cudaSuccess;
+    PZ_TRY(cudaMalloc(&G.tile_off, sizeof(int) * static_cast<size_t>(n_tiles) * (np + 1)));
+    PZ_TRY(cudaMalloc(&G.tile_clo, sizeof(int) * static_cast<size_t>(n_tiles) * np));
+    PZ_TRY(cudaMalloc(&G.tile_ebase, sizeof(int) * (n_tiles + 1)));
+    PZ_TRY(planar_tile_ranges(P, base.seg_a, base.seg_b, Z.tiles_x, Z.tiles_y, kPatch, kPatch, G.tile_off, G.tile_clo));
+    std::vector<int> last(n_tiles), ebase(n_tiles + 1, 0);
+    PZ_TRY(cudaMemcpy2D(last.data(), sizeof(int), G.tile_off + np, sizeof(int) * (np + 1), sizeof(int), n_tiles,
+                        cudaMemcpyDeviceToHost));
+    long long total = 0;
+    for (int t = 0; t < n_tiles; ++t) { ebase[t] = static_cast<int>(total); total += last[t]; }
+    ebase[n_tiles] = static_cast<int>(std::min<long long>(total, INT32_MAX));
+    size_t free_b = 0, total_b = 0;
+    PZ_TRY(cudaMemGetInfo(&free_b, &total_b));
+    const unsigned long long need = static_cast<unsigned long long>(total) * (sizeof(float4) * 4 + sizeof(int));
+    if (total <= 0 || total >= (1ll << 31) - 1 || need > free_b / 4) {  // too large: keep the scatter kernel
+        planarg_release(G);
+        return cudaSuccess;
+    }
+    PZ_TRY(cudaMemcpy(G.tile_ebase, ebase.data(), sizeof(int) * (n_tiles + 1), cudaMemcpyHostToDevice));
+    PZ_TRY(cudaMalloc(&G.coef, sizeof(float4) * 4 * static_cast<size_t>(total)));
+    PZ_TRY(cudaMalloc(&G.ray, sizeof(int) * static_cast<size_t>(total)));
+    Z.tile_off = G.tile_off; Z.tile_clo = G.tile_clo; Z.tile_ebase = G.tile_ebase;
+    gsetup_kernel<<<static_cast<unsigned>((total + 255) / 256), 256>>>(P, Z, G.coef, G.ray, static_cast<int>(total));
+    count_launch();
+    PZ_TRY(cudaGetLastError());
+    PZ_TRY(cudaDeviceSynchronize());
+    G.pairs = total;
+    G.valid = true;
+    return cudaSuccess;
+}
+
+// DRTVAM_PLANARG=registers selects the register-prefetch kernel for the 128-layer blocks (A/B tests)
+static bool g4_staged() {
+    static const bool staged = [] {
+        const char* e = std::getenv("DRTVAM_PLANARG");
+        if (e != nullptr && std::strcmp(e, "registers") == 0) return false;
+        return cudaFuncSetAttribute(planarg4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    static_cast<int>(kG4SmemBytes)) == cudaSuccess;
+    }();
+    return staged;
+}
+
+cudaError_t launch_planarg_forward(const SceneParams& P, PlanarZHost& H, PlanarGHost& G, const int* gate,
+                                   const float* active_data, const uint32_t* active_pixels, uint64_t n_active,
+                                   float ray_weight, float* film, cudaStream_t stream) {
+    const int nk = static_cast<int>(n_active / (static_cast<uint64_t>(P.res_x) * P.res_y));
+    PZ_TRY(z_scratch(H, sizeof(float) * static_cast<size_t>(nk) * P.res_x * H.nz_pad));
+    const dim3 pgrid((P.res_x + 31) / 32, H.nz_pad / 32, nk);
+    zpack_kernel<<<pgrid, 256, 0, stream>>>(P, H.sub[0].plan, active_data, H.scratch, nk, gate);
+    count_launch();
+    PZ_TRY(cudaGetLastError());
+    const PlanarZPlan& Z = G.plan;
+    const int regions = ((Z.tiles_x + kGWarpsX - 1) / kGWarpsX) * ((Z.tiles_y + kGWarpsY - 1) / kGWarpsY);
+    constexpr int threads = 32 * kGWarpsX * kGWarpsY;
+    for (int i = 0; i < H.n_sub; ++i) {
+        const PlanarZSub& S = H.sub[i];
+        const dim3 grid(regions, S.n_blocks);
+        const int kL = S.plan.lanes_l, a_begin = S.plan.a_begin;
+        if (kL == 1)
+            planarg_kernel<1><<<grid, threads, 0, stream>>>(P, Z, G.coef, G.ray, H.scratch, film, active_pixels,
+                                                            n_active, ray_weight, gate, a_begin);
+        else if (kL == 2)
+            planarg_kernel<2><<<grid, threads, 0, stream>>>(P, Z, G.coef, G.ray, H.scratch, film, active_pixels,
+                                                            n_active, ray_weight, gate, a_begin);
+        else if (g4_staged())
+            planarg4_kernel<<<grid, threads, kG4SmemBytes, stream>>>(P, Z, G.coef, G.ray, H.scratch, film, active_pixels,
+                                                                    n_active, ray_weight, gate, a_begin);
+        else
+            planarg_kernel<4><<<grid, threads, 0, stream>>>(P, Z, G.coef, G.ray, H.scratch, film, active_pixels,
+                                                            n_active, ray_weight, gate, a_begin);
+        count_launch();
+        PZ_TRY(cudaGetLastError());
+    }
+    return cudaSuccess;
 }
 
 }  // namespace drtvam
