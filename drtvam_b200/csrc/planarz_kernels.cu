@@ -562,34 +562,60 @@ gsetup_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pla
     o[1] = make_float4(cf[4], cf[5], cf[6], cf[7]);
     o[2] = make_float4(cf[8], cf[9], cf[10], cf[11]);
     o[3] = make_float4(cf[12], cf[13], cf[14], cf[15]);
-    ray[g] = k * P.res_x + c;
+    int mask = 0;
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+        if (cf[4 * q] != 0.f || cf[4 * q + 1] != 0.f || cf[4 * q + 2] != 0.f || cf[4 * q + 3] != 0.f) mask |= 1 << q;
+    ray[g] = (k * P.res_x + c) | (mask << 24);  // planarg_build guarantees n_patterns * res_x < 2^24
 }
 
 constexpr int kGWarpsX = 4, kGWarpsY = 2;  // patches per CTA: a 16 x 8 voxel region, one warp per patch
 
-// in = pT [angle][column][layer], out = film.  grid = (regions, z-blocks of this sub-plan).
+// ---- the forward pass proper --------------------------------------------------------------------
+// The two streams a warp consumes - 64 B of coefficients per pair (contiguous in g) and the
+// 128 * kL byte pattern line of the pair's ray (lane l holds layers kL*l .. kL*l + kL-1) - are copied
+// to shared memory one chunk of kGChunk pairs ahead with cp.async, so the FMA loop only reads shared
+// memory (a first version that prefetched into registers sat at 42 % issue activity on
+// long-scoreboard stalls, profiles/r01l_*).  ray[g] carries a 4-bit mask of the patch rows the
+// segment touches (2.2 of 4 on average), so the FMAs and coefficient loads of untouched rows are
+// skipped with warp-uniform branches.
+constexpr int kGChunk = 8;
+constexpr int g_buf_floats(int kL) { return kGChunk * 32 * kL + kGChunk * 16 + kGChunk; }
+constexpr size_t g_smem_bytes(int kL) { return sizeof(float) * 2 * g_buf_floats(kL) * kGWarpsX * kGWarpsY; }
+
+template <int kBytes>
+__device__ __forceinline__ void cp_async(void* smem, const void* gmem) {
+    const uint32_t d = static_cast<uint32_t>(__cvta_generic_to_shared(smem));
+    if constexpr (kBytes == 16) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gmem) : "memory");
+    else if constexpr (kBytes == 8) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(gmem) : "memory");
+    else asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(gmem) : "memory");
+}
+
 template <int kL>
 __global__ void __launch_bounds__(32 * kGWarpsX * kGWarpsY)
 planarg_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ PlanarZPlan Z,
                const float4* __restrict__ coef, const int* __restrict__ ray, const float* __restrict__ in,
                float* __restrict__ out, const uint32_t* __restrict__ active_pixels, uint64_t n_active, float ray_weight,
                const int* __restrict__ gate, int a_begin) {
+    extern __shared__ __align__(16) float g_smem[];
     if (*gate != 0) return;
+    constexpr int kBuf = g_buf_floats(kL), kLine = 32 * kL;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int regions_x = (Z.tiles_x + kGWarpsX - 1) / kGWarpsX;
     const int px = (blockIdx.x % regions_x) * kGWarpsX + (warp % kGWarpsX);
     const int py = (blockIdx.x / regions_x) * kGWarpsY + (warp / kGWarpsX);
     if (px >= Z.tiles_x || py >= Z.tiles_y) return;
     const int tile_id = py * Z.tiles_x + px;
-    const int a_base = a_begin + blockIdx.y * (32 * kL);
+    const int a_base = a_begin + blockIdx.y * kLine;
+    float* buf = g_smem + warp * (2 * kBuf);
 
     const uint32_t hw = static_cast<uint32_t>(P.res_x) * P.res_y;
     const int k0 = __ldg(active_pixels) / hw, nk = static_cast<int>(n_active / hw);
     const int* __restrict__ off = Z.tile_off + static_cast<size_t>(tile_id) * (P.n_patterns + 1);
     const int ebase = __ldg(Z.tile_ebase + tile_id);
     const int g0 = ebase + __ldg(off + k0), g1 = ebase + __ldg(off + k0 + nk);
-    // pattern values of this lane's layers for ray r: xb[r * nz_pad + 32 m]
-    const float* __restrict__ xb = in + a_base + lane - static_cast<long long>(k0) * P.res_x * Z.nz_pad;
+    const float* __restrict__ xb = in + a_base + kL * lane - static_cast<long long>(k0) * P.res_x * Z.nz_pad;
+    const int n_chunks = (g1 - g0 + kGChunk - 1) / kGChunk;
 
     float acc[16][kL];
 #pragma unroll
@@ -597,111 +623,22 @@ planarg_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
 #pragma unroll
         for (int m = 0; m < kL; ++m) acc[i][m] = 0.f;
 
-    float xn[kL];
-    float4 cn[4];
-    auto fetch = [&](int g) {
-        const int r = __ldg(ray + g);
-        const float* x = xb + static_cast<size_t>(r) * Z.nz_pad;
-#pragma unroll
-        for (int m = 0; m < kL; ++m) xn[m] = __ldg(x + 32 * m);
-#pragma unroll
-        for (int q = 0; q < 4; ++q) cn[q] = __ldg(coef + 4 * static_cast<size_t>(g) + q);
-    };
-    if (g0 < g1) fetch(g0);
-    for (int g = g0; g < g1; ++g) {
-        float x[kL];
-        float c[16];
-        bool any = false;
-#pragma unroll
-        for (int m = 0; m < kL; ++m) { x[m] = xn[m]; any = any || (x[m] != 0.f); }
-#pragma unroll
-        for (int q = 0; q < 4; ++q) { c[4 * q] = cn[q].x; c[4 * q + 1] = cn[q].y; c[4 * q + 2] = cn[q].z; c[4 * q + 3] = cn[q].w; }
-        if (g + 1 < g1) fetch(g + 1);  // the loads of the next pair fly during this pair's FMAs
-        if (!__any_sync(0xffffffffu, any)) continue;  // dark in all of this block's layers
-#pragma unroll
-        for (int i = 0; i < 16; ++i)
-#pragma unroll
-            for (int m = 0; m < kL; ++m) acc[i][m] = fmaf(c[i], x[m], acc[i][m]);
-    }
-
-    // the warp is the only writer of its (patch, layers) in this launch: plain read-add-write
-    const int x0 = px * kPatch, y0 = py * kPatch;
-    const size_t layer_elems = static_cast<size_t>(P.res[0]) * P.res[1];
-#pragma unroll
-    for (int m = 0; m < kL; ++m) {
-        const int z = __ldg(Z.zl + a_base + lane + 32 * m);
-        if (z < 0) continue;
-        float* o = out + z * layer_elems;
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-            const int xx = x0 + (i & 3), yy = y0 + (i >> 2);
-            if (xx < P.res[0] && yy < P.res[1] && acc[i][m] != 0.f)
-                o[static_cast<size_t>(yy) * P.res[0] + xx] += acc[i][m] * ray_weight;
-        }
-    }
-}
-
-// ---- the same pass for 128-layer blocks with the operand streams staged by cp.async ------------
-// ncu of planarg_kernel<4> (profiles/r01l_*): 42 % issue activity, long-scoreboard stalls, 16
-// resident warps per SM: the warp waits for its own global loads.  Here the two streams a warp
-// consumes - 64 B of coefficients per pair (contiguous in g) and the 512 B pattern line of the
-// pair's ray (lane l holds layers 4l .. 4l+3) - are copied to shared memory one chunk of kGChunk
-// pairs ahead with cp.async, so the FMA loop only ever reads shared memory.
-constexpr int kGChunk = 8;
-constexpr int kGBufFloats = kGChunk * 128 + kGChunk * 16;  // x lines + coefficient blocks of one chunk
-constexpr size_t kG4SmemBytes = sizeof(float) * 2 * kGBufFloats * kGWarpsX * kGWarpsY;
-
-__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(static_cast<uint32_t>(__cvta_generic_to_shared(smem))),
-                 "l"(gmem)
-                 : "memory");
-}
-
-__global__ void __launch_bounds__(32 * kGWarpsX * kGWarpsY)
-planarg4_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ PlanarZPlan Z,
-                const float4* __restrict__ coef, const int* __restrict__ ray, const float* __restrict__ in,
-                float* __restrict__ out, const uint32_t* __restrict__ active_pixels, uint64_t n_active, float ray_weight,
-                const int* __restrict__ gate, int a_begin) {
-    extern __shared__ __align__(16) float g4_smem[];
-    if (*gate != 0) return;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int regions_x = (Z.tiles_x + kGWarpsX - 1) / kGWarpsX;
-    const int px = (blockIdx.x % regions_x) * kGWarpsX + (warp % kGWarpsX);
-    const int py = (blockIdx.x / regions_x) * kGWarpsY + (warp / kGWarpsX);
-    if (px >= Z.tiles_x || py >= Z.tiles_y) return;
-    const int tile_id = py * Z.tiles_x + px;
-    const int a_base = a_begin + blockIdx.y * 128;
-    float* buf = g4_smem + warp * (2 * kGBufFloats);
-
-    const uint32_t hw = static_cast<uint32_t>(P.res_x) * P.res_y;
-    const int k0 = __ldg(active_pixels) / hw, nk = static_cast<int>(n_active / hw);
-    const int* __restrict__ off = Z.tile_off + static_cast<size_t>(tile_id) * (P.n_patterns + 1);
-    const int ebase = __ldg(Z.tile_ebase + tile_id);
-    const int g0 = ebase + __ldg(off + k0), g1 = ebase + __ldg(off + k0 + nk);
-    const float* __restrict__ xb = in + a_base + 4 * lane - static_cast<long long>(k0) * P.res_x * Z.nz_pad;
-    const int n_chunks = (g1 - g0 + kGChunk - 1) / kGChunk;
-
-    float acc[16][4];
-#pragma unroll
-    for (int i = 0; i < 16; ++i)
-#pragma unroll
-        for (int m = 0; m < 4; ++m) acc[i][m] = 0.f;
-
-    // ray index of pair (lane % kGChunk) of a chunk, loaded one chunk before it is needed
+    // ray word of pair (lane % kGChunk) of a chunk, loaded one chunk before it is needed
     auto load_rays = [&](int c) {
         const int g = g0 + c * kGChunk + (lane & (kGChunk - 1));
-        return (c < n_chunks && g < g1) ? __ldg(ray + g) : -1;
+        return (c < n_chunks && g < g1) ? __ldg(ray + g) : 0;  // mask 0: nothing to do
     };
     auto issue = [&](int c, int rl) {
-        float* b = buf + (c & 1) * kGBufFloats;
+        float* b = buf + (c & 1) * kBuf;
         const int g = g0 + c * kGChunk;
 #pragma unroll
         for (int j = 0; j < kGChunk; ++j) {
             const int r = __shfl_sync(0xffffffffu, rl, j);
-            if (r >= 0) cp_async16(b + j * 128 + 4 * lane, xb + static_cast<size_t>(r) * Z.nz_pad);
+            if (r >> 24) cp_async<4 * kL>(b + j * kLine + kL * lane, xb + static_cast<size_t>(r & 0xffffff) * Z.nz_pad);
         }
         // 8 pairs x 4 float4 of coefficients = one 16-byte copy per lane
-        if (g + (lane >> 2) < g1) cp_async16(b + kGChunk * 128 + 4 * lane, coef + 4 * static_cast<size_t>(g) + lane);
+        if (g + (lane >> 2) < g1) cp_async<16>(b + kGChunk * kLine + 4 * lane, coef + 4 * static_cast<size_t>(g) + lane);
+        if (lane < kGChunk) reinterpret_cast<int*>(b)[kGChunk * kLine + kGChunk * 16 + lane] = rl;
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
 
@@ -717,34 +654,37 @@ planarg4_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ P
             asm volatile("cp.async.wait_group 0;" ::: "memory");
         }
         __syncwarp();
-        const float* b = buf + (c & 1) * kGBufFloats;
+        const float* b = buf + (c & 1) * kBuf;
         const int n_here = min(kGChunk, g1 - (g0 + c * kGChunk));
         for (int j = 0; j < n_here; ++j) {
-            const float4 x = *reinterpret_cast<const float4*>(b + j * 128 + 4 * lane);
-            const bool any = x.x != 0.f || x.y != 0.f || x.z != 0.f || x.w != 0.f;
+            const int mask = reinterpret_cast<const int*>(b)[kGChunk * kLine + kGChunk * 16 + j] >> 24;
+            if (mask == 0) continue;  // the segment does not deposit in this patch
+            float x[kL];
+            bool any = false;
+#pragma unroll
+            for (int m = 0; m < kL; ++m) { x[m] = b[j * kLine + kL * lane + m]; any = any || (x[m] != 0.f); }
             if (!__any_sync(0xffffffffu, any)) continue;  // dark in all of this block's layers
-            const float4* cj = reinterpret_cast<const float4*>(b + kGChunk * 128 + 16 * j);
+            const float4* cj = reinterpret_cast<const float4*>(b + kGChunk * kLine + 16 * j);
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
-                const float4 cq = cj[q];  // warp-uniform address: one shared wavefront
+                if (!(mask & (1 << q))) continue;  // warp-uniform
+                const float4 cq = cj[q];           // warp-uniform address: one shared wavefront
                 const float cs[4] = {cq.x, cq.y, cq.z, cq.w};
 #pragma unroll
-                for (int t = 0; t < 4; ++t) {
-                    acc[4 * q + t][0] = fmaf(cs[t], x.x, acc[4 * q + t][0]);
-                    acc[4 * q + t][1] = fmaf(cs[t], x.y, acc[4 * q + t][1]);
-                    acc[4 * q + t][2] = fmaf(cs[t], x.z, acc[4 * q + t][2]);
-                    acc[4 * q + t][3] = fmaf(cs[t], x.w, acc[4 * q + t][3]);
-                }
+                for (int t = 0; t < 4; ++t)
+#pragma unroll
+                    for (int m = 0; m < kL; ++m) acc[4 * q + t][m] = fmaf(cs[t], x[m], acc[4 * q + t][m]);
             }
         }
         __syncwarp();  // the buffer is refilled by the issue of the next iteration
     }
 
+    // the warp is the only writer of its (patch, layers) in this launch: plain read-add-write
     const int x0 = px * kPatch, y0 = py * kPatch;
     const size_t layer_elems = static_cast<size_t>(P.res[0]) * P.res[1];
 #pragma unroll
-    for (int m = 0; m < 4; ++m) {
-        const int z = __ldg(Z.zl + a_base + 4 * lane + m);
+    for (int m = 0; m < kL; ++m) {
+        const int z = __ldg(Z.zl + a_base + kL * lane + m);
         if (z < 0) continue;
         float* o = out + z * layer_elems;
 #pragma unroll
@@ -964,6 +904,12 @@ cudaError_t launch_planarz_adjoint(const SceneParams& P, PlanarZHost& H, const i
     return cudaGetLastError();
 }
 
+template <int kL>
+static cudaError_t g_set_smem() {
+    return cudaFuncSetAttribute(planarg_kernel<kL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                static_cast<int>(g_smem_bytes(kL)));
+}
+
 void planarg_release(PlanarGHost& G) {
     void* ptrs[] = {G.tile_off, G.tile_clo, G.tile_ebase, G.coef, G.ray};
     for (void* p : ptrs)
@@ -989,6 +935,11 @@ cudaError_t planarg_build(const SceneParams& P, const PlanarHost& base, const Pl
     Z.entries = nullptr;
     const int n_tiles = Z.tiles_x * Z.tiles_y;
     if (static_cast<long long>(n_tiles) * (np + 1) >= (1ll << 29)) return cudaSuccess;
+    if (static_cast<long long>(np) * P.res_x >= (1ll << 24)) return cudaSuccess;  // ray index + row mask share a word
+    if (g_set_smem<1>() != cudaSuccess || g_set_smem<2>() != cudaSuccess || g_set_smem<4>() != cudaSuccess) {
+        cudaGetLastError();
+        return cudaSuccess;
+    }
     PZ_TRY(cudaMalloc(&G.tile_off, sizeof(int) * static_cast<size_t>(n_tiles) * (np + 1)));
     PZ_TRY(cudaMalloc(&G.tile_clo, sizeof(int) * static_cast<size_t>(n_tiles) * np));
     PZ_TRY(cudaMalloc(&G.tile_ebase, sizeof(int) * (n_tiles + 1)));
@@ -1019,17 +970,6 @@ cudaError_t planarg_build(const SceneParams& P, const PlanarHost& base, const Pl
     return cudaSuccess;
 }
 
-// DRTVAM_PLANARG=registers selects the register-prefetch kernel for the 128-layer blocks (A/B tests)
-static bool g4_staged() {
-    static const bool staged = [] {
-        const char* e = std::getenv("DRTVAM_PLANARG");
-        if (e != nullptr && std::strcmp(e, "registers") == 0) return false;
-        return cudaFuncSetAttribute(planarg4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    static_cast<int>(kG4SmemBytes)) == cudaSuccess;
-    }();
-    return staged;
-}
-
 cudaError_t launch_planarg_forward(const SceneParams& P, PlanarZHost& H, PlanarGHost& G, const int* gate,
                                    const float* active_data, const uint32_t* active_pixels, uint64_t n_active,
                                    float ray_weight, float* film, cudaStream_t stream) {
@@ -1047,17 +987,14 @@ cudaError_t launch_planarg_forward(const SceneParams& P, PlanarZHost& H, PlanarG
         const dim3 grid(regions, S.n_blocks);
         const int kL = S.plan.lanes_l, a_begin = S.plan.a_begin;
         if (kL == 1)
-            planarg_kernel<1><<<grid, threads, 0, stream>>>(P, Z, G.coef, G.ray, H.scratch, film, active_pixels,
-                                                            n_active, ray_weight, gate, a_begin);
+            planarg_kernel<1><<<grid, threads, g_smem_bytes(1), stream>>>(P, Z, G.coef, G.ray, H.scratch, film,
+                                                                         active_pixels, n_active, ray_weight, gate, a_begin);
         else if (kL == 2)
-            planarg_kernel<2><<<grid, threads, 0, stream>>>(P, Z, G.coef, G.ray, H.scratch, film, active_pixels,
-                                                            n_active, ray_weight, gate, a_begin);
-        else if (g4_staged())
-            planarg4_kernel<<<grid, threads, kG4SmemBytes, stream>>>(P, Z, G.coef, G.ray, H.scratch, film, active_pixels,
-                                                                    n_active, ray_weight, gate, a_begin);
+            planarg_kernel<2><<<grid, threads, g_smem_bytes(2), stream>>>(P, Z, G.coef, G.ray, H.scratch, film,
+                                                                         active_pixels, n_active, ray_weight, gate, a_begin);
         else
-            planarg_kernel<4><<<grid, threads, 0, stream>>>(P, Z, G.coef, G.ray, H.scratch, film, active_pixels,
-                                                            n_active, ray_weight, gate, a_begin);
+            planarg_kernel<4><<<grid, threads, g_smem_bytes(4), stream>>>(P, Z, G.coef, G.ray, H.scratch, film,
+                                                                         active_pixels, n_active, ray_weight, gate, a_begin);
         count_launch();
         PZ_TRY(cudaGetLastError());
     }
