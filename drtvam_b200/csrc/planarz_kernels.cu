@@ -581,14 +581,34 @@ constexpr int kGWarpsX = 4, kGWarpsY = 2;  // patches per CTA: a 16 x 8 voxel re
 // skipped with warp-uniform branches.
 constexpr int kGChunk = 8;
 constexpr int g_buf_floats(int kL) { return kGChunk * 32 * kL + kGChunk * 16 + kGChunk; }
-constexpr size_t g_smem_bytes(int kL) { return sizeof(float) * 2 * g_buf_floats(kL) * kGWarpsX * kGWarpsY; }
+constexpr size_t g_smem_bytes(int kL) {
+    return (sizeof(float) * 2 * g_buf_floats(kL) + 2 * sizeof(uint64_t)) * kGWarpsX * kGWarpsY;
+}
 
-template <int kBytes>
-__device__ __forceinline__ void cp_async(void* smem, const void* gmem) {
-    const uint32_t d = static_cast<uint32_t>(__cvta_generic_to_shared(smem));
-    if constexpr (kBytes == 16) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gmem) : "memory");
-    else if constexpr (kBytes == 8) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(gmem) : "memory");
-    else asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(gmem) : "memory");
+// TMA bulk copy (one instruction of one thread moves a whole line) completing on an mbarrier
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* smem, const void* gmem, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(smem)),
+                 "l"(gmem), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
 }
 
 template <int kL>
@@ -608,13 +628,21 @@ planarg_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
     const int tile_id = py * Z.tiles_x + px;
     const int a_base = a_begin + blockIdx.y * kLine;
     float* buf = g_smem + warp * (2 * kBuf);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(g_smem + kGWarpsX * kGWarpsY * 2 * kBuf) + 2 * warp;
+    if (lane == 0) {
+        mbar_init(bars, 1);
+        mbar_init(bars + 1, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
 
     const uint32_t hw = static_cast<uint32_t>(P.res_x) * P.res_y;
     const int k0 = __ldg(active_pixels) / hw, nk = static_cast<int>(n_active / hw);
     const int* __restrict__ off = Z.tile_off + static_cast<size_t>(tile_id) * (P.n_patterns + 1);
     const int ebase = __ldg(Z.tile_ebase + tile_id);
     const int g0 = ebase + __ldg(off + k0), g1 = ebase + __ldg(off + k0 + nk);
-    const float* __restrict__ xb = in + a_base + kL * lane - static_cast<long long>(k0) * P.res_x * Z.nz_pad;
+    // pattern line of ray r for this block's layers: xb + r * nz_pad, 128 * kL bytes
+    const float* __restrict__ xb = in + a_base - static_cast<long long>(k0) * P.res_x * Z.nz_pad;
     const int n_chunks = (g1 - g0 + kGChunk - 1) / kGChunk;
 
     float acc[16][kL];
@@ -628,18 +656,19 @@ planarg_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
         const int g = g0 + c * kGChunk + (lane & (kGChunk - 1));
         return (c < n_chunks && g < g1) ? __ldg(ray + g) : 0;  // mask 0: nothing to do
     };
+    // lane j < kGChunk copies the pattern line of pair j, lane kGChunk the coefficient blocks of the chunk
     auto issue = [&](int c, int rl) {
         float* b = buf + (c & 1) * kBuf;
+        uint64_t* bar = bars + (c & 1);
         const int g = g0 + c * kGChunk;
-#pragma unroll
-        for (int j = 0; j < kGChunk; ++j) {
-            const int r = __shfl_sync(0xffffffffu, rl, j);
-            if (r >> 24) cp_async<4 * kL>(b + j * kLine + kL * lane, xb + static_cast<size_t>(r & 0xffffff) * Z.nz_pad);
-        }
-        // 8 pairs x 4 float4 of coefficients = one 16-byte copy per lane
-        if (g + (lane >> 2) < g1) cp_async<16>(b + kGChunk * kLine + 4 * lane, coef + 4 * static_cast<size_t>(g) + lane);
+        const int n_here = min(kGChunk, g1 - g);
+        const bool wants = lane < kGChunk && (rl >> 24) != 0;
+        const unsigned lines = __popc(__ballot_sync(0xffffffffu, wants));
+        if (lane == 0) mbar_expect_tx(bar, lines * (4u * kLine) + 64u * n_here);
+        __syncwarp();
+        if (wants) bulk_g2s(b + lane * kLine, xb + static_cast<size_t>(rl & 0xffffff) * Z.nz_pad, 4u * kLine, bar);
+        if (lane == kGChunk) bulk_g2s(b + kGChunk * kLine, coef + 4 * static_cast<size_t>(g), 64u * n_here, bar);
         if (lane < kGChunk) reinterpret_cast<int*>(b)[kGChunk * kLine + kGChunk * 16 + lane] = rl;
-        asm volatile("cp.async.commit_group;" ::: "memory");
     };
 
     int rl_next = load_rays(0);
@@ -649,10 +678,8 @@ planarg_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
         if (c + 1 < n_chunks) {
             issue(c + 1, rl_next);
             rl_next = load_rays(c + 2);
-            asm volatile("cp.async.wait_group 1;" ::: "memory");
-        } else {
-            asm volatile("cp.async.wait_group 0;" ::: "memory");
         }
+        mbar_wait(bars + (c & 1), (c >> 1) & 1);
         __syncwarp();
         const float* b = buf + (c & 1) * kBuf;
         const int n_here = min(kGChunk, g1 - (g0 + c * kGChunk));
