@@ -612,7 +612,7 @@ __device__ __forceinline__ void bulk_g2s(void* smem, const void* gmem, uint32_t 
 }
 
 template <int kL>
-__global__ void __launch_bounds__(32 * kGWarpsX * kGWarpsY)
+__global__ void __launch_bounds__(32 * kGWarpsX * kGWarpsY, 3)
 planarg_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ PlanarZPlan Z,
                const float4* __restrict__ coef, const int* __restrict__ ray, const float* __restrict__ in,
                float* __restrict__ out, const uint32_t* __restrict__ active_pixels, uint64_t n_active, float ray_weight,
