@@ -323,9 +323,17 @@ def main():
     peak, how = measured_peaks()
     achieved = 4.0 * visits / (fwd_ms * 1e-3) * 1e-9
     hbm_alg_bytes = 4.0 * n_local * 2 + 4.0 * int(np.prod(desc_full.film_shape()))
+    # DRAM bytes of the forward pass from ncu --set full (profiles/r01t_planarg_tma_ncu_details.txt and the
+    # launch list r01p/r01r: planarg_kernel<4> 6.42 GB read + 0.24 GB written, tail + pack kernels 1.9 GB);
+    # only quoted for the workload and kernel family it was captured on
+    plan_now = int(lib.drtvam_scene_plan(h, n_local, spp))
+    traffic = 8.6e9 if (args.workload == "C2" and not args.n and plan_now == 2 and world == 1) else None
     roofline = {
-        "bound": "hbm", "kernel": "forward dose scatter (A p)", "achieved": achieved, "peak": peak, "unit": "GB/s",
-        "frac": achieved / peak, "traffic": None, "peak_source": how,
+        "bound": "hbm", "kernel": "forward projection (A p): zpack + planarg_kernel patch gather"
+        if plan_now == 2 else "forward projection (A p)", "achieved": achieved, "peak": peak, "unit": "GB/s",
+        "frac": achieved / peak, "traffic": traffic, "peak_source": how,
+        "note": "achieved = 4 B per voxel visit (SURVEY 8(d)) / pass time; the visits are accumulated in registers / "
+                "shared memory, so the figure can exceed the HBM copy peak; traffic = measured DRAM bytes per pass",
         "algorithmic_bytes_per_visit": 4, "visits_per_launch": visits, "kernel_ms": fwd_ms,
         "adjoint_ms": adj_ms, "adjoint_achieved": 4.0 * visits / (adj_ms * 1e-3) * 1e-9 if adj_ms else None,
         "allreduce_ms": ar_ms,
