@@ -17,7 +17,7 @@ tail -c 1500 $O/${TAG}_bench_ref.json
 if [ $rc -eq 0 ]; then
   timeout 900 ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
     --log-file $O/${TAG}_launches.csv python bench.py --workload $WL --steps 2 --warmup 3 --no-cpu-baseline > $O/${TAG}_ncu1.log 2>&1
-  timeout 1200 ncu --profile-from-start off --set full --clock-control none --import-source on -k regex:planarz_kernel -c 8 \
-    -o $O/${TAG}_planarz python bench.py --workload $WL --steps 1 --warmup 3 --no-cpu-baseline > $O/${TAG}_ncu2.log 2>&1
+  timeout 1200 ncu --profile-from-start off --set full --clock-control none --import-source on -k regex:planar[gz]_kernel -c 6 \
+    -o $O/${TAG}_planar python bench.py --workload $WL --steps 1 --warmup 3 --no-cpu-baseline > $O/${TAG}_ncu2.log 2>&1
   ls -la $O
 fi
