@@ -4,6 +4,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <vector>
@@ -55,6 +56,8 @@ using namespace drtvam;
 struct DrtvamScene {
     int device = 0;
     SceneParams P{};
+    SceneParams P1{};                // one-channel view of P (no target, plain film) for the planar kernels
+    InsideHost inside;               // inside-target segment records of a surface-aware planar scene
     float print_time = 1.f;
     float* motion_dev = nullptr;
     int force_mode = 0;              // 0 auto, 1 general tracer, 2 planar v1 (per-ray tile DDA)
@@ -107,7 +110,9 @@ int check_call(const DrtvamScene* s, uint64_t n_active, uint32_t& spp) {
 bool planar_static_eligible(const DrtvamScene* s) {
     const SceneParams& P = s->P;
     if (P.proj_kind != DRTVAM_PROJ_COLLIMATED || P.sample_time) return false;  // jitter keeps d_z = 0
-    if (P.albedo != 0.f || P.sensor_kind != DRTVAM_SENSOR_DDA || P.surface_aware || P.target.n_tri > 0) return false;
+    if (P.albedo != 0.f || P.sensor_kind != DRTVAM_SENSOR_DDA) return false;
+    // surface-aware film: the planar kernels make the channel sum, the inside records split it (inside_kernels.cu)
+    if (P.surface_aware && !P.regular_sampling) return false;
     if (!P.transmission_only) return false;
     if (P.max_depth < 1 || P.max_depth - 1 > P.rr_depth) return false;  // Russian roulette never fires
     if (!P.motion_analytic) {
@@ -139,8 +144,13 @@ int ensure_planar(DrtvamScene* s) {
     if (s->planar_tried) return DRTVAM_OK;
     s->planar_tried = true;
     s->planar_ok = false;
+    inside_release(s->inside);
+    s->P1 = s->P;
+    s->P1.surface_aware = 0;
+    s->P1.target = MeshView{};
     if (!planar_static_eligible(s)) return DRTVAM_OK;
-    cudaError_t e = planar_build(s->P, s->planar);
+    if (s->P.surface_aware && getenv("DRTVAM_SURFACE_AWARE_GENERAL")) return DRTVAM_OK;  // A/B tests
+    cudaError_t e = planar_build(s->P1, s->planar);
     if (e != cudaSuccess) {
         planar_release(s->planar);
         return fail(DRTVAM_E_CUDA, "planar plan build failed: %s", cudaGetErrorString(e));
@@ -149,17 +159,28 @@ int ensure_planar(DrtvamScene* s) {
     planarz_release(s->zplan);
     planarg_release(s->gplan);
     if (s->planar_ok && s->P.regular_sampling) {
-        e = planarz_build(s->P, s->planar, s->planar.row_layer, s->zplan);
+        e = planarz_build(s->P1, s->planar, s->planar.row_layer, s->zplan);
         if (e != cudaSuccess) {
             planarz_release(s->zplan);
             return fail(DRTVAM_E_CUDA, "layer-parallel plan build failed: %s", cudaGetErrorString(e));
         }
-        e = planarg_build(s->P, s->planar, s->zplan, s->gplan);
+        e = planarg_build(s->P1, s->planar, s->zplan, s->gplan);
         if (e != cudaSuccess) {  // e.g. out of memory: the scatter kernel serves the forward pass
             cudaGetLastError();
             planarg_release(s->gplan);
         }
     }
+    if (s->planar_ok && s->P.surface_aware) {
+        e = inside_build(s->P, s->P1, s->inside);
+        if (e != cudaSuccess) {  // the general tracer serves the scene
+            cudaGetLastError();
+            s->planar_ok = false;
+        }
+    }
+    if (getenv("DRTVAM_DEBUG"))
+        fprintf(stderr, "[drtvam] planar_ok %d zplan %d gplan %d (pairs %lld) frozen %d inside records %llu\n",
+                int(s->planar_ok), int(s->zplan.valid), int(s->gplan.valid), s->gplan.pairs, s->planar.n_frozen,
+                static_cast<unsigned long long>(s->inside.n_rec));
     return DRTVAM_OK;
 }
 
@@ -278,6 +299,7 @@ void drtvam_scene_destroy(DrtvamScene* s) {
     planar_release(s->planar);
     planarz_release(s->zplan);
     planarg_release(s->gplan);
+    inside_release(s->inside);
     mesh_release(s->target);
     s->dl_scaled.release();
     for (auto& b : s->host_io) b.release();
@@ -349,20 +371,27 @@ int drtvam_forward(DrtvamScene* s, const float* active_data, const uint32_t* act
         return fail(DRTVAM_E_INVALID, "an accumulating forward call cannot apply the per-voxel inverse volume");
     if (use_planar(s, n_active)) {
         // the device decides: gate = 0 -> planar kernels, gate != 0 -> general tracer
-        CUDA_TRY(launch_planar_check(s->P, s->planar, active_pixels, n_active, st));
-        if (!s->P.regular_sampling)
-            CUDA_TRY(launch_planar_lane_forward(s->P, s->planar, active_data, active_pixels, n_active, spp, seed, w, dose,
+        const bool sa = s->inside.valid;  // surface-aware: the planar kernels fill a one-channel plane
+        const SceneParams& P1 = s->P1;
+        float* plane = sa ? s->inside.planes : dose;
+        if (sa) CUDA_TRY(inside_forward_begin(s->inside, st));
+        CUDA_TRY(launch_planar_check(P1, s->planar, active_pixels, n_active, st));
+        if (!P1.regular_sampling)
+            CUDA_TRY(launch_planar_lane_forward(P1, s->planar, active_data, active_pixels, n_active, spp, seed, w, plane,
                                                 st));
         else if (s->zplan.valid && s->gplan.valid && s->force_mode != 2)
-            CUDA_TRY(launch_planarg_forward(s->P, s->zplan, s->gplan, s->planar.gate, active_data, active_pixels,
-                                            n_active, w, dose, st));
+            CUDA_TRY(launch_planarg_forward(P1, s->zplan, s->gplan, s->planar.gate, active_data, active_pixels,
+                                            n_active, w, plane, st));
         else if (s->zplan.valid && s->force_mode != 2)
-            CUDA_TRY(launch_planarz_forward(s->P, s->zplan, s->planar.gate, active_data, active_pixels, n_active, w, dose,
+            CUDA_TRY(launch_planarz_forward(P1, s->zplan, s->planar.gate, active_data, active_pixels, n_active, w, plane,
                                             st));
         else
-            CUDA_TRY(launch_planar_forward(s->P, s->planar, active_data, active_pixels, n_active, w, dose, st));
-        if (s->P.regular_sampling)
-            CUDA_TRY(launch_planar_frozen(s->P, s->planar, 0, active_data, dose, active_pixels, n_active, w, st));
+            CUDA_TRY(launch_planar_forward(P1, s->planar, active_data, active_pixels, n_active, w, plane, st));
+        if (P1.regular_sampling)
+            CUDA_TRY(launch_planar_frozen(P1, s->planar, 0, active_data, plane, active_pixels, n_active, w, st));
+        if (sa)
+            CUDA_TRY(inside_forward_finish(P1, s->inside, s->planar.gate, active_data, active_pixels, n_active, w, dose,
+                                           st));
         CUDA_TRY(launch_forward_general(s->P, active_data, active_pixels, n_active * spp, spp, seed, w, dose, st,
                                         s->planar.gate));
         if (s->inv_volume) CUDA_TRY(launch_mul_inplace(dose, s->inv_volume, film_elems(s), st));  // volume.py:54
@@ -388,20 +417,29 @@ int drtvam_adjoint(DrtvamScene* s, const float* dose_grad, const uint32_t* activ
         dose_grad = static_cast<const float*>(s->dl_scaled.ptr);
     }
     if (use_planar(s, n_active)) {
-        CUDA_TRY(launch_planar_check(s->P, s->planar, active_pixels, n_active, st));
-        if (!s->P.regular_sampling) {
+        const bool sa = s->inside.valid;
+        const SceneParams& P1 = s->P1;
+        const float* dl1 = dose_grad;  // one-channel gradient plane the planar kernels gather from
+        if (sa) {
+            CUDA_TRY(inside_adjoint_begin(s->inside, dose_grad, st));
+            dl1 = s->inside.planes;
+        }
+        CUDA_TRY(launch_planar_check(P1, s->planar, active_pixels, n_active, st));
+        if (!P1.regular_sampling) {
             CUDA_TRY(cudaMemsetAsync(pattern_grad, 0, sizeof(float) * n_active, st));
-            CUDA_TRY(launch_planar_lane_adjoint(s->P, s->planar, dose_grad, active_pixels, n_active, spp, seed, w,
+            CUDA_TRY(launch_planar_lane_adjoint(P1, s->planar, dl1, active_pixels, n_active, spp, seed, w,
                                                 pattern_grad, st));
         } else if (s->zplan.valid && s->force_mode != 2) {
-            CUDA_TRY(launch_planarz_adjoint(s->P, s->zplan, s->planar.gate, dose_grad, active_pixels, n_active, w,
+            CUDA_TRY(launch_planarz_adjoint(P1, s->zplan, s->planar.gate, dl1, active_pixels, n_active, w,
                                             pattern_grad, st));
         } else {
             CUDA_TRY(cudaMemsetAsync(pattern_grad, 0, sizeof(float) * n_active, st));
-            CUDA_TRY(launch_planar_adjoint(s->P, s->planar, dose_grad, active_pixels, n_active, w, pattern_grad, st));
+            CUDA_TRY(launch_planar_adjoint(P1, s->planar, dl1, active_pixels, n_active, w, pattern_grad, st));
         }
-        if (s->P.regular_sampling)
-            CUDA_TRY(launch_planar_frozen(s->P, s->planar, 1, dose_grad, pattern_grad, active_pixels, n_active, w, st));
+        if (P1.regular_sampling)
+            CUDA_TRY(launch_planar_frozen(P1, s->planar, 1, dl1, pattern_grad, active_pixels, n_active, w, st));
+        if (sa)
+            CUDA_TRY(inside_adjoint_finish(P1, s->inside, s->planar.gate, active_pixels, n_active, w, pattern_grad, st));
         CUDA_TRY(launch_adjoint_general(s->P, dose_grad, active_pixels, n_active * spp, spp, seed, w, pattern_grad, st,
                                         s->planar.gate));
         return DRTVAM_OK;

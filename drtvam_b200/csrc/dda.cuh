@@ -79,8 +79,12 @@ struct DdaWalk {
     float u_end, e_prev, w0;
 
     // `w0_` is the throughput at the segment origin times sigma_a / sigma_t.  False: no overlap.
+    // kSub: the walk covers [t_lo, maxt] of the segment only - the tail of a walk that something else
+    // has made in full (inside_kernels.cu) - so a start that rounding puts a hair past a voxel
+    // boundary must not freeze the axis (sensor.py:359 applies to the start of a segment).
+    template <bool kSub = false>
     __device__ __forceinline__ bool begin(const SceneParams& P, const Ray& ray, float maxt, float w0_,
-                                          bool inside_target) {
+                                          bool inside_target, float t_lo = 0.f) {
         const float o[3] = {ray.ox, ray.oy, ray.oz};
         const float d[3] = {ray.dx, ray.dy, ray.dz};
         // slab clip (sensor.py:328-337)
@@ -92,7 +96,7 @@ struct DdaWalk {
             t_near = fmaxf(t_near, fminf(t0, t1));
             t_far = fminf(t_far, fmaxf(t0, t1));
         }
-        const float t_start = fmaxf(t_near, 0.f);
+        const float t_start = fmaxf(t_near, kSub ? t_lo : 0.f);
         const float t_end = fminf(t_far, maxt);
         if (!(isfinite(t_start) && isfinite(t_end) && t_start < t_end)) return false;
 
@@ -114,7 +118,7 @@ struct DdaWalk {
             if (d[a] < 0.f) boundary += vs;
             const bool valid = fabsf(d[a]) > 1e-8f;
             float first = valid ? (boundary - gs) / d[a] : INFINITY;
-            if (first < 0.f) first = INFINITY;  // sensor.py:359: this axis never steps
+            if (first < 0.f) first = kSub ? 0.f : INFINITY;  // sensor.py:359: this axis never steps
             const int n = (first < INFINITY) ? max(stp[a] > 0 ? endv - cur[a] : cur[a] - endv, 0) : 0;
             lim[a] = static_cast<float>(n);
             b0[a] = n > 0 ? fmaf(sig, first, u_start) : INFINITY;

@@ -136,6 +136,26 @@ cudaError_t launch_compute_volume(const SceneParams& P, uint32_t sample_count, f
 cudaError_t launch_mul_inplace(float* a, const float* b, size_t n, cudaStream_t stream);
 cudaError_t launch_mul(const float* a, const float* b, float* out, size_t n, cudaStream_t stream);
 
+// inside-target segment records: the surface-aware film on top of the planar kernels (inside_kernels.cu)
+struct InsideHost {
+    bool valid = false;
+    uint32_t* pixel = nullptr;  // [n_rec] global pixel id of the lane
+    float4* seg = nullptr;      // [n_rec][2] {origin, length}, {direction, throughput at the origin}
+    float* t_lo = nullptr;      // [n_rec] > 0: walk the record from here on only (the negative record)
+    uint64_t n_rec = 0;
+    float* planes = nullptr;    // [2][n_vox] plane A (outside channel), plane B (inside channel)
+    size_t n_vox = 0;
+};
+cudaError_t inside_build(const SceneParams& P, const SceneParams& P1, InsideHost& H);
+void inside_release(InsideHost& H);
+cudaError_t inside_forward_begin(InsideHost& H, cudaStream_t stream);
+cudaError_t inside_forward_finish(const SceneParams& P1, InsideHost& H, const int* gate, const float* active_data,
+                                  const uint32_t* active_pixels, uint64_t n_active, float ray_weight, float* film,
+                                  cudaStream_t stream);
+cudaError_t inside_adjoint_begin(InsideHost& H, const float* dL, cudaStream_t stream);
+cudaError_t inside_adjoint_finish(const SceneParams& P1, InsideHost& H, const int* gate, const uint32_t* active_pixels,
+                                  uint64_t n_active, float ray_weight, float* grad, cudaStream_t stream);
+
 // fused thresholded loss + gradient on the dose volume (loss_kernels.cu)
 cudaError_t launch_thresholded_loss(const float* x, const float* x_b, float alpha, const float* target, size_t n,
                                     float tl, float tu, float w_obj, float w_void, float w_lim, int K, float grad_scale,

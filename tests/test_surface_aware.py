@@ -90,12 +90,30 @@ def test_surface_aware_forward_adjoint_match_oracle(name, workdir):
     p, g = random_inputs(d, pix.size, 5)
     o = orc.Oracle(d.as_dict(), "f64")
     h = _handle(d)
-    assert h.lib.drtvam_scene_plan(h.h, pix.size, 1) == 0      # two-channel film: general tracer
+    # planar kernels for the channel sum + the cached inside-target segments (inside_kernels.cu)
+    assert h.lib.drtvam_scene_plan(h.h, pix.size, 1) == 2
     f_gpu, f_cpu = h.forward(p, pix), o.forward(p, pix)
     assert f_gpu.shape == f_cpu.shape and f_gpu.shape[-1] == 2
     assert rel_l2(f_gpu, f_cpu) < 1e-4
     assert rel_l2(f_gpu[..., 0], f_cpu[..., 0]) < 2e-4
-    assert rel_l2(h.adjoint(g, pix), o.adjoint(g, pix)) < 1e-4
+    assert rel_l2(f_gpu[..., 1], f_cpu[..., 1]) < 2e-4
+    a_gpu = h.adjoint(g, pix)
+    assert rel_l2(a_gpu, o.adjoint(g, pix)) < 1e-4
+    # the same scene through the general tracer (BVH walk in every pass)
+    from drtvam_b200 import _lib
+    _lib.check(h.lib.drtvam_scene_force_general(h.h, 1))
+    assert h.lib.drtvam_scene_plan(h.h, pix.size, 1) == 0
+    assert rel_l2(h.forward(p, pix), f_gpu) < 1e-4
+    assert rel_l2(h.adjoint(g, pix), a_gpu) < 1e-4
+    _lib.check(h.lib.drtvam_scene_force_general(h.h, 0))
+    # an angle shard (whole patterns from angle 3 on) and a ragged list (general tracer through the gate)
+    hw = d.res_x * d.res_y
+    sl = slice(3 * hw, 11 * hw)
+    assert rel_l2(h.forward(p[sl], pix[sl]), o.forward(p[sl], pix[sl])) < 1e-4
+    assert rel_l2(h.adjoint(g, pix[sl]), a_gpu[sl]) < 1e-4
+    rag = np.arange(5, pix.size, 3)
+    assert rel_l2(h.forward(p[rag], pix[rag]), o.forward(p[rag], pix[rag])) < 1e-4
+    assert rel_l2(h.adjoint(g, pix[rag]), a_gpu[rag]) < 1e-4
 
 
 @pytest.mark.gpu
