@@ -178,8 +178,8 @@ int ensure_planar(DrtvamScene* s) {
         }
     }
     if (getenv("DRTVAM_DEBUG"))
-        fprintf(stderr, "[drtvam] planar_ok %d zplan %d gplan %d (pairs %lld) frozen %d inside records %llu\n",
-                int(s->planar_ok), int(s->zplan.valid), int(s->gplan.valid), s->gplan.pairs, s->planar.n_frozen,
+        fprintf(stderr, "[drtvam] planar_ok %d zplan %d gplan %d (pairs %lld of %lld) frozen %d inside records %llu\n",
+                int(s->planar_ok), int(s->zplan.valid), int(s->gplan.valid), s->gplan.pairs, s->gplan.candidates, s->planar.n_frozen,
                 static_cast<unsigned long long>(s->inside.n_rec));
     return DRTVAM_OK;
 }

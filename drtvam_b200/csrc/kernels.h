@@ -106,7 +106,8 @@ struct PlanarGHost {
     int* tile_ebase = nullptr;
     float4* coef = nullptr;    // [pairs][4] float4 = 16 coefficients, voxel (yy, xx) at 4 * yy + xx
     int* ray = nullptr;        // [pairs] k * res_x + c
-    long long pairs = 0;
+    long long pairs = 0;       // after the pairs that touch nothing are dropped
+    long long candidates = 0;  // before
 };
 cudaError_t planarz_build(const SceneParams& P, const PlanarHost& base, const std::vector<int>& row_layer,
                           PlanarZHost& H);

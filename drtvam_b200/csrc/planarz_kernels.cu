@@ -28,6 +28,8 @@
 #include <cstring>
 #include <vector>
 
+#include <cub/device/device_scan.cuh>
+
 #include "kernels.h"
 #include "planar.cuh"
 
@@ -569,6 +571,46 @@ gsetup_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pla
     ray[g] = (k * P.res_x + c) | (mask << 24);  // planarg_build guarantees n_patterns * res_x < 2^24
 }
 
+// ---- dropping the pairs that touch nothing -------------------------------------------------------
+// planar_tile_ranges gives ONE column range per (patch, angle).  Behind a refracting box (C4) two
+// faces are lit at most angles and the two ray families cross inside the resin, so the range spans
+// everything between them: 7 of 8 candidate pairs miss the patch.  The tables are compacted to the
+// pairs with a non-empty row mask; the kernel only ever sees a contiguous range of pairs per
+// (patch, angle range), so nothing else changes.
+__global__ void __launch_bounds__(256) gkeep_kernel(const int* __restrict__ ray, int total, int* __restrict__ keep) {
+    const int g = blockIdx.x * 256 + threadIdx.x;
+    if (g <= total) keep[g] = (g < total && (__ldg(ray + g) >> 24) != 0) ? 1 : 0;
+}
+
+__global__ void __launch_bounds__(256)
+gcompact_kernel(const float4* __restrict__ coef_in, const int* __restrict__ ray_in, const int* __restrict__ pos,
+                int total, float4* __restrict__ coef_out, int* __restrict__ ray_out) {
+    const int g = blockIdx.x * 256 + threadIdx.x;
+    if (g >= total) return;
+    const int r = __ldg(ray_in + g);
+    if ((r >> 24) == 0) return;
+    const int q = __ldg(pos + g);
+    ray_out[q] = r;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) coef_out[4 * static_cast<size_t>(q) + i] = __ldg(coef_in + 4 * static_cast<size_t>(g) + i);
+}
+
+// off[t][a] (prefix inside the tile) and ebase[t] follow the kept pairs; one thread per (tile, angle slot)
+__global__ void __launch_bounds__(256)
+gremap_kernel(int n_tiles, int np, const int* __restrict__ ebase_old, const int* __restrict__ off_old,
+              const int* __restrict__ pos, int* __restrict__ ebase_new, int* __restrict__ off_new) {
+    const long long i = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x;
+    if (i >= static_cast<long long>(n_tiles) * (np + 1)) return;
+    const int t = static_cast<int>(i / (np + 1));
+    const int e = __ldg(ebase_old + t);
+    const int p0 = __ldg(pos + e);
+    off_new[i] = __ldg(pos + e + __ldg(off_old + i)) - p0;
+    if (i % (np + 1) == 0) {
+        ebase_new[t] = p0;
+        if (t == n_tiles - 1) ebase_new[n_tiles] = __ldg(pos + __ldg(ebase_old + n_tiles));
+    }
+}
+
 constexpr int kGWarpsX = 4, kGWarpsY = 2;  // patches per CTA: a 16 x 8 voxel region, one warp per patch
 
 // ---- the forward pass proper --------------------------------------------------------------------
@@ -991,6 +1033,53 @@ cudaError_t planarg_build(const SceneParams& P, const PlanarHost& base, const Pl
     gsetup_kernel<<<static_cast<unsigned>((total + 255) / 256), 256>>>(P, Z, G.coef, G.ray, static_cast<int>(total));
     count_launch();
     PZ_TRY(cudaGetLastError());
+    // compaction (see gkeep_kernel)
+    {
+        int *keep = nullptr, *pos = nullptr, *ebase_new = nullptr, *off_new = nullptr, *ray_new = nullptr;
+        float4* coef_new = nullptr;
+        void* tmp = nullptr;
+        auto run = [&]() -> cudaError_t {
+            const int n1 = static_cast<int>(total) + 1;
+            PZ_TRY(cudaMalloc(&keep, sizeof(int) * n1));
+            PZ_TRY(cudaMalloc(&pos, sizeof(int) * n1));
+            gkeep_kernel<<<(n1 + 255) / 256, 256>>>(G.ray, static_cast<int>(total), keep);
+            count_launch();
+            size_t tmp_bytes = 0;
+            PZ_TRY(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, keep, pos, n1));
+            PZ_TRY(cudaMalloc(&tmp, tmp_bytes));
+            PZ_TRY(cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, keep, pos, n1));
+            count_launch();
+            int kept = 0;
+            PZ_TRY(cudaMemcpy(&kept, pos + total, sizeof(int), cudaMemcpyDeviceToHost));
+            if (kept <= 0 || kept > total - total / 16) return cudaSuccess;  // nothing worth dropping
+            PZ_TRY(cudaMalloc(&coef_new, sizeof(float4) * 4 * static_cast<size_t>(kept)));
+            PZ_TRY(cudaMalloc(&ray_new, sizeof(int) * static_cast<size_t>(kept)));
+            PZ_TRY(cudaMalloc(&ebase_new, sizeof(int) * (n_tiles + 1)));
+            PZ_TRY(cudaMalloc(&off_new, sizeof(int) * static_cast<size_t>(n_tiles) * (np + 1)));
+            gcompact_kernel<<<static_cast<unsigned>((total + 255) / 256), 256>>>(G.coef, G.ray, pos,
+                                                                                 static_cast<int>(total), coef_new, ray_new);
+            count_launch();
+            const long long slots = static_cast<long long>(n_tiles) * (np + 1);
+            gremap_kernel<<<static_cast<unsigned>((slots + 255) / 256), 256>>>(n_tiles, np, G.tile_ebase, G.tile_off, pos,
+                                                                               ebase_new, off_new);
+            count_launch();
+            PZ_TRY(cudaGetLastError());
+            PZ_TRY(cudaDeviceSynchronize());
+            std::swap(G.coef, coef_new);
+            std::swap(G.ray, ray_new);
+            std::swap(G.tile_ebase, ebase_new);
+            std::swap(G.tile_off, off_new);
+            Z.tile_off = G.tile_off; Z.tile_ebase = G.tile_ebase;
+            G.candidates = total;
+            total = kept;
+            return cudaSuccess;
+        };
+        const cudaError_t ce = run();
+        void* ptrs[] = {keep, pos, ebase_new, off_new, ray_new, coef_new, tmp};
+        for (void* q : ptrs)
+            if (q) cudaFree(q);
+        if (ce != cudaSuccess) return ce;
+    }
     PZ_TRY(cudaDeviceSynchronize());
     G.pairs = total;
     G.valid = true;
