@@ -11,10 +11,10 @@
 //
 //   set-up   trace every lane once with the general tracer (tracer.cuh, BVH walk of mesh.cuh), with
 //            and without the mesh.  A lane that crosses the mesh at t1 keeps records
-//            {pixel, origin, direction, length, throughput at the origin, start}:
+//            {origin, direction, length, throughput at the origin, start}:
 //              - the UNSPLIT segment with negative throughput, walked from t1 on only, and
 //              - each sub-segment after the first crossing, tagged inside / outside,
-//            ordered by lane (count -> exclusive scan -> fill);
+//            stored lane after lane behind an offset table (count -> exclusive scan -> fill);
 //   forward  plane A = planar kernels (unsplit rays)  +  DDA over the negative and the outside records
 //            plane B = DDA over the inside records            (red.global.add into the planes)
 //            film[v][0] += B[v],  film[v][1] += A[v]
@@ -50,8 +50,8 @@ constexpr int kThreads = 256;
 template <bool kFill>
 __global__ void __launch_bounds__(kThreads)
 inside_trace_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ SceneParams P1, uint64_t n_lanes,
-                    uint32_t* __restrict__ cnt, const uint64_t* __restrict__ off, uint32_t* __restrict__ pixel,
-                    float4* __restrict__ seg, float* __restrict__ t_lo, int* __restrict__ flag) {
+                    uint32_t* __restrict__ cnt, const uint64_t* __restrict__ off, float4* __restrict__ seg,
+                    float* __restrict__ t_lo, int* __restrict__ flag) {
     const uint64_t lane = static_cast<uint64_t>(blockIdx.x) * kThreads + threadIdx.x;
     if (lane >= n_lanes) return;
     Sampler rng;
@@ -60,7 +60,6 @@ inside_trace_kernel(const __grid_constant__ SceneParams P, const __grid_constant
     uint64_t at = kFill ? off[lane] : 0;
     auto emit = [&](const Ray& r, float maxt, float w0, bool inside, float start) {
         if (kFill) {
-            pixel[at] = static_cast<uint32_t>(lane);
             seg[2 * at] = make_float4(r.ox, r.oy, r.oz, inside ? -maxt : maxt);  // sign of the length = plane
             seg[2 * at + 1] = make_float4(r.dx, r.dy, r.dz, w0);
             t_lo[at] = start;
@@ -103,39 +102,54 @@ __global__ void widen_kernel(const uint32_t* __restrict__ in, uint64_t* __restri
     if (i < n) out[i] = in[i];
 }
 
+__global__ void narrow_kernel(const uint64_t* __restrict__ in, uint32_t* __restrict__ out, uint64_t n) {
+    const uint64_t i = static_cast<uint64_t>(blockIdx.x) * kThreads + threadIdx.x;
+    if (i < n) out[i] = static_cast<uint32_t>(in[i]);
+}
+
 // P is the one-channel view of the scene (surface_aware = 0): the planes are indexed by voxel.
+// One thread per listed lane walks the lane's records one after the other: neighbouring lanes
+// (columns of one DMD row) have records of the same kind and nearly the same length, so a warp
+// stays together, and the adjoint adds to its pattern pixel without an atomic.
 template <int kMode>
 __global__ void __launch_bounds__(kThreads)
-inside_pass_kernel(const __grid_constant__ SceneParams P, const uint32_t* __restrict__ pixel,
-                   const float4* __restrict__ seg, const float* __restrict__ t_lo, uint64_t n_rec,
-                   const float* __restrict__ in,
+inside_pass_kernel(const __grid_constant__ SceneParams P, const uint32_t* __restrict__ off,
+                   const float4* __restrict__ seg, const float* __restrict__ t_lo, const float* __restrict__ in,
                    float* __restrict__ out, size_t n_vox, const uint32_t* __restrict__ active_pixels,
                    uint64_t n_active, float ray_weight, const int* __restrict__ gate) {
     if (*gate != 0) return;
-    const uint64_t i = static_cast<uint64_t>(blockIdx.x) * kThreads + threadIdx.x;
-    if (i >= n_rec) return;
-    const uint32_t lane = __ldg(pixel + i) - __ldg(active_pixels);  // the pixel list is base + j (planar check)
-    if (lane >= n_active) return;
-    const float4 a = __ldg(seg + 2 * i), b = __ldg(seg + 2 * i + 1);
-    Ray r;
-    r.ox = a.x; r.oy = a.y; r.oz = a.z;
-    r.dx = b.x; r.dy = b.y; r.dz = b.z;
-    const size_t plane = a.w < 0.f ? n_vox : 0;  // plane B (inside the target) after plane A
-    const float start = __ldg(t_lo + i);
-    DdaWalk W;
-    const bool any = start > 0.f ? W.begin<true>(P, r, fabsf(a.w), b.w, false, start)
-                                 : W.begin<false>(P, r, fabsf(a.w), b.w, false);
-    if (!any) return;
+    const uint64_t j = static_cast<uint64_t>(blockIdx.x) * kThreads + threadIdx.x;
+    if (j >= n_active) return;
+    const uint64_t lane = __ldg(active_pixels) + j;  // the pixel list is base + j (planar check)
+    const uint32_t r0 = __ldg(off + lane), r1 = __ldg(off + lane + 1);
+    if (r0 == r1) return;
+    float em = 0.f;
     if (kMode == 0) {
-        const float em = __ldg(in + lane) * ray_weight;
+        em = __ldg(in + j) * ray_weight;
         if (em == 0.f) return;
-        ScatterSink sink{out + plane, em};
-        while (W.step(sink)) {}
-    } else {
-        GatherSink sink{in + plane};
-        while (W.step(sink)) {}
-        if (sink.acc != 0.f) atomicAdd(out + lane, sink.acc * ray_weight);
     }
+    float acc = 0.f;
+    for (uint32_t i = r0; i < r1; ++i) {
+        const float4 a = __ldg(seg + 2 * static_cast<size_t>(i)), b = __ldg(seg + 2 * static_cast<size_t>(i) + 1);
+        Ray r;
+        r.ox = a.x; r.oy = a.y; r.oz = a.z;
+        r.dx = b.x; r.dy = b.y; r.dz = b.z;
+        const size_t plane = a.w < 0.f ? n_vox : 0;  // plane B (inside the target) after plane A
+        const float start = __ldg(t_lo + i);
+        DdaWalk W;
+        const bool any = start > 0.f ? W.begin<true>(P, r, fabsf(a.w), b.w, false, start)
+                                     : W.begin<false>(P, r, fabsf(a.w), b.w, false);
+        if (!any) continue;
+        if (kMode == 0) {
+            ScatterSink sink{out + plane, em};
+            while (W.step(sink)) {}
+        } else {
+            GatherSink sink{in + plane};
+            while (W.step(sink)) {}
+            acc += sink.acc;
+        }
+    }
+    if (kMode == 1) out[j] += acc * ray_weight;
 }
 
 __global__ void __launch_bounds__(kThreads)
@@ -164,7 +178,7 @@ unsigned blocks_for(uint64_t n) { return static_cast<unsigned>((n + kThreads - 1
 }  // namespace
 
 void inside_release(InsideHost& H) {
-    if (H.pixel) cudaFree(H.pixel);
+    if (H.off) cudaFree(H.off);
     if (H.seg) cudaFree(H.seg);
     if (H.t_lo) cudaFree(H.t_lo);
     if (H.planes) cudaFree(H.planes);
@@ -197,7 +211,7 @@ cudaError_t inside_build(const SceneParams& P, const SceneParams& P1, InsideHost
         IN_TRY(cudaMalloc(&flag, sizeof(int)));
         IN_TRY(cudaMemset(flag, 0, sizeof(int)));
         inside_trace_kernel<false><<<blocks_for(n_lanes), kThreads>>>(P, P1, n_lanes, cnt, nullptr, nullptr, nullptr,
-                                                                     nullptr, flag);
+                                                                     flag);
         count_launch();
         widen_kernel<<<blocks_for(n_lanes), kThreads>>>(cnt, wide, n_lanes);
         count_launch();
@@ -214,14 +228,16 @@ cudaError_t inside_build(const SceneParams& P, const SceneParams& P1, InsideHost
         if (total) {
             size_t free_b = 0, all_b = 0;
             IN_TRY(cudaMemGetInfo(&free_b, &all_b));
-            if (total * 40 > free_b / 2) return cudaErrorMemoryAllocation;
-            IN_TRY(cudaMalloc(&H.pixel, sizeof(uint32_t) * total));
+            if (total * 40 > free_b / 2 || total >= (1ull << 32)) return cudaErrorMemoryAllocation;
             IN_TRY(cudaMalloc(&H.seg, sizeof(float4) * 2 * total));
             IN_TRY(cudaMalloc(&H.t_lo, sizeof(float) * total));
-            inside_trace_kernel<true><<<blocks_for(n_lanes), kThreads>>>(P, P1, n_lanes, nullptr, off, H.pixel, H.seg,
-                                                                        H.t_lo, flag);
+            inside_trace_kernel<true><<<blocks_for(n_lanes), kThreads>>>(P, P1, n_lanes, nullptr, off, H.seg, H.t_lo,
+                                                                        flag);
             count_launch();
         }
+        IN_TRY(cudaMalloc(&H.off, sizeof(uint32_t) * (n_lanes + 1)));
+        narrow_kernel<<<blocks_for(n_lanes + 1), kThreads>>>(off, H.off, n_lanes + 1);
+        count_launch();
         IN_TRY(cudaMalloc(&H.planes, sizeof(float) * 2 * n_vox));
         IN_TRY(cudaDeviceSynchronize());
         return cudaGetLastError();
@@ -247,7 +263,7 @@ cudaError_t inside_forward_finish(const SceneParams& P1, InsideHost& H, const in
                                   const uint32_t* active_pixels, uint64_t n_active, float ray_weight, float* film,
                                   cudaStream_t stream) {
     if (H.n_rec) {
-        inside_pass_kernel<0><<<blocks_for(H.n_rec), kThreads, 0, stream>>>(P1, H.pixel, H.seg, H.t_lo, H.n_rec,
+        inside_pass_kernel<0><<<blocks_for(n_active), kThreads, 0, stream>>>(P1, H.off, H.seg, H.t_lo,
                                                                            active_data, H.planes, H.n_vox, active_pixels, n_active,
                                                                            ray_weight, gate);
         count_launch();
@@ -270,7 +286,7 @@ cudaError_t inside_adjoint_begin(InsideHost& H, const float* dL, cudaStream_t st
 cudaError_t inside_adjoint_finish(const SceneParams& P1, InsideHost& H, const int* gate, const uint32_t* active_pixels,
                                   uint64_t n_active, float ray_weight, float* grad, cudaStream_t stream) {
     if (!H.n_rec) return cudaSuccess;
-    inside_pass_kernel<1><<<blocks_for(H.n_rec), kThreads, 0, stream>>>(P1, H.pixel, H.seg, H.t_lo, H.n_rec, H.planes,
+    inside_pass_kernel<1><<<blocks_for(n_active), kThreads, 0, stream>>>(P1, H.off, H.seg, H.t_lo, H.planes,
                                                                        grad, H.n_vox, active_pixels, n_active, ray_weight,
                                                                        gate);
     count_launch();

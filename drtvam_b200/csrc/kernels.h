@@ -140,7 +140,7 @@ cudaError_t launch_mul(const float* a, const float* b, float* out, size_t n, cud
 // inside-target segment records: the surface-aware film on top of the planar kernels (inside_kernels.cu)
 struct InsideHost {
     bool valid = false;
-    uint32_t* pixel = nullptr;  // [n_rec] global pixel id of the lane
+    uint32_t* off = nullptr;    // [lanes + 1] first record of every lane of the full pixel grid
     float4* seg = nullptr;      // [n_rec][2] {origin, length}, {direction, throughput at the origin}
     float* t_lo = nullptr;      // [n_rec] > 0: walk the record from here on only (the negative record)
     uint64_t n_rec = 0;
