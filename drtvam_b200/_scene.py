@@ -16,7 +16,7 @@ SURF_CYLINDER, SURF_BOX = 0, 1
 BSDF_NULL, BSDF_DIELECTRIC, BSDF_ABSORBER = 0, 1, 2
 PROJ_KINDS = {"collimated": 0, "telecentric": 1, "lens": 2}
 PHASE_KINDS = {"isotropic": 0, "rayleigh": 1, "hg": 2}
-SENSOR_KINDS = {"dda": 0, "ratio": 1}
+SENSOR_KINDS = {"dda": 0, "ratio": 1, "delta": 2}
 
 # Mitsuba's named indices of refraction (dielectric plugin table); "air" is the
 # default ext_ior the square vial's outer wall relies on (geometry.py:201-204).

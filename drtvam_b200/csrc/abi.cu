@@ -215,8 +215,12 @@ int drtvam_scene_create(const DrtvamSceneDesc* d, int device, DrtvamScene** out)
         return fail(DRTVAM_E_INVALID, "surface count %d outside [1, %d]", d->n_surf, DRTVAM_MAX_SURFACES);
     if (!(d->sigma_t > 0.f)) return fail(DRTVAM_E_INVALID, "medium extinction must be positive");
     if (d->albedo < 0.f || d->albedo > 1.f) return fail(DRTVAM_E_INVALID, "albedo outside [0, 1]");
-    if (d->sensor_kind != DRTVAM_SENSOR_DDA && d->sensor_kind != DRTVAM_SENSOR_RATIO)
+    if (d->sensor_kind != DRTVAM_SENSOR_DDA && d->sensor_kind != DRTVAM_SENSOR_RATIO &&
+        d->sensor_kind != DRTVAM_SENSOR_DELTA)
         return fail(DRTVAM_E_INVALID, "unsupported sensor kind %d", d->sensor_kind);
+    if (d->sensor_kind == DRTVAM_SENSOR_DELTA && !(d->albedo > 0.f))  // volume.py:156-157
+        return fail(DRTVAM_E_INVALID, "Tried to render a purely absorptive volume with a delta tracking sensor. "
+                                      "This is not supported.");
     if (d->sensor_kind == DRTVAM_SENSOR_RATIO && !(d->majorant > 0.f))
         return fail(DRTVAM_E_INVALID, "ratio sensor needs a positive majorant");
     if (!d->motion_analytic && !d->motion_table_host)

@@ -221,6 +221,28 @@ __device__ __forceinline__ bool dda_has_frozen_axis(const SceneParams& P, const 
     return frozen;
 }
 
+// Delta-tracking sensor (sensor.py:141-178): one deposit at the collision point of a lane whose free
+// flight ended inside the medium.  contrib = throughput * sigma_a * tr / (tr * sigma_t), zero when
+// the pdf tr * sigma_t underflows; voxel by floor, points outside the grid dropped (sensor.py:144-146).
+template <class Sink>
+__device__ __forceinline__ void delta_deposit(const SceneParams& P, const Ray& ray, float t_coll, float w0,
+                                              bool inside_target, Sink& sink) {
+    if (!(t_coll < INFINITY)) return;  // mei.is_valid()
+    if (expf(-P.sigma_t * t_coll) * P.sigma_t == 0.f) return;
+    const float p[3] = {fmaf(ray.dx, t_coll, ray.ox), fmaf(ray.dy, t_coll, ray.oy), fmaf(ray.dz, t_coll, ray.oz)};
+    int v[3];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        const float vs = (P.bmax[a] - P.bmin[a]) / static_cast<float>(P.res[a]);
+        const float f = floorf((p[a] - P.bmin[a]) / vs);
+        if (!(f >= 0.f && f < static_cast<float>(P.res[a]))) return;
+        v[a] = static_cast<int>(f);
+    }
+    const size_t flat = static_cast<size_t>(v[0]) + static_cast<size_t>(v[1]) * P.res[0] +
+                        static_cast<size_t>(v[2]) * P.res[0] * P.res[1];
+    sink.visit(P.surface_aware ? (2 * flat + (inside_target ? 0 : 1)) : flat, w0);
+}
+
 // Ratio-tracking estimator (sensor.py:243-293): exponential steps with the
 // majorant, one deposit per tentative collision.
 template <class Sink>

@@ -174,8 +174,16 @@ general_persistent_kernel(const __grid_constant__ SceneParams P, const float* __
             if (need && has_ray) {
                 bool alive = true, begun = false;
                 do {
-                    alive = bounce_once<kScatter>(P, T, rng, [&](const Ray& r, float maxt, float w0, bool inside) {
-                        if (P.sensor_kind == 1) {  // ratio tracking draws from the lane's stream: not deferred
+                    alive = bounce_once<kScatter>(P, T, rng, [&](const Ray& r, float maxt, float w0, bool inside,
+                                                                float t_coll) {
+                        if (P.sensor_kind == 2) {  // delta sensor: a single deposit, nothing to walk
+                            if (kMode == 0) {
+                                ScatterSink sink{out, em};
+                                delta_deposit(P, r, t_coll, w0, inside, sink);
+                            } else {
+                                delta_deposit(P, r, t_coll, w0, inside, gsink);
+                            }
+                        } else if (P.sensor_kind == 1) {  // ratio tracking draws from the lane's stream: not deferred
                             if (kMode == 0) {
                                 ScatterSink sink{out, em};
                                 ratio_segment(P, r, maxt, w0, inside, rng, sink);

@@ -71,7 +71,7 @@ inside_trace_kernel(const __grid_constant__ SceneParams P, const __grid_constant
     T.ray = ray0;
     uint32_t n_sub = 0;
     float t1 = 0.f;
-    while (bounce_once<false>(P, T, rng, [&](const Ray& r, float maxt, float w0, bool inside) {
+    while (bounce_once<false>(P, T, rng, [&](const Ray& r, float maxt, float w0, bool inside, float) {
         if (n_sub == 0) t1 = maxt;
         else emit(r, maxt, w0, inside, 0.f);
         ++n_sub;
@@ -86,7 +86,7 @@ inside_trace_kernel(const __grid_constant__ SceneParams P, const __grid_constant
     uint32_t n_u = 0;
     Ray ur = ray0;
     float u_maxt = 0.f, u_w0 = 0.f;
-    while (bounce_once<false>(P1, U, rng, [&](const Ray& r, float maxt, float w0, bool) {
+    while (bounce_once<false>(P1, U, rng, [&](const Ray& r, float maxt, float w0, bool, float) {
         if (n_u == 0) { ur = r; u_maxt = maxt; u_w0 = w0; }
         ++n_u;
     })) {}

@@ -61,7 +61,8 @@ struct TraceState {
 
 // ONE trip of the bounce loop of volume.py:179-272: Russian roulette, nearest interface (vial
 // surfaces and, in surface-aware runs, the target mesh), free flight, the medium segment of this
-// trip handed to `on_segment(ray, maxt, w0, inside_target)` with the throughput at its origin, then
+// trip handed to `on_segment(ray, maxt, w0, inside_target, t_coll)` with the throughput at its origin
+// (t_coll: free-flight distance of a lane that collides inside the segment, else +inf), then
 // the interface / phase event and the bookkeeping.  Nothing after the hand-over depends on how the
 // segment is deposited, so the caller may walk it later.  Returns false when the lane is finished.
 // kScatter is the scalar `has_scattering` branch of volume.py:154-155,199.
@@ -112,7 +113,7 @@ __device__ __forceinline__ bool bounce_once(const SceneParams& P, TraceState& T,
     const bool collide = T.in_medium && !reached_surface;
 
     // both collision and surface lanes deposit along the whole [0, si.t] (volume.py:216)
-    if (T.in_medium) on_segment(ray, H.t, T.attenuation * absorb, T.inside_target);
+    if (T.in_medium) on_segment(ray, H.t, T.attenuation * absorb, T.inside_target, t_coll);
 
     T.inside_target = T.inside_target != hit_target;  // volume.py:219
 
@@ -155,8 +156,9 @@ template <bool kScatter, class Sink>
 __device__ __forceinline__ void trace_lane(const SceneParams& P, Ray ray, Sampler& rng, Sink& sink) {
     TraceState T;
     T.ray = ray;
-    while (bounce_once<kScatter>(P, T, rng, [&](const Ray& r, float maxt, float w0, bool inside) {
+    while (bounce_once<kScatter>(P, T, rng, [&](const Ray& r, float maxt, float w0, bool inside, float t_coll) {
         if constexpr (Sink::kRecordOnly) sink.record(r, maxt, w0);
+        else if (P.sensor_kind == 2) delta_deposit(P, r, t_coll, w0, inside, sink);
         else if (P.sensor_kind == 1) ratio_segment(P, r, maxt, w0, inside, rng, sink);
         else dda_segment(P, r, maxt, w0, inside, sink);
     })) {}

@@ -109,6 +109,9 @@ class Scene:
         if sensor.kind not in SENSOR_KINDS:
             raise NotImplementedError(f"sensor '{sensor.kind}' has no kernel")
         d.sensor_kind = SENSOR_KINDS[sensor.kind]
+        if sensor.kind == 'delta' and not d.albedo > 0:  # volume.py:156-157
+            raise ValueError("Tried to render a purely absorptive volume with a delta tracking sensor. "
+                             "This is not supported.")
         d.majorant = float(getattr(sensor, 'majorant', 0.0))
         d.target_triangles = self.target_triangles()
         return d
@@ -255,8 +258,6 @@ def load_dict(scene_dict: dict, device=None) -> Scene:
             if device is not None:
                 props['device'] = device
             sensors[name] = _sensors[t](props)
-        elif t == 'delta':
-            raise NotImplementedError("the delta-tracking sensor has no kernel yet")
         elif t in _integrators:
             integrator = _integrators[t](entry)
         elif t == 'homogeneous':

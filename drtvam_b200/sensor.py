@@ -1,10 +1,11 @@
 """Dose sensors.  Mirrors ``src/drtvam/sensor.py``: ``VolumetricSensor``
 (:5-110: bounding box from ``to_world``, ``voxel_size``, ``compute_volume``),
-``DDAVolumetricSensor`` (:297-440), ``RatioVolumetricSensor`` (:193-295).
+``DDAVolumetricSensor`` (:297-440), ``RatioVolumetricSensor`` (:193-295),
+``DeltaVolumetricSensor`` (:112-191).
 
 ``accumulate`` -- the voxel walk itself -- is the CUDA hot loop
 (``csrc/dda.cuh``, ``csrc/planar_kernels.cu``); these classes carry the
-geometry.  The delta-tracking sensor (:112-191) is not built yet.  The surface-aware
+geometry.  The surface-aware
 sub-voxel volumes (:53-110) are ``drtvam_compute_volume`` (``csrc/mesh_kernels.cu``).
 """
 from __future__ import annotations
@@ -85,7 +86,13 @@ class RatioVolumetricSensor(VolumetricSensor):
         self.majorant = props['majorant']
 
 
+class DeltaVolumetricSensor(VolumetricSensor):
+    """One deposit per medium collision (sensor.py:112-191); scattering media only."""
+    kind = 'delta'
+
+
 sensors = {
     'dda': DDAVolumetricSensor,
     'ratio': RatioVolumetricSensor,
+    'delta': DeltaVolumetricSensor,
 }

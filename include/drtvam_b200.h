@@ -58,6 +58,7 @@ extern "C" {
 
 #define DRTVAM_SENSOR_DDA 0   /* sensor.py:297-440 */
 #define DRTVAM_SENSOR_RATIO 1 /* sensor.py:193-295 */
+#define DRTVAM_SENSOR_DELTA 2 /* sensor.py:112-191; scattering media only (volume.py:156-157) */
 
 typedef struct DrtvamSurface {
     int32_t kind, bsdf;

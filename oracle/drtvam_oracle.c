@@ -518,6 +518,35 @@ static real ratio_accumulate(Acc *A, Ray ray, real em, int inside_target, real a
     return g_em;
 }
 
+/* sensor.py:112-191 DeltaVolumetricSensor.accumulate: one deposit at the collision point ray(mei.t)
+ * of the lanes whose free flight ended inside the medium (mei.is_valid(), sensor.py:141):
+ * contrib = throughput * sigma_a * tr / (tr * sigma_t) * em (sensor.py:169-178), zero when the pdf
+ * tr * sigma_t underflows.  Voxel by floor, lanes outside the grid dropped (sensor.py:144-146). */
+static real delta_accumulate(Acc *A, Ray ray, real em, int inside_target, real attenuation,
+                             real t_prev, real mei_t) {
+    const OrcScene *s = A->s;
+    if (!(mei_t < RINF)) return 0;
+    real st = (real)s->sigma_t, ss = st * (real)s->albedo, sa = st - ss;
+    real tr = rexp(-st * mei_t), tr_pdf = tr * st;
+    real inv_pdf = tr_pdf != 0 ? 1 / tr_pdf : 0;
+    real throughput = attenuation * rexp(st * t_prev) * rexp(-st * t_prev);
+    real p[3] = {ray.o.x + ray.d.x * mei_t, ray.o.y + ray.d.y * mei_t, ray.o.z + ray.d.z * mei_t};
+    size_t v[3];
+    for (int a = 0; a < 3; ++a) {
+        real lo = (real)s->bbox_min[a], hi = (real)s->bbox_max[a];
+        real vs = (hi - lo) / (real)s->res[a];
+        double f = floor((double)((p[a] - lo) / vs));
+        if (!(f >= 0 && f < (double)s->res[a])) return 0;
+        v[a] = (size_t)f;
+    }
+    size_t flat = v[0] + v[1] * s->res[0] + v[2] * (size_t)s->res[0] * s->res[1];
+    size_t idx = s->surface_aware ? (inside_target ? 2 * flat : 2 * flat + 1) : flat;
+    real cw = throughput * sa * tr * inv_pdf;
+    A->visits++;
+    if (A->mode == 0) { film_add(A->film, idx, cw * em); return 0; }
+    return cw * A->dL[idx];
+}
+
 /* ------------------------------------------------------------------ integrator */
 
 /* volume.py:136-282 VolumeIntegrator.sample for one lane.  Returns em_grad
@@ -563,7 +592,8 @@ static real trace_lane(Acc *A, Ray ray, real Le, Pcg32 *rng) {
 
         if (active_medium || reached_surface) {
             real g;
-            if (s->sensor_kind == 1) g = ratio_accumulate(A, ray, Le, inside_target, attenuation, total_t, n_scat, si.t, rng);
+            if (s->sensor_kind == 2) g = delta_accumulate(A, ray, Le, inside_target, attenuation, total_t, active_medium ? mei_t : RINF);
+            else if (s->sensor_kind == 1) g = ratio_accumulate(A, ray, Le, inside_target, attenuation, total_t, n_scat, si.t, rng);
             else g = dda_accumulate(A, ray, Le, inside_target, attenuation, total_t, n_scat, si.t);
             em_grad += g;
         }

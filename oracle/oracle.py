@@ -92,6 +92,9 @@ class Oracle:
                   "transmission_only", "regular_sampling", "sample_time", "print_time", "sigma_t", "albedo",
                   "phase_kind", "hg_g", "surface_aware", "sensor_kind", "majorant"):
             setattr(s, k, desc[k])
+        if desc["sensor_kind"] == 2 and not desc["albedo"] > 0:  # volume.py:156-157
+            raise ValueError("Tried to render a purely absorptive volume with a delta tracking sensor. "
+                             "This is not supported.")
         self._table = None
         if desc.get("motion_table") is not None:
             self._table = np.ascontiguousarray(np.asarray(desc["motion_table"], np.float64).reshape(-1, 16))
