@@ -11,7 +11,7 @@ import os
 from . import build as _build
 
 MAX_SURFACES = 8
-ABI_VERSION = 5
+ABI_VERSION = 6
 
 
 class DrtvamSurface(C.Structure):
@@ -61,6 +61,8 @@ SYMBOLS = {
     "drtvam_forward": (C.c_int, [_vp, _vp, _vp, _u64, _u32, _u32, _f32, _vp, _i32, _vp]),
     "drtvam_adjoint": (C.c_int, [_vp, _vp, _vp, _u64, _u32, _u32, _f32, _vp, _vp]),
     "drtvam_raygen": (C.c_int, [_vp, _vp, _u64, _u32, _u32, _vp, _vp]),
+    "drtvam_radon": (C.c_int, [_vp, _vp, _u64, _u32, _u32, _vp, _vp]),
+    "drtvam_corner_filter": (C.c_int, [_vp, _vp, _u64, _u32, _u32, _f32, _f32, _vp, _vp]),
     "drtvam_count_visits": (C.c_int, [_vp, _vp, _u64, _u32, _u32, C.POINTER(_u64)]),
     "drtvam_forward_host": (C.c_int, [_vp, _vp, _vp, _u64, _u32, _u32, _f32, _vp]),
     "drtvam_adjoint_host": (C.c_int, [_vp, _vp, _vp, _u64, _u32, _u32, _f32, _vp]),

@@ -463,6 +463,27 @@ int drtvam_raygen(DrtvamScene* s, const uint32_t* active_pixels, uint64_t n_acti
     return DRTVAM_OK;
 }
 
+int drtvam_radon(DrtvamScene* s, const uint32_t* active_pixels, uint64_t n_active, uint32_t spp, uint32_t seed,
+                 float* image, void* stream) {
+    if (int rc = check_call(s, n_active, spp)) return rc;
+    if (!image || (n_active && !active_pixels)) return fail(DRTVAM_E_INVALID, "NULL buffer");
+    if (s->P.target.n_tri <= 0) return fail(DRTVAM_E_INVALID, "No target shape found in the scene");  // radon.py:57-58
+    DeviceGuard guard(s->device);
+    CUDA_TRY(launch_radon(s->P, active_pixels, n_active * spp, spp, seed, ray_weight(s, n_active ? n_active : 1, spp),
+                          image, static_cast<cudaStream_t>(stream)));
+    return DRTVAM_OK;
+}
+
+int drtvam_corner_filter(DrtvamScene* s, const uint32_t* active_pixels, uint64_t n_active, uint32_t spp, uint32_t seed,
+                         float dist, float radius, float* image, void* stream) {
+    if (int rc = check_call(s, n_active, spp)) return rc;
+    if (!image || (n_active && !active_pixels)) return fail(DRTVAM_E_INVALID, "NULL buffer");
+    DeviceGuard guard(s->device);
+    CUDA_TRY(launch_corner(s->P, active_pixels, n_active * spp, spp, seed, ray_weight(s, n_active ? n_active : 1, spp),
+                           dist, radius, image, static_cast<cudaStream_t>(stream)));
+    return DRTVAM_OK;
+}
+
 int drtvam_count_visits(DrtvamScene* s, const uint32_t* active_pixels, uint64_t n_active, uint32_t spp,
                         uint32_t seed, uint64_t* out_host) {
     if (int rc = check_call(s, n_active, spp)) return rc;

@@ -157,6 +157,13 @@ cudaError_t inside_adjoint_begin(InsideHost& H, const float* dL, cudaStream_t st
 cudaError_t inside_adjoint_finish(const SceneParams& P1, InsideHost& H, const int* gate, const uint32_t* active_pixels,
                                   uint64_t n_active, float ray_weight, float* grad, cudaStream_t stream);
 
+// one-shot pixel pre-filters (filter_kernels.cu); `image` has n_patterns * res_y * res_x floats and is cleared
+cudaError_t launch_radon(const SceneParams& P, const uint32_t* active_pixels, uint64_t n_lanes, uint32_t spp,
+                         uint32_t seed, float ray_weight, float* image, cudaStream_t stream);
+cudaError_t launch_corner(const SceneParams& P, const uint32_t* active_pixels, uint64_t n_lanes, uint32_t spp,
+                          uint32_t seed, float ray_weight, float dist, float radius, float* image,
+                          cudaStream_t stream);
+
 // fused thresholded loss + gradient on the dose volume (loss_kernels.cu)
 cudaError_t launch_thresholded_loss(const float* x, const float* x_b, float alpha, const float* target, size_t n,
                                     float tl, float tu, float w_obj, float w_void, float w_lim, int K, float grad_scale,

@@ -16,7 +16,7 @@ import torch
 
 from . import parallel
 from .geometry import geometries
-from .integrators import VolumeIntegrator
+from .integrators import CornerIntegrator, RadonIntegrator, VolumeIntegrator
 from .lbfgs import LinearLBFGS
 from .loss import losses
 from .scene import load_dict, render, traverse
@@ -108,8 +108,24 @@ def optimize(config, patterns_fwd=None, progress=True):
         raise ValueError("The final sensor is used to generate visualizations and metrics of the final simulated print. Therefore, it must not be surface-aware. If you are using the surface-aware discretization for optimization, please specify another sensor called 'final_sensor' in the configuration file.")
 
     surface_aware = sensor.film().surface_aware
-    if config.get('filter_radon', False) or 'filter_corner' in config:
-        raise NotImplementedError("filter_radon / filter_corner pre-filters are not built yet (SURVEY.md 8(f) row 2)")
+
+    def keep_positive(image):
+        # optimize.py:151-159 / 173-181: the pixels whose filter image is positive, patterns reset to zero
+        active_pixels = torch.nonzero(image.reshape(-1) > 0.).reshape(-1).to(torch.int32)
+        if active_pixels.numel() == 0:
+            raise ValueError("No active pixels found in the Radon transform.")
+        params['projector.active_pixels'] = active_pixels
+        params['projector.active_data'] = torch.zeros(active_pixels.numel(), device=image.device,
+                                                      dtype=torch.float32)
+        params.update()
+
+    if config.get('filter_radon', False) and patterns_fwd is None:
+        # Deactivate pixels where the Radon transform is zero (optimize.py:143-163)
+        radon_integrator = RadonIntegrator({'max_depth': 5})
+        keep_positive(render(scene, integrator=radon_integrator, spp=config.get('spp_filter_radon', 4)))
+    if 'filter_corner' in config and patterns_fwd is None:
+        corner_integrator = CornerIntegrator({'regular_sampling': True} | config['filter_corner'])
+        keep_positive(render(scene, integrator=corner_integrator, spp=1))
 
     integrator = VolumeIntegrator({
         'max_depth': 3 if progressive else max_depth,

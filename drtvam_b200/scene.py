@@ -121,7 +121,12 @@ class Scene:
         scene (surface-aware runs), else None."""
         if not self.target_active:
             return None
+        return self.all_target_triangles()
+
+    def all_target_triangles(self):
         t = self.target
+        if t is None:
+            return None
         return np.ascontiguousarray(np.asarray(t['vertices'], np.float64)[np.asarray(t['triangles'])].astype(np.float32))
 
     def handle(self, integrator, sensor):
@@ -147,6 +152,27 @@ class Scene:
         _lib.check(lib.drtvam_scene_set_depth(h, int(integrator.max_depth), int(integrator.rr_depth)))
         _lib.check(lib.drtvam_scene_force_general(h, int(self.force_general)))
         return h
+
+    def filter_handle(self, integrator, sensor):
+        """One-off C handle for the pixel pre-filters (optimize.py:143-185): they run before the target
+        is moved away (optimize.py:188-191), so the mesh is attached whether or not the run is
+        surface-aware.  The caller destroys it."""
+        lib = _lib.load()
+        desc = self.describe(integrator, sensor)
+        cdesc, keep = desc.to_c()
+        out = C.c_void_p()
+        dev = self.projector.active_data.device
+        if dev.type != 'cuda':
+            raise RuntimeError("drtvam_b200 has no CPU path: scene tensors must live on a CUDA device")
+        _lib.check(lib.drtvam_scene_create(C.byref(cdesc), dev.index or 0, C.byref(out)))
+        tri = self.all_target_triangles()
+        if tri is not None:
+            try:
+                _lib.check(lib.drtvam_scene_set_target(out.value, tri.ctypes.data, tri.shape[0]))
+            except Exception:
+                lib.drtvam_scene_destroy(out.value)
+                raise
+        return out.value
 
     def geometry_integrator(self):
         """Integrator options for calls that only need the geometry (compute_volume)."""

@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define DRTVAM_ABI_VERSION 5
+#define DRTVAM_ABI_VERSION 6
 #define DRTVAM_MAX_SURFACES 8
 
 #define DRTVAM_OK 0
@@ -163,6 +163,22 @@ int drtvam_adjoint(DrtvamScene *scene, const float *dose_grad, const uint32_t *a
 /* TVAMIntegrator.sample_rays (common.py:70-116): rays_out[lanes][6] = o,d. */
 int drtvam_raygen(DrtvamScene *scene, const uint32_t *active_pixels, uint64_t n_active,
                   uint32_t spp, uint32_t seed, float *rays_out, void *stream);
+
+/* Pixel pre-filters of optimize.py:143-185.  Both write
+ * image[n_patterns * res_y * res_x] (cleared first): image[pixel] += L * ray weight
+ * over the spp lanes of each listed pixel (radon.py:42-44); the caller keeps the
+ * pixels with image > 0 (optimize.py:151,173).
+ * drtvam_radon: RadonIntegrator.render / sample (integrators/radon.py:13-106), the
+ * absorbed fraction along the parts of the path inside the target mesh; needs the
+ * target (drtvam_scene_set_target) and uses the scene's max_depth
+ * (optimize.py:145-148 sets 5).
+ * drtvam_corner_filter: CornerIntegrator.render / sample
+ * (integrators/filter_corner.py:17-66), 1 unless the first hit lies within `radius`
+ * of the vial edge |x| = |y| = dist. */
+int drtvam_radon(DrtvamScene *scene, const uint32_t *active_pixels, uint64_t n_active, uint32_t spp,
+                 uint32_t seed, float *image, void *stream);
+int drtvam_corner_filter(DrtvamScene *scene, const uint32_t *active_pixels, uint64_t n_active, uint32_t spp,
+                         uint32_t seed, float dist, float radius, float *image, void *stream);
 
 /* Number of DDA trips (sensor.py:383) one forward pass makes; the unit of
  * work of the roofline.  Synchronises and returns the count in *out_host. */

@@ -733,6 +733,87 @@ int orc_adjoint(const OrcScene *s, const real *dL, const uint32_t *active_pixels
 }
 
 /* common.py:70-116: the rays alone (tests/test_projector.py). out = [n_active*spp][6]. */
+/* integrators/radon.py:48-106 RadonIntegrator.sample for one lane: the absorbed fraction along the
+ * parts of the path that lie inside the target mesh (purely absorptive assumption, radon.py:76).
+ * No Russian roulette, no free flight; `depth` of radon.py:93 is the never-incremented argument,
+ * so every interface is sampled with the transmission lobe only. */
+static real radon_lane(const OrcScene *s, Ray ray, Pcg32 *rng) {
+    real st = (real)s->sigma_t;
+    int active = 1, active_medium = 0, inside_target = 0;
+    real throughput = 1, L = 0, t = 0;
+    uint32_t d = 0;
+    while (active) {
+        Hit si = scene_intersect(s, ray);
+        active = active && si.valid;
+        real seg = si.valid ? si.t : RINF;
+        real contrib = throughput * rexp(-st * t) * (1 - rexp(-st * seg));
+        int hit_target = active && si.shape == ORC_SHAPE_TARGET;
+        if (inside_target && active_medium) L += contrib; /* radon.py:79: not masked by `active` */
+        if (!active) break;
+        t += si.t;
+        inside_target = inside_target != hit_target;
+        (void)next_1d(rng); (void)next_1d(rng); (void)next_1d(rng);
+        const OrcSurface *sf = hit_target ? NULL : &s->surf[si.shape];
+        V3 wo = ray.d; real bw = 1;
+        if (!hit_target && sf->bsdf == 2) bw = 0;
+        else if (!hit_target && sf->bsdf == 1) {
+            real cos_i = -vdot(si.n, ray.d), cos_t, eta_it, eta_ti;
+            real F = fresnel(cos_i, (real)sf->eta, &cos_t, &eta_it, &eta_ti);
+            wo = vadd(vscale(ray.d, eta_ti), vscale(si.n, eta_ti * cos_i + cos_t));
+            bw = (1 - F) * eta_ti * eta_ti;
+        }
+        throughput *= bw;
+        ray.o = offset_p(si.p, si.n, wo);
+        ray.d = wo;
+        if (!hit_target) d += 1;
+        active = d < (uint32_t)s->max_depth;
+        if (!hit_target) { /* radon.py:104: only shapes that carry a medium are transitions */
+            int outward = vdot(wo, si.n) > 0;
+            if (sf->interior_medium != sf->exterior_medium)
+                active_medium = outward ? sf->exterior_medium != 0 : sf->interior_medium != 0;
+        }
+    }
+    return L;
+}
+
+/* RadonIntegrator.render (radon.py:13-46): image[pixel] += L * weight over the spp lanes of a pixel.
+ * `image` has n_patterns * res_y * res_x entries and is cleared first. */
+int orc_radon(const OrcScene *s, const uint32_t *active_pixels, uint64_t n_active, uint32_t spp, uint32_t seed,
+              real *image) {
+    if (s->regular_sampling) spp = 1;
+    real w = ray_weight(s, n_active, spp);
+    size_t n_img = (size_t)s->n_patterns * s->res_x * s->res_y;
+    for (size_t i = 0; i < n_img; ++i) image[i] = 0;
+    for (uint64_t lane = 0; lane < n_active * spp; ++lane) {
+        Pcg32 rng; sampler_seed(&rng, seed, (uint32_t)lane);
+        uint32_t px = active_pixels[lane / spp];
+        Ray ray = gen_ray(s, px, &rng);
+        image[px] += radon_lane(s, ray, &rng) * w;
+    }
+    return 0;
+}
+
+/* CornerIntegrator (filter_corner.py:17-66): 1 * weight unless the first hit lies within `radius` of
+ * the vertical edge |x| = |y| = dist of a square vial. */
+int orc_corner(const OrcScene *s, const uint32_t *active_pixels, uint64_t n_active, uint32_t spp, uint32_t seed,
+               double dist, double radius, real *image) {
+    if (s->regular_sampling) spp = 1;
+    real w = ray_weight(s, n_active, spp);
+    size_t n_img = (size_t)s->n_patterns * s->res_x * s->res_y;
+    for (size_t i = 0; i < n_img; ++i) image[i] = 0;
+    for (uint64_t lane = 0; lane < n_active * spp; ++lane) {
+        Pcg32 rng; sampler_seed(&rng, seed, (uint32_t)lane);
+        uint32_t px = active_pixels[lane / spp];
+        Ray ray = gen_ray(s, px, &rng);
+        Hit si = scene_intersect(s, ray);
+        if (!si.valid) continue;
+        real ex = rabs(si.p.x) - (real)dist, ey = rabs(si.p.y) - (real)dist;
+        real nrm = sizeof(real) == 4 ? (real)sqrtf((float)(ex * ex + ey * ey)) : (real)sqrt((double)(ex * ex + ey * ey));
+        if (!(nrm < (real)radius)) image[px] += w;
+    }
+    return 0;
+}
+
 int orc_raygen(const OrcScene *s, const uint32_t *active_pixels, uint64_t n_active, uint32_t spp,
                uint32_t seed, real *out) {
     if (s->regular_sampling) spp = 1;

@@ -70,6 +70,11 @@ def _lib(precision: str):
                                     C.c_void_p, C.c_int]
         lib.orc_raygen.restype = C.c_int
         lib.orc_raygen.argtypes = [C.POINTER(OrcScene), C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_void_p]
+        lib.orc_radon.restype = C.c_int
+        lib.orc_radon.argtypes = [C.POINTER(OrcScene), C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_void_p]
+        lib.orc_corner.restype = C.c_int
+        lib.orc_corner.argtypes = [C.POINTER(OrcScene), C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_double,
+                                   C.c_double, C.c_void_p]
         lib.orc_compute_volume.restype = C.c_int
         lib.orc_compute_volume.argtypes = [C.POINTER(OrcScene), C.c_uint32, C.c_void_p, C.c_int]
         lib.orc_rng_stream.restype = C.c_int
@@ -142,6 +147,21 @@ class Oracle:
                                   out.ctypes.data, self.threads)
         assert rc == 0
         return out
+
+    def radon(self, active_pixels, spp=1, seed=0):
+        """RadonIntegrator.render (integrators/radon.py:13-46): image (n_patterns, res_y, res_x)."""
+        pix = np.ascontiguousarray(active_pixels, np.uint32)
+        img = np.zeros((self.scene.n_patterns, self.scene.res_y, self.scene.res_x), self.real)
+        assert self.lib.orc_radon(C.byref(self.scene), pix.ctypes.data, pix.size, spp, seed, img.ctypes.data) == 0
+        return img
+
+    def corner(self, active_pixels, dist, radius=0.1, spp=1, seed=0):
+        """CornerIntegrator.render (integrators/filter_corner.py:17-66)."""
+        pix = np.ascontiguousarray(active_pixels, np.uint32)
+        img = np.zeros((self.scene.n_patterns, self.scene.res_y, self.scene.res_x), self.real)
+        assert self.lib.orc_corner(C.byref(self.scene), pix.ctypes.data, pix.size, spp, seed, float(dist),
+                                   float(radius), img.ctypes.data) == 0
+        return img
 
     def compute_volume(self, sample_count=2 ** 14):
         """Surface-aware sub-voxel volumes (sensor.py:47-110), shape (rz, ry, rx, 2) = (in, out)."""
