@@ -244,8 +244,10 @@ def main():
     d_host = d_dev.cpu().pin_memory()
     g_host = torch.empty(n_local, dtype=torch.float32).pin_memory()
 
-    def step(seed, p, d, record=False):
-        """One L-BFGS iteration's projections on device-resident inputs."""
+    def step(seed, p, d, record=False, d_ready=None, on_grad=None):
+        """One L-BFGS iteration's projections on device-resident inputs.  `d_ready` (an event) is
+        waited for before A d reads the search direction; `on_grad` sees the pattern gradient as soon
+        as the adjoint is queued (the end-to-end loop uses both to overlap its copies)."""
         p = p.detach().requires_grad_(True)
         scene.projector.active_data = p
         integ.events = pass_events if record else None
@@ -253,7 +255,11 @@ def main():
         vol = dv.render(scene, prm, integrator=integ, sensor=sensor, spp=spp, seed=seed)
         loss = loss_fn(vol, target, p)
         loss.backward()                                     # adjoint A^T g
+        if on_grad is not None:
+            on_grad(p.grad)
         with torch.no_grad():
+            if d_ready is not None:
+                torch.cuda.current_stream(dev).wait_event(d_ready)
             scene.projector.active_data = d
             dvol = dv.render(scene, None, integrator=integ, sensor=sensor, spp=spp, seed=seed)   # A d
             f_new = loss_fn(LazyAxpy(vol.detach(), dvol, 1.0), target, d)                        # Armijo trial
@@ -286,17 +292,34 @@ def main():
     launches = lib.drtvam_launch_count() - launches0
     clock_info = clocks.stop() if clocks else None
 
-    # end to end: host (pinned) inputs copied in and results copied out every step
+    # end to end: host (pinned) inputs copied in and results copied out every step.  The patterns are
+    # uploaded on the compute stream (A p needs all of them); the search direction is uploaded and the
+    # pattern gradient downloaded on a copy stream, under A p / A^T g and under A d respectively.
+    # Every copy of step i is issued and completed inside step i (no prefetch across steps).
     barrier()
+    main_stream = torch.cuda.current_stream(dev)
+    copy_stream = torch.cuda.Stream(dev)
     e0 = torch.cuda.Event(enable_timing=True)
     e1 = torch.cuda.Event(enable_timing=True)
     e0.record()
     loss_host = 0.0
     for i in range(args.steps):
+        copy_stream.wait_stream(main_stream)                 # step i's copies start with step i
         p_in = p_host.to(dev, non_blocking=True)
-        d_in = d_host.to(dev, non_blocking=True)
-        loss, f_new, grad = step(100 + i, p_in, d_in)
-        g_host.copy_(grad, non_blocking=True)
+        d_ready = torch.cuda.Event()
+        with torch.cuda.stream(copy_stream):
+            d_in = d_host.to(dev, non_blocking=True)
+            d_ready.record(copy_stream)
+        d_in.record_stream(main_stream)
+
+        def download(grad):
+            copy_stream.wait_stream(main_stream)             # after the adjoint
+            grad.record_stream(copy_stream)
+            with torch.cuda.stream(copy_stream):
+                g_host.copy_(grad, non_blocking=True)
+
+        loss, f_new, grad = step(100 + i, p_in, d_in, d_ready=d_ready, on_grad=download)
+        main_stream.wait_stream(copy_stream)                 # the gradient is on the host before the step ends
         loss_host = float(loss)                              # D2H of the scalar: syncs the step
     e1.record()
     barrier()

@@ -55,6 +55,7 @@ SYMBOLS = {
     "drtvam_scene_set_depth": (C.c_int, [_vp, _i32, _i32]),
     "drtvam_scene_set_target": (C.c_int, [_vp, _vp, _u32]),
     "drtvam_compute_volume": (C.c_int, [_vp, _u32, _vp, _vp]),
+    "drtvam_discretize": (C.c_int, [_vp, _vp, _vp]),
     "drtvam_scene_set_inv_volume": (C.c_int, [_vp, _vp]),
     "drtvam_scene_plan": (C.c_int, [_vp, _u64, _u32]),
     "drtvam_scene_force_general": (C.c_int, [_vp, _i32]),

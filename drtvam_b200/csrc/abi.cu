@@ -352,6 +352,15 @@ int drtvam_compute_volume(DrtvamScene* s, uint32_t sample_count, float* volumes,
     return DRTVAM_OK;
 }
 
+int drtvam_discretize(DrtvamScene* s, float* voxels, void* stream) {
+    if (!s) return fail(DRTVAM_E_INVALID, "scene handle is NULL");
+    if (!voxels) return fail(DRTVAM_E_INVALID, "NULL buffer");
+    if (s->P.target.n_tri <= 0) return fail(DRTVAM_E_INVALID, "No target shape found in the scene");  // utils.py:95-96
+    DeviceGuard guard(s->device);
+    CUDA_TRY(launch_discretize(s->P, voxels, static_cast<cudaStream_t>(stream)));
+    return DRTVAM_OK;
+}
+
 int drtvam_scene_plan(DrtvamScene* s, uint64_t n_active, uint32_t) {
     if (!s) return fail(DRTVAM_E_INVALID, "scene handle is NULL");
     DeviceGuard guard(s->device);

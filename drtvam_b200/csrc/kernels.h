@@ -134,6 +134,8 @@ cudaError_t mesh_build(const float* tri_host, uint32_t n_tri, MeshHost& H);
 void mesh_release(MeshHost& H);
 // sensor.py:47-110; synchronises the stream (one-off set-up work)
 cudaError_t launch_compute_volume(const SceneParams& P, uint32_t sample_count, float* volumes, cudaStream_t stream);
+// utils.py:83-128: binary occupancy of the target at the voxel centres, voxels[res_z][res_y][res_x].
+cudaError_t launch_discretize(const SceneParams& P, float* voxels, cudaStream_t stream);
 cudaError_t launch_mul_inplace(float* a, const float* b, size_t n, cudaStream_t stream);
 cudaError_t launch_mul(const float* a, const float* b, float* out, size_t n, cudaStream_t stream);
 

@@ -225,6 +225,30 @@ __global__ void mul_kernel(const float* __restrict__ a, const float* __restrict_
     if (i < n) out[i] = a[i] * b[i];
 }
 
+
+// utils.py:83-128 discretize: one ray in a random direction from every voxel centre; the voxel is
+// occupied when the centre lies in the mesh bounding box and the first hit is a back face.  Lane
+// idx of sampler.seed(0, n_voxels) (utils.py:114-115) draws the direction (next_2d).
+__global__ void __launch_bounds__(256)
+discretize_kernel(const __grid_constant__ SceneParams P, float* __restrict__ voxels) {
+    const size_t n_vox = static_cast<size_t>(P.res[0]) * P.res[1] * P.res[2];
+    const size_t idx = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x;
+    if (idx >= n_vox) return;
+    const int x = static_cast<int>(idx % P.res[0]), y = static_cast<int>((idx / P.res[0]) % P.res[1]);
+    const int z = static_cast<int>(idx / (static_cast<size_t>(P.res[0]) * P.res[1]));
+    float vs[3];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) vs[a] = (P.bmax[a] - P.bmin[a]) / static_cast<float>(P.res[a]);
+    Sampler rng;
+    rng.seed(0u, static_cast<uint32_t>(idx));
+    const float u0 = rng.next(), u1 = rng.next();
+    const float cz = 1.f - 2.f * u1, rr = sqrtf(fmaxf(1.f - cz * cz, 0.f));
+    float sp, cp;
+    sincosf(6.28318530717958647692f * u0, &sp, &cp);
+    const bool in = point_inside(P.target, P.bmin[0] + (x + 0.5f) * vs[0], P.bmin[1] + (y + 0.5f) * vs[1],
+                                 P.bmin[2] + (z + 0.5f) * vs[2], rr * cp, rr * sp, cz);
+    voxels[idx] = in ? 1.f : 0.f;
+}
 }  // namespace
 
 void mesh_release(MeshHost& H) {
@@ -304,6 +328,14 @@ cudaError_t launch_compute_volume(const SceneParams& P, uint32_t sample_count, f
     if (list) cudaFree(list);
     if (count) cudaFree(count);
     return e;
+}
+
+cudaError_t launch_discretize(const SceneParams& P, float* voxels, cudaStream_t stream) {
+    const size_t n_vox = static_cast<size_t>(P.res[0]) * P.res[1] * P.res[2];
+    if (n_vox == 0) return cudaSuccess;
+    discretize_kernel<<<static_cast<unsigned>((n_vox + 255) / 256), 256, 0, stream>>>(P, voxels);
+    count_launch();
+    return cudaGetLastError();
 }
 
 cudaError_t launch_mul_inplace(float* a, const float* b, size_t n, cudaStream_t stream) {

@@ -225,31 +225,28 @@ def mesh_inside(points, dirs, verts, tris, chunk=1 << 16):
 
 
 @torch.no_grad()
-def discretize(scene, sensor=0, seed=0):
+def discretize(scene, sensor=0):
     """Binary occupancy grid of the target mesh at the voxel centres: one ray in
-    a random direction per voxel, inside iff the first hit faces away
-    (utils.py:83-128).  Returns (resz, resy, resx, 1)."""
+    a random direction per voxel (lane idx of ``sampler.seed(0, n_voxels)``),
+    inside iff the centre lies in the mesh bounding box and the first hit faces
+    away (utils.py:83-128).  Runs on the device through ``drtvam_discretize``
+    (``csrc/mesh_kernels.cu``, the BVH of the scene's target).  Returns
+    (resz, resy, resx, 1)."""
     if isinstance(sensor, int):
         sensor = scene.sensors()[sensor]
     if scene.target is None:
         raise ValueError("No target shape found in the scene")
-    verts, tris = scene.target["vertices"], scene.target["triangles"]
-    dev = scene.projector.active_data.device
-    rx, ry, rz = sensor.resolution()
-    vs = torch.as_tensor(sensor.voxel_size, dtype=torch.float32, device=dev)
-    bmin = torch.as_tensor(sensor.bbox_min, dtype=torch.float32, device=dev)
-    zz, yy, xx = torch.meshgrid(torch.arange(rz, device=dev), torch.arange(ry, device=dev),
-                                torch.arange(rx, device=dev), indexing="ij")
-    idx = torch.stack([xx, yy, zz], -1).reshape(-1, 3).to(torch.float32)
-    pos = bmin + (0.5 + idx) * vs
-    g = torch.Generator(device="cpu").manual_seed(seed)
-    u = torch.rand(pos.shape[0], 2, generator=g).to(dev)
-    dirs = _uniform_sphere(u[:, 0], u[:, 1])
-    lo = torch.as_tensor(verts.min(0), dtype=torch.float32, device=dev)
-    hi = torch.as_tensor(verts.max(0), dtype=torch.float32, device=dev)
-    in_box = ((pos > lo) & (pos < hi)).all(-1)
-    inside = torch.zeros(pos.shape[0], dtype=torch.bool, device=dev)
-    sel = torch.nonzero(in_box).reshape(-1)
-    if sel.numel():
-        inside[sel] = mesh_inside(pos[sel], dirs[sel], verts, tris)
-    return inside.to(torch.float32).reshape(rz, ry, rx, 1)
+    from . import _lib
+    lib = _lib.load()
+    # a one-off handle with the mesh attached: the optimisation handles only carry it when the run
+    # is surface-aware (optimize.py:188-191 moves it away otherwise)
+    handle = scene.filter_handle(scene.geometry_integrator(), sensor)
+    try:
+        dev = scene.projector.active_data.device
+        rx, ry, rz = sensor.resolution()
+        voxels = torch.empty((rz, ry, rx, 1), device=dev, dtype=torch.float32)
+        _lib.check(lib.drtvam_discretize(handle, voxels.data_ptr(), torch.cuda.current_stream(dev).cuda_stream))
+        torch.cuda.synchronize(dev)
+    finally:
+        lib.drtvam_scene_destroy(handle)
+    return voxels

@@ -128,6 +128,14 @@ int drtvam_scene_set_target(DrtvamScene *scene, const float *triangles_host, uin
  * per-voxel PCG32 streams seeded as sensor.py:83-84.  Synchronises. */
 int drtvam_compute_volume(DrtvamScene *scene, uint32_t sample_count, float *volumes, void *stream);
 
+/* utils.discretize (utils.py:83-128): binary occupancy grid of the target,
+ * voxels[res_z][res_y][res_x] = 1 where a ray from the voxel centre in the
+ * random direction of lane idx of sampler.seed(0, n_voxels) first hits a back
+ * face of the target (and the centre lies in the target's bounding box), else
+ * 0.  The reference for the loss (optimize.py:131-139).  Asynchronous on
+ * `stream`. */
+int drtvam_discretize(DrtvamScene *scene, float *voxels, void *stream);
+
 /* inv_vol of volume.py:41-42,54,130 when it is a tensor (surface-aware): a
  * caller-owned DEVICE array of film size that drtvam_forward multiplies the
  * film by and drtvam_adjoint multiplies dose_grad by.  NULL (default) = the

@@ -880,6 +880,53 @@ int orc_compute_volume(const OrcScene *s, uint32_t sample_count, real *volumes, 
     return 0;
 }
 
+/* utils.py:83-128 discretize: voxels[rz][ry][rx] = 1 where the voxel centre lies in the target's
+ * bounding box and a ray from it, in the direction lane idx of sampler.seed(0, n_voxels) draws
+ * (square_to_uniform_sphere(next_2d), utils.py:114-117), first hits a back face. */
+int orc_discretize(const OrcScene *s, real *voxels, int n_threads) {
+    if (s->n_tri <= 0) return -1;
+    real mbmin[3] = {RINF, RINF, RINF}, mbmax[3] = {-RINF, -RINF, -RINF};
+    for (int i = 0; i < s->n_tri * 3; ++i)
+        for (int a = 0; a < 3; ++a) {
+            real v = (real)s->tri[3 * (size_t)i + a];
+            if (v < mbmin[a]) mbmin[a] = v;
+            if (v > mbmax[a]) mbmax[a] = v;
+        }
+    real bmin[3], vs[3];
+    for (int a = 0; a < 3; ++a) {
+        bmin[a] = (real)s->bbox_min[a];
+        vs[a] = ((real)s->bbox_max[a] - (real)s->bbox_min[a]) / (real)s->res[a];
+    }
+    int64_t n_vox = (int64_t)s->res[0] * s->res[1] * s->res[2];
+#ifdef _OPENMP
+    if (n_threads > 0) omp_set_num_threads(n_threads);
+#pragma omp parallel for schedule(dynamic, 1024)
+#endif
+    for (int64_t idx = 0; idx < n_vox; ++idx) {
+        int x = (int)(idx % s->res[0]), y = (int)((idx / s->res[0]) % s->res[1]), z = (int)(idx / ((int64_t)s->res[0] * s->res[1]));
+        Pcg32 rng; sampler_seed(&rng, 0u, (uint32_t)idx);
+        real u0 = next_1d(&rng), u1 = next_1d(&rng);
+        Ray r;
+        r.o = v3(bmin[0] + vs[0] * ((real)x + (real)0.5), bmin[1] + vs[1] * ((real)y + (real)0.5),
+                 bmin[2] + vs[2] * ((real)z + (real)0.5));
+        real cz = 1 - 2 * u1, rr = safe_sqrt(1 - cz * cz);
+        const real pi = (real)3.14159265358979323846;
+        real phi = 2 * pi * u0;
+        real sp = sizeof(real) == 4 ? (real)sinf((float)phi) : (real)sin((double)phi);
+        real cp = sizeof(real) == 4 ? (real)cosf((float)phi) : (real)cos((double)phi);
+        r.d = v3(rr * cp, rr * sp, cz);
+        int in_bbox = r.o.x > mbmin[0] && r.o.x < mbmax[0] && r.o.y > mbmin[1] && r.o.y < mbmax[1] &&
+                      r.o.z > mbmin[2] && r.o.z < mbmax[2];
+        int inside = 0;
+        if (in_bbox) {
+            V3 n; real t = mesh_intersect(s, r, &n);
+            inside = t < RINF && vdot(r.d, n) > 0;
+        }
+        voxels[idx] = inside ? (real)1 : (real)0;
+    }
+    return 0;
+}
+
 /* first `n` floats of lane `lane`'s stream (RNG unit test). */
 int orc_rng_stream(uint32_t seed, uint32_t lane, int n, float *out) {
     Pcg32 rng; sampler_seed(&rng, seed, lane);

@@ -77,6 +77,8 @@ def _lib(precision: str):
                                    C.c_double, C.c_void_p]
         lib.orc_compute_volume.restype = C.c_int
         lib.orc_compute_volume.argtypes = [C.POINTER(OrcScene), C.c_uint32, C.c_void_p, C.c_int]
+        lib.orc_discretize.restype = C.c_int
+        lib.orc_discretize.argtypes = [C.POINTER(OrcScene), C.c_void_p, C.c_int]
         lib.orc_rng_stream.restype = C.c_int
         lib.orc_rng_stream.argtypes = [C.c_uint32, C.c_uint32, C.c_int, C.c_void_p]
         assert lib.orc_sizeof_real() == C.sizeof(real)
@@ -169,6 +171,14 @@ class Oracle:
         out = np.zeros((rz, ry, rx, 2), self.real)
         rc = self.lib.orc_compute_volume(C.byref(self.scene), int(sample_count), out.ctypes.data, self.threads)
         assert rc == 0, "compute_volume needs a target mesh"
+        return out
+
+    def discretize(self):
+        """Binary occupancy of the target at the voxel centres (utils.py:83-128), shape (rz, ry, rx, 1)."""
+        rz, ry, rx, _ = self.film_shape
+        out = np.zeros((rz, ry, rx, 1), self.real)
+        rc = self.lib.orc_discretize(C.byref(self.scene), out.ctypes.data, self.threads)
+        assert rc == 0, "discretize needs a target mesh"
         return out
 
     def raygen(self, active_pixels, spp=1, seed=0):
