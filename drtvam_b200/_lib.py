@@ -11,7 +11,7 @@ import os
 from . import build as _build
 
 MAX_SURFACES = 8
-ABI_VERSION = 6
+ABI_VERSION = 7
 
 
 class DrtvamSurface(C.Structure):
@@ -54,6 +54,7 @@ SYMBOLS = {
     "drtvam_scene_destroy": (None, [_vp]),
     "drtvam_scene_set_depth": (C.c_int, [_vp, _i32, _i32]),
     "drtvam_scene_set_target": (C.c_int, [_vp, _vp, _u32]),
+    "drtvam_scene_add_mesh_surface": (C.c_int, [_vp, _vp, _u32, C.c_int32, C.c_float, C.c_int32, C.c_int32]),
     "drtvam_compute_volume": (C.c_int, [_vp, _u32, _vp, _vp]),
     "drtvam_discretize": (C.c_int, [_vp, _vp, _vp]),
     "drtvam_scene_set_inv_volume": (C.c_int, [_vp, _vp]),

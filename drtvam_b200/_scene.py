@@ -12,7 +12,7 @@ import numpy as np
 
 from . import _lib
 
-SURF_CYLINDER, SURF_BOX = 0, 1
+SURF_CYLINDER, SURF_BOX, SURF_MESH = 0, 1, 2
 BSDF_NULL, BSDF_DIELECTRIC, BSDF_ABSORBER = 0, 1, 2
 PROJ_KINDS = {"collimated": 0, "telecentric": 1, "lens": 2}
 PHASE_KINDS = {"isotropic": 0, "rayleigh": 1, "hg": 2}
@@ -54,6 +54,9 @@ class SurfaceDesc:
     hz: float = 0.0
     eta: float = 1.0
     name: str = ""
+    # SURF_MESH: [n_tri, 3, 3] float32 world-space vertices (uploaded with
+    # drtvam_scene_add_mesh_surface, not part of the C struct)
+    triangles: object = None
 
 
 @dataclass
@@ -112,8 +115,13 @@ class SceneDesc:
         d = asdict(self)
         self.target_triangles = tri
         d["target_triangles"] = tri
-        d["surfaces"] = [asdict(s) for s in self.surfaces]
+        d["surfaces"] = [asdict(s) for s in self.ordered_surfaces()]
         return d
+
+    def ordered_surfaces(self):
+        """Closed-form surfaces first, then the meshes: the order they have on the device (the
+        meshes are appended to the handle after drtvam_scene_create)."""
+        return [s for s in self.surfaces if s.kind != SURF_MESH] + [s for s in self.surfaces if s.kind == SURF_MESH]
 
     def to_c(self):
         """Returns (DrtvamSceneDesc, keepalive) for drtvam_scene_create."""
@@ -132,8 +140,9 @@ class SceneDesc:
             tab = np.ascontiguousarray(np.asarray(self.motion_table, np.float64)[:, :3, :].astype(np.float32))
             keep = tab
             d.motion_table_host = tab.ctypes.data_as(C.POINTER(C.c_float))
-        d.n_surf = len(self.surfaces)
-        for i, s in enumerate(self.surfaces):
+        closed = [s for s in self.surfaces if s.kind != SURF_MESH]
+        d.n_surf = len(closed)
+        for i, s in enumerate(closed):
             c = d.surf[i]
             for k in ("kind", "bsdf", "interior_medium", "exterior_medium", "radius", "z0", "z1", "hx", "hy", "hz",
                       "eta"):
@@ -194,6 +203,41 @@ def surface_from_shape_dict(name: str, sd: dict) -> SurfaceDesc:
             raise NotImplementedError("only origin-centred axis-aligned boxes have a closed-form kernel")
         s.kind = SURF_BOX
         s.hx, s.hy, s.hz = float(m[0, 0]), float(m[1, 1]), float(m[2, 2])
+    elif t in ("ply", "obj"):
+        # custom vial walls (geometry.py:113-134) and occluders (geometry.py:55-72): a triangle
+        # soup with face normals, walked through a BVH on the device
+        from .transform import Transform4f
+        from .utils import load_mesh
+        verts, tris = load_mesh(sd["filename"])
+        tw = sd.get("to_world")
+        if tw is not None:
+            verts = Transform4f(tw) @ verts
+        s.kind = SURF_MESH
+        s.triangles = np.ascontiguousarray(np.asarray(verts, np.float64)[np.asarray(tris)].astype(np.float32))
     else:
-        raise NotImplementedError(f"shape type '{t}' has no closed-form interface kernel (mesh vials are a later row)")
+        raise NotImplementedError(f"shape type '{t}' is not supported")
     return s
+
+
+def create_handle(desc: SceneDesc, device_index: int, target_triangles=None):
+    """drtvam_scene_create + the mesh interfaces + (optionally) the target mesh.  Returns
+    (handle, keepalive); the caller destroys the handle."""
+    lib = _lib.load()
+    cdesc, keep = desc.to_c()
+    out = C.c_void_p()
+    _lib.check(lib.drtvam_scene_create(C.byref(cdesc), device_index, C.byref(out)))
+    h = out.value
+    try:
+        for s in desc.ordered_surfaces():
+            if s.kind != SURF_MESH:
+                continue
+            tri = np.ascontiguousarray(s.triangles, np.float32)
+            _lib.check(lib.drtvam_scene_add_mesh_surface(h, tri.ctypes.data, tri.shape[0], int(s.bsdf), float(s.eta),
+                                                         int(s.interior_medium), int(s.exterior_medium)))
+        if target_triangles is not None:
+            tri = np.ascontiguousarray(target_triangles, np.float32)
+            _lib.check(lib.drtvam_scene_set_target(h, tri.ctypes.data, tri.shape[0]))
+    except Exception:
+        lib.drtvam_scene_destroy(h)
+        raise
+    return h, keep

@@ -68,6 +68,8 @@ struct DrtvamScene {
     bool planar_tried = false;       // planar_build ran for the current depth setting
     bool planar_ok = false;
     MeshHost target;                 // target mesh (surface-aware runs only)
+    MeshHost mesh_surf[kMaxMeshSurfaces];  // triangle-mesh interfaces (custom vial walls, occluders)
+    int n_mesh_surf = 0;
     const float* inv_volume = nullptr;  // caller-owned [film_elems] 1/sub-voxel volume (volume.py:41-42), or NULL
     Scratch dl_scaled;               // grad_in * inv_vol of the adjoint
     Scratch host_io[3];      // device staging for the *_host calls
@@ -95,6 +97,11 @@ int check_call(const DrtvamScene* s, uint64_t n_active, uint32_t& spp) {
     if (!s) return fail(DRTVAM_E_INVALID, "scene handle is NULL");
     if (spp == 0) return fail(DRTVAM_E_INVALID, "spp must be >= 1");
     if (s->P.regular_sampling) spp = 1;  // integrators/common.py:49-51
+    int medium_surfaces = 0;
+    for (int i = 0; i < s->P.n_surf; ++i)
+        medium_surfaces += (s->P.surf[i].interior_medium != 0) + (s->P.surf[i].exterior_medium != 0);
+    if (medium_surfaces == 0)
+        return fail(DRTVAM_E_INVALID, "No printing medium found in the scene");  // common.py:36-37
     const unsigned __int128 lanes = static_cast<unsigned __int128>(n_active) * spp;
     if (lanes > (static_cast<unsigned __int128>(1) << 32))
         return fail(DRTVAM_E_TOO_MANY_RAYS,
@@ -129,6 +136,7 @@ bool planar_static_eligible(const DrtvamScene* s) {
     float zmax = fmaxf(fabsf(P.bmin[2]), fabsf(P.bmax[2]));
     for (int i = 0; i < P.n_surf; ++i) {
         const Surface& S = P.surf[i];
+        if (S.kind == DRTVAM_SURF_MESH) return false;  // arbitrary interface: general tracer
         if (S.kind == DRTVAM_SURF_CYLINDER) {
             if (!(S.z0 < P.bmin[2] && S.z1 > P.bmax[2])) return false;
             // spawn offset (1 + max|p|) eps must not depend on z
@@ -211,8 +219,9 @@ int drtvam_scene_create(const DrtvamSceneDesc* d, int device, DrtvamScene** out)
     if (d->proj_kind < 0 || d->proj_kind > 2) return fail(DRTVAM_E_INVALID, "unknown projector kind %d", d->proj_kind);
     if (d->n_patterns <= 0 || d->res_x <= 0 || d->res_y <= 0)
         return fail(DRTVAM_E_INVALID, "projector size must be positive");
-    if (d->n_surf <= 0 || d->n_surf > DRTVAM_MAX_SURFACES)
-        return fail(DRTVAM_E_INVALID, "surface count %d outside [1, %d]", d->n_surf, DRTVAM_MAX_SURFACES);
+    // n_surf = 0: every interface is a mesh added afterwards (custom vial)
+    if (d->n_surf < 0 || d->n_surf > DRTVAM_MAX_SURFACES)
+        return fail(DRTVAM_E_INVALID, "surface count %d outside [0, %d]", d->n_surf, DRTVAM_MAX_SURFACES);
     if (!(d->sigma_t > 0.f)) return fail(DRTVAM_E_INVALID, "medium extinction must be positive");
     if (d->albedo < 0.f || d->albedo > 1.f) return fail(DRTVAM_E_INVALID, "albedo outside [0, 1]");
     if (d->sensor_kind != DRTVAM_SENSOR_DDA && d->sensor_kind != DRTVAM_SENSOR_RATIO &&
@@ -237,7 +246,7 @@ int drtvam_scene_create(const DrtvamSceneDesc* d, int device, DrtvamScene** out)
             return fail(DRTVAM_E_INVALID, "surface %d: dielectric needs eta > 0", i);
         medium_surfaces += (s.interior_medium != 0) + (s.exterior_medium != 0);
     }
-    if (medium_surfaces == 0)
+    if (medium_surfaces == 0 && d->n_surf > 0)
         return fail(DRTVAM_E_INVALID, "No printing medium found in the scene");  // common.py:36-37
     for (int a = 0; a < 3; ++a) {
         if (d->res[a] <= 0) return fail(DRTVAM_E_INVALID, "film resolution must be positive");
@@ -271,6 +280,7 @@ int drtvam_scene_create(const DrtvamSceneDesc* d, int device, DrtvamScene** out)
         Surface& b = P.surf[i];
         b.kind = a.kind; b.bsdf = a.bsdf; b.interior_medium = a.interior_medium; b.exterior_medium = a.exterior_medium;
         b.radius = a.radius; b.z0 = a.z0; b.z1 = a.z1; b.hx = a.hx; b.hy = a.hy; b.hz = a.hz; b.eta = a.eta;
+        b.mesh = -1;
     }
     for (int a = 0; a < 3; ++a) { P.bmin[a] = d->bbox_min[a]; P.bmax[a] = d->bbox_max[a]; P.res[a] = d->res[a]; }
     P.surface_aware = d->surface_aware; P.sensor_kind = d->sensor_kind; P.majorant = d->majorant;
@@ -305,6 +315,7 @@ void drtvam_scene_destroy(DrtvamScene* s) {
     planarg_release(s->gplan);
     inside_release(s->inside);
     mesh_release(s->target);
+    for (auto& m : s->mesh_surf) mesh_release(m);
     s->dl_scaled.release();
     for (auto& b : s->host_io) b.release();
     delete s;
@@ -333,6 +344,32 @@ int drtvam_scene_set_target(DrtvamScene* s, const float* triangles_host, uint32_
     CUDA_TRY(cudaDeviceSynchronize());
     CUDA_TRY(mesh_build(triangles_host, n_triangles, s->target));
     s->P.target = s->target.view;
+    s->planar_tried = false;
+    return DRTVAM_OK;
+}
+
+int drtvam_scene_add_mesh_surface(DrtvamScene* s, const float* triangles_host, uint32_t n_triangles, int32_t bsdf,
+                                  float eta, int32_t interior_medium, int32_t exterior_medium) {
+    if (!s) return fail(DRTVAM_E_INVALID, "scene handle is NULL");
+    if (!triangles_host || n_triangles == 0) return fail(DRTVAM_E_INVALID, "empty triangle buffer");
+    if (n_triangles > (1u << 28)) return fail(DRTVAM_E_INVALID, "too many triangles");
+    if (bsdf < 0 || bsdf > 2) return fail(DRTVAM_E_INVALID, "unknown bsdf %d", bsdf);
+    if (bsdf == DRTVAM_BSDF_DIELECTRIC && !(eta > 0.f)) return fail(DRTVAM_E_INVALID, "dielectric needs eta > 0");
+    if (s->n_mesh_surf >= kMaxMeshSurfaces || s->P.n_surf >= kMaxSurfaces)
+        return fail(DRTVAM_E_INVALID, "too many surfaces (%d of %d, %d of %d meshes)", s->P.n_surf, kMaxSurfaces,
+                    s->n_mesh_surf, kMaxMeshSurfaces);
+    DeviceGuard guard(s->device);
+    CUDA_TRY(cudaDeviceSynchronize());
+    const int m = s->n_mesh_surf;
+    CUDA_TRY(mesh_build(triangles_host, n_triangles, s->mesh_surf[m]));
+    s->P.mesh_surf[m] = s->mesh_surf[m].view;
+    Surface& b = s->P.surf[s->P.n_surf];
+    b = Surface{};
+    b.kind = DRTVAM_SURF_MESH; b.bsdf = bsdf; b.interior_medium = interior_medium; b.exterior_medium = exterior_medium;
+    b.eta = bsdf == DRTVAM_BSDF_DIELECTRIC ? eta : 1.f;
+    b.mesh = m;
+    s->n_mesh_surf = m + 1;
+    s->P.n_surf += 1;
     s->planar_tried = false;
     return DRTVAM_OK;
 }

@@ -9,15 +9,17 @@
 namespace drtvam {
 
 constexpr int kMaxSurfaces = 8;
+constexpr int kMaxMeshSurfaces = 4;
 
 struct Surface {
-    int kind;             // 0 cylinder about z, 1 origin-centred box
+    int kind;             // 0 cylinder about z, 1 origin-centred box, 2 triangle mesh (mesh_surf[mesh])
     int bsdf;             // 0 null, 1 dielectric, 2 absorber
     int interior_medium;  // printing medium inside
     int exterior_medium;  // printing medium outside
     float radius, z0, z1;
     float hx, hy, hz;
     float eta;            // int_ior / ext_ior
+    int mesh;             // kind 2: index into SceneParams::mesh_surf
 };
 
 struct SceneParams {
@@ -37,6 +39,8 @@ struct SceneParams {
     // surfaces
     int n_surf;
     Surface surf[kMaxSurfaces];
+    // triangle-mesh interfaces: custom vials (geometry.py:98-138) and occluders (geometry.py:55-72)
+    MeshView mesh_surf[kMaxMeshSurfaces];
     // sensor / film
     float bmin[3], bmax[3];
     int res[3];

@@ -3,7 +3,8 @@
 // Replaces scene.ray_intersect / si.bsdf().sample / si.spawn_ray of the
 // reference loop (integrators/volume.py:191,230-247) for the vials of
 // geometry.py:82-96 (index matched), :152-183 (cylindrical), :195-219 (square),
-// :257-308 (double cylindrical).
+// :257-308 (double cylindrical); triangle-mesh interfaces (custom vials :98-138,
+// occluders :55-72) go through the flat BVH of mesh.cuh.
 #pragma once
 #include "device_scene.cuh"
 
@@ -93,7 +94,10 @@ __device__ __forceinline__ SurfaceHit nearest_surface(const SceneParams& P, cons
     for (int i = 0; i < P.n_surf; ++i) {
         const Surface& S = P.surf[i];
         float nx = 0.f, ny = 0.f, nz = 1.f;
-        const float t = (S.kind == 0) ? hit_cylinder(S, r) : hit_box(S, r, nx, ny, nz);
+        float t;
+        if (S.kind == 0) t = hit_cylinder(S, r);
+        else if (S.kind == 1) t = hit_box(S, r, nx, ny, nz);
+        else t = mesh_nearest(P.mesh_surf[S.mesh], r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, H.t, nx, ny, nz);  // face normals
         if (t < H.t) {
             H.t = t; H.shape = i;
             H.nx = nx; H.ny = ny; H.nz = nz;

@@ -19,7 +19,8 @@ import numpy as np
 import torch
 
 from . import _lib
-from ._scene import (PHASE_KINDS, PROJ_KINDS, SENSOR_KINDS, SceneDesc, SurfaceDesc, surface_from_shape_dict)
+from ._scene import (PHASE_KINDS, PROJ_KINDS, SENSOR_KINDS, SceneDesc, SurfaceDesc, create_handle,
+                     surface_from_shape_dict)
 from .integrators import integrators as _integrators
 from .motion import CircularMotion
 from .projector import TVAMProjector, projectors
@@ -137,16 +138,10 @@ class Scene:
         h = self._handles.get(key)
         if h is None:
             desc = self.describe(integrator, sensor)
-            cdesc, keep = desc.to_c()
-            out = C.c_void_p()
             dev = self.projector.active_data.device
             if dev.type != 'cuda':
                 raise RuntimeError("drtvam_b200 has no CPU path: scene tensors must live on a CUDA device")
-            _lib.check(lib.drtvam_scene_create(C.byref(cdesc), dev.index or 0, C.byref(out)))
-            h = out.value
-            if desc.target_triangles is not None:
-                tri = desc.target_triangles
-                _lib.check(lib.drtvam_scene_set_target(h, tri.ctypes.data, tri.shape[0]))
+            h, keep = create_handle(desc, dev.index or 0, desc.target_triangles)
             self._handles[key] = h
             self._keepalive[key] = keep
         _lib.check(lib.drtvam_scene_set_depth(h, int(integrator.max_depth), int(integrator.rr_depth)))
@@ -157,22 +152,12 @@ class Scene:
         """One-off C handle for the pixel pre-filters (optimize.py:143-185): they run before the target
         is moved away (optimize.py:188-191), so the mesh is attached whether or not the run is
         surface-aware.  The caller destroys it."""
-        lib = _lib.load()
         desc = self.describe(integrator, sensor)
-        cdesc, keep = desc.to_c()
-        out = C.c_void_p()
         dev = self.projector.active_data.device
         if dev.type != 'cuda':
             raise RuntimeError("drtvam_b200 has no CPU path: scene tensors must live on a CUDA device")
-        _lib.check(lib.drtvam_scene_create(C.byref(cdesc), dev.index or 0, C.byref(out)))
-        tri = self.all_target_triangles()
-        if tri is not None:
-            try:
-                _lib.check(lib.drtvam_scene_set_target(out.value, tri.ctypes.data, tri.shape[0]))
-            except Exception:
-                lib.drtvam_scene_destroy(out.value)
-                raise
-        return out.value
+        h, _ = create_handle(desc, dev.index or 0, self.all_target_triangles())
+        return h
 
     def geometry_integrator(self):
         """Integrator options for calls that only need the geometry (compute_volume)."""
@@ -298,7 +283,10 @@ def load_dict(scene_dict: dict, device=None) -> Scene:
                 medium = inline
             surfaces.append(surface_from_shape_dict(name, entry))
         elif t in ('ply', 'obj'):
-            if name == 'target':
+            if name != 'target':
+                # custom vial wall or occluder (geometry.py:55-72,113-134)
+                surfaces.append(surface_from_shape_dict(name, entry))
+            elif name == 'target':
                 from .utils import load_mesh
                 from .transform import Transform4f
                 verts, tris = load_mesh(entry['filename'])
@@ -306,9 +294,6 @@ def load_dict(scene_dict: dict, device=None) -> Scene:
                 if tw is not None:
                     verts = Transform4f(tw) @ verts
                 target = dict(entry, vertices=np.asarray(verts, np.float64), triangles=tris)
-            else:
-                raise NotImplementedError(
-                    f"shape '{name}' is a triangle mesh; mesh vials / occluders need the BVH row (SURVEY.md 8(f))")
         else:
             raise NotImplementedError(f"scene entry '{name}' of type '{t}' is not supported")
     if projector is None:

@@ -33,8 +33,9 @@
 extern "C" {
 #endif
 
-#define DRTVAM_ABI_VERSION 6
+#define DRTVAM_ABI_VERSION 7
 #define DRTVAM_MAX_SURFACES 8
+#define DRTVAM_MAX_MESH_SURFACES 4
 
 #define DRTVAM_OK 0
 #define DRTVAM_E_INVALID -1      /* bad argument / unsupported configuration */
@@ -44,6 +45,7 @@ extern "C" {
 /* surface kinds / bsdf kinds */
 #define DRTVAM_SURF_CYLINDER 0   /* open tube about the z axis: geometry.py:85-89,157-160 */
 #define DRTVAM_SURF_BOX 1        /* origin-centred axis-aligned box: geometry.py:198-208 */
+#define DRTVAM_SURF_MESH 2       /* triangle mesh added with drtvam_scene_add_mesh_surface: geometry.py:55-72,113-134 */
 #define DRTVAM_BSDF_NULL 0       /* geometry.py:90 */
 #define DRTVAM_BSDF_DIELECTRIC 1 /* geometry.py:161-165,172-176,201-204,209-213 */
 #define DRTVAM_BSDF_ABSORBER 2   /* diffuse occluder, no transmission lobe: geometry.py:57-63 */
@@ -112,6 +114,19 @@ void drtvam_scene_destroy(DrtvamScene *scene);
 /* integrator.max_depth = ... (optimize.py:288-289) and the *_ref integrator
  * (optimize.py:231-238) without rebuilding the scene. */
 int drtvam_scene_set_depth(DrtvamScene *scene, int32_t max_depth, int32_t rr_depth);
+
+/* A triangle-mesh interface of the traced scene: the 'ply' shapes of a custom
+ * vial (CustomVial.to_dict, geometry.py:113-134: dielectric outer / inner wall,
+ * face normals) and the occluders of Container.add_occlusions
+ * (geometry.py:55-72: by default a black diffuse BSDF, i.e. an absorber, whose
+ * exterior is the printing medium).  n_triangles x 9 floats (three world-space
+ * vertices each, counter-clockwise seen from outside) in HOST memory.  The
+ * surface is appended after the closed-form ones of the scene description (at
+ * most DRTVAM_MAX_SURFACES in total, DRTVAM_MAX_MESH_SURFACES meshes); scenes
+ * with a mesh interface run on the general tracer.  Builds a BVH; synchronises
+ * the device. */
+int drtvam_scene_add_mesh_surface(DrtvamScene *scene, const float *triangles_host, uint32_t n_triangles,
+                                  int32_t bsdf, float eta, int32_t interior_medium, int32_t exterior_medium);
 
 /* Target mesh of a surface-aware run: the shape 'target' of optimize.py:66-73
  * (null BSDF), n_triangles x 9 floats (three world-space vertices each) in HOST

@@ -43,13 +43,18 @@ typedef ORC_REAL real;
 /* ------------------------------------------------------------------ scene */
 
 typedef struct {
-    int32_t kind;            /* 0 cylinder (axis = z through origin), 1 axis-aligned box centred at 0 */
+    int32_t kind;            /* 0 cylinder (axis = z through origin), 1 axis-aligned box centred at 0,
+                              * 2 triangle mesh with face normals (custom vial walls geometry.py:113-134,
+                              * occluders geometry.py:55-72) */
     int32_t bsdf;            /* 0 null, 1 dielectric, 2 absorber (diffuse occluder: no transmission lobe) */
     int32_t interior_medium; /* shape.interior_medium() is the printing medium */
     int32_t exterior_medium; /* shape.exterior_medium() is the printing medium */
     double radius, z0, z1;   /* cylinder: geometry.py:85-89,157-160,168-171 */
     double hx, hy, hz;       /* box half extents: geometry.py:200,208 */
     double eta;              /* int_ior / ext_ior (Mitsuba dielectric m_eta) */
+    int32_t n_tri;           /* kind 2: world-space triangles, 9 doubles each */
+    int32_t _pad_tri;
+    const double *tri;
 } OrcSurface;
 
 typedef struct {
@@ -332,14 +337,27 @@ static real mesh_intersect(const OrcScene *s, Ray r, V3 *n) {
     return best;
 }
 
+/* nearest hit on a mesh interface (brute force over its triangles), geometric face normal */
+static real surface_mesh_intersect(const OrcSurface *sf, Ray r, V3 *n) {
+    real best = RINF;
+    for (int i = 0; i < sf->n_tri; ++i) {
+        V3 ng; real t = isect_triangle(sf->tri + 9 * (size_t)i, r, &ng);
+        if (t < best) { best = t; *n = ng; }
+    }
+    if (best < RINF) *n = vnorm(*n);
+    return best;
+}
+
 /* scene.ray_intersect (volume.py:191): nearest hit over the vial surfaces and the target mesh. */
 static Hit scene_intersect(const OrcScene *s, Ray r) {
     Hit h; h.valid = 0; h.shape = -1; h.t = RINF; h.p = v3(0, 0, 0); h.n = v3(0, 0, 1);
     for (int i = 0; i < s->n_surf; ++i) {
         const OrcSurface *sf = &s->surf[i];
         V3 n = v3(0, 0, 1); real t;
-        if (sf->kind == 0) t = isect_cylinder(sf, r); else t = isect_box(sf, r, &n);
-        if (t < h.t) { h.t = t; h.shape = i; h.valid = 1; if (sf->kind == 1) h.n = n; }
+        if (sf->kind == 0) t = isect_cylinder(sf, r);
+        else if (sf->kind == 1) t = isect_box(sf, r, &n);
+        else t = surface_mesh_intersect(sf, r, &n);
+        if (t < h.t) { h.t = t; h.shape = i; h.valid = 1; if (sf->kind != 0) h.n = n; }
     }
     if (s->n_tri > 0) {
         V3 n = v3(0, 0, 1); real t = mesh_intersect(s, r, &n);

@@ -21,7 +21,8 @@ MAX_SURF = 8
 class OrcSurface(C.Structure):
     _fields_ = [("kind", C.c_int32), ("bsdf", C.c_int32), ("interior_medium", C.c_int32),
                 ("exterior_medium", C.c_int32), ("radius", C.c_double), ("z0", C.c_double), ("z1", C.c_double),
-                ("hx", C.c_double), ("hy", C.c_double), ("hz", C.c_double), ("eta", C.c_double)]
+                ("hx", C.c_double), ("hy", C.c_double), ("hz", C.c_double), ("eta", C.c_double),
+                ("n_tri", C.c_int32), ("_pad_tri", C.c_int32), ("tri", C.POINTER(C.c_double))]
 
 
 class OrcScene(C.Structure):
@@ -108,10 +109,16 @@ class Oracle:
             s.motion_table = self._table.ctypes.data_as(C.POINTER(C.c_double))
         surfs = desc["surfaces"]
         s.n_surf = len(surfs)
+        self._surf_tri = []
         for i, sd in enumerate(surfs):
             for k in ("kind", "bsdf", "interior_medium", "exterior_medium", "radius", "z0", "z1", "hx", "hy", "hz",
                       "eta"):
                 setattr(s.surf[i], k, sd[k])
+            if sd["kind"] == 2:  # mesh interface: [n_tri][3][3] world-space vertices
+                tri = np.ascontiguousarray(np.asarray(sd["triangles"], np.float64).reshape(-1, 9))
+                self._surf_tri.append(tri)
+                s.surf[i].n_tri = tri.shape[0]
+                s.surf[i].tri = tri.ctypes.data_as(C.POINTER(C.c_double))
         for a in range(3):
             s.bbox_min[a] = desc["bbox_min"][a]
             s.bbox_max[a] = desc["bbox_max"][a]
