@@ -24,6 +24,17 @@ def cube_mesh(side=1.0):
     return v, np.asarray(tris)
 
 
+def box_mesh(sx, sy, sz, caps=True):
+    """Axis-aligned box centred on the origin, outward-facing; `caps=False` leaves the +-z faces out
+    (the open cuvette walls of tests/files/cuvette_*.ply)."""
+    v, t = cube_mesh(1.0)
+    v = v * np.array([sx, sy, sz], np.float64)
+    if not caps:
+        n = np.cross(v[t[:, 1]] - v[t[:, 0]], v[t[:, 2]] - v[t[:, 0]])
+        t = t[np.abs(n[:, 2]) < 1e-12 * np.abs(n).max()]
+    return v, t
+
+
 def box_hole_mesh(sx=80.0, sy=80.0, sz=40.0, hole_r=20.0, hole_cx=-10.0, hole_cy=0.0, segments=48):
     """Box [-sx/2,sx/2]x[-sy/2,sy/2]x[-sz/2,sz/2] with a through hole along z
     (outward-facing, watertight).  Defaults reproduce the analytic reference

@@ -18,7 +18,7 @@ import oracle as orc
 from drtvam_b200.optimize import load_scene, optimize
 from drtvam_b200.integrators import VolumeIntegrator
 from drtvam_b200.scene import load_dict
-from drtvam_b200.synthetic import box_hole_mesh
+from drtvam_b200.synthetic import box_hole_mesh, box_mesh
 from drtvam_b200.utils import write_ply
 
 PROJECTOR = {"type": "collimated", "n_patterns": 200, "resx": 200, "resy": 20, "pixel_size": 0.05,
@@ -53,16 +53,57 @@ FIXTURES = {
 }
 
 
+# fixtures with triangle-mesh interfaces (an occluder inside a square vial; a custom cuvette made of
+# two open boxes seen through a telecentric projector): tests/files/box_hole_occlusion.json,
+# box_hole_occlusion_filter_radon.json, box_hole_custom_cuvette.json
+MESH_FIXTURES = {
+    "box_hole_occlusion": {
+        "vial": {"type": "square", "w_int": 7.191, "w_ext": 7.6, "ior": 1.3,
+                 "medium": {"ior": 1.15, "phase": RAYLEIGH, "extinction": 0.06, "albedo": 0.0},
+                 "occlusions": [{"filename": "occlusion.ply"}]},
+        "loss": {"type": "threshold", "tl": 0.9, "tu": 0.97}},
+    "box_hole_custom_cuvette": {
+        "vial": {"type": "custom", "filename_vial_outer": "cuvette_outer.ply",
+                 "filename_vial_inner": "cuvette_inner.ply", "ior": 1.4702,
+                 "medium": {"ior": 1.33, "phase": RAYLEIGH, "extinction": 0.06, "albedo": 0.0}},
+        "projector": {"type": "telecentric", "n_patterns": 200, "resx": 200, "resy": 20, "pixel_size": 0.05,
+                      "motion": "circular", "distance": 20, "focus_distance": 20, "aperture_radius": 0.01},
+        "loss": {"type": "threshold", "tl": 0.9, "tu": 0.97}, "n_steps": 35},
+}
+MESH_FIXTURES["box_hole_occlusion_filter_radon"] = dict(copy.deepcopy(MESH_FIXTURES["box_hole_occlusion"]),
+                                                        filter_radon=True)
+FIXTURES_ALL = {**FIXTURES, **MESH_FIXTURES}
+
+
+def write_fixture_meshes(workdir):
+    """The shapes of tests/files/{occlusion,cuvette_outer,cuvette_inner}.ply, regenerated: a closed
+    2 x 1 x 0.5 box, and two open (no +-z faces) boxes 7.53 x 7.42 x 10 and 5 x 4.82 x 10."""
+    for name, size, caps in (("occlusion.ply", (2.0, 1.0, 0.5), True),
+                             ("cuvette_outer.ply", (7.53, 7.42, 10.0), False),
+                             ("cuvette_inner.ply", (5.0, 4.82, 10.0), False)):
+        path = os.path.join(workdir, name)
+        if not os.path.exists(path):
+            v, t = box_mesh(*size, caps=caps)
+            write_ply(path, v, t)
+
+
 def fixture_config(name, workdir):
     target = os.path.join(workdir, "box_hole_fixture.ply")
     if not os.path.exists(target):
         # box 40 x 40 x 10, hole r = 10 centred at (-10, 0): the shape of tests/files/box_hole.ply
         v, t = box_hole_mesh(sx=40.0, sy=40.0, sz=10.0, hole_r=10.0, hole_cx=-10.0, hole_cy=0.0)
         write_ply(target, v, t)
+    write_fixture_meshes(workdir)
     cfg = {"projector": copy.deepcopy(PROJECTOR), "sensor": copy.deepcopy(SENSOR),
            "target": {"filename": target, "size": 4.0}, "progressive": True, "n_steps": 30,
            "output": os.path.join(workdir, "out_" + name), "save_pattern_images": False}
-    cfg.update(copy.deepcopy(FIXTURES[name]))
+    cfg.update(copy.deepcopy(FIXTURES_ALL[name]))
+    vial = cfg["vial"]
+    for key in ("filename_vial_outer", "filename_vial_inner"):
+        if key in vial:
+            vial[key] = os.path.join(workdir, vial[key])
+    for occ in vial.get("occlusions", []):
+        occ["filename"] = os.path.join(workdir, occ["filename"])
     return cfg
 
 
@@ -131,3 +172,29 @@ def test_square_hole_optimization(name, workdir):
     assert percentage_correct > (99.0 if name == "box_hole_scattering" else 99.4)
     loss = np.load(os.path.join(cfg["output"], "loss.npy"))
     assert loss[-1] < loss[0]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["box_hole_occlusion", "box_hole_occlusion_filter_radon"])
+def test_square_hole_occlusion_optimization(name, workdir):
+    """tests/test_optimization.py:43-99: an absorbing box inside the vial shadows part of the target."""
+    cfg = fixture_config(name, workdir)
+    vol_final = optimize(cfg, progress=False).cpu().numpy()
+    occlusion = np.zeros((50, 100, 100))
+    occlusion[15:35, 40:60, 30:70] = 1
+    reference = (analytic_reference() - occlusion) > 0
+    thr = (cfg["loss"]["tl"] + cfg["loss"]["tu"]) / 2
+    percentage_correct = np.mean(np.isclose(reference, vol_final[:, :, :, 0] > thr)) * 100
+    print(name, percentage_correct)
+    assert percentage_correct > 97.0
+
+
+@pytest.mark.gpu
+def test_custom_cuvette_optimization(workdir):
+    """tests/test_optimization.py:104-151, fixture box_hole_custom_cuvette.json (threshold 99.0)."""
+    cfg = fixture_config("box_hole_custom_cuvette", workdir)
+    vol_final = optimize(cfg, progress=False).cpu().numpy()
+    thr = (cfg["loss"]["tl"] + cfg["loss"]["tu"]) / 2
+    percentage_correct = np.mean(np.isclose(analytic_reference(), vol_final[:, :, :, 0] > thr)) * 100
+    print("box_hole_custom_cuvette", percentage_correct)
+    assert percentage_correct > 99.0
