@@ -21,6 +21,7 @@
 // Reference: DDAVolumetricSensor.accumulate (sensor.py:306-440), film.write
 // (film.py:40-41), VolumeIntegrator.render / render_backward
 // (integrators/volume.py:18-56, 97-134).
+#include <type_traits>
 #include <algorithm>
 #include <climits>
 #include <cmath>
@@ -653,6 +654,26 @@ __device__ __forceinline__ void bulk_g2s(void* smem, const void* gmem, uint32_t 
                  : "memory");
 }
 
+// packed fp32 pairs (Blackwell FFMA2)
+__device__ __forceinline__ uint64_t pack_f32x2(float lo, float hi) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ float lo_f32x2(uint64_t v) {
+    float lo, hi;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+    return lo;
+}
+__device__ __forceinline__ float hi_f32x2(uint64_t v) {
+    float lo, hi;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+    return hi;
+}
+__device__ __forceinline__ void fma_f32x2(uint64_t& acc, uint64_t a, uint64_t b) {
+    asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc) : "l"(a), "l"(b));
+}
+
 template <int kL>
 __global__ void __launch_bounds__(32 * kGWarpsX * kGWarpsY, 3)
 planarg_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ PlanarZPlan Z,
@@ -687,11 +708,15 @@ planarg_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
     const float* __restrict__ xb = in + a_base - static_cast<long long>(k0) * P.res_x * Z.nz_pad;
     const int n_chunks = (g1 - g0 + kGChunk - 1) / kGChunk;
 
-    float acc[16][kL];
+    // kL even: the accumulators of layers (m, m + 1) share a 64-bit register pair and are advanced by
+    // one packed FFMA2 (fma.rn.f32x2, two IEEE fp32 fmas: same bits as two fmaf) - half the issue slots
+    constexpr bool kPacked = (kL % 2 == 0);
+    constexpr int kA = kPacked ? kL / 2 : kL;
+    typename std::conditional<kPacked, uint64_t, float>::type acc[16][kA];
 #pragma unroll
     for (int i = 0; i < 16; ++i)
 #pragma unroll
-        for (int m = 0; m < kL; ++m) acc[i][m] = 0.f;
+        for (int m = 0; m < kA; ++m) acc[i][m] = 0;
 
     // ray word of pair (lane % kGChunk) of a chunk, loaded one chunk before it is needed
     auto load_rays = [&](int c) {
@@ -739,10 +764,22 @@ planarg_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
                 if (!(mask & (1 << q))) continue;  // warp-uniform
                 const float4 cq = cj[q];           // warp-uniform address: one shared wavefront
                 const float cs[4] = {cq.x, cq.y, cq.z, cq.w};
+                if constexpr (kPacked) {
+                    uint64_t xp[kA];
 #pragma unroll
-                for (int t = 0; t < 4; ++t)
+                    for (int m = 0; m < kA; ++m) xp[m] = pack_f32x2(x[2 * m], x[2 * m + 1]);
 #pragma unroll
-                    for (int m = 0; m < kL; ++m) acc[4 * q + t][m] = fmaf(cs[t], x[m], acc[4 * q + t][m]);
+                    for (int t = 0; t < 4; ++t) {
+                        const uint64_t cc = pack_f32x2(cs[t], cs[t]);
+#pragma unroll
+                        for (int m = 0; m < kA; ++m) fma_f32x2(acc[4 * q + t][m], cc, xp[m]);
+                    }
+                } else {
+#pragma unroll
+                    for (int t = 0; t < 4; ++t)
+#pragma unroll
+                        for (int m = 0; m < kL; ++m) acc[4 * q + t][m] = fmaf(cs[t], x[m], acc[4 * q + t][m]);
+                }
             }
         }
         __syncwarp();  // the buffer is refilled by the issue of the next iteration
@@ -759,8 +796,11 @@ planarg_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
             const int xx = x0 + (i & 3), yy = y0 + (i >> 2);
-            if (xx < P.res[0] && yy < P.res[1] && acc[i][m] != 0.f)
-                o[static_cast<size_t>(yy) * P.res[0] + xx] += acc[i][m] * ray_weight;
+            float a;
+            if constexpr (kPacked) a = (m & 1) ? hi_f32x2(acc[i][m / 2]) : lo_f32x2(acc[i][m / 2]);
+            else a = acc[i][m];
+            if (xx < P.res[0] && yy < P.res[1] && a != 0.f)
+                o[static_cast<size_t>(yy) * P.res[0] + xx] += a * ray_weight;
         }
     }
 }

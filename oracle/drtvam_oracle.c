@@ -12,8 +12,12 @@
  * golden dose volumes or gradients.  What this file is
  * pinned against: the ray-origin bound of tests/test_projector.py:7-38, the
  * adjoint/FD consistency test of tests/test_integrators.py:69-110 (restated
- * in tests/), analytic single-ray and energy identities, and the f32 build is
- * compared with the f64 build.  The Mitsuba pieces are restated from the
+ * in tests/), analytic single-ray and energy identities, the f32 build is
+ * compared with the f64 build, orc_discretize reproduces the reference's own
+ * tests/files/target_hollow_gear.npy exactly, and the CUDA path held to this
+ * oracle passes the nine end-to-end known answers of tests/test_optimization.py
+ * at the reference's thresholds.  Absolute dose values stay unpinned.  The
+ * Mitsuba pieces are restated from the
  * published Mitsuba 3.6 algorithms (look_at, orthographic/perspective
  * projection, cylinder/cube intersection, dielectric Fresnel + refraction
  * with radiance scaling, spawn_ray offset, homogeneous medium free flight,

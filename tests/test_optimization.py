@@ -87,6 +87,30 @@ def write_fixture_meshes(workdir):
             write_ply(path, v, t)
 
 
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "reference_fixtures")
+
+# tests/files/double_cylindrical.json, restated; target and known answer are the reference's own data
+DOUBLE_CYLINDRICAL = {
+    "vial": {"type": "double_cylindrical", "r_ext_outer": 7, "r_int_outer": 6, "r_ext_inner": 3, "r_int_inner": 2,
+             "ior_outer": 1.53, "ior_inner": 1.553, "ior_inside_inner": 1.33,
+             "medium": {"ior": 1.48, "extinction": 0.05, "albedo": 0.0}},
+    "projector": {"type": "collimated", "n_patterns": 200, "resx": 200, "resy": 10, "pixel_size": 0.075,
+                  "motion": "circular", "distance": 20},
+    "sensor": {"type": "dda", "scalex": 14, "scaley": 14, "scalez": 1,
+               "film": {"type": "vfilm", "resx": 50, "resy": 50, "resz": 1}},
+    "target": {"filename": os.path.join(GOLDEN, "hollow_gear.ply"), "size": 8.0},
+    "loss": {"type": "threshold", "tl": 0.6, "tu": 0.85},
+    "progressive": True, "filter_radon": True, "spp": 2, "n_steps": 30, "max_depth": 10,
+}
+
+
+def double_cylindrical_config(workdir):
+    cfg = copy.deepcopy(DOUBLE_CYLINDRICAL)
+    cfg["output"] = os.path.join(workdir, "out_double_cylindrical")
+    cfg["save_pattern_images"] = False
+    return cfg
+
+
 def fixture_config(name, workdir):
     target = os.path.join(workdir, "box_hole_fixture.ply")
     if not os.path.exists(target):
@@ -137,6 +161,46 @@ def test_oracle_discretize_matches_analytic_volume(workdir):
     assert set(np.unique(vox)) <= {0.0, 1.0}
     agree = np.mean(np.isclose(analytic_reference(), vox[..., 0])) * 100
     assert agree > 99.4
+
+
+def test_discretize_matches_reference_golden(workdir):
+    """target_hollow_gear.npy was written by the reference's discretize: the oracle restatement must
+    reproduce it except for voxels whose centre is within rounding of the surface or whose random
+    ray grazes an edge."""
+    cfg = double_cylindrical_config(workdir)
+    scene = load_dict(load_scene(cfg), device="cpu")
+    sensor = scene.sensor("sensor")
+    desc = scene.describe(VolumeIntegrator({}), sensor)
+    desc.target_triangles = scene.all_target_triangles()
+    vox = orc.Oracle(desc.as_dict(), "f32").discretize()
+    golden = np.load(os.path.join(GOLDEN, "target_hollow_gear.npy"))
+    assert vox.shape == golden.shape == (1, 50, 50, 1)
+    assert golden.sum() > 100
+    mismatch = int((vox != golden).sum())
+    print("voxels differing from the reference's discretize:", mismatch, "of", golden.size)
+    assert mismatch <= 2
+
+
+@pytest.mark.gpu
+def test_discretize_matches_reference_golden_gpu(workdir):
+    from drtvam_b200.utils import discretize
+    cfg = double_cylindrical_config(workdir)
+    scene = load_dict(load_scene(cfg), device="cuda")
+    vox = discretize(scene, sensor=scene.sensor("sensor")).cpu().numpy()
+    golden = np.load(os.path.join(GOLDEN, "target_hollow_gear.npy"))
+    assert int((vox != golden).sum()) <= 2
+
+
+@pytest.mark.gpu
+def test_double_cylindrical(workdir):
+    """tests/test_optimization.py:18-40."""
+    cfg = double_cylindrical_config(workdir)
+    vol_final = optimize(cfg, progress=False).cpu().numpy()
+    reference = 1.0 * np.load(os.path.join(GOLDEN, "target_hollow_gear.npy"))
+    almost_equal = np.isclose(reference, 1.0 * (vol_final > 0.6))
+    percentage_correct = np.mean(almost_equal) * 100
+    print("double_cylindrical", percentage_correct)
+    assert percentage_correct > 99.4
 
 
 @pytest.mark.gpu
