@@ -147,6 +147,30 @@ __device__ __forceinline__ void z_scatter(uint32_t addr, const float (&em)[kL], 
     }
 }
 
+// packed fp32 pairs (Blackwell FFMA2)
+__device__ __forceinline__ uint64_t pack_f32x2(float lo, float hi) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ float lo_f32x2(uint64_t v) {
+    float lo, hi;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+    return lo;
+}
+__device__ __forceinline__ float hi_f32x2(uint64_t v) {
+    float lo, hi;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+    return hi;
+}
+__device__ __forceinline__ void fma_f32x2(uint64_t& acc, uint64_t a, uint64_t b) {
+    asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc) : "l"(a), "l"(b));
+}
+
+__device__ __forceinline__ void unpack_f32x2(uint64_t v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+
 // acc[0..kL) += tile[addr .. addr + kL) * de
 template <int kL>
 __device__ __forceinline__ void z_gather(uint32_t addr, float (&acc)[kL], float de) {
@@ -155,17 +179,19 @@ __device__ __forceinline__ void z_gather(uint32_t addr, float (&acc)[kL], float 
         asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
         acc[0] = fmaf(v, de, acc[0]);
     } else if constexpr (kL == 2) {
-        float v0, v1;
-        asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v0), "=f"(v1) : "r"(addr));
-        acc[0] = fmaf(v0, de, acc[0]);
-        acc[1] = fmaf(v1, de, acc[1]);
+        // packed pair: one FFMA2 (two IEEE fp32 fmas, same bits as two fmaf) per two layers
+        uint64_t v01, a01 = pack_f32x2(acc[0], acc[1]);
+        asm volatile("ld.shared.b64 %0, [%1];" : "=l"(v01) : "r"(addr));
+        fma_f32x2(a01, v01, pack_f32x2(de, de));
+        unpack_f32x2(a01, acc[0], acc[1]);
     } else {
-        float v0, v1, v2, v3;
-        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v0), "=f"(v1), "=f"(v2), "=f"(v3) : "r"(addr));
-        acc[0] = fmaf(v0, de, acc[0]);
-        acc[1] = fmaf(v1, de, acc[1]);
-        acc[2] = fmaf(v2, de, acc[2]);
-        acc[3] = fmaf(v3, de, acc[3]);
+        uint64_t v01, v23, a01 = pack_f32x2(acc[0], acc[1]), a23 = pack_f32x2(acc[2], acc[3]);
+        asm volatile("ld.shared.v2.b64 {%0, %1}, [%2];" : "=l"(v01), "=l"(v23) : "r"(addr));
+        const uint64_t dd = pack_f32x2(de, de);
+        fma_f32x2(a01, v01, dd);
+        fma_f32x2(a23, v23, dd);
+        unpack_f32x2(a01, acc[0], acc[1]);
+        unpack_f32x2(a23, acc[2], acc[3]);
     }
 }
 
@@ -654,26 +680,6 @@ __device__ __forceinline__ void bulk_g2s(void* smem, const void* gmem, uint32_t 
                  : "memory");
 }
 
-// packed fp32 pairs (Blackwell FFMA2)
-__device__ __forceinline__ uint64_t pack_f32x2(float lo, float hi) {
-    uint64_t r;
-    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
-    return r;
-}
-__device__ __forceinline__ float lo_f32x2(uint64_t v) {
-    float lo, hi;
-    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
-    return lo;
-}
-__device__ __forceinline__ float hi_f32x2(uint64_t v) {
-    float lo, hi;
-    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
-    return hi;
-}
-__device__ __forceinline__ void fma_f32x2(uint64_t& acc, uint64_t a, uint64_t b) {
-    asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc) : "l"(a), "l"(b));
-}
-
 template <int kL>
 __global__ void __launch_bounds__(32 * kGWarpsX * kGWarpsY, 3)
 planarg_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ PlanarZPlan Z,
@@ -708,15 +714,11 @@ planarg_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
     const float* __restrict__ xb = in + a_base - static_cast<long long>(k0) * P.res_x * Z.nz_pad;
     const int n_chunks = (g1 - g0 + kGChunk - 1) / kGChunk;
 
-    // kL even: the accumulators of layers (m, m + 1) share a 64-bit register pair and are advanced by
-    // one packed FFMA2 (fma.rn.f32x2, two IEEE fp32 fmas: same bits as two fmaf) - half the issue slots
-    constexpr bool kPacked = (kL % 2 == 0);
-    constexpr int kA = kPacked ? kL / 2 : kL;
-    typename std::conditional<kPacked, uint64_t, float>::type acc[16][kA];
+    float acc[16][kL];
 #pragma unroll
     for (int i = 0; i < 16; ++i)
 #pragma unroll
-        for (int m = 0; m < kA; ++m) acc[i][m] = 0;
+        for (int m = 0; m < kL; ++m) acc[i][m] = 0.f;
 
     // ray word of pair (lane % kGChunk) of a chunk, loaded one chunk before it is needed
     auto load_rays = [&](int c) {
@@ -764,22 +766,15 @@ planarg_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
                 if (!(mask & (1 << q))) continue;  // warp-uniform
                 const float4 cq = cj[q];           // warp-uniform address: one shared wavefront
                 const float cs[4] = {cq.x, cq.y, cq.z, cq.w};
-                if constexpr (kPacked) {
-                    uint64_t xp[kA];
+                // (packed FFMA2 accumulators were measured here too: half the FMA issue slots, same
+                // 11.2 ms - the loop is bound by dependent shared-memory latencies at 6 warps per
+                // scheduler, not by issue slots or the FMA pipe (28 % busy); fetching pair j + 1's mask
+                // and pattern values ahead of pair j's FMAs spills at 80 registers: 16.1 ms.
+                // profiles/r01o_*, r01s_*)
 #pragma unroll
-                    for (int m = 0; m < kA; ++m) xp[m] = pack_f32x2(x[2 * m], x[2 * m + 1]);
+                for (int t = 0; t < 4; ++t)
 #pragma unroll
-                    for (int t = 0; t < 4; ++t) {
-                        const uint64_t cc = pack_f32x2(cs[t], cs[t]);
-#pragma unroll
-                        for (int m = 0; m < kA; ++m) fma_f32x2(acc[4 * q + t][m], cc, xp[m]);
-                    }
-                } else {
-#pragma unroll
-                    for (int t = 0; t < 4; ++t)
-#pragma unroll
-                        for (int m = 0; m < kL; ++m) acc[4 * q + t][m] = fmaf(cs[t], x[m], acc[4 * q + t][m]);
-                }
+                    for (int m = 0; m < kL; ++m) acc[4 * q + t][m] = fmaf(cs[t], x[m], acc[4 * q + t][m]);
             }
         }
         __syncwarp();  // the buffer is refilled by the issue of the next iteration
@@ -796,11 +791,8 @@ planarg_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
             const int xx = x0 + (i & 3), yy = y0 + (i >> 2);
-            float a;
-            if constexpr (kPacked) a = (m & 1) ? hi_f32x2(acc[i][m / 2]) : lo_f32x2(acc[i][m / 2]);
-            else a = acc[i][m];
-            if (xx < P.res[0] && yy < P.res[1] && a != 0.f)
-                o[static_cast<size_t>(yy) * P.res[0] + xx] += a * ray_weight;
+            if (xx < P.res[0] && yy < P.res[1] && acc[i][m] != 0.f)
+                o[static_cast<size_t>(yy) * P.res[0] + xx] += acc[i][m] * ray_weight;
         }
     }
 }
