@@ -227,6 +227,166 @@ general_persistent_kernel(const __grid_constant__ SceneParams P, const float* __
     }
 }
 
+// ---- two-phase tracer for scattering media (DDA sensor) ------------------------------------------
+// Phase 1: every thread runs the bounce loops of kQLanes lanes WITHOUT walking anything; each medium
+// segment (origin, direction, length, weight) goes to a queue in shared memory (bounce_once hands
+// the segment over before anything depends on how it is deposited).  Phase 2: the threads of the
+// block drain the queue, one segment per thread at a time, in bursts of voxel steps; a thread whose
+// segment ends takes the next one, so the 32 threads of a warp keep stepping whatever the depth of
+// the path or the length of the segment they came from.  The nested kernels above sit at 7.2 of 32
+// threads active per instruction on C5 because every lane waits for the longest segment of each
+// bounce and the deepest path of its warp (profiles/r01d_*).  Same lanes, same PCG32 streams, same
+// deposits as the nested kernels; only the order of the (unordered) atomics differs.
+constexpr int kQLanes = 2;   // lanes traced per thread
+constexpr int kQCap = 3;     // queue slots per lane; a segment that finds the queue full is walked in place
+constexpr int kQBurst = 16;  // voxel steps between two looks at the queue
+constexpr int kQSlots = kThreads * kQLanes * kQCap;
+constexpr size_t kQSmemBytes = static_cast<size_t>(kQSlots) * (2 * sizeof(float4) + sizeof(int)) +
+                               sizeof(float) * kThreads * kQLanes;
+
+// kMode 0: in = active_data, out = film (red.global).  kMode 1: in = dL, out = pattern gradient.
+template <bool kScatter, int kMode>
+__global__ void __launch_bounds__(kThreads)
+general_queue_kernel(const __grid_constant__ SceneParams P, const float* __restrict__ in,
+                     const uint32_t* __restrict__ active_pixels, uint64_t n_lanes, uint32_t spp, uint32_t seed,
+                     float ray_weight, float* __restrict__ out, const int* __restrict__ gate) {
+    extern __shared__ __align__(16) float4 q_rec[];  // two float4 per slot
+    int* q_flag = reinterpret_cast<int*>(q_rec + 2 * kQSlots);
+    float* grad_s = reinterpret_cast<float*>(q_flag + kQSlots);
+    __shared__ int q_count, q_head;
+    if (gate && *gate == 0) return;  // the planar fast path owns this call
+    const int tid = threadIdx.x;
+    if (tid == 0) { q_count = 0; q_head = 0; }
+    if (kMode == 1)
+        for (int l = 0; l < kQLanes; ++l) grad_s[l * kThreads + tid] = 0.f;
+    __syncthreads();
+    const uint64_t block_base = static_cast<uint64_t>(blockIdx.x) * (kThreads * kQLanes);
+
+    // ---- phase 1: bounce loops, segments to the queue
+    for (int l = 0; l < kQLanes; ++l) {
+        const int local = l * kThreads + tid;
+        const uint64_t lane = block_base + local;
+        if (lane >= n_lanes) continue;
+        const uint64_t j = lane / spp;
+        float em = 1.f;
+        if (kMode == 0) {
+            em = __ldg(in + j) * ray_weight;
+            if (em == 0.f) continue;  // every deposit of the lane is proportional to em
+        }
+        Sampler rng;
+        rng.seed(seed, static_cast<uint32_t>(lane));
+        TraceState T;
+        T.ray = generate_ray(P, __ldg(active_pixels + j), rng);
+        while (bounce_once<kScatter>(P, T, rng, [&](const Ray& r, float maxt, float w0, bool inside, float) {
+            const int slot = atomicAdd(&q_count, 1);
+            if (slot < kQSlots) {
+                q_rec[2 * slot] = make_float4(r.ox, r.oy, r.oz, maxt);
+                q_rec[2 * slot + 1] = make_float4(r.dx, r.dy, r.dz, w0 * em);
+                q_flag[slot] = local | (inside ? (1 << 24) : 0);
+            } else if (kMode == 0) {
+                ScatterSink sink{out, em};
+                dda_segment(P, r, maxt, w0, inside, sink);
+            } else {
+                GatherSink sink{in};
+                dda_segment(P, r, maxt, w0, inside, sink);
+                atomicAdd(grad_s + local, sink.acc);
+            }
+        })) {}
+    }
+    __syncthreads();
+    const int n_seg = min(q_count, kQSlots);
+
+    // ---- phase 2: drain the queue
+    {
+        DdaWalk W;
+        bool walking = false, exhausted = false, open = false;
+        int owner = 0;
+        ScatterSink ssink{out, 1.f};  // the record's weight carries em
+        PipelinedGatherSink gsink{in};
+        for (;;) {
+            while (!walking && !exhausted) {
+                const int slot = atomicAdd(&q_head, 1);
+                if (slot >= n_seg) { exhausted = true; break; }
+                const float4 a = q_rec[2 * slot], b = q_rec[2 * slot + 1];
+                const int flag = q_flag[slot];
+                owner = flag & 0xffffff;
+                Ray r;
+                r.ox = a.x; r.oy = a.y; r.oz = a.z; r.dx = b.x; r.dy = b.y; r.dz = b.z;
+                walking = W.begin(P, r, a.w, b.w, (flag >> 24) != 0);
+                open = walking;
+            }
+            if (__all_sync(0xffffffffu, !walking)) break;
+            if (kMode == 0) {
+#pragma unroll 1
+                for (int i = 0; i < kQBurst; ++i)
+                    if (walking) walking = W.step(ssink);
+            } else {
+#pragma unroll 1
+                for (int i = 0; i < kQBurst; ++i)
+                    if (walking) walking = W.step(gsink);
+                if (open && !walking) {
+                    atomicAdd(grad_s + owner, gsink.finish());
+                    open = false;
+                }
+            }
+        }
+    }
+    if (kMode == 0) return;
+    __syncthreads();
+
+    // ---- sum over the spp lanes of one pixel (the dr.repeat of common.py:82)
+    for (int l = 0; l < kQLanes; ++l) {
+        const int local = l * kThreads + tid;
+        const uint64_t lane = block_base + local;
+        const bool live = lane < n_lanes;
+        const uint64_t j = live ? lane / spp : 0;
+        float g = live ? grad_s[local] * ray_weight : 0.f;
+        if (spp == 1) {
+            if (live) out[j] = g;
+        } else if ((spp & (spp - 1)) == 0 && spp <= 32) {
+            for (uint32_t off = spp >> 1; off > 0; off >>= 1) g += __shfl_xor_sync(0xffffffffu, g, off);
+            if (live && (lane % spp) == 0) out[j] = g;
+        } else {
+            if (live) atomicAdd(out + j, g);  // grad pre-zeroed by the host
+        }
+    }
+}
+
+// 0 nested (default for absorptive media), 1 persistent (opt-in), 2 two-phase queue (default for
+// scattering media with the DDA sensor).  DRTVAM_GENERAL_KERNELS = nested | persistent | queue.
+inline int general_kernel_family(const SceneParams& P) {
+    static const int forced = [] {
+        const char* e = std::getenv("DRTVAM_GENERAL_KERNELS");
+        if (e == nullptr) return -1;
+        if (std::strcmp(e, "persistent") == 0) return 1;
+        if (std::strcmp(e, "queue") == 0) return 2;
+        if (std::strcmp(e, "nested") == 0) return 0;
+        return -1;
+    }();
+    if (forced == 2 || forced == -1) {
+        const bool fits = P.sensor_kind == 0 && P.albedo != 0.f;
+        if (fits) return 2;
+        return 0;
+    }
+    return forced;
+}
+
+template <int kMode>
+cudaError_t launch_queue(const SceneParams& P, const float* in, const uint32_t* active_pixels, uint64_t n_lanes,
+                         uint32_t spp, uint32_t seed, float ray_weight, float* out, cudaStream_t stream,
+                         const int* gate) {
+    static const cudaError_t attr = cudaFuncSetAttribute(general_queue_kernel<true, kMode>,
+                                                         cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                         static_cast<int>(kQSmemBytes));
+    if (attr != cudaSuccess) return attr;
+    const uint64_t per_block = static_cast<uint64_t>(kThreads) * kQLanes;
+    const unsigned grid = static_cast<unsigned>((n_lanes + per_block - 1) / per_block);
+    general_queue_kernel<true, kMode><<<grid, kThreads, kQSmemBytes, stream>>>(P, in, active_pixels, n_lanes, spp, seed,
+                                                                             ray_weight, out, gate);
+    count_launch();
+    return cudaGetLastError();
+}
+
 // The persistent kernel is opt-in (DRTVAM_GENERAL_KERNELS=persistent): on B200 it is not yet faster
 // than the nested kernels (profiles/r01_general_tracer_sweep.txt), see DESIGN.md section 5.
 inline bool use_simple_kernels() {
@@ -277,6 +437,8 @@ cudaError_t launch_forward_general(const SceneParams& P, const float* active_dat
                                    uint64_t n_lanes, uint32_t spp, uint32_t seed, float ray_weight, float* film,
                                    cudaStream_t stream, const int* gate) {
     if (n_lanes == 0) return cudaSuccess;
+    if (general_kernel_family(P) == 2)
+        return launch_queue<0>(P, active_data, active_pixels, n_lanes, spp, seed, ray_weight, film, stream, gate);
     if (!use_simple_kernels()) {
         if (P.albedo != 0.f)
             return launch_persistent<true, 0>(P, active_data, active_pixels, n_lanes, spp, seed, ray_weight, film, stream,
@@ -298,7 +460,8 @@ cudaError_t launch_adjoint_general(const SceneParams& P, const float* dL, const 
                                    uint64_t n_lanes, uint32_t spp, uint32_t seed, float ray_weight, float* grad,
                                    cudaStream_t stream, const int* gate) {
     if (n_lanes == 0) return cudaSuccess;
-    const bool simple = use_simple_kernels();
+    const bool queue = general_kernel_family(P) == 2;
+    const bool simple = use_simple_kernels() || queue;
     const bool pow2 = (spp & (spp - 1)) == 0 && spp <= 32;
     // lanes of one pixel are summed with atomics (always in the persistent kernel, for odd spp in the
     // simple one); a gated call hands in a zeroed gradient (abi.cu)
@@ -306,6 +469,8 @@ cudaError_t launch_adjoint_general(const SceneParams& P, const float* dL, const 
         cudaError_t e = cudaMemsetAsync(grad, 0, sizeof(float) * (n_lanes / spp), stream);
         if (e != cudaSuccess) return e;
     }
+    if (queue)
+        return launch_queue<1>(P, dL, active_pixels, n_lanes, spp, seed, ray_weight, grad, stream, gate);
     if (!simple) {
         if (P.albedo != 0.f)
             return launch_persistent<true, 1>(P, dL, active_pixels, n_lanes, spp, seed, ray_weight, grad, stream, gate);
