@@ -37,6 +37,8 @@ def parse_args():
     ap.add_argument("--general", action="store_true", help="force the general per-lane tracer")
     ap.add_argument("--surface-aware", action="store_true",
                     help="surface-aware discretization (two-channel film + target-mesh crossings; BASELINE config 4)")
+    ap.add_argument("--emulate-shard", type=int, default=0, metavar="W",
+                    help="profiling aid: run rank 0's angle shard of a W-rank job on one GPU (no collective)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     return ap.parse_args()
@@ -231,6 +233,10 @@ def main():
         target = discretize(scene, sensor=sensor)
     if world > 1:
         scene.shard(rank, world)
+    elif args.emulate_shard > 1:
+        scene.shard(0, args.emulate_shard)
+        scene.world_size = 1
+        workload += f" [rank 0's shard of {args.emulate_shard}, profiling aid]"
     n_local = scene.projector.active_size()
     pixels = scene.projector.active_pixels
     loss_fn = ThresholdedLoss({})

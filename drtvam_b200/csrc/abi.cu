@@ -430,8 +430,10 @@ int drtvam_forward(DrtvamScene* s, const float* active_data, const uint32_t* act
             CUDA_TRY(launch_planar_lane_forward(P1, s->planar, active_data, active_pixels, n_active, spp, seed, w, plane,
                                                 st));
         else if (s->zplan.valid && s->gplan.valid && s->force_mode != 2)
+            // fresh: the plane was cleared above (zero_first, or the planes of a surface-aware scene) and
+            // the patch gather is its first writer, so it stores instead of read-add-write
             CUDA_TRY(launch_planarg_forward(P1, s->zplan, s->gplan, s->planar.gate, active_data, active_pixels,
-                                            n_active, w, plane, st));
+                                            n_active, w, plane, sa || zero_first != 0, st));
         else if (s->zplan.valid && s->force_mode != 2)
             CUDA_TRY(launch_planarz_forward(P1, s->zplan, s->planar.gate, active_data, active_pixels, n_active, w, plane,
                                             st));

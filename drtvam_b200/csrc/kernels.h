@@ -115,7 +115,7 @@ cudaError_t planarg_build(const SceneParams& P, const PlanarHost& base, const Pl
 void planarg_release(PlanarGHost& G);
 cudaError_t launch_planarg_forward(const SceneParams& P, PlanarZHost& H, PlanarGHost& G, const int* gate,
                                    const float* active_data, const uint32_t* active_pixels, uint64_t n_active,
-                                   float ray_weight, float* film, cudaStream_t stream);
+                                   float ray_weight, float* film, bool fresh, cudaStream_t stream);
 void planarz_release(PlanarZHost& H);
 cudaError_t launch_planarz_forward(const SceneParams& P, PlanarZHost& H, const int* gate, const float* active_data,
                                    const uint32_t* active_pixels, uint64_t n_active, float ray_weight, float* film,

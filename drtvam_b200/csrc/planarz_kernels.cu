@@ -685,7 +685,7 @@ __global__ void __launch_bounds__(32 * kGWarpsX * kGWarpsY, 3)
 planarg_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ PlanarZPlan Z,
                const float4* __restrict__ coef, const int* __restrict__ ray, const float* __restrict__ in,
                float* __restrict__ out, const uint32_t* __restrict__ active_pixels, uint64_t n_active, float ray_weight,
-               const int* __restrict__ gate, int a_begin) {
+               const int* __restrict__ gate, int a_begin, int fresh) {
     extern __shared__ __align__(16) float g_smem[];
     if (*gate != 0) return;
     constexpr int kBuf = g_buf_floats(kL), kLine = 32 * kL;
@@ -780,19 +780,42 @@ planarg_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
         __syncwarp();  // the buffer is refilled by the issue of the next iteration
     }
 
-    // the warp is the only writer of its (patch, layers) in this launch: plain read-add-write
+    // the warp is the only writer of its (patch, layers) in this launch.  `fresh`: the film was
+    // cleared in this call and nothing has been added yet, so the rows are stored without reading
+    // them back (no load latency at the end of the warp - with one eighth of the angles per rank
+    // that wait was a third of the kernel, profiles/r01x2_*); otherwise read-add-write.  A patch row
+    // is 16 aligned bytes when res_x is a multiple of 4.
     const int x0 = px * kPatch, y0 = py * kPatch;
     const size_t layer_elems = static_cast<size_t>(P.res[0]) * P.res[1];
+    const bool vec = ((P.res[0] & 3) == 0) && ((reinterpret_cast<uintptr_t>(out) & 15) == 0) && (x0 + 3 < P.res[0]);
 #pragma unroll
     for (int m = 0; m < kL; ++m) {
         const int z = __ldg(Z.zl + a_base + kL * lane + m);
         if (z < 0) continue;
         float* o = out + z * layer_elems;
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-            const int xx = x0 + (i & 3), yy = y0 + (i >> 2);
-            if (xx < P.res[0] && yy < P.res[1] && acc[i][m] != 0.f)
-                o[static_cast<size_t>(yy) * P.res[0] + xx] += acc[i][m] * ray_weight;
+        for (int r = 0; r < 4; ++r) {
+            const int yy = y0 + r;
+            if (yy >= P.res[1]) continue;
+            float* row = o + static_cast<size_t>(yy) * P.res[0] + x0;
+            if (vec) {
+                float4 v = make_float4(acc[4 * r][m] * ray_weight, acc[4 * r + 1][m] * ray_weight,
+                                       acc[4 * r + 2][m] * ray_weight, acc[4 * r + 3][m] * ray_weight);
+                if (!fresh) {
+                    if (v.x == 0.f && v.y == 0.f && v.z == 0.f && v.w == 0.f) continue;
+                    const float4 old = *reinterpret_cast<const float4*>(row);
+                    v.x += old.x; v.y += old.y; v.z += old.z; v.w += old.w;
+                }
+                *reinterpret_cast<float4*>(row) = v;
+            } else {
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    if (x0 + t >= P.res[0]) continue;
+                    const float a = acc[4 * r + t][m] * ray_weight;
+                    if (fresh) row[t] = a;
+                    else if (a != 0.f) row[t] += a;
+                }
+            }
         }
     }
 }
@@ -1120,7 +1143,7 @@ cudaError_t planarg_build(const SceneParams& P, const PlanarHost& base, const Pl
 
 cudaError_t launch_planarg_forward(const SceneParams& P, PlanarZHost& H, PlanarGHost& G, const int* gate,
                                    const float* active_data, const uint32_t* active_pixels, uint64_t n_active,
-                                   float ray_weight, float* film, cudaStream_t stream) {
+                                   float ray_weight, float* film, bool fresh, cudaStream_t stream) {
     const int nk = static_cast<int>(n_active / (static_cast<uint64_t>(P.res_x) * P.res_y));
     PZ_TRY(z_scratch(H, sizeof(float) * static_cast<size_t>(nk) * P.res_x * H.nz_pad));
     const dim3 pgrid((P.res_x + 31) / 32, H.nz_pad / 32, nk);
@@ -1136,13 +1159,13 @@ cudaError_t launch_planarg_forward(const SceneParams& P, PlanarZHost& H, PlanarG
         const int kL = S.plan.lanes_l, a_begin = S.plan.a_begin;
         if (kL == 1)
             planarg_kernel<1><<<grid, threads, g_smem_bytes(1), stream>>>(P, Z, G.coef, G.ray, H.scratch, film,
-                                                                         active_pixels, n_active, ray_weight, gate, a_begin);
+                                                                         active_pixels, n_active, ray_weight, gate, a_begin, fresh ? 1 : 0);
         else if (kL == 2)
             planarg_kernel<2><<<grid, threads, g_smem_bytes(2), stream>>>(P, Z, G.coef, G.ray, H.scratch, film,
-                                                                         active_pixels, n_active, ray_weight, gate, a_begin);
+                                                                         active_pixels, n_active, ray_weight, gate, a_begin, fresh ? 1 : 0);
         else
             planarg_kernel<4><<<grid, threads, g_smem_bytes(4), stream>>>(P, Z, G.coef, G.ray, H.scratch, film,
-                                                                         active_pixels, n_active, ray_weight, gate, a_begin);
+                                                                         active_pixels, n_active, ray_weight, gate, a_begin, fresh ? 1 : 0);
         count_launch();
         PZ_TRY(cudaGetLastError());
     }
