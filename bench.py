@@ -352,11 +352,12 @@ def main():
     peak, how = measured_peaks()
     achieved = 4.0 * visits / (fwd_ms * 1e-3) * 1e-9
     hbm_alg_bytes = 4.0 * n_local * 2 + 4.0 * int(np.prod(desc_full.film_shape()))
-    # DRAM bytes of the forward pass from ncu --set full (profiles/r01u_planar_ncu_details.txt and the
-    # launch list r01u: planarg_kernel<4> 6.19 GB read + 0.29 GB written, tail kernel 1.39 GB, pack kernel 0.7 GB);
-    # only quoted for the workload and kernel family it was captured on
+    # DRAM bytes of the forward pass from ncu --set full (profiles/r01final_planar_ncu_details.txt:
+    # planarg_kernel<4> 5.99 GB read + 0.32 GB written, tail kernel planarg_kernel<1> 1.36 + 0.01 GB; pack kernel
+    # 0.26 + 0.23 GB, profiles/r01o_planar_ncu_details.txt); only quoted for the workload and kernel family it
+    # was captured on
     plan_now = int(lib.drtvam_scene_plan(h, n_local, spp))
-    traffic = 8.6e9 if (args.workload == "C2" and not args.n and plan_now == 2 and world == 1) else None
+    traffic = 8.2e9 if (args.workload == "C2" and not args.n and plan_now == 2 and world == 1) else None
     roofline = {
         "bound": "hbm", "kernel": "forward projection (A p): zpack + planarg_kernel patch gather"
         if plan_now == 2 else "forward projection (A p)", "achieved": achieved, "peak": peak, "unit": "GB/s",

@@ -324,6 +324,31 @@ def test_planar_rectangular_grid_and_scale(mode, workdir):
     assert rel_l2(film.cpu().numpy() - 1.0, ref) < TOL
 
 
+def test_patch_gather_store_and_accumulate_paths(workdir):
+    """The patch-gather forward stores its rows when the film was cleared in the same call
+    (zero_first = 1) and read-add-writes them otherwise; both as 16-byte vectors when res_x is a
+    multiple of 4.  Accumulating twice onto a non-zero film must equal 1 + 2 A p."""
+    scene, integ, sensor, d, _ = build("C2", workdir, 64, n_patterns=12)
+    pix = pixels_np(scene)
+    p, _ = random_inputs(d, pix.size, 21)
+    h = Handle(d)
+    assert _plan(h, pix.size) == 2
+    ref = orc.Oracle(d.as_dict(), "f64").forward(p, pix)
+    fresh = h.forward(p, pix)
+    assert rel_l2(fresh, ref) < TOL
+    pt = torch.as_tensor(p, device="cuda")
+    pixt = torch.as_tensor(pix.astype(np.int64), device="cuda").to(torch.int32)
+    film = torch.ones(d.film_shape(), device="cuda")
+    for _ in range(2):
+        _lib.check(h.lib.drtvam_forward(h.h, pt.data_ptr(), pixt.data_ptr(), pt.numel(), 1, 0, 1.0, film.data_ptr(), 0,
+                                        None))
+    assert rel_l2(film.cpu().numpy() - 1.0, 2.0 * ref) < TOL
+    # a cleared film holds no stale values where the projection is zero
+    film.fill_(7.0)
+    _lib.check(h.lib.drtvam_forward(h.h, pt.data_ptr(), pixt.data_ptr(), pt.numel(), 1, 0, 1.0, film.data_ptr(), 1, None))
+    assert np.array_equal(film.cpu().numpy(), fresh)
+
+
 @pytest.mark.parametrize("mode", PLANAR_MODES)
 def test_planar_angle_shard_and_sparse_fallback(mode, workdir):
     """An angle shard (active_pixels = base + j) stays on the planar plan; a
