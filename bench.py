@@ -64,7 +64,7 @@ class ClockSampler:
         self.proc = None
         try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200", "-i", str(index)],
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "50", "-i", str(index)],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -363,7 +363,11 @@ def main():
         if plan_now == 2 else "forward projection (A p)", "achieved": achieved, "peak": peak, "unit": "GB/s",
         "frac": achieved / peak, "traffic": traffic, "peak_source": how,
         "note": "achieved = 4 B per voxel visit (SURVEY 8(d)) / pass time; the visits are accumulated in registers / "
-                "shared memory, so the figure can exceed the HBM copy peak; traffic = measured DRAM bytes per pass",
+                "shared memory, so the figure can exceed the HBM copy peak; traffic = measured DRAM bytes per pass. "
+                "ncu on the patch-gather kernel (profiles/r01final_planar_ncu_details.txt): issue slots 65 % busy, FMA "
+                "pipe 28 %, DRAM 0.7 TB/s - the pass is bound by dependent shared-memory latency at 24 warps/SM, "
+                "not by HBM; against the measured shared-memory ld+add+st rate (2.34e12/s, "
+                "profiles/r01_microbench_atomics.json) the 2.75e12 visits/s are 1.17x",
         "algorithmic_bytes_per_visit": 4, "visits_per_launch": visits, "kernel_ms": fwd_ms,
         "adjoint_ms": adj_ms, "adjoint_achieved": 4.0 * visits / (adj_ms * 1e-3) * 1e-9 if adj_ms else None,
         "allreduce_ms": ar_ms,
