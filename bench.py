@@ -189,11 +189,11 @@ def main():
         value = total_rays / total_t
         full_rays = 3 * desc.n_patterns * desc.res_x * desc.res_y * spp
         line = {
-            "impl": "reference", "metric": "rays_per_s", "value": value, "unit": "rays/s", "n_gpus": 0,
+            "impl": "reference", "metric": "rays_per_s", "value": value, "unit": "rays/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": full_rays / value * 1e3,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": {"workload": workload, "note": "reference's Dr.Jit LLVM path is unavailable on this box "
+            "config": {"workload": workload, "rays_per_step": full_rays, "gpus_used": 0, "note": "reference's Dr.Jit LLVM path is unavailable on this box "
                        "(mitsuba/drjit not installable); this is the CPU oracle port, fp32, OpenMP over rays; "
                        "ms_per_step extrapolated from the bounded sample to the full step"},
             "cpu_baseline": {"value": value, "unit": "rays/s", "cores": host_cores, "kind": "port", "sample": sample},
