@@ -180,7 +180,7 @@ def main():
         per_step = max(2.0, min(20.0, 120.0 / max(1, args.steps + args.warmup)))
         sample = ""
         for i in range(args.warmup + args.steps):
-            rps, rays, t, n_ang = oracle_sample(cfg, desc, per_step)
+            rps, rays, t, n_ang = oracle_sample(cfg, desc, per_step, threads=host_cores)
             if i >= args.warmup:
                 vals.append((rps, rays, t))
             sample = f"{n_ang} of {desc.n_patterns} angles x {desc.res_x}x{desc.res_y} rays, 3 passes (A p, A^T g, A d)"
@@ -379,7 +379,7 @@ def main():
     if rank == 0:
         cpu_baseline = None
         if not args.no_cpu_baseline and world == 1:
-            rps, rays, t, n_ang = oracle_sample(cfg, desc_full, args.cpu_seconds)
+            rps, rays, t, n_ang = oracle_sample(cfg, desc_full, args.cpu_seconds, threads=host_cores)
             cpu_baseline = {"value": rps, "unit": "rays/s", "cores": host_cores, "kind": "port",
                             "sample": f"{n_ang} of {desc_full.n_patterns} angles x {desc_full.res_x}x{desc_full.res_y} "
                                       f"rays, 3 passes, {t:.1f} s of oracle (fp32, OpenMP) time"}
