@@ -966,13 +966,24 @@ static cudaError_t z_scratch(PlanarZHost& H, size_t bytes) {
     return cudaSuccess;
 }
 
-// Angle groups of one sub-plan: enough CTAs for two waves of the 148 SMs.
-static int z_groups(const PlanarZSub& S, int nk) {
+// Angle groups of one sub-plan: enough CTAs for two waves of the 148 SMs.  The gather (adjoint) kernel runs one
+// 1024-thread CTA per SM, so a grid just past a multiple of 148 pays a whole extra wave (the 1-layer tail of C2:
+// 100 tiles x 3 groups = 300 CTAs = 3 waves for 2.03 waves of work); there the group count is raised to the one
+// with the fewest waves per group.  The scatter kernel keeps the plain rule (its group count fixes the order of
+// its atomic adds).
+static int z_groups(const PlanarZSub& S, int nk, bool gather) {
     const long long ctas = static_cast<long long>(S.plan.tiles_x) * S.plan.tiles_y * S.n_blocks;
+    const long long g_max = std::min<long long>(64, std::max(1, nk / 8));
     long long g = (148 * 2 + ctas - 1) / std::max<long long>(ctas, 1);
-    g = std::min<long long>(g, std::max(1, nk / 8));
-    g = std::min<long long>(g, 64);
-    return g < 1 ? 1 : static_cast<int>(g);
+    g = std::max<long long>(1, std::min(g, g_max));
+    if (!gather) return static_cast<int>(g);
+    auto waves_per_group = [&](long long n) { return static_cast<double>((ctas * n + 147) / 148) / n; };
+    const double ideal = static_cast<double>(ctas) / 148.0;
+    if (waves_per_group(g) <= 1.15 * ideal) return static_cast<int>(g);
+    long long best = g;
+    for (long long n = g + 1; n <= std::min<long long>(g_max, 16); ++n)
+        if (waves_per_group(n) < 0.96 * waves_per_group(best)) best = n;
+    return static_cast<int>(best);
 }
 
 template <int kMode>
@@ -983,7 +994,7 @@ static cudaError_t z_launch(const SceneParams& P, PlanarZHost& H, const float* i
     for (int i = 0; i < H.n_sub; ++i) {
         const PlanarZSub& S = H.sub[i];
         PlanarZPlan Z = S.plan;
-        const int groups = z_groups(S, nk);
+        const int groups = z_groups(S, nk, kMode == kGather);
         Z.groups = groups;
         const dim3 grid(Z.tiles_x * Z.tiles_y, S.n_blocks, groups);
         if (Z.lanes_l == 1)
