@@ -8,7 +8,13 @@ index-matched vial, 400x400 DMD, 400 angles, 400^3 dose grid, 1 spp).
 One "step" is the projection work of one L-BFGS iteration (optimize.py:294,308
 and lbfgs.py:248): forward A p, thresholded loss + its gradient, adjoint A^T g,
 forward A d (signed search direction) and one Armijo loss evaluation.  Prints
-ONE JSON line (see the contract in the task description).
+ONE JSON line (see the contract in the task description).  Beside the headline
+(the configuration BASELINE.json quotes the metric on) the line carries
+  default_sampling  the identical step with regular_sampling=false, the reference's default
+                    (integrators/common.py:22);
+  lbfgs_iteration   a whole LinearLBFGS iteration (history, two-loop recursion, Armijo search,
+                    pattern update, clamp) timed around the same projections;
+  multi_gpu_check   (N > 1) the N-rank dose and pattern gradient against the 1-rank ones.
 """
 from __future__ import annotations
 
@@ -33,13 +39,19 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="C2")
     ap.add_argument("--n", type=int, default=0, help="override DMD/grid edge (default: full size)")
-    ap.add_argument("--jitter", action="store_true", help="regular_sampling=false (per-ray jitter, general tracer)")
+    ap.add_argument("--jitter", action="store_true", help="headline on regular_sampling=false (per-ray jitter)")
     ap.add_argument("--general", action="store_true", help="force the general per-lane tracer")
     ap.add_argument("--surface-aware", action="store_true",
                     help="surface-aware discretization (two-channel film + target-mesh crossings; BASELINE config 4)")
     ap.add_argument("--emulate-shard", type=int, default=0, metavar="W",
-                    help="profiling aid: run rank 0's angle shard of a W-rank job on one GPU (no collective)")
+                    help="profiling aid: run rank 0's shard of a W-rank job on one GPU (no collective)")
+    ap.add_argument("--partition", default="auto", choices=["auto", "angle", "zslab"],
+                    help="multi-GPU partitioning: by projection angle (one all-reduce of the dose per forward) or, "
+                         "for planar scenes, by z-slab / DMD row (no dose collective)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-default-sampling", action="store_true", help="skip the regular_sampling=false record")
+    ap.add_argument("--no-lbfgs", action="store_true", help="skip the whole-L-BFGS-iteration record")
+    ap.add_argument("--no-verify", action="store_true", help="skip the N-rank == 1-rank check")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     return ap.parse_args()
 
@@ -51,6 +63,15 @@ WORKLOAD_TEXT = {
     "C3": "C3: as C2 with a cylindrical glass vial (refraction)",
     "C4": "C4: as C2 with a square glass vial (refraction)",
     "C5": "C5: as C3 with a Henyey-Greenstein scattering resin, 16 spp",
+}
+
+# shared-memory / L2 atomic peaks measured with csrc/microbench.cu on this pool's B200
+# (profiles/r01_microbench_atomics.json); visits/s are set against them
+ATOMIC_PEAKS = {
+    "smem_lds_fadd_sts": (2.34482e12, "shared-memory ld + add + st per lane, conflict free"),
+    "smem_atoms_f32_cas": (1.51375e12, "shared-memory fp32 CAS add"),
+    "red_v4_l2_resident": (1.57674e12, "red.global.add.v4.f32, 64 MiB (L2 resident), per float"),
+    "red_f32_scattered_l2": (1.9876e11, "red.global.add.f32, one 32-byte sector per lane, 64 MiB (L2 resident)"),
 }
 
 
@@ -106,8 +127,25 @@ def measured_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
         with open(path) as f:
-            return json.load(f).get("hbm_gbs", 6650.0), "measured"
-    return 6650.0, "fallback"
+            return json.load(f).get("hbm_gbs", 6650.0), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def measured_traffic(workload, plan, world, edge):
+    """DRAM bytes per forward pass from the ncu --set full capture committed under profiles/
+    (profiles/ncu_traffic.json, written by tools/ncu_summary.py traffic); None when no capture of this
+    workload / kernel family exists."""
+    path = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if world != 1 or edge or not os.path.exists(path):
+        return None, None
+    try:
+        with open(path) as f:
+            rec = json.load(f).get(f"{workload}:plan{plan}")
+    except (OSError, ValueError):
+        return None, None
+    if not rec:
+        return None, None
+    return rec["forward_dram_bytes"], rec["source"]
 
 
 def oracle_sample(cfg, desc, seconds, threads=0):
@@ -156,16 +194,26 @@ def main():
     from drtvam_b200.synthetic import make_config
 
     workdir = os.path.join(tempfile.gettempdir(), f"drtvam_bench_{os.getuid()}_{rank}")
-    cfg = make_config(args.workload, workdir, n=args.n or None, regular_sampling=not args.jitter,
-                      surface_aware=args.surface_aware)
-    if args.workload == "C5":
-        cfg["regular_sampling"] = False
+
+    def config_for(regular):
+        cfg = make_config(args.workload, workdir, n=args.n or None, regular_sampling=regular,
+                          surface_aware=args.surface_aware)
+        if args.workload == "C5":
+            cfg["regular_sampling"] = False
+        return cfg
+
+    cfg = config_for(not args.jitter)
     spp = int(cfg["spp"])
     host_cores = os.cpu_count() or 1
-    workload = WORKLOAD_TEXT[args.workload] + (f" [edge overridden to {args.n}]" if args.n else "")
-    workload += ", regular_sampling=%s" % str(bool(cfg["regular_sampling"])).lower()
-    if args.surface_aware:
-        workload += ", surface-aware discretization (2-channel film, target mesh traced)"
+
+    def workload_text(c):
+        w = WORKLOAD_TEXT[args.workload] + (f" [edge overridden to {args.n}]" if args.n else "")
+        w += ", regular_sampling=%s" % str(bool(c["regular_sampling"])).lower()
+        if args.surface_aware:
+            w += ", surface-aware discretization (2-channel film, target mesh traced)"
+        return w
+
+    workload = workload_text(cfg)
 
     # ------------------------------------------------------------ reference arm (CPU)
     if args.impl == "reference":
@@ -193,9 +241,11 @@ def main():
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": full_rays / value * 1e3,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": {"workload": workload, "rays_per_step": full_rays, "gpus_used": 0, "note": "reference's Dr.Jit LLVM path is unavailable on this box "
-                       "(mitsuba/drjit not installable); this is the CPU oracle port, fp32, OpenMP over rays; "
-                       "ms_per_step extrapolated from the bounded sample to the full step"},
+            "config": {"workload": workload, "rays_per_step": full_rays, "gpus_used": 0,
+                       "note": "the reference's Dr.Jit LLVM path is unavailable on this box (mitsuba/drjit not "
+                               "installable); this is the CPU oracle PORT, fp32, OpenMP over rays with one "
+                               "`omp atomic` per deposit (an untuned baseline); every step times a bounded sample "
+                               "of whole angles and ms_per_step is EXTRAPOLATED from it to the full step"},
             "cpu_baseline": {"value": value, "unit": "rays/s", "cores": host_cores, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0,
@@ -215,197 +265,340 @@ def main():
     import drtvam_b200 as dv
     from drtvam_b200 import _lib
     from drtvam_b200.integrators import VolumeIntegrator
+    from drtvam_b200.lbfgs import LinearLBFGS
     from drtvam_b200.loss import LazyAxpy, ThresholdedLoss
     from drtvam_b200.optimize import load_scene
+    from drtvam_b200 import parallel
     from drtvam_b200.utils import discretize
 
     lib = _lib.load()
-    scene = dv.load_dict(load_scene(cfg), device=dev)
-    scene.force_general = bool(args.general)
-    integ = VolumeIntegrator({"max_depth": cfg["max_depth"], "rr_depth": cfg["rr_depth"],
-                              "regular_sampling": cfg["regular_sampling"], "print_time": 1.0})
-    sensor = scene.sensor("sensor")
-    desc_full = scene.describe(integ, sensor)
-    n_active_total = scene.projector.active_size()
-    if sensor.film().surface_aware:
-        target = sensor.compute_volume(scene)     # sensor.py:47-110, once per run (optimize.py:131-134)
-    else:
-        target = discretize(scene, sensor=sensor)
-    if world > 1:
-        scene.shard(rank, world)
-    elif args.emulate_shard > 1:
-        scene.shard(0, args.emulate_shard)
-        scene.world_size = 1
-        workload += f" [rank 0's shard of {args.emulate_shard}, profiling aid]"
-    n_local = scene.projector.active_size()
-    pixels = scene.projector.active_pixels
-    loss_fn = ThresholdedLoss({})
-
-    gen = torch.Generator(device=dev).manual_seed(1234 + rank)
-    # dense, strictly non-zero inputs so that no ray is skipped
-    p_dev = (torch.rand(n_local, device=dev, generator=gen) * 2e-3 + 1e-4)
-    d_dev = (torch.rand(n_local, device=dev, generator=gen) - 0.5) * 1e-3
-    d_dev = torch.where(d_dev == 0, torch.full_like(d_dev, 1e-4), d_dev)
-    p_host = p_dev.cpu().pin_memory()
-    d_host = d_dev.cpu().pin_memory()
-    g_host = torch.empty(n_local, dtype=torch.float32).pin_memory()
-
-    def step(seed, p, d, record=False, d_ready=None, on_grad=None):
-        """One L-BFGS iteration's projections on device-resident inputs.  `d_ready` (an event) is
-        waited for before A d reads the search direction; `on_grad` sees the pattern gradient as soon
-        as the adjoint is queued (the end-to-end loop uses both to overlap its copies)."""
-        p = p.detach().requires_grad_(True)
-        scene.projector.active_data = p
-        integ.events = pass_events if record else None
-        prm = dv.traverse(scene)
-        vol = dv.render(scene, prm, integrator=integ, sensor=sensor, spp=spp, seed=seed)
-        loss = loss_fn(vol, target, p)
-        loss.backward()                                     # adjoint A^T g
-        if on_grad is not None:
-            on_grad(p.grad)
-        with torch.no_grad():
-            if d_ready is not None:
-                torch.cuda.current_stream(dev).wait_event(d_ready)
-            scene.projector.active_data = d
-            dvol = dv.render(scene, None, integrator=integ, sensor=sensor, spp=spp, seed=seed)   # A d
-            f_new = loss_fn(LazyAxpy(vol.detach(), dvol, 1.0), target, d)                        # Armijo trial
-        return loss.detach(), f_new, p.grad
-
-    pass_events = {}
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize(dev)
 
-    for i in range(args.warmup):
-        step(i, p_dev, d_dev)
-    barrier()
+    def rel_l2(a, b):
+        return float(torch.linalg.norm((a.double() - b.double())) / torch.linalg.norm(b.double()).clamp_min(1e-300))
 
-    clocks = ClockSampler(local_rank) if rank == 0 else None
-    launches0 = lib.drtvam_launch_count()
-    t0 = torch.cuda.Event(enable_timing=True)
-    t1 = torch.cuda.Event(enable_timing=True)
-    barrier()
-    torch.cuda.cudart().cudaProfilerStart()   # ncu --profile-from-start off: only the timed steps are listed
-    t0.record()
-    for i in range(args.steps):
-        out = step(100 + i, p_dev, d_dev, record=True)
-    t1.record()
-    barrier()
-    torch.cuda.cudart().cudaProfilerStop()
-    ms = t0.elapsed_time(t1)
-    launches = lib.drtvam_launch_count() - launches0
-    clock_info = clocks.stop() if clocks else None
+    def setup(c):
+        """Scene, integrator, sensor, loss target and (N > 1) the shard of this rank."""
+        scene = dv.load_dict(load_scene(c), device=dev)
+        scene.force_general = bool(args.general)
+        integ = VolumeIntegrator({"max_depth": c["max_depth"], "rr_depth": c["rr_depth"],
+                                  "regular_sampling": c["regular_sampling"], "print_time": 1.0})
+        sensor = scene.sensor("sensor")
+        desc_full = scene.describe(integ, sensor)
+        n_total = scene.projector.active_size()
+        if sensor.film().surface_aware:
+            target = sensor.compute_volume(scene)     # sensor.py:47-110, once per run (optimize.py:131-134)
+        else:
+            target = discretize(scene, sensor=sensor)
+        return scene, integ, sensor, desc_full, n_total, target
 
-    # end to end: host (pinned) inputs copied in and results copied out every step.  The patterns are
-    # uploaded on the compute stream (A p needs all of them); the search direction is uploaded and the
-    # pattern gradient downloaded on a copy stream, under A p / A^T g and under A d respectively.
-    # Every copy of step i is issued and completed inside step i (no prefetch across steps).
-    barrier()
-    main_stream = torch.cuda.current_stream(dev)
-    copy_stream = torch.cuda.Stream(dev)
-    e0 = torch.cuda.Event(enable_timing=True)
-    e1 = torch.cuda.Event(enable_timing=True)
-    e0.record()
-    loss_host = 0.0
-    for i in range(args.steps):
-        copy_stream.wait_stream(main_stream)                 # step i's copies start with step i
-        p_in = p_host.to(dev, non_blocking=True)
-        d_ready = torch.cuda.Event()
-        with torch.cuda.stream(copy_stream):
-            d_in = d_host.to(dev, non_blocking=True)
-            d_ready.record(copy_stream)
-        d_in.record_stream(main_stream)
+    def verify_multi_gpu(scene, integ, sensor, n_total, c_spp):
+        """N-rank result == 1-rank result, on hardware, before the timed loop: every rank draws the SAME full
+        pattern vector and dose gradient; rank 0 projects them unsharded (no collective), then all ranks
+        project their shards; the reduced dose and the concatenated pattern gradient must match."""
+        gen = torch.Generator(device=dev).manual_seed(4242)
+        p_full = torch.rand(n_total, device=dev, generator=gen) * 2e-3 + 1e-4
+        film_shape = tuple(sensor.film().shape)
+        g_full = torch.randn(film_shape, device=dev, generator=gen)
+        ref = {}
+        if rank == 0:
+            with torch.no_grad():
+                scene.projector.active_data = p_full
+                ref["dose"] = integ._project(scene, sensor, 77, c_spp, p_full).clone()
+                ref["grad"] = integ.render_backward(scene, None, g_full, sensor, 77, c_spp).clone()
+        return p_full, g_full, ref
 
-        def download(grad):
-            copy_stream.wait_stream(main_stream)             # after the adjoint
-            grad.record_stream(copy_stream)
-            with torch.cuda.stream(copy_stream):
-                g_host.copy_(grad, non_blocking=True)
+    def measure(c, steps, warmup, headline):
+        """Times `steps` projection steps of config `c`; returns a dict of numbers."""
+        c_spp = int(c["spp"])
+        scene, integ, sensor, desc_full, n_total, target = setup(c)
+        check = None
+        verify = world > 1 and headline and not args.no_verify
+        if verify:
+            p_full, g_full, ref = verify_multi_gpu(scene, integ, sensor, n_total, c_spp)
+        partition = "single"
+        if world > 1:
+            partition = scene.shard(rank, world, partition=args.partition, integrator=integ, sensor=sensor)[2]
+        elif args.emulate_shard > 1:
+            partition = scene.shard(0, args.emulate_shard, partition=args.partition, integrator=integ,
+                                    sensor=sensor)[2]
+            scene.world_size = 1
+        n_local = scene.projector.active_size()
+        pixels = scene.projector.active_pixels
+        if verify:
+            with torch.no_grad():
+                idx = scene.shard_index                      # positions of this rank's entries in the full vector
+                p_loc = p_full[idx].contiguous()
+                scene.projector.active_data = p_loc
+                dose_n = integ._project(scene, sensor, 77, c_spp, p_loc)
+                dose_n = scene.gather_dose(dose_n)           # identity when every rank holds the full dose
+                grad_loc = integ.render_backward(scene, None, scene.local_dose_grad(g_full), sensor, 77, c_spp)
+                grad_n = torch.zeros(n_total, device=dev)
+                grad_n[idx] = grad_loc
+                dist.all_reduce(grad_n)
+                if rank == 0:
+                    check = {"partition": partition, "ranks": world,
+                             "dose_rel_l2_vs_1_rank": rel_l2(dose_n, ref["dose"]),
+                             "grad_rel_l2_vs_1_rank": rel_l2(grad_n, ref["grad"]), "bound": 1e-6}
+                    check["ok"] = bool(check["dose_rel_l2_vs_1_rank"] <= 1e-6 and check["grad_rel_l2_vs_1_rank"] <= 1e-6)
+            del p_full, g_full, ref, dose_n, grad_n
+            torch.cuda.empty_cache()
+        loss_fn = ThresholdedLoss({})
+        if world > 1:
+            loss_fn.dose_allsum = scene.dose_allsum()         # z-slab sharding: the dose term is a sharded sum
+        target_loc = scene.local_target(target)
 
-        loss, f_new, grad = step(100 + i, p_in, d_in, d_ready=d_ready, on_grad=download)
-        main_stream.wait_stream(copy_stream)                 # the gradient is on the host before the step ends
-        loss_host = float(loss)                              # D2H of the scalar: syncs the step
-    e1.record()
-    barrier()
-    ms_e2e = e0.elapsed_time(e1)
+        gen = torch.Generator(device=dev).manual_seed(1234 + rank)
+        # dense, strictly non-zero inputs so that no ray is skipped
+        p_dev = (torch.rand(n_local, device=dev, generator=gen) * 2e-3 + 1e-4)
+        d_dev = (torch.rand(n_local, device=dev, generator=gen) - 0.5) * 1e-3
+        d_dev = torch.where(d_dev == 0, torch.full_like(d_dev, 1e-4), d_dev)
+        pass_events = {}
 
-    times = torch.tensor([ms, ms_e2e], device=dev, dtype=torch.float64)
+        def step(seed, p, d, record=False, d_ready=None, on_grad=None):
+            """One L-BFGS iteration's projections on device-resident inputs.  `d_ready` (an event) is
+            waited for before A d reads the search direction; `on_grad` sees the pattern gradient as soon
+            as the adjoint is queued (the end-to-end loop uses both to overlap its copies)."""
+            p = p.detach().requires_grad_(True)
+            scene.projector.active_data = p
+            integ.events = pass_events if record else None
+            prm = dv.traverse(scene)
+            vol = dv.render(scene, prm, integrator=integ, sensor=sensor, spp=c_spp, seed=seed)
+            loss = loss_fn(vol, target_loc, p)
+            loss.backward()                                     # adjoint A^T g
+            if on_grad is not None:
+                on_grad(p.grad)
+            with torch.no_grad():
+                if d_ready is not None:
+                    torch.cuda.current_stream(dev).wait_event(d_ready)
+                scene.projector.active_data = d
+                dvol = dv.render(scene, None, integrator=integ, sensor=sensor, spp=c_spp, seed=seed)   # A d
+                f_new = loss_fn(LazyAxpy(vol.detach(), dvol, 1.0), target_loc, d)                      # Armijo trial
+            return loss.detach(), f_new, p.grad
+
+        for i in range(warmup):
+            step(i, p_dev, d_dev)
+        barrier()
+
+        clocks = ClockSampler(local_rank) if (rank == 0 and headline) else None
+        launches0 = lib.drtvam_launch_count()
+        t0 = torch.cuda.Event(enable_timing=True)
+        t1 = torch.cuda.Event(enable_timing=True)
+        barrier()
+        if headline:
+            torch.cuda.cudart().cudaProfilerStart()   # ncu --profile-from-start off: only the timed steps are listed
+        t0.record()
+        for i in range(steps):
+            out = step(100 + i, p_dev, d_dev, record=True)
+        t1.record()
+        barrier()
+        if headline:
+            torch.cuda.cudart().cudaProfilerStop()
+        ms = t0.elapsed_time(t1)
+        launches = lib.drtvam_launch_count() - launches0
+        clock_info = clocks.stop() if clocks else None
+        res = {"ms": ms, "launches": launches, "clocks": clock_info, "loss": float(out[0]), "check": check,
+               "partition": partition, "n_local": n_local, "n_total": n_total, "spp": c_spp}
+
+        def mean_ms(name):
+            ev = pass_events.get(name, [])
+            return sum(a.elapsed_time(b) for a, b in ev) / max(1, len(ev))
+        res["fwd_ms"], res["adj_ms"], res["ar_ms"] = mean_ms("forward"), mean_ms("adjoint"), mean_ms("allreduce")
+        h = scene.handle(integ, sensor)
+        res["plan"] = int(lib.drtvam_scene_plan(h, n_local, c_spp))
+
+        if headline:
+            # end to end: host (pinned) inputs copied in and results copied out every step.  The patterns are
+            # uploaded on the compute stream (A p needs all of them); the search direction is uploaded and the
+            # pattern gradient downloaded on a copy stream, under A p / A^T g and under A d respectively.
+            # Every copy of step i is issued and completed inside step i (no prefetch across steps).
+            p_host = p_dev.cpu().pin_memory()
+            d_host = d_dev.cpu().pin_memory()
+            g_host = torch.empty(n_local, dtype=torch.float32).pin_memory()
+            barrier()
+            main_stream = torch.cuda.current_stream(dev)
+            copy_stream = torch.cuda.Stream(dev)
+            e0 = torch.cuda.Event(enable_timing=True)
+            e1 = torch.cuda.Event(enable_timing=True)
+            e0.record()
+            loss_host = 0.0
+            for i in range(steps):
+                copy_stream.wait_stream(main_stream)                 # step i's copies start with step i
+                p_in = p_host.to(dev, non_blocking=True)
+                d_ready = torch.cuda.Event()
+                with torch.cuda.stream(copy_stream):
+                    d_in = d_host.to(dev, non_blocking=True)
+                    d_ready.record(copy_stream)
+                d_in.record_stream(main_stream)
+
+                def download(grad):
+                    copy_stream.wait_stream(main_stream)             # after the adjoint
+                    grad.record_stream(copy_stream)
+                    with torch.cuda.stream(copy_stream):
+                        g_host.copy_(grad, non_blocking=True)
+
+                loss, f_new, grad = step(100 + i, p_in, d_in, d_ready=d_ready, on_grad=download)
+                main_stream.wait_stream(copy_stream)                 # the gradient is on the host before the step ends
+                loss_host = float(loss)                              # D2H of the scalar: syncs the step
+            e1.record()
+            barrier()
+            res["ms_e2e"] = e0.elapsed_time(e1)
+            res["loss"] = loss_host
+            n_vis = _lib.C.c_uint64(0)
+            _lib.check(lib.drtvam_count_visits(h, pixels.data_ptr(), n_local, c_spp, 100, _lib.C.byref(n_vis)))
+            res["visits"] = int(n_vis.value)
+            res["film_elems"] = int(np.prod(desc_full.film_shape()))
+            res["desc"] = desc_full
+
+            if not args.no_lbfgs:
+                # a whole LinearLBFGS iteration as optimize() runs it (optimize.py:286-320): A p, loss,
+                # backward, history + two-loop recursion, A d, Armijo search, pattern update, clamp
+                state = {"i": 0}
+
+                def render_fn(vars_):
+                    scene.projector.active_data = vars_["projector.active_data"].detach()
+                    return dv.render(scene, None, integrator=integ, sensor=sensor, spp=c_spp, seed=state["i"])
+
+                def loss2(y, patterns):
+                    return loss_fn(y, target_loc, patterns)
+                loss2.accepts_lazy = True
+                opt = LinearLBFGS(loss_fn=loss2, render_fn=render_fn, dot=parallel.make_dot(None, world))
+                opt["projector.active_data"] = p_dev.clone()
+                it_ev = []
+                n_it = warmup + steps
+                for i in range(n_it):
+                    state["i"] = i
+                    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    a.record()
+                    p = opt["projector.active_data"]
+                    scene.projector.active_data = p
+                    prm = dv.traverse(scene)
+                    vol = dv.render(scene, prm, integrator=integ, sensor=sensor, spp=c_spp, seed=i)
+                    loss = loss_fn(vol, target_loc, p)
+                    loss.backward()
+                    opt.step(vol.detach(), loss.detach())
+                    opt["projector.active_data"] = torch.clamp_min(opt["projector.active_data"].detach(), 0)
+                    b.record()
+                    it_ev.append((a, b, opt.last_trials))
+                barrier()
+                its = sorted(a.elapsed_time(b) for a, b, _ in it_ev[warmup:])
+                res["lbfgs_ms_median"] = its[len(its) // 2]
+                res["lbfgs_trials_mean"] = sum(t for _, _, t in it_ev[warmup:]) / max(1, len(it_ev) - warmup)
+        scene.close()
+        del scene, target, target_loc, p_dev, d_dev
+        torch.cuda.empty_cache()
+        return res
+
+    R = measure(cfg, args.steps, args.warmup, headline=True)
+
+    D = None
+    if not args.no_default_sampling and cfg["regular_sampling"] and args.workload != "C5":
+        D = measure(config_for(False), max(2, min(args.steps, 5)), 3, headline=False)
+
+    times = torch.tensor([R["ms"], R["ms_e2e"], D["ms"] if D else 0.0, R.get("lbfgs_ms_median", 0.0)], device=dev,
+                         dtype=torch.float64)
     if world > 1:
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
-    ms, ms_e2e = times.tolist()
+    ms, ms_e2e, ms_default, ms_lbfgs = times.tolist()
 
+    n_active_total, n_local = R["n_total"], R["n_local"]
     rays_per_step = 3 * n_active_total * spp
     value = rays_per_step * args.steps / (ms * 1e-3)
     e2e_value = rays_per_step * args.steps / (ms_e2e * 1e-3)
 
-    # roofline of the dominant kernel (forward dose scatter)
-    def mean_ms(name):
-        ev = pass_events.get(name, [])
-        return sum(a.elapsed_time(b) for a, b in ev) / max(1, len(ev))
-    fwd_ms, adj_ms, ar_ms = mean_ms("forward"), mean_ms("adjoint"), mean_ms("allreduce")
-    n_vis = _lib.C.c_uint64(0)
-    h = scene.handle(integ, sensor)
-    _lib.check(lib.drtvam_count_visits(h, pixels.data_ptr(), n_local, spp, 100, _lib.C.byref(n_vis)))
-    visits = int(n_vis.value)
+    # ---- roofline of the dominant kernel family: the forward projection A p (SURVEY.md 8(d))
+    fwd_ms, adj_ms, ar_ms, visits, plan_now = R["fwd_ms"], R["adj_ms"], R["ar_ms"], R["visits"], R["plan"]
     peak, how = measured_peaks()
-    achieved = 4.0 * visits / (fwd_ms * 1e-3) * 1e-9
-    hbm_alg_bytes = 4.0 * n_local * 2 + 4.0 * int(np.prod(desc_full.film_shape()))
-    # DRAM bytes of the forward pass from ncu --set full (profiles/r01final_planar_ncu_details.txt:
-    # planarg_kernel<4> 5.99 GB read + 0.32 GB written, tail kernel planarg_kernel<1> 1.36 + 0.01 GB; pack kernel
-    # 0.26 + 0.23 GB, profiles/r01o_planar_ncu_details.txt); only quoted for the workload and kernel family it
-    # was captured on
-    plan_now = int(lib.drtvam_scene_plan(h, n_local, spp))
-    traffic = 8.2e9 if (args.workload == "C2" and not args.n and plan_now == 2 and world == 1) else None
+    # algorithmic HBM bytes of one forward pass of this rank: pattern values + pixel indices read once, the
+    # (local part of the) dose volume written once
+    film_local = R["film_elems"] if R["partition"] != "zslab" else R["film_elems"] // max(world, 1)
+    hbm_alg_bytes = 4.0 * n_local * 2 + 4.0 * film_local
+    achieved = hbm_alg_bytes / (fwd_ms * 1e-3) * 1e-9
+    visits_per_s = visits / (fwd_ms * 1e-3)
+    atomic_key = {2: "smem_lds_fadd_sts", 3: "smem_atoms_f32_cas", 1: "smem_atoms_f32_cas"}.get(plan_now,
+                                                                                                "red_f32_scattered_l2")
+    traffic, traffic_src = measured_traffic(args.workload, plan_now, world, args.n)
     roofline = {
-        "bound": "hbm", "kernel": "forward projection (A p): zpack + planarg_kernel patch gather"
-        if plan_now == 2 else "forward projection (A p)", "achieved": achieved, "peak": peak, "unit": "GB/s",
-        "frac": achieved / peak, "traffic": traffic, "peak_source": how,
-        "note": "achieved = 4 B per voxel visit (SURVEY 8(d)) / pass time; the visits are accumulated in registers / "
-                "shared memory, so the figure can exceed the HBM copy peak; traffic = measured DRAM bytes per pass. "
-                "ncu on the patch-gather kernel (profiles/r01final_planar_ncu_details.txt): issue slots 65 % busy, FMA "
-                "pipe 28 %, DRAM 0.7 TB/s - the pass is bound by dependent shared-memory latency at 24 warps/SM, "
-                "not by HBM; against the measured shared-memory ld+add+st rate (2.34e12/s, "
-                "profiles/r01_microbench_atomics.json) the 2.75e12 visits/s are 1.17x",
-        "algorithmic_bytes_per_visit": 4, "visits_per_launch": visits, "kernel_ms": fwd_ms,
-        "adjoint_ms": adj_ms, "adjoint_achieved": 4.0 * visits / (adj_ms * 1e-3) * 1e-9 if adj_ms else None,
-        "allreduce_ms": ar_ms,
-        "hbm_algorithmic_gb": hbm_alg_bytes * 1e-9, "hbm_floor_frac": hbm_alg_bytes * 1e-9 / (fwd_ms * 1e-3) / peak,
-        "plan": int(lib.drtvam_scene_plan(h, n_local, spp)),
+        "bound": "issue slots / shared-memory latency (ncu: see `evidence`); neither HBM nor tensor",
+        "kernel": {2: "forward projection A p: zpack + planarg_kernel (patch gather, register accumulators)",
+                   3: "forward projection A p: planar per-lane kernels (jittered rays)",
+                   0: "forward projection A p: general per-lane tracer"}.get(plan_now, "forward projection A p"),
+        "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+        "traffic": traffic, "traffic_source": traffic_src, "peak_source": how,
+        "frac_hbm": achieved / peak, "hbm_algorithmic_bytes": hbm_alg_bytes,
+        "frac_atomic": visits_per_s / ATOMIC_PEAKS[atomic_key][0],
+        "atomic_peak": {"name": atomic_key, "ops_per_s": ATOMIC_PEAKS[atomic_key][0], "what": ATOMIC_PEAKS[atomic_key][1],
+                        "source": "profiles/r01_microbench_atomics.json (csrc/microbench.cu)"},
+        "visits_per_launch": visits, "visits_per_s": visits_per_s, "kernel_ms": fwd_ms,
+        "adjoint_ms": adj_ms, "adjoint_visits_per_s": visits / (adj_ms * 1e-3) if adj_ms else None,
+        "allreduce_ms": ar_ms, "plan": plan_now,
+        "note": "achieved = algorithmic HBM bytes of one forward pass (pattern values + pixel indices read, dose "
+                "written) / CUDA-event time of the pass, against the measured copy peak: the pass is far from the "
+                "HBM roof because its work is 478 voxel visits per ray on data that stays on chip.  frac_atomic "
+                "= voxel visits per second / the measured peak of the on-chip update it would otherwise need "
+                "(SURVEY 8(d)); plan 2 keeps its accumulators in registers, so it can exceed 1.",
+        "evidence": "profiles/ (ncu --set full details and launch lists of this round, named r02*)",
     }
 
     line = None
     if rank == 0:
         cpu_baseline = None
         if not args.no_cpu_baseline and world == 1:
-            rps, rays, t, n_ang = oracle_sample(cfg, desc_full, args.cpu_seconds, threads=host_cores)
+            rps, rays, t, n_ang = oracle_sample(cfg, R["desc"], args.cpu_seconds, threads=host_cores)
+            d_ = R["desc"]
             cpu_baseline = {"value": rps, "unit": "rays/s", "cores": host_cores, "kind": "port",
-                            "sample": f"{n_ang} of {desc_full.n_patterns} angles x {desc_full.res_x}x{desc_full.res_y} "
-                                      f"rays, 3 passes, {t:.1f} s of oracle (fp32, OpenMP) time"}
+                            "sample": f"{n_ang} of {d_.n_patterns} angles x {d_.res_x}x{d_.res_y} "
+                                      f"rays, 3 passes, {t:.1f} s of oracle (fp32, OpenMP, omp atomic per deposit) time; "
+                                      "whole-step figures derived from it are extrapolations"}
+        par = {"single": "1 GPU", "angle": f"angle-sharded x{world}, 1 all_reduce(dose) per forward",
+               "zslab": f"z-slab / DMD-row sharded x{world}: every rank owns {1}/{world} of the layers for all angles, "
+                        "no dose collective, scalar all-reduces for the loss and the L-BFGS dots"}[R["partition"]]
         line = {
             "metric": "rays_per_s", "value": value, "unit": "rays/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms / args.steps, "sec_per_lbfgs_iter": ms / args.steps * 1e-3,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "sec_per_projection_step": ms / args.steps * 1e-3,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": workload, "rays_per_step": rays_per_step,
                        "step": "A p + thresholded loss + A^T g + A d + 1 Armijo trial (one L-BFGS iteration's "
                                "projections), dense non-zero patterns",
                        "l2": "inputs (patterns 256 MB, dose 256 MB at C2) exceed the 126 MB L2",
-                       "parallelism": f"angle-sharded x{world}, 1 all_reduce(dose) per forward" if world > 1 else "1 GPU"},
-            "clocks": clock_info,
+                       "parallelism": par},
+            "clocks": R["clocks"],
             "e2e": {"value": e2e_value, "unit": "rays/s", "ms_per_step": ms_e2e / args.steps,
                     "h2d_bytes_per_step": 8 * n_local, "d2h_bytes_per_step": 4 * n_local + 4},
-            "gpu_launches": int(launches),
+            "gpu_launches": int(R["launches"]),
             "roofline": roofline,
             "cpu_baseline": cpu_baseline,
-            "loss": loss_host,
+            "loss": R["loss"],
         }
+        if D is not None:
+            line["default_sampling"] = {
+                "workload": workload_text(config_for(False)), "ms_per_step": ms_default / D_steps(args),
+                "fwd_ms": D["fwd_ms"], "adj_ms": D["adj_ms"], "allreduce_ms": D["ar_ms"], "plan": D["plan"],
+                "steps": D_steps(args), "rays_per_s": rays_per_step * D_steps(args) / (ms_default * 1e-3),
+                "note": "the identical step with regular_sampling=false, the reference's default "
+                        "(integrators/common.py:22): every ray has its own pixel jitter"}
+        if "lbfgs_ms_median" in R:
+            line["lbfgs_iteration"] = {
+                "ms_median": ms_lbfgs, "armijo_trials_mean": R["lbfgs_trials_mean"],
+                "what": "one whole LinearLBFGS iteration as optimize() runs it (optimize.py:286-320, lbfgs.py:198-275): "
+                        "A p, loss, backward, history update, two-loop recursion, A d, Armijo search, pattern update, "
+                        "clamp; median over the timed iterations"}
+        if R["check"] is not None:
+            line["multi_gpu_check"] = R["check"]
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
     return 0
+
+
+def D_steps(args):
+    return max(2, min(args.steps, 5))
 
 
 if __name__ == "__main__":

@@ -11,7 +11,7 @@ import os
 from . import build as _build
 
 MAX_SURFACES = 8
-ABI_VERSION = 7
+ABI_VERSION = 8
 
 
 class DrtvamSurface(C.Structure):
@@ -58,6 +58,14 @@ SYMBOLS = {
     "drtvam_compute_volume": (C.c_int, [_vp, _u32, _vp, _vp]),
     "drtvam_discretize": (C.c_int, [_vp, _vp, _vp]),
     "drtvam_scene_set_inv_volume": (C.c_int, [_vp, _vp]),
+    "drtvam_scene_set_z_window": (C.c_int, [_vp, _i32, _i32, C.POINTER(_i32), C.POINTER(_i32)]),
+    "drtvam_scene_set_sampler_index": (C.c_int, [_vp, _vp]),
+    "drtvam_scene_pin_pixels": (C.c_int, [_vp, _vp, _u64]),
+    "drtvam_comm_unique_id": (C.c_int, [_vp]),
+    "drtvam_comm_init": (C.c_int, [_vp, _vp, _i32, _i32]),
+    "drtvam_comm_destroy": (C.c_int, [_vp]),
+    "drtvam_allreduce_dose": (C.c_int, [_vp, _vp, _u64, _vp]),
+    "drtvam_allreduce_scalars": (C.c_int, [_vp, _vp, _u64, _vp]),
     "drtvam_scene_plan": (C.c_int, [_vp, _u64, _u32]),
     "drtvam_scene_force_general": (C.c_int, [_vp, _i32]),
     "drtvam_forward": (C.c_int, [_vp, _vp, _vp, _u64, _u32, _u32, _f32, _vp, _i32, _vp]),

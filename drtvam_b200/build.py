@@ -26,7 +26,8 @@ NVCC_FLAGS = [
     "-Xptxas", "-v",
 ]
 
-LIB_SOURCES = ["abi.cu", "general_kernels.cu", "planar_kernels.cu", "planarz_kernels.cu", "loss_kernels.cu",
+LIB_SOURCES = ["abi.cu", "general_kernels.cu", "planar_kernels.cu", "planarz_kernels.cu", "planarj_kernels.cu",
+               "loss_kernels.cu",
                "mesh_kernels.cu", "inside_kernels.cu", "filter_kernels.cu"]
 MICRO_SOURCES = ["microbench.cu"]
 
@@ -59,15 +60,33 @@ def _build_one(out: str, sources, force: bool, verbose: bool) -> bool:
             if f.read().strip() == digest:
                 return False
     os.makedirs(LIBDIR, exist_ok=True)
-    cmd = [_nvcc(), *NVCC_FLAGS, "-o", out, *srcs]
-    env = dict(os.environ)
+    objdir = os.path.join(LIBDIR, "obj")
+    os.makedirs(objdir, exist_ok=True)
     # the image exports CC=/opt/gcc/bin/gcc; nvcc needs the system host compiler
-    cmd[1:1] = ["-ccbin", "/usr/bin/g++"] if os.path.exists("/usr/bin/g++") else []
-    proc = subprocess.run(cmd, capture_output=True, text=True, env=env)
-    log = proc.stdout + proc.stderr
+    ccbin = ["-ccbin", "/usr/bin/g++"] if os.path.exists("/usr/bin/g++") else []
+    compile_flags = [f for f in NVCC_FLAGS if f != "-shared"]
+
+    def compile_one(src):
+        obj = os.path.join(objdir, os.path.basename(out) + "." + os.path.basename(src) + ".o")
+        cmd = [_nvcc(), *ccbin, *compile_flags, "-c", "-o", obj, src]
+        proc = subprocess.run(cmd, capture_output=True, text=True)
+        return obj, " ".join(cmd) + "\n" + proc.stdout + proc.stderr, proc.returncode
+
+    # one translation unit per nvcc process, all of them at once (nvcc cross-compiles without a GPU)
+    from concurrent.futures import ThreadPoolExecutor
+    with ThreadPoolExecutor(max_workers=min(len(srcs), os.cpu_count() or 4)) as pool:
+        results = list(pool.map(compile_one, srcs))
+    log = "".join(r[1] for r in results)
+    rc = max(r[2] for r in results)
+    if rc == 0:
+        cmd = [_nvcc(), *ccbin, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-Xcompiler", "-fPIC",
+               "-o", out, *[r[0] for r in results], "-ldl"]
+        proc = subprocess.run(cmd, capture_output=True, text=True)
+        log += " ".join(cmd) + "\n" + proc.stdout + proc.stderr
+        rc = proc.returncode
     with open(out + ".buildlog", "w") as f:
-        f.write(" ".join(cmd) + "\n" + log)
-    if proc.returncode != 0:
+        f.write(log)
+    if rc != 0:
         sys.stderr.write(log)
         raise RuntimeError(f"nvcc failed building {os.path.basename(out)}")
     if verbose:

@@ -1,5 +1,7 @@
 // C-ABI of the hot path (include/drtvam_b200.h): handle management, argument
 // validation, kernel-family selection, host-buffer convenience calls.
+#include <dlfcn.h>
+
 #include <atomic>
 #include <cmath>
 #include <cstdarg>
@@ -53,6 +55,8 @@ struct Scratch {
 
 using namespace drtvam;
 
+struct NcclId { char internal[128]; };   // ncclUniqueId (nccl.h: NCCL_UNIQUE_ID_BYTES = 128), passed by value
+
 struct DrtvamScene {
     int device = 0;
     SceneParams P{};
@@ -65,6 +69,15 @@ struct DrtvamScene {
     PlanarHost planar;
     PlanarZHost zplan;               // layer-parallel kernels on top of the planar tables
     PlanarGHost gplan;               // patch-gather forward on top of the layer-parallel plan
+    PlanarJHost jplan;               // jittered planar passes (regular_sampling = false)
+    // pinned pixel list (drtvam_scene_pin_pixels): verified once, then the per-call layout check and the
+    // stand-by launch of the other kernel family are skipped
+    const uint32_t* pinned_pixels = nullptr;
+    uint64_t pinned_n = 0;
+    int pinned_gate = -1;            // -1 = to be verified at the next call, 0 = planar layout, 1 = general
+    // collectives for bindings without torch.distributed (drtvam_comm_init)
+    void* nccl_comm = nullptr;
+    int comm_rank = 0, comm_world = 1;
     bool planar_tried = false;       // planar_build ran for the current depth setting
     bool planar_ok = false;
     MeshHost target;                 // target mesh (surface-aware runs only)
@@ -148,10 +161,27 @@ bool planar_static_eligible(const DrtvamScene* s) {
     return true;
 }
 
+// The sensor as the film buffers of a call see it: the z window [z_begin, z_end) of a z-slab shard as a
+// box of its own.  Used by everything that walks with the general 3-D DDA into / out of those buffers.
+SceneParams windowed(const SceneParams& P) {
+    SceneParams W = P;
+    if (P.z_begin == 0 && P.z_end == P.res[2]) return W;
+    const float vs = (P.bmax[2] - P.bmin[2]) / static_cast<float>(P.res[2]);
+    W.bmin[2] = P.bmin[2] + static_cast<float>(P.z_begin) * vs;
+    W.bmax[2] = P.bmin[2] + static_cast<float>(P.z_end) * vs;
+    W.res[2] = P.z_end - P.z_begin;
+    W.z_begin = 0;
+    W.z_end = W.res[2];
+    return W;
+}
+
+bool has_window(const SceneParams& P) { return P.z_begin != 0 || P.z_end != P.res[2] || P.n_rows != P.res_y; }
+
 int ensure_planar(DrtvamScene* s) {
     if (s->planar_tried) return DRTVAM_OK;
     s->planar_tried = true;
     s->planar_ok = false;
+    if (s->pinned_pixels) s->pinned_gate = -1;   // the plan changed: verify the pinned list again
     inside_release(s->inside);
     s->P1 = s->P;
     s->P1.surface_aware = 0;
@@ -166,6 +196,18 @@ int ensure_planar(DrtvamScene* s) {
     s->planar_ok = s->planar.valid && s->planar.flags == 0 && s->planar.n_rows_in_sensor > 0;
     planarz_release(s->zplan);
     planarg_release(s->gplan);
+    planarj_release(s->jplan);
+    if (s->planar_ok && !s->P.regular_sampling) {
+        // jittered passes: the layer tables of the layer-parallel plan (no walks) + the per-lane kernels
+        e = planarz_build(s->P1, s->planar, s->planar.row_layer, s->zplan, false);
+        if (e == cudaSuccess) e = planarj_build(s->P1, s->planar, s->zplan, s->jplan);
+        if (e != cudaSuccess) {
+            planarz_release(s->zplan);
+            planarj_release(s->jplan);
+            return fail(DRTVAM_E_CUDA, "jittered planar plan build failed: %s", cudaGetErrorString(e));
+        }
+        if (!s->jplan.valid) s->planar_ok = false;
+    }
     if (s->planar_ok && s->P.regular_sampling) {
         e = planarz_build(s->P1, s->planar, s->planar.row_layer, s->zplan);
         if (e != cudaSuccess) {
@@ -194,12 +236,39 @@ int ensure_planar(DrtvamScene* s) {
 
 bool use_planar(DrtvamScene* s, uint64_t n_active) {
     if (s->force_mode == 1 || !s->planar_ok || n_active == 0) return false;
-    const uint64_t hw = static_cast<uint64_t>(s->P.res_x) * s->P.res_y;
-    return n_active % hw == 0;
+    if (s->force_mode == 2 && has_window(s->P)) return false;   // the per-ray tile DDA (A/B tests) knows no window
+    const uint64_t rw = static_cast<uint64_t>(s->P.res_x) * s->P.n_rows;
+    return n_active % rw == 0;
 }
 
+// elements of the film buffers of a call: the layers of the z window (all of them by default)
 size_t film_elems(const DrtvamScene* s) {
-    return static_cast<size_t>(s->P.res[0]) * s->P.res[1] * s->P.res[2] * (s->P.surface_aware ? 2 : 1);
+    return static_cast<size_t>(s->P.res[0]) * s->P.res[1] * (s->P.z_end - s->P.z_begin) * (s->P.surface_aware ? 2 : 1);
+}
+
+// Layout gate of a planar call.  Returns the device gate word the kernels of the call read and sets
+// `host_gate`: 0 = the list is known to have the planar layout (only planar kernels are launched),
+// 1 = known not to (only the general tracer), -1 = decided on the device (both families are launched,
+// the one that does not own the call exits in its first instruction).
+cudaError_t planar_gate(DrtvamScene* s, const uint32_t* active_pixels, uint64_t n_active, cudaStream_t st,
+                        const int** gate, int* host_gate) {
+    *gate = s->planar.gate;
+    *host_gate = -1;
+    if (active_pixels == s->pinned_pixels && n_active == s->pinned_n) {
+        if (s->pinned_gate < 0) {   // first call after the pin or after a plan rebuild: verify once, synchronously
+            cudaError_t e = launch_planar_check(s->P1, s->planar, active_pixels, n_active, st);
+            if (e != cudaSuccess) return e;
+            int g = 0;
+            e = cudaMemcpyAsync(&g, s->planar.gate, sizeof(int), cudaMemcpyDeviceToHost, st);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+            if (e != cudaSuccess) return e;
+            s->pinned_gate = g != 0 ? 1 : 0;
+        }
+        *host_gate = s->pinned_gate;
+        *gate = s->planar.gate + 3;   // a word that is always 0: the planar kernels own the call
+        return cudaSuccess;
+    }
+    return launch_planar_check(s->P1, s->planar, active_pixels, n_active, st);
 }
 
 }  // namespace
@@ -284,6 +353,8 @@ int drtvam_scene_create(const DrtvamSceneDesc* d, int device, DrtvamScene** out)
     }
     for (int a = 0; a < 3; ++a) { P.bmin[a] = d->bbox_min[a]; P.bmax[a] = d->bbox_max[a]; P.res[a] = d->res[a]; }
     P.surface_aware = d->surface_aware; P.sensor_kind = d->sensor_kind; P.majorant = d->majorant;
+    P.z_begin = 0; P.z_end = d->res[2]; P.row_begin = 0; P.n_rows = d->res_y;
+    P.sampler_index = nullptr;
     P.motion_table = nullptr;
     if (d->motion_table_host) {
         const size_t bytes = sizeof(float) * 12 * static_cast<size_t>(d->n_patterns);
@@ -307,12 +378,14 @@ int drtvam_scene_create(const DrtvamSceneDesc* d, int device, DrtvamScene** out)
 
 void drtvam_scene_destroy(DrtvamScene* s) {
     if (!s) return;
+    drtvam_comm_destroy(s);
     DeviceGuard guard(s->device);
     if (s->motion_dev) cudaFree(s->motion_dev);
     if (s->counter_dev) cudaFree(s->counter_dev);
     planar_release(s->planar);
     planarz_release(s->zplan);
     planarg_release(s->gplan);
+    planarj_release(s->jplan);
     inside_release(s->inside);
     mesh_release(s->target);
     for (auto& m : s->mesh_surf) mesh_release(m);
@@ -380,6 +453,171 @@ int drtvam_scene_set_inv_volume(DrtvamScene* s, const float* inv_volume) {
     return DRTVAM_OK;
 }
 
+int drtvam_scene_set_z_window(DrtvamScene* s, int32_t z_begin, int32_t z_end, int32_t* row_begin, int32_t* row_end) {
+    if (!s) return fail(DRTVAM_E_INVALID, "scene handle is NULL");
+    const int rz = s->P.res[2];
+    if (z_begin < 0 || z_end > rz || z_begin >= z_end)
+        return fail(DRTVAM_E_INVALID, "z window [%d, %d) outside [0, %d)", z_begin, z_end, rz);
+    DeviceGuard guard(s->device);
+    // the row -> layer table of the whole film decides which rows the window owns
+    s->P.z_begin = 0; s->P.z_end = rz; s->P.row_begin = 0; s->P.n_rows = s->P.res_y;
+    s->planar_tried = false;
+    if (z_begin == 0 && z_end == rz) {
+        if (row_begin) *row_begin = 0;
+        if (row_end) *row_end = s->P.res_y;
+        return DRTVAM_OK;
+    }
+    if (s->P.surface_aware) return fail(DRTVAM_E_INVALID, "a z window is not supported with a surface-aware film");
+    if (int rc = ensure_planar(s)) return rc;
+    if (!s->planar_ok)
+        return fail(DRTVAM_E_INVALID, "a z window needs a planar scene (collimated projector, rotation about z, "
+                                      "vertical vial walls, no scattering): shard by projection angle instead");
+    const std::vector<int>& rl = s->planar.row_layer;
+    const std::vector<float>& rzv = s->planar.row_z;
+    int r0 = -1, r1 = -1;
+    for (int r = 0; r < s->P.res_y; ++r) {
+        if (rl[r] < z_begin || rl[r] >= z_end) continue;
+        if (r0 < 0) r0 = r;
+        else if (r != r1) return fail(DRTVAM_E_INVALID, "the DMD rows of z window [%d, %d) are not contiguous", z_begin, z_end);
+        r1 = r + 1;
+    }
+    if (r0 < 0) return fail(DRTVAM_E_INVALID, "no DMD row deposits in z window [%d, %d)", z_begin, z_end);
+    if (!s->P.regular_sampling) {
+        // jittered rays of a row spread over the row's height: every row must lie inside ONE layer, otherwise
+        // its pattern gradient would need contributions from two windows
+        const float vs = (s->P.bmax[2] - s->P.bmin[2]) / static_cast<float>(rz);
+        const float dz = s->P.res_y > 1 ? fabsf(rzv[1] - rzv[0]) : s->P.pixel_y;
+        for (int r = r0; r < r1; ++r) {
+            const float lo = (rzv[r] - 0.5f * dz - s->P.bmin[2]) / vs, hi = (rzv[r] + 0.5f * dz - s->P.bmin[2]) / vs;
+            if (static_cast<int>(floorf(lo + 1e-3f)) != rl[r] || static_cast<int>(floorf(hi - 1e-3f)) != rl[r])
+                return fail(DRTVAM_E_INVALID, "DMD row %d straddles two voxel layers: a z window cannot own it with "
+                                              "jittered sampling; shard by projection angle instead", r);
+        }
+    }
+    s->P.z_begin = z_begin; s->P.z_end = z_end; s->P.row_begin = r0; s->P.n_rows = r1 - r0;
+    s->planar_tried = false;   // tables of the window
+    if (row_begin) *row_begin = r0;
+    if (row_end) *row_end = r1;
+    return DRTVAM_OK;
+}
+
+int drtvam_scene_pin_pixels(DrtvamScene* s, const uint32_t* active_pixels, uint64_t n_active) {
+    if (!s) return fail(DRTVAM_E_INVALID, "scene handle is NULL");
+    s->pinned_pixels = active_pixels;
+    s->pinned_n = active_pixels ? n_active : 0;
+    s->pinned_gate = -1;
+    return DRTVAM_OK;
+}
+
+int drtvam_scene_set_sampler_index(DrtvamScene* s, const uint32_t* global_index) {
+    if (!s) return fail(DRTVAM_E_INVALID, "scene handle is NULL");
+    s->P.sampler_index = global_index;
+    s->P1.sampler_index = global_index;
+    return DRTVAM_OK;
+}
+
+// ---- collectives for bindings that have no torch.distributed: NCCL, resolved at run time ------------
+namespace {
+struct NcclApi {
+    void* lib = nullptr;
+    int (*GetUniqueId)(void*) = nullptr;
+    int (*CommInitRank)(void**, int, NcclId, int) = nullptr;
+    int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    int (*CommGetAsyncError)(void*, int*) = nullptr;
+    int (*CommDestroy)(void*) = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+};
+NcclApi g_nccl;
+
+int load_nccl() {
+    if (g_nccl.lib) return DRTVAM_OK;
+    // the copy the process already uses (torch's bundled NCCL, if any) wins over the system one
+    void* lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
+    if (!lib) lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!lib) lib = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!lib) return fail(DRTVAM_E_INVALID, "NCCL not found: %s", dlerror());
+    NcclApi a;
+    a.lib = lib;
+    a.GetUniqueId = reinterpret_cast<decltype(a.GetUniqueId)>(dlsym(lib, "ncclGetUniqueId"));
+    a.CommInitRank = reinterpret_cast<decltype(a.CommInitRank)>(dlsym(lib, "ncclCommInitRank"));
+    a.AllReduce = reinterpret_cast<decltype(a.AllReduce)>(dlsym(lib, "ncclAllReduce"));
+    a.CommGetAsyncError = reinterpret_cast<decltype(a.CommGetAsyncError)>(dlsym(lib, "ncclCommGetAsyncError"));
+    a.CommDestroy = reinterpret_cast<decltype(a.CommDestroy)>(dlsym(lib, "ncclCommDestroy"));
+    a.GetErrorString = reinterpret_cast<decltype(a.GetErrorString)>(dlsym(lib, "ncclGetErrorString"));
+    if (!a.GetUniqueId || !a.CommInitRank || !a.AllReduce || !a.CommGetAsyncError || !a.CommDestroy || !a.GetErrorString)
+        return fail(DRTVAM_E_INVALID, "NCCL library lacks a required symbol");
+    g_nccl = a;
+    return DRTVAM_OK;
+}
+
+int nccl_fail(const char* what, int rc) {
+    return fail(DRTVAM_E_NCCL, "%s failed: %s", what, g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "?");
+}
+
+// ncclCommGetAsyncError: a peer that died or a network error surfaces here, not in the enqueue call
+int comm_check(DrtvamScene* s) {
+    int async = 0;
+    const int rc = g_nccl.CommGetAsyncError(s->nccl_comm, &async);
+    if (rc != 0) return nccl_fail("ncclCommGetAsyncError", rc);
+    if (async != 0 && async != 7 /* ncclInProgress */) return nccl_fail("NCCL communicator (asynchronous error)", async);
+    return DRTVAM_OK;
+}
+
+int comm_allreduce(DrtvamScene* s, void* buf, uint64_t n, int dtype, void* stream) {
+    if (!s) return fail(DRTVAM_E_INVALID, "scene handle is NULL");
+    if (!s->nccl_comm) return fail(DRTVAM_E_INVALID, "drtvam_comm_init has not been called on this handle");
+    if (!buf && n) return fail(DRTVAM_E_INVALID, "NULL buffer");
+    DeviceGuard guard(s->device);
+    if (int rc = comm_check(s)) return rc;
+    const int rc = g_nccl.AllReduce(buf, buf, n, dtype, 0 /* ncclSum */, s->nccl_comm, static_cast<cudaStream_t>(stream));
+    if (rc != 0) return nccl_fail("ncclAllReduce", rc);
+    return comm_check(s);
+}
+}  // namespace
+
+int drtvam_comm_unique_id(void* id_out) {
+    if (!id_out) return fail(DRTVAM_E_INVALID, "NULL buffer");
+    if (int rc = load_nccl()) return rc;
+    const int rc = g_nccl.GetUniqueId(id_out);
+    if (rc != 0) return nccl_fail("ncclGetUniqueId", rc);
+    return DRTVAM_OK;
+}
+
+int drtvam_comm_init(DrtvamScene* s, const void* unique_id, int32_t rank, int32_t world) {
+    if (!s) return fail(DRTVAM_E_INVALID, "scene handle is NULL");
+    if (!unique_id || world < 1 || rank < 0 || rank >= world) return fail(DRTVAM_E_INVALID, "bad rank / world / id");
+    if (s->nccl_comm) return fail(DRTVAM_E_INVALID, "the handle already has a communicator");
+    if (int rc = load_nccl()) return rc;
+    DeviceGuard guard(s->device);
+    NcclId id;
+    memcpy(&id, unique_id, sizeof(id));
+    void* comm = nullptr;
+    const int rc = g_nccl.CommInitRank(&comm, world, id, rank);
+    if (rc != 0) return nccl_fail("ncclCommInitRank", rc);
+    s->nccl_comm = comm;
+    s->comm_rank = rank;
+    s->comm_world = world;
+    return comm_check(s);
+}
+
+int drtvam_comm_destroy(DrtvamScene* s) {
+    if (!s) return fail(DRTVAM_E_INVALID, "scene handle is NULL");
+    if (!s->nccl_comm) return DRTVAM_OK;
+    DeviceGuard guard(s->device);
+    const int rc = g_nccl.CommDestroy(s->nccl_comm);
+    s->nccl_comm = nullptr;
+    if (rc != 0) return nccl_fail("ncclCommDestroy", rc);
+    return DRTVAM_OK;
+}
+
+int drtvam_allreduce_dose(DrtvamScene* s, float* dose, uint64_t n, void* stream) {
+    return comm_allreduce(s, dose, n, 7 /* ncclFloat32 */, stream);
+}
+
+int drtvam_allreduce_scalars(DrtvamScene* s, double* values, uint64_t n, void* stream) {
+    return comm_allreduce(s, values, n, 8 /* ncclFloat64 */, stream);
+}
+
 int drtvam_compute_volume(DrtvamScene* s, uint32_t sample_count, float* volumes, void* stream) {
     if (!s) return fail(DRTVAM_E_INVALID, "scene handle is NULL");
     if (!volumes || sample_count == 0) return fail(DRTVAM_E_INVALID, "NULL buffer or zero sample count");
@@ -419,37 +657,42 @@ int drtvam_forward(DrtvamScene* s, const float* active_data, const uint32_t* act
     if (int rc = ensure_planar(s)) return rc;
     if (s->inv_volume && !zero_first)
         return fail(DRTVAM_E_INVALID, "an accumulating forward call cannot apply the per-voxel inverse volume");
+    const SceneParams Pw = windowed(s->P);
     if (use_planar(s, n_active)) {
-        // the device decides: gate = 0 -> planar kernels, gate != 0 -> general tracer
-        const bool sa = s->inside.valid;  // surface-aware: the planar kernels fill a one-channel plane
-        const SceneParams& P1 = s->P1;
-        float* plane = sa ? s->inside.planes : dose;
-        if (sa) CUDA_TRY(inside_forward_begin(s->inside, st));
-        CUDA_TRY(launch_planar_check(P1, s->planar, active_pixels, n_active, st));
-        if (!P1.regular_sampling)
-            CUDA_TRY(launch_planar_lane_forward(P1, s->planar, active_data, active_pixels, n_active, spp, seed, w, plane,
-                                                st));
-        else if (s->zplan.valid && s->gplan.valid && s->force_mode != 2)
-            // fresh: the plane was cleared above (zero_first, or the planes of a surface-aware scene) and
-            // the patch gather is its first writer, so it stores instead of read-add-write
-            CUDA_TRY(launch_planarg_forward(P1, s->zplan, s->gplan, s->planar.gate, active_data, active_pixels,
-                                            n_active, w, plane, sa || zero_first != 0, st));
-        else if (s->zplan.valid && s->force_mode != 2)
-            CUDA_TRY(launch_planarz_forward(P1, s->zplan, s->planar.gate, active_data, active_pixels, n_active, w, plane,
-                                            st));
-        else
-            CUDA_TRY(launch_planar_forward(P1, s->planar, active_data, active_pixels, n_active, w, plane, st));
-        if (P1.regular_sampling)
-            CUDA_TRY(launch_planar_frozen(P1, s->planar, 0, active_data, plane, active_pixels, n_active, w, st));
-        if (sa)
-            CUDA_TRY(inside_forward_finish(P1, s->inside, s->planar.gate, active_data, active_pixels, n_active, w, dose,
-                                           st));
-        CUDA_TRY(launch_forward_general(s->P, active_data, active_pixels, n_active * spp, spp, seed, w, dose, st,
-                                        s->planar.gate));
+        const int* gate = nullptr;
+        int host_gate = -1;
+        CUDA_TRY(planar_gate(s, active_pixels, n_active, st, &gate, &host_gate));
+        if (host_gate != 1) {
+            // gate word 0 -> the planar kernels own the call (decided on the device unless the list is pinned)
+            const bool sa = s->inside.valid;  // surface-aware: the planar kernels fill a one-channel plane
+            const SceneParams& P1 = s->P1;
+            float* plane = sa ? s->inside.planes : dose;
+            if (sa) CUDA_TRY(inside_forward_begin(s->inside, st));
+            if (!P1.regular_sampling)
+                CUDA_TRY(launch_planarj_forward(P1, windowed(P1), s->zplan, s->jplan, gate, active_data, active_pixels,
+                                                n_active, spp, seed, w, plane, zero_first != 0, st));
+            else if (s->zplan.valid && s->gplan.valid && s->force_mode != 2)
+                // fresh: the plane was cleared above (zero_first, or the planes of a surface-aware scene) and
+                // the patch gather is its first writer, so it stores instead of read-add-write
+                CUDA_TRY(launch_planarg_forward(P1, s->zplan, s->gplan, gate, active_data, active_pixels, n_active, w,
+                                                plane, sa || zero_first != 0, st));
+            else if (s->zplan.valid && s->force_mode != 2)
+                CUDA_TRY(launch_planarz_forward(P1, s->zplan, gate, active_data, active_pixels, n_active, w, plane, st));
+            else
+                CUDA_TRY(launch_planar_forward(P1, s->planar, active_data, active_pixels, n_active, w, plane, st, gate));
+            if (P1.regular_sampling)
+                CUDA_TRY(launch_planar_frozen(windowed(P1), s->planar, 0, active_data, plane, active_pixels, n_active, w,
+                                              st, gate));
+            if (sa)
+                CUDA_TRY(inside_forward_finish(P1, s->inside, gate, active_data, active_pixels, n_active, w, dose, st));
+        }
+        if (host_gate != 0)
+            CUDA_TRY(launch_forward_general(Pw, active_data, active_pixels, n_active * spp, spp, seed, w, dose, st,
+                                            host_gate < 0 ? s->planar.gate : nullptr));
         if (s->inv_volume) CUDA_TRY(launch_mul_inplace(dose, s->inv_volume, film_elems(s), st));  // volume.py:54
         return DRTVAM_OK;
     }
-    CUDA_TRY(launch_forward_general(s->P, active_data, active_pixels, n_active * spp, spp, seed, w, dose, st));
+    CUDA_TRY(launch_forward_general(Pw, active_data, active_pixels, n_active * spp, spp, seed, w, dose, st));
     if (s->inv_volume) CUDA_TRY(launch_mul_inplace(dose, s->inv_volume, film_elems(s), st));  // volume.py:54
     return DRTVAM_OK;
 }
@@ -468,35 +711,40 @@ int drtvam_adjoint(DrtvamScene* s, const float* dose_grad, const uint32_t* activ
         CUDA_TRY(launch_mul(dose_grad, s->inv_volume, static_cast<float*>(s->dl_scaled.ptr), film_elems(s), st));
         dose_grad = static_cast<const float*>(s->dl_scaled.ptr);
     }
+    const SceneParams Pw = windowed(s->P);
     if (use_planar(s, n_active)) {
-        const bool sa = s->inside.valid;
-        const SceneParams& P1 = s->P1;
-        const float* dl1 = dose_grad;  // one-channel gradient plane the planar kernels gather from
-        if (sa) {
-            CUDA_TRY(inside_adjoint_begin(s->inside, dose_grad, st));
-            dl1 = s->inside.planes;
+        const int* gate = nullptr;
+        int host_gate = -1;
+        CUDA_TRY(planar_gate(s, active_pixels, n_active, st, &gate, &host_gate));
+        if (host_gate != 1) {
+            const bool sa = s->inside.valid;
+            const SceneParams& P1 = s->P1;
+            const float* dl1 = dose_grad;  // one-channel gradient plane the planar kernels gather from
+            if (sa) {
+                CUDA_TRY(inside_adjoint_begin(s->inside, dose_grad, st));
+                dl1 = s->inside.planes;
+            }
+            if (!P1.regular_sampling) {
+                CUDA_TRY(launch_planarj_adjoint(P1, windowed(P1), s->zplan, s->jplan, gate, dl1, active_pixels, n_active,
+                                                spp, seed, w, pattern_grad, st));
+            } else if (s->zplan.valid && s->force_mode != 2) {
+                CUDA_TRY(launch_planarz_adjoint(P1, s->zplan, gate, dl1, active_pixels, n_active, w, pattern_grad, st));
+            } else {
+                CUDA_TRY(cudaMemsetAsync(pattern_grad, 0, sizeof(float) * n_active, st));
+                CUDA_TRY(launch_planar_adjoint(P1, s->planar, dl1, active_pixels, n_active, w, pattern_grad, st, gate));
+            }
+            if (P1.regular_sampling)
+                CUDA_TRY(launch_planar_frozen(windowed(P1), s->planar, 1, dl1, pattern_grad, active_pixels, n_active, w,
+                                              st, gate));
+            if (sa)
+                CUDA_TRY(inside_adjoint_finish(P1, s->inside, gate, active_pixels, n_active, w, pattern_grad, st));
         }
-        CUDA_TRY(launch_planar_check(P1, s->planar, active_pixels, n_active, st));
-        if (!P1.regular_sampling) {
-            CUDA_TRY(cudaMemsetAsync(pattern_grad, 0, sizeof(float) * n_active, st));
-            CUDA_TRY(launch_planar_lane_adjoint(P1, s->planar, dl1, active_pixels, n_active, spp, seed, w,
-                                                pattern_grad, st));
-        } else if (s->zplan.valid && s->force_mode != 2) {
-            CUDA_TRY(launch_planarz_adjoint(P1, s->zplan, s->planar.gate, dl1, active_pixels, n_active, w,
-                                            pattern_grad, st));
-        } else {
-            CUDA_TRY(cudaMemsetAsync(pattern_grad, 0, sizeof(float) * n_active, st));
-            CUDA_TRY(launch_planar_adjoint(P1, s->planar, dl1, active_pixels, n_active, w, pattern_grad, st));
-        }
-        if (P1.regular_sampling)
-            CUDA_TRY(launch_planar_frozen(P1, s->planar, 1, dl1, pattern_grad, active_pixels, n_active, w, st));
-        if (sa)
-            CUDA_TRY(inside_adjoint_finish(P1, s->inside, s->planar.gate, active_pixels, n_active, w, pattern_grad, st));
-        CUDA_TRY(launch_adjoint_general(s->P, dose_grad, active_pixels, n_active * spp, spp, seed, w, pattern_grad, st,
-                                        s->planar.gate));
+        if (host_gate != 0)
+            CUDA_TRY(launch_adjoint_general(Pw, dose_grad, active_pixels, n_active * spp, spp, seed, w, pattern_grad, st,
+                                            host_gate < 0 ? s->planar.gate : nullptr));
         return DRTVAM_OK;
     }
-    CUDA_TRY(launch_adjoint_general(s->P, dose_grad, active_pixels, n_active * spp, spp, seed, w, pattern_grad, st));
+    CUDA_TRY(launch_adjoint_general(Pw, dose_grad, active_pixels, n_active * spp, spp, seed, w, pattern_grad, st));
     return DRTVAM_OK;
 }
 

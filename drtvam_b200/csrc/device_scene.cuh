@@ -49,7 +49,28 @@ struct SceneParams {
     // target mesh; n_tri = 0 unless the run is surface-aware (otherwise the reference moves the mesh
     // 1e5 away, optimize.py:188-191, and no ray meets it)
     MeshView target;
+    // z-slab shard of a planar scene (drtvam_scene_set_z_window): the film buffers of a call hold the
+    // layers [z_begin, z_end) only and the active list holds the DMD rows [row_begin, row_begin + n_rows)
+    // of every pattern.  Defaults: the whole film / every row.
+    int z_begin, z_end, row_begin, n_rows;
+    // position of every entry of the call's active list in the UNSHARDED list (device, n_active entries),
+    // or NULL = the list is the whole one.  A lane's PCG32 stream is seeded with its position in the
+    // wavefront (integrators/common.py:67); with this a shard draws exactly the samples the unsharded run
+    // draws for the same pixels.
+    const uint32_t* sampler_index;
 };
+
+// PCG32 stream of lane `lane` (= position in the active list x spp + sample) of a call
+__device__ __forceinline__ uint32_t sampler_lane(const SceneParams& P, uint64_t lane, uint32_t spp) {
+    if (!P.sampler_index) return static_cast<uint32_t>(lane);
+    const uint64_t j = lane / spp;
+    return static_cast<uint32_t>(static_cast<uint64_t>(__ldg(P.sampler_index + j)) * spp + (lane - j * spp));
+}
+
+// index of (pattern kk of the call, DMD row, column) in the active list of a planar call
+__host__ __device__ __forceinline__ size_t active_index(const SceneParams& P, int kk, int row, int col) {
+    return (static_cast<size_t>(kk) * P.n_rows + (row - P.row_begin)) * P.res_x + col;
+}
 
 struct Ray {
     float ox, oy, oz, dx, dy, dz;

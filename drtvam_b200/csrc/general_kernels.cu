@@ -42,7 +42,7 @@ forward_general_kernel(const __grid_constant__ SceneParams P, const float* __res
     const float em = __ldg(active_data + j) * ray_weight;
     if (em == 0.f && !kScatter) return;  // a zero pixel deposits nothing
     Sampler rng;
-    rng.seed(seed, static_cast<uint32_t>(lane));
+    rng.seed(seed, sampler_lane(P, lane, spp));
     const Ray ray = generate_ray(P, __ldg(active_pixels + j), rng);
     ScatterSink sink{film, em};
     trace_lane<kScatter>(P, ray, rng, sink);
@@ -60,7 +60,7 @@ adjoint_general_kernel(const __grid_constant__ SceneParams P, const float* __res
     float g = 0.f;
     if (live) {
         Sampler rng;
-        rng.seed(seed, static_cast<uint32_t>(lane));
+        rng.seed(seed, sampler_lane(P, lane, spp));
         const Ray ray = generate_ray(P, __ldg(active_pixels + j), rng);
         PipelinedGatherSink sink{dL};
         trace_lane<kScatter>(P, ray, rng, sink);
@@ -84,7 +84,7 @@ raygen_kernel(const __grid_constant__ SceneParams P, const uint32_t* __restrict_
     const uint64_t lane = static_cast<uint64_t>(blockIdx.x) * kThreads + threadIdx.x;
     if (lane >= n_lanes) return;
     Sampler rng;
-    rng.seed(seed, static_cast<uint32_t>(lane));
+    rng.seed(seed, sampler_lane(P, lane, spp));
     const Ray r = generate_ray(P, __ldg(active_pixels + lane / spp), rng);
     float* o = out + 6 * lane;
     o[0] = r.ox; o[1] = r.oy; o[2] = r.oz; o[3] = r.dx; o[4] = r.dy; o[5] = r.dz;
@@ -98,7 +98,7 @@ count_general_kernel(const __grid_constant__ SceneParams P, const uint32_t* __re
     unsigned long long n = 0;
     if (lane < n_lanes) {
         Sampler rng;
-        rng.seed(seed, static_cast<uint32_t>(lane));
+        rng.seed(seed, sampler_lane(P, lane, spp));
         const Ray ray = generate_ray(P, __ldg(active_pixels + lane / spp), rng);
         CountSink sink;
         trace_lane<kScatter>(P, ray, rng, sink);
@@ -162,7 +162,7 @@ general_persistent_kernel(const __grid_constant__ SceneParams P, const float* __
                     }
                     if (take) {
                         item = mine;
-                        rng.seed(seed, static_cast<uint32_t>(mine));
+                        rng.seed(seed, sampler_lane(P, mine, spp));
                         T = TraceState();
                         T.ray = generate_ray(P, __ldg(active_pixels + j), rng);
                         has_ray = true;
@@ -274,7 +274,7 @@ general_queue_kernel(const __grid_constant__ SceneParams P, const float* __restr
             if (em == 0.f) continue;  // every deposit of the lane is proportional to em
         }
         Sampler rng;
-        rng.seed(seed, static_cast<uint32_t>(lane));
+        rng.seed(seed, sampler_lane(P, lane, spp));
         TraceState T;
         T.ray = generate_ray(P, __ldg(active_pixels + j), rng);
         while (bounce_once<kScatter>(P, T, rng, [&](const Ray& r, float maxt, float w0, bool inside, float) {

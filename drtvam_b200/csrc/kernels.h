@@ -36,18 +36,12 @@ struct PlanarHost {
     int* tile_off = nullptr;
     int* tile_clo = nullptr;
     int* gate = nullptr;  // [0] per-call pixel-layout gate, [1] build flags
-    // jittered passes
-    int* jlayer_row_begin = nullptr;
-    int* jlayer_rows = nullptr;
-    int* jtile_off = nullptr;
-    int* jtile_clo = nullptr;
     int* frozen_list = nullptr;    // (angle, column) rays with a frozen DDA axis (sensor.py:359), walked generally
     int n_frozen = 0;
-    void* lane_scratch = nullptr;  // per-lane segment table of the current angle chunk
-    size_t lane_scratch_bytes = 0;
     PlanarPlan plan{};
     size_t smem_bytes = 0;
     std::vector<int> row_layer;  // host copy: film layer of every DMD row, -1 = outside the sensor
+    std::vector<float> row_z;    // host copy: world z of every DMD row's pixel centres
 };
 cudaError_t planar_build(const SceneParams& P, PlanarHost& H);
 void planar_release(PlanarHost& H);
@@ -55,9 +49,10 @@ cudaError_t launch_planar_check(const SceneParams& P, PlanarHost& H, const uint3
                                 cudaStream_t stream);
 cudaError_t launch_planar_forward(const SceneParams& P, PlanarHost& H, const float* active_data,
                                   const uint32_t* active_pixels, uint64_t n_active, float ray_weight, float* film,
-                                  cudaStream_t stream);
+                                  cudaStream_t stream, const int* gate = nullptr);
 cudaError_t launch_planar_adjoint(const SceneParams& P, PlanarHost& H, const float* dL, const uint32_t* active_pixels,
-                                  uint64_t n_active, float ray_weight, float* grad, cudaStream_t stream);
+                                  uint64_t n_active, float ray_weight, float* grad, cudaStream_t stream,
+                                  const int* gate = nullptr);
 
 // per-(tile, angle) first crossing column and prefix sums of the crossing-column counts
 cudaError_t planar_tile_ranges(const SceneParams& P, const float4* seg_a, const float2* seg_b, int tiles_x, int tiles_y,
@@ -65,14 +60,7 @@ cudaError_t planar_tile_ranges(const SceneParams& P, const float4* seg_a, const 
 // mode 0: deposit the frozen-axis rays into the film; mode 1: write their pattern gradients
 cudaError_t launch_planar_frozen(const SceneParams& P, PlanarHost& H, int mode, const float* in, float* out,
                                  const uint32_t* active_pixels, uint64_t n_active, float ray_weight,
-                                 cudaStream_t stream);
-// jittered planar passes (per-lane segment table)
-cudaError_t launch_planar_lane_forward(const SceneParams& P, PlanarHost& H, const float* active_data,
-                                       const uint32_t* active_pixels, uint64_t n_active, uint32_t spp, uint32_t seed,
-                                       float ray_weight, float* film, cudaStream_t stream);
-cudaError_t launch_planar_lane_adjoint(const SceneParams& P, PlanarHost& H, const float* dL,
-                                       const uint32_t* active_pixels, uint64_t n_active, uint32_t spp, uint32_t seed,
-                                       float ray_weight, float* grad, cudaStream_t stream);
+                                 cudaStream_t stream, const int* gate = nullptr);
 
 // layer-parallel planar kernels (planarz_kernels.cu), the deterministic fast path
 struct PlanarZSub {      // a run of z-blocks that all hold 32 * lanes_l active layers
@@ -89,10 +77,13 @@ struct PlanarZHost {
     int n_sub = 0;
     PlanarZSub sub[3];       // e.g. 400 layers = 3 blocks of 128 (4 per lane) + 1 block of 32 (1 per lane)
     int nz = 0, nz_pad = 0;
+    int rows_max = 0;        // most DMD rows that deposit in one layer
     int* zl = nullptr;
     int* a_row_begin = nullptr;
     int* a_rows = nullptr;
     int* row_a = nullptr;
+    int* layer_a = nullptr;    // [res_z] active layer of film layer z, -1 = no DMD row deposits there (or outside the z window)
+    int* row_ri = nullptr;     // [res_y] position of DMD row r among the rows of its layer
     float* scratch = nullptr;  // [angles][columns][active layers] repack of patterns / gradients
     size_t scratch_bytes = 0;
 };
@@ -110,7 +101,29 @@ struct PlanarGHost {
     long long candidates = 0;  // before
 };
 cudaError_t planarz_build(const SceneParams& P, const PlanarHost& base, const std::vector<int>& row_layer,
-                          PlanarZHost& H);
+                          PlanarZHost& H, bool walks = true);
+
+// jittered planar passes (planarj_kernels.cu): regular_sampling = false, every lane its own segment
+struct PlanarJHost {
+    bool valid = false;
+    int tiles_x = 0, tiles_y = 0, tile_w = 0, tile_h = 0;
+    int* tile_off = nullptr;       // [n_tiles][n_patterns + 1] prefix of the (conservative) column counts
+    int* tile_clo = nullptr;       // [n_tiles][n_patterns]
+    void* table = nullptr;         // per-lane segment table of the current angle chunk
+    size_t table_bytes = 0;
+    float* gT = nullptr;           // adjoint: per-lane gradients in table order
+    size_t gT_bytes = 0;
+    size_t smem_bytes = 0;
+};
+cudaError_t planarj_build(const SceneParams& P, const PlanarHost& base, const PlanarZHost& Zh, PlanarJHost& J);
+void planarj_release(PlanarJHost& J);
+cudaError_t launch_planarj_forward(const SceneParams& P, const SceneParams& Pw, PlanarZHost& Zh, PlanarJHost& J,
+                                   const int* gate, const float* active_data, const uint32_t* active_pixels,
+                                   uint64_t n_active, uint32_t spp, uint32_t seed, float ray_weight, float* film,
+                                   bool fresh, cudaStream_t stream);
+cudaError_t launch_planarj_adjoint(const SceneParams& P, const SceneParams& Pw, PlanarZHost& Zh, PlanarJHost& J,
+                                   const int* gate, const float* dL, const uint32_t* active_pixels, uint64_t n_active,
+                                   uint32_t spp, uint32_t seed, float ray_weight, float* grad, cudaStream_t stream);
 cudaError_t planarg_build(const SceneParams& P, const PlanarHost& base, const PlanarZHost& Zh, PlanarGHost& G);
 void planarg_release(PlanarGHost& G);
 cudaError_t launch_planarg_forward(const SceneParams& P, PlanarZHost& H, PlanarGHost& G, const int* gate,

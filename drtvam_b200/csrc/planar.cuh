@@ -11,6 +11,8 @@
 #include <cstdint>
 #include <cuda_runtime.h>
 
+#include "device_scene.cuh"
+
 namespace drtvam {
 
 // One medium segment per (angle, column): origin, direction, length and the
@@ -23,12 +25,6 @@ struct PlanarPlan {
     const int* layer_rows;       // DMD rows sorted by the layer they deposit in
     const int* tile_off;         // [n_tiles][n_patterns + 1] prefix of per-angle column counts
     const int* tile_clo;         // [n_tiles][n_patterns] first column crossing the tile
-    // jittered passes: conservative variants (a jittered ray of column c lies within half a pixel of
-    // the centre ray of c; a DMD row can reach the layers next to the one its centre is in)
-    const int* jlayer_row_begin;
-    const int* jlayer_rows;
-    const int* jtile_off;
-    const int* jtile_clo;
     int tiles_x, tiles_y, tile_w, tile_h, pitch, groups;
 };
 
@@ -60,6 +56,27 @@ struct PlanarZPlan {
 };
 
 #ifdef __CUDACC__
+// Records the medium segments of one lane instead of depositing them.
+struct RecordSink {
+    static constexpr bool kRecordOnly = true;
+    Ray seg;
+    float tmax = 0.f, w0 = 0.f;
+    int count = 0;
+    __device__ __forceinline__ void record(const Ray& r, float maxt, float w) {
+        if (count == 0) { seg = r; tmax = maxt; w0 = w; }
+        ++count;
+    }
+    __device__ __forceinline__ void visit(size_t, float) {}
+};
+
+// first pattern and pattern count of a planar call: the active list holds rows
+// [row_begin, row_begin + n_rows) of patterns [k0, k0 + nk), every column
+__device__ __forceinline__ void call_angles(const SceneParams& P, const uint32_t* __restrict__ active_pixels,
+                                            uint64_t n_active, int& k0, int& nk) {
+    k0 = static_cast<int>(__ldg(active_pixels) / (static_cast<uint32_t>(P.res_x) * P.res_y));
+    nk = static_cast<int>(n_active / (static_cast<uint64_t>(P.n_rows) * P.res_x));
+}
+
 __device__ __forceinline__ float ex2_approx(float x) {
     float y;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));

@@ -25,19 +25,6 @@ namespace {
 constexpr int kPlanarThreads = 256;
 constexpr float kLog2e = 1.4426950408889634f;
 
-// Records the medium segments of one lane instead of depositing them.
-struct RecordSink {
-    static constexpr bool kRecordOnly = true;
-    Ray seg;
-    float tmax = 0.f, w0 = 0.f;
-    int count = 0;
-    __device__ __forceinline__ void record(const Ray& r, float maxt, float w) {
-        if (count == 0) { seg = r; tmax = maxt; w0 = w; }
-        ++count;
-    }
-    __device__ __forceinline__ void visit(size_t, float) {}
-};
-
 // Segment table: one thread per (angle, column), traced at row `row_ref`
 // through the general interface loop so both plans share the same arithmetic.
 __global__ void __launch_bounds__(kPlanarThreads)
@@ -114,18 +101,21 @@ __global__ void planar_ranges_kernel(const __grid_constant__ SceneParams P, cons
     cnt[i] = hi >= lo ? hi - lo + 1 : 0;
 }
 
-// gate[0] != 0  <=>  active_pixels is not `base + j` with whole patterns, i.e.
-// the planar kernels must stand down and the general tracer runs instead.
+// gate[0] != 0  <=>  active_pixels is not the dense layout the planar kernels index implicitly - DMD rows
+// [row_begin, row_begin + n_rows) of consecutive whole patterns, every column, in order - i.e. the planar
+// kernels must stand down and the general tracer runs instead.
 __global__ void planar_check_pixels_kernel(const uint32_t* __restrict__ active_pixels, uint64_t n_active, uint32_t hw,
-                                           int* __restrict__ gate) {
+                                           uint32_t rw, uint32_t first, int* __restrict__ gate) {
     const uint64_t j = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     const uint32_t base = __ldg(active_pixels);
     bool bad = false;
-    if (j == 0) bad = (base % hw) != 0;
-    if (j < n_active) bad = bad || (__ldg(active_pixels + j) != base + static_cast<uint32_t>(j));
+    if (j == 0) bad = (base % hw) != first;
+    if (j < n_active) {
+        const uint64_t kk = j / rw;
+        bad = bad || (__ldg(active_pixels + j) != base + static_cast<uint32_t>(kk * hw + (j - kk * rw)));
+    }
     if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) atomicOr(gate, 1);
 }
-
 
 
 // Rays of the deterministic table whose walk has a frozen axis (sensor.py:359):
@@ -138,13 +128,13 @@ planar_frozen_kernel(const __grid_constant__ SceneParams P, const int* __restric
                      uint64_t n_active, float ray_weight, const int* __restrict__ gate) {
     if (*gate != 0) return;
     const int i = blockIdx.x * kPlanarThreads + threadIdx.x;
-    if (i >= n_frozen * P.res_y) return;
-    const int e = __ldg(frozen_list + i / P.res_y), row = i % P.res_y;
+    if (i >= n_frozen * P.n_rows) return;
+    const int e = __ldg(frozen_list + i / P.n_rows), row = P.row_begin + i % P.n_rows;
     const int k = e / P.res_x, c = e - k * P.res_x;
-    const uint32_t hw = static_cast<uint32_t>(P.res_x) * P.res_y;
-    const int k0 = __ldg(active_pixels) / hw, nk = static_cast<int>(n_active / hw);
+    int k0, nk;
+    call_angles(P, active_pixels, n_active, k0, nk);
     if (k < k0 || k >= k0 + nk) return;
-    const size_t j = (static_cast<size_t>(k - k0) * P.res_y + row) * P.res_x + c;
+    const size_t j = active_index(P, k - k0, row, c);
     Sampler rng;
     rng.seed(0u, 0u);  // never consumed: deterministic configuration
     const Ray ray = generate_ray(P, __ldg(active_pixels + j), rng);
@@ -266,9 +256,8 @@ planar_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pla
     int* off = reinterpret_cast<int*>(smem + (L.tile_h + 2) * pitch);
     int* clo = off + P.n_patterns + 1;
 
-    const uint32_t hw = static_cast<uint32_t>(P.res_x) * P.res_y;
-    const uint32_t base = __ldg(active_pixels);
-    const int k0 = base / hw, nk = static_cast<int>(n_active / hw);
+    int k0, nk;
+    call_angles(P, active_pixels, n_active, k0, nk);
     const int ka = k0 + static_cast<int>(static_cast<long long>(nk) * group / L.groups);
     const int kb = k0 + static_cast<int>(static_cast<long long>(nk) * (group + 1) / L.groups);
 
@@ -298,7 +287,7 @@ planar_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pla
             const int s = k * P.res_x + c;
             const float2 b = __ldg(L.seg_b + s);
             if (b.y == 0.f) continue;
-            const size_t j = (static_cast<size_t>(k - k0) * P.res_y + row) * P.res_x + c;
+            const size_t j = active_index(P, k - k0, row, c);
             float em = 0.f;
             if (kMode != kGather) {
                 em = __ldg(in + j) * (ray_weight * b.y);
@@ -336,155 +325,6 @@ planar_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pla
 }
 
 
-// ---------------------------------------------------------------------------
-// Jittered planar pass (regular_sampling = false, the reference default): rays
-// of a planar scene still have d_z = 0 and stay in one layer, but each lane has
-// its own pixel jitter (integrators/common.py:92-95), so the segment table is
-// per lane.  A pre-pass traces the interfaces of every lane once and writes
-// (layer, segment); lanes whose path is not one planar segment are deposited
-// right there by the general walk.  The tile kernel then marches the lanes of
-// its layer exactly like the deterministic per-ray kernel.
-// ---------------------------------------------------------------------------
-struct LaneTable {
-    float4* a;   // ox, oy, dx, dy
-    float2* b;   // tmax, w0
-    int* layer;  // film layer, -1 = nothing to march (miss, outside, or already deposited)
-};
-
-template <int kMode>
-__global__ void __launch_bounds__(kPlanarThreads)
-planar_lane_table_kernel(const __grid_constant__ SceneParams P, const float* __restrict__ in, float* __restrict__ out,
-                         const uint32_t* __restrict__ active_pixels, uint64_t lane0, uint64_t n_lanes, uint32_t spp,
-                         uint32_t seed, float ray_weight, LaneTable T, const int* __restrict__ gate) {
-    if (*gate != 0) return;
-    const uint64_t i = static_cast<uint64_t>(blockIdx.x) * kPlanarThreads + threadIdx.x;
-    if (i >= n_lanes) return;
-    const uint64_t lane = lane0 + i;
-    const uint64_t j = lane / spp;
-    const uint32_t pixel = __ldg(active_pixels + j);
-    Sampler rng;
-    rng.seed(seed, static_cast<uint32_t>(lane));
-    const Ray ray = generate_ray(P, pixel, rng);
-    RecordSink sink;
-    sink.seg = ray;
-    trace_lane<false>(P, ray, rng, sink);
-    const bool odd = sink.count > 1 || ray.dz != 0.f || (sink.count == 1 && sink.seg.dz != 0.f) ||
-                     (sink.count == 1 && dda_has_frozen_axis(P, sink.seg, sink.tmax));
-    int layer = -1;
-    if (odd) {
-        // not a single planar segment (e.g. a square-vial corner): general walk, deposited here
-        Sampler rng2;
-        rng2.seed(seed, static_cast<uint32_t>(lane));
-        const Ray ray2 = generate_ray(P, pixel, rng2);
-        if (kMode == kGather) {
-            GatherSink g{in};
-            trace_lane<false>(P, ray2, rng2, g);
-            if (g.acc != 0.f) atomicAdd(out + j, g.acc * ray_weight);
-        } else {
-            const float em = __ldg(in + j) * ray_weight;
-            if (em != 0.f) {
-                ScatterSink sc{out, em};
-                trace_lane<false>(P, ray2, rng2, sc);
-            }
-        }
-    } else if (sink.count == 1 && sink.w0 != 0.f && sink.tmax > 0.f && isfinite(sink.tmax)) {
-        const float z = sink.seg.oz;
-        if (z > P.bmin[2] && z < P.bmax[2]) {
-            const float vs = (P.bmax[2] - P.bmin[2]) / static_cast<float>(P.res[2]);
-            layer = min(max(__float2int_rz((z - P.bmin[2]) / vs), 0), P.res[2] - 1);
-        }
-    }
-    T.a[i] = make_float4(sink.seg.ox, sink.seg.oy, sink.seg.dx, sink.seg.dy);
-    T.b[i] = make_float2(sink.tmax, sink.w0);
-    T.layer[i] = layer;
-}
-
-// kScatter: in = active_data, out = film.  kGather: in = dL, out = pattern_grad (pre-zeroed).
-// Angles [kc, kc + nkc) of the call (relative to its first angle) are in the lane table.
-template <int kMode>
-__global__ void __launch_bounds__(kPlanarThreads)
-planar_lane_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ PlanarPlan L, LaneTable T,
-                   const float* __restrict__ in, float* __restrict__ out, const uint32_t* __restrict__ active_pixels,
-                   int kc, int nkc, uint32_t spp, float ray_weight, const int* __restrict__ gate) {
-    extern __shared__ __align__(16) float smem[];
-    if (*gate != 0) return;
-    const int tile_id = blockIdx.x, layer = blockIdx.y, group = blockIdx.z;
-    const int rb = L.jlayer_row_begin[layer], re = L.jlayer_row_begin[layer + 1];
-    if (rb == re) return;
-
-    const int x0 = (tile_id % L.tiles_x) * L.tile_w, y0 = (tile_id / L.tiles_x) * L.tile_h;
-    const int w = min(L.tile_w, P.res[0] - x0), h = min(L.tile_h, P.res[1] - y0);
-    const int pitch = L.pitch;
-    float* tile = smem;
-    const int* __restrict__ off = L.jtile_off + static_cast<size_t>(tile_id) * (P.n_patterns + 1);
-    const int* __restrict__ clo = L.jtile_clo + static_cast<size_t>(tile_id) * P.n_patterns;
-
-    const uint32_t hw = static_cast<uint32_t>(P.res_x) * P.res_y;
-    const int k0 = __ldg(active_pixels) / hw;
-    const int kfirst = k0 + kc;  // first angle held by the lane table
-    const int ka = kfirst + static_cast<int>(static_cast<long long>(nkc) * group / L.groups);
-    const int kb = kfirst + static_cast<int>(static_cast<long long>(nkc) * (group + 1) / L.groups);
-
-    const size_t layer_base = static_cast<size_t>(layer) * P.res[0] * P.res[1];
-    for (int i = threadIdx.x; i < (h + 2) * pitch; i += kPlanarThreads) {
-        float v = 0.f;
-        if (kMode == kGather) {
-            const int yy = i / pitch - 1, xx = i - (yy + 1) * pitch - 1;
-            if (yy >= 0 && yy < h && xx >= 0 && xx < w)
-                v = __ldg(in + layer_base + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx));
-        }
-        tile[i] = v;
-    }
-    __syncthreads();
-
-    const int f_base = __ldg(off + ka);
-    const long long total = static_cast<long long>(__ldg(off + kb) - f_base) * spp;
-    for (int ri = rb; ri < re; ++ri) {
-        const int row = L.jlayer_rows[ri];
-        int k = ka;
-        for (long long f = threadIdx.x; f < total; f += kPlanarThreads) {
-            const int g = static_cast<int>(f / spp) + f_base;
-            const int smp = static_cast<int>(f - static_cast<long long>(g - f_base) * spp);
-            while (__ldg(off + k + 1) <= g) ++k;
-            const int c = __ldg(clo + k) + (g - __ldg(off + k));
-            const size_t idx = ((static_cast<size_t>(k - kfirst) * P.res_y + row) * P.res_x + c) * spp + smp;
-            if (__ldg(T.layer + idx) != layer) continue;
-            const float2 b = __ldg(T.b + idx);
-            const size_t j = (static_cast<size_t>(k - k0) * P.res_y + row) * P.res_x + c;
-            float em = 0.f;
-            if (kMode != kGather) {
-                em = __ldg(in + j) * (ray_weight * b.y);
-                if (em == 0.f) continue;
-            }
-            const float4 a = __ldg(T.a + idx);
-            float t0, t1;
-            if (!clip_to_tile(P, a, b.x, x0, y0, w, h, t0, t1)) continue;
-            const float acc = march_tile<kMode>(P, tile, pitch, a, t0, t1, x0, y0, w, h, em);
-            if (kMode == kGather && acc != 0.f) atomicAdd(out + j, acc * (ray_weight * b.y));
-        }
-    }
-    if (kMode == kGather) return;
-    __syncthreads();
-
-    float* dst = out + layer_base;
-    if (((x0 | w | P.res[0]) & 3) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
-        const int w4 = w >> 2;
-        for (int i = threadIdx.x; i < h * w4; i += kPlanarThreads) {
-            const int yy = i / w4, xx = (i - yy * w4) << 2;
-            const int t = (yy + 1) * pitch + xx + 1;
-            const float v0 = tile[t], v1 = tile[t + 1], v2 = tile[t + 2], v3 = tile[t + 3];
-            if (v0 != 0.f || v1 != 0.f || v2 != 0.f || v3 != 0.f)
-                red_add_v4(dst + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx), v0, v1, v2, v3);
-        }
-    } else {
-        for (int i = threadIdx.x; i < h * w; i += kPlanarThreads) {
-            const int yy = i / w, xx = i - yy * w;
-            const float v = tile[(yy + 1) * pitch + xx + 1];
-            if (v != 0.f) atomicAdd(dst + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx), v);
-        }
-    }
-}
-
 }  // namespace
 
 // ---------------------------------------------------------------------------
@@ -497,8 +337,7 @@ planar_lane_kernel(const __grid_constant__ SceneParams P, const __grid_constant_
     } while (0)
 
 void planar_release(PlanarHost& H) {
-    void* ptrs[] = {H.seg_a, H.seg_b, H.layer_row_begin, H.layer_rows, H.tile_off, H.tile_clo, H.gate,
-                    H.jlayer_row_begin, H.jlayer_rows, H.jtile_off, H.jtile_clo, H.lane_scratch, H.frozen_list};
+    void* ptrs[] = {H.seg_a, H.seg_b, H.layer_row_begin, H.layer_rows, H.tile_off, H.tile_clo, H.gate, H.frozen_list};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     H = PlanarHost();
@@ -603,45 +442,7 @@ cudaError_t planar_build(const SceneParams& P, PlanarHost& H) {
 
     PL_TRY(planar_tile_ranges(P, H.seg_a, H.seg_b, L.tiles_x, L.tiles_y, L.tile_w, L.tile_h, H.tile_off, H.tile_clo));
     H.row_layer = row_layer;
-
-    // jittered passes: a row's samples span [row, row + 1] pixels in z, which can reach the
-    // neighbouring layers; the lane table holds the exact layer of every lane
-    {
-        const float vs = (P.bmax[2] - P.bmin[2]) / static_cast<float>(rz);
-        const float dz = Hh > 1 ? std::fabs(row_z[1] - row_z[0]) : P.pixel_y;
-        const float slack = 1e-3f * vs;
-        std::vector<std::vector<int>> rows_of(rz);
-        for (int r = 0; r < Hh; ++r) {
-            const float zlo = row_z[r] - 0.5f * dz - slack, zhi = row_z[r] + 0.5f * dz + slack;
-            if (zhi <= P.bmin[2] || zlo >= P.bmax[2]) continue;
-            int la = static_cast<int>(std::floor((zlo - P.bmin[2]) / vs));
-            int lb = static_cast<int>(std::floor((zhi - P.bmin[2]) / vs));
-            la = std::max(la, 0);
-            lb = std::min(lb, rz - 1);
-            for (int z = la; z <= lb; ++z) rows_of[z].push_back(r);
-        }
-        std::vector<int> jbegin(rz + 1, 0), jrows;
-        for (int z = 0; z < rz; ++z) {
-            jrows.insert(jrows.end(), rows_of[z].begin(), rows_of[z].end());
-            jbegin[z + 1] = static_cast<int>(jrows.size());
-        }
-        if (jrows.empty()) jrows.push_back(0);
-        PL_TRY(cudaMalloc(&H.jlayer_row_begin, sizeof(int) * (rz + 1)));
-        PL_TRY(cudaMalloc(&H.jlayer_rows, sizeof(int) * jrows.size()));
-        PL_TRY(cudaMemcpy(H.jlayer_row_begin, jbegin.data(), sizeof(int) * (rz + 1), cudaMemcpyHostToDevice));
-        PL_TRY(cudaMemcpy(H.jlayer_rows, jrows.data(), sizeof(int) * jrows.size(), cudaMemcpyHostToDevice));
-        PL_TRY(cudaMalloc(&H.jtile_off, sizeof(int) * n_tiles * (np + 1)));
-        PL_TRY(cudaMalloc(&H.jtile_clo, sizeof(int) * n_tiles * np));
-        const float margin = 1.5f * std::fmax(P.pixel_x, P.pixel_y);
-        PL_TRY(planar_tile_ranges(P, H.seg_a, H.seg_b, L.tiles_x, L.tiles_y, L.tile_w, L.tile_h, H.jtile_off,
-                                  H.jtile_clo, margin));
-        L.jlayer_row_begin = H.jlayer_row_begin; L.jlayer_rows = H.jlayer_rows;
-        L.jtile_off = H.jtile_off; L.jtile_clo = H.jtile_clo;
-    }
-    PL_TRY(cudaFuncSetAttribute(planar_lane_kernel<kScatter>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                static_cast<int>(H.smem_bytes)));
-    PL_TRY(cudaFuncSetAttribute(planar_lane_kernel<kGather>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                static_cast<int>(H.smem_bytes)));
+    H.row_z = row_z;
 
     PL_TRY(cudaFuncSetAttribute(planar_kernel<kScatter>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 static_cast<int>(H.smem_bytes)));
@@ -653,7 +454,7 @@ cudaError_t planar_build(const SceneParams& P, PlanarHost& H) {
 
 static int planar_groups(const SceneParams& P, const PlanarPlan& L, uint64_t n_active) {
     const long long ctas = static_cast<long long>(L.tiles_x) * L.tiles_y * P.res[2];
-    const long long nk = static_cast<long long>(n_active / (static_cast<uint64_t>(P.res_x) * P.res_y));
+    const long long nk = static_cast<long long>(n_active / (static_cast<uint64_t>(P.res_x) * P.n_rows));
     long long g = (148 * 8 + ctas - 1) / ctas;
     if (g > nk) g = nk;
     if (g > 32) g = 32;
@@ -663,113 +464,54 @@ static int planar_groups(const SceneParams& P, const PlanarPlan& L, uint64_t n_a
 cudaError_t launch_planar_check(const SceneParams& P, PlanarHost& H, const uint32_t* active_pixels, uint64_t n_active,
                                 cudaStream_t stream) {
     PL_TRY(cudaMemsetAsync(H.gate, 0, sizeof(int), stream));
-    const uint32_t hw = static_cast<uint32_t>(P.res_x) * P.res_y;
-    planar_check_pixels_kernel<<<static_cast<unsigned>((n_active + 255) / 256), 256, 0, stream>>>(active_pixels,
-                                                                                                n_active, hw, H.gate);
+    const uint32_t hw = static_cast<uint32_t>(P.res_x) * P.res_y, rw = static_cast<uint32_t>(P.res_x) * P.n_rows;
+    planar_check_pixels_kernel<<<static_cast<unsigned>((n_active + 255) / 256), 256, 0, stream>>>(
+        active_pixels, n_active, hw, rw, static_cast<uint32_t>(P.row_begin) * P.res_x, H.gate);
     count_launch();
     return cudaGetLastError();
 }
 
 cudaError_t launch_planar_forward(const SceneParams& P, PlanarHost& H, const float* active_data,
                                   const uint32_t* active_pixels, uint64_t n_active, float ray_weight, float* film,
-                                  cudaStream_t stream) {
+                                  cudaStream_t stream, const int* gate) {
+    if (!gate) gate = H.gate;
     PlanarPlan L = H.plan;
     L.groups = planar_groups(P, L, n_active);
     const dim3 grid(L.tiles_x * L.tiles_y, P.res[2], L.groups);
     planar_kernel<kScatter><<<grid, kPlanarThreads, H.smem_bytes, stream>>>(P, L, active_data, film, active_pixels,
-                                                                           n_active, ray_weight, H.gate);
+                                                                           n_active, ray_weight, gate);
     count_launch();
     return cudaGetLastError();
 }
 
 cudaError_t launch_planar_adjoint(const SceneParams& P, PlanarHost& H, const float* dL, const uint32_t* active_pixels,
-                                  uint64_t n_active, float ray_weight, float* grad, cudaStream_t stream) {
+                                  uint64_t n_active, float ray_weight, float* grad, cudaStream_t stream,
+                                  const int* gate) {
+    if (!gate) gate = H.gate;
     PlanarPlan L = H.plan;
     L.groups = planar_groups(P, L, n_active);
     const dim3 grid(L.tiles_x * L.tiles_y, P.res[2], L.groups);
     planar_kernel<kGather><<<grid, kPlanarThreads, H.smem_bytes, stream>>>(P, L, dL, grad, active_pixels, n_active,
-                                                                          ray_weight, H.gate);
+                                                                          ray_weight, gate);
     count_launch();
     return cudaGetLastError();
 }
 
 cudaError_t launch_planar_frozen(const SceneParams& P, PlanarHost& H, int mode, const float* in, float* out,
                                  const uint32_t* active_pixels, uint64_t n_active, float ray_weight,
-                                 cudaStream_t stream) {
+                                 cudaStream_t stream, const int* gate) {
     if (H.n_frozen <= 0) return cudaSuccess;
-    const unsigned blocks = static_cast<unsigned>((static_cast<size_t>(H.n_frozen) * P.res_y + kPlanarThreads - 1) /
+    if (!gate) gate = H.gate;
+    const unsigned blocks = static_cast<unsigned>((static_cast<size_t>(H.n_frozen) * P.n_rows + kPlanarThreads - 1) /
                                                   kPlanarThreads);
     if (mode == 1)
         planar_frozen_kernel<1><<<blocks, kPlanarThreads, 0, stream>>>(P, H.frozen_list, H.n_frozen, in, out,
-                                                                       active_pixels, n_active, ray_weight, H.gate);
+                                                                       active_pixels, n_active, ray_weight, gate);
     else
         planar_frozen_kernel<0><<<blocks, kPlanarThreads, 0, stream>>>(P, H.frozen_list, H.n_frozen, in, out,
-                                                                       active_pixels, n_active, ray_weight, H.gate);
+                                                                       active_pixels, n_active, ray_weight, gate);
     count_launch();
     return cudaGetLastError();
-}
-
-// Angles per chunk of the per-lane table (28 bytes per lane, at most ~3 GB of scratch).
-static int lane_chunk_angles(const SceneParams& P, uint32_t spp, int nk) {
-    const double per_angle = 28.0 * P.res_x * P.res_y * spp;
-    long long n = static_cast<long long>(3.0e9 / per_angle);
-    if (n < 1) n = 1;
-    return static_cast<int>(n < nk ? n : nk);
-}
-
-template <int kMode>
-static cudaError_t planar_lane_pass(const SceneParams& P, PlanarHost& H, const float* in, float* out,
-                                    const uint32_t* active_pixels, uint64_t n_active, uint32_t spp, uint32_t seed,
-                                    float ray_weight, cudaStream_t stream) {
-    const uint64_t hw = static_cast<uint64_t>(P.res_x) * P.res_y;
-    const int nk = static_cast<int>(n_active / hw);
-    const int chunk = lane_chunk_angles(P, spp, nk);
-    const size_t lanes_max = static_cast<size_t>(chunk) * hw * spp;
-    const size_t a_bytes = (sizeof(float4) * lanes_max + 255) & ~static_cast<size_t>(255);
-    const size_t b_bytes = (sizeof(float2) * lanes_max + 255) & ~static_cast<size_t>(255);
-    const size_t bytes = a_bytes + b_bytes + sizeof(int) * lanes_max;
-    if (bytes > H.lane_scratch_bytes) {
-        if (H.lane_scratch) cudaFree(H.lane_scratch);
-        H.lane_scratch = nullptr;
-        H.lane_scratch_bytes = 0;
-        PL_TRY(cudaMalloc(&H.lane_scratch, bytes));
-        H.lane_scratch_bytes = bytes;
-    }
-    LaneTable T;
-    char* base = static_cast<char*>(H.lane_scratch);
-    T.a = reinterpret_cast<float4*>(base);
-    T.b = reinterpret_cast<float2*>(base + a_bytes);
-    T.layer = reinterpret_cast<int*>(base + a_bytes + b_bytes);
-    for (int kc = 0; kc < nk; kc += chunk) {
-        const int nkc = (nk - kc) < chunk ? (nk - kc) : chunk;
-        const uint64_t lane0 = static_cast<uint64_t>(kc) * hw * spp, n_lanes = static_cast<uint64_t>(nkc) * hw * spp;
-        planar_lane_table_kernel<kMode><<<static_cast<unsigned>((n_lanes + kPlanarThreads - 1) / kPlanarThreads),
-                                          kPlanarThreads, 0, stream>>>(P, in, out, active_pixels, lane0, n_lanes, spp,
-                                                                        seed, ray_weight, T, H.gate);
-        count_launch();
-        PL_TRY(cudaGetLastError());
-        PlanarPlan L = H.plan;
-        L.groups = planar_groups(P, L, static_cast<uint64_t>(nkc) * hw);
-        const dim3 grid(L.tiles_x * L.tiles_y, P.res[2], L.groups);
-        const size_t smem = sizeof(float) * static_cast<size_t>(L.tile_h + 2) * L.pitch;
-        planar_lane_kernel<kMode><<<grid, kPlanarThreads, smem, stream>>>(P, L, T, in, out, active_pixels, kc, nkc, spp,
-                                                                          ray_weight, H.gate);
-        count_launch();
-        PL_TRY(cudaGetLastError());
-    }
-    return cudaSuccess;
-}
-
-cudaError_t launch_planar_lane_forward(const SceneParams& P, PlanarHost& H, const float* active_data,
-                                       const uint32_t* active_pixels, uint64_t n_active, uint32_t spp, uint32_t seed,
-                                       float ray_weight, float* film, cudaStream_t stream) {
-    return planar_lane_pass<kScatter>(P, H, active_data, film, active_pixels, n_active, spp, seed, ray_weight, stream);
-}
-
-cudaError_t launch_planar_lane_adjoint(const SceneParams& P, PlanarHost& H, const float* dL,
-                                       const uint32_t* active_pixels, uint64_t n_active, uint32_t spp, uint32_t seed,
-                                       float ray_weight, float* grad, cudaStream_t stream) {
-    return planar_lane_pass<kGather>(P, H, dL, grad, active_pixels, n_active, spp, seed, ray_weight, stream);
 }
 
 }  // namespace drtvam

@@ -1,0 +1,476 @@
+// Jittered planar passes: regular_sampling = false, the reference's default
+// (integrators/common.py:22,92-95).
+//
+// Every lane (pixel, sample) has its own sub-pixel jitter, so no two rays share a segment and the
+// coefficient tables of the deterministic kernels (planarz_kernels.cu) do not apply.  What survives is
+// the planar structure: a ray never leaves its voxel layer (d_z = 0, sensor.py:345), the 32 DMD rows
+// above one another at one (angle, column) walk almost the same 2-D path, and the dose of a layer tile
+// can live in shared memory for all angles.  So, as in the layer-parallel kernels, a WARP takes one
+// (angle, column) and its 32 lanes are 32 voxel layers - but every lane marches its OWN jittered segment:
+//   - a pre-pass (jtable_kernel) draws each lane's samples from its PCG32 stream, traces the vial
+//     interfaces once per pass and writes the medium segment (origin, direction, length, weight) into a
+//     table ordered [angle][column][32-layer block][item][layer lane], so a warp's 32 entries are one
+//     coalesced kilobyte.  Lanes that are not one planar segment inside their block (a frozen DDA axis,
+//     sensor.py:359; a corner of a square vial; a jitter sample that lands in the next block of layers)
+//     are walked right there by the general voxel walk;
+//   - the tile kernel (planarj_kernel) owns [tile_h][tile_w][32 layers] floats of shared memory for all
+//     angles; lane = layer puts the 32 lanes of a warp on 32 different banks, so the red.shared.add of
+//     a deposit never meets a bank conflict (the per-ray tile kernel of round 1 serialised ~3.5 lanes per
+//     bank on average); the tile is flushed once with red.global.add.v4.f32.  The adjoint stages the dose
+//     gradient in the same tile and gathers with plain ld.shared.
+// Reference: TVAMIntegrator.sample_rays (integrators/common.py:70-116), DDAVolumetricSensor.accumulate
+// (sensor.py:306-440), VolumeIntegrator.render / render_backward (integrators/volume.py:18-56, 97-134).
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
+#include <vector>
+
+#include "kernels.h"
+#include "planar.cuh"
+#include "tracer.cuh"
+
+namespace drtvam {
+
+namespace {
+
+constexpr int kJThreads = 1024;
+constexpr int kJWarps = kJThreads / 32;
+constexpr int kJStride = 33;  // floats per voxel: 32 layer lanes + 1 pad (conflict-free flush)
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr int kScatter = 0, kGather = 1;
+
+struct JTable {
+    float4* a;  // ox, oy, dx, dy
+    float4* b;  // tmax, weight, layer lane inside the block (int bits, -1 = nothing to march), unused
+};
+
+// layout of the table: slot = ((((kk * res_x + c) * n_blk + blk) * items + q) * 32 + lane
+struct JLayout {
+    int n_blk;   // 32-layer blocks
+    int items;   // rows of the fullest layer x samples per pixel
+    int kc;      // first angle of the chunk, relative to the first angle of the call
+    int nkc;     // angles in the chunk
+};
+
+__device__ __forceinline__ uint32_t sampler_stream(const SceneParams& P, size_t j, uint32_t smp, uint32_t spp) {
+    const size_t g = P.sampler_index ? static_cast<size_t>(__ldg(P.sampler_index + j)) : j;
+    return static_cast<uint32_t>(g * spp + smp);
+}
+
+// One thread per table slot.  kScatter: in = active_data, out = film (only lanes walked here touch it).
+// kGather: in = dL, gT = per-slot gradient (lanes walked here write theirs, every other slot is zeroed).
+template <int kMode>
+__global__ void __launch_bounds__(256)
+jtable_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ SceneParams Pw,
+              const __grid_constant__ PlanarZPlan Z, const int* __restrict__ layer_a, const JLayout Ly,
+              const float* __restrict__ in, float* __restrict__ out, float* __restrict__ gT,
+              const uint32_t* __restrict__ active_pixels, uint64_t n_active, uint32_t spp, uint32_t seed,
+              float ray_weight, JTable T, const int* __restrict__ gate) {
+    if (*gate != 0) return;
+    const size_t t = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x;
+    const size_t total = static_cast<size_t>(Ly.nkc) * P.res_x * Ly.n_blk * Ly.items * 32;
+    if (t >= total) return;
+    const int lane = static_cast<int>(t & 31);
+    size_t r = t >> 5;
+    const int q = static_cast<int>(r % Ly.items); r /= Ly.items;
+    const int blk = static_cast<int>(r % Ly.n_blk); r /= Ly.n_blk;
+    const int c = static_cast<int>(r % P.res_x);
+    const int kk = Ly.kc + static_cast<int>(r / P.res_x);
+
+    float4 ea = make_float4(0.f, 0.f, 1.f, 0.f);
+    float4 eb = make_float4(0.f, 0.f, __int_as_float(-1), 0.f);
+    float g_here = 0.f;
+    const int a = blk * 32 + lane;
+    const int ri = q / static_cast<int>(spp), smp = q - ri * static_cast<int>(spp);
+    bool live = a < Z.nz;
+    int row = 0;
+    if (live) {
+        const int rb = __ldg(Z.a_row_begin + a), re = __ldg(Z.a_row_begin + a + 1);
+        live = ri < re - rb;
+        if (live) row = __ldg(Z.a_rows + rb + ri);
+    }
+    if (live) {
+        int k0, nk;
+        call_angles(P, active_pixels, n_active, k0, nk);
+        const size_t j = active_index(P, kk, row, c);
+        // the gate has verified the layout, so the pixel index follows from (angle, row, column)
+        const uint32_t pixel = (static_cast<uint32_t>(k0 + kk) * P.res_y + row) * P.res_x + c;
+        const uint32_t stream = sampler_stream(P, j, smp, spp);
+        Sampler rng;
+        rng.seed(seed, stream);
+        const Ray ray = generate_ray(P, pixel, rng);
+        RecordSink sink;
+        sink.seg = ray;
+        trace_lane<false>(P, ray, rng, sink);
+        const bool one = sink.count == 1 && sink.w0 != 0.f && sink.tmax > 0.f && isfinite(sink.tmax);
+        bool odd = sink.count > 1 || ray.dz != 0.f || (sink.count == 1 && sink.seg.dz != 0.f) ||
+                   (sink.count == 1 && dda_has_frozen_axis(P, sink.seg, sink.tmax));
+        int lyr = -1;
+        if (!odd && one) {
+            const float z = sink.seg.oz;
+            if (z > P.bmin[2] && z < P.bmax[2]) {
+                const float vs = (P.bmax[2] - P.bmin[2]) / static_cast<float>(P.res[2]);
+                const int layer = min(max(__float2int_rz((z - P.bmin[2]) / vs), 0), P.res[2] - 1);
+                const int aa = __ldg(layer_a + layer);   // -1: outside the z window of this handle
+                if (aa >= 0) {
+                    if ((aa >> 5) == blk) lyr = aa & 31;
+                    else odd = true;   // the jitter moved the lane into another block of layers
+                }
+            }
+        }
+        float em = 1.f;
+        if (kMode == kScatter) em = __ldg(in + j);
+        if (odd) {
+            // not a single planar segment of this block: general walk, deposited / gathered here
+            Sampler rng2;
+            rng2.seed(seed, stream);
+            const Ray ray2 = generate_ray(P, pixel, rng2);
+            if (kMode == kGather) {
+                GatherSink gs{in};
+                trace_lane<false>(Pw, ray2, rng2, gs);
+                g_here = gs.acc * ray_weight;
+            } else if (em != 0.f) {
+                ScatterSink sc{out, em * ray_weight};
+                trace_lane<false>(Pw, ray2, rng2, sc);
+            }
+        } else if (lyr >= 0) {
+            ea = make_float4(sink.seg.ox, sink.seg.oy, sink.seg.dx, sink.seg.dy);
+            eb = make_float4(sink.tmax, em * ray_weight * sink.w0, __int_as_float(lyr), 0.f);
+        }
+    }
+    T.a[t] = ea;
+    T.b[t] = eb;
+    if (kMode == kGather) gT[t] = g_here;
+}
+
+// kScatter: out = film (red.global flush).  kGather: in = dL (film layout), out = gT (red.global per lane).
+template <int kMode>
+__global__ void __launch_bounds__(kJThreads, 1)
+planarj_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ PlanarZPlan Z, const JLayout Ly,
+               const JTable T, const float* __restrict__ in, float* __restrict__ out,
+               const uint32_t* __restrict__ active_pixels, uint64_t n_active, const int* __restrict__ gate) {
+    extern __shared__ __align__(16) float tile[];
+    if (*gate != 0) return;
+    const int tile_id = blockIdx.x, blk = blockIdx.y, group = blockIdx.z;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int x0 = (tile_id % Z.tiles_x) * Z.tile_w, y0 = (tile_id / Z.tiles_x) * Z.tile_h;
+    const int w = min(Z.tile_w, P.res[0] - x0), h = min(Z.tile_h, P.res[1] - y0);
+    const int tw = Z.tile_w;
+    const int tile_floats = Z.tile_h * tw * kJStride;
+    const int a_base = blk * 32;
+    const size_t layer_elems = static_cast<size_t>(P.res[0]) * P.res[1];
+
+    // ---- stage the tile
+    if (kMode == kScatter) {
+        for (int i = threadIdx.x; i < tile_floats; i += kJThreads) tile[i] = 0.f;
+    } else {
+        const int per_layer = h * w;
+        for (int i = threadIdx.x; i < 32 * per_layer; i += kJThreads) {
+            const int al = i / per_layer, rem = i - al * per_layer;
+            const int yy = rem / w, xx = rem - yy * w;
+            const int z = (a_base + al < Z.nz) ? __ldg(Z.zl + a_base + al) : -1;
+            float v = 0.f;
+            if (z >= 0) v = __ldg(in + z * layer_elems + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx));
+            tile[(yy * tw + xx) * kJStride + al] = v;
+        }
+    }
+    __syncthreads();
+
+    int k0, nk;
+    call_angles(P, active_pixels, n_active, k0, nk);
+    const int kfirst = k0 + Ly.kc;   // first angle held by the table
+    const int ka = kfirst + static_cast<int>(static_cast<long long>(Ly.nkc) * group / Z.groups);
+    const int kb = kfirst + static_cast<int>(static_cast<long long>(Ly.nkc) * (group + 1) / Z.groups);
+    const int* __restrict__ off = Z.tile_off + static_cast<size_t>(tile_id) * (P.n_patterns + 1);
+    const int* __restrict__ clo = Z.tile_clo + static_cast<size_t>(tile_id) * P.n_patterns;
+
+    const float sig = P.sigma_t * kLog2e;
+    const float vsx = (P.bmax[0] - P.bmin[0]) / static_cast<float>(P.res[0]);
+    const float vsy = (P.bmax[1] - P.bmin[1]) / static_cast<float>(P.res[1]);
+    const uint32_t tile_s = static_cast<uint32_t>(__cvta_generic_to_shared(tile));
+    const int sxb = 4 * kJStride, syb = 4 * kJStride * tw;
+
+    const int f_base = __ldg(off + ka);
+    const int tasks = (__ldg(off + kb) - f_base) * Ly.items;   // < 2^31: checked by planarj_pass
+    int k = ka;
+    for (int f = warp; f < tasks; f += kJWarps) {
+        const int g = f / Ly.items + f_base;
+        const int q = f - (g - f_base) * Ly.items;
+        while (__ldg(off + k + 1) <= g) ++k;
+        const int c = __ldg(clo + k) + (g - __ldg(off + k));
+        const size_t slot = ((((static_cast<size_t>(k - kfirst) * P.res_x + c) * Ly.n_blk + blk) * Ly.items + q) << 5) + lane;
+        const float4 eb = __ldg(T.b + slot);
+        const int lyr = __float_as_int(eb.z);
+        bool live = lyr >= 0 && eb.y != 0.f;
+        if (!__any_sync(0xffffffffu, live)) continue;
+        float4 ea = make_float4(0.f, 0.f, 1.f, 0.f);
+        if (live) ea = __ldg(T.a + slot);
+
+        // ---- clip to the tile; entry / exit voxel by truncation then clip (sensor.py:345-346), tile-local
+        float t0 = 0.f, t1 = 0.f;
+        live = live && clip_to_tile(P, ea, eb.x, x0, y0, w, h, t0, t1);
+        float acc = 0.f;
+        if (live) {
+            const float gx = fmaf(ea.z, t0, ea.x), gy = fmaf(ea.w, t0, ea.y);
+            const float hx = fmaf(ea.z, t1, ea.x), hy = fmaf(ea.w, t1, ea.y);
+            const int ix = min(max(__float2int_rz((gx - P.bmin[0]) / vsx) - x0, 0), w - 1);
+            const int iy = min(max(__float2int_rz((gy - P.bmin[1]) / vsy) - y0, 0), h - 1);
+            const int jx = min(max(__float2int_rz((hx - P.bmin[0]) / vsx) - x0, 0), w - 1);
+            const int jy = min(max(__float2int_rz((hy - P.bmin[1]) / vsy) - y0, 0), h - 1);
+            const float u0 = sig * t0, u1 = sig * t1;
+            float ux = INFINITY, uy = INFINITY, ax = 0.f, ay = 0.f, bx = 0.f, by = 0.f, fx = 0.f, fy = 0.f;
+            int nx = 0, ny = 0, sx = 0, sy = 0;
+            if (fabsf(ea.z) > 1e-8f) {
+                const float inv = sig / ea.z;
+                const bool pos = ea.z > 0.f;
+                nx = max(pos ? jx - ix : ix - jx, 0);
+                sx = pos ? sxb : -sxb;
+                ax = fabsf(vsx * inv);
+                // boundary times relative to the tile entry: the cancellation sits in (boundary - g)
+                bx = fmaf(fmaf(static_cast<float>(x0 + ix + (pos ? 1 : 0)), vsx, P.bmin[0]) - gx, inv, u0);
+                if (nx > 0) ux = bx;
+            }
+            if (fabsf(ea.w) > 1e-8f) {
+                const float inv = sig / ea.w;
+                const bool pos = ea.w > 0.f;
+                ny = max(pos ? jy - iy : iy - jy, 0);
+                sy = pos ? syb : -syb;
+                ay = fabsf(vsy * inv);
+                by = fmaf(fmaf(static_cast<float>(y0 + iy + (pos ? 1 : 0)), vsy, P.bmin[1]) - gy, inv, u0);
+                if (ny > 0) uy = by;
+            }
+            uint32_t addr = tile_s + 4u * static_cast<uint32_t>((iy * tw + ix) * kJStride + lyr);
+            float e_prev = ex2_approx(-u0);
+            const float wgt = eb.y;
+            // every lane walks its own segment; lanes of a warp differ by a sub-pixel shift, so their step
+            // counts agree to within a voxel or two and the loop stays nearly converged
+            for (int n = nx + ny; n > 0; --n) {
+                const bool px = ux <= uy;
+                const float e = ex2_approx(-(px ? ux : uy));
+                const float de = e_prev - e;
+                e_prev = e;
+                if (kMode == kGather) {
+                    float v;
+                    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+                    acc = fmaf(v, de, acc);
+                } else {
+                    asm volatile("red.shared.add.f32 [%0], %1;" ::"r"(addr), "f"(wgt * de) : "memory");
+                }
+                if (px) {
+                    fx += 1.f;
+                    ux = fmaf(fx, ax, bx);
+                    addr += sx;
+                    if (--nx == 0) ux = INFINITY;
+                } else {
+                    fy += 1.f;
+                    uy = fmaf(fy, ay, by);
+                    addr += sy;
+                    if (--ny == 0) uy = INFINITY;
+                }
+            }
+            const float de = e_prev - ex2_approx(-u1);
+            if (kMode == kGather) {
+                float v;
+                asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+                acc = fmaf(v, de, acc);
+            } else {
+                asm volatile("red.shared.add.f32 [%0], %1;" ::"r"(addr), "f"(wgt * de) : "memory");
+            }
+        }
+        if (kMode == kGather && live && acc != 0.f) atomicAdd(out + slot, acc * eb.y);
+    }
+    if (kMode == kGather) return;
+    __syncthreads();
+
+    // ---- flush: one red.global per voxel (v4 when the rows are 16-byte aligned in the film)
+    const bool vec = ((x0 | w | P.res[0]) & 3) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0;
+    if (vec) {
+        const int w4 = w >> 2, per_layer = h * w4;
+        for (int i = threadIdx.x; i < 32 * per_layer; i += kJThreads) {
+            const int al = i / per_layer, rem = i - al * per_layer;
+            const int yy = rem / w4, xx = (rem - yy * w4) << 2;
+            const int z = (a_base + al < Z.nz) ? __ldg(Z.zl + a_base + al) : -1;
+            if (z < 0) continue;
+            const float* src = tile + (yy * tw + xx) * kJStride + al;
+            const float v0 = src[0], v1 = src[kJStride], v2 = src[2 * kJStride], v3 = src[3 * kJStride];
+            if (v0 != 0.f || v1 != 0.f || v2 != 0.f || v3 != 0.f)
+                red_add_v4(out + z * layer_elems + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx), v0, v1, v2, v3);
+        }
+    } else {
+        const int per_layer = h * w;
+        for (int i = threadIdx.x; i < 32 * per_layer; i += kJThreads) {
+            const int al = i / per_layer, rem = i - al * per_layer;
+            const int yy = rem / w, xx = rem - yy * w;
+            const int z = (a_base + al < Z.nz) ? __ldg(Z.zl + a_base + al) : -1;
+            if (z < 0) continue;
+            const float v = tile[(yy * tw + xx) * kJStride + al];
+            if (v != 0.f) atomicAdd(out + z * layer_elems + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx), v);
+        }
+    }
+}
+
+// gT [slot]  ->  pattern_grad [kk][row][col] = sum over the samples of the pixel (the dr.repeat of common.py:82)
+__global__ void __launch_bounds__(256)
+junpack_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ PlanarZPlan Z, const int* __restrict__ row_ri,
+               const JLayout Ly, const float* __restrict__ gT, float* __restrict__ grad, uint32_t spp,
+               const int* __restrict__ gate) {
+    __shared__ float tr[32][33];
+    if (*gate != 0) return;
+    const int kk = blockIdx.z;   // relative to the chunk
+    const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    for (int j = ty; j < 32; j += 8) {
+        const int c = c0 + j, r = P.row_begin + r0 + tx;
+        float v = 0.f;
+        if (c < P.res_x && r < P.row_begin + P.n_rows) {
+            const int a = __ldg(Z.row_a + r);
+            if (a >= 0) {
+                const int ri = __ldg(row_ri + r);
+                const size_t base = ((((static_cast<size_t>(kk) * P.res_x + c) * Ly.n_blk + (a >> 5)) * Ly.items +
+                                      static_cast<size_t>(ri) * spp) << 5) + (a & 31);
+                for (uint32_t s = 0; s < spp; ++s) v += __ldg(gT + base + (static_cast<size_t>(s) << 5));
+            }
+        }
+        tr[j][tx] = v;
+    }
+    __syncthreads();
+    for (int j = ty; j < 32; j += 8) {
+        const int r = P.row_begin + r0 + j, c = c0 + tx;
+        if (r < P.row_begin + P.n_rows && c < P.res_x) grad[active_index(P, Ly.kc + kk, r, c)] = tr[tx][j];
+    }
+}
+
+}  // namespace
+
+#define PJ_TRY(expr)                      \
+    do {                                  \
+        cudaError_t _e = (expr);          \
+        if (_e != cudaSuccess) return _e; \
+    } while (0)
+
+void planarj_release(PlanarJHost& J) {
+    void* ptrs[] = {J.tile_off, J.tile_clo, J.table, J.gT};
+    for (void* p : ptrs)
+        if (p) cudaFree(p);
+    J = PlanarJHost();
+}
+
+// Tile geometry (the largest xy tile whose [h][w][33] float slab fits the 227 KB of opt-in shared
+// memory) and the conservative per-(tile, angle) column ranges: a jittered ray of column c lies within
+// half a pixel of the centre ray of c, refraction can magnify that, hence the margin of 1.5 pixels.
+cudaError_t planarj_build(const SceneParams& P, const PlanarHost& base, const PlanarZHost& Zh, PlanarJHost& J) {
+    planarj_release(J);
+    if (!Zh.valid || Zh.nz == 0) return cudaSuccess;
+    const int np = P.n_patterns, rx = P.res[0], ry = P.res[1];
+    const int area = (227 * 1024 / 4) / kJStride;
+    const int side = static_cast<int>(std::floor(std::sqrt(static_cast<double>(area))));
+    const int tw_max = std::max(4, side & ~3);
+    J.tiles_x = (rx + tw_max - 1) / tw_max;
+    J.tile_w = (((rx + J.tiles_x - 1) / J.tiles_x) + 3) & ~3;
+    J.tiles_x = (rx + J.tile_w - 1) / J.tile_w;
+    const int th_max = std::max(1, area / J.tile_w);
+    J.tiles_y = (ry + th_max - 1) / th_max;
+    J.tile_h = (ry + J.tiles_y - 1) / J.tiles_y;
+    J.smem_bytes = sizeof(float) * static_cast<size_t>(J.tile_h) * J.tile_w * kJStride;
+    const int n_tiles = J.tiles_x * J.tiles_y;
+    PJ_TRY(cudaMalloc(&J.tile_off, sizeof(int) * static_cast<size_t>(n_tiles) * (np + 1)));
+    PJ_TRY(cudaMalloc(&J.tile_clo, sizeof(int) * static_cast<size_t>(n_tiles) * np));
+    const float margin = 1.5f * std::fmax(P.pixel_x, P.pixel_y);
+    PJ_TRY(planar_tile_ranges(P, base.seg_a, base.seg_b, J.tiles_x, J.tiles_y, J.tile_w, J.tile_h, J.tile_off, J.tile_clo,
+                              margin));
+    PJ_TRY(cudaFuncSetAttribute(planarj_kernel<kScatter>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                static_cast<int>(J.smem_bytes)));
+    PJ_TRY(cudaFuncSetAttribute(planarj_kernel<kGather>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                static_cast<int>(J.smem_bytes)));
+    J.valid = true;
+    return cudaSuccess;
+}
+
+static cudaError_t j_reserve(void*& ptr, size_t& have, size_t need) {
+    if (need <= have) return cudaSuccess;
+    if (ptr) cudaFree(ptr);
+    ptr = nullptr;
+    have = 0;
+    PJ_TRY(cudaMalloc(&ptr, need));
+    have = need;
+    return cudaSuccess;
+}
+
+template <int kMode>
+static cudaError_t planarj_pass(const SceneParams& P, const SceneParams& Pw, PlanarZHost& Zh, PlanarJHost& J,
+                                const int* gate, const float* in, float* out, const uint32_t* active_pixels,
+                                uint64_t n_active, uint32_t spp, uint32_t seed, float ray_weight,
+                                cudaStream_t stream) {
+    const int nk = static_cast<int>(n_active / (static_cast<uint64_t>(P.res_x) * P.n_rows));
+    JLayout Ly{};
+    Ly.n_blk = Zh.nz_pad / 32;
+    Ly.items = std::max(1, Zh.rows_max) * static_cast<int>(spp);
+    if (static_cast<long long>(P.n_patterns) * P.res_x * Ly.items >= (1ll << 31)) return cudaErrorInvalidValue;
+    const size_t slots_per_angle = static_cast<size_t>(P.res_x) * Ly.n_blk * Ly.items * 32;
+    // at most ~4 GB of table (32 bytes per slot, + 4 for the adjoint's per-slot gradients)
+    size_t cap = 4ull << 30;
+    if (const char* env = std::getenv("DRTVAM_JTABLE_MB")) cap = static_cast<size_t>(std::atoll(env)) << 20;
+    const size_t per_slot = 32 + (kMode == kGather ? 4 : 0);
+    int chunk = static_cast<int>(std::max<size_t>(1, cap / (slots_per_angle * per_slot)));
+    chunk = std::min(chunk, nk);
+    const size_t slots_max = slots_per_angle * chunk;
+    PJ_TRY(j_reserve(J.table, J.table_bytes, slots_max * 32));
+    if (kMode == kGather) {
+        void* g = J.gT;
+        PJ_TRY(j_reserve(g, J.gT_bytes, slots_max * 4));
+        J.gT = static_cast<float*>(g);
+    }
+    JTable T;
+    T.a = static_cast<float4*>(J.table);
+    T.b = T.a + slots_max;
+
+    PlanarZPlan Z{};
+    Z.zl = Zh.zl; Z.a_row_begin = Zh.a_row_begin; Z.a_rows = Zh.a_rows; Z.row_a = Zh.row_a;
+    Z.nz = Zh.nz; Z.nz_pad = Zh.nz_pad;
+    Z.tiles_x = J.tiles_x; Z.tiles_y = J.tiles_y; Z.tile_w = J.tile_w; Z.tile_h = J.tile_h;
+    Z.tile_off = J.tile_off; Z.tile_clo = J.tile_clo;
+    Z.lanes_l = 1;
+    const long long ctas = static_cast<long long>(J.tiles_x) * J.tiles_y * Ly.n_blk;
+
+    for (int kc = 0; kc < nk; kc += chunk) {
+        Ly.kc = kc;
+        Ly.nkc = std::min(chunk, nk - kc);
+        const size_t slots = slots_per_angle * Ly.nkc;
+        jtable_kernel<kMode><<<static_cast<unsigned>((slots + 255) / 256), 256, 0, stream>>>(
+            P, Pw, Z, Zh.layer_a, Ly, in, out, J.gT, active_pixels, n_active, spp, seed, ray_weight, T, gate);
+        count_launch();
+        PJ_TRY(cudaGetLastError());
+        // enough CTAs for two waves of the 148 SMs: the tile flush is a red.global, so angle groups are free
+        long long groups = (148 * 2 + ctas - 1) / std::max<long long>(ctas, 1);
+        groups = std::max<long long>(1, std::min<long long>(groups, std::max(1, Ly.nkc / 4)));
+        Z.groups = static_cast<int>(groups);
+        const dim3 grid(J.tiles_x * J.tiles_y, Ly.n_blk, Z.groups);
+        planarj_kernel<kMode><<<grid, kJThreads, J.smem_bytes, stream>>>(P, Z, Ly, T, in, kMode == kGather ? J.gT : out,
+                                                                        active_pixels, n_active, gate);
+        count_launch();
+        PJ_TRY(cudaGetLastError());
+        if (kMode == kGather) {
+            const dim3 ugrid((P.res_x + 31) / 32, (P.n_rows + 31) / 32, Ly.nkc);
+            junpack_kernel<<<ugrid, 256, 0, stream>>>(P, Z, Zh.row_ri, Ly, J.gT, out, spp, gate);
+            count_launch();
+            PJ_TRY(cudaGetLastError());
+        }
+    }
+    return cudaSuccess;
+}
+
+cudaError_t launch_planarj_forward(const SceneParams& P, const SceneParams& Pw, PlanarZHost& Zh, PlanarJHost& J,
+                                   const int* gate, const float* active_data, const uint32_t* active_pixels,
+                                   uint64_t n_active, uint32_t spp, uint32_t seed, float ray_weight, float* film,
+                                   bool, cudaStream_t stream) {
+    return planarj_pass<kScatter>(P, Pw, Zh, J, gate, active_data, film, active_pixels, n_active, spp, seed, ray_weight,
+                                  stream);
+}
+
+cudaError_t launch_planarj_adjoint(const SceneParams& P, const SceneParams& Pw, PlanarZHost& Zh, PlanarJHost& J,
+                                   const int* gate, const float* dL, const uint32_t* active_pixels, uint64_t n_active,
+                                   uint32_t spp, uint32_t seed, float ray_weight, float* grad, cudaStream_t stream) {
+    return planarj_pass<kGather>(P, Pw, Zh, J, gate, dL, grad, active_pixels, n_active, spp, seed, ray_weight, stream);
+}
+
+}  // namespace drtvam

@@ -60,7 +60,7 @@ zpack_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Plan
             const int rb = __ldg(Z.a_row_begin + a), re = __ldg(Z.a_row_begin + a + 1);
             for (int ri = rb; ri < re; ++ri) {
                 const int r = __ldg(Z.a_rows + ri);
-                v += __ldg(active_data + (static_cast<size_t>(kk) * P.res_y + r) * P.res_x + c);
+                v += __ldg(active_data + active_index(P, kk, r, c));
             }
         }
         tr[j][tx] = v;
@@ -84,9 +84,9 @@ zunpack_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
     const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     for (int j = ty; j < 32; j += 8) {
-        const int c = c0 + j, r = r0 + tx;
+        const int c = c0 + j, r = P.row_begin + r0 + tx;
         float v = 0.f;
-        if (c < P.res_x && r < P.res_y) {
+        if (c < P.res_x && r < P.row_begin + P.n_rows) {
             const int a = __ldg(Z.row_a + r);
             if (a >= 0) v = __ldg(gT + (static_cast<size_t>(kk) * P.res_x + c) * Z.nz_pad + a);
         }
@@ -94,8 +94,8 @@ zunpack_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
     }
     __syncthreads();
     for (int j = ty; j < 32; j += 8) {
-        const int r = r0 + j, c = c0 + tx;
-        if (r < P.res_y && c < P.res_x) grad[(static_cast<size_t>(kk) * P.res_y + r) * P.res_x + c] = tr[tx][j];
+        const int r = P.row_begin + r0 + j, c = c0 + tx;
+        if (r < P.row_begin + P.n_rows && c < P.res_x) grad[active_index(P, kk, r, c)] = tr[tx][j];
     }
 }
 
@@ -367,9 +367,8 @@ planarz_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
     }
     __syncthreads();
 
-    const uint32_t hw = static_cast<uint32_t>(P.res_x) * P.res_y;
-    const uint32_t base = __ldg(active_pixels);
-    const int k0 = base / hw, nk = static_cast<int>(n_active / hw);
+    int k0, nk;
+    call_angles(P, active_pixels, n_active, k0, nk);
     const int ka = k0 + static_cast<int>(static_cast<long long>(nk) * group / Z.groups);
     const int kb = k0 + static_cast<int>(static_cast<long long>(nk) * (group + 1) / Z.groups);
     const int* __restrict__ off = Z.tile_off + static_cast<size_t>(tile_id) * (P.n_patterns + 1);
@@ -705,8 +704,8 @@ planarg_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
     }
     __syncwarp();
 
-    const uint32_t hw = static_cast<uint32_t>(P.res_x) * P.res_y;
-    const int k0 = __ldg(active_pixels) / hw, nk = static_cast<int>(n_active / hw);
+    int k0, nk;
+    call_angles(P, active_pixels, n_active, k0, nk);
     const int* __restrict__ off = Z.tile_off + static_cast<size_t>(tile_id) * (P.n_patterns + 1);
     const int ebase = __ldg(Z.tile_ebase + tile_id);
     const int g0 = ebase + __ldg(off + k0), g1 = ebase + __ldg(off + k0 + nk);
@@ -834,7 +833,7 @@ void planarz_release(PlanarZHost& H) {
         for (void* p : ptrs)
             if (p) cudaFree(p);
     }
-    void* ptrs[] = {H.zl, H.a_row_begin, H.a_rows, H.row_a, H.scratch};
+    void* ptrs[] = {H.zl, H.a_row_begin, H.a_rows, H.row_a, H.layer_a, H.row_ri, H.scratch};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     H = PlanarZHost();
@@ -907,7 +906,7 @@ static cudaError_t z_build_sub(const SceneParams& P, const PlanarHost& base, con
 }
 
 cudaError_t planarz_build(const SceneParams& P, const PlanarHost& base, const std::vector<int>& row_layer,
-                          PlanarZHost& H) {
+                          PlanarZHost& H, bool walks) {
     planarz_release(H);
     int max_l = 4;
     if (const char* env = std::getenv("DRTVAM_Z_LAYERS")) {
@@ -916,14 +915,18 @@ cudaError_t planarz_build(const SceneParams& P, const PlanarHost& base, const st
     }
     const int rz = P.res[2], Hh = P.res_y;
     // active layers and their rows
-    std::vector<int> zl, a_row_begin(1, 0), a_rows, row_a(Hh, -1);
+    std::vector<int> zl, a_row_begin(1, 0), a_rows, row_a(Hh, -1), layer_a(rz, -1), row_ri(Hh, 0);
     std::vector<std::vector<int>> rows_of(rz);
-    for (int r = 0; r < Hh; ++r)
-        if (row_layer[r] >= 0) rows_of[row_layer[r]].push_back(r);
+    // only rows of the call's row range and layers of its z window (drtvam_scene_set_z_window) take part;
+    // zl holds the layer index inside the window, i.e. inside the film buffers of a call
+    for (int r = P.row_begin; r < P.row_begin + P.n_rows && r < Hh; ++r)
+        if (row_layer[r] >= P.z_begin && row_layer[r] < P.z_end) rows_of[row_layer[r]].push_back(r);
     for (int z = 0; z < rz; ++z) {
         if (rows_of[z].empty()) continue;
-        for (int r : rows_of[z]) { a_rows.push_back(r); row_a[r] = static_cast<int>(zl.size()); }
-        zl.push_back(z);
+        int ri = 0;
+        for (int r : rows_of[z]) { a_rows.push_back(r); row_a[r] = static_cast<int>(zl.size()); row_ri[r] = ri++; }
+        layer_a[z] = static_cast<int>(zl.size());
+        zl.push_back(z - P.z_begin);
         a_row_begin.push_back(static_cast<int>(a_rows.size()));
     }
     const int nz = static_cast<int>(zl.size());
@@ -937,13 +940,20 @@ cudaError_t planarz_build(const SceneParams& P, const PlanarHost& base, const st
     PZ_TRY(cudaMalloc(&H.a_row_begin, sizeof(int) * (nz + 1)));
     PZ_TRY(cudaMalloc(&H.a_rows, sizeof(int) * a_rows.size()));
     PZ_TRY(cudaMalloc(&H.row_a, sizeof(int) * Hh));
+    PZ_TRY(cudaMalloc(&H.layer_a, sizeof(int) * rz));
+    PZ_TRY(cudaMalloc(&H.row_ri, sizeof(int) * Hh));
+    PZ_TRY(cudaMemcpy(H.layer_a, layer_a.data(), sizeof(int) * rz, cudaMemcpyHostToDevice));
+    PZ_TRY(cudaMemcpy(H.row_ri, row_ri.data(), sizeof(int) * Hh, cudaMemcpyHostToDevice));
     PZ_TRY(cudaMemcpy(H.zl, zl.data(), sizeof(int) * H.nz_pad, cudaMemcpyHostToDevice));
     PZ_TRY(cudaMemcpy(H.a_row_begin, a_row_begin.data(), sizeof(int) * (nz + 1), cudaMemcpyHostToDevice));
     PZ_TRY(cudaMemcpy(H.a_rows, a_rows.data(), sizeof(int) * a_rows.size(), cudaMemcpyHostToDevice));
     PZ_TRY(cudaMemcpy(H.row_a, row_a.data(), sizeof(int) * Hh, cudaMemcpyHostToDevice));
 
-    // split the layer units into runs of blocks with 4, 2 and 1 layers per lane (no padded blocks)
-    int done = 0;
+    H.rows_max = 0;
+    for (int a = 0; a < nz; ++a) H.rows_max = std::max(H.rows_max, a_row_begin[a + 1] - a_row_begin[a]);
+    // split the layer units into runs of blocks with 4, 2 and 1 layers per lane (no padded blocks);
+    // the jittered kernels (planarj_kernels.cu) only need the layer tables above
+    int done = walks ? 0 : units;
     for (int kL = max_l; kL >= 1 && done < units; kL >>= 1) {
         const int n_blocks = (units - done) / kL;
         if (n_blocks == 0) continue;
@@ -990,7 +1000,7 @@ template <int kMode>
 static cudaError_t z_launch(const SceneParams& P, PlanarZHost& H, const float* in, float* out,
                             const uint32_t* active_pixels, uint64_t n_active, float w, const int* gate,
                             cudaStream_t stream) {
-    const int nk = static_cast<int>(n_active / (static_cast<uint64_t>(P.res_x) * P.res_y));
+    const int nk = static_cast<int>(n_active / (static_cast<uint64_t>(P.res_x) * P.n_rows));
     for (int i = 0; i < H.n_sub; ++i) {
         const PlanarZSub& S = H.sub[i];
         PlanarZPlan Z = S.plan;
@@ -1015,7 +1025,7 @@ static cudaError_t z_launch(const SceneParams& P, PlanarZHost& H, const float* i
 cudaError_t launch_planarz_forward(const SceneParams& P, PlanarZHost& H, const int* gate, const float* active_data,
                                    const uint32_t* active_pixels, uint64_t n_active, float ray_weight, float* film,
                                    cudaStream_t stream) {
-    const int nk = static_cast<int>(n_active / (static_cast<uint64_t>(P.res_x) * P.res_y));
+    const int nk = static_cast<int>(n_active / (static_cast<uint64_t>(P.res_x) * P.n_rows));
     const PlanarZPlan& Z0 = H.sub[0].plan;
     PZ_TRY(z_scratch(H, sizeof(float) * static_cast<size_t>(nk) * P.res_x * H.nz_pad));
     const dim3 pgrid((P.res_x + 31) / 32, H.nz_pad / 32, nk);
@@ -1028,12 +1038,12 @@ cudaError_t launch_planarz_forward(const SceneParams& P, PlanarZHost& H, const i
 cudaError_t launch_planarz_adjoint(const SceneParams& P, PlanarZHost& H, const int* gate, const float* dL,
                                    const uint32_t* active_pixels, uint64_t n_active, float ray_weight, float* grad,
                                    cudaStream_t stream) {
-    const int nk = static_cast<int>(n_active / (static_cast<uint64_t>(P.res_x) * P.res_y));
+    const int nk = static_cast<int>(n_active / (static_cast<uint64_t>(P.res_x) * P.n_rows));
     const size_t bytes = sizeof(float) * static_cast<size_t>(nk) * P.res_x * H.nz_pad;
     PZ_TRY(z_scratch(H, bytes));
     PZ_TRY(cudaMemsetAsync(H.scratch, 0, bytes, stream));
     PZ_TRY(z_launch<kGather>(P, H, dL, H.scratch, active_pixels, n_active, ray_weight, gate, stream));
-    const dim3 ugrid((P.res_x + 31) / 32, (P.res_y + 31) / 32, nk);
+    const dim3 ugrid((P.res_x + 31) / 32, (P.n_rows + 31) / 32, nk);
     zunpack_kernel<<<ugrid, 256, 0, stream>>>(P, H.sub[0].plan, H.scratch, grad, gate);
     count_launch();
     return cudaGetLastError();
@@ -1155,7 +1165,7 @@ cudaError_t planarg_build(const SceneParams& P, const PlanarHost& base, const Pl
 cudaError_t launch_planarg_forward(const SceneParams& P, PlanarZHost& H, PlanarGHost& G, const int* gate,
                                    const float* active_data, const uint32_t* active_pixels, uint64_t n_active,
                                    float ray_weight, float* film, bool fresh, cudaStream_t stream) {
-    const int nk = static_cast<int>(n_active / (static_cast<uint64_t>(P.res_x) * P.res_y));
+    const int nk = static_cast<int>(n_active / (static_cast<uint64_t>(P.res_x) * P.n_rows));
     PZ_TRY(z_scratch(H, sizeof(float) * static_cast<size_t>(nk) * P.res_x * H.nz_pad));
     const dim3 pgrid((P.res_x + 31) / 32, H.nz_pad / 32, nk);
     zpack_kernel<<<pgrid, 256, 0, stream>>>(P, H.sub[0].plan, active_data, H.scratch, nk, gate);

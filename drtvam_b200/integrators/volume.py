@@ -68,9 +68,10 @@ class VolumeIntegrator(TVAMIntegrator):
         handle = scene.handle(self, sensor)
         inv_scalar, inv_tensor = _inv_volume(sensor, scene)
         film = sensor.film()
-        film.data = torch.empty(film.shape, device=projector.active_data.device, dtype=torch.float32)
+        film.data = torch.empty(scene.film_shape(sensor), device=projector.active_data.device, dtype=torch.float32)
         data = active_data.detach().to(torch.float32).contiguous()
         pixels = projector.active_pixels
+        scene.pin_pixels(handle, pixels)
         if data.numel() != pixels.numel():
             raise ValueError(f"[{projector.__class__.__name__}] active_data and active_pixels must have the same length.")
         lib = _lib.load()
@@ -97,14 +98,21 @@ class VolumeIntegrator(TVAMIntegrator):
         with torch.no_grad():
             return self._project(scene, sensor, seed, spp, scene.emitters()[0].active_data)
 
-    def render_forward(self, scene, params=None, sensor=0, seed: int = 0, spp: int = 0, tangent=None):
-        """Forward-mode derivative: A is linear in the patterns, so the JVP is A
-        applied to the tangent (volume.py:58-95)."""
+    def render_forward(self, scene, params, sensor=0, seed: int = 0, spp: int = 0):
+        """Forward-mode derivative (volume.py:58-95), same signature as the reference.  There the
+        tangent is the gradient attached to the pattern values (`dr.set_grad(params[key], tangent)`,
+        picked up by `dr.forward_to(Le)`, volume.py:159-160); here it is the `.grad` of
+        `params['projector.active_data']` (or of the projector's own tensor when `params` is None).  A is
+        linear in the patterns, so the derivative is A applied to the tangent; without an attached
+        tangent it is zero."""
         _check_emitters(scene)
-        if tangent is None:
-            raise ValueError("render_forward needs the tangent of projector.active_data")
+        data = params['projector.active_data'] if params is not None else scene.emitters()[0].active_data
+        tangent = getattr(data, 'grad', None)
         with torch.no_grad():
-            return self._project(scene, sensor, seed, spp, tangent)
+            if tangent is None:
+                return torch.zeros(scene.film_shape(_sensor_of(scene, sensor)),
+                                   device=scene.emitters()[0].active_data.device, dtype=torch.float32)
+            return self._project(scene, sensor, seed, spp, tangent.reshape(-1))
 
     def render_backward(self, scene, params, grad_in, sensor=0, seed: int = 0, spp: int = 0):
         """Adjoint A^T grad_in; returns d loss / d projector.active_data."""
@@ -114,12 +122,12 @@ class VolumeIntegrator(TVAMIntegrator):
         spp, _ = self.prepare(projector, seed, spp)
         handle = scene.handle(self, sensor)
         inv_scalar, inv_tensor = _inv_volume(sensor, scene)
-        film = sensor.film()
         g = grad_in.detach().to(torch.float32)
-        if tuple(g.shape) != tuple(film.shape):
-            g = g.reshape(film.shape)
+        if tuple(g.shape) != tuple(scene.film_shape(sensor)):
+            g = g.reshape(scene.film_shape(sensor))
         g = g.contiguous()
         pixels = projector.active_pixels
+        scene.pin_pixels(handle, pixels)
         out = torch.empty(pixels.numel(), device=g.device, dtype=torch.float32)
         lib = _lib.load()
         ev = self._event_pair('adjoint')

@@ -41,6 +41,7 @@ class _FusedThresholded(torch.autograd.Function):
         from . import _lib
         lib = _lib.load()
         n = x.numel()
+        n_mean = loss.dose_count if (loss.dose_allsum is not None and loss.dose_count) else n
         need_grad = x.requires_grad and torch.is_grad_enabled()
         ctx.has_grad = bool(x.requires_grad)
         grad = torch.empty_like(x) if x.requires_grad else None
@@ -49,12 +50,15 @@ class _FusedThresholded(torch.autograd.Function):
         _lib.check(lib.drtvam_thresholded_loss(
             x.device.index or 0, x.data_ptr(), dx.data_ptr() if dx is not None else None, float(alpha),
             target.data_ptr(), n, float(loss.tl), float(loss.tu), float(loss.weight_object), float(loss.weight_void),
-            float(loss.weight_limit), int(loss.K), (1.0 / n) if mean else 1.0,
+            float(loss.weight_limit), int(loss.K), (1.0 / n_mean) if mean else 1.0,
             grad.data_ptr() if grad is not None else None, out.data_ptr(),
             torch.cuda.current_stream(x.device).cuda_stream))
         ctx.grad = grad
         del need_grad
-        res = out[0] / n if mean else out[0]
+        total = out[0]
+        if loss.dose_allsum is not None:      # z-slab shard: the dose term is a sum over ranks
+            total = loss.dose_allsum(total)
+        res = total / n_mean if mean else total
         return res.to(torch.float32)
 
     @staticmethod
@@ -74,6 +78,9 @@ class Loss:
             raise ValueError(f"Invalid reduction method: '{reduction}'.")
         # sum of the (angle-sharded) pattern term over ranks; identity on one GPU
         self.pattern_allsum = None
+        # z-slab sharding: every rank holds a slab of the dose, so the dose term is summed over ranks too
+        self.dose_allsum = None
+        self.dose_count = None   # total number of dose elements over all ranks (reduction 'mean')
 
     def eval_in(self, x):
         raise NotImplementedError
@@ -96,6 +103,19 @@ class Loss:
             n = self.pattern_allsum(torch.tensor(float(lp.numel()), device=lp.device))
             return self.pattern_allsum(lp.sum()) / n
         return self.pattern_allsum(lp.sum())
+
+    def _reduce_dose(self, l):
+        """Reduction of the per-voxel dose term; with a z-slab shard the value is the sum over all ranks
+        while the gradient still flows to the local voxels (d total / d local = d local sum / d local)."""
+        if self.dose_allsum is None:
+            return self.reduction(l)
+        local = l.sum()
+        total = local + (self.dose_allsum(local.detach()) - local.detach())
+        if self.reduction is torch.mean:
+            n = self.dose_count if self.dose_count else float(
+                self.dose_allsum(torch.tensor(float(l.numel()), device=l.device)))
+            return total / n
+        return total
 
     accepts_lazy = True
 
@@ -120,7 +140,7 @@ class Loss:
             raise ValueError(f"[Loss] Received tensors of invalid shape: {tuple(target.shape)}. "
                              "The last dimension should be either 1 or 2.")
         # the two terms have different shapes, hence separate reductions
-        return self.reduction(loss) + self._reduce_patterns(loss_patterns)
+        return self._reduce_dose(loss) + self._reduce_patterns(loss_patterns)
 
 
 class L2Loss(Loss):

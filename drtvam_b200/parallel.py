@@ -70,3 +70,37 @@ def make_sum(group=None, world_size: int = 1):
         return v
 
     return allsum
+
+
+def zslab_shard(scene, rank: int, world_size: int, integrator, sensor):
+    """z-slab / DMD-row partition of a planar scene ("alternative worth
+    measuring"): rank r owns the film layers [z0, z1) and, for every projection angle, the DMD rows whose
+    rays deposit there.  Returns {"window": (z0, z1), "index": positions of the owned entries in the
+    full active vector} or None when the scene does not allow it (not planar, rows that straddle
+    layers, sparse pixel lists, CPU tensors)."""
+    p = scene.projector
+    if p.active_pixels.device.type != 'cuda' or sensor.film().surface_aware:
+        return None
+    from . import _lib
+    import ctypes as C
+    lib = _lib.load()
+    n, h, w = p.size()
+    if p.active_pixels.numel() != n * h * w:
+        return None                                  # filtered / cropped pixel lists: shard by angle
+    if any(not scene._same_grid(s_, sensor) for s_ in scene.sensors()):
+        return None                                  # e.g. a final_sensor with another grid: shard by angle
+    handle = scene.handle(integrator, sensor)
+    rz = int(sensor.resolution()[2])
+    # balance by layer count (every layer of a planar scene costs the same)
+    z0 = rz * rank // world_size
+    z1 = rz * (rank + 1) // world_size
+    if z1 <= z0:
+        return None
+    r0, r1 = C.c_int32(0), C.c_int32(0)
+    if lib.drtvam_scene_set_z_window(handle, z0, z1, C.byref(r0), C.byref(r1)) != 0:
+        return None
+    rows = torch.arange(r0.value, r1.value, device=p.active_pixels.device, dtype=torch.int64)
+    cols = torch.arange(w, device=rows.device, dtype=torch.int64)
+    k = torch.arange(n, device=rows.device, dtype=torch.int64)
+    index = (k[:, None, None] * (h * w) + rows[None, :, None] * w + cols[None, None, :]).reshape(-1)
+    return {"window": (z0, z1), "index": index, "rows": (r0.value, r1.value)}

@@ -55,6 +55,10 @@ class Scene:
         self.default_integrator = integrator
         self._handles = {}
         self._keepalive = {}
+        self._handle_sensor = {}
+        self._pinned = {}
+        self._sampler_index = None
+        self._z_sensor = None
         self.group = None      # torch.distributed process group when angle-sharded
         self.world_size = 1
         self.rank = 0
@@ -144,9 +148,45 @@ class Scene:
             h, keep = create_handle(desc, dev.index or 0, desc.target_triangles)
             self._handles[key] = h
             self._keepalive[key] = keep
+            self._handle_sensor[h] = sensor
+            self._apply_shard(h, sensor)
         _lib.check(lib.drtvam_scene_set_depth(h, int(integrator.max_depth), int(integrator.rr_depth)))
         _lib.check(lib.drtvam_scene_force_general(h, int(self.force_general)))
         return h
+
+    def _apply_shard(self, h, sensor):
+        """Shard state of a handle: the z window (z-slab partition; only sensors with the geometry of the one
+        the partition was made for) and the positions of the local entries in the unsharded list, which seed
+        the PCG32 streams so that a shard draws the samples of the unsharded run."""
+        lib = _lib.load()
+        if self.partition == "zslab":
+            if not self._same_grid(sensor, self._z_sensor):
+                raise NotImplementedError("a z-slab sharded scene can only render into sensors with the grid of the "
+                                          "sensor it was sharded for; shard by angle (partition='angle') instead")
+            r0, r1 = C.c_int32(0), C.c_int32(0)
+            _lib.check(lib.drtvam_scene_set_z_window(h, self.z_window[0], self.z_window[1], C.byref(r0), C.byref(r1)))
+        if self._sampler_index is not None:
+            _lib.check(lib.drtvam_scene_set_sampler_index(h, self._sampler_index.data_ptr()))
+
+    @staticmethod
+    def _same_grid(a, b):
+        return a is b or (tuple(a.resolution()) == tuple(b.resolution()) and np.array_equal(a.bbox_min, b.bbox_min)
+                          and np.array_equal(a.bbox_max, b.bbox_max)
+                          and a.film().surface_aware == b.film().surface_aware)
+
+    def film_shape(self, sensor):
+        """Shape of the dose buffers of this rank: the film, or its z window when z-slab sharded."""
+        shape = tuple(sensor.film().shape)
+        if self.partition == "zslab":
+            return (self.z_window[1] - self.z_window[0],) + shape[1:]
+        return shape
+
+    def pin_pixels(self, h, pixels):
+        """Tells the library that `pixels` (projector.active_pixels, only ever REPLACED by params.update(),
+        optimize.py:157-159) stays as it is, so the planar layout check runs once instead of per call."""
+        if self._pinned.get(h) is not pixels:
+            _lib.check(_lib.load().drtvam_scene_pin_pixels(h, pixels.data_ptr(), pixels.numel()))
+            self._pinned[h] = pixels
 
     def filter_handle(self, integrator, sensor):
         """One-off C handle for the pixel pre-filters (optimize.py:143-185): they run before the target
@@ -175,6 +215,8 @@ class Scene:
                 lib.drtvam_scene_destroy(h)
         self._handles.clear()
         self._keepalive.clear()
+        self._handle_sensor.clear()
+        self._pinned.clear()
 
     def __del__(self):
         try:
@@ -183,21 +225,86 @@ class Scene:
             pass
 
     # -- multi-GPU ---------------------------------------------------------
-    def shard(self, rank: int, world_size: int, group=None):
-        """Keep only this rank's projection angles (contiguous range balanced
-        by active-pixel count)."""
-        from .parallel import shard_bounds
+    def shard(self, rank: int, world_size: int, group=None, partition: str = "angle", integrator=None, sensor=None):
+        """Keep only this rank's part of the projection.
+
+        partition "angle": a contiguous range of projection angles balanced by active-pixel count; every
+        forward is followed by one all_reduce(SUM) of the dose.  "zslab": for planar scenes (every ray
+        stays in its voxel layer, sensor.py:345) a slab of film layers and the DMD rows that map to it,
+        for ALL angles -- no dose collective, the loss is a sharded sum.  "auto" takes "zslab" where the
+        scene allows it.  Returns (lo, hi, partition) with [lo, hi) the owned index range for "angle"."""
+        from .parallel import shard_bounds, zslab_shard
         p = self.projector
+        self.rank, self.world_size, self.group = rank, world_size, group
+        n_full = p.active_pixels.numel()
+        if partition in ("auto", "zslab") and world_size > 1:
+            z = zslab_shard(self, rank, world_size, integrator, sensor) if integrator is not None else None
+            if z is not None:
+                self.partition = "zslab"
+                self._z_sensor = sensor
+                self.z_window, self.shard_index = z["window"], z["index"]
+                p.active_pixels = p.active_pixels[z["index"]].contiguous()
+                p.active_data = p.active_data[z["index"]].contiguous()
+                self._shard_handles()
+                return 0, n_full, "zslab"
+            if partition == "zslab":
+                raise ValueError("z-slab sharding needs a planar scene whose DMD rows map to whole voxel layers")
         lo, hi = shard_bounds(p.active_pixels, p.n_patterns, p.res[0] * p.res[1], rank, world_size)
+        self.partition = "angle"
+        self.shard_index = torch.arange(lo, hi, device=p.active_pixels.device)
         p.active_pixels = p.active_pixels[lo:hi].contiguous()
         p.active_data = p.active_data[lo:hi].contiguous()
-        self.rank, self.world_size, self.group = rank, world_size, group
-        return lo, hi
+        self._shard_handles()
+        return lo, hi, "angle"
+
+    def _shard_handles(self):
+        if self.shard_index.device.type == 'cuda':
+            self._sampler_index = self.shard_index.to(torch.int64).to(torch.int32).contiguous()
+        self._pinned.clear()
+        for h in self._handles.values():
+            self._apply_shard(h, self._handle_sensor[h])
+
+    partition = "single"
+    z_window = None
+    shard_index = None
 
     def reduce_dose(self, dose: torch.Tensor):
-        if self.world_size > 1:
+        """all_reduce(SUM) of the partial doses of an angle-sharded forward; a z-slab shard owns its
+        layers outright."""
+        if self.world_size > 1 and self.partition != "zslab":
             import torch.distributed as dist
             dist.all_reduce(dose, op=dist.ReduceOp.SUM, group=self.group)
+
+    def local_target(self, target: torch.Tensor) -> torch.Tensor:
+        """The part of a film-shaped tensor (loss target, dose gradient) this rank's film holds."""
+        if self.partition != "zslab":
+            return target
+        z0, z1 = self.z_window
+        return target[z0:z1].contiguous()
+
+    local_dose_grad = local_target
+
+    def gather_dose(self, dose: torch.Tensor) -> torch.Tensor:
+        """The full dose volume on every rank (checks, final outputs): identity unless z-slab sharded."""
+        if self.partition != "zslab" or self.world_size == 1:
+            return dose
+        import torch.distributed as dist
+        z0, z1 = self.z_window
+        bounds = [None] * self.world_size
+        dist.all_gather_object(bounds, (z0, z1), group=self.group)
+        nz = max(b[1] - b[0] for b in bounds)
+        pad = torch.zeros((nz,) + tuple(dose.shape[1:]), device=dose.device, dtype=dose.dtype)
+        pad[:z1 - z0] = dose
+        parts = [torch.empty_like(pad) for _ in range(self.world_size)]
+        dist.all_gather(parts, pad, group=self.group)
+        return torch.cat([parts[r][:bounds[r][1] - bounds[r][0]] for r in range(self.world_size)], 0)
+
+    def dose_allsum(self):
+        """Sum over ranks of a scalar reduced over the local film (z-slab sharding), else None."""
+        if self.partition != "zslab" or self.world_size == 1:
+            return None
+        from .parallel import make_sum
+        return make_sum(self.group, self.world_size)
 
 
 class Params(dict):
@@ -224,7 +331,8 @@ class Params(dict):
         if not isinstance(pixels, torch.Tensor):
             pixels = torch.as_tensor(np.asarray(pixels, np.int64))
         dev = p.active_data.device
-        p.active_data = data.to(dev, torch.float32).reshape(-1)
+        data = data.to(dev, torch.float32)      # no-op (same object, .grad kept) when already there
+        p.active_data = data if data.dim() == 1 else data.reshape(-1)
         if pixels.dtype != torch.int32:
             pixels = pixels.to(torch.int64).to(torch.int32)
         p.active_pixels = pixels.to(dev).reshape(-1).contiguous()

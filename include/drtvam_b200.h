@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define DRTVAM_ABI_VERSION 7
+#define DRTVAM_ABI_VERSION 8
 #define DRTVAM_MAX_SURFACES 8
 #define DRTVAM_MAX_MESH_SURFACES 4
 
@@ -41,6 +41,7 @@ extern "C" {
 #define DRTVAM_E_INVALID -1      /* bad argument / unsupported configuration */
 #define DRTVAM_E_CUDA -2         /* CUDA runtime error */
 #define DRTVAM_E_TOO_MANY_RAYS -3 /* wavefront > 2^32, common.py:60-65 */
+#define DRTVAM_E_NCCL -4         /* NCCL error, incl. asynchronous ones (ncclCommGetAsyncError) */
 
 /* surface kinds / bsdf kinds */
 #define DRTVAM_SURF_CYLINDER 0   /* open tube about the z axis: geometry.py:85-89,157-160 */
@@ -157,10 +158,56 @@ int drtvam_discretize(DrtvamScene *scene, float *voxels, void *stream);
  * scalar out_scale / in_scale only. */
 int drtvam_scene_set_inv_volume(DrtvamScene *scene, const float *inv_volume);
 
+/* ---- multi-GPU (SURVEY.md section 8(b),(e)) -------------------------------------------------------
+ * The path shards in two ways.  By projection angle (A = sum_k A_k; each ray belongs to one pattern,
+ * integrators/common.py:83): every rank passes the slice of active_pixels / active_data of its angles
+ * and the full-size partial doses are summed with drtvam_allreduce_dose.  Or, for planar scenes
+ * (every ray keeps d_z = 0 and never leaves its voxel layer, sensor.py:345), by z-slab: */
+
+/* z-slab shard: this handle projects the film layers [z_begin, z_end) only.  From now on the dose /
+ * dose_grad buffers of drtvam_forward / drtvam_adjoint hold those layers only, i.e.
+ * (z_end - z_begin) * res_y * res_x floats, and the caller lists in active_pixels, for every pattern,
+ * every column of the DMD rows [*row_begin, *row_end) - the rows whose rays deposit in the window.  No
+ * dose collective is needed: every rank owns its layers outright; the loss is a sum over ranks
+ * (drtvam_allreduce_scalars) and pattern vectors are sharded by row.  DRTVAM_E_INVALID when the scene is
+ * not planar, the rows of the window are not contiguous, or (jittered sampling) a row straddles two
+ * layers: shard by angle then.  z_begin = 0, z_end = res_z restores the whole film. */
+int drtvam_scene_set_z_window(DrtvamScene *scene, int32_t z_begin, int32_t z_end, int32_t *row_begin,
+                              int32_t *row_end);
+
+/* Position of every entry of a shard's active list in the unsharded list (DEVICE array, caller-owned,
+ * n_active entries; NULL = identity).  sampler.seed(seed, wavefront_size) gives lane i of the wavefront
+ * the i-th PCG32 stream (integrators/common.py:67); with the index a shard draws exactly the samples the
+ * unsharded run draws for the same pixels, so N-rank results equal 1-rank results for jittered and
+ * scattering runs too. */
+int drtvam_scene_set_sampler_index(DrtvamScene *scene, const uint32_t *global_index);
+
+/* A promise that the n_active entries at active_pixels do not change until the next pin (NULL unpins):
+ * the planar kernels index the list implicitly and check its layout on the device in every call
+ * (0.3 ms at 6.4e7 pixels); for a pinned list the check runs once (synchronising the stream of the
+ * first call) and later calls skip it and the stand-by launch of the other kernel family.  The host
+ * mirror pins projector.active_pixels, which only params.update() replaces (optimize.py:157-159). */
+int drtvam_scene_pin_pixels(DrtvamScene *scene, const uint32_t *active_pixels, uint64_t n_active);
+
+/* NCCL plumbing for bindings without torch.distributed (the Python mirror uses torch.distributed and
+ * never calls these).  libnccl is resolved at run time (the copy already loaded in the process wins), so
+ * the library has no link-time dependency on it.  drtvam_comm_unique_id fills 128 bytes (ncclUniqueId) on
+ * rank 0; the caller hands them to every rank by its own means; drtvam_comm_init joins the communicator
+ * (one per handle, on the handle's device).  Both collectives reduce in place with ncclSum on `stream`
+ * and query ncclCommGetAsyncError before and after enqueueing, so a dead peer surfaces as
+ * DRTVAM_E_NCCL instead of a hang at the next synchronisation. */
+int drtvam_comm_unique_id(void *id_out_128_bytes);
+int drtvam_comm_init(DrtvamScene *scene, const void *unique_id_128_bytes, int32_t rank, int32_t world);
+int drtvam_comm_destroy(DrtvamScene *scene);
+/* sum of the per-rank partial doses of an angle-sharded forward (n floats, DEVICE) */
+int drtvam_allreduce_dose(DrtvamScene *scene, float *dose, uint64_t n, void *stream);
+/* sum of n doubles (DEVICE): the loss of a z-slab shard, batched L-BFGS dot products (lbfgs.py:191-231) */
+int drtvam_allreduce_scalars(DrtvamScene *scene, double *values, uint64_t n, void *stream);
+
 /* Which kernel family a call will use for this scene and spp:
  * 0 = general per-lane tracer, 1 = planar per-ray tile DDA,
  * 2 = planar layer-parallel kernels (deterministic fast path),
- * 3 = planar per-lane table kernels (jittered sampling). */
+ * 3 = planar layer-lane kernels with a per-lane segment table (jittered sampling). */
 int drtvam_scene_plan(DrtvamScene *scene, uint64_t n_active, uint32_t spp);
 /* 0 = let the library choose, 1 = force the general tracer, 2 = force the
  * planar per-ray tile DDA where the scene is planar (A/B tests). */

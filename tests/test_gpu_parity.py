@@ -12,7 +12,7 @@ import torch
 
 import oracle as orc
 from drtvam_b200 import _lib
-from helpers import build, pixels_np, random_inputs, rel_l2, rel_l2_trimmed
+from helpers import assert_jitter_parity, build, pixels_np, random_inputs, rel_l2
 
 pytestmark = pytest.mark.gpu
 
@@ -396,14 +396,18 @@ def test_jittered_planar_matches_general_and_oracle(name, workdir):
         f_fast, f_slow = fast.forward(p, pix, spp, seed), slow.forward(p, pix, spp, seed)
         a_fast, a_slow = fast.adjoint(g, pix, spp, seed), slow.adjoint(g, pix, spp, seed)
         f_ref, a_ref = o32.forward(p, pix, spp, seed), o32.adjoint(g, pix, spp, seed)
-        # knife-edge rays may flip between compilations (helpers.rel_l2_trimmed); everything else: 1e-4
-        assert rel_l2_trimmed(f_fast, f_slow) < TOL and rel_l2_trimmed(a_fast, a_slow) < TOL
+        # knife-edge rays may flip between compilations (helpers.flip_report): their COUNT is asserted,
+        # everything else is held to 1e-4 and the plain norm to the jitter band of
+        # test_jittered_sampling_matches_oracle.  One flipped ray flags one gradient entry, or at most
+        # the voxels of its two chords (< 3 n) in the dose.
+        n = 144
+        assert_jitter_parity(f_fast, f_slow, 4 * spp, 3 * n, TOL, what=f"{name} spp {spp} dose fast/general")
+        assert_jitter_parity(a_fast, a_slow, 4 * spp, 1, TOL, what=f"{name} spp {spp} grad fast/general")
         # gcc (oracle) and nvcc differ in more places (fma contraction in the ray generation), so a few
-        # more rays flip against the oracle: allow 1e-3 of the entries there
-        assert rel_l2_trimmed(f_fast, f_ref, 1e-3) < TOL and rel_l2_trimmed(a_fast, a_ref, 1e-3) < TOL
-        # and the flipped rays stay a handful: the plain norm is inside the jitter band of
-        # test_jittered_sampling_matches_oracle
-        assert rel_l2(f_fast, f_ref) < 3e-2 and rel_l2(a_fast, a_ref) < 3e-2
+        # more rays flip against the oracle: at most 2e-4 of the rays
+        rays = pix.size * spp
+        assert_jitter_parity(f_fast, f_ref, max(8, rays // 5000), 3 * n, TOL, what=f"{name} spp {spp} dose vs f32 oracle")
+        assert_jitter_parity(a_fast, a_ref, max(8, rays // 5000), 1, TOL, what=f"{name} spp {spp} grad vs f32 oracle")
 
 
 def test_jittered_planar_rectangular_grid(workdir):
@@ -414,8 +418,11 @@ def test_jittered_planar_rectangular_grid(workdir):
     h = Handle(d)
     assert _plan(h, pix.size) == 3
     o32 = orc.Oracle(d.as_dict(), "f32")
-    assert rel_l2_trimmed(h.forward(p, pix, 1, 5), o32.forward(p, pix, 1, 5), 1e-3) < TOL
-    assert rel_l2_trimmed(h.adjoint(g, pix, 1, 5), o32.adjoint(g, pix, 1, 5), 1e-3) < TOL
+    rays = pix.size
+    assert_jitter_parity(h.forward(p, pix, 1, 5), o32.forward(p, pix, 1, 5), max(8, rays // 5000), 3 * 54, TOL,
+                         what="C3 rectangular dose")
+    assert_jitter_parity(h.adjoint(g, pix, 1, 5), o32.adjoint(g, pix, 1, 5), max(8, rays // 5000), 1, TOL,
+                         what="C3 rectangular grad")
 
 
 @pytest.mark.parametrize("mode", PLANAR_MODES)

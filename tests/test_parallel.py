@@ -50,7 +50,8 @@ def _worker(rank, world, port, workdir, result):
     scene, integ, sensor, d, _ = build("C3", workdir, 16)
     pix_all = pixels_np(scene)
     p_all = np.random.default_rng(0).random(pix_all.size).astype(np.float32)
-    lo, hi = scene.shard(rank, world)
+    lo, hi, partition = scene.shard(rank, world)
+    assert partition == "angle" and scene.shard_index.tolist() == list(range(lo, hi))
     o = orc.Oracle(d.as_dict(), "f64", threads=1)
     dose = torch.from_numpy(o.forward(p_all[lo:hi], pixels_np(scene)))
     scene.reduce_dose(dose)                           # the one all_reduce of the forward pass

@@ -118,15 +118,17 @@ def test_surface_aware_forward_adjoint_match_oracle(name, workdir):
 
 @pytest.mark.gpu
 def test_surface_aware_jittered_and_scattering(workdir):
-    """Jittered absorptive: same PCG32 streams, 1e-4 after trimming knife-edge rays.
+    """Jittered absorptive: same PCG32 streams; the knife-edge rays (here also: rays that graze a
+    triangle edge of the target) are counted and bounded, everything else is held to 1e-4.
     Scattering: statistical band (fp32 branch flips change single walks)."""
-    from helpers import rel_l2_trimmed
+    from helpers import assert_jitter_parity
     scene, integ, sensor, d, _ = build("C4", workdir, 32, surface_aware=True, regular_sampling=False)
     pix = pixels_np(scene)
     p, g = random_inputs(d, pix.size, 6)
     o = orc.Oracle(d.as_dict(), "f32")
     h = _handle(d)
-    assert rel_l2_trimmed(h.forward(p, pix, 2, 9), o.forward(p, pix, 2, 9), 1e-3) < 1e-4
+    assert_jitter_parity(h.forward(p, pix, 2, 9), o.forward(p, pix, 2, 9), max(8, pix.size * 2 // 2000), 3 * 32, 1e-4,
+                         what="C4 surface-aware jittered dose")
     scene, integ, sensor, d, _ = build("C5", workdir, 24, surface_aware=True, spp=4)
     pix = pixels_np(scene)
     p, g = random_inputs(d, pix.size, 7)

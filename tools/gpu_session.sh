@@ -1,23 +1,68 @@
 #!/bin/bash
-# One gpurun session: GPU parity tests, the default bench, the reference arm, then
-# (only after those exit 0) the ncu launch list and one --set full capture.
-# Usage (from the repo root, under gpurun):  bash tools/gpu_session.sh TAG [WORKLOAD]
-TAG=${1:-s}
-WL=${2:-C2}
-O=gpurun_out
-mkdir -p $O
-nvidia-smi --query-gpu=name,clocks.max.sm,clocks.max.mem,power.limit --format=csv > $O/${TAG}_gpu.txt 2>&1
-nproc >> $O/${TAG}_gpu.txt
-timeout 900 python -m pytest tests -m gpu -x -q > $O/${TAG}_pytest.log 2>&1; echo "pytest exit $?" >> $O/${TAG}_pytest.log
-tail -3 $O/${TAG}_pytest.log
-timeout 600 python bench.py --workload $WL > $O/${TAG}_bench.json 2> $O/${TAG}_bench.err; rc=$?
-echo "bench exit $rc"; tail -c 3000 $O/${TAG}_bench.json
-timeout 400 python bench.py --impl reference --steps 3 --warmup 1 --workload $WL > $O/${TAG}_bench_ref.json 2> $O/${TAG}_bench_ref.err
-tail -c 1500 $O/${TAG}_bench_ref.json
-if [ $rc -eq 0 ]; then
-  timeout 900 ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
-    --log-file $O/${TAG}_launches.csv python bench.py --workload $WL --steps 2 --warmup 3 --no-cpu-baseline > $O/${TAG}_ncu1.log 2>&1
-  timeout 1200 ncu --profile-from-start off --set full --clock-control none --import-source on -k regex:planar[gz]_kernel -c 6 \
-    -o $O/${TAG}_planar python bench.py --workload $WL --steps 1 --warmup 3 --no-cpu-baseline > $O/${TAG}_ncu2.log 2>&1
-  ls -la $O
-fi
+# One parameterised GPU session (run under gpurun from the repo root).  Every step writes under
+# gpurun_out/ with the tag as prefix; copy what should be judged into profiles/.
+#
+#   tools/gpu_session.sh TAG step [step ...]
+#
+# steps:
+#   tests[:EXPR]        pytest -m gpu (optionally -k EXPR)
+#   bench[:WL[:FLAGS]]  bench.py --workload WL (default C2) with extra flags ('+' separates flags)
+#   ref                 bench.py --impl reference
+#   launches[:WL]       ncu launch list of the timed steps (gpu__time_duration)
+#   ncu:REGEX[:WL]      ncu --set full on the kernels matching REGEX, 4 launches
+#   san:TOOL:EXPR       compute-sanitizer --tool TOOL on pytest -k EXPR (ONE sanitizer tool per gpurun call)
+#   scale:N[:WL]        torchrun bench.py at N GPUs, launched as the driver does
+#   smoke               __graft_entry__.smoke()
+#   wall[:WL]           tools/optimize_wall.py
+TAG=${1:?tag}; shift
+O=gpurun_out; mkdir -p $O
+for step in "$@"; do
+    IFS=: read -r kind a b <<< "$step"
+    case $kind in
+    tests)
+        timeout 1500 python -m pytest tests -m gpu -x -q ${a:+-k "$a"} > $O/${TAG}_tests.log 2>&1
+        echo "[$TAG] tests exit $?: $(tail -1 $O/${TAG}_tests.log)";;
+    bench)
+        wl=${a:-C2}; flags=${b//+/ }
+        timeout 1200 python bench.py --workload $wl $flags > $O/${TAG}_bench_${wl}${b:+_${b//[^a-zA-Z0-9]/}}.json \
+            2> $O/${TAG}_bench_${wl}.err
+        echo "[$TAG] bench $wl $flags exit $?"
+        python tools/bench_brief.py $O/${TAG}_bench_${wl}${b:+_${b//[^a-zA-Z0-9]/}}.json;;
+    ref)
+        timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > $O/${TAG}_bench_reference.json 2> $O/${TAG}_ref.err
+        echo "[$TAG] reference arm exit $?";;
+    launches)
+        wl=${a:-C2}
+        timeout 900 ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
+            --log-file $O/${TAG}_launches_${wl}_raw.csv python bench.py --workload $wl --steps 2 --warmup 3 --no-cpu-baseline \
+            > $O/${TAG}_launches_${wl}.log 2>&1
+        echo "[$TAG] launch list exit $?"
+        python tools/ncu_summary.py launches $O/${TAG}_launches_${wl}_raw.csv > $O/${TAG}_launches_${wl}.csv 2>&1
+        tail -12 $O/${TAG}_launches_${wl}.csv;;
+    ncu)
+        wl=${b:-C2}
+        timeout 900 ncu --profile-from-start off --set full --clock-control none --import-source on -k regex:"$a" -c 4 \
+            -o $O/${TAG}_${wl}_full python bench.py --workload $wl --steps 1 --warmup 3 --no-cpu-baseline \
+            > $O/${TAG}_ncu_${wl}.log 2>&1
+        echo "[$TAG] ncu --set full exit $?"
+        python tools/ncu_summary.py details $O/${TAG}_${wl}_full.ncu-rep > $O/${TAG}_${wl}_ncu_details.txt 2>&1
+        grep -E "^==|gpu__time_duration|dram__bytes|issue_active" $O/${TAG}_${wl}_ncu_details.txt | head -40;;
+    san)
+        timeout 1500 compute-sanitizer --tool $a --error-exitcode 9 python -m pytest tests -m gpu -x -q -k "$b" \
+            > $O/${TAG}_sanitizer_${a}.log 2>&1
+        echo "[$TAG] compute-sanitizer $a exit $?: $(grep -E 'ERROR SUMMARY|passed|failed' $O/${TAG}_sanitizer_${a}.log | tail -2 | tr '\n' ' ')";;
+    scale)
+        wl=${b:-C2}
+        timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $a --master-addr 127.0.0.1 --master-port 29511 \
+            bench.py --gpus $a --workload $wl --steps 10 --warmup 3 > $O/${TAG}_bench_${wl}_${a}gpu.json 2> $O/${TAG}_bench_${wl}_${a}gpu.err
+        echo "[$TAG] scale $a exit $?"
+        python tools/bench_brief.py $O/${TAG}_bench_${wl}_${a}gpu.json;;
+    smoke)
+        timeout 600 python -c "import __graft_entry__ as g; g.smoke()" > $O/${TAG}_smoke.log 2>&1
+        echo "[$TAG] smoke exit $?: $(tail -1 $O/${TAG}_smoke.log)";;
+    wall)
+        timeout 900 python tools/optimize_wall.py ${a:-C2} > $O/${TAG}_optimize_wall_${a:-C2}.jsonl 2> $O/${TAG}_wall.err
+        echo "[$TAG] optimize wall exit $?: $(tail -1 $O/${TAG}_optimize_wall_${a:-C2}.jsonl | cut -c1-300)";;
+    *) echo "unknown step $step";;
+    esac
+done
