@@ -11,7 +11,7 @@ import os
 from . import build as _build
 
 MAX_SURFACES = 8
-ABI_VERSION = 8
+ABI_VERSION = 9
 
 
 class DrtvamSurface(C.Structure):
@@ -44,6 +44,7 @@ class DrtvamSceneDesc(C.Structure):
         ("res", C.c_int32 * 3),
         ("surface_aware", C.c_int32), ("sensor_kind", C.c_int32),
         ("majorant", C.c_float),
+        ("motion_table_host_f64", C.POINTER(C.c_double)),
     ]
 
 

@@ -138,8 +138,10 @@ class SceneDesc:
         keep = None
         if self.motion_table is not None:
             tab = np.ascontiguousarray(np.asarray(self.motion_table, np.float64)[:, :3, :].astype(np.float32))
-            keep = tab
+            tab64 = np.ascontiguousarray(np.asarray(self.motion_table, np.float64)[:, :3, :])
+            keep = (tab, tab64)
             d.motion_table_host = tab.ctypes.data_as(C.POINTER(C.c_float))
+            d.motion_table_host_f64 = tab64.ctypes.data_as(C.POINTER(C.c_double))
         closed = [s for s in self.surfaces if s.kind != SURF_MESH]
         d.n_surf = len(closed)
         for i, s in enumerate(closed):

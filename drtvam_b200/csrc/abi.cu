@@ -64,6 +64,7 @@ struct DrtvamScene {
     InsideHost inside;               // inside-target segment records of a surface-aware planar scene
     float print_time = 1.f;
     float* motion_dev = nullptr;
+    double* motion_f64_dev = nullptr;
     int force_mode = 0;              // 0 auto, 1 general tracer, 2 planar v1 (per-ray tile DDA)
     std::vector<float> motion_host;  // copy of the motion table for the plan check
     PlanarHost planar;
@@ -356,6 +357,7 @@ int drtvam_scene_create(const DrtvamSceneDesc* d, int device, DrtvamScene** out)
     P.z_begin = 0; P.z_end = d->res[2]; P.row_begin = 0; P.n_rows = d->res_y;
     P.sampler_index = nullptr;
     P.motion_table = nullptr;
+    P.motion_table_f64 = nullptr;
     if (d->motion_table_host) {
         const size_t bytes = sizeof(float) * 12 * static_cast<size_t>(d->n_patterns);
         cudaError_t e = cudaMalloc(&s->motion_dev, bytes);
@@ -366,6 +368,17 @@ int drtvam_scene_create(const DrtvamSceneDesc* d, int device, DrtvamScene** out)
         }
         P.motion_table = s->motion_dev;
         s->motion_host.assign(d->motion_table_host, d->motion_table_host + 12 * static_cast<size_t>(d->n_patterns));
+        // double-precision copy for the set-up of the planar tables (given, or the fp32 one promoted)
+        std::vector<double> m64(12 * static_cast<size_t>(d->n_patterns));
+        for (size_t i = 0; i < m64.size(); ++i)
+            m64[i] = d->motion_table_host_f64 ? d->motion_table_host_f64[i] : static_cast<double>(d->motion_table_host[i]);
+        e = cudaMalloc(&s->motion_f64_dev, sizeof(double) * m64.size());
+        if (e == cudaSuccess) e = cudaMemcpy(s->motion_f64_dev, m64.data(), sizeof(double) * m64.size(), cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) {
+            drtvam_scene_destroy(s);
+            return fail(DRTVAM_E_CUDA, "motion table upload failed: %s", cudaGetErrorString(e));
+        }
+        P.motion_table_f64 = s->motion_f64_dev;
     }
     cudaError_t e = cudaMalloc(&s->counter_dev, sizeof(unsigned long long));
     if (e != cudaSuccess) {
@@ -381,6 +394,7 @@ void drtvam_scene_destroy(DrtvamScene* s) {
     drtvam_comm_destroy(s);
     DeviceGuard guard(s->device);
     if (s->motion_dev) cudaFree(s->motion_dev);
+    if (s->motion_f64_dev) cudaFree(s->motion_f64_dev);
     if (s->counter_dev) cudaFree(s->counter_dev);
     planar_release(s->planar);
     planarz_release(s->zplan);
@@ -506,6 +520,7 @@ int drtvam_scene_pin_pixels(DrtvamScene* s, const uint32_t* active_pixels, uint6
     s->pinned_pixels = active_pixels;
     s->pinned_n = active_pixels ? n_active : 0;
     s->pinned_gate = -1;
+    s->jplan.cache_valid = false;   // a segment table kept for the previous list is void
     return DRTVAM_OK;
 }
 
@@ -669,8 +684,10 @@ int drtvam_forward(DrtvamScene* s, const float* active_data, const uint32_t* act
             float* plane = sa ? s->inside.planes : dose;
             if (sa) CUDA_TRY(inside_forward_begin(s->inside, st));
             if (!P1.regular_sampling)
+                // a pinned list stays as it is, so the segment table of this pass can serve the next forward
+                // pass with the same seed (A d after A p, lbfgs.py:248)
                 CUDA_TRY(launch_planarj_forward(P1, windowed(P1), s->zplan, s->jplan, gate, active_data, active_pixels,
-                                                n_active, spp, seed, w, plane, zero_first != 0, st));
+                                                n_active, spp, seed, w, plane, host_gate == 0, st));
             else if (s->zplan.valid && s->gplan.valid && s->force_mode != 2)
                 // fresh: the plane was cleared above (zero_first, or the planes of a surface-aware scene) and
                 // the patch gather is its first writer, so it stores instead of read-add-write

@@ -5,6 +5,7 @@
 // sensor.py:419 the Sink of the adjoint.
 #pragma once
 #include "device_scene.cuh"
+#include "expm.cuh"
 #include "rng.cuh"
 
 namespace drtvam {
@@ -77,6 +78,7 @@ struct DdaWalk {
     float fx, fy, fz, lx, ly, lz;      // steps taken / allowed
     float bx, by, bz, dx, dy, dz;      // first boundary and boundary spacing
     float u_end, e_prev, w0;
+    float u_prev;                      // kAccurate steps: optical depth at the entry of the current voxel
 
     // `w0_` is the throughput at the segment origin times sigma_a / sigma_t.  False: no overlap.
     // kSub: the walk covers [t_lo, maxt] of the segment only - the tail of a walk that something else
@@ -135,17 +137,28 @@ struct DdaWalk {
         lx = lim[0]; ly = lim[1]; lz = lim[2];
         fx = fy = fz = 0.f;
         e_prev = ex2_approx_dda(-u_start);
+        u_prev = u_start;
         w0 = w0_;
         return true;
     }
 
     // Deposits the current voxel and moves to the next one.  False: that was the last voxel.
-    template <class Sink>
+    // kAccurate: the deposit is 2^-u_in (1 - 2^-(u_out - u_in)) with the small factor evaluated directly
+    // (expm.cuh) instead of the difference of two ex2.approx of absolute depths - 5 more instructions per
+    // visit, for walks whose results are SUBTRACTED from others (the negative records of
+    // inside_kernels.cu), where the 1e-4 noise of the difference form does not average out.
+    template <bool kAccurate = false, class Sink>
     __device__ __forceinline__ bool step(Sink& sink) {
         const float un = fminf(fminf(ux, uy), uz);
         const bool more = un < u_end;  // false also when every axis has used up its steps (all inf)
-        const float e = ex2_approx_dda(-(more ? un : u_end));
-        sink.visit(static_cast<size_t>(static_cast<unsigned>(idx)), w0 * (e_prev - e));
+        const float u_out = more ? un : u_end;
+        const float e = ex2_approx_dda(-u_out);
+        if (kAccurate) {
+            sink.visit(static_cast<size_t>(static_cast<unsigned>(idx)), w0 * (e_prev * one_minus_ex2_neg(fmaxf(u_out - u_prev, 0.f))));
+            u_prev = u_out;
+        } else {
+            sink.visit(static_cast<size_t>(static_cast<unsigned>(idx)), w0 * (e_prev - e));
+        }
         e_prev = e;
         // branch-free choice of the axis that was crossed (lanes of a warp cross different axes)
         const bool px = ux == un;

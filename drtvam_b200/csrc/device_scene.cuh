@@ -30,6 +30,7 @@ struct SceneParams {
     int motion_analytic, clockwise;
     float distance;
     const float* motion_table;  // device, [n_patterns][12] row-major 3x4
+    const double* motion_table_f64;  // the same in double precision (set-up of the planar tables), or NULL
     // integrator
     int max_depth, rr_depth, transmission_only, regular_sampling, sample_time;
     // medium

@@ -141,11 +141,13 @@ inside_pass_kernel(const __grid_constant__ SceneParams P, const uint32_t* __rest
                                      : W.begin<false>(P, r, fabsf(a.w), b.w, false);
         if (!any) continue;
         if (kMode == 0) {
+            // accurate deposits: the negative record must cancel the planar kernels' deposits, whose
+            // coefficients are accurate too (planarz_kernels.cu::walk_entry), to well below 1e-4
             ScatterSink sink{out + plane, em};
-            while (W.step(sink)) {}
+            while (W.step<true>(sink)) {}
         } else {
             GatherSink sink{in + plane};
-            while (W.step(sink)) {}
+            while (W.step<true>(sink)) {}
             acc += sink.acc;
         }
     }

@@ -31,6 +31,7 @@ struct PlanarHost {
     int n_rows_in_sensor = 0;  // DMD rows whose z lies inside the sensor box
     float4* seg_a = nullptr;
     float2* seg_b = nullptr;
+    SegmentD* seg_d = nullptr;   // double-precision copy for the set-up kernels (planar_f64.cuh)
     int* layer_row_begin = nullptr;
     int* layer_rows = nullptr;
     int* tile_off = nullptr;
@@ -109,18 +110,27 @@ struct PlanarJHost {
     int tiles_x = 0, tiles_y = 0, tile_w = 0, tile_h = 0;
     int* tile_off = nullptr;       // [n_tiles][n_patterns + 1] prefix of the (conservative) column counts
     int* tile_clo = nullptr;       // [n_tiles][n_patterns]
-    void* table = nullptr;         // per-lane segment table of the current angle chunk
+    void* table = nullptr;         // per-lane segment table of the current angle chunk (forward passes)
     size_t table_bytes = 0;
+    void* table_adj = nullptr;     // the same for adjoint passes
+    size_t table_adj_bytes = 0;
     float* gT = nullptr;           // adjoint: per-lane gradients in table order
     size_t gT_bytes = 0;
     size_t smem_bytes = 0;
+    // the table still holds the geometry of the last forward pass (same pixels, seed, spp, weight)
+    bool cache_valid = false;
+    uint32_t cache_seed = 0, cache_spp = 0;
+    const uint32_t* cache_pixels = nullptr;
+    uint64_t cache_n = 0;
+    float cache_weight = 0.f;
+    const uint32_t* cache_index = nullptr;
 };
 cudaError_t planarj_build(const SceneParams& P, const PlanarHost& base, const PlanarZHost& Zh, PlanarJHost& J);
 void planarj_release(PlanarJHost& J);
 cudaError_t launch_planarj_forward(const SceneParams& P, const SceneParams& Pw, PlanarZHost& Zh, PlanarJHost& J,
                                    const int* gate, const float* active_data, const uint32_t* active_pixels,
                                    uint64_t n_active, uint32_t spp, uint32_t seed, float ray_weight, float* film,
-                                   bool fresh, cudaStream_t stream);
+                                   bool cacheable, cudaStream_t stream);
 cudaError_t launch_planarj_adjoint(const SceneParams& P, const SceneParams& Pw, PlanarZHost& Zh, PlanarJHost& J,
                                    const int* gate, const float* dL, const uint32_t* active_pixels, uint64_t n_active,
                                    uint32_t spp, uint32_t seed, float ray_weight, float* grad, cudaStream_t stream);

@@ -12,6 +12,7 @@
 #include <cuda_runtime.h>
 
 #include "device_scene.cuh"
+#include "planar_f64.cuh"
 
 namespace drtvam {
 
@@ -40,6 +41,7 @@ constexpr int kPlanarFlagNotPlanar = 2;     // a segment had d_z != 0
 struct PlanarZPlan {
     const float4* seg_a;     // shared with PlanarPlan
     const float2* seg_b;
+    const SegmentD* seg_d;   // the same segments in double precision (set-up kernels only)
     const int* tile_off;     // [n_tiles][n_patterns + 1] prefix of per-angle column counts
     const int* tile_clo;     // [n_tiles][n_patterns]
     const int* tile_ebase;   // [n_tiles + 1] first walk entry of every tile

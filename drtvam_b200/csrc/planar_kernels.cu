@@ -29,8 +29,8 @@ constexpr float kLog2e = 1.4426950408889634f;
 // through the general interface loop so both plans share the same arithmetic.
 __global__ void __launch_bounds__(kPlanarThreads)
 planar_segments_kernel(const __grid_constant__ SceneParams P, int row_ref, float4* __restrict__ seg_a,
-                       float2* __restrict__ seg_b, int* __restrict__ flags, int* __restrict__ frozen_list,
-                       int* __restrict__ frozen_count) {
+                       float2* __restrict__ seg_b, SegmentD* __restrict__ seg_d, int* __restrict__ flags,
+                       int* __restrict__ frozen_list, int* __restrict__ frozen_count) {
     const int i = blockIdx.x * kPlanarThreads + threadIdx.x;
     const int n = P.n_patterns * P.res_x;
     if (i >= n) return;
@@ -55,6 +55,17 @@ planar_segments_kernel(const __grid_constant__ SceneParams P, int row_ref, float
     }
     seg_a[i] = make_float4(sink.seg.ox, sink.seg.oy, sink.seg.dx, sink.seg.dy);
     seg_b[i] = ok ? make_float2(sink.tmax, sink.w0) : make_float2(0.f, 0.f);
+    // the same segment in double precision for the set-up of the walk tables (planar_f64.cuh); the fp32
+    // tracer above decides, this one refines, and a walk that disagrees is not trusted
+    SegmentD D{sink.seg.ox, sink.seg.oy, sink.seg.dx, sink.seg.dy, ok ? sink.tmax : 0.f, ok ? sink.w0 : 0.f};
+    if (ok && P.motion_table_f64 && P.proj_kind == 0 && !P.sample_time) {
+        SegmentD R;
+        if (f64::trace_segment(P, P.motion_table_f64, k, row_ref, c, R) &&
+            fabs(R.tmax - D.tmax) < 1e-3 * (1.0 + D.tmax) && fabs(R.ox - D.ox) < 1e-3 && fabs(R.oy - D.oy) < 1e-3 &&
+            fabs(R.w0 - D.w0) < 1e-3 * fabs(D.w0))
+            D = R;
+    }
+    seg_d[i] = D;
 }
 
 // Layer each DMD row deposits in (the z part of sensor.py:328-346), -1 = none.
@@ -186,11 +197,10 @@ __device__ __forceinline__ float march_tile(const SceneParams& P, float* __restr
         const bool pos = a.z > 0.f;
         sx = pos ? 4 : -4;  // byte strides
         nx = max(pos ? jx - ix : ix - jx, 0);
-        // boundary times relative to the tile entry: u = u(t0) + (boundary - g) * sig / d keeps the
-        // cancellation in (boundary - g), a difference of nearby positions; later boundaries are
+        // boundary times relative to the tile entry, u = (boundary - g) * sig / d; later boundaries are
         // fx whole voxels further (fx counts the steps taken)
         ax = fabsf(vsx * inv);
-        bx = fmaf(fmaf(static_cast<float>(x0 + ix + (pos ? 1 : 0)), vsx, P.bmin[0]) - gx, inv, sig * t0);
+        bx = (fmaf(static_cast<float>(x0 + ix + (pos ? 1 : 0)), vsx, P.bmin[0]) - gx) * inv;
         fx = 0.f;
         if (nx > 0) ux = bx;
     }
@@ -200,13 +210,16 @@ __device__ __forceinline__ float march_tile(const SceneParams& P, float* __restr
         sy = pos ? 4 * pitch : -4 * pitch;
         ny = max(pos ? jy - iy : iy - jy, 0);
         ay = fabsf(vsy * inv);
-        by = fmaf(fmaf(static_cast<float>(y0 + iy + (pos ? 1 : 0)), vsy, P.bmin[1]) - gy, inv, sig * t0);
+        by = (fmaf(static_cast<float>(y0 + iy + (pos ? 1 : 0)), vsy, P.bmin[1]) - gy) * inv;
         fy = 0.f;
         if (ny > 0) uy = by;
     }
     // one-voxel halo around the tile; shared-window byte address
     uint32_t addr = static_cast<uint32_t>(__cvta_generic_to_shared(tile)) + 4u * ((iy + 1) * pitch + ix + 1);
-    float e_prev = ex2_approx(-sig * t0);
+    // optical depths relative to the tile entry; the throughput at the entry scales the result
+    const float e_in = ex2_approx(-sig * t0);
+    em *= e_in;
+    float e_prev = 1.f;
     float acc = 0.f;
     auto deposit = [&](float de) {
         if (kMode == kGather) {
@@ -232,8 +245,8 @@ __device__ __forceinline__ float march_tile(const SceneParams& P, float* __restr
             addr += sy;
         }
     }
-    deposit(e_prev - ex2_approx(-sig * t1));
-    return acc;
+    deposit(e_prev - ex2_approx(-sig * (t1 - t0)));
+    return acc * e_in;
 }
 
 // kScatter: in = active_data [n_active], out = film (accumulated with red.global)
@@ -337,7 +350,7 @@ planar_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pla
     } while (0)
 
 void planar_release(PlanarHost& H) {
-    void* ptrs[] = {H.seg_a, H.seg_b, H.layer_row_begin, H.layer_rows, H.tile_off, H.tile_clo, H.gate, H.frozen_list};
+    void* ptrs[] = {H.seg_a, H.seg_b, H.seg_d, H.layer_row_begin, H.layer_rows, H.tile_off, H.tile_clo, H.gate, H.frozen_list};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     H = PlanarHost();
@@ -385,6 +398,7 @@ cudaError_t planar_build(const SceneParams& P, PlanarHost& H) {
 
     PL_TRY(cudaMalloc(&H.seg_a, sizeof(float4) * np * W));
     PL_TRY(cudaMalloc(&H.seg_b, sizeof(float2) * np * W));
+    PL_TRY(cudaMalloc(&H.seg_d, sizeof(SegmentD) * np * W));
     PL_TRY(cudaMalloc(&H.layer_row_begin, sizeof(int) * (rz + 1)));
     PL_TRY(cudaMalloc(&H.layer_rows, sizeof(int) * Hh));
     PL_TRY(cudaMalloc(&H.tile_off, sizeof(int) * n_tiles * (np + 1)));
@@ -430,9 +444,8 @@ cudaError_t planar_build(const SceneParams& P, PlanarHost& H) {
     if (row_ref < 0) row_ref = Hh / 2;
 
     // segment table (flags live in gate[1])
-    planar_segments_kernel<<<(np * W + kPlanarThreads - 1) / kPlanarThreads, kPlanarThreads>>>(R, row_ref, H.seg_a,
-                                                                                             H.seg_b, H.gate + 1,
-                                                                                             H.frozen_list, H.gate + 2);
+    planar_segments_kernel<<<(np * W + kPlanarThreads - 1) / kPlanarThreads, kPlanarThreads>>>(
+        R, row_ref, H.seg_a, H.seg_b, H.seg_d, H.gate + 1, H.frozen_list, H.gate + 2);
     count_launch();
     PL_TRY(cudaGetLastError());
     int flags = 0;

@@ -35,13 +35,13 @@ namespace {
 
 constexpr int kJThreads = 1024;
 constexpr int kJWarps = kJThreads / 32;
-constexpr int kJStride = 33;  // floats per voxel: 32 layer lanes + 1 pad (conflict-free flush)
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr int kScatter = 0, kGather = 1;
 
 struct JTable {
     float4* a;  // ox, oy, dx, dy
-    float4* b;  // tmax, weight, layer lane inside the block (int bits, -1 = nothing to march), unused
+    float4* b;  // tmax, ray weight x throughput at the origin, layer lane inside the block (int bits; -1 =
+                // nothing to march, -2 = walked by the table kernel), pattern value (forward passes)
 };
 
 // layout of the table: slot = ((((kk * res_x + c) * n_blk + blk) * items + q) * 32 + lane
@@ -59,7 +59,10 @@ __device__ __forceinline__ uint32_t sampler_stream(const SceneParams& P, size_t 
 
 // One thread per table slot.  kScatter: in = active_data, out = film (only lanes walked here touch it).
 // kGather: in = dL, gT = per-slot gradient (lanes walked here write theirs, every other slot is zeroed).
-template <int kMode>
+// kRefresh (forward only): the geometry in the table is that of this very call - same pixels, seed and
+// spp, as for A d after A p of one L-BFGS iteration (lbfgs.py:248 renders the direction with the seed of
+// the primal pass) - so only the pattern values are written again and the odd lanes walked again.
+template <int kMode, bool kRefresh>
 __global__ void __launch_bounds__(256)
 jtable_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ SceneParams Pw,
               const __grid_constant__ PlanarZPlan Z, const int* __restrict__ layer_a, const JLayout Ly,
@@ -77,6 +80,11 @@ jtable_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Sce
     const int c = static_cast<int>(r % P.res_x);
     const int kk = Ly.kc + static_cast<int>(r / P.res_x);
 
+    int state = -1;   // layer lane inside the block, -1 = nothing to march, -2 = walked here (odd lane)
+    if (kRefresh) {
+        state = __float_as_int(__ldg(&T.b[t].z));
+        if (state == -1) return;
+    }
     float4 ea = make_float4(0.f, 0.f, 1.f, 0.f);
     float4 eb = make_float4(0.f, 0.f, __int_as_float(-1), 0.f);
     float g_here = 0.f;
@@ -93,33 +101,40 @@ jtable_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Sce
         int k0, nk;
         call_angles(P, active_pixels, n_active, k0, nk);
         const size_t j = active_index(P, kk, row, c);
+        float em = 1.f;
+        if (kMode == kScatter) em = __ldg(in + j);
+        if (kRefresh && state >= 0) {
+            T.b[t].w = em;
+            return;
+        }
         // the gate has verified the layout, so the pixel index follows from (angle, row, column)
         const uint32_t pixel = (static_cast<uint32_t>(k0 + kk) * P.res_y + row) * P.res_x + c;
         const uint32_t stream = sampler_stream(P, j, smp, spp);
         Sampler rng;
         rng.seed(seed, stream);
         const Ray ray = generate_ray(P, pixel, rng);
+        bool odd = kRefresh;
+        int lyr = -1;
         RecordSink sink;
         sink.seg = ray;
-        trace_lane<false>(P, ray, rng, sink);
-        const bool one = sink.count == 1 && sink.w0 != 0.f && sink.tmax > 0.f && isfinite(sink.tmax);
-        bool odd = sink.count > 1 || ray.dz != 0.f || (sink.count == 1 && sink.seg.dz != 0.f) ||
-                   (sink.count == 1 && dda_has_frozen_axis(P, sink.seg, sink.tmax));
-        int lyr = -1;
-        if (!odd && one) {
-            const float z = sink.seg.oz;
-            if (z > P.bmin[2] && z < P.bmax[2]) {
-                const float vs = (P.bmax[2] - P.bmin[2]) / static_cast<float>(P.res[2]);
-                const int layer = min(max(__float2int_rz((z - P.bmin[2]) / vs), 0), P.res[2] - 1);
-                const int aa = __ldg(layer_a + layer);   // -1: outside the z window of this handle
-                if (aa >= 0) {
-                    if ((aa >> 5) == blk) lyr = aa & 31;
-                    else odd = true;   // the jitter moved the lane into another block of layers
+        if (!kRefresh) {
+            trace_lane<false>(P, ray, rng, sink);
+            const bool one = sink.count == 1 && sink.w0 != 0.f && sink.tmax > 0.f && isfinite(sink.tmax);
+            odd = sink.count > 1 || ray.dz != 0.f || (sink.count == 1 && sink.seg.dz != 0.f) ||
+                  (sink.count == 1 && dda_has_frozen_axis(P, sink.seg, sink.tmax));
+            if (!odd && one) {
+                const float z = sink.seg.oz;
+                if (z > P.bmin[2] && z < P.bmax[2]) {
+                    const float vs = (P.bmax[2] - P.bmin[2]) / static_cast<float>(P.res[2]);
+                    const int layer = min(max(__float2int_rz((z - P.bmin[2]) / vs), 0), P.res[2] - 1);
+                    const int aa = __ldg(layer_a + layer);   // -1: outside the z window of this handle
+                    if (aa >= 0) {
+                        if ((aa >> 5) == blk) lyr = aa & 31;
+                        else odd = true;   // the jitter moved the lane into another block of layers
+                    }
                 }
             }
         }
-        float em = 1.f;
-        if (kMode == kScatter) em = __ldg(in + j);
         if (odd) {
             // not a single planar segment of this block: general walk, deposited / gathered here
             Sampler rng2;
@@ -133,17 +148,29 @@ jtable_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Sce
                 ScatterSink sc{out, em * ray_weight};
                 trace_lane<false>(Pw, ray2, rng2, sc);
             }
+            eb.z = __int_as_float(-2);
         } else if (lyr >= 0) {
             ea = make_float4(sink.seg.ox, sink.seg.oy, sink.seg.dx, sink.seg.dy);
-            eb = make_float4(sink.tmax, em * ray_weight * sink.w0, __int_as_float(lyr), 0.f);
+            eb = make_float4(sink.tmax, ray_weight * sink.w0, __int_as_float(lyr), em);
         }
     }
+    if (kRefresh) return;
     T.a[t] = ea;
     T.b[t] = eb;
     if (kMode == kGather) gT[t] = g_here;
 }
 
 // kScatter: out = film (red.global flush).  kGather: in = dL (film layout), out = gT (red.global per lane).
+//
+// Shared tile: [(tile_h + 2)][(tile_w + 2)][32] floats - lane = layer, so the bank of an access is the
+// lane's layer whatever voxel the lane stands in (lanes of a warp stand in neighbouring voxels: with the
+// 33-float voxel pitch of the deterministic kernels they met 2.7 bank conflicts per deposit,
+// profiles/r02b_*); a one-voxel rim catches the step a walk takes when rounding puts its last boundary a
+// hair before the tile exit.
+//
+// Walk of one lane: optical depths relative to the tile entry; each trip deposits the current voxel up
+// to min(next boundary, tile exit) and steps across the nearer boundary, so the last voxel needs no
+// code of its own and the loop carries no step counters: 17 instructions per visit instead of 27.
 template <int kMode>
 __global__ void __launch_bounds__(kJThreads, 1)
 planarj_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ PlanarZPlan Z, const JLayout Ly,
@@ -155,26 +182,35 @@ planarj_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int x0 = (tile_id % Z.tiles_x) * Z.tile_w, y0 = (tile_id / Z.tiles_x) * Z.tile_h;
     const int w = min(Z.tile_w, P.res[0] - x0), h = min(Z.tile_h, P.res[1] - y0);
-    const int tw = Z.tile_w;
-    const int tile_floats = Z.tile_h * tw * kJStride;
+    const int pitch = Z.tile_w + 2;                       // voxels per tile row, rim included
+    const int tile_floats = (Z.tile_h + 2) * pitch * 32;
     const int a_base = blk * 32;
     const size_t layer_elems = static_cast<size_t>(P.res[0]) * P.res[1];
+    const int z_mine = (a_base + lane < Z.nz) ? __ldg(Z.zl + a_base + lane) : -1;   // film layer of this lane
+    const bool vec = ((x0 | w | P.res[0]) & 3) == 0 && (reinterpret_cast<uintptr_t>(kMode == kScatter ? out : in) & 15) == 0;
 
-    // ---- stage the tile
-    if (kMode == kScatter) {
-        for (int i = threadIdx.x; i < tile_floats; i += kJThreads) tile[i] = 0.f;
-    } else {
-        const int per_layer = h * w;
-        for (int i = threadIdx.x; i < 32 * per_layer; i += kJThreads) {
-            const int al = i / per_layer, rem = i - al * per_layer;
-            const int yy = rem / w, xx = rem - yy * w;
-            const int z = (a_base + al < Z.nz) ? __ldg(Z.zl + a_base + al) : -1;
-            float v = 0.f;
-            if (z >= 0) v = __ldg(in + z * layer_elems + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx));
-            tile[(yy * tw + xx) * kJStride + al] = v;
+    // ---- stage the tile: lane = layer, a warp takes 4 voxels of a row at a time (conflict-free in shared
+    // memory; in global memory every lane reads 16 contiguous bytes of its own layer)
+    for (int i = threadIdx.x; i < tile_floats; i += kJThreads) tile[i] = 0.f;
+    __syncthreads();
+    if (kMode == kGather && z_mine >= 0) {
+        const float* src = in + z_mine * layer_elems;
+        if (vec) {
+            const int w4 = w >> 2;
+            for (int i = warp; i < h * w4; i += kJWarps) {
+                const int yy = i / w4, xx = (i - yy * w4) << 2;
+                const float4 v = __ldg(reinterpret_cast<const float4*>(src + static_cast<size_t>(y0 + yy) * P.res[0] + x0 + xx));
+                float* d = tile + ((yy + 1) * pitch + xx + 1) * 32 + lane;
+                d[0] = v.x; d[32] = v.y; d[64] = v.z; d[96] = v.w;
+            }
+        } else {
+            for (int i = warp; i < h * w; i += kJWarps) {
+                const int yy = i / w, xx = i - yy * w;
+                tile[((yy + 1) * pitch + xx + 1) * 32 + lane] = __ldg(src + static_cast<size_t>(y0 + yy) * P.res[0] + x0 + xx);
+            }
         }
     }
-    __syncthreads();
+    if (kMode == kGather) __syncthreads();
 
     int k0, nk;
     call_angles(P, active_pixels, n_active, k0, nk);
@@ -187,68 +223,86 @@ planarj_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
     const float sig = P.sigma_t * kLog2e;
     const float vsx = (P.bmax[0] - P.bmin[0]) / static_cast<float>(P.res[0]);
     const float vsy = (P.bmax[1] - P.bmin[1]) / static_cast<float>(P.res[1]);
+    const float rvx = 1.f / vsx, rvy = 1.f / vsy;
+    // tile rectangle in world units
+    const float xl = P.bmin[0] + static_cast<float>(x0) * vsx, xh = P.bmin[0] + static_cast<float>(x0 + w) * vsx;
+    const float yl = P.bmin[1] + static_cast<float>(y0) * vsy, yh = P.bmin[1] + static_cast<float>(y0 + h) * vsy;
     const uint32_t tile_s = static_cast<uint32_t>(__cvta_generic_to_shared(tile));
-    const int sxb = 4 * kJStride, syb = 4 * kJStride * tw;
+    const int sxb = 4 * 32, syb = 4 * 32 * pitch;
 
     const int f_base = __ldg(off + ka);
     const int tasks = (__ldg(off + kb) - f_base) * Ly.items;   // < 2^31: checked by planarj_pass
+    const unsigned slots_kc = static_cast<unsigned>(P.res_x) * Ly.n_blk * Ly.items;   // slots / 32 per angle
     int k = ka;
     for (int f = warp; f < tasks; f += kJWarps) {
         const int g = f / Ly.items + f_base;
         const int q = f - (g - f_base) * Ly.items;
         while (__ldg(off + k + 1) <= g) ++k;
         const int c = __ldg(clo + k) + (g - __ldg(off + k));
-        const size_t slot = ((((static_cast<size_t>(k - kfirst) * P.res_x + c) * Ly.n_blk + blk) * Ly.items + q) << 5) + lane;
+        // < 2^31 slots per chunk (planarj_pass): 32-bit index arithmetic
+        const unsigned slot = ((static_cast<unsigned>(k - kfirst) * slots_kc + (static_cast<unsigned>(c) * Ly.n_blk + blk) * Ly.items + q) << 5) + lane;
         const float4 eb = __ldg(T.b + slot);
         const int lyr = __float_as_int(eb.z);
-        bool live = lyr >= 0 && eb.y != 0.f;
+        float wgt = kMode == kScatter ? eb.y * eb.w : eb.y;
+        bool live = lyr >= 0 && wgt != 0.f;
         if (!__any_sync(0xffffffffu, live)) continue;
         float4 ea = make_float4(0.f, 0.f, 1.f, 0.f);
         if (live) ea = __ldg(T.a + slot);
 
-        // ---- clip to the tile; entry / exit voxel by truncation then clip (sensor.py:345-346), tile-local
-        float t0 = 0.f, t1 = 0.f;
-        live = live && clip_to_tile(P, ea, eb.x, x0, y0, w, h, t0, t1);
+        // ---- clip to the tile (slab test with reciprocals: the clip only places the entry and the exit)
+        float t0 = 0.f, t1 = eb.x;
+        const bool mx = fabsf(ea.z) > 1e-8f, my = fabsf(ea.w) > 1e-8f;
+        const float rdx = rcp_approx(ea.z), rdy = rcp_approx(ea.w);
+        if (mx) {
+            const float ta = (xl - ea.x) * rdx, tb = (xh - ea.x) * rdx;
+            t0 = fmaxf(t0, fminf(ta, tb));
+            t1 = fminf(t1, fmaxf(ta, tb));
+        } else if (ea.x < xl || ea.x >= xh) {
+            live = false;
+        }
+        if (my) {
+            const float ta = (yl - ea.y) * rdy, tb = (yh - ea.y) * rdy;
+            t0 = fmaxf(t0, fminf(ta, tb));
+            t1 = fminf(t1, fmaxf(ta, tb));
+        } else if (ea.y < yl || ea.y >= yh) {
+            live = false;
+        }
+        live = live && t0 < t1;
         float acc = 0.f;
         if (live) {
+            // entry voxel by truncation then clip (sensor.py:345-346), tile-local
             const float gx = fmaf(ea.z, t0, ea.x), gy = fmaf(ea.w, t0, ea.y);
-            const float hx = fmaf(ea.z, t1, ea.x), hy = fmaf(ea.w, t1, ea.y);
-            const int ix = min(max(__float2int_rz((gx - P.bmin[0]) / vsx) - x0, 0), w - 1);
-            const int iy = min(max(__float2int_rz((gy - P.bmin[1]) / vsy) - y0, 0), h - 1);
-            const int jx = min(max(__float2int_rz((hx - P.bmin[0]) / vsx) - x0, 0), w - 1);
-            const int jy = min(max(__float2int_rz((hy - P.bmin[1]) / vsy) - y0, 0), h - 1);
-            const float u0 = sig * t0, u1 = sig * t1;
-            float ux = INFINITY, uy = INFINITY, ax = 0.f, ay = 0.f, bx = 0.f, by = 0.f, fx = 0.f, fy = 0.f;
-            int nx = 0, ny = 0, sx = 0, sy = 0;
-            if (fabsf(ea.z) > 1e-8f) {
-                const float inv = sig / ea.z;
+            const int ix = min(max(__float2int_rz((gx - P.bmin[0]) * rvx) - x0, 0), w - 1);
+            const int iy = min(max(__float2int_rz((gy - P.bmin[1]) * rvy) - y0, 0), h - 1);
+            // optical depths relative to the tile entry (see planarz_kernels.cu): the throughput at the
+            // entry goes into the weight, the differences below are then 16 x less noisy
+            const float u1 = sig * (t1 - t0);
+            float ux = INFINITY, uy = INFINITY, ax = 0.f, ay = 0.f;
+            int sx = 0, sy = 0;
+            if (mx) {
+                const float inv = sig * rdx;
                 const bool pos = ea.z > 0.f;
-                nx = max(pos ? jx - ix : ix - jx, 0);
                 sx = pos ? sxb : -sxb;
                 ax = fabsf(vsx * inv);
-                // boundary times relative to the tile entry: the cancellation sits in (boundary - g)
-                bx = fmaf(fmaf(static_cast<float>(x0 + ix + (pos ? 1 : 0)), vsx, P.bmin[0]) - gx, inv, u0);
-                if (nx > 0) ux = bx;
+                ux = (fmaf(static_cast<float>(x0 + ix + (pos ? 1 : 0)), vsx, P.bmin[0]) - gx) * inv;
             }
-            if (fabsf(ea.w) > 1e-8f) {
-                const float inv = sig / ea.w;
+            if (my) {
+                const float inv = sig * rdy;
                 const bool pos = ea.w > 0.f;
-                ny = max(pos ? jy - iy : iy - jy, 0);
                 sy = pos ? syb : -syb;
                 ay = fabsf(vsy * inv);
-                by = fmaf(fmaf(static_cast<float>(y0 + iy + (pos ? 1 : 0)), vsy, P.bmin[1]) - gy, inv, u0);
-                if (ny > 0) uy = by;
+                uy = (fmaf(static_cast<float>(y0 + iy + (pos ? 1 : 0)), vsy, P.bmin[1]) - gy) * inv;
             }
-            uint32_t addr = tile_s + 4u * static_cast<uint32_t>((iy * tw + ix) * kJStride + lyr);
-            float e_prev = ex2_approx(-u0);
-            const float wgt = eb.y;
-            // every lane walks its own segment; lanes of a warp differ by a sub-pixel shift, so their step
-            // counts agree to within a voxel or two and the loop stays nearly converged
-            for (int n = nx + ny; n > 0; --n) {
+            uint32_t addr = tile_s + 4u * static_cast<uint32_t>(((iy + 1) * pitch + ix + 1) * 32 + lyr);
+            wgt *= ex2_approx(-sig * t0);
+            float e_prev = 1.f;
+            // one trip: deposit the current voxel up to min(next boundary, tile exit), step across the
+            // nearer boundary.  Unrolled by two so that the carried 2^-u needs no register move.
+            auto trip = [&](float e_in, float& e_out) -> bool {
+                const float un = fminf(ux, uy);
                 const bool px = ux <= uy;
-                const float e = ex2_approx(-(px ? ux : uy));
-                const float de = e_prev - e;
-                e_prev = e;
+                e_out = ex2_approx(-fminf(un, u1));
+                const float de = e_in - e_out;
                 if (kMode == kGather) {
                     float v;
                     asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
@@ -256,55 +310,38 @@ planarj_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
                 } else {
                     asm volatile("red.shared.add.f32 [%0], %1;" ::"r"(addr), "f"(wgt * de) : "memory");
                 }
-                if (px) {
-                    fx += 1.f;
-                    ux = fmaf(fx, ax, bx);
-                    addr += sx;
-                    if (--nx == 0) ux = INFINITY;
-                } else {
-                    fy += 1.f;
-                    uy = fmaf(fy, ay, by);
-                    addr += sy;
-                    if (--ny == 0) uy = INFINITY;
-                }
-            }
-            const float de = e_prev - ex2_approx(-u1);
-            if (kMode == kGather) {
-                float v;
-                asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
-                acc = fmaf(v, de, acc);
-            } else {
-                asm volatile("red.shared.add.f32 [%0], %1;" ::"r"(addr), "f"(wgt * de) : "memory");
+                addr += px ? sx : sy;
+                if (px) ux += ax; else uy += ay;
+                return un < u1;
+            };
+            for (;;) {
+                float e_mid;
+                if (!trip(e_prev, e_mid)) break;
+                if (!trip(e_mid, e_prev)) break;
             }
         }
-        if (kMode == kGather && live && acc != 0.f) atomicAdd(out + slot, acc * eb.y);
+        if (kMode == kGather && live && acc != 0.f) atomicAdd(out + slot, acc * wgt);
     }
     if (kMode == kGather) return;
     __syncthreads();
 
-    // ---- flush: one red.global per voxel (v4 when the rows are 16-byte aligned in the film)
-    const bool vec = ((x0 | w | P.res[0]) & 3) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0;
+    // ---- flush: lane = layer; every lane adds 4 voxels of a row of its own layer with one red.global.add.v4
+    if (z_mine < 0) return;
+    float* dst = out + z_mine * layer_elems;
     if (vec) {
-        const int w4 = w >> 2, per_layer = h * w4;
-        for (int i = threadIdx.x; i < 32 * per_layer; i += kJThreads) {
-            const int al = i / per_layer, rem = i - al * per_layer;
-            const int yy = rem / w4, xx = (rem - yy * w4) << 2;
-            const int z = (a_base + al < Z.nz) ? __ldg(Z.zl + a_base + al) : -1;
-            if (z < 0) continue;
-            const float* src = tile + (yy * tw + xx) * kJStride + al;
-            const float v0 = src[0], v1 = src[kJStride], v2 = src[2 * kJStride], v3 = src[3 * kJStride];
+        const int w4 = w >> 2;
+        for (int i = warp; i < h * w4; i += kJWarps) {
+            const int yy = i / w4, xx = (i - yy * w4) << 2;
+            const float* src = tile + ((yy + 1) * pitch + xx + 1) * 32 + lane;
+            const float v0 = src[0], v1 = src[32], v2 = src[64], v3 = src[96];
             if (v0 != 0.f || v1 != 0.f || v2 != 0.f || v3 != 0.f)
-                red_add_v4(out + z * layer_elems + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx), v0, v1, v2, v3);
+                red_add_v4(dst + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx), v0, v1, v2, v3);
         }
     } else {
-        const int per_layer = h * w;
-        for (int i = threadIdx.x; i < 32 * per_layer; i += kJThreads) {
-            const int al = i / per_layer, rem = i - al * per_layer;
-            const int yy = rem / w, xx = rem - yy * w;
-            const int z = (a_base + al < Z.nz) ? __ldg(Z.zl + a_base + al) : -1;
-            if (z < 0) continue;
-            const float v = tile[(yy * tw + xx) * kJStride + al];
-            if (v != 0.f) atomicAdd(out + z * layer_elems + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx), v);
+        for (int i = warp; i < h * w; i += kJWarps) {
+            const int yy = i / w, xx = i - yy * w;
+            const float v = tile[((yy + 1) * pitch + xx + 1) * 32 + lane];
+            if (v != 0.f) atomicAdd(dst + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx), v);
         }
     }
 }
@@ -349,7 +386,7 @@ junpack_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
     } while (0)
 
 void planarj_release(PlanarJHost& J) {
-    void* ptrs[] = {J.tile_off, J.tile_clo, J.table, J.gT};
+    void* ptrs[] = {J.tile_off, J.tile_clo, J.table, J.table_adj, J.gT};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     J = PlanarJHost();
@@ -362,16 +399,16 @@ cudaError_t planarj_build(const SceneParams& P, const PlanarHost& base, const Pl
     planarj_release(J);
     if (!Zh.valid || Zh.nz == 0) return cudaSuccess;
     const int np = P.n_patterns, rx = P.res[0], ry = P.res[1];
-    const int area = (227 * 1024 / 4) / kJStride;
-    const int side = static_cast<int>(std::floor(std::sqrt(static_cast<double>(area))));
+    const int area = (227 * 1024 / 4) / 32;   // voxels of [32 layers], the one-voxel rim included
+    const int side = static_cast<int>(std::floor(std::sqrt(static_cast<double>(area)))) - 2;
     const int tw_max = std::max(4, side & ~3);
     J.tiles_x = (rx + tw_max - 1) / tw_max;
     J.tile_w = (((rx + J.tiles_x - 1) / J.tiles_x) + 3) & ~3;
     J.tiles_x = (rx + J.tile_w - 1) / J.tile_w;
-    const int th_max = std::max(1, area / J.tile_w);
+    const int th_max = std::max(1, area / (J.tile_w + 2) - 2);
     J.tiles_y = (ry + th_max - 1) / th_max;
     J.tile_h = (ry + J.tiles_y - 1) / J.tiles_y;
-    J.smem_bytes = sizeof(float) * static_cast<size_t>(J.tile_h) * J.tile_w * kJStride;
+    J.smem_bytes = sizeof(float) * static_cast<size_t>(J.tile_h + 2) * (J.tile_w + 2) * 32;
     const int n_tiles = J.tiles_x * J.tiles_y;
     PJ_TRY(cudaMalloc(&J.tile_off, sizeof(int) * static_cast<size_t>(n_tiles) * (np + 1)));
     PJ_TRY(cudaMalloc(&J.tile_clo, sizeof(int) * static_cast<size_t>(n_tiles) * np));
@@ -399,7 +436,7 @@ static cudaError_t j_reserve(void*& ptr, size_t& have, size_t need) {
 template <int kMode>
 static cudaError_t planarj_pass(const SceneParams& P, const SceneParams& Pw, PlanarZHost& Zh, PlanarJHost& J,
                                 const int* gate, const float* in, float* out, const uint32_t* active_pixels,
-                                uint64_t n_active, uint32_t spp, uint32_t seed, float ray_weight,
+                                uint64_t n_active, uint32_t spp, uint32_t seed, float ray_weight, bool cacheable,
                                 cudaStream_t stream) {
     const int nk = static_cast<int>(n_active / (static_cast<uint64_t>(P.res_x) * P.n_rows));
     JLayout Ly{};
@@ -412,16 +449,24 @@ static cudaError_t planarj_pass(const SceneParams& P, const SceneParams& Pw, Pla
     if (const char* env = std::getenv("DRTVAM_JTABLE_MB")) cap = static_cast<size_t>(std::atoll(env)) << 20;
     const size_t per_slot = 32 + (kMode == kGather ? 4 : 0);
     int chunk = static_cast<int>(std::max<size_t>(1, cap / (slots_per_angle * per_slot)));
+    chunk = std::min<long long>(chunk, ((1ll << 31) - 64) / static_cast<long long>(slots_per_angle));   // 32-bit slot indices
+    if (chunk < 1) return cudaErrorInvalidValue;
     chunk = std::min(chunk, nk);
     const size_t slots_max = slots_per_angle * chunk;
-    PJ_TRY(j_reserve(J.table, J.table_bytes, slots_max * 32));
+    // forward and adjoint passes keep tables of their own: the forward one is reused by the next forward
+    // pass of the same iteration (A d after A p), which the adjoint pass in between must not overwrite
+    JTable T;
     if (kMode == kGather) {
+        PJ_TRY(j_reserve(J.table_adj, J.table_adj_bytes, slots_max * 32));
         void* g = J.gT;
         PJ_TRY(j_reserve(g, J.gT_bytes, slots_max * 4));
         J.gT = static_cast<float*>(g);
+        T.a = static_cast<float4*>(J.table_adj);
+    } else {
+        if (slots_max * 32 > J.table_bytes) J.cache_valid = false;
+        PJ_TRY(j_reserve(J.table, J.table_bytes, slots_max * 32));
+        T.a = static_cast<float4*>(J.table);
     }
-    JTable T;
-    T.a = static_cast<float4*>(J.table);
     T.b = T.a + slots_max;
 
     PlanarZPlan Z{};
@@ -432,12 +477,22 @@ static cudaError_t planarj_pass(const SceneParams& P, const SceneParams& Pw, Pla
     Z.lanes_l = 1;
     const long long ctas = static_cast<long long>(J.tiles_x) * J.tiles_y * Ly.n_blk;
 
+    // the geometry of a forward pass survives in the table when the whole call fits one chunk
+    const bool reuse = kMode == kScatter && cacheable && chunk == nk && J.cache_valid && J.cache_seed == seed && J.cache_spp == spp &&
+                       J.cache_pixels == active_pixels && J.cache_n == n_active && J.cache_weight == ray_weight &&
+                       J.cache_index == P.sampler_index && !std::getenv("DRTVAM_JTABLE_NOCACHE");
+    if (kMode == kScatter) J.cache_valid = false;
     for (int kc = 0; kc < nk; kc += chunk) {
         Ly.kc = kc;
         Ly.nkc = std::min(chunk, nk - kc);
         const size_t slots = slots_per_angle * Ly.nkc;
-        jtable_kernel<kMode><<<static_cast<unsigned>((slots + 255) / 256), 256, 0, stream>>>(
-            P, Pw, Z, Zh.layer_a, Ly, in, out, J.gT, active_pixels, n_active, spp, seed, ray_weight, T, gate);
+        const unsigned tblocks = static_cast<unsigned>((slots + 255) / 256);
+        if (reuse)
+            jtable_kernel<kScatter, true><<<tblocks, 256, 0, stream>>>(P, Pw, Z, Zh.layer_a, Ly, in, out, J.gT, active_pixels,
+                                                                      n_active, spp, seed, ray_weight, T, gate);
+        else
+            jtable_kernel<kMode, false><<<tblocks, 256, 0, stream>>>(P, Pw, Z, Zh.layer_a, Ly, in, out, J.gT, active_pixels,
+                                                                    n_active, spp, seed, ray_weight, T, gate);
         count_launch();
         PJ_TRY(cudaGetLastError());
         // enough CTAs for two waves of the 148 SMs: the tile flush is a red.global, so angle groups are free
@@ -456,21 +511,28 @@ static cudaError_t planarj_pass(const SceneParams& P, const SceneParams& Pw, Pla
             PJ_TRY(cudaGetLastError());
         }
     }
+    if (kMode == kScatter && cacheable && chunk == nk) {
+        J.cache_valid = true;
+        J.cache_seed = seed; J.cache_spp = spp; J.cache_pixels = active_pixels; J.cache_n = n_active;
+        J.cache_weight = ray_weight;
+        J.cache_index = P.sampler_index;
+    }
     return cudaSuccess;
 }
 
 cudaError_t launch_planarj_forward(const SceneParams& P, const SceneParams& Pw, PlanarZHost& Zh, PlanarJHost& J,
                                    const int* gate, const float* active_data, const uint32_t* active_pixels,
                                    uint64_t n_active, uint32_t spp, uint32_t seed, float ray_weight, float* film,
-                                   bool, cudaStream_t stream) {
+                                   bool cacheable, cudaStream_t stream) {
     return planarj_pass<kScatter>(P, Pw, Zh, J, gate, active_data, film, active_pixels, n_active, spp, seed, ray_weight,
-                                  stream);
+                                  cacheable, stream);
 }
 
 cudaError_t launch_planarj_adjoint(const SceneParams& P, const SceneParams& Pw, PlanarZHost& Zh, PlanarJHost& J,
                                    const int* gate, const float* dL, const uint32_t* active_pixels, uint64_t n_active,
                                    uint32_t spp, uint32_t seed, float ray_weight, float* grad, cudaStream_t stream) {
-    return planarj_pass<kGather>(P, Pw, Zh, J, gate, dL, grad, active_pixels, n_active, spp, seed, ray_weight, stream);
+    return planarj_pass<kGather>(P, Pw, Zh, J, gate, dL, grad, active_pixels, n_active, spp, seed, ray_weight, false,
+                                 stream);
 }
 
 }  // namespace drtvam

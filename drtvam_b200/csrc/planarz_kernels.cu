@@ -31,6 +31,7 @@
 
 #include <cub/device/device_scan.cuh>
 
+#include "expm.cuh"
 #include "kernels.h"
 #include "planar.cuh"
 
@@ -242,59 +243,75 @@ __device__ __forceinline__ void z_scatter2(uint32_t addr_a, float de_a, uint32_t
 // Walk entries.  The clipped 2-D walk of a (tile, angle, column) triple depends
 // only on the scene, not on the patterns, so it is computed once per scene
 // (and depth setting) and every pass of every z-block just reads it:
-//   e[0] = { u0, u1, ux, uy }   u = sigma_t log2(e) t at tile entry / exit and
-//                               at the first x / y voxel boundary (inf = none)
-//   e[1] = { ax, ay, w0, bits } boundary-to-boundary increments of u, the
-//                               throughput at the segment origin, and
+//   e[0] = { w, u1, ux, uy }    w = throughput at the TILE ENTRY (w0 2^-u(t0)); u = sigma_t log2(e) (t - t0)
+//                               at the tile exit and at the first x / y voxel boundary (inf = none)
+//   e[1] = { ax, ay, -, bits }  boundary-to-boundary increments of u and
 //                               ix | iy<<7 | nx<<14 | ny<<21 | xneg<<28 | yneg<<29 | valid<<30
-// Times are taken relative to the tile entry, u = u(t0) + (boundary - g) sig / d,
-// so the cancellation sits in (boundary - g), a difference of nearby positions.
+// Optical depths are RELATIVE to the tile entry, u = (boundary - g) sig / d: the deposit of a voxel is
+// w (2^-u_in - 2^-u_out), and the rounding of an absolute u ~ 2 (2.4e-7) would be divided by the
+// per-voxel extinction ~2.5e-3 - 1e-4 of noise per deposit; relative to the tile it is 16 x smaller.
 // ---------------------------------------------------------------------------
 constexpr unsigned kEntryValid = 1u << 30;
 
-// The walk entry of one (angle k, column c) segment clipped to the tile [x0, x0+w) x [y0, y0+h).
-__device__ __forceinline__ void make_entry(const SceneParams& P, const float4* __restrict__ seg_a,
-                                           const float2* __restrict__ seg_b, int k, int c, int x0, int y0, int w, int h,
-                                           float4& e0, float4& e1) {
+// The walk entry of one (angle k, column c) segment clipped to the tile [x0, x0+w) x [y0, y0+h).  Runs once
+// per scene, in double precision on the double-precision segment (planar_f64.cuh): positions of ~10 mm have
+// an fp32 ulp of 4e-5 voxels of 25 um, which would sit in the first and last deposit of EVERY tile crossing.
+__device__ __forceinline__ void make_entry(const SceneParams& P, const SegmentD* __restrict__ seg_d, int k, int c, int x0,
+                                           int y0, int w, int h, float4& e0, float4& e1) {
     e0 = make_float4(0.f, 0.f, INFINITY, INFINITY);
     e1 = make_float4(0.f, 0.f, 0.f, __uint_as_float(0u));
-    const int s = k * P.res_x + c;
-    const float2 b = seg_b[s];
-    const float4 a = seg_a[s];
-    float t0, t1;
-    if (b.y != 0.f && clip_to_tile(P, a, b.x, x0, y0, w, h, t0, t1)) {
-        const float sig = P.sigma_t * kLog2e;
-        const float vsx = (P.bmax[0] - P.bmin[0]) / static_cast<float>(P.res[0]);
-        const float vsy = (P.bmax[1] - P.bmin[1]) / static_cast<float>(P.res[1]);
-        // entry / exit voxel: truncation then clip (sensor.py:345-346), tile-local
-        const float gx = fmaf(a.z, t0, a.x), gy = fmaf(a.w, t0, a.y);
-        const float hx = fmaf(a.z, t1, a.x), hy = fmaf(a.w, t1, a.y);
-        const int ix = min(max(__float2int_rz((gx - P.bmin[0]) / vsx) - x0, 0), w - 1);
-        const int iy = min(max(__float2int_rz((gy - P.bmin[1]) / vsy) - y0, 0), h - 1);
-        const int jx = min(max(__float2int_rz((hx - P.bmin[0]) / vsx) - x0, 0), w - 1);
-        const int jy = min(max(__float2int_rz((hy - P.bmin[1]) / vsy) - y0, 0), h - 1);
-        const float u0 = sig * t0;
-        unsigned bits = kEntryValid | static_cast<unsigned>(ix) | (static_cast<unsigned>(iy) << 7);
-        float ux = INFINITY, uy = INFINITY, ax = 0.f, ay = 0.f;
-        if (fabsf(a.z) > 1e-8f) {
-            const float inv = sig / a.z;
-            const bool pos = a.z > 0.f;
-            const int nx = max(pos ? jx - ix : ix - jx, 0);
-            ax = fabsf(vsx * inv);
-            if (nx > 0) ux = fmaf(fmaf(static_cast<float>(x0 + ix + (pos ? 1 : 0)), vsx, P.bmin[0]) - gx, inv, u0);
-            bits |= (static_cast<unsigned>(nx) << 14) | (pos ? 0u : (1u << 28));
-        }
-        if (fabsf(a.w) > 1e-8f) {
-            const float inv = sig / a.w;
-            const bool pos = a.w > 0.f;
-            const int ny = max(pos ? jy - iy : iy - jy, 0);
-            ay = fabsf(vsy * inv);
-            if (ny > 0) uy = fmaf(fmaf(static_cast<float>(y0 + iy + (pos ? 1 : 0)), vsy, P.bmin[1]) - gy, inv, u0);
-            bits |= (static_cast<unsigned>(ny) << 21) | (pos ? 0u : (1u << 29));
-        }
-        e0 = make_float4(u0, sig * t1, ux, uy);
-        e1 = make_float4(ax, ay, b.y, __uint_as_float(bits));
+    const SegmentD S = seg_d[k * P.res_x + c];
+    if (S.w0 == 0.0) return;
+    const double bx0 = P.bmin[0], by0 = P.bmin[1];
+    const double vsx = (static_cast<double>(P.bmax[0]) - bx0) / P.res[0];
+    const double vsy = (static_cast<double>(P.bmax[1]) - by0) / P.res[1];
+    // clip to the tile rectangle
+    const double xl = bx0 + x0 * vsx, xh = bx0 + (x0 + w) * vsx, yl = by0 + y0 * vsy, yh = by0 + (y0 + h) * vsy;
+    double t0 = 0.0, t1 = S.tmax;
+    if (fabs(S.dx) > 1e-8) {
+        const double ta = (xl - S.ox) / S.dx, tb = (xh - S.ox) / S.dx;
+        t0 = fmax(t0, fmin(ta, tb));
+        t1 = fmin(t1, fmax(ta, tb));
+    } else if (S.ox < xl || S.ox >= xh) {
+        return;
     }
+    if (fabs(S.dy) > 1e-8) {
+        const double ta = (yl - S.oy) / S.dy, tb = (yh - S.oy) / S.dy;
+        t0 = fmax(t0, fmin(ta, tb));
+        t1 = fmin(t1, fmax(ta, tb));
+    } else if (S.oy < yl || S.oy >= yh) {
+        return;
+    }
+    if (!(t0 < t1)) return;
+    const double sig = static_cast<double>(P.sigma_t) * 1.4426950408889634;
+    // entry / exit voxel: truncation then clip (sensor.py:345-346), tile-local
+    const double gx = fma(S.dx, t0, S.ox), gy = fma(S.dy, t0, S.oy);
+    const double hx = fma(S.dx, t1, S.ox), hy = fma(S.dy, t1, S.oy);
+    const int ix = min(max(static_cast<int>((gx - bx0) / vsx) - x0, 0), w - 1);
+    const int iy = min(max(static_cast<int>((gy - by0) / vsy) - y0, 0), h - 1);
+    const int jx = min(max(static_cast<int>((hx - bx0) / vsx) - x0, 0), w - 1);
+    const int jy = min(max(static_cast<int>((hy - by0) / vsy) - y0, 0), h - 1);
+    unsigned bits = kEntryValid | static_cast<unsigned>(ix) | (static_cast<unsigned>(iy) << 7);
+    double ux = INFINITY, uy = INFINITY, ax = 0.0, ay = 0.0;
+    if (fabs(S.dx) > 1e-8) {
+        const double inv = sig / S.dx;
+        const bool pos = S.dx > 0.0;
+        const int nx = max(pos ? jx - ix : ix - jx, 0);
+        ax = fabs(vsx * inv);
+        if (nx > 0) ux = (bx0 + (x0 + ix + (pos ? 1 : 0)) * vsx - gx) * inv;
+        bits |= (static_cast<unsigned>(nx) << 14) | (pos ? 0u : (1u << 28));
+    }
+    if (fabs(S.dy) > 1e-8) {
+        const double inv = sig / S.dy;
+        const bool pos = S.dy > 0.0;
+        const int ny = max(pos ? jy - iy : iy - jy, 0);
+        ay = fabs(vsy * inv);
+        if (ny > 0) uy = (by0 + (y0 + iy + (pos ? 1 : 0)) * vsy - gy) * inv;
+        bits |= (static_cast<unsigned>(ny) << 21) | (pos ? 0u : (1u << 29));
+    }
+    e0 = make_float4(static_cast<float>(S.w0 * exp2(-sig * t0)), static_cast<float>(sig * (t1 - t0)),
+                     static_cast<float>(ux), static_cast<float>(uy));
+    e1 = make_float4(static_cast<float>(ax), static_cast<float>(ay), 0.f, __uint_as_float(bits));
 }
 
 // (tile, angle, column) of walk entry e of a plan (binary searches in the prefix tables)
@@ -328,7 +345,7 @@ zsetup_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pla
     const int x0 = (tile_id % Z.tiles_x) * Z.tile_w, y0 = (tile_id / Z.tiles_x) * Z.tile_h;
     const int w = min(Z.tile_w, P.res[0] - x0), h = min(Z.tile_h, P.res[1] - y0);
     float4 e0, e1;
-    make_entry(P, Z.seg_a, Z.seg_b, k, c, x0, y0, w, h, e0, e1);
+    make_entry(P, Z.seg_d, k, c, x0, y0, w, h, e0, e1);
     entries[2 * static_cast<size_t>(e)] = e0;
     entries[2 * static_cast<size_t>(e) + 1] = e1;
 }
@@ -389,7 +406,7 @@ planarz_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
         while (__ldg(off + k + 1) <= g) ++k;
         const int c = __ldg(clo + k) + (g - __ldg(off + k));
 
-        const float wray = ray_weight * e1.z;
+        const float wray = ray_weight * e0.x;
         const size_t tbase = (static_cast<size_t>(k - k0) * P.res_x + c) * Z.nz_pad + a_base + lane;
         float em[kL], acc[kL];
 #pragma unroll
@@ -412,7 +429,7 @@ planarz_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
         const float ax = e1.x, ay = e1.y, bx = e0.z, by = e0.w;
         float fx = 0.f, fy = 0.f;
         uint32_t addr = tile_s + static_cast<uint32_t>((iy * tw + ix) * (4 * kVox));
-        float e_prev = ex2_approx(-e0.x);
+        float e_prev = 1.f;   // 2^-0: optical depths are relative to the tile entry
         // every branch below is warp-uniform: all lanes walk the same (angle, column) segment.
         // `next` yields the voxel address and the deposit E(u_in) - E(u_out) of the current voxel
         // and steps to the neighbour across the nearer boundary (the last voxel ends at u1).
@@ -531,7 +548,8 @@ planarz_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
 constexpr int kPatch = 4;
 
 // Marches the clipped walk of entry (e0, e1) and calls visit(yy * tw + xx, de) for every voxel, with
-// de = 2^-u_in - 2^-u_out (the arithmetic of the `next` lambda of planarz_kernel).
+// de = 2^-u_in (1 - 2^-(u_out - u_in)) evaluated without cancellation (expm.cuh): this runs once per
+// scene, to make the coefficient blocks of the patch gather.
 template <class Visit>
 __device__ __forceinline__ void walk_entry(const float4 e0, const float4 e1, int tw, Visit&& visit) {
     const unsigned bits = __float_as_uint(e1.w);
@@ -543,7 +561,7 @@ __device__ __forceinline__ void walk_entry(const float4 e0, const float4 e1, int
     const float ax = e1.x, ay = e1.y, bx = e0.z, by = e0.w;
     float fx = 0.f, fy = 0.f;
     int v = iy * tw + ix;
-    float e_prev = ex2_approx(-e0.x);
+    float u_prev = 0.f;
     for (int n = nx + ny; n >= 0; --n) {
         float u_out = e0.y;
         const int v_here = v;
@@ -558,9 +576,8 @@ __device__ __forceinline__ void walk_entry(const float4 e0, const float4 e1, int
                 if (--ny == 0) uy = INFINITY;
             }
         }
-        const float e = ex2_approx(-u_out);
-        visit(v_here, e_prev - e);
-        e_prev = e;
+        visit(v_here, exp2f(-u_prev) * one_minus_ex2_neg(fmaxf(u_out - u_prev, 0.f)));
+        u_prev = u_out;
     }
 }
 
@@ -575,11 +592,11 @@ gsetup_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pla
     const int x0 = (tile_id % Z.tiles_x) * kPatch, y0 = (tile_id / Z.tiles_x) * kPatch;
     const int w = min(kPatch, P.res[0] - x0), h = min(kPatch, P.res[1] - y0);
     float4 e0, e1;
-    make_entry(P, Z.seg_a, Z.seg_b, k, c, x0, y0, w, h, e0, e1);
+    make_entry(P, Z.seg_d, k, c, x0, y0, w, h, e0, e1);
     float cf[16];
 #pragma unroll
     for (int i = 0; i < 16; ++i) cf[i] = 0.f;
-    const float w0 = e1.z;  // throughput at the segment origin times sigma_a / sigma_t
+    const float w0 = e0.x;  // throughput at the patch entry times sigma_a / sigma_t
     walk_entry(e0, e1, kPatch, [&](int v, float de) {
 #pragma unroll
         for (int i = 0; i < 16; ++i)
@@ -867,6 +884,7 @@ static cudaError_t z_build_sub(const SceneParams& P, const PlanarHost& base, con
     PlanarZPlan& Z = S.plan;
     Z.seg_a = base.seg_a;
     Z.seg_b = base.seg_b;
+    Z.seg_d = base.seg_d;
     z_tile_dims(P.res[0], P.res[1], kL, Z.tile_w, Z.tile_h);
     Z.tiles_x = (P.res[0] + Z.tile_w - 1) / Z.tile_w;
     Z.tiles_y = (P.res[1] + Z.tile_h - 1) / Z.tile_h;
@@ -921,8 +939,23 @@ cudaError_t planarz_build(const SceneParams& P, const PlanarHost& base, const st
     // zl holds the layer index inside the window, i.e. inside the film buffers of a call
     for (int r = P.row_begin; r < P.row_begin + P.n_rows && r < Hh; ++r)
         if (row_layer[r] >= P.z_begin && row_layer[r] < P.z_end) rows_of[row_layer[r]].push_back(r);
+    // jittered passes (walks == false): a lane of row r lands anywhere in the row's height, which can
+    // reach layers that hold no row CENTRE (e.g. 0.05 mm pixels over 0.025 mm layers); those layers are
+    // active too, with no rows of their own
+    std::vector<char> reach(rz, 0);
+    if (!walks && base.row_z.size() == static_cast<size_t>(Hh)) {
+        const float vs = (P.bmax[2] - P.bmin[2]) / static_cast<float>(rz);
+        const float dz = Hh > 1 ? std::fabs(base.row_z[1] - base.row_z[0]) : P.pixel_y;
+        for (int r = P.row_begin; r < P.row_begin + P.n_rows && r < Hh; ++r) {
+            if (row_layer[r] < P.z_begin || row_layer[r] >= P.z_end) continue;
+            const float lo = (base.row_z[r] - 0.5f * dz - P.bmin[2]) / vs, hi = (base.row_z[r] + 0.5f * dz - P.bmin[2]) / vs;
+            const int la = std::max(static_cast<int>(std::floor(lo - 1e-3f)), P.z_begin);
+            const int lb = std::min(static_cast<int>(std::floor(hi + 1e-3f)), P.z_end - 1);
+            for (int z = la; z <= lb; ++z) reach[z] = 1;
+        }
+    }
     for (int z = 0; z < rz; ++z) {
-        if (rows_of[z].empty()) continue;
+        if (rows_of[z].empty() && !reach[z]) continue;
         int ri = 0;
         for (int r : rows_of[z]) { a_rows.push_back(r); row_a[r] = static_cast<int>(zl.size()); row_ri[r] = ri++; }
         layer_a[z] = static_cast<int>(zl.size());
@@ -1074,6 +1107,7 @@ cudaError_t planarg_build(const SceneParams& P, const PlanarHost& base, const Pl
     Z = Zh.sub[0].plan;
     Z.seg_a = base.seg_a;
     Z.seg_b = base.seg_b;
+    Z.seg_d = base.seg_d;
     Z.tile_w = Z.tile_h = kPatch;
     Z.tiles_x = (P.res[0] + kPatch - 1) / kPatch;
     Z.tiles_y = (P.res[1] + kPatch - 1) / kPatch;

@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define DRTVAM_ABI_VERSION 8
+#define DRTVAM_ABI_VERSION 9
 #define DRTVAM_MAX_SURFACES 8
 #define DRTVAM_MAX_MESH_SURFACES 4
 
@@ -104,6 +104,11 @@ typedef struct DrtvamSceneDesc {
     int32_t surface_aware;
     int32_t sensor_kind;
     float majorant;
+    /* optional: the motion table in double precision (HOST, n_patterns row-major 3x4), or NULL.  The
+     * per-pass kernels compute in fp32 like the reference; the ONE-OFF set-up of the planar walk tables
+     * runs in double, so that the rounding of ~10 mm positions (4e-5 of a 25 um voxel per fp32 ulp) is
+     * not baked into every deposit of every pass.  NULL: the fp32 table is promoted. */
+    const double *motion_table_host_f64;
 } DrtvamSceneDesc;
 
 typedef struct DrtvamScene DrtvamScene;

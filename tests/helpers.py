@@ -69,3 +69,18 @@ def assert_jitter_parity(a, b, max_flipped_rays, voxels_per_ray=1, tol=1e-4, ban
     assert rel_rest < tol, msg
     assert rel_all < band, msg
     return flagged
+
+
+def record(test, **numbers):
+    """Appends the measured parity numbers of a GPU test to gpurun_out/parity_numbers.jsonl (evidence for
+    profiles/; a no-op when the directory is not writable)."""
+    import json
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    try:
+        os.makedirs(os.path.join(root, "gpurun_out"), exist_ok=True)
+        with open(os.path.join(root, "gpurun_out", "parity_numbers.jsonl"), "a") as f:
+            f.write(json.dumps({"test": test, **{k: (float(v) if isinstance(v, (int, float, np.floating, np.integer)) else v)
+                                                  for k, v in numbers.items()}}) + "\n")
+    except OSError:
+        pass

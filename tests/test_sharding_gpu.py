@@ -62,7 +62,9 @@ def test_z_window_equals_slab_of_full_projection(name, n, grid, workdir):
         assert f.shape[0] == z1 - z0
         assert rel_l2(f, f_full[z0:z1]) < 1e-6
         a = h.adjoint(np.ascontiguousarray(g[z0:z1]), pix[idx])
-        assert rel_l2(a, a_full[idx]) < 1e-6
+        # the adjoint adds ~10 tile partials per ray with fp32 atomics in arbitrary order (and the window
+        # regroups its layers): equal to rounding, not bit for bit
+        assert rel_l2(a, a_full[idx]) < 1e-5
     # rows that belong to no window see no layer of the film: their gradient is zero
     assert np.abs(a_full[~covered]).max(initial=0.0) == 0.0
     # back to the whole film
@@ -100,9 +102,9 @@ def test_z_window_jittered_with_sampler_index(workdir):
         h.set_film(z1 - z0, d)
         assert h.lib.drtvam_scene_plan(h.h, idx.size, spp) == 3
         flagged, rest, _ = flip_report(h.forward(p[idx], pix[idx], spp, seed), f_full[z0:z1])
-        assert flagged <= 3 * 64 and rest < 1e-6
+        assert flagged <= 3 * 64 and rest < 1e-5
         flagged, rest, _ = flip_report(h.adjoint(np.ascontiguousarray(g[z0:z1]), pix[idx], spp, seed), a_full[idx])
-        assert flagged <= 2 and rest < 1e-6
+        assert flagged <= 2 and rest < 1e-5
     # a grid whose rows straddle layers cannot be z-sharded with jitter
     scene, integ, sensor, d2, _ = build("C3", workdir, 48, n_patterns=4, grid=20, regular_sampling=False)
     h2 = Handle(d2)
@@ -159,8 +161,8 @@ def test_pinned_pixel_list(workdir):
     n1 = h.lib.drtvam_launch_count()
     f2, a2 = run(pixt, pt)
     n2 = h.lib.drtvam_launch_count()
-    assert np.array_equal(f1, f_ref) and np.array_equal(f2, f_ref)
-    assert np.array_equal(a1, a_ref) and np.array_equal(a2, a_ref)
+    assert np.array_equal(f1, f_ref) and np.array_equal(f2, f_ref)     # the patch gather is deterministic
+    assert rel_l2(a1, a_ref) < 1e-5 and rel_l2(a2, a_ref) < 1e-5       # fp32 atomics in arbitrary order
     assert n2 - n1 < n1 - n0                      # the layout check ran once
     # a permuted list of the same length, pinned: the general tracer alone serves it
     perm = torch.as_tensor(np.random.default_rng(0).permutation(pix.size), device="cuda")
@@ -172,6 +174,40 @@ def test_pinned_pixel_list(workdir):
     _lib.check(h.lib.drtvam_scene_pin_pixels(h.h, None, 0))
     f4, _ = run(pixt, pt)
     assert np.array_equal(f4, f_ref)
+
+
+def test_jittered_segment_table_is_reused_for_the_direction_pass(workdir):
+    """One L-BFGS iteration renders A p and A d with the same seed (lbfgs.py:248), with A^T g (another seed)
+    in between: for a pinned list the per-lane segment table of A p serves A d.  Same result as a handle
+    that rebuilds it, fewer launches' worth of work, and a new pin voids the table."""
+    scene, integ, sensor, d, _ = build("C4", workdir, 48, n_patterns=8, regular_sampling=False)
+    pix = pixels_np(scene)
+    p, g = random_inputs(d, pix.size, 55)
+    dvec = (np.random.default_rng(1).random(pix.size) - 0.5).astype(np.float32)
+    ref = Handle(d)
+    f_p, f_d = ref.forward(p, pix, 2, 5), ref.forward(dvec, pix, 2, 5)
+    h = Handle(d)
+    pixt = torch.as_tensor(pix.astype(np.int64), device="cuda").to(torch.int32)
+    film = torch.empty(d.film_shape(), device="cuda")
+    out = torch.empty(pix.size, device="cuda")
+    gt = torch.as_tensor(g, device="cuda")
+
+    def fwd(vec, seed):
+        v = torch.as_tensor(vec, device="cuda")
+        _lib.check(h.lib.drtvam_forward(h.h, v.data_ptr(), pixt.data_ptr(), pixt.numel(), 2, seed, 1.0, film.data_ptr(), 1,
+                                        None))
+        torch.cuda.synchronize()
+        return film.cpu().numpy()
+
+    _lib.check(h.lib.drtvam_scene_pin_pixels(h.h, pixt.data_ptr(), pixt.numel()))
+    assert rel_l2(fwd(p, 5), f_p) < 1e-5
+    _lib.check(h.lib.drtvam_adjoint(h.h, gt.data_ptr(), pixt.data_ptr(), pixt.numel(), 2, 77, 1.0, out.data_ptr(), None))
+    assert rel_l2(out.cpu().numpy(), ref.adjoint(g, pix, 2, 77)) < 1e-5
+    assert rel_l2(fwd(dvec, 5), f_d) < 1e-5             # table of the first pass, new pattern values
+    assert rel_l2(fwd(dvec, 6), ref.forward(dvec, pix, 2, 6)) < 1e-5   # another seed: rebuilt
+    # the same address pinned again (its contents may have changed): rebuilt as well
+    _lib.check(h.lib.drtvam_scene_pin_pixels(h.h, pixt.data_ptr(), pixt.numel()))
+    assert rel_l2(fwd(p, 6), ref.forward(p, pix, 2, 6)) < 1e-5
 
 
 def test_nccl_entry_points_single_rank(workdir):

@@ -5,11 +5,11 @@
 #   tools/gpu_session.sh TAG step [step ...]
 #
 # steps:
-#   tests[:EXPR]        pytest -m gpu (optionally -k EXPR)
+#   tests[:EXPR]        pytest -m gpu -x (optionally -k EXPR); testsall[:EXPR] the same without -x
 #   bench[:WL[:FLAGS]]  bench.py --workload WL (default C2) with extra flags ('+' separates flags)
 #   ref                 bench.py --impl reference
-#   launches[:WL]       ncu launch list of the timed steps (gpu__time_duration)
-#   ncu:REGEX[:WL]      ncu --set full on the kernels matching REGEX, 4 launches
+#   launches[:WL[:FLAGS]]  ncu launch list of the timed steps (gpu__time_duration)
+#   ncu:REGEX[:WL[:FLAGS]]  ncu --set full on the kernels matching REGEX, 4 launches
 #   san:TOOL:EXPR       compute-sanitizer --tool TOOL on pytest -k EXPR (ONE sanitizer tool per gpurun call)
 #   scale:N[:WL]        torchrun bench.py at N GPUs, launched as the driver does
 #   smoke               __graft_entry__.smoke()
@@ -22,6 +22,10 @@ for step in "$@"; do
     tests)
         timeout 1500 python -m pytest tests -m gpu -x -q ${a:+-k "$a"} > $O/${TAG}_tests.log 2>&1
         echo "[$TAG] tests exit $?: $(tail -1 $O/${TAG}_tests.log)";;
+    testsall)   # no -x: every failure is listed
+        timeout 2400 python -m pytest tests -m gpu -q -rf --durations=15 ${a:+-k "$a"} > $O/${TAG}_tests.log 2>&1
+        echo "[$TAG] tests exit $?: $(tail -1 $O/${TAG}_tests.log)"
+        grep -E "^FAILED|^ERROR" $O/${TAG}_tests.log | cut -c1-260 | head -40;;
     bench)
         wl=${a:-C2}; flags=${b//+/ }
         timeout 1200 python bench.py --workload $wl $flags > $O/${TAG}_bench_${wl}${b:+_${b//[^a-zA-Z0-9]/}}.json \
@@ -32,18 +36,19 @@ for step in "$@"; do
         timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > $O/${TAG}_bench_reference.json 2> $O/${TAG}_ref.err
         echo "[$TAG] reference arm exit $?";;
     launches)
-        wl=${a:-C2}
+        wl=${a:-C2}; flags=${b//+/ }
         timeout 900 ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
             --log-file $O/${TAG}_launches_${wl}_raw.csv python bench.py --workload $wl --steps 2 --warmup 3 --no-cpu-baseline \
-            > $O/${TAG}_launches_${wl}.log 2>&1
+            --no-default-sampling --no-lbfgs $flags > $O/${TAG}_launches_${wl}.log 2>&1
         echo "[$TAG] launch list exit $?"
         python tools/ncu_summary.py launches $O/${TAG}_launches_${wl}_raw.csv > $O/${TAG}_launches_${wl}.csv 2>&1
         tail -12 $O/${TAG}_launches_${wl}.csv;;
     ncu)
-        wl=${b:-C2}
+        IFS=: read -r kind a wl flags <<< "$step"
+        wl=${wl:-C2}; flags=${flags//+/ }
         timeout 900 ncu --profile-from-start off --set full --clock-control none --import-source on -k regex:"$a" -c 4 \
             -o $O/${TAG}_${wl}_full python bench.py --workload $wl --steps 1 --warmup 3 --no-cpu-baseline \
-            > $O/${TAG}_ncu_${wl}.log 2>&1
+            --no-default-sampling --no-lbfgs $flags > $O/${TAG}_ncu_${wl}.log 2>&1
         echo "[$TAG] ncu --set full exit $?"
         python tools/ncu_summary.py details $O/${TAG}_${wl}_full.ncu-rep > $O/${TAG}_${wl}_ncu_details.txt 2>&1
         grep -E "^==|gpu__time_duration|dram__bytes|issue_active" $O/${TAG}_${wl}_ncu_details.txt | head -40;;
