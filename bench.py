@@ -76,27 +76,74 @@ ATOMIC_PEAKS = {
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons during the timed region."""
+    """SM clock and throttle reasons DURING the timed region: NVML polled every few milliseconds from a
+    thread (nvidia-smi's own loop yields 2-3 samples in a 0.3 s region), nvidia-smi as the fallback."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.rows = []
+        self.index = index
+        self.samples, self.reason_bits, self.max_mhz = [], 0, None
+        self.stop_flag = threading.Event()
         self.proc = None
+        self.rows = []
+        self.mode = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nvml = pynvml
+            # CUDA_VISIBLE_DEVICES may renumber: resolve through the PCI bus id of the torch device
+            try:
+                import torch
+                bus = torch.cuda.get_device_properties(index).pci_bus_id
+                dom = torch.cuda.get_device_properties(index).pci_domain_id
+                dev_id = torch.cuda.get_device_properties(index).pci_device_id
+                self.handle = pynvml.nvmlDeviceGetHandleByPciBusId(f"{dom:08X}:{bus:02X}:{dev_id:02X}.0")
+            except Exception:
+                self.handle = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))
+            self.mode = "nvml"
+            self.thread = threading.Thread(target=self._poll, daemon=True)
+            self.thread.start()
+            return
+        except Exception:
+            self.mode = None
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "50", "-i", str(index)],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.mode = "nvidia-smi"
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
         except Exception:
             self.proc = None
+
+    def _poll(self):
+        n = self.nvml
+        while not self.stop_flag.is_set():
+            try:
+                self.samples.append(float(n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM)))
+                self.reason_bits |= int(n.nvmlDeviceGetCurrentClocksEventReasons(self.handle))
+            except Exception:
+                try:
+                    self.reason_bits |= int(n.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle))
+                except Exception:
+                    pass
+            time.sleep(0.004)
 
     def _read(self):
         for line in self.proc.stdout:
             self.rows.append(line.strip())
 
     def stop(self):
+        if self.mode == "nvml":
+            self.stop_flag.set()
+            self.thread.join(timeout=2)
+            sm = sorted(self.samples)
+            bits = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
+            reasons = sorted(k for k, b in bits.items() if self.reason_bits & b)
+            return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.max_mhz, "reasons": reasons,
+                    "samples": len(sm), "source": "nvml, 4 ms period, inside the timed region"}
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -120,7 +167,7 @@ class ClockSampler:
                     reasons.add(n)
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
-                "samples": len(sm)}
+                "samples": len(sm), "source": "nvidia-smi -lms 50"}
 
 
 def measured_peaks():
@@ -296,20 +343,27 @@ def main():
             target = discretize(scene, sensor=sensor)
         return scene, integ, sensor, desc_full, n_total, target
 
-    def verify_multi_gpu(scene, integ, sensor, n_total, c_spp):
+    def verify_multi_gpu(scene, integ, sensor, n_total, c_spp, target):
         """N-rank result == 1-rank result, on hardware, before the timed loop: every rank draws the SAME full
-        pattern vector and dose gradient; rank 0 projects them unsharded (no collective), then all ranks
-        project their shards; the reduced dose and the concatenated pattern gradient must match."""
+        pattern vector; rank 0 projects it unsharded (no collective), forms the dose gradient of the
+        thresholded loss there and back-projects it; the gradient is broadcast, then all ranks project
+        their shards; the reduced dose and the concatenated pattern gradient must match."""
         gen = torch.Generator(device=dev).manual_seed(4242)
         p_full = torch.rand(n_total, device=dev, generator=gen) * 2e-3 + 1e-4
         film_shape = tuple(sensor.film().shape)
-        g_full = torch.randn(film_shape, device=dev, generator=gen)
+        g_full = torch.zeros(film_shape, device=dev)
         ref = {}
         if rank == 0:
+            scene.projector.active_data = p_full
             with torch.no_grad():
-                scene.projector.active_data = p_full
-                ref["dose"] = integ._project(scene, sensor, 77, c_spp, p_full).clone()
+                dose = integ._project(scene, sensor, 77, c_spp, p_full).clone()
+            x = dose.clone().requires_grad_(True)
+            ThresholdedLoss({})(x, target, p_full).backward()
+            g_full = x.grad.detach().clone()
+            with torch.no_grad():
+                ref["dose"] = dose
                 ref["grad"] = integ.render_backward(scene, None, g_full, sensor, 77, c_spp).clone()
+        dist.broadcast(g_full, 0)
         return p_full, g_full, ref
 
     def measure(c, steps, warmup, headline):
@@ -319,7 +373,7 @@ def main():
         check = None
         verify = world > 1 and headline and not args.no_verify
         if verify:
-            p_full, g_full, ref = verify_multi_gpu(scene, integ, sensor, n_total, c_spp)
+            p_full, g_full, ref = verify_multi_gpu(scene, integ, sensor, n_total, c_spp, target)
         partition = "single"
         if world > 1:
             partition = scene.shard(rank, world, partition=args.partition, integrator=integ, sensor=sensor)[2]
@@ -343,7 +397,9 @@ def main():
                 if rank == 0:
                     check = {"partition": partition, "ranks": world,
                              "dose_rel_l2_vs_1_rank": rel_l2(dose_n, ref["dose"]),
-                             "grad_rel_l2_vs_1_rank": rel_l2(grad_n, ref["grad"]), "bound": 1e-6}
+                             "grad_rel_l2_vs_1_rank": rel_l2(grad_n, ref["grad"]), "bound": 1e-6,
+                             "inputs": "same seeded full pattern vector on every rank; dose gradient = that of the "
+                                       "thresholded loss at the 1-rank dose, broadcast from rank 0"}
                     check["ok"] = bool(check["dose_rel_l2_vs_1_rank"] <= 1e-6 and check["grad_rel_l2_vs_1_rank"] <= 1e-6)
             del p_full, g_full, ref, dose_n, grad_n
             torch.cuda.empty_cache()

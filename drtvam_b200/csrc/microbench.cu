@@ -127,9 +127,57 @@ float time_launches(cudaEvent_t a, cudaEvent_t b) {
     return ms;
 }
 
+// Legacy tensor path: mma.sync.aligned.m16n8k8 tf32 (SASS HMMA), kIlp independent accumulator tiles per warp.
+// The question it answers (patch gather as a GEMM): how many of these can a B200 SM retire?
+template <int kIlp>
+__global__ void mma_tf32_kernel(float* out, int iters) {
+    float c[kIlp][4];
+#pragma unroll
+    for (int i = 0; i < kIlp; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) c[i][j] = 0.f;
+    uint32_t a[4], b[2];
+    const uint32_t lane = threadIdx.x & 31;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) a[j] = __float_as_uint(1.0f + 0.125f * ((lane + j) & 7));
+    b[0] = __float_as_uint(0.5f + 0.0625f * (lane & 3));
+    b[1] = __float_as_uint(0.25f);
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int i = 0; i < kIlp; ++i)
+            asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                         : "+f"(c[i][0]), "+f"(c[i][1]), "+f"(c[i][2]), "+f"(c[i][3])
+                         : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+    }
+    float acc = 0.f;
+#pragma unroll
+    for (int i = 0; i < kIlp; ++i) acc += c[i][0] + c[i][1] + c[i][2] + c[i][3];
+    if (acc == 123.456f) out[0] = acc;
+}
+
 }  // namespace
 
 extern "C" {
+
+// mma.sync m16n8k8 tf32: returns dense TFLOP/s (2 * 16 * 8 * 8 flop per instruction and warp)
+double drtvam_mb_mma_tf32(float* out, int ilp, int iters, int blocks, int threads) {
+    cudaEvent_t a, b;
+    cudaEventCreate(&a); cudaEventCreate(&b);
+    for (int rep = 0; rep < 2; ++rep) {
+        cudaEventRecord(a);
+        if (ilp == 1) mma_tf32_kernel<1><<<blocks, threads>>>(out, iters);
+        else if (ilp == 2) mma_tf32_kernel<2><<<blocks, threads>>>(out, iters);
+        else if (ilp == 4) mma_tf32_kernel<4><<<blocks, threads>>>(out, iters);
+        else if (ilp == 8) mma_tf32_kernel<8><<<blocks, threads>>>(out, iters);
+        else mma_tf32_kernel<16><<<blocks, threads>>>(out, iters);
+        cudaEventRecord(b);
+    }
+    if (cudaGetLastError() != cudaSuccess) return -1.0;
+    const float ms = time_launches(a, b);
+    cudaEventDestroy(a); cudaEventDestroy(b);
+    const double mmas = static_cast<double>(blocks) * (threads / 32) * iters * (ilp > 8 ? 16 : ilp);
+    return mmas * 2048.0 / (ms * 1e-3) * 1e-12;
+}
 
 // Returns giga-adds per second (fp32 adds landed in memory), or < 0 on error.
 // buf must hold (n_mask + 1 + 32*stride) floats.

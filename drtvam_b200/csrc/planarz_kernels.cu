@@ -836,6 +836,183 @@ planarg_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
     }
 }
 
+// ---- the patch gather on the tensor cores -------------------------------------------------------
+// acc[16 voxels][layers] += coef[16 voxels][8 segments] . x[8 segments][layers], summed over the ~2 440
+// segments that cross a patch, IS a matrix product (M = 16 voxels of the patch, K = the segments of a
+// chunk, N = the layers, the rows of B gathered by ray index).  Here it runs as
+// mma.sync.aligned.m16n8k8 tf32 (SASS HMMA: 276 dense TFLOP/s measured on this B200,
+// profiles/r02g_microbench.json), with both operands split into a tf32 head and tail and three products
+// per tile (hi.hi + lo.hi + hi.lo, error ~2^-20 per product) so that the 1e-4 bound holds for signed
+// pattern vectors too.  Same staging as the FFMA kernel: TMA bulk copies on mbarriers, one chunk ahead.
+//
+// Fragment layout (PTX ISA, m16n8k8 .tf32): with g = lane / 4, q = lane % 4
+//   A (16 x 8):  a0 = A[g][q]  a1 = A[g + 8][q]  a2 = A[g][q + 4]  a3 = A[g + 8][q + 4]
+//   B ( 8 x 8):  b0 = B[q][g]  b1 = B[q + 4][g]
+//   C (16 x 8):  c0 = C[g][2q] c1 = C[g][2q + 1] c2 = C[g + 8][2q] c3 = C[g + 8][2q + 1]
+// Column n of n-tile t stands for layer NT * n + t of the block, so the NT values a lane needs of one
+// pattern line are contiguous (LDS.128) and the lines sit 8 * NT + 4 floats apart (no bank conflicts).
+__device__ __forceinline__ void split_tf32(float x, uint32_t& hi, uint32_t& lo) {
+    hi = __float_as_uint(x) & 0xffffe000u;
+    lo = __float_as_uint(x - __uint_as_float(hi));
+}
+
+__device__ __forceinline__ void mma_tf32(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+constexpr int gm_line(int NT) { return 8 * NT + 4; }   // floats between two staged pattern lines
+constexpr int gm_buf_floats(int NT) { return kGChunk * gm_line(NT) + kGChunk * 16 + kGChunk; }
+constexpr size_t gm_smem_bytes(int NT) {
+    return (sizeof(float) * 2 * gm_buf_floats(NT) + 2 * sizeof(uint64_t)) * kGWarpsX * kGWarpsY;
+}
+
+template <int NT>
+__global__ void __launch_bounds__(32 * kGWarpsX * kGWarpsY, 2)
+planarg_mma_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ PlanarZPlan Z,
+                   const float4* __restrict__ coef, const int* __restrict__ ray, const float* __restrict__ in,
+                   float* __restrict__ out, const uint32_t* __restrict__ active_pixels, uint64_t n_active,
+                   float ray_weight, const int* __restrict__ gate, int a_begin, int fresh) {
+    extern __shared__ __align__(16) float g_smem[];
+    if (*gate != 0) return;
+    constexpr int kLayers = 8 * NT, kLine = gm_line(NT), kBuf = gm_buf_floats(NT);
+    static_assert(kGChunk == 8, "one chunk is one k-step of the m16n8k8 product");
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int regions_x = (Z.tiles_x + kGWarpsX - 1) / kGWarpsX;
+    const int px = (blockIdx.x % regions_x) * kGWarpsX + (warp % kGWarpsX);
+    const int py = (blockIdx.x / regions_x) * kGWarpsY + (warp / kGWarpsX);
+    if (px >= Z.tiles_x || py >= Z.tiles_y) return;
+    const int tile_id = py * Z.tiles_x + px;
+    const int a_base = a_begin + blockIdx.y * kLayers;
+    float* buf = g_smem + warp * (2 * kBuf);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(g_smem + kGWarpsX * kGWarpsY * 2 * kBuf) + 2 * warp;
+    if (lane == 0) {
+        mbar_init(bars, 1);
+        mbar_init(bars + 1, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+
+    int k0, nk;
+    call_angles(P, active_pixels, n_active, k0, nk);
+    const int* __restrict__ off = Z.tile_off + static_cast<size_t>(tile_id) * (P.n_patterns + 1);
+    const int ebase = __ldg(Z.tile_ebase + tile_id);
+    const int g0 = ebase + __ldg(off + k0), g1 = ebase + __ldg(off + k0 + nk);
+    const float* __restrict__ xb = in + a_base - static_cast<long long>(k0) * P.res_x * Z.nz_pad;
+    const int n_chunks = (g1 - g0 + kGChunk - 1) / kGChunk;
+
+    float acc[NT][4];
+#pragma unroll
+    for (int t = 0; t < NT; ++t)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) acc[t][i] = 0.f;
+
+    auto load_rays = [&](int c) {
+        const int g = g0 + c * kGChunk + (lane & (kGChunk - 1));
+        return (c < n_chunks && g < g1) ? __ldg(ray + g) : 0;
+    };
+    // lane j < 8 copies the pattern line of pair j (8 * NT layers), lane 8 the coefficient blocks of the chunk
+    auto issue = [&](int c, int rl) {
+        float* b = buf + (c & 1) * kBuf;
+        uint64_t* bar = bars + (c & 1);
+        const int g = g0 + c * kGChunk;
+        const int n_here = min(kGChunk, g1 - g);
+        const bool wants = lane < kGChunk && (rl >> 24) != 0;
+        const unsigned lines = __popc(__ballot_sync(0xffffffffu, wants));
+        if (lane == 0) mbar_expect_tx(bar, lines * (4u * kLayers) + 64u * n_here);
+        __syncwarp();
+        if (wants) bulk_g2s(b + lane * kLine, xb + static_cast<size_t>(rl & 0xffffff) * Z.nz_pad, 4u * kLayers, bar);
+        if (lane == kGChunk) bulk_g2s(b + kGChunk * kLine, coef + 4 * static_cast<size_t>(g), 64u * n_here, bar);
+        if (lane < kGChunk) reinterpret_cast<int*>(b)[kGChunk * kLine + kGChunk * 16 + lane] = rl;
+    };
+
+    const int gq = lane >> 2, q = lane & 3;
+    int rl_next = load_rays(0);
+    if (n_chunks > 0) issue(0, rl_next);
+    rl_next = load_rays(1);
+    for (int c = 0; c < n_chunks; ++c) {
+        if (c + 1 < n_chunks) {
+            issue(c + 1, rl_next);
+            rl_next = load_rays(c + 2);
+        }
+        mbar_wait(bars + (c & 1), (c >> 1) & 1);
+        __syncwarp();
+        const float* b = buf + (c & 1) * kBuf;
+        const int n_here = min(kGChunk, g1 - (g0 + c * kGChunk));
+        const int* rw = reinterpret_cast<const int*>(b) + kGChunk * kLine + kGChunk * 16;
+        // pairs beyond the end of the list, and pairs that touch nothing (their line is not fetched),
+        // enter with zero coefficients: whatever their stale line holds is multiplied by 0
+        const bool v_lo = q < n_here && (rw[q] >> 24) != 0, v_hi = q + 4 < n_here && (rw[q + 4] >> 24) != 0;
+        const float* cf = b + kGChunk * kLine;
+        const float a_f[4] = {v_lo ? cf[16 * q + gq] : 0.f, v_lo ? cf[16 * q + gq + 8] : 0.f,
+                              v_hi ? cf[16 * (q + 4) + gq] : 0.f, v_hi ? cf[16 * (q + 4) + gq + 8] : 0.f};
+        uint32_t a_hi[4], a_lo[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) split_tf32(a_f[i], a_hi[i], a_lo[i]);
+        const float* x_lo = b + q * kLine + gq * NT;          // layers NT * gq + t of pair q
+        const float* x_hi = b + (q + 4) * kLine + gq * NT;    // ... of pair q + 4
+        if constexpr (NT >= 4) {
+#pragma unroll
+            for (int t4 = 0; t4 < NT / 4; ++t4) {
+                float4 xl = *reinterpret_cast<const float4*>(x_lo + 4 * t4);
+                float4 xh = *reinterpret_cast<const float4*>(x_hi + 4 * t4);
+                if (!v_lo) xl = make_float4(0.f, 0.f, 0.f, 0.f);   // a stale line may hold inf / nan
+                if (!v_hi) xh = make_float4(0.f, 0.f, 0.f, 0.f);
+                const float bl[4] = {xl.x, xl.y, xl.z, xl.w}, bh[4] = {xh.x, xh.y, xh.z, xh.w};
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    uint32_t b0h, b0l, b1h, b1l;
+                    split_tf32(bl[i], b0h, b0l);
+                    split_tf32(bh[i], b1h, b1l);
+                    mma_tf32(acc[4 * t4 + i], a_hi, b0h, b1h);
+                    mma_tf32(acc[4 * t4 + i], a_lo, b0h, b1h);
+                    mma_tf32(acc[4 * t4 + i], a_hi, b0l, b1l);
+                }
+            }
+        } else {
+#pragma unroll
+            for (int t = 0; t < NT; ++t) {
+                const float xl = v_lo ? x_lo[t] : 0.f, xh = v_hi ? x_hi[t] : 0.f;
+                uint32_t b0h, b0l, b1h, b1l;
+                split_tf32(xl, b0h, b0l);
+                split_tf32(xh, b1h, b1l);
+                mma_tf32(acc[t], a_hi, b0h, b1h);
+                mma_tf32(acc[t], a_lo, b0h, b1h);
+                mma_tf32(acc[t], a_hi, b0l, b1l);
+            }
+        }
+        __syncwarp();  // the buffer is refilled by the issue of the next iteration
+    }
+
+    // lane (g, q) holds voxels g and g + 8 of the patch (row g / 4 resp. g / 4 + 2, column g % 4) for the
+    // layers NT * 2q + t and NT * (2q + 1) + t; the four lanes of consecutive g write 16 contiguous bytes
+    const int x0 = px * kPatch, y0 = py * kPatch;
+    const size_t layer_elems = static_cast<size_t>(P.res[0]) * P.res[1];
+    const int xx = x0 + (gq & 3), yy0 = y0 + (gq >> 2), yy1 = yy0 + 2;
+    if (xx < P.res[0]) {
+#pragma unroll
+        for (int t = 0; t < NT; ++t) {
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int z = __ldg(Z.zl + a_base + NT * (2 * q + h) + t);
+                if (z < 0) continue;
+                float* o = out + z * layer_elems + xx;
+                if (yy0 < P.res[1]) {
+                    const float v = acc[t][h] * ray_weight;
+                    float* d = o + static_cast<size_t>(yy0) * P.res[0];
+                    if (fresh) *d = v; else if (v != 0.f) *d += v;
+                }
+                if (yy1 < P.res[1]) {
+                    const float v = acc[t][2 + h] * ray_weight;
+                    float* d = o + static_cast<size_t>(yy1) * P.res[0];
+                    if (fresh) *d = v; else if (v != 0.f) *d += v;
+                }
+            }
+        }
+    }
+}
+
 }  // namespace
 
 #define PZ_TRY(expr)                      \
@@ -1084,6 +1261,8 @@ cudaError_t launch_planarz_adjoint(const SceneParams& P, PlanarZHost& H, const i
 
 template <int kL>
 static cudaError_t g_set_smem() {
+    PZ_TRY(cudaFuncSetAttribute(planarg_mma_kernel<4 * kL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                static_cast<int>(gm_smem_bytes(4 * kL))));
     return cudaFuncSetAttribute(planarg_kernel<kL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 static_cast<int>(g_smem_bytes(kL)));
 }
@@ -1208,11 +1387,23 @@ cudaError_t launch_planarg_forward(const SceneParams& P, PlanarZHost& H, PlanarG
     const PlanarZPlan& Z = G.plan;
     const int regions = ((Z.tiles_x + kGWarpsX - 1) / kGWarpsX) * ((Z.tiles_y + kGWarpsY - 1) / kGWarpsY);
     constexpr int threads = 32 * kGWarpsX * kGWarpsY;
+    // DRTVAM_PLANAR_FORWARD=ffma keeps the products on the FMA pipe (A/B measurements)
+    static const bool use_mma = !(std::getenv("DRTVAM_PLANAR_FORWARD") && std::strcmp(std::getenv("DRTVAM_PLANAR_FORWARD"), "ffma") == 0);
     for (int i = 0; i < H.n_sub; ++i) {
         const PlanarZSub& S = H.sub[i];
         const dim3 grid(regions, S.n_blocks);
         const int kL = S.plan.lanes_l, a_begin = S.plan.a_begin;
-        if (kL == 1)
+        if (use_mma) {
+            if (kL == 1)
+                planarg_mma_kernel<4><<<grid, threads, gm_smem_bytes(4), stream>>>(P, Z, G.coef, G.ray, H.scratch, film,
+                                                                                  active_pixels, n_active, ray_weight, gate, a_begin, fresh ? 1 : 0);
+            else if (kL == 2)
+                planarg_mma_kernel<8><<<grid, threads, gm_smem_bytes(8), stream>>>(P, Z, G.coef, G.ray, H.scratch, film,
+                                                                                  active_pixels, n_active, ray_weight, gate, a_begin, fresh ? 1 : 0);
+            else
+                planarg_mma_kernel<16><<<grid, threads, gm_smem_bytes(16), stream>>>(P, Z, G.coef, G.ray, H.scratch, film,
+                                                                                    active_pixels, n_active, ray_weight, gate, a_begin, fresh ? 1 : 0);
+        } else if (kL == 1)
             planarg_kernel<1><<<grid, threads, g_smem_bytes(1), stream>>>(P, Z, G.coef, G.ray, H.scratch, film,
                                                                          active_pixels, n_active, ray_weight, gate, a_begin, fresh ? 1 : 0);
         else if (kL == 2)

@@ -45,6 +45,13 @@ def main():
             for threads in (256, 1024):
                 g = lib.drtvam_mb_smem2(o.data_ptr(), mode, 8192, 148 * (4 if threads == 256 else 2), threads, share)
                 out[f"smem2_{name}_share{share}_t{threads}_Gops"] = round(g, 2)
+    # legacy tensor path (mma.sync m16n8k8 tf32 -> HMMA): dense TFLOP/s by warps per SM and accumulator tiles per warp
+    lib.drtvam_mb_mma_tf32.restype = C.c_double
+    lib.drtvam_mb_mma_tf32.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int]
+    for threads in (128, 256, 512, 1024):
+        for ilp in (1, 4, 16):
+            t = lib.drtvam_mb_mma_tf32(o.data_ptr(), ilp, 4096, 148, threads)
+            out[f"mma_sync_tf32_m16n8k8_w{threads // 32}_ilp{ilp}_TFLOPs"] = round(t, 1)
     torch.cuda.synchronize()
     print(json.dumps(out))
 
