@@ -70,6 +70,10 @@ struct PlanarZSub {      // a run of z-blocks that all hold 32 * lanes_l active 
     int* tile_clo = nullptr;
     int* tile_ebase = nullptr;
     float4* entries = nullptr;
+    // visit lists of the adjoint (planarv_kernel): per entry a head {weight, start | n, offset} and, from
+    // `offset` on, the n deposit factors of its voxels with the step direction in the lowest mantissa bit
+    float4* vhead = nullptr;
+    float* vde = nullptr;
     size_t smem_bytes = 0;
     int n_blocks = 0;
 };

@@ -46,6 +46,8 @@ struct PlanarZPlan {
     const int* tile_clo;     // [n_tiles][n_patterns]
     const int* tile_ebase;   // [n_tiles + 1] first walk entry of every tile
     const float4* entries;   // 2 x float4 per (tile, angle, column): the clipped walk, ready to march
+    const float4* vhead;     // visit lists of the adjoint: head per entry ...
+    const float* vde;        // ... and the deposit factors of its voxels
     const int* zl;           // [nz_pad] film layer of active layer a (-1 = padding)
     const int* a_row_begin;  // [nz + 1] CSR over a_rows: DMD rows that deposit in active layer a
     const int* a_rows;

@@ -533,6 +533,166 @@ planarz_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
 }
 
 // ---------------------------------------------------------------------------
+// Visit lists: the adjoint without a DDA.  The walk of a (tile, angle, column) entry is the same in every
+// pass, so the set-up also writes it out: the deposit factor 2^-u_in (1 - 2^-(u_out - u_in)) of every voxel
+// the segment crosses in the tile - evaluated without cancellation (expm.cuh) - with the direction of the
+// step that follows (0 = across an x boundary, 1 = across a y boundary) in the lowest mantissa bit.  The
+// gather kernel then spends, per voxel and 32 * kL layers, one shuffle, one predicate and one address
+// add next to the shared-memory load and the FMAs, instead of a compare, an ex2.approx, two subtractions,
+// a counter and a select: 8 instructions instead of 25 (profiles/r02i_*: the DDA form was issue bound at
+// 85 %).  3.6e8 bytes at C2, streamed once per z-block.
+// ---------------------------------------------------------------------------
+constexpr int kVisitMax = 64;   // a head carries no more; longer walks keep the DDA kernel
+
+__global__ void __launch_bounds__(256)
+vcount_kernel(const float4* __restrict__ entries, int total, int* __restrict__ count) {
+    const int e = blockIdx.x * 256 + threadIdx.x;
+    if (e > total) return;
+    int n = 0;
+    if (e < total) {
+        const unsigned bits = __float_as_uint(__ldg(entries + 2 * static_cast<size_t>(e) + 1).w);
+        if (bits & kEntryValid) n = static_cast<int>(((bits >> 14) & 127) + ((bits >> 21) & 127) + 1);
+    }
+    count[e] = (n + 3) & ~3;   // 16-byte aligned lists
+}
+
+__global__ void __launch_bounds__(256)
+vfill_kernel(const float4* __restrict__ entries, const int* __restrict__ voff, int total, int tw, float4* __restrict__ vhead,
+             float* __restrict__ vde, int* __restrict__ too_long) {
+    const int e = blockIdx.x * 256 + threadIdx.x;
+    if (e >= total) return;
+    const float4 e0 = __ldg(entries + 2 * static_cast<size_t>(e)), e1 = __ldg(entries + 2 * static_cast<size_t>(e) + 1);
+    const unsigned bits = __float_as_uint(e1.w);
+    const int off = __ldg(voff + e);
+    if (!(bits & kEntryValid)) {
+        vhead[e] = make_float4(0.f, __int_as_float(0), __int_as_float(off), 0.f);
+        return;
+    }
+    const int ix = bits & 127, iy = (bits >> 7) & 127;
+    int nx = (bits >> 14) & 127, ny = (bits >> 21) & 127;
+    const int n = nx + ny + 1;
+    if (n > kVisitMax) atomicOr(too_long, 1);
+    float ux = e0.z, uy = e0.w;
+    const float ax = e1.x, ay = e1.y, bx = e0.z, by = e0.w;
+    float fx = 0.f, fy = 0.f, u_prev = 0.f;
+    for (int i = 0; i < n; ++i) {
+        float u_out = e0.y;
+        unsigned step_y = 0;
+        if (i < n - 1) {
+            if (ux <= uy) {
+                u_out = ux; fx += 1.f;
+                ux = fmaf(fx, ax, bx);
+                if (--nx == 0) ux = INFINITY;
+            } else {
+                u_out = uy; fy += 1.f; step_y = 1;
+                uy = fmaf(fy, ay, by);
+                if (--ny == 0) uy = INFINITY;
+            }
+        }
+        const float de = exp2f(-u_prev) * one_minus_ex2_neg(fmaxf(u_out - u_prev, 0.f));
+        vde[off + i] = __uint_as_float((__float_as_uint(de) & ~1u) | step_y);
+        u_prev = u_out;
+    }
+    // start voxel | n << 16 | x step negative << 30 | y step negative << 31
+    const unsigned packed = static_cast<unsigned>(iy * tw + ix) | (static_cast<unsigned>(n) << 16) | (bits & (3u << 28)) << 2;
+    vhead[e] = make_float4(e0.x, __uint_as_float(packed), __int_as_float(off), 0.f);
+}
+
+// in = dL (film layout), out = gT.  Same CTA / tile / z-block structure as planarz_kernel<kGather>.
+template <int kL>
+__global__ void __launch_bounds__(kZThreads, 1)
+planarv_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ PlanarZPlan Z,
+               const float* __restrict__ in, float* __restrict__ out, const uint32_t* __restrict__ active_pixels,
+               uint64_t n_active, float ray_weight, const int* __restrict__ gate) {
+    extern __shared__ __align__(16) float tile[];
+    if (*gate != 0) return;
+    const int tile_id = blockIdx.x, zb = blockIdx.y, group = blockIdx.z;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int x0 = (tile_id % Z.tiles_x) * Z.tile_w, y0 = (tile_id / Z.tiles_x) * Z.tile_h;
+    const int w = min(Z.tile_w, P.res[0] - x0), h = min(Z.tile_h, P.res[1] - y0);
+    const int tw = Z.tile_w;
+    constexpr int kVox = kZLaneStride * kL;
+    const int a_base = Z.a_begin + zb * (32 * kL);
+    const size_t layer_elems = static_cast<size_t>(P.res[0]) * P.res[1];
+
+    // ---- stage the dose-gradient tile (as planarz_kernel)
+    {
+        const int per_layer = h * w;
+        for (int i = threadIdx.x; i < kL * 32 * per_layer; i += kZThreads) {
+            const int al = i / per_layer, rem = i - al * per_layer;
+            const int yy = rem / w, xx = rem - yy * w;
+            const int z = __ldg(Z.zl + a_base + al);
+            float v = 0.f;
+            if (z >= 0) v = __ldg(in + z * layer_elems + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx));
+            tile[(yy * tw + xx) * kVox + (al & 31) * kL + (al >> 5)] = v;
+        }
+    }
+    __syncthreads();
+
+    int k0, nk;
+    call_angles(P, active_pixels, n_active, k0, nk);
+    const int ka = k0 + static_cast<int>(static_cast<long long>(nk) * group / Z.groups);
+    const int kb = k0 + static_cast<int>(static_cast<long long>(nk) * (group + 1) / Z.groups);
+    const int* __restrict__ off = Z.tile_off + static_cast<size_t>(tile_id) * (P.n_patterns + 1);
+    const int* __restrict__ clo = Z.tile_clo + static_cast<size_t>(tile_id) * P.n_patterns;
+    const size_t ebase = static_cast<size_t>(__ldg(Z.tile_ebase + tile_id));
+    const float4* __restrict__ vhead = Z.vhead + ebase;
+    const uint32_t tile_s = static_cast<uint32_t>(__cvta_generic_to_shared(tile)) + 4u * kL * lane;
+    const int sxb = 4 * kVox, syb = 4 * kVox * tw;
+
+    const int f_base = __ldg(off + ka), total = __ldg(off + kb) - f_base;
+    int k = ka;
+    // the head and the list of the NEXT entry are fetched while the current one is walked
+    float4 head = make_float4(0.f, 0.f, 0.f, 0.f);
+    float d_lo = 0.f, d_hi = 0.f;
+    auto fetch = [&](int f, float4& hd, float& lo, float& hi) {
+        hd = make_float4(0.f, 0.f, 0.f, 0.f);
+        lo = hi = 0.f;
+        if (f < total) {
+            hd = __ldg(vhead + f + f_base);
+            const int n = (__float_as_uint(hd.y) >> 16) & 0x7f;
+            const float* lst = Z.vde + __float_as_int(hd.z);
+            if (lane < n) lo = __ldg(lst + lane);
+            if (lane + 32 < n) hi = __ldg(lst + lane + 32);
+        }
+    };
+    fetch(warp, head, d_lo, d_hi);
+    for (int f = warp; f < total; f += kZWarps) {
+        const float4 hd = head;
+        const float my_lo = d_lo, my_hi = d_hi;
+        fetch(f + kZWarps, head, d_lo, d_hi);
+        const unsigned packed = __float_as_uint(hd.y);
+        const int n = (packed >> 16) & 0x7f;
+        if (n == 0) continue;
+        const int g = f + f_base;
+        while (__ldg(off + k + 1) <= g) ++k;
+        const int c = __ldg(clo + k) + (g - __ldg(off + k));
+        const size_t tbase = (static_cast<size_t>(k - k0) * P.res_x + c) * Z.nz_pad + a_base + lane;
+        const int sx = (packed & (1u << 30)) ? -sxb : sxb, sy = (packed & (1u << 31)) ? -syb : syb;
+        uint32_t addr = tile_s + static_cast<uint32_t>((packed & 0xffffu) * (4 * kVox));
+        float acc[kL];
+#pragma unroll
+        for (int m = 0; m < kL; ++m) acc[m] = 0.f;
+        const int n_lo = min(n, 32);
+#pragma unroll 4
+        for (int i = 0; i < n_lo; ++i) {
+            const float de = __shfl_sync(0xffffffffu, my_lo, i);
+            z_gather<kL>(addr, acc, de);
+            addr += (__float_as_uint(de) & 1u) ? sy : sx;
+        }
+        for (int i = 32; i < n; ++i) {
+            const float de = __shfl_sync(0xffffffffu, my_hi, i - 32);
+            z_gather<kL>(addr, acc, de);
+            addr += (__float_as_uint(de) & 1u) ? sy : sx;
+        }
+        const float wray = ray_weight * hd.x;
+#pragma unroll
+        for (int m = 0; m < kL; ++m)
+            if (acc[m] != 0.f) atomicAdd(out + tbase + 32 * m, acc[m] * wray);
+    }
+}
+
+// ---------------------------------------------------------------------------
 // Patch-gather forward.  The scatter kernel above spends its time on the
 // read-modify-write of the shared tile (12 shared wavefronts and ~50 issue slots
 // per 128 visits, profiles/r01a_planarz_ncu_details.txt).  Here a warp OWNS a
@@ -960,6 +1120,8 @@ planarg_mma_kernel(const __grid_constant__ SceneParams P, const __grid_constant_
                 if (!v_lo) xl = make_float4(0.f, 0.f, 0.f, 0.f);   // a stale line may hold inf / nan
                 if (!v_hi) xh = make_float4(0.f, 0.f, 0.f, 0.f);
                 const float bl[4] = {xl.x, xl.y, xl.z, xl.w}, bh[4] = {xh.x, xh.y, xh.z, xh.w};
+                // (issuing the three products of a tile four tiles apart, and a non-volatile asm that lets
+                // ptxas interleave them, were measured: 6.50 ms against 6.08 ms for this order, r02j)
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
                     uint32_t b0h, b0l, b1h, b1l;
@@ -1023,7 +1185,7 @@ planarg_mma_kernel(const __grid_constant__ SceneParams P, const __grid_constant_
 
 void planarz_release(PlanarZHost& H) {
     for (PlanarZSub& S : H.sub) {
-        void* ptrs[] = {S.tile_off, S.tile_clo, S.tile_ebase, S.entries};
+        void* ptrs[] = {S.tile_off, S.tile_clo, S.tile_ebase, S.entries, S.vhead, S.vde};
         for (void* p : ptrs)
             if (p) cudaFree(p);
     }
@@ -1051,6 +1213,7 @@ template <int kL>
 static cudaError_t z_set_smem(size_t bytes) {
     PZ_TRY(cudaFuncSetAttribute(planarz_kernel<kScatter, kL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 static_cast<int>(bytes)));
+    PZ_TRY(cudaFuncSetAttribute(planarv_kernel<kL>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(bytes)));
     return cudaFuncSetAttribute(planarz_kernel<kGather, kL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 static_cast<int>(bytes));
 }
@@ -1094,6 +1257,56 @@ static cudaError_t z_build_sub(const SceneParams& P, const PlanarHost& base, con
         zsetup_kernel<<<static_cast<unsigned>((total + 255) / 256), 256>>>(P, Z, S.entries, static_cast<int>(total));
         count_launch();
         PZ_TRY(cudaGetLastError());
+    }
+    // visit lists of the adjoint (left out when they would not fit comfortably, or on request)
+    const char* env = std::getenv("DRTVAM_PLANAR_ADJOINT");
+    if (total > 0 && !(env && std::strcmp(env, "dda") == 0)) {
+        int *count = nullptr, *voff = nullptr, *flag = nullptr;
+        void* tmp = nullptr;
+        auto run = [&]() -> cudaError_t {
+            const int n1 = static_cast<int>(total) + 1;
+            PZ_TRY(cudaMalloc(&count, sizeof(int) * n1));
+            PZ_TRY(cudaMalloc(&voff, sizeof(int) * n1));
+            PZ_TRY(cudaMalloc(&flag, sizeof(int)));
+            PZ_TRY(cudaMemset(flag, 0, sizeof(int)));
+            vcount_kernel<<<(n1 + 255) / 256, 256>>>(S.entries, static_cast<int>(total), count);
+            count_launch();
+            size_t tmp_bytes = 0;
+            PZ_TRY(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, count, voff, n1));
+            PZ_TRY(cudaMalloc(&tmp, tmp_bytes));
+            PZ_TRY(cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, count, voff, n1));
+            count_launch();
+            int visits = 0;
+            PZ_TRY(cudaMemcpy(&visits, voff + total, sizeof(int), cudaMemcpyDeviceToHost));
+            size_t free_b = 0, total_b = 0;
+            PZ_TRY(cudaMemGetInfo(&free_b, &total_b));
+            if (visits <= 0 || (sizeof(float) * static_cast<size_t>(visits) + sizeof(float4) * total) > free_b / 4) return cudaSuccess;
+            PZ_TRY(cudaMalloc(&S.vhead, sizeof(float4) * static_cast<size_t>(total)));
+            PZ_TRY(cudaMalloc(&S.vde, sizeof(float) * static_cast<size_t>(visits)));
+            PZ_TRY(cudaMemset(S.vde, 0, sizeof(float) * static_cast<size_t>(visits)));
+            vfill_kernel<<<static_cast<unsigned>((total + 255) / 256), 256>>>(S.entries, voff, static_cast<int>(total), Z.tile_w,
+                                                                              S.vhead, S.vde, flag);
+            count_launch();
+            PZ_TRY(cudaGetLastError());
+            int too_long = 0;
+            PZ_TRY(cudaMemcpy(&too_long, flag, sizeof(int), cudaMemcpyDeviceToHost));
+            if (too_long) {   // a walk of more than kVisitMax voxels: this sub-plan keeps the DDA kernel
+                cudaFree(S.vhead); cudaFree(S.vde);
+                S.vhead = nullptr; S.vde = nullptr;
+            }
+            return cudaSuccess;
+        };
+        const cudaError_t ve = run();
+        void* ptrs[] = {count, voff, flag, tmp};
+        for (void* q : ptrs)
+            if (q) cudaFree(q);
+        if (ve != cudaSuccess) {
+            cudaGetLastError();
+            if (S.vhead) cudaFree(S.vhead);
+            if (S.vde) cudaFree(S.vde);
+            S.vhead = nullptr; S.vde = nullptr;
+        }
+        Z.vhead = S.vhead; Z.vde = S.vde;
     }
     if (kL == 1) return z_set_smem<1>(S.smem_bytes);
     if (kL == 2) return z_set_smem<2>(S.smem_bytes);
@@ -1217,7 +1430,14 @@ static cudaError_t z_launch(const SceneParams& P, PlanarZHost& H, const float* i
         const int groups = z_groups(S, nk, kMode == kGather);
         Z.groups = groups;
         const dim3 grid(Z.tiles_x * Z.tiles_y, S.n_blocks, groups);
-        if (Z.lanes_l == 1)
+        if (kMode == kGather && Z.vhead) {   // the visit-list adjoint
+            if (Z.lanes_l == 1)
+                planarv_kernel<1><<<grid, kZThreads, S.smem_bytes, stream>>>(P, Z, in, out, active_pixels, n_active, w, gate);
+            else if (Z.lanes_l == 2)
+                planarv_kernel<2><<<grid, kZThreads, S.smem_bytes, stream>>>(P, Z, in, out, active_pixels, n_active, w, gate);
+            else
+                planarv_kernel<4><<<grid, kZThreads, S.smem_bytes, stream>>>(P, Z, in, out, active_pixels, n_active, w, gate);
+        } else if (Z.lanes_l == 1)
             planarz_kernel<kMode, 1><<<grid, kZThreads, S.smem_bytes, stream>>>(P, Z, in, out, active_pixels, n_active,
                                                                                w, gate);
         else if (Z.lanes_l == 2)
