@@ -11,7 +11,7 @@ import os
 from . import build as _build
 
 MAX_SURFACES = 8
-ABI_VERSION = 9
+ABI_VERSION = 10
 
 
 class DrtvamSurface(C.Structure):
@@ -79,6 +79,13 @@ SYMBOLS = {
     "drtvam_adjoint_host": (C.c_int, [_vp, _vp, _vp, _u64, _u32, _u32, _f32, _vp]),
     "drtvam_thresholded_loss": (C.c_int, [C.c_int, _vp, _vp, _f32, _vp, _u64, _f32, _f32, _f32, _f32, _f32, _i32, _f32,
                                           _vp, _vp, _vp]),
+    "drtvam_lbfgs_history": (C.c_int, [C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, _u64, _i32, _vp]),
+    "drtvam_lbfgs_direction": (C.c_int, [C.c_int, _vp, _i32, _u64, _vp, _i32, _vp, _vp]),
+    "drtvam_lbfgs_combine": (C.c_int, [C.c_int, _vp, _i32, _vp, _u64, _vp, _vp]),
+    "drtvam_armijo_losses": (C.c_int, [C.c_int, _vp, _vp, _vp, _u64, _f32, _f32, _f32, _f32, _f32, _i32, _i32, _i32, _vp,
+                                       _vp, _vp]),
+    "drtvam_armijo_select": (C.c_int, [C.c_int, _vp, _i32, _i32, C.c_double, _vp, _vp, _vp, C.c_double, _vp, _vp]),
+    "drtvam_lbfgs_update": (C.c_int, [C.c_int, _vp, _vp, _vp, _u64, _vp, _vp]),
     "drtvam_launch_count": (_u64, []),
     "drtvam_last_error": (C.c_char_p, []),
     "drtvam_abi_version": (C.c_int, []),

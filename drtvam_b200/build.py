@@ -27,7 +27,7 @@ NVCC_FLAGS = [
 ]
 
 LIB_SOURCES = ["abi.cu", "general_kernels.cu", "planar_kernels.cu", "planarz_kernels.cu", "planarj_kernels.cu",
-               "loss_kernels.cu",
+               "loss_kernels.cu", "lbfgs_kernels.cu",
                "mesh_kernels.cu", "inside_kernels.cu", "filter_kernels.cu"]
 MICRO_SOURCES = ["microbench.cu"]
 

@@ -828,6 +828,70 @@ int drtvam_thresholded_loss(int device, const float* dose, const float* dose_b, 
     return DRTVAM_OK;
 }
 
+// ---- LinearLBFGS on the device (lbfgs.py:146-275) ---------------------------------------------------
+#define LB_GUARD(dev)                                                                 \
+    DeviceGuard guard(dev);                                                           \
+    if (!guard.ok) return fail(DRTVAM_E_CUDA, "cudaSetDevice(%d) failed", dev)
+
+int drtvam_lbfgs_history(int device, const float* p, const float* g, float* p_old, float* g_old, float* s_new,
+                         float* y_new, uint64_t n, int32_t first, void* stream) {
+    if (!p || !g || !p_old || !g_old || (!first && (!s_new || !y_new))) return fail(DRTVAM_E_INVALID, "NULL buffer");
+    LB_GUARD(device);
+    CUDA_TRY(launch_lbfgs_history(p, g, p_old, g_old, s_new, y_new, n, first, static_cast<cudaStream_t>(stream)));
+    return DRTVAM_OK;
+}
+
+int drtvam_lbfgs_direction(int device, const float* const* vectors, int32_t h, uint64_t n, double* gram, int32_t solve_only,
+                           double* coef, void* stream) {
+    if (!vectors || !gram || !coef) return fail(DRTVAM_E_INVALID, "NULL buffer");
+    if (h < 0 || h > 6) return fail(DRTVAM_E_INVALID, "history length %d outside [0, 6]", h);
+    LB_GUARD(device);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (solve_only != 1) CUDA_TRY(launch_lbfgs_gram(vectors, 2 * h + 1, n, gram, st));
+    if (solve_only != 2) CUDA_TRY(launch_lbfgs_solve(gram, h, h == 0, coef, st));
+    return DRTVAM_OK;
+}
+
+int drtvam_lbfgs_combine(int device, const float* const* vectors, int32_t h, const double* coef, uint64_t n,
+                         float* direction, void* stream) {
+    if (!vectors || !coef || !direction) return fail(DRTVAM_E_INVALID, "NULL buffer");
+    if (h < 0 || h > 6) return fail(DRTVAM_E_INVALID, "history length %d outside [0, 6]", h);
+    LB_GUARD(device);
+    CUDA_TRY(launch_lbfgs_combine(vectors, 2 * h + 1, coef, n, direction, static_cast<cudaStream_t>(stream)));
+    return DRTVAM_OK;
+}
+
+int drtvam_armijo_losses(int device, const float* dose, const float* ddose, const float* target, uint64_t n, float tl,
+                         float tu, float weight_object, float weight_void, float weight_limit, int32_t K, int32_t first,
+                         int32_t count, double* losses, const float* skip, void* stream) {
+    if (!dose || !ddose || !target || !losses) return fail(DRTVAM_E_INVALID, "NULL buffer");
+    if (K < 1 || K > 4) return fail(DRTVAM_E_INVALID, "exponent K = %d outside [1, 4]", K);
+    if (first < 0 || count < 1 || count > 16 || first + count > 32)
+        return fail(DRTVAM_E_INVALID, "trials [%d, %d) outside [0, 32) or more than 16 at once", first, first + count);
+    LB_GUARD(device);
+    CUDA_TRY(launch_armijo_losses(dose, ddose, target, n, tl, tu, weight_object, weight_void, weight_limit, K, first, count,
+                                  losses, skip, static_cast<cudaStream_t>(stream)));
+    return DRTVAM_OK;
+}
+
+int drtvam_armijo_select(int device, const double* losses, int32_t first, int32_t last, double scale, const double* f0,
+                         const double* pattern_term, const double* g_dot_d, double c1, float* out, void* stream) {
+    if (!losses || !f0 || !g_dot_d || !out) return fail(DRTVAM_E_INVALID, "NULL buffer");
+    if (first < 0 || last <= first || last > 32) return fail(DRTVAM_E_INVALID, "trials [%d, %d) outside [0, 32)", first, last);
+    LB_GUARD(device);
+    CUDA_TRY(launch_armijo_select(losses, first, last, last, scale, f0, pattern_term, g_dot_d, c1, out,
+                                  static_cast<cudaStream_t>(stream)));
+    return DRTVAM_OK;
+}
+
+int drtvam_lbfgs_update(int device, const float* p, const float* direction, const float* alpha, uint64_t n, float* out,
+                        void* stream) {
+    if (!p || !direction || !alpha || !out) return fail(DRTVAM_E_INVALID, "NULL buffer");
+    LB_GUARD(device);
+    CUDA_TRY(launch_lbfgs_update(p, direction, alpha, n, out, static_cast<cudaStream_t>(stream)));
+    return DRTVAM_OK;
+}
+
 int drtvam_forward_host(DrtvamScene* s, const float* active_data_host, const uint32_t* active_pixels_host,
                         uint64_t n_active, uint32_t spp, uint32_t seed, float out_scale, float* dose_host) {
     if (!s) return fail(DRTVAM_E_INVALID, "scene handle is NULL");

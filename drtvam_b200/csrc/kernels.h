@@ -198,4 +198,19 @@ cudaError_t launch_thresholded_loss(const float* x, const float* x_b, float alph
                                     float tl, float tu, float w_obj, float w_void, float w_lim, int K, float grad_scale,
                                     float* grad, double* loss_out, cudaStream_t stream);
 
+
+// LinearLBFGS on the device (lbfgs_kernels.cu)
+cudaError_t launch_lbfgs_history(const float* p, const float* g, float* p_old, float* g_old, float* s, float* y, size_t n,
+                                 int first, cudaStream_t st);
+cudaError_t launch_lbfgs_gram(const float* const* vectors, int n_vec, size_t n, double* gram, cudaStream_t st);
+cudaError_t launch_lbfgs_solve(const double* gram, int h, int first_step, double* coef, cudaStream_t st);
+cudaError_t launch_lbfgs_combine(const float* const* vectors, int n_vec, const double* coef, size_t n, float* out,
+                                 cudaStream_t st);
+cudaError_t launch_armijo_losses(const float* dose, const float* ddose, const float* target, size_t n, float tl, float tu,
+                                 float w_obj, float w_void, float w_lim, int K, int k0, int count, double* losses,
+                                 const float* skip, cudaStream_t st);
+cudaError_t launch_armijo_select(const double* losses, int k0, int k1, int trials, double scale, const double* f0,
+                                 const double* pattern_term, const double* gd, double c1, float* out, cudaStream_t st);
+cudaError_t launch_lbfgs_update(const float* p, const float* d, const float* alpha, size_t n, float* out, cudaStream_t st);
+
 }  // namespace drtvam

@@ -41,7 +41,7 @@ class Optimizer:
 
 
 class LinearLBFGS(Optimizer):
-    def __init__(self, lr=1.0, m=5, params=None, render_fn=None, loss_fn=None, search_it=20, dot=None):
+    def __init__(self, lr=1.0, m=5, params=None, render_fn=None, loss_fn=None, search_it=20, dot=None, allsum=None):
         super().__init__(lr, params)
         self.m = m                # history size
         self.p_old, self.g_old = {}, {}
@@ -49,9 +49,23 @@ class LinearLBFGS(Optimizer):
         self.render_fn = render_fn
         self.loss_fn = loss_fn
         self.search_it = search_it  # back-tracking iterations
+        self._default_dot = dot is None
         self.dot = dot if dot is not None else (lambda a, b: torch.dot(a.reshape(-1), b.reshape(-1)))
-        self.last_alpha = None
-        self.last_trials = 0
+        # sum of a small tensor over the ranks that share the (sharded) pattern vector: with it the device
+        # path needs ONE collective per iteration (the Gram matrix) instead of one per dot product
+        self.allsum = allsum
+        self._alpha = None        # python float, or a device tensor {alpha, trials, loss} of the last step
+        self._dev = {}            # device-path state per variable
+
+    @property
+    def last_alpha(self):
+        a = self._alpha
+        return float(a[0]) if isinstance(a, torch.Tensor) else a
+
+    @property
+    def last_trials(self):
+        a = self._alpha
+        return int(a[1]) if isinstance(a, torch.Tensor) else getattr(self, '_trials', 0)
 
     def reset(self, k):
         self.s[k], self.y[k], self.ys[k] = [], [], []
@@ -95,7 +109,104 @@ class LinearLBFGS(Optimizer):
             z = z + (alphas[i] - b) * s[i]
         return -z
 
+    # -- device path ----------------------------------------------------------------------------------
+    def _device_ok(self, vol):
+        """One CUDA fp32 variable, a loss that can sweep all Armijo trials at once, and - when the pattern
+        vector is sharded - a way to sum the Gram matrix over ranks."""
+        if len(self.variables) != 1 or not 1 <= self.m <= 6 or not 1 <= self.search_it <= 32:
+            return False
+        v = next(iter(self.variables.values()))
+        if not (v.is_cuda and v.dtype == torch.float32 and v.grad is not None and v.grad.is_cuda):
+            return False
+        if not (self._default_dot or self.allsum is not None):
+            return False
+        return getattr(self.loss_fn, 'armijo_sweep', None) is not None and isinstance(vol, torch.Tensor) and vol.is_cuda
+
+    @torch.no_grad()
+    def _step_device(self, vol, loss):
+        """lbfgs.py:198-275 as a queue of kernels (csrc/lbfgs_kernels.cu): no host round trip, every history
+        vector read twice per iteration (Gram matrix, combination) instead of ~13 times."""
+        import ctypes as C
+        from . import _lib
+        lib = _lib.load()
+        k, var = next(iter(self.variables.items()))
+        dev = var.device
+        st = torch.cuda.current_stream(dev).cuda_stream
+        di = dev.index or 0
+        p = var.detach().reshape(-1).contiguous()
+        g = var.grad.detach().reshape(-1).to(torch.float32).contiguous()
+        n = p.numel()
+        S = self._dev.get(k)
+        if S is None or S['n'] != n:
+            S = {'n': n, 't': 0, 's': [], 'y': [], 'p_old': torch.empty_like(p), 'g_old': torch.empty_like(p),
+                 'gram': torch.empty(13 * 13, device=dev, dtype=torch.float64),
+                 'coef': torch.empty(16, device=dev, dtype=torch.float64),
+                 'out': torch.zeros(4, device=dev, dtype=torch.float32), 'd': torch.empty_like(p),
+                 'sums': torch.zeros(32, device=dev, dtype=torch.float64)}
+            self._dev[k] = S
+        # ---- history (lbfgs.py:176-196)
+        first = S['t'] == 0
+        s_new = y_new = None
+        if not first:
+            if S['t'] > self.m:      # discard the oldest pair, reuse its storage
+                s_new, y_new = S['s'].pop(0), S['y'].pop(0)
+            else:
+                s_new, y_new = torch.empty_like(p), torch.empty_like(p)
+            S['s'].append(s_new)
+            S['y'].append(y_new)
+        _lib.check(lib.drtvam_lbfgs_history(di, p.data_ptr(), g.data_ptr(), S['p_old'].data_ptr(), S['g_old'].data_ptr(),
+                                            s_new.data_ptr() if s_new is not None else None,
+                                            y_new.data_ptr() if y_new is not None else None, n, int(first), st))
+        S['t'] += 1
+        # ---- direction (lbfgs.py:213-234): Gram matrix of [s.., y.., g], recursion on coefficients, combination
+        h = len(S['s'])
+        vecs = S['s'] + S['y'] + [S['g_old']]
+        table = (C.c_void_p * len(vecs))(*[v.data_ptr() for v in vecs])
+        if self.allsum is None:
+            _lib.check(lib.drtvam_lbfgs_direction(di, table, h, n, S['gram'].data_ptr(), 0, S['coef'].data_ptr(), st))
+        else:
+            _lib.check(lib.drtvam_lbfgs_direction(di, table, h, n, S['gram'].data_ptr(), 2, S['coef'].data_ptr(), st))
+            nn = (2 * h + 1) ** 2
+            S['gram'][:nn] = self.allsum(S['gram'][:nn])
+            _lib.check(lib.drtvam_lbfgs_direction(di, table, h, n, S['gram'].data_ptr(), 1, S['coef'].data_ptr(), st))
+        d = S['d']
+        _lib.check(lib.drtvam_lbfgs_combine(di, table, h, S['coef'].data_ptr(), n, d.data_ptr(), st))
+        # ---- one forward projection of the direction, then every Armijo trial in one sweep
+        params = {k: d.reshape(var.shape)}
+        dvol = self.render_fn(params)
+        # stages of 4 and then up to 16 trials: alpha = 1 is accepted in almost every iteration, and a stage
+        # that finds the search over (S['out'][3]) returns in its first instruction
+        f0 = loss.detach().to(torch.float64).reshape(1)
+        S['sums'].zero_()
+        first = 0
+        for count in (4, 16, 12):
+            count = min(count, self.search_it - first)
+            if count <= 0:
+                break
+            stage = self.loss_fn.armijo_sweep(vol.detach(), dvol, d, first, count, S['sums'],
+                                              S['out'][3:4] if first else None)
+            if stage is None:
+                if first:
+                    raise RuntimeError("the fused Armijo sweep became unavailable between two stages")
+                return None
+            scale, term = stage
+            _lib.check(lib.drtvam_armijo_select(di, S['sums'].data_ptr(), first, first + count, float(scale), f0.data_ptr(),
+                                                term.data_ptr() if term is not None else None,
+                                                S['coef'][13:14].data_ptr(), 1e-4, S['out'].data_ptr(), st))
+            first += count
+        new = torch.empty_like(p)
+        _lib.check(lib.drtvam_lbfgs_update(di, p.data_ptr(), d.data_ptr(), S['out'].data_ptr(), n, new.data_ptr(), st))
+        self._alpha = S['out'].clone()
+        new = new.reshape(var.shape)
+        new.requires_grad_(True)
+        self.variables[k] = new
+        return True
+
     def step(self, vol, loss):
+        if self._device_ok(vol):
+            with torch.no_grad():
+                if self._step_device(vol, loss):
+                    return
         search_dirs = {}
         with torch.no_grad():
             for k in self.variables:
@@ -127,7 +238,7 @@ class LinearLBFGS(Optimizer):
                 if bool((f_new <= loss + c1 * alpha * g_dot_z).all()):
                     break
                 alpha *= 0.5
-            self.last_alpha, self.last_trials = alpha, trials
+            self._alpha, self._trials = alpha, trials
 
             for k, p in list(self.variables.items()):
                 new = (p.detach() + alpha * params[k]).detach()

@@ -207,6 +207,31 @@ class ThresholdedLoss(Loss):
             return False  # surface-aware two-channel volumes take the generic path
         return float(self.K).is_integer() and 1 <= int(self.K) <= 8
 
+    def armijo_sweep(self, x, dx, target, direction, first, count, sums, skip=None):
+        """One stage of the Armijo back-tracking search (lbfgs.py:256-266), trials [first, first + count), in
+        one sweep of the two volumes: sums[k] (device float64[32]) += sum over the local voxels of the loss
+        at x + 2^-k dx, summed over ranks when the dose is z-slab sharded.  Returns (scale, pattern_term) -
+        the reference evaluates the pattern term on the DIRECTION (lbfgs.py:260) - or None when this
+        volume pair cannot take the fused path.  `skip`: device float, non-zero = search already over."""
+        if not (self._fusable(x, target) and self._fusable(dx, target)) or int(self.K) > 4:
+            return None
+        from . import _lib
+        lib = _lib.load()
+        _lib.check(lib.drtvam_armijo_losses(
+            x.device.index or 0, x.data_ptr(), dx.data_ptr(), target.data_ptr(), x.numel(), float(self.tl), float(self.tu),
+            float(self.weight_object), float(self.weight_void), float(self.weight_limit), int(self.K), int(first),
+            int(count), sums.data_ptr(), skip.data_ptr() if skip is not None else None,
+            torch.cuda.current_stream(x.device).cuda_stream))
+        n = x.numel()
+        if self.dose_allsum is not None:
+            sums[first:first + count] = self.dose_allsum(sums[first:first + count])
+            n = self.dose_count if self.dose_count else n
+        scale = 1.0 / n if self.reduction is torch.mean else 1.0
+        term = None
+        if self.weight_sparsity != 0:
+            term = self._reduce_patterns(self.eval_sparsity(direction)).to(torch.float64).reshape(1)
+        return scale, term
+
     def __call__(self, x, target, patterns):
         lazy = isinstance(x, LazyAxpy)
         base = x.x if lazy else x

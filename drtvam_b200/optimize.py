@@ -177,8 +177,11 @@ def optimize(config, patterns_fwd=None, progress=True):
     def loss_fn2(y, patterns):
         return loss_fn(y, target, patterns)
     loss_fn2.accepts_lazy = getattr(loss_fn, 'accepts_lazy', False)
+    if getattr(loss_fn, 'armijo_sweep', None) is not None:
+        loss_fn2.armijo_sweep = lambda x, dx, direction, *a: loss_fn.armijo_sweep(x, dx, target, direction, *a)
 
-    opt = LinearLBFGS(loss_fn=loss_fn2, render_fn=render_fn, dot=parallel.make_dot(None, world), **opt_cfg)
+    opt = LinearLBFGS(loss_fn=loss_fn2, render_fn=render_fn, dot=parallel.make_dot(None, world) if world > 1 else None,
+                      allsum=parallel.make_sum(None, world) if world > 1 else None, **opt_cfg)
     opt[patterns_key] = params[patterns_key]
     n_steps = config.get('n_steps', 40)
     loss_hist = np.zeros(n_steps)

@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define DRTVAM_ABI_VERSION 9
+#define DRTVAM_ABI_VERSION 10
 #define DRTVAM_MAX_SURFACES 8
 #define DRTVAM_MAX_MESH_SURFACES 4
 
@@ -278,6 +278,43 @@ int drtvam_thresholded_loss(int device, const float *dose, const float *dose_b, 
                             uint64_t n, float tl, float tu, float weight_object, float weight_void,
                             float weight_limit, int32_t K, float grad_scale, float *grad, double *loss_out,
                             void *stream);
+
+/* ---- LinearLBFGS on the device (lbfgs.py:146-275) --------------------------
+ * All buffers are DEVICE buffers of fp32 pattern vectors of n elements unless stated; nothing below
+ * synchronises or reads a result back, so a whole iteration is queued without a host round trip.
+ *
+ * history (lbfgs.py:176-196): s_new = p - p_old, y_new = g - g_old (skipped when first != 0), then
+ * p_old = p, g_old = g. */
+int drtvam_lbfgs_history(int device, const float *p, const float *g, float *p_old, float *g_old, float *s_new,
+                         float *y_new, uint64_t n, int32_t first, void *stream);
+/* two-loop recursion (lbfgs.py:213-234).  vectors: HOST array of 2h + 1 device pointers
+ * [s_0 .. s_{h-1}, y_0 .. y_{h-1}, g], oldest pair first.  gram: DEVICE double[(2h+1)^2], the Gram matrix of
+ * the vectors - every dot product of the recursion, each vector read once (13 separate passes in the
+ * reference).  coef: DEVICE double[16]: coef[j] with d = - sum_j coef[j] vectors[j], coef[13] = g . d
+ * (lbfgs.py:251-254), coef[14] = 1 when a curvature y_i . s_i was zero or NaN.  solve_only: 0 = both
+ * steps; 2 = only form the Gram matrix (the caller sums it over ranks: pattern vectors are sharded, this is
+ * the ONE collective of the iteration); 1 = only run the recursion on `gram`. */
+int drtvam_lbfgs_direction(int device, const float *const *vectors, int32_t h, uint64_t n, double *gram,
+                           int32_t solve_only, double *coef, void *stream);
+int drtvam_lbfgs_combine(int device, const float *const *vectors, int32_t h, const double *coef, uint64_t n,
+                         float *direction, void *stream);
+/* Armijo back-tracking (lbfgs.py:252-266) without a host decision per trial, in stages of trials
+ * [first, first + count), count <= 16: losses[k] (DEVICE double[32], cleared by the caller before the first
+ * stage) += sum over voxels of the thresholded loss (loss.py:102-132) at dose + 2^-k ddose, every trial of
+ * the stage in ONE sweep of the two volumes.  select looks at trials [first, last): the first k with
+ * scale * losses[k] + pattern_term <= f0 + c1 * 2^-k * g_dot_d (all DEVICE doubles; pattern_term may be
+ * NULL) ends the search: out[0] = alpha, out[1] = trials used, out[2] = the loss at alpha, out[3] = 1
+ * (DEVICE floats).  Passing out + 3 as `skip` makes the next stage return in its first instruction once
+ * the search is over - alpha = 1 is accepted in almost every iteration, so the usual cost is the first
+ * stage of 4 trials.  With the dose sharded over ranks (z-slab) the caller sums `losses` between the two. */
+int drtvam_armijo_losses(int device, const float *dose, const float *ddose, const float *target, uint64_t n, float tl,
+                         float tu, float weight_object, float weight_void, float weight_limit, int32_t K,
+                         int32_t first, int32_t count, double *losses, const float *skip, void *stream);
+int drtvam_armijo_select(int device, const double *losses, int32_t first, int32_t last, double scale, const double *f0,
+                         const double *pattern_term, const double *g_dot_d, double c1, float *out, void *stream);
+/* out = p + alpha * direction with alpha read from DEVICE memory (lbfgs.py:271-274) */
+int drtvam_lbfgs_update(int device, const float *p, const float *direction, const float *alpha, uint64_t n, float *out,
+                        void *stream);
 
 /* number of kernels this library has launched since load (bench gpu_launches) */
 uint64_t drtvam_launch_count(void);

@@ -37,9 +37,10 @@ for step in "$@"; do
         echo "[$TAG] reference arm exit $?";;
     launches)
         wl=${a:-C2}; flags=${b//+/ }
+        extra="--no-default-sampling --no-lbfgs"; [[ "$flags" == *lbfgs* ]] && extra="--no-default-sampling"
         timeout 900 ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
-            --log-file $O/${TAG}_launches_${wl}_raw.csv python bench.py --workload $wl --steps 2 --warmup 3 --no-cpu-baseline \
-            --no-default-sampling --no-lbfgs $flags > $O/${TAG}_launches_${wl}.log 2>&1
+            --log-file $O/${TAG}_launches_${wl}_raw.csv python bench.py --workload $wl --steps 6 --warmup 3 --no-cpu-baseline \
+            $extra $flags > $O/${TAG}_launches_${wl}.log 2>&1
         echo "[$TAG] launch list exit $?"
         python tools/ncu_summary.py launches $O/${TAG}_launches_${wl}_raw.csv > $O/${TAG}_launches_${wl}.csv 2>&1
         tail -12 $O/${TAG}_launches_${wl}.csv;;
