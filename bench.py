@@ -470,13 +470,17 @@ def main():
         res["plan"] = int(lib.drtvam_scene_plan(h, n_local, c_spp))
 
         if headline:
-            # end to end: host (pinned) inputs copied in and results copied out every step.  The patterns are
-            # uploaded on the compute stream (A p needs all of them); the search direction is uploaded and the
-            # pattern gradient downloaded on a copy stream, under A p / A^T g and under A d respectively.
-            # Every copy of step i is issued and completed inside step i (no prefetch across steps).
+            # end to end through the integrator's own entry points (VolumeIntegrator.render / render_backward,
+            # what mi.render and dr.backward call): host (pinned) inputs copied in and results copied out
+            # every step.  The patterns are uploaded in blocks of angles under the projection of the previous
+            # block (render(host_patterns=...)); the search direction is uploaded and the pattern gradient
+            # downloaded on a copy stream, under A^T g and under A d respectively.  Every copy of step i is
+            # issued and completed inside step i (no prefetch across steps).
+            from drtvam_b200.scene import sample_tea_32
             p_host = p_dev.cpu().pin_memory()
             d_host = d_dev.cpu().pin_memory()
             g_host = torch.empty(n_local, dtype=torch.float32).pin_memory()
+            integ.events = None
             barrier()
             main_stream = torch.cuda.current_stream(dev)
             copy_stream = torch.cuda.Stream(dev)
@@ -485,21 +489,28 @@ def main():
             e0.record()
             loss_host = 0.0
             for i in range(steps):
-                copy_stream.wait_stream(main_stream)                 # step i's copies start with step i
-                p_in = p_host.to(dev, non_blocking=True)
-                d_ready = torch.cuda.Event()
+                seed = 100 + i
+                vol = integ.render(scene, sensor, seed=seed, spp=c_spp, host_patterns=p_host)      # upload + A p
+                p_in = scene.projector.active_data
+                copy_stream.wait_stream(scene.copy_stream())         # the direction follows the patterns on the bus
                 with torch.cuda.stream(copy_stream):
                     d_in = d_host.to(dev, non_blocking=True)
+                    d_ready = torch.cuda.Event()
                     d_ready.record(copy_stream)
                 d_in.record_stream(main_stream)
-
-                def download(grad):
-                    copy_stream.wait_stream(main_stream)             # after the adjoint
-                    grad.record_stream(copy_stream)
-                    with torch.cuda.stream(copy_stream):
-                        g_host.copy_(grad, non_blocking=True)
-
-                loss, f_new, grad = step(100 + i, p_in, d_in, d_ready=d_ready, on_grad=download)
+                x = vol.detach().requires_grad_(True)
+                loss = loss_fn(x, target_loc, p_in)
+                loss.backward()
+                grad = integ.render_backward(scene, None, x.grad, sensor, sample_tea_32(seed, 1)[0], c_spp)   # A^T g
+                copy_stream.wait_stream(main_stream)                 # after the adjoint
+                grad.record_stream(copy_stream)
+                with torch.cuda.stream(copy_stream):
+                    g_host.copy_(grad, non_blocking=True)
+                with torch.no_grad():
+                    main_stream.wait_event(d_ready)
+                    scene.projector.active_data = d_in
+                    dvol = dv.render(scene, None, integrator=integ, sensor=sensor, spp=c_spp, seed=seed)      # A d
+                    f_new = loss_fn(LazyAxpy(vol.detach(), dvol, 1.0), target_loc, d_in)                        # Armijo trial
                 main_stream.wait_stream(copy_stream)                 # the gradient is on the host before the step ends
                 loss_host = float(loss)                              # D2H of the scalar: syncs the step
             e1.record()

@@ -255,9 +255,15 @@ cudaError_t planar_gate(DrtvamScene* s, const uint32_t* active_pixels, uint64_t 
                         const int** gate, int* host_gate) {
     *gate = s->planar.gate;
     *host_gate = -1;
-    if (active_pixels == s->pinned_pixels && n_active == s->pinned_n) {
+    // the pinned list itself, or whole patterns out of it (blocks of angles of a streamed call): a
+    // sub-range of a dense layout is dense
+    const uint64_t rw = static_cast<uint64_t>(s->P.res_x) * s->P.n_rows;
+    const bool inside = s->pinned_pixels && active_pixels >= s->pinned_pixels &&
+                        active_pixels + n_active <= s->pinned_pixels + s->pinned_n &&
+                        static_cast<uint64_t>(active_pixels - s->pinned_pixels) % rw == 0 && n_active % rw == 0;
+    if (inside) {
         if (s->pinned_gate < 0) {   // first call after the pin or after a plan rebuild: verify once, synchronously
-            cudaError_t e = launch_planar_check(s->P1, s->planar, active_pixels, n_active, st);
+            cudaError_t e = launch_planar_check(s->P1, s->planar, s->pinned_pixels, s->pinned_n, st);
             if (e != cudaSuccess) return e;
             int g = 0;
             e = cudaMemcpyAsync(&g, s->planar.gate, sizeof(int), cudaMemcpyDeviceToHost, st);

@@ -92,11 +92,86 @@ class VolumeIntegrator(TVAMIntegrator):
             ev[1].record()
         return film.data
 
-    def render(self, scene, sensor=0, seed: int = 0, spp: int = 0, develop: bool = True, evaluate: bool = True):
-        """Primal A p with p = projector.active_data; returns (resz, resy, resx, C)."""
+    def render(self, scene, sensor=0, seed: int = 0, spp: int = 0, develop: bool = True, evaluate: bool = True,
+               host_patterns=None, blocks: int = 4):
+        """Primal A p with p = projector.active_data; returns (resz, resy, resx, C).
+
+        `host_patterns` (an addition to the reference signature): the pattern values in PINNED host memory.
+        They become projector.active_data, uploaded in `blocks` blocks of whole projection angles on a copy
+        stream while the projection of the previous block runs (A = sum_k A_k, so the blocks accumulate into
+        the film): the 256 MB upload of C2 hides behind the kernels instead of preceding them."""
         _check_emitters(scene)
         with torch.no_grad():
+            if host_patterns is not None:
+                return self._project_streamed(scene, sensor, seed, spp, host_patterns, blocks)
             return self._project(scene, sensor, seed, spp, scene.emitters()[0].active_data)
+
+    def _project_streamed(self, scene, sensor, seed, spp, host, blocks):
+        sensor = _sensor_of(scene, sensor)
+        projector = scene.emitters()[0]
+        pixels = projector.active_pixels
+        dev = pixels.device
+        n = pixels.numel()
+        hw = projector.res[0] * projector.res[1]
+        rows = getattr(scene, '_z_rows', None)
+        per_pattern = hw if rows is None else (rows[1] - rows[0]) * projector.res[0]
+        host = host.reshape(-1)
+        if host.numel() != n:
+            raise ValueError(f"[{projector.__class__.__name__}] active_data and active_pixels must have the same length.")
+        inv_scalar, inv_tensor = _inv_volume(sensor, scene)
+        nk = n // per_pattern if per_pattern and n % per_pattern == 0 else 0
+        blocks = max(1, min(int(blocks), nk))
+        if inv_tensor is not None or nk == 0 or blocks == 1 or not host.is_pinned():
+            # per-voxel volumes / ragged lists / pageable memory: one upload, one projection
+            projector.active_data = host.to(dev, torch.float32, non_blocking=True)
+            return self._project(scene, sensor, seed, spp, projector.active_data)
+        spp, _ = self.prepare(projector, seed, spp)
+        handle = scene.handle(self, sensor)
+        film = sensor.film()
+        film.data = torch.empty(scene.film_shape(sensor), device=dev, dtype=torch.float32)
+        data = torch.empty(n, device=dev, dtype=torch.float32)
+        scene.pin_pixels(handle, pixels)
+        main = torch.cuda.current_stream(dev)
+        copy = scene.copy_stream()
+        copy.wait_stream(main)
+        bounds = [per_pattern * (nk * b // blocks) for b in range(blocks + 1)]
+        ready = []
+        with torch.cuda.stream(copy):
+            for b in range(blocks):
+                lo, hi = bounds[b], bounds[b + 1]
+                data[lo:hi].copy_(host[lo:hi], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(copy)
+                ready.append(ev)
+        data.record_stream(copy)
+        lib = _lib.load()
+        ev = self._event_pair('forward')
+        _lib.check(lib.drtvam_scene_set_inv_volume(handle, None))
+        # position of every entry in the wavefront of the whole call: only integrators that draw samples need it
+        draws = not (self.regular_sampling and not self.sample_time and projector.kind == 'collimated'
+                     and float(scene.medium.get('albedo', 0.0)) == 0.0 and sensor.kind == 'dda')
+        base = scene.sampler_base(n) if draws else None
+        try:
+            for b in range(blocks):
+                lo, hi = bounds[b], bounds[b + 1]
+                main.wait_event(ready[b])
+                if base is not None:
+                    _lib.check(lib.drtvam_scene_set_sampler_index(handle, base[lo:hi].data_ptr()))
+                _lib.check(lib.drtvam_forward(handle, data[lo:hi].data_ptr(), pixels[lo:hi].data_ptr(), hi - lo, spp,
+                                              seed & 0xFFFFFFFF, inv_scalar, film.data.data_ptr(), int(b == 0),
+                                              main.cuda_stream))
+        finally:
+            if base is not None:
+                _lib.check(lib.drtvam_scene_set_sampler_index(
+                    handle, scene._sampler_index.data_ptr() if scene._sampler_index is not None else None))
+        if ev is not None:
+            ev[1].record()
+        projector.active_data = data
+        ev = self._event_pair('allreduce') if scene.world_size > 1 else None
+        scene.reduce_dose(film.data)
+        if ev is not None:
+            ev[1].record()
+        return film.data
 
     def render_forward(self, scene, params, sensor=0, seed: int = 0, spp: int = 0):
         """Forward-mode derivative (volume.py:58-95), same signature as the reference.  There the

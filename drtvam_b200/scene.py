@@ -181,6 +181,22 @@ class Scene:
             return (self.z_window[1] - self.z_window[0],) + shape[1:]
         return shape
 
+    def copy_stream(self):
+        """The stream host <-> device copies of streamed calls run on."""
+        if getattr(self, '_copy_stream', None) is None:
+            self._copy_stream = torch.cuda.Stream(self.projector.active_pixels.device)
+        return self._copy_stream
+
+    def sampler_base(self, n):
+        """Positions of the n local entries in the wavefront of the whole (unsharded, unblocked) call, as a
+        device int32 tensor - what a call on a sub-range of the list must seed its PCG32 streams with - or
+        None when the integrator draws no samples that depend on it."""
+        if self._sampler_index is not None:
+            return self._sampler_index
+        if getattr(self, '_arange', None) is None or self._arange.numel() != n:
+            self._arange = torch.arange(n, device=self.projector.active_pixels.device, dtype=torch.int32)
+        return self._arange
+
     def pin_pixels(self, h, pixels):
         """Tells the library that `pixels` (projector.active_pixels, only ever REPLACED by params.update(),
         optimize.py:157-159) stays as it is, so the planar layout check runs once instead of per call."""
@@ -242,6 +258,7 @@ class Scene:
             if z is not None:
                 self.partition = "zslab"
                 self._z_sensor = sensor
+                self._z_rows = z["rows"]
                 self.z_window, self.shard_index = z["window"], z["index"]
                 p.active_pixels = p.active_pixels[z["index"]].contiguous()
                 p.active_data = p.active_data[z["index"]].contiguous()
