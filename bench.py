@@ -48,6 +48,7 @@ def parse_args():
     ap.add_argument("--partition", default="auto", choices=["auto", "angle", "zslab"],
                     help="multi-GPU partitioning: by projection angle (one all-reduce of the dose per forward) or, "
                          "for planar scenes, by z-slab / DMD row (no dose collective)")
+    ap.add_argument("--grid", default="", help="A,S: angle groups x z-slabs of the zslab partition (default: parallel.slab_grid)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-default-sampling", action="store_true", help="skip the regular_sampling=false record")
     ap.add_argument("--no-lbfgs", action="store_true", help="skip the whole-L-BFGS-iteration record")
@@ -377,11 +378,12 @@ def main():
         if verify:
             p_full, g_full, ref = verify_multi_gpu(scene, integ, sensor, n_total, c_spp, target)
         partition = "single"
+        grid = tuple(int(v) for v in args.grid.split(",")) if args.grid else None
         if world > 1:
-            partition = scene.shard(rank, world, partition=args.partition, integrator=integ, sensor=sensor)[2]
+            partition = scene.shard(rank, world, partition=args.partition, integrator=integ, sensor=sensor, grid=grid)[2]
         elif args.emulate_shard > 1:
             partition = scene.shard(0, args.emulate_shard, partition=args.partition, integrator=integ,
-                                    sensor=sensor)[2]
+                                    sensor=sensor, grid=grid)[2]
             scene.world_size = 1
         n_local = scene.projector.active_size()
         pixels = scene.projector.active_pixels
@@ -397,12 +399,17 @@ def main():
                 grad_n[idx] = grad_loc
                 dist.all_reduce(grad_n)
                 if rank == 0:
-                    check = {"partition": partition, "ranks": world,
+                    check = {"partition": partition, "grid": list(scene.grid), "ranks": world,
                              "dose_rel_l2_vs_1_rank": rel_l2(dose_n, ref["dose"]),
-                             "grad_rel_l2_vs_1_rank": rel_l2(grad_n, ref["grad"]), "bound": 1e-6,
+                             "grad_rel_l2_vs_1_rank": rel_l2(grad_n, ref["grad"]),
+                             # ranks that sum partial doses of different angles re-order the accumulation of the
+                             # tensor-core products (their fp32 accumulators truncate): 2e-5 measured; slabs a
+                             # rank owns alone must match to rounding
+                             "bound": 1e-6 if scene.dose_group_size == 1 and partition == "zslab" else 5e-5,
                              "inputs": "same seeded full pattern vector on every rank; dose gradient = that of the "
                                        "thresholded loss at the 1-rank dose, broadcast from rank 0"}
-                    check["ok"] = bool(check["dose_rel_l2_vs_1_rank"] <= 1e-6 and check["grad_rel_l2_vs_1_rank"] <= 1e-6)
+                    check["ok"] = bool(check["dose_rel_l2_vs_1_rank"] <= check["bound"] and
+                                       check["grad_rel_l2_vs_1_rank"] <= check["bound"])
             del p_full, g_full, ref, dose_n, grad_n
             torch.cuda.empty_cache()
         loss_fn = ThresholdedLoss({})
@@ -460,7 +467,7 @@ def main():
         launches = lib.drtvam_launch_count() - launches0
         clock_info = clocks.stop() if clocks else None
         res = {"ms": ms, "launches": launches, "clocks": clock_info, "loss": float(out[0]), "check": check,
-               "partition": partition, "n_local": n_local, "n_total": n_total, "spp": c_spp}
+               "partition": partition, "grid": tuple(scene.grid), "n_local": n_local, "n_total": n_total, "spp": c_spp}
 
         def mean_ms(name):
             ev = pass_events.get(name, [])
@@ -591,7 +598,7 @@ def main():
     peak, how = measured_peaks()
     # algorithmic HBM bytes of one forward pass of this rank: pattern values + pixel indices read once, the
     # (local part of the) dose volume written once
-    film_local = R["film_elems"] if R["partition"] != "zslab" else R["film_elems"] // max(world, 1)
+    film_local = R["film_elems"] if R["partition"] != "zslab" else R["film_elems"] // max(R["grid"][1], 1)
     hbm_alg_bytes = 4.0 * n_local * 2 + 4.0 * film_local
     achieved = hbm_alg_bytes / (fwd_ms * 1e-3) * 1e-9
     visits_per_s = visits / (fwd_ms * 1e-3)
@@ -631,8 +638,10 @@ def main():
                                       f"rays, 3 passes, {t:.1f} s of oracle (fp32, OpenMP, omp atomic per deposit) time; "
                                       "whole-step figures derived from it are extrapolations"}
         par = {"single": "1 GPU", "angle": f"angle-sharded x{world}, 1 all_reduce(dose) per forward",
-               "zslab": f"z-slab / DMD-row sharded x{world}: every rank owns {1}/{world} of the layers for all angles, "
-                        "no dose collective, scalar all-reduces for the loss and the L-BFGS dots"}[R["partition"]]
+               "zslab": f"{R['grid'][0]} angle groups x {R['grid'][1]} z-slabs (DMD rows): a rank projects its angles "
+                        f"into its slab of layers; the dose of a slab is all-reduced among the {R['grid'][0]} ranks that "
+                        "share it (no collective when that is one rank), scalar all-reduces for the loss and the "
+                        "L-BFGS Gram matrix"}[R["partition"]]
         line = {
             "metric": "rays_per_s", "value": value, "unit": "rays/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "sec_per_projection_step": ms / args.steps * 1e-3,

@@ -120,7 +120,8 @@ class VolumeIntegrator(TVAMIntegrator):
             raise ValueError(f"[{projector.__class__.__name__}] active_data and active_pixels must have the same length.")
         inv_scalar, inv_tensor = _inv_volume(sensor, scene)
         nk = n // per_pattern if per_pattern and n % per_pattern == 0 else 0
-        blocks = max(1, min(int(blocks), nk))
+        import os
+        blocks = max(1, min(int(os.environ.get("DRTVAM_STREAM_BLOCKS", blocks)), nk))
         if inv_tensor is not None or nk == 0 or blocks == 1 or not host.is_pinned():
             # per-voxel volumes / ragged lists / pageable memory: one upload, one projection
             projector.active_data = host.to(dev, torch.float32, non_blocking=True)

@@ -241,38 +241,74 @@ class Scene:
             pass
 
     # -- multi-GPU ---------------------------------------------------------
-    def shard(self, rank: int, world_size: int, group=None, partition: str = "angle", integrator=None, sensor=None):
+    def shard(self, rank: int, world_size: int, group=None, partition: str = "angle", integrator=None, sensor=None,
+              grid=None):
         """Keep only this rank's part of the projection.
 
         partition "angle": a contiguous range of projection angles balanced by active-pixel count; every
         forward is followed by one all_reduce(SUM) of the dose.  "zslab": for planar scenes (every ray
-        stays in its voxel layer, sensor.py:345) a slab of film layers and the DMD rows that map to it,
-        for ALL angles -- no dose collective, the loss is a sharded sum.  "auto" takes "zslab" where the
-        scene allows it.  Returns (lo, hi, partition) with [lo, hi) the owned index range for "angle"."""
-        from .parallel import shard_bounds, zslab_shard
+        stays in its voxel layer, sensor.py:345) a slab of film layers and the DMD rows that map to it -
+        no dose collective for the layers a rank owns alone, the loss is a sharded sum.  The two combine:
+        `grid` = (A, S) makes A angle groups x S slabs (rank = a * S + s); the dose of a slab is then
+        all-reduced among the A ranks that share it, a tensor A times smaller than the film.  "auto" takes
+        the slab grid parallel.slab_grid proposes where the scene allows it, else "angle".
+        Returns (lo, hi, partition) with [lo, hi) the owned index range for a pure "angle" partition."""
+        from .parallel import shard_bounds, slab_grid, zslab_shard
         p = self.projector
         self.rank, self.world_size, self.group = rank, world_size, group
         n_full = p.active_pixels.numel()
-        if partition in ("auto", "zslab") and world_size > 1:
-            z = zslab_shard(self, rank, world_size, integrator, sensor) if integrator is not None else None
+        if partition in ("auto", "zslab") and world_size > 1 and integrator is not None:
+            rz = int(sensor.resolution()[2])
+            A, S = grid if grid is not None else (slab_grid(world_size, rz) if partition == "auto" else (1, world_size))
+            if A * S != world_size:
+                raise ValueError(f"grid {A} x {S} does not match the world size {world_size}")
+            a, sl = rank // S, rank % S
+            n_pat = p.n_patterns
+            k_lo, k_hi = n_pat * a // A, n_pat * (a + 1) // A
+            z = zslab_shard(self, sl, S, integrator, sensor, k_lo, k_hi) if S > 1 else None
             if z is not None:
                 self.partition = "zslab"
+                self.grid = (A, S)
                 self._z_sensor = sensor
                 self._z_rows = z["rows"]
                 self.z_window, self.shard_index = z["window"], z["index"]
                 p.active_pixels = p.active_pixels[z["index"]].contiguous()
                 p.active_data = p.active_data[z["index"]].contiguous()
+                self._make_groups(A, S, a, sl)
                 self._shard_handles()
                 return 0, n_full, "zslab"
             if partition == "zslab":
                 raise ValueError("z-slab sharding needs a planar scene whose DMD rows map to whole voxel layers")
         lo, hi = shard_bounds(p.active_pixels, p.n_patterns, p.res[0] * p.res[1], rank, world_size)
         self.partition = "angle"
+        self.grid = (world_size, 1)
         self.shard_index = torch.arange(lo, hi, device=p.active_pixels.device)
         p.active_pixels = p.active_pixels[lo:hi].contiguous()
         p.active_data = p.active_data[lo:hi].contiguous()
         self._shard_handles()
         return lo, hi, "angle"
+
+    def _make_groups(self, A, S, a, sl):
+        """Process groups of an A x S grid: the ranks that share a slab (they all-reduce its dose) and the
+        ranks that share an angle group (their slabs make up the film: loss sums, gathers).  Every rank
+        creates every group, in the same order, as torch.distributed requires."""
+        self.dose_group = self.film_group = None
+        self.dose_group_size, self.film_group_size = A, S
+        import torch.distributed as dist
+        if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() != A * S:
+            return                                    # ranks run one after the other (tests, --emulate-shard)
+        for s_ in range(S):
+            g = dist.new_group([a_ * S + s_ for a_ in range(A)]) if A > 1 else None
+            if s_ == sl:
+                self.dose_group = g
+        for a_ in range(A):
+            g = dist.new_group([a_ * S + s_ for s_ in range(S)]) if A > 1 else None
+            if a_ == a:
+                self.film_group = g
+
+    grid = (1, 1)
+    dose_group = film_group = None
+    dose_group_size = film_group_size = 1
 
     def _shard_handles(self):
         if self.shard_index.device.type == 'cuda':
@@ -286,11 +322,16 @@ class Scene:
     shard_index = None
 
     def reduce_dose(self, dose: torch.Tensor):
-        """all_reduce(SUM) of the partial doses of an angle-sharded forward; a z-slab shard owns its
-        layers outright."""
-        if self.world_size > 1 and self.partition != "zslab":
-            import torch.distributed as dist
+        """all_reduce(SUM) of the partial doses of the ranks that project different angles into the same
+        layers: everybody for an angle partition, the angle groups of one slab in a grid, nobody when a
+        rank owns its slab alone."""
+        if self.world_size <= 1:
+            return
+        import torch.distributed as dist
+        if self.partition != "zslab":
             dist.all_reduce(dose, op=dist.ReduceOp.SUM, group=self.group)
+        elif self.dose_group_size > 1 and self.dose_group is not None:
+            dist.all_reduce(dose, op=dist.ReduceOp.SUM, group=self.dose_group)
 
     def local_target(self, target: torch.Tensor) -> torch.Tensor:
         """The part of a film-shaped tensor (loss target, dose gradient) this rank's film holds."""
@@ -306,22 +347,24 @@ class Scene:
         if self.partition != "zslab" or self.world_size == 1:
             return dose
         import torch.distributed as dist
+        S = self.film_group_size
         z0, z1 = self.z_window
-        bounds = [None] * self.world_size
-        dist.all_gather_object(bounds, (z0, z1), group=self.group)
+        bounds = [None] * S
+        dist.all_gather_object(bounds, (z0, z1), group=self.film_group)
         nz = max(b[1] - b[0] for b in bounds)
         pad = torch.zeros((nz,) + tuple(dose.shape[1:]), device=dose.device, dtype=dose.dtype)
         pad[:z1 - z0] = dose
-        parts = [torch.empty_like(pad) for _ in range(self.world_size)]
-        dist.all_gather(parts, pad, group=self.group)
-        return torch.cat([parts[r][:bounds[r][1] - bounds[r][0]] for r in range(self.world_size)], 0)
+        parts = [torch.empty_like(pad) for _ in range(S)]
+        dist.all_gather(parts, pad, group=self.film_group)
+        return torch.cat([parts[r][:bounds[r][1] - bounds[r][0]] for r in range(S)], 0)
 
     def dose_allsum(self):
-        """Sum over ranks of a scalar reduced over the local film (z-slab sharding), else None."""
+        """Sum of a scalar reduced over the local film across the slabs of the film (z-slab sharding): over the
+        ranks of this rank's angle group, each of which holds one slab, fully reduced.  Else None."""
         if self.partition != "zslab" or self.world_size == 1:
             return None
         from .parallel import make_sum
-        return make_sum(self.group, self.world_size)
+        return make_sum(self.film_group, self.film_group_size)
 
 
 class Params(dict):

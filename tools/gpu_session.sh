@@ -11,7 +11,7 @@
 #   launches[:WL[:FLAGS]]  ncu launch list of the timed steps (gpu__time_duration)
 #   ncu:REGEX[:WL[:FLAGS]]  ncu --set full on the kernels matching REGEX, 4 launches
 #   san:TOOL:EXPR       compute-sanitizer --tool TOOL on pytest -k EXPR (ONE sanitizer tool per gpurun call)
-#   scale:N[:WL]        torchrun bench.py at N GPUs, launched as the driver does
+#   scale:N[:WL[:FLAGS]]  torchrun bench.py at N GPUs, launched as the driver does
 #   smoke               __graft_entry__.smoke()
 #   wall[:WL]           tools/optimize_wall.py
 TAG=${1:?tag}; shift
@@ -58,9 +58,10 @@ for step in "$@"; do
             > $O/${TAG}_sanitizer_${a}.log 2>&1
         echo "[$TAG] compute-sanitizer $a exit $?: $(grep -E 'ERROR SUMMARY|passed|failed' $O/${TAG}_sanitizer_${a}.log | tail -2 | tr '\n' ' ')";;
     scale)
-        wl=${b:-C2}
+        IFS=: read -r kind a wl flags <<< "$step"
+        wl=${wl:-C2}; flags=${flags//+/ }
         timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $a --master-addr 127.0.0.1 --master-port 29511 \
-            bench.py --gpus $a --workload $wl --steps 10 --warmup 3 > $O/${TAG}_bench_${wl}_${a}gpu.json 2> $O/${TAG}_bench_${wl}_${a}gpu.err
+            bench.py --gpus $a --workload $wl --steps 10 --warmup 3 $flags > $O/${TAG}_bench_${wl}_${a}gpu.json 2> $O/${TAG}_bench_${wl}_${a}gpu.err
         echo "[$TAG] scale $a exit $?"
         python tools/bench_brief.py $O/${TAG}_bench_${wl}_${a}gpu.json;;
     smoke)
