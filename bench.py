@@ -173,6 +173,11 @@ class ClockSampler:
                 "samples": len(sm), "source": "nvidia-smi -lms 50"}
 
 
+# mma.sync.aligned.m16n8k8 tf32 (SASS HMMA), 8 warps per SM x 16 accumulator tiles: dense TFLOP/s measured by
+# tools/microbench.py on this pool's B200 (profiles/r02g_microbench.json)
+MMA_SYNC_TF32_PEAK = 276.0
+
+
 def measured_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -475,6 +480,11 @@ def main():
         res["fwd_ms"], res["adj_ms"], res["ar_ms"] = mean_ms("forward"), mean_ms("adjoint"), mean_ms("allreduce")
         h = scene.handle(integ, sensor)
         res["plan"] = int(lib.drtvam_scene_plan(h, n_local, c_spp))
+        stat = _lib.C.c_uint64(0)
+        res["stat"] = {}
+        for name, which in (("pairs", 0), ("layers", 1), ("records", 2), ("coef_bytes", 3)):
+            _lib.check(lib.drtvam_scene_stat(h, which, _lib.C.byref(stat)))
+            res["stat"][name] = int(stat.value)
 
         if headline:
             # end to end through the integrator's own entry points (VolumeIntegrator.render / render_backward,
@@ -605,27 +615,55 @@ def main():
     atomic_key = {2: "smem_lds_fadd_sts", 3: "smem_atoms_f32_cas", 1: "smem_atoms_f32_cas"}.get(plan_now,
                                                                                                 "red_f32_scattered_l2")
     traffic, traffic_src = measured_traffic(args.workload, plan_now, world, args.n)
+    pairs, layers = R["stat"]["pairs"], R["stat"]["layers"]
+    on_tensor = plan_now == 2 and pairs > 0 and os.environ.get("DRTVAM_PLANAR_FORWARD", "") != "ffma"
     roofline = {
-        "bound": "issue slots / shared-memory latency (ncu: see `evidence`); neither HBM nor tensor",
-        "kernel": {2: "forward projection A p: zpack + planarg_kernel (patch gather, register accumulators)",
-                   3: "forward projection A p: planar per-lane kernels (jittered rays)",
+        "kernel": {2: "forward projection A p: zpack + planarg_mma_kernel (patch gather as mma.sync m16n8k8 tf32, "
+                      "3xTF32 split)" if on_tensor else "forward projection A p: zpack + planarg_kernel (patch gather, FFMA)",
+                   3: "forward projection A p: jtable_kernel + planarj_kernel (jittered rays, shared-memory tiles)",
                    0: "forward projection A p: general per-lane tracer"}.get(plan_now, "forward projection A p"),
-        "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-        "traffic": traffic, "traffic_source": traffic_src, "peak_source": how,
-        "frac_hbm": achieved / peak, "hbm_algorithmic_bytes": hbm_alg_bytes,
+        "traffic": traffic, "traffic_source": traffic_src,
+        "frac_hbm": achieved / peak, "hbm_algorithmic_GBps": achieved, "hbm_peak_GBps": peak, "hbm_peak_source": how,
+        "hbm_algorithmic_bytes": hbm_alg_bytes,
         "frac_atomic": visits_per_s / ATOMIC_PEAKS[atomic_key][0],
         "atomic_peak": {"name": atomic_key, "ops_per_s": ATOMIC_PEAKS[atomic_key][0], "what": ATOMIC_PEAKS[atomic_key][1],
                         "source": "profiles/r01_microbench_atomics.json (csrc/microbench.cu)"},
         "visits_per_launch": visits, "visits_per_s": visits_per_s, "kernel_ms": fwd_ms,
         "adjoint_ms": adj_ms, "adjoint_visits_per_s": visits / (adj_ms * 1e-3) if adj_ms else None,
         "allreduce_ms": ar_ms, "plan": plan_now,
-        "note": "achieved = algorithmic HBM bytes of one forward pass (pattern values + pixel indices read, dose "
-                "written) / CUDA-event time of the pass, against the measured copy peak: the pass is far from the "
-                "HBM roof because its work is 478 voxel visits per ray on data that stays on chip.  frac_atomic "
-                "= voxel visits per second / the measured peak of the on-chip update it would otherwise need "
-                "(SURVEY 8(d)); plan 2 keeps its accumulators in registers, so it can exceed 1.",
         "evidence": "profiles/ (ncu --set full details and launch lists of this round, named r02*)",
     }
+    if on_tensor:
+        # the dominant kernel is a block-sparse x dense product on the tensor pipe (ncu: tensor pipe 54 %, the
+        # busiest unit; profiles/r02i_planarg_mma_planarz_ncu_details.txt).  Dense-equivalent flops of one pass:
+        # 3 products (tf32 head/tail split) x pairs x 16 voxels x layers x 2.
+        flops = 3.0 * pairs * 16.0 * layers * 2.0
+        tf = flops / (fwd_ms * 1e-3) * 1e-12
+        roofline.update({
+            "bound": "tensor", "achieved": tf, "peak": MMA_SYNC_TF32_PEAK, "unit": "TFLOP/s",
+            "frac": tf / MMA_SYNC_TF32_PEAK,
+            "peak_source": "measured on this pool's B200 for the instruction the kernel issues (mma.sync.m16n8k8 tf32 "
+                           "-> SASS HMMA, csrc/microbench.cu, profiles/r02g_microbench.json); MEASURED_PEAKS.json only "
+                           "holds the cuBLAS bf16 tcgen05 figure, which this gathered 16x8x8 product cannot be fed into "
+                           "(DESIGN.md section 5)",
+            "flops_per_launch": flops, "coefficient_pairs": pairs, "layers": layers,
+            "useful_flops_per_launch": 2.0 * visits,
+            "note": "achieved = dense-equivalent tf32 flops of one forward pass / CUDA-event time of the pass; 80 % "
+                    "of them multiply zeros of the block-sparse coefficient blocks (useful = 2 flops per voxel visit). "
+                    "frac_hbm = algorithmic HBM bytes (pattern values + pixel indices read, dose written) / time "
+                    "against the measured copy peak; frac_atomic = voxel visits/s against the measured rate of the "
+                    "shared-memory read-add-write the scatter form would need (accumulators live in registers here, so "
+                    "it can exceed 1)."})
+    else:
+        roofline.update({
+            "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+            "peak_source": how,
+            "note": "achieved = algorithmic HBM bytes of one forward pass (pattern values + pixel indices read, dose "
+                    "written) / CUDA-event time of the pass, against the measured copy peak.  The pass is NOT near "
+                    "that roof: its work is ~478 voxel visits per ray on data that stays on chip, and ncu shows it "
+                    "bound by instruction issue and on-chip atomics (plan 3: shared-memory red.add, plan 0: L2 "
+                    "red.global.add); frac_atomic = voxel visits/s against the measured peak rate of that atomic "
+                    "(SURVEY 8(d)) is the fraction that describes it."})
 
     line = None
     if rank == 0:

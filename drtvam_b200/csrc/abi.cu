@@ -429,6 +429,22 @@ int drtvam_scene_force_general(DrtvamScene* s, int32_t on) {
     return DRTVAM_OK;
 }
 
+int drtvam_scene_stat(DrtvamScene* s, int32_t which, uint64_t* value) {
+    if (!s) return fail(DRTVAM_E_INVALID, "scene handle is NULL");
+    if (!value) return fail(DRTVAM_E_INVALID, "NULL buffer");
+    DeviceGuard guard(s->device);
+    if (int rc = ensure_planar(s)) return rc;
+    const bool tables = s->zplan.valid && s->gplan.valid && s->P.regular_sampling;
+    switch (which) {
+        case 0: *value = tables ? static_cast<uint64_t>(s->gplan.pairs) : 0; break;
+        case 1: *value = s->zplan.valid ? static_cast<uint64_t>(s->zplan.nz) : 0; break;
+        case 2: *value = s->inside.valid ? s->inside.n_rec : 0; break;
+        case 3: *value = tables ? static_cast<uint64_t>(s->gplan.pairs) * 68u : 0; break;
+        default: return fail(DRTVAM_E_INVALID, "unknown statistic %d", which);
+    }
+    return DRTVAM_OK;
+}
+
 int drtvam_scene_set_target(DrtvamScene* s, const float* triangles_host, uint32_t n_triangles) {
     if (!s) return fail(DRTVAM_E_INVALID, "scene handle is NULL");
     if (n_triangles && !triangles_host) return fail(DRTVAM_E_INVALID, "NULL triangle buffer");

@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define DRTVAM_ABI_VERSION 10
+#define DRTVAM_ABI_VERSION 11
 #define DRTVAM_MAX_SURFACES 8
 #define DRTVAM_MAX_MESH_SURFACES 4
 
@@ -217,6 +217,13 @@ int drtvam_scene_plan(DrtvamScene *scene, uint64_t n_active, uint32_t spp);
 /* 0 = let the library choose, 1 = force the general tracer, 2 = force the
  * planar per-ray tile DDA where the scene is planar (A/B tests). */
 int drtvam_scene_force_general(DrtvamScene *scene, int32_t on);
+/* Sizes of the per-scene tables behind the planar kernels (bench.py's roofline is counted from them; the
+ * reference has no counterpart, its kernels are JIT-generated per call).  which:
+ *   0 = (4x4 patch, segment) coefficient pairs of the patch-gather forward (0 = tables not in use),
+ *   1 = voxel layers that receive dose from the DMD rows of this handle (inside the z window),
+ *   2 = target-crossing records of a surface-aware deterministic scene,
+ *   3 = bytes of the coefficient table of the patch-gather forward (64 B of coefficients + 4 B ray index per pair). */
+int drtvam_scene_stat(DrtvamScene *scene, int32_t which, uint64_t *value);
 
 /* A p : VolumeIntegrator.render (volume.py:18-56).  dose has
  * res_z*res_y*res_x*C floats (C = 2 when surface_aware; film.py:17-21,

@@ -3,6 +3,8 @@
 
     python tools/ncu_summary.py launches gpurun_out/X_launches.csv  > profiles/rNN_launches.csv
     python tools/ncu_summary.py details  gpurun_out/X_prof.ncu-rep  > profiles/rNN_details.txt
+    python tools/ncu_summary.py traffic  profiles/rNN_details.txt C2:plan2 planarg_mma_kernel<16>
+        -> adds DRAM bytes per launch of that kernel to profiles/ncu_traffic.json (bench.py's roofline.traffic)
 """
 import collections
 import csv
@@ -61,5 +63,42 @@ def details(path):
                 print(f"   {k} [{units[i]}] = {r[i]}")
 
 
+def traffic(path, key, kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the FIRST launch of `kernel` in a details file."""
+    import json
+    import os
+    import re
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    found, rd, wr, ms = False, None, None, None
+    for line in open(path):
+        if line.startswith("=="):
+            if found and rd is not None:
+                break
+            found = kernel in line
+            continue
+        if not found:
+            continue
+        m = re.match(r"\s+(\S+) \[(\w+)\] = ([\d.,]+)", line)
+        if not m:
+            continue
+        v = float(m.group(3).replace(",", ""))
+        if m.group(1) == "dram__bytes_read.sum":
+            rd = v * scale[m.group(2)]
+        elif m.group(1) == "dram__bytes_write.sum":
+            wr = v * scale[m.group(2)]
+        elif m.group(1) == "gpu__time_duration.sum":
+            ms = v * {"ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3}.get(m.group(2), 1.0)
+    if rd is None or wr is None:
+        sys.exit(f"{kernel}: no dram__bytes_* rows in {path}")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = os.path.join(root, "profiles", "ncu_traffic.json")
+    table = json.load(open(out)) if os.path.exists(out) else {}
+    table[key] = {"kernel": kernel, "forward_dram_bytes": rd + wr, "dram_bytes_read": rd, "dram_bytes_write": wr,
+                  "ncu_duration_ms": ms, "source": os.path.relpath(os.path.abspath(path), root) +
+                  " (ncu --set full --clock-control none, one launch)"}
+    json.dump(table, open(out, "w"), indent=1, sort_keys=True)
+    print(json.dumps(table[key]))
+
+
 if __name__ == "__main__":
-    {"launches": launches, "details": details}[sys.argv[1]](sys.argv[2])
+    {"launches": launches, "details": details, "traffic": traffic}[sys.argv[1]](*sys.argv[2:])
