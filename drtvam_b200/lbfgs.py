@@ -41,7 +41,8 @@ class Optimizer:
 
 
 class LinearLBFGS(Optimizer):
-    def __init__(self, lr=1.0, m=5, params=None, render_fn=None, loss_fn=None, search_it=20, dot=None, allsum=None):
+    def __init__(self, lr=1.0, m=5, params=None, render_fn=None, loss_fn=None, search_it=20, dot=None, allsum=None,
+                 consensus=None):
         super().__init__(lr, params)
         self.m = m                # history size
         self.p_old, self.g_old = {}, {}
@@ -54,6 +55,8 @@ class LinearLBFGS(Optimizer):
         # sum of a small tensor over the ranks that share the (sharded) pattern vector: with it the device
         # path needs ONE collective per iteration (the Gram matrix) instead of one per dot product
         self.allsum = allsum
+        # rank-mean of redundantly computed scalars, so that every rank takes the same Armijo decision
+        self.consensus = consensus
         self._alpha = None        # python float, or a device tensor {alpha, trials, loss} of the last step
         self._dev = {}            # device-path state per variable
 
@@ -177,6 +180,8 @@ class LinearLBFGS(Optimizer):
         # stages of 4 and then up to 16 trials: alpha = 1 is accepted in almost every iteration, and a stage
         # that finds the search over (S['out'][3]) returns in its first instruction
         f0 = loss.detach().to(torch.float64).reshape(1)
+        if self.consensus is not None:
+            f0 = self.consensus(f0)
         S['sums'].zero_()
         first = 0
         for count in (4, 16, 12):
@@ -190,6 +195,8 @@ class LinearLBFGS(Optimizer):
                     raise RuntimeError("the fused Armijo sweep became unavailable between two stages")
                 return None
             scale, term = stage
+            if self.consensus is not None:
+                S['sums'][first:first + count] = self.consensus(S['sums'][first:first + count])
             _lib.check(lib.drtvam_armijo_select(di, S['sums'].data_ptr(), first, first + count, float(scale), f0.data_ptr(),
                                                 term.data_ptr() if term is not None else None,
                                                 S['coef'][13:14].data_ptr(), 1e-4, S['out'].data_ptr(), st))
@@ -227,6 +234,8 @@ class LinearLBFGS(Optimizer):
             c1 = 1e-4
             vol = vol.detach()
             loss = loss.detach()
+            if self.consensus is not None:
+                loss = self.consensus(loss)
             trials = 0
             for _ in range(self.search_it):
                 trials += 1
@@ -235,6 +244,8 @@ class LinearLBFGS(Optimizer):
                     else vol + alpha * dvol
                 f_new = self.loss_fn(y_trial, params['projector.active_data']
                                      if 'projector.active_data' in params else next(iter(params.values())))
+                if self.consensus is not None:
+                    f_new = self.consensus(f_new.detach())
                 if bool((f_new <= loss + c1 * alpha * g_dot_z).all()):
                     break
                 alpha *= 0.5

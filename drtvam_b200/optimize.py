@@ -33,15 +33,27 @@ def load_scene(config):
         raise ValueError("The vial geometry must have a 'type' field.")
     if config['vial']['type'] not in geometries.keys():
         raise ValueError(f"Unknown vial geometry: '{config['vial']['type']}'")
-    vial = geometries[config['vial']['type']](config['vial'])
+    # the reference resolves mesh paths against the working directory only (optimize.py:15-79); a config
+    # loaded through the CLI also finds the vial and occluder meshes next to the config file
+    def resolve(path):
+        if not os.path.isabs(path) and not os.path.exists(path) and '_config_dir' in config:
+            return os.path.join(config['_config_dir'], path)
+        return path
+
+    vial_cfg = dict(config['vial'])
+    for key in ('filename_vial_outer', 'filename_vial_inner'):
+        if key in vial_cfg:
+            vial_cfg[key] = resolve(vial_cfg[key])
+    if 'occlusions' in vial_cfg:
+        vial_cfg['occlusions'] = [dict(o) | ({'filename': resolve(o['filename'])} if 'filename' in o else {})
+                                  for o in vial_cfg['occlusions']]
+    vial = geometries[config['vial']['type']](vial_cfg)
 
     if 'filename' not in config['target']:
         raise ValueError("Missing field 'filename' for the target shape.")
 
     # Scale and centre the target: T(center) S(size / max extent) T(-bbox centre)
-    filename = config['target']['filename']
-    if not os.path.isabs(filename) and not os.path.exists(filename) and '_config_dir' in config:
-        filename = os.path.join(config['_config_dir'], filename)
+    filename = resolve(config['target']['filename'])
     mesh_type = os.path.splitext(filename)[1][1:]
     verts, tris = load_mesh(filename)
     lo, hi = verts.min(0), verts.max(0)
@@ -180,8 +192,9 @@ def optimize(config, patterns_fwd=None, progress=True):
     if getattr(loss_fn, 'armijo_sweep', None) is not None:
         loss_fn2.armijo_sweep = lambda x, dx, direction, *a: loss_fn.armijo_sweep(x, dx, target, direction, *a)
 
+    consensus = parallel.make_consensus(None, world) if world > 1 else None
     opt = LinearLBFGS(loss_fn=loss_fn2, render_fn=render_fn, dot=parallel.make_dot(None, world) if world > 1 else None,
-                      allsum=parallel.make_sum(None, world) if world > 1 else None, **opt_cfg)
+                      allsum=parallel.make_sum(None, world) if world > 1 else None, consensus=consensus, **opt_cfg)
     opt[patterns_key] = params[patterns_key]
     n_steps = config.get('n_steps', 40)
     loss_hist = np.zeros(n_steps)
@@ -223,10 +236,12 @@ def optimize(config, patterns_fwd=None, progress=True):
             scene.projector.active_data = p
             vol = _RenderWithGrad(scene, integrator, sensor, spp, spp_grad, i, p)
             loss = loss_fn(vol, target, p)
-            loss_hist[i] = float(loss.detach())
+            # every rank holds the same all-reduced dose, but its loss sum uses atomics: the value that decides
+            # to stop is the rank mean, identical everywhere
+            loss_hist[i] = float(loss.detach() if consensus is None else consensus(loss.detach()))
             ev[1].record()
             loss.backward()
-            if float(loss.detach()) == 0.0:
+            if loss_hist[i] == 0.0:
                 print("Converged")
                 break
             opt.step(vol.detach(), loss.detach())
@@ -248,8 +263,9 @@ def optimize(config, patterns_fwd=None, progress=True):
         save_vol(vol_final, os.path.join(output, "final.exr"))
         np.save(os.path.join(output, "loss.npy"), loss_hist)
         np.save(os.path.join(output, "timing.npy"), timing_hist)
-    if world == 1:
-        imgs_final = scene.projector.patterns()
+    # the ranks' pattern shards -> the one pattern stack the reference saves (optimize.py:331-358)
+    imgs_final = scene.full_patterns()
+    if rank == 0:
         array = imgs_final.cpu().numpy()
         if config.get('save_pattern_images', True):
             print("Saving images...")

@@ -72,6 +72,23 @@ def make_sum(group=None, world_size: int = 1):
     return allsum
 
 
+def make_consensus(group=None, world_size: int = 1):
+    """Rank-mean of a tensor: identical bits on every rank afterwards.  Quantities that every rank computes
+    redundantly from the same all-reduced dose (loss sums, the Armijo candidates) can differ in their last
+    bits between ranks because their reductions use atomics; a back-tracking decision taken on them has to
+    be the same everywhere, or the ranks would step to different patterns."""
+    if world_size == 1:
+        return lambda v: v
+    import torch.distributed as dist
+
+    def consensus(v):
+        v = v.clone()
+        dist.all_reduce(v, op=dist.ReduceOp.SUM, group=group)
+        return v / world_size
+
+    return consensus
+
+
 def slab_grid(world_size: int, n_layers: int):
     """(angle groups A, z-slabs S) with A * S = world_size for a planar scene.  The planar kernels amortise one
     2-D walk over the layers of a block (up to 128), so a slab should keep ~100 layers: cutting thinner

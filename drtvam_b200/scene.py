@@ -257,6 +257,7 @@ class Scene:
         p = self.projector
         self.rank, self.world_size, self.group = rank, world_size, group
         n_full = p.active_pixels.numel()
+        self._full_active_pixels = p.active_pixels     # the unsharded list: gather_patterns / final pattern export
         if partition in ("auto", "zslab") and world_size > 1 and integrator is not None:
             rz = int(sensor.resolution()[2])
             A, S = grid if grid is not None else (slab_grid(world_size, rz) if partition == "auto" else (1, world_size))
@@ -287,6 +288,33 @@ class Scene:
         p.active_data = p.active_data[lo:hi].contiguous()
         self._shard_handles()
         return lo, hi, "angle"
+
+    _full_active_pixels = None
+
+    def gather_patterns(self, local=None):
+        """The pattern vector over the UNSHARDED active-pixel list, assembled from the ranks' shards (every
+        pixel is owned by exactly one rank, so a zero-filled scatter + all_reduce(SUM) is a gather); every
+        rank gets it.  The reference keeps one vector (optimize.py:331-358 saves it); this is the step that
+        makes a multi-GPU optimisation end with the same files."""
+        local = (self.projector.active_data if local is None else local).detach()
+        if self.world_size == 1 or self._full_active_pixels is None:
+            return local
+        full = torch.zeros(self._full_active_pixels.numel(), device=local.device, dtype=local.dtype)
+        full[self.shard_index.long()] = local
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized():
+            dist.all_reduce(full, op=dist.ReduceOp.SUM, group=self.group)
+        return full
+
+    def full_patterns(self, local=None):
+        """Dense [n_patterns, h, w] pattern images of the whole job (projector.py:100-105 for one rank)."""
+        p = self.projector
+        full = self.gather_patterns(local)
+        pixels = p.active_pixels if self._full_active_pixels is None or self.world_size == 1 else self._full_active_pixels
+        n, h, w = p.size()
+        out = torch.zeros(n * h * w, device=full.device, dtype=torch.float32)
+        out[pixels.long() & 0xFFFFFFFF] = full
+        return out.reshape(n, h, w)
 
     def _make_groups(self, A, S, a, sl):
         """Process groups of an A x S grid: the ranks that share a slab (they all-reduce its dose) and the

@@ -44,7 +44,7 @@ def _worker(rank, world, port, workdir, result):
             sys.path.insert(0, p)
     import oracle as orc
     from drtvam_b200.lbfgs import LinearLBFGS
-    from drtvam_b200.parallel import make_dot
+    from drtvam_b200.parallel import make_consensus, make_dot
     from helpers import build, pixels_np
 
     scene, integ, sensor, d, _ = build("C3", workdir, 16)
@@ -104,8 +104,21 @@ def _worker(rank, world, port, workdir, result):
     x_shard = run(A[:, cols], dot, True)
     x_full = run(A, None, False)
     err_lbfgs = float((x_shard - x_full[cols]).abs().max())
+    # the pattern shards come back as ONE vector / image stack in the order of the unsharded pixel list
+    # (what optimize() saves as patterns.npz at world > 1)
+    scene.projector.active_data = torch.from_numpy(p_all[lo:hi].copy())
+    err_gather = float((scene.gather_patterns() - torch.from_numpy(p_all)).abs().max())
+    imgs = scene.full_patterns().reshape(-1).numpy()
+    dense = np.zeros(imgs.size, np.float32)
+    dense[pix_all.astype(np.int64)] = p_all
+    err_gather = max(err_gather, float(np.abs(imgs - dense).max()))
+    # consensus: redundantly computed scalars that differ in the last bits become identical on every rank
+    c = make_consensus(None, world)(torch.tensor([1.0 + rank * 1e-15, 2.0], dtype=torch.float64))
+    both = [torch.zeros_like(c) for _ in range(world)]
+    dist.all_gather(both, c)
+    same = all(torch.equal(both[0], b_) for b_ in both)
     if rank == 0:
-        result.put((err_fwd, err_adj, err_dot, err_lbfgs))
+        result.put((err_fwd, err_adj, err_dot, err_lbfgs, err_gather, same))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -120,5 +133,62 @@ def test_two_rank_angle_sharding_gloo(workdir):
     for p in procs:
         p.join(180)
         assert p.exitcode == 0
-    err_fwd, err_adj, err_dot, err_lbfgs = result.get(timeout=10)
+    err_fwd, err_adj, err_dot, err_lbfgs, err_gather, same = result.get(timeout=10)
     assert err_fwd < 1e-12 and err_adj < 1e-12 and err_dot < 1e-9 and err_lbfgs < 1e-8
+    assert err_gather == 0.0 and same
+
+
+def _optimize_worker(rank, world, port, cfg, result):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)   # both ranks on cuda:0; gloo stages CUDA tensors
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    if root not in sys.path:
+        sys.path.insert(0, root)
+    from drtvam_b200.optimize import optimize
+    vol = optimize(cfg, progress=False)
+    if rank == 0:
+        result.put(vol.cpu().numpy())
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+def test_two_rank_optimize_saves_the_same_files_as_one_rank(workdir):
+    """optimize() at world size 2 (angle shards, both ranks on the one GPU of the test box, gloo): the run ends
+    with the files of a one-rank run (optimize.py:331-358) - patterns.npz holds the gathered pattern stack,
+    not a shard - and prints the same part."""
+    import copy
+    from test_optimization import analytic_reference, fixture_config
+    from drtvam_b200.optimize import optimize
+    cfg1 = fixture_config("box_hole_index_matched", workdir)
+    cfg1["regular_sampling"] = True          # same rays on one and on two ranks
+    cfg1["n_steps"] = 12
+    cfg2 = copy.deepcopy(cfg1)
+    cfg1["output"] += "_w1"
+    cfg2["output"] += "_w2"
+    vol1 = optimize(cfg1, progress=False).cpu().numpy()
+    ctx = mp.get_context("spawn")
+    result = ctx.Queue()
+    port = 29500 + (os.getpid() % 2000)
+    procs = [ctx.Process(target=_optimize_worker, args=(r, 2, port, cfg2, result)) for r in range(2)]
+    for p in procs:
+        p.start()
+    vol2 = result.get(timeout=600)
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    pat1 = np.load(os.path.join(cfg1["output"], "patterns.npz"))["patterns"]
+    pat2 = np.load(os.path.join(cfg2["output"], "patterns.npz"))["patterns"]
+    assert pat1.shape == pat2.shape == (200, 20, 200)
+    assert os.path.exists(os.path.join(cfg2["output"], "patterns_normalized_uint8.npz"))
+    # same iterates up to the summation order of the all-reduced dose and dots
+    rel = np.linalg.norm(pat2 - pat1) / np.linalg.norm(pat1)
+    relv = np.linalg.norm(vol2 - vol1) / np.linalg.norm(vol1)
+    print("two-rank optimize: patterns", rel, "final dose", relv)
+    assert rel < 1e-2 and relv < 1e-3
+    l1, l2 = np.load(os.path.join(cfg1["output"], "loss.npy")), np.load(os.path.join(cfg2["output"], "loss.npy"))
+    assert np.allclose(l1, l2, rtol=1e-3, atol=1e-6 * l1[0])
+    thr = (cfg2["loss"]["tl"] + cfg2["loss"]["tu"]) / 2
+    agree = np.mean(np.isclose(analytic_reference(), vol2[:, :, :, 0] > thr)) * 100
+    assert agree > 97.0
