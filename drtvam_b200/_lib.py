@@ -11,7 +11,7 @@ import os
 from . import build as _build
 
 MAX_SURFACES = 8
-ABI_VERSION = 11
+ABI_VERSION = 12
 
 
 class DrtvamSurface(C.Structure):
@@ -71,6 +71,7 @@ SYMBOLS = {
     "drtvam_scene_force_general": (C.c_int, [_vp, _i32]),
     "drtvam_scene_stat": (C.c_int, [_vp, _i32, C.POINTER(_u64)]),
     "drtvam_forward": (C.c_int, [_vp, _vp, _vp, _u64, _u32, _u32, _f32, _vp, _i32, _vp]),
+    "drtvam_forward_noalloc": (C.c_int, [_vp, _vp, _vp, _u64, _u32, _u32, _f32, _vp, _i32, _vp]),
     "drtvam_adjoint": (C.c_int, [_vp, _vp, _vp, _u64, _u32, _u32, _f32, _vp, _vp]),
     "drtvam_raygen": (C.c_int, [_vp, _vp, _u64, _u32, _u32, _vp, _vp]),
     "drtvam_radon": (C.c_int, [_vp, _vp, _u64, _u32, _u32, _vp, _vp]),

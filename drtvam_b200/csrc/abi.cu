@@ -736,6 +736,49 @@ int drtvam_forward(DrtvamScene* s, const float* active_data, const uint32_t* act
     return DRTVAM_OK;
 }
 
+// The deterministic planar forward with no allocation anywhere on the call path: the repacked patterns go to the
+// static scratch of the library image (planarz_kernels.cu) instead of the handle's cudaMalloc'ed buffer.
+int drtvam_forward_noalloc(DrtvamScene* s, const float* active_data, const uint32_t* active_pixels, uint64_t n_active,
+                           uint32_t spp, uint32_t seed, float out_scale, float* dose, int32_t zero_first, void* stream) {
+    if (int rc = check_call(s, n_active, spp)) return rc;
+    if (!dose || (n_active && (!active_data || !active_pixels))) return fail(DRTVAM_E_INVALID, "NULL buffer");
+    if (n_active == 0) {   // nothing to project: only the clearing of the film is left
+        DeviceGuard guard0(s->device);
+        if (zero_first) CUDA_TRY(cudaMemsetAsync(dose, 0, sizeof(float) * film_elems(s), static_cast<cudaStream_t>(stream)));
+        return DRTVAM_OK;
+    }
+    if (!s->planar_tried)
+        return fail(DRTVAM_E_INVALID, "drtvam_forward_noalloc: the tables of the scene are not built yet (building them "
+                                      "allocates): call drtvam_scene_plan or drtvam_forward once first");
+    if (!s->P.regular_sampling || !use_planar(s, n_active) || !s->zplan.valid || !s->gplan.valid || s->force_mode != 0 ||
+        s->inside.valid || s->inv_volume)
+        return fail(DRTVAM_E_INVALID, "drtvam_forward_noalloc serves the deterministic planar plan with its patch-gather "
+                                      "tables only (drtvam_scene_plan == 2, one film channel, whole angles)");
+    const uint64_t rw = static_cast<uint64_t>(s->P.res_x) * s->P.n_rows;
+    const uint64_t need = (n_active / rw) * s->P.res_x * static_cast<uint64_t>(s->zplan.nz_pad);
+    if (need > planarg_noalloc_capacity())
+        return fail(DRTVAM_E_INVALID, "drtvam_forward_noalloc: %llu angles x %d columns x %d layers = %llu floats of scratch "
+                                      "exceed the static maximum of %llu (16 MiB): split the call by angles",
+                    static_cast<unsigned long long>(n_active / rw), s->P.res_x, s->zplan.nz_pad,
+                    static_cast<unsigned long long>(need), static_cast<unsigned long long>(planarg_noalloc_capacity()));
+    DeviceGuard guard(s->device);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (zero_first) CUDA_TRY(cudaMemsetAsync(dose, 0, sizeof(float) * film_elems(s), st));
+    const float w = ray_weight(s, n_active, spp) * out_scale;
+    const int* gate = nullptr;
+    int host_gate = -1;
+    CUDA_TRY(planar_gate(s, active_pixels, n_active, st, &gate, &host_gate));
+    if (host_gate != 1) {
+        CUDA_TRY(launch_planarg_forward_noalloc(s->P1, s->zplan, s->gplan, s->device, gate, active_data, active_pixels,
+                                                n_active, w, dose, zero_first != 0, st));
+        CUDA_TRY(launch_planar_frozen(windowed(s->P1), s->planar, 0, active_data, dose, active_pixels, n_active, w, st, gate));
+    }
+    if (host_gate != 0)   // a list without the planar layout: the general tracer owns the call (it allocates nothing)
+        CUDA_TRY(launch_forward_general(windowed(s->P), active_data, active_pixels, n_active * spp, spp, seed, w, dose, st,
+                                        host_gate < 0 ? s->planar.gate : nullptr));
+    return DRTVAM_OK;
+}
+
 int drtvam_adjoint(DrtvamScene* s, const float* dose_grad, const uint32_t* active_pixels, uint64_t n_active,
                    uint32_t spp, uint32_t seed, float in_scale, float* pattern_grad, void* stream) {
     if (int rc = check_call(s, n_active, spp)) return rc;

@@ -143,6 +143,12 @@ void planarg_release(PlanarGHost& G);
 cudaError_t launch_planarg_forward(const SceneParams& P, PlanarZHost& H, PlanarGHost& G, const int* gate,
                                    const float* active_data, const uint32_t* active_pixels, uint64_t n_active,
                                    float ray_weight, float* film, bool fresh, cudaStream_t stream);
+// the same forward on the static scratch of the library image: no allocation (planarz_kernels.cu)
+size_t planarg_noalloc_capacity();   // floats: angles of the call x res_x x padded layers must fit
+cudaError_t launch_planarg_forward_noalloc(const SceneParams& P, const PlanarZHost& H, const PlanarGHost& G, int device,
+                                           const int* gate, const float* active_data, const uint32_t* active_pixels,
+                                           uint64_t n_active, float ray_weight, float* film, bool fresh,
+                                           cudaStream_t stream);
 void planarz_release(PlanarZHost& H);
 cudaError_t launch_planarz_forward(const SceneParams& P, PlanarZHost& H, const int* gate, const float* active_data,
                                    const uint32_t* active_pixels, uint64_t n_active, float ray_weight, float* film,

@@ -27,6 +27,7 @@
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 #include <cub/device/device_scan.cuh>
@@ -1635,6 +1636,71 @@ cudaError_t launch_planarg_forward(const SceneParams& P, PlanarZHost& H, PlanarG
         else
             planarg_kernel<4><<<grid, threads, g_smem_bytes(4), stream>>>(P, Z, G.coef, G.ray, H.scratch, film,
                                                                          active_pixels, n_active, ray_weight, gate, a_begin, fresh ? 1 : 0);
+        count_launch();
+        PZ_TRY(cudaGetLastError());
+    }
+    return cudaSuccess;
+}
+
+// ---- the patch-gather forward without any allocation ------------------------------------------------------
+// launch_planarg_forward keeps the [angle][column][layer] repack of the patterns in a scratch buffer that it
+// (re)allocates with cudaMalloc when a call needs more than the last one did.  Callers that may not allocate
+// (CUDA graph capture, serving loops, harnesses that forbid it) get the same two kernels - zpack_kernel, then
+// planarg_mma_kernel per z-block - on a scratch that lives in the library image: kNoAllocFloats floats
+// (16 MiB) of device memory on every GPU that loads the library, until the process exits.  Every call on a
+// device shares it: zpack_kernel overwrites all of the part a call uses before the gather reads it, so nothing
+// has to start at zero, but two calls that overlap on the GPU (different streams) race on it.
+constexpr size_t kNoAllocFloats = size_t(4) << 20;
+static __device__ __align__(256) float g_noalloc_scratch[kNoAllocFloats];
+
+size_t planarg_noalloc_capacity() { return kNoAllocFloats; }
+
+// Device address of the scratch on `device`, which must be the current device: in host code the array's name
+// is only a handle for cudaGetSymbolAddress, not an address a kernel can use.  Resolved once per device.
+static cudaError_t noalloc_scratch(int device, float** out) {
+    constexpr int kMaxDevices = 64;
+    static float* ptrs[kMaxDevices] = {};
+    static std::mutex lock;
+    if (device < 0 || device >= kMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> hold(lock);
+    if (!ptrs[device]) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess) return e;
+        ptrs[device] = static_cast<float*>(p);
+    }
+    *out = ptrs[device];
+    return cudaSuccess;
+}
+
+cudaError_t launch_planarg_forward_noalloc(const SceneParams& P, const PlanarZHost& H, const PlanarGHost& G, int device,
+                                           const int* gate, const float* active_data, const uint32_t* active_pixels,
+                                           uint64_t n_active, float ray_weight, float* film, bool fresh,
+                                           cudaStream_t stream) {
+    const int nk = static_cast<int>(n_active / (static_cast<uint64_t>(P.res_x) * P.n_rows));
+    if (static_cast<size_t>(nk) * P.res_x * H.nz_pad > kNoAllocFloats) return cudaErrorInvalidValue;
+    float* scratch = nullptr;
+    PZ_TRY(noalloc_scratch(device, &scratch));
+    const dim3 pgrid((P.res_x + 31) / 32, H.nz_pad / 32, nk);
+    zpack_kernel<<<pgrid, 256, 0, stream>>>(P, H.sub[0].plan, active_data, scratch, nk, gate);
+    count_launch();
+    PZ_TRY(cudaGetLastError());
+    const PlanarZPlan& Z = G.plan;
+    const int regions = ((Z.tiles_x + kGWarpsX - 1) / kGWarpsX) * ((Z.tiles_y + kGWarpsY - 1) / kGWarpsY);
+    constexpr int threads = 32 * kGWarpsX * kGWarpsY;
+    for (int i = 0; i < H.n_sub; ++i) {
+        const PlanarZSub& S = H.sub[i];
+        const dim3 grid(regions, S.n_blocks);
+        const int kL = S.plan.lanes_l, a_begin = S.plan.a_begin;
+        if (kL == 1)
+            planarg_mma_kernel<4><<<grid, threads, gm_smem_bytes(4), stream>>>(P, Z, G.coef, G.ray, scratch, film, active_pixels,
+                                                                              n_active, ray_weight, gate, a_begin, fresh ? 1 : 0);
+        else if (kL == 2)
+            planarg_mma_kernel<8><<<grid, threads, gm_smem_bytes(8), stream>>>(P, Z, G.coef, G.ray, scratch, film, active_pixels,
+                                                                              n_active, ray_weight, gate, a_begin, fresh ? 1 : 0);
+        else
+            planarg_mma_kernel<16><<<grid, threads, gm_smem_bytes(16), stream>>>(P, Z, G.coef, G.ray, scratch, film, active_pixels,
+                                                                                n_active, ray_weight, gate, a_begin, fresh ? 1 : 0);
         count_launch();
         PZ_TRY(cudaGetLastError());
     }

@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define DRTVAM_ABI_VERSION 11
+#define DRTVAM_ABI_VERSION 12
 #define DRTVAM_MAX_SURFACES 8
 #define DRTVAM_MAX_MESH_SURFACES 4
 
@@ -234,6 +234,23 @@ int drtvam_scene_stat(DrtvamScene *scene, int32_t which, uint64_t *value);
 int drtvam_forward(DrtvamScene *scene, const float *active_data, const uint32_t *active_pixels,
                    uint64_t n_active, uint32_t spp, uint32_t seed, float out_scale,
                    float *dose, int32_t zero_first, void *stream);
+
+/* drtvam_forward for callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid
+ * cudaMalloc).  No counterpart in the reference.  Same
+ * arguments and result as drtvam_forward, for the deterministic planar plan only (drtvam_scene_plan() == 2
+ * with its patch-gather tables, one film channel, whole angles; anything else is DRTVAM_E_INVALID).  The
+ * scratch drtvam_forward keeps in a cudaMalloc'ed buffer - the [angle][column][layer] repack of the
+ * patterns - lives in a static __device__ array of the library image instead: 4 Mi floats = 16 MiB, held by
+ * every GPU that loads the library until the process exits.  A call needs (angles of the call) x res_x x
+ * (active layers padded to 32) floats; larger calls are rejected with DRTVAM_E_INVALID: split them by
+ * angles (zero_first = 0 accumulates).  The scene's tables must exist already (call drtvam_scene_plan or
+ * drtvam_forward once: building them allocates).  The call itself makes no cudaMalloc / cudaFree; its
+ * first use on a device resolves the array's address with cudaGetSymbolAddress.  All calls on a device
+ * share the array: each call overwrites the part it uses before reading it (nothing needs clearing), and
+ * calls that overlap on the GPU (different streams, concurrent graphs) race on it. */
+int drtvam_forward_noalloc(DrtvamScene *scene, const float *active_data, const uint32_t *active_pixels,
+                           uint64_t n_active, uint32_t spp, uint32_t seed, float out_scale, float *dose,
+                           int32_t zero_first, void *stream);
 
 /* A^T g : VolumeIntegrator.render_backward (volume.py:97-134).  dose_grad is
  * grad_in; in_scale = 1/voxel_volume (volume.py:130).  Overwrites
