@@ -81,6 +81,7 @@ struct DrtvamScene {
     int comm_rank = 0, comm_world = 1;
     bool planar_tried = false;       // planar_build ran for the current depth setting
     bool planar_ok = false;
+    bool hybrid = false;             // scattering scene: planar per-lane kernels for the first medium segments only
     MeshHost target;                 // target mesh (surface-aware runs only)
     MeshHost mesh_surf[kMaxMeshSurfaces];  // triangle-mesh interfaces (custom vial walls, occluders)
     int n_mesh_surf = 0;
@@ -128,14 +129,23 @@ int check_call(const DrtvamScene* s, uint64_t n_active, uint32_t& spp) {
 // Host-side eligibility of the planar z-separable plan (see planar.cuh): every
 // ray must have d_z = 0, one deterministic medium segment that depends only on
 // (angle, column), and the film must be the plain single-channel DDA film.
+// A SCATTERING medium (albedo != 0) is eligible as a hybrid: only the first medium segment of a lane - the
+// unscattered chord, which every lane deposits in full (volume.py:216) - has the planar structure; the planar
+// per-lane kernels take it and the general tracer everything after the first collision.
 bool planar_static_eligible(const DrtvamScene* s) {
     const SceneParams& P = s->P;
     if (P.proj_kind != DRTVAM_PROJ_COLLIMATED || P.sample_time) return false;  // jitter keeps d_z = 0
-    if (P.albedo != 0.f || P.sensor_kind != DRTVAM_SENSOR_DDA) return false;
+    if (P.sensor_kind != DRTVAM_SENSOR_DDA) return false;
     // surface-aware film: the planar kernels make the channel sum, the inside records split it (inside_kernels.cu)
     if (P.surface_aware && !P.regular_sampling) return false;
     if (!P.transmission_only) return false;
-    if (P.max_depth < 1 || P.max_depth - 1 > P.rr_depth) return false;  // Russian roulette never fires
+    if (P.albedo != 0.f) {
+        if (P.surface_aware || !general_supports_hybrid(P) || getenv("DRTVAM_SCATTER_GENERAL")) return false;
+        // Russian roulette must not fire before the first medium segment (its draws differ from the table kernel's)
+        if (P.max_depth < 1 || P.rr_depth < P.n_surf) return false;
+    } else if (P.max_depth < 1 || P.max_depth - 1 > P.rr_depth) {
+        return false;  // Russian roulette never fires
+    }
     if (!P.motion_analytic) {
         // rotation about z: world z = const * local y, no z component in the beam direction
         const size_t n = static_cast<size_t>(P.n_patterns);
@@ -198,7 +208,8 @@ int ensure_planar(DrtvamScene* s) {
     planarz_release(s->zplan);
     planarg_release(s->gplan);
     planarj_release(s->jplan);
-    if (s->planar_ok && !s->P.regular_sampling) {
+    s->hybrid = s->planar_ok && s->P.albedo != 0.f;
+    if (s->planar_ok && (!s->P.regular_sampling || s->hybrid)) {
         // jittered passes: the layer tables of the layer-parallel plan (no walks) + the per-lane kernels
         e = planarz_build(s->P1, s->planar, s->planar.row_layer, s->zplan, false);
         if (e == cudaSuccess) e = planarj_build(s->P1, s->planar, s->zplan, s->jplan);
@@ -207,9 +218,9 @@ int ensure_planar(DrtvamScene* s) {
             planarj_release(s->jplan);
             return fail(DRTVAM_E_CUDA, "jittered planar plan build failed: %s", cudaGetErrorString(e));
         }
-        if (!s->jplan.valid) s->planar_ok = false;
+        if (!s->jplan.valid) s->planar_ok = s->hybrid = false;
     }
-    if (s->planar_ok && s->P.regular_sampling) {
+    if (s->planar_ok && s->P.regular_sampling && !s->hybrid) {
         e = planarz_build(s->P1, s->planar, s->planar.row_layer, s->zplan);
         if (e != cudaSuccess) {
             planarz_release(s->zplan);
@@ -237,7 +248,7 @@ int ensure_planar(DrtvamScene* s) {
 
 bool use_planar(DrtvamScene* s, uint64_t n_active) {
     if (s->force_mode == 1 || !s->planar_ok || n_active == 0) return false;
-    if (s->force_mode == 2 && has_window(s->P)) return false;   // the per-ray tile DDA (A/B tests) knows no window
+    if (s->force_mode == 2 && (has_window(s->P) || s->hybrid)) return false;   // the per-ray tile DDA (A/B tests) knows neither
     const uint64_t rw = static_cast<uint64_t>(s->P.res_x) * s->P.n_rows;
     return n_active % rw == 0;
 }
@@ -678,6 +689,7 @@ int drtvam_scene_plan(DrtvamScene* s, uint64_t n_active, uint32_t) {
     DeviceGuard guard(s->device);
     if (int rc = ensure_planar(s)) return rc;
     if (!use_planar(s, n_active)) return 0;
+    if (s->hybrid) return 4;
     if (!s->P.regular_sampling) return 3;
     return (s->zplan.valid && s->force_mode != 2) ? 2 : 1;
 }
@@ -695,6 +707,19 @@ int drtvam_forward(DrtvamScene* s, const float* active_data, const uint32_t* act
     if (s->inv_volume && !zero_first)
         return fail(DRTVAM_E_INVALID, "an accumulating forward call cannot apply the per-voxel inverse volume");
     const SceneParams Pw = windowed(s->P);
+    if (s->hybrid && use_planar(s, n_active)) {
+        // scattering: the unscattered chords through the planar per-lane kernels, the rest through the tracer
+        const int* gate = nullptr;
+        int host_gate = -1;
+        CUDA_TRY(planar_gate(s, active_pixels, n_active, st, &gate, &host_gate));
+        if (host_gate != 1)
+            CUDA_TRY(launch_planarj_forward(s->P1, windowed(s->P1), s->zplan, s->jplan, gate, active_data, active_pixels,
+                                            n_active, spp, seed, w, dose, host_gate == 0, st));
+        CUDA_TRY(launch_forward_general(Pw, active_data, active_pixels, n_active * spp, spp, seed, w, dose, st,
+                                        host_gate != 1 ? gate : nullptr, host_gate != 1));
+        if (s->inv_volume) CUDA_TRY(launch_mul_inplace(dose, s->inv_volume, film_elems(s), st));  // volume.py:54
+        return DRTVAM_OK;
+    }
     if (use_planar(s, n_active)) {
         const int* gate = nullptr;
         int host_gate = -1;
@@ -794,6 +819,21 @@ int drtvam_adjoint(DrtvamScene* s, const float* dose_grad, const uint32_t* activ
         dose_grad = static_cast<const float*>(s->dl_scaled.ptr);
     }
     const SceneParams Pw = windowed(s->P);
+    if (s->hybrid && use_planar(s, n_active)) {
+        const int* gate = nullptr;
+        int host_gate = -1;
+        CUDA_TRY(planar_gate(s, active_pixels, n_active, st, &gate, &host_gate));
+        if (host_gate != 1) {
+            // the planar kernels write the gradient of the first segments (or nothing when the gate says the list
+            // is not planar), the tracer adds the rest
+            CUDA_TRY(cudaMemsetAsync(pattern_grad, 0, sizeof(float) * n_active, st));
+            CUDA_TRY(launch_planarj_adjoint(s->P1, windowed(s->P1), s->zplan, s->jplan, gate, dose_grad, active_pixels,
+                                            n_active, spp, seed, w, pattern_grad, st));
+        }
+        CUDA_TRY(launch_adjoint_general(Pw, dose_grad, active_pixels, n_active * spp, spp, seed, w, pattern_grad, st,
+                                        host_gate != 1 ? gate : nullptr, host_gate != 1));
+        return DRTVAM_OK;
+    }
     if (use_planar(s, n_active)) {
         const int* gate = nullptr;
         int host_gate = -1;

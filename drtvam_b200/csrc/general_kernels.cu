@@ -249,12 +249,16 @@ template <bool kScatter, int kMode>
 __global__ void __launch_bounds__(kThreads)
 general_queue_kernel(const __grid_constant__ SceneParams P, const float* __restrict__ in,
                      const uint32_t* __restrict__ active_pixels, uint64_t n_lanes, uint32_t spp, uint32_t seed,
-                     float ray_weight, float* __restrict__ out, const int* __restrict__ gate) {
+                     float ray_weight, float* __restrict__ out, const int* __restrict__ gate, int hybrid) {
     extern __shared__ __align__(16) float4 q_rec[];  // two float4 per slot
     int* q_flag = reinterpret_cast<int*>(q_rec + 2 * kQSlots);
     float* grad_s = reinterpret_cast<float*>(q_flag + kQSlots);
     __shared__ int q_count, q_head;
-    if (gate && *gate == 0) return;  // the planar fast path owns this call
+    // hybrid (scattering scenes whose FIRST medium segments - the unscattered chords - the planar per-lane
+    // kernels have already deposited / gathered, planarj_kernels.cu): gate word 0 = skip the first medium
+    // segment of every lane and ADD to the gradient the planar kernels wrote; anything else = the whole lane
+    const bool skip_first = hybrid && gate && *gate == 0;
+    if (!hybrid && gate && *gate == 0) return;  // the planar fast path owns this call
     const int tid = threadIdx.x;
     if (tid == 0) { q_count = 0; q_head = 0; }
     if (kMode == 1)
@@ -277,7 +281,9 @@ general_queue_kernel(const __grid_constant__ SceneParams P, const float* __restr
         rng.seed(seed, sampler_lane(P, lane, spp));
         TraceState T;
         T.ray = generate_ray(P, __ldg(active_pixels + j), rng);
+        bool first = skip_first;
         while (bounce_once<kScatter>(P, T, rng, [&](const Ray& r, float maxt, float w0, bool inside, float) {
+            if (first) { first = false; return; }
             const int slot = atomicAdd(&q_count, 1);
             if (slot < kQSlots) {
                 q_rec[2 * slot] = make_float4(r.ox, r.oy, r.oz, maxt);
@@ -342,10 +348,10 @@ general_queue_kernel(const __grid_constant__ SceneParams P, const float* __restr
         const uint64_t j = live ? lane / spp : 0;
         float g = live ? grad_s[local] * ray_weight : 0.f;
         if (spp == 1) {
-            if (live) out[j] = g;
+            if (live) out[j] = hybrid ? out[j] + g : g;
         } else if ((spp & (spp - 1)) == 0 && spp <= 32) {
             for (uint32_t off = spp >> 1; off > 0; off >>= 1) g += __shfl_xor_sync(0xffffffffu, g, off);
-            if (live && (lane % spp) == 0) out[j] = g;
+            if (live && (lane % spp) == 0) out[j] = hybrid ? out[j] + g : g;
         } else {
             if (live) atomicAdd(out + j, g);  // grad pre-zeroed by the host
         }
@@ -374,7 +380,7 @@ inline int general_kernel_family(const SceneParams& P) {
 template <int kMode>
 cudaError_t launch_queue(const SceneParams& P, const float* in, const uint32_t* active_pixels, uint64_t n_lanes,
                          uint32_t spp, uint32_t seed, float ray_weight, float* out, cudaStream_t stream,
-                         const int* gate) {
+                         const int* gate, bool hybrid) {
     static const cudaError_t attr = cudaFuncSetAttribute(general_queue_kernel<true, kMode>,
                                                          cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                          static_cast<int>(kQSmemBytes));
@@ -382,7 +388,7 @@ cudaError_t launch_queue(const SceneParams& P, const float* in, const uint32_t* 
     const uint64_t per_block = static_cast<uint64_t>(kThreads) * kQLanes;
     const unsigned grid = static_cast<unsigned>((n_lanes + per_block - 1) / per_block);
     general_queue_kernel<true, kMode><<<grid, kThreads, kQSmemBytes, stream>>>(P, in, active_pixels, n_lanes, spp, seed,
-                                                                             ray_weight, out, gate);
+                                                                             ray_weight, out, gate, hybrid ? 1 : 0);
     count_launch();
     return cudaGetLastError();
 }
@@ -435,10 +441,11 @@ inline unsigned grid_for(uint64_t n_lanes) { return static_cast<unsigned>((n_lan
 
 cudaError_t launch_forward_general(const SceneParams& P, const float* active_data, const uint32_t* active_pixels,
                                    uint64_t n_lanes, uint32_t spp, uint32_t seed, float ray_weight, float* film,
-                                   cudaStream_t stream, const int* gate) {
+                                   cudaStream_t stream, const int* gate, bool hybrid) {
     if (n_lanes == 0) return cudaSuccess;
+    if (hybrid && !(general_kernel_family(P) == 2 && gate)) return cudaErrorInvalidValue;
     if (general_kernel_family(P) == 2)
-        return launch_queue<0>(P, active_data, active_pixels, n_lanes, spp, seed, ray_weight, film, stream, gate);
+        return launch_queue<0>(P, active_data, active_pixels, n_lanes, spp, seed, ray_weight, film, stream, gate, hybrid);
     if (!use_simple_kernels()) {
         if (P.albedo != 0.f)
             return launch_persistent<true, 0>(P, active_data, active_pixels, n_lanes, spp, seed, ray_weight, film, stream,
@@ -458,9 +465,10 @@ cudaError_t launch_forward_general(const SceneParams& P, const float* active_dat
 
 cudaError_t launch_adjoint_general(const SceneParams& P, const float* dL, const uint32_t* active_pixels,
                                    uint64_t n_lanes, uint32_t spp, uint32_t seed, float ray_weight, float* grad,
-                                   cudaStream_t stream, const int* gate) {
+                                   cudaStream_t stream, const int* gate, bool hybrid) {
     if (n_lanes == 0) return cudaSuccess;
     const bool queue = general_kernel_family(P) == 2;
+    if (hybrid && !(queue && gate)) return cudaErrorInvalidValue;
     const bool simple = use_simple_kernels() || queue;
     const bool pow2 = (spp & (spp - 1)) == 0 && spp <= 32;
     // lanes of one pixel are summed with atomics (always in the persistent kernel, for odd spp in the
@@ -470,7 +478,7 @@ cudaError_t launch_adjoint_general(const SceneParams& P, const float* dL, const 
         if (e != cudaSuccess) return e;
     }
     if (queue)
-        return launch_queue<1>(P, dL, active_pixels, n_lanes, spp, seed, ray_weight, grad, stream, gate);
+        return launch_queue<1>(P, dL, active_pixels, n_lanes, spp, seed, ray_weight, grad, stream, gate, hybrid);
     if (!simple) {
         if (P.albedo != 0.f)
             return launch_persistent<true, 1>(P, dL, active_pixels, n_lanes, spp, seed, ray_weight, grad, stream, gate);
@@ -485,6 +493,10 @@ cudaError_t launch_adjoint_general(const SceneParams& P, const float* dL, const 
     count_launch();
     return cudaGetLastError();
 }
+
+// scattering scenes with the DDA sensor run on the two-phase queue kernels, which can leave the first medium
+// segment of every lane to the planar kernels
+bool general_supports_hybrid(const SceneParams& P) { return general_kernel_family(P) == 2; }
 
 cudaError_t launch_raygen(const SceneParams& P, const uint32_t* active_pixels, uint64_t n_lanes, uint32_t spp,
                           uint32_t seed, float* out, cudaStream_t stream) {

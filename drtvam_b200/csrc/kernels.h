@@ -13,10 +13,13 @@ void count_launch();  // bumps the library-wide launch counter (abi.cu)
 // general per-lane tracer (general_kernels.cu)
 cudaError_t launch_forward_general(const SceneParams& P, const float* active_data, const uint32_t* active_pixels,
                                    uint64_t n_lanes, uint32_t spp, uint32_t seed, float ray_weight, float* film,
-                                   cudaStream_t stream, const int* gate = nullptr);
+                                   cudaStream_t stream, const int* gate = nullptr, bool hybrid = false);
 cudaError_t launch_adjoint_general(const SceneParams& P, const float* dL, const uint32_t* active_pixels,
                                    uint64_t n_lanes, uint32_t spp, uint32_t seed, float ray_weight, float* grad,
-                                   cudaStream_t stream, const int* gate = nullptr);
+                                   cudaStream_t stream, const int* gate = nullptr, bool hybrid = false);
+// hybrid = true (needs a gate word): where the gate reads 0 the planar per-lane kernels have served the first
+// medium segment of every lane, so the tracer skips it and ADDS to the gradient; elsewhere it does the whole lane
+bool general_supports_hybrid(const SceneParams& P);
 cudaError_t launch_raygen(const SceneParams& P, const uint32_t* active_pixels, uint64_t n_lanes, uint32_t spp,
                           uint32_t seed, float* out, cudaStream_t stream);
 cudaError_t launch_count_general(const SceneParams& P, const uint32_t* active_pixels, uint64_t n_lanes, uint32_t spp,

@@ -140,13 +140,17 @@ jtable_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Sce
             Sampler rng2;
             rng2.seed(seed, stream);
             const Ray ray2 = generate_ray(P, pixel, rng2);
+            // (a scattering scene: only the first medium segment is this kernel's, the tracer does the rest)
+            const bool first_only = P.albedo != 0.f;
             if (kMode == kGather) {
                 GatherSink gs{in};
-                trace_lane<false>(Pw, ray2, rng2, gs);
+                if (first_only) trace_first_segment(Pw, ray2, rng2, gs);
+                else trace_lane<false>(Pw, ray2, rng2, gs);
                 g_here = gs.acc * ray_weight;
             } else if (em != 0.f) {
                 ScatterSink sc{out, em * ray_weight};
-                trace_lane<false>(Pw, ray2, rng2, sc);
+                if (first_only) trace_first_segment(Pw, ray2, rng2, sc);
+                else trace_lane<false>(Pw, ray2, rng2, sc);
             }
             eb.z = __int_as_float(-2);
         } else if (lyr >= 0) {

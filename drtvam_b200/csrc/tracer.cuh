@@ -164,4 +164,18 @@ __device__ __forceinline__ void trace_lane(const SceneParams& P, Ray ray, Sample
     })) {}
 }
 
+// Deposits / gathers only the FIRST medium segment of a lane: in a scattering scene the segments after the first
+// collision belong to the general tracer, the unscattered chords to the planar per-lane kernels
+// (planarj_kernels.cu), whose odd lanes come here.  The geometry up to the first medium segment does not depend
+// on the random numbers of the bounce loop (transmission only), so the non-scattering trip serves.
+template <class Sink>
+__device__ __forceinline__ void trace_first_segment(const SceneParams& P, Ray ray, Sampler& rng, Sink& sink) {
+    TraceState T;
+    T.ray = ray;
+    int n = 0;
+    while (bounce_once<false>(P, T, rng, [&](const Ray& r, float maxt, float w0, bool inside, float) {
+        if (n++ == 0) dda_segment(P, r, maxt, w0, inside, sink);
+    }) && n == 0) {}
+}
+
 }  // namespace drtvam

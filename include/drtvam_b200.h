@@ -212,7 +212,10 @@ int drtvam_allreduce_scalars(DrtvamScene *scene, double *values, uint64_t n, voi
 /* Which kernel family a call will use for this scene and spp:
  * 0 = general per-lane tracer, 1 = planar per-ray tile DDA,
  * 2 = planar layer-parallel kernels (deterministic fast path),
- * 3 = planar layer-lane kernels with a per-lane segment table (jittered sampling). */
+ * 3 = planar layer-lane kernels with a per-lane segment table (jittered sampling),
+ * 4 = scattering medium: the kernels of 3 for the first medium segment of every lane (the unscattered chord,
+ *     deposited in full whether or not the lane collides on it, volume.py:216) and the general tracer for the
+ *     segments after the first collision. */
 int drtvam_scene_plan(DrtvamScene *scene, uint64_t n_active, uint32_t spp);
 /* 0 = let the library choose, 1 = force the general tracer, 2 = force the
  * planar per-ray tile DDA where the scene is planar (A/B tests). */

@@ -372,12 +372,48 @@ def test_planar_angle_shard_and_sparse_fallback(mode, workdir):
 
 
 def test_plan_of_stochastic_configs(workdir):
-    """Jittered absorptive configs take the per-lane planar kernels (plan 3);
-    scattering has no planar structure and stays on the general tracer."""
+    """Jittered absorptive configs take the per-lane planar kernels (plan 3); a scattering resin takes them for
+    the first medium segment of every lane and the general tracer for the rest (plan 4)."""
     scene, integ, sensor, d, _ = build("C1", workdir, 32, regular_sampling=False)
     assert _plan(Handle(d), 32 ** 3) == 3
     scene, integ, sensor, d, _ = build("C5", workdir, 32, spp=2)
-    assert _plan(Handle(d), 32 ** 3) == 0
+    assert _plan(Handle(d), 32 ** 3) == 4
+    assert _plan(Handle(d, force_general=True), 32 ** 3) == 0
+
+
+@pytest.mark.parametrize("spp,seed", [(1, 3), (4, 2), (3, 9)])
+def test_scattering_hybrid_matches_general_tracer(spp, seed, workdir):
+    """C5 (Henyey-Greenstein resin, jittered): every lane deposits its first medium segment along the whole
+    unscattered chord (volume.py:216), which has the planar structure, so the per-lane planar kernels take it
+    and the two-phase tracer skips it.  Same lanes, same PCG32 streams as the general tracer on its own: the
+    two agree like the absorptive jittered kernels do (knife-edge rays counted), forward and adjoint, on a
+    multi-tile grid; an angle shard and a list that is not planar go through the same gate."""
+    n = 144
+    scene, integ, sensor, d, _ = build("C5", workdir, n, n_patterns=6, spp=spp)
+    pix = pixels_np(scene)
+    p, g = random_inputs(d, pix.size, 19)
+    p = (p - 0.3).astype(np.float32)
+    fast, slow = Handle(d), Handle(d, force_general=True)
+    assert _plan(fast, pix.size, spp) == 4 and _plan(slow, pix.size, spp) == 0
+    f_fast, f_slow = fast.forward(p, pix, spp, seed), slow.forward(p, pix, spp, seed)
+    a_fast, a_slow = fast.adjoint(g, pix, spp, seed), slow.adjoint(g, pix, spp, seed)
+    assert_jitter_parity(f_fast, f_slow, 4 * spp, 3 * n, TOL, what=f"C5 spp {spp} dose hybrid/general")
+    assert_jitter_parity(a_fast, a_slow, 4 * spp, 1, TOL, what=f"C5 spp {spp} grad hybrid/general")
+    # the first segments are about half of the dose: the planar part did run
+    assert abs(f_slow.sum()) > 0 and abs(f_fast.sum() - f_slow.sum()) < 1e-4 * abs(f_slow).sum()
+    # angles [2, 5): a dense shard, still the hybrid
+    hw = d.res_x * d.res_y
+    sl = slice(2 * hw, 5 * hw)
+    assert_jitter_parity(fast.forward(p[sl], pix[sl], spp, seed), slow.forward(p[sl], pix[sl], spp, seed), 4 * spp, 3 * n,
+                         TOL, what="C5 shard dose")
+    assert_jitter_parity(fast.adjoint(g, pix[sl], spp, seed), slow.adjoint(g, pix[sl], spp, seed), 4 * spp, 1, TOL,
+                         what="C5 shard grad")
+    # a ragged list of whole-angle length: the gate hands the whole lanes to the tracer
+    perm = np.random.default_rng(1).permutation(pix.size)[:2 * hw].astype(np.int64)
+    perm.sort()
+    pr = pix[perm]
+    assert rel_l2(fast.forward(p[perm], pr, spp, seed), slow.forward(p[perm], pr, spp, seed)) < 1e-5
+    assert rel_l2(fast.adjoint(g, pr, spp, seed), slow.adjoint(g, pr, spp, seed)) < 1e-5
 
 
 @pytest.mark.parametrize("name", ["C2", "C3", "C4"])
