@@ -233,22 +233,27 @@ int ensure_planar(DrtvamScene* s) {
         }
     }
     if (s->planar_ok && s->P.surface_aware) {
-        e = inside_build(s->P, s->P1, s->inside);
+        // tile lanes need kernels that can mask them: the patch-gather forward and the layer-parallel adjoint
+        const bool allow_tiles = s->zplan.valid && s->gplan.valid && !has_window(s->P);
+        e = inside_build(s->P, s->P1, s->planar, s->zplan, allow_tiles, s->inside);
         if (e != cudaSuccess) {  // the general tracer serves the scene
             cudaGetLastError();
             s->planar_ok = false;
         }
     }
     if (getenv("DRTVAM_DEBUG"))
-        fprintf(stderr, "[drtvam] planar_ok %d zplan %d gplan %d (pairs %lld of %lld) frozen %d inside records %llu\n",
+        fprintf(stderr, "[drtvam] planar_ok %d zplan %d gplan %d (pairs %lld of %lld) frozen %d inside: %llu records of %u odd lanes, "
+                        "tiles %d with %llu table rows\n",
                 int(s->planar_ok), int(s->zplan.valid), int(s->gplan.valid), s->gplan.pairs, s->gplan.candidates, s->planar.n_frozen,
-                static_cast<unsigned long long>(s->inside.n_rec));
+                static_cast<unsigned long long>(s->inside.n_rec), s->inside.n_odd, int(s->inside.tiles),
+                static_cast<unsigned long long>(s->inside.n_rows));
     return DRTVAM_OK;
 }
 
 bool use_planar(DrtvamScene* s, uint64_t n_active) {
     if (s->force_mode == 1 || !s->planar_ok || n_active == 0) return false;
-    if (s->force_mode == 2 && (has_window(s->P) || s->hybrid)) return false;   // the per-ray tile DDA (A/B tests) knows neither
+    // the per-ray tile DDA (A/B tests) knows no window, no hybrid and no masked lanes
+    if (s->force_mode == 2 && (has_window(s->P) || s->hybrid || s->inside.tiles)) return false;
     const uint64_t rw = static_cast<uint64_t>(s->P.res_x) * s->P.n_rows;
     return n_active % rw == 0;
 }
@@ -449,7 +454,7 @@ int drtvam_scene_stat(DrtvamScene* s, int32_t which, uint64_t* value) {
     switch (which) {
         case 0: *value = tables ? static_cast<uint64_t>(s->gplan.pairs) : 0; break;
         case 1: *value = s->zplan.valid ? static_cast<uint64_t>(s->zplan.nz) : 0; break;
-        case 2: *value = s->inside.valid ? s->inside.n_rec : 0; break;
+        case 2: *value = s->inside.valid ? s->inside.n_rec + s->inside.n_rows * 32 : 0; break;
         case 3: *value = tables ? static_cast<uint64_t>(s->gplan.pairs) * 68u : 0; break;
         default: return fail(DRTVAM_E_INVALID, "unknown statistic %d", which);
     }
@@ -739,7 +744,8 @@ int drtvam_forward(DrtvamScene* s, const float* active_data, const uint32_t* act
                 // fresh: the plane was cleared above (zero_first, or the planes of a surface-aware scene) and
                 // the patch gather is its first writer, so it stores instead of read-add-write
                 CUDA_TRY(launch_planarg_forward(P1, s->zplan, s->gplan, gate, active_data, active_pixels, n_active, w,
-                                                plane, sa || zero_first != 0, st));
+                                                plane, sa || zero_first != 0, st,
+                                                sa && s->inside.tiles ? s->inside.mask : nullptr));
             else if (s->zplan.valid && s->force_mode != 2)
                 CUDA_TRY(launch_planarz_forward(P1, s->zplan, gate, active_data, active_pixels, n_active, w, plane, st));
             else
@@ -748,7 +754,8 @@ int drtvam_forward(DrtvamScene* s, const float* active_data, const uint32_t* act
                 CUDA_TRY(launch_planar_frozen(windowed(P1), s->planar, 0, active_data, plane, active_pixels, n_active, w,
                                               st, gate));
             if (sa)
-                CUDA_TRY(inside_forward_finish(P1, s->inside, gate, active_data, active_pixels, n_active, w, dose, st));
+                CUDA_TRY(inside_forward_finish(P1, s->inside, s->zplan, gate, active_data, active_pixels, n_active, w, dose,
+                                               st));
         }
         if (host_gate != 0)
             CUDA_TRY(launch_forward_general(Pw, active_data, active_pixels, n_active * spp, spp, seed, w, dose, st,
@@ -850,7 +857,8 @@ int drtvam_adjoint(DrtvamScene* s, const float* dose_grad, const uint32_t* activ
                 CUDA_TRY(launch_planarj_adjoint(P1, windowed(P1), s->zplan, s->jplan, gate, dl1, active_pixels, n_active,
                                                 spp, seed, w, pattern_grad, st));
             } else if (s->zplan.valid && s->force_mode != 2) {
-                CUDA_TRY(launch_planarz_adjoint(P1, s->zplan, gate, dl1, active_pixels, n_active, w, pattern_grad, st));
+                CUDA_TRY(launch_planarz_adjoint(P1, s->zplan, gate, dl1, active_pixels, n_active, w, pattern_grad, st,
+                                                sa ? &s->inside : nullptr));
             } else {
                 CUDA_TRY(cudaMemsetAsync(pattern_grad, 0, sizeof(float) * n_active, st));
                 CUDA_TRY(launch_planar_adjoint(P1, s->planar, dl1, active_pixels, n_active, w, pattern_grad, st, gate));

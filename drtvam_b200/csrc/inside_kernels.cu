@@ -26,9 +26,14 @@
 // cancelled in full and its head is added back as a record of its own.
 // The BVH traversal leaves the per-pass work altogether, and lanes that miss the target cost nothing
 // beyond the planar kernels.
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
+
 #include <cub/device/device_scan.cuh>
 
 #include "kernels.h"
+#include "planar.cuh"
 #include "tracer.cuh"
 
 namespace drtvam {
@@ -43,41 +48,96 @@ constexpr int kThreads = 256;
         if (_e != cudaSuccess) return _e; \
     } while (0)
 
-// kFill = false: cnt[lane] = number of records of the lane.
-// kFill = true : the records are written at off[lane].
-// P is the full scene (mesh attached), P1 its one-channel view without the mesh.
+// Layer tables of the layer-parallel plan, for the classification of lanes (enabled = 0: every lane is odd).
+struct TileInfo {
+    const int* row_a;   // [res_y] active layer of DMD row r, -1 = none
+    const int* zl;      // film layer of active layer a
+    int nz_pad;         // active layers padded to 32
+    int enabled;
+};
+
+constexpr int kMaxTileRecords = 255;
+
+// One thread per lane of the full pixel grid, run twice.
+//   kFill = false: cnt_old[lane] / cnt_tile[lane] = number of records of the lane as an odd lane / as a tile lane
+//                  (one of the two is 0; both 0: the lane misses the target).
+//   kFill = true : the records are written - odd lanes at off[lane] into seg / t_lo, tile lanes into the table
+//                  rows of their (angle, column, block) group, and the lane's bit is set in `mask`.
+// A lane is a TILE lane when every one of its sub-segments, the head included, has d_z = 0, lies in the voxel layer
+// of the lane's DMD row and starts without a frozen DDA axis (sensor.py:359), and its unsplit segment is the plain
+// planar one.  P is the full scene (mesh attached), P1 its one-channel view without the mesh.
 // flag[0] |= 1 when a lane that meets the mesh has more than one unsplit medium segment (not planar).
 template <bool kFill>
 __global__ void __launch_bounds__(kThreads)
 inside_trace_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ SceneParams P1, uint64_t n_lanes,
-                    uint32_t* __restrict__ cnt, const uint64_t* __restrict__ off, float4* __restrict__ seg,
-                    float* __restrict__ t_lo, int* __restrict__ flag) {
+                    const TileInfo TI, uint32_t* __restrict__ cnt_old, uint8_t* __restrict__ cnt_tile,
+                    const uint64_t* __restrict__ off, float4* __restrict__ seg, float* __restrict__ t_lo,
+                    const uint2* __restrict__ grp, float4* __restrict__ table, uint32_t* __restrict__ mask,
+                    int* __restrict__ flag) {
     const uint64_t lane = static_cast<uint64_t>(blockIdx.x) * kThreads + threadIdx.x;
     if (lane >= n_lanes) return;
+    const uint32_t hw = static_cast<uint32_t>(P.res_x) * P.res_y;
+    const uint32_t k = static_cast<uint32_t>(lane / hw), rem = static_cast<uint32_t>(lane - static_cast<uint64_t>(k) * hw);
+    const uint32_t row = rem / P.res_x, c = rem - row * P.res_x;
+    const int a = TI.enabled ? __ldg(TI.row_a + row) : -1;
+    const int z_row = a >= 0 ? __ldg(TI.zl + a) : -1;
+    const float vsz = (P.bmax[2] - P.bmin[2]) / static_cast<float>(P.res[2]);
+
+    bool as_tile = false, as_odd = false;
+    size_t trow = 0;   // first table row of the lane's group
+    if (kFill) {
+        as_tile = cnt_tile[lane] != 0;
+        as_odd = cnt_old[lane] != 0;
+        if (!as_tile && !as_odd) return;
+        if (as_tile) {
+            const size_t g = (static_cast<size_t>(k) * P.res_x + c) * (TI.nz_pad >> 5) + (a >> 5);
+            trow = __ldg(grp + g).x;
+            const size_t m = (static_cast<size_t>(k) * P.res_x + c) * TI.nz_pad + a;
+            atomicOr(mask + (m >> 5), 1u << (m & 31));
+        }
+    }
     Sampler rng;
     rng.seed(0u, 0u);  // never consumed: deterministic configuration
     const Ray ray0 = generate_ray(P, static_cast<uint32_t>(lane), rng);
-    uint64_t at = kFill ? off[lane] : 0;
-    auto emit = [&](const Ray& r, float maxt, float w0, bool inside, float start) {
-        if (kFill) {
+    uint64_t at = kFill && as_odd ? off[lane] : 0;
+    uint32_t n_tile = 0;
+    auto emit_old = [&](const Ray& r, float maxt, float w0, bool inside, float start) {
+        if (kFill && as_odd) {
             seg[2 * at] = make_float4(r.ox, r.oy, r.oz, inside ? -maxt : maxt);  // sign of the length = plane
             seg[2 * at + 1] = make_float4(r.dx, r.dy, r.dz, w0);
             t_lo[at] = start;
             ++at;
         }
     };
-    // with the mesh: sub-segment 0 is the head of the unsplit segment and stays with the planar kernels
+    auto emit_tile = [&](const Ray& r, float maxt, float w0, bool inside) {
+        if (kFill && as_tile) {
+            const size_t slot = ((trow + n_tile) << 5) + (a & 31);
+            table[2 * slot] = make_float4(r.ox, r.oy, r.dx, r.dy);
+            table[2 * slot + 1] = make_float4(inside ? -maxt : maxt, w0, 0.f, 0.f);
+        }
+        ++n_tile;
+    };
+    // is this sub-segment one the tile kernel can march?
+    bool tile_ok = z_row >= 0;
+    auto check = [&](const Ray& r, float maxt) {
+        const int z = min(max(__float2int_rz((r.oz - P.bmin[2]) / vsz), 0), P.res[2] - 1);
+        tile_ok = tile_ok && r.dz == 0.f && z == z_row && r.oz > P.bmin[2] && r.oz < P.bmax[2] && maxt > 0.f &&
+                  isfinite(maxt) && !dda_has_frozen_axis(P1, r, maxt);
+    };
+    // with the mesh: sub-segment 0 is the head of the unsplit segment
     TraceState T;
     T.ray = ray0;
     uint32_t n_sub = 0;
     float t1 = 0.f;
     while (bounce_once<false>(P, T, rng, [&](const Ray& r, float maxt, float w0, bool inside, float) {
         if (n_sub == 0) t1 = maxt;
-        else emit(r, maxt, w0, inside, 0.f);
+        else emit_old(r, maxt, w0, inside, 0.f);
+        if (!kFill) check(r, maxt);
+        emit_tile(r, maxt, w0, inside);
         ++n_sub;
     })) {}
     if (n_sub < 2) {
-        if (!kFill) cnt[lane] = 0;
+        if (!kFill) { cnt_old[lane] = 0; cnt_tile[lane] = 0; }
         return;
     }
     // without the mesh: what the planar kernels deposit for this lane
@@ -92,9 +152,56 @@ inside_trace_kernel(const __grid_constant__ SceneParams P, const __grid_constant
     })) {}
     if (n_u != 1) atomicOr(flag, 1);
     const bool whole = dda_has_frozen_axis(P1, ur, u_maxt) || !(t1 > 0.f);
-    if (whole) emit(ur, t1, u_w0, false, 0.f);
-    emit(ur, u_maxt, -u_w0, false, whole ? 0.f : t1);
-    if (!kFill) cnt[lane] = n_sub + (whole ? 1u : 0u);
+    if (!kFill) {
+        const bool tile = tile_ok && !whole && n_u == 1 && n_tile <= kMaxTileRecords;
+        cnt_tile[lane] = tile ? static_cast<uint8_t>(n_tile) : 0;
+        cnt_old[lane] = tile ? 0u : n_sub + (whole ? 1u : 0u);
+        return;
+    }
+    // odd lane: the planar kernels keep the unsplit segment, its tail is cancelled by a negative record
+    if (whole) emit_old(ur, t1, u_w0, false, 0.f);
+    emit_old(ur, u_maxt, -u_w0, false, whole ? 0.f : t1);
+}
+
+// rows[g] = most records any of the 32 lanes of group g = (angle, column, 32-layer block) holds
+__global__ void __launch_bounds__(kThreads)
+inside_group_rows_kernel(const __grid_constant__ SceneParams P, const int* __restrict__ a_row_begin,
+                         const int* __restrict__ a_rows, int nz, int n_blk, const uint8_t* __restrict__ cnt_tile,
+                         uint32_t* __restrict__ rows, size_t n_groups) {
+    const size_t g = static_cast<size_t>(blockIdx.x) * kThreads + threadIdx.x;
+    if (g >= n_groups) return;
+    const int blk = static_cast<int>(g % n_blk);
+    const size_t kc = g / n_blk;
+    const uint32_t c = static_cast<uint32_t>(kc % P.res_x), k = static_cast<uint32_t>(kc / P.res_x);
+    uint32_t m = 0;
+    for (int l = 0; l < 32; ++l) {
+        const int a = blk * 32 + l;
+        if (a >= nz) break;
+        const int row = a_rows[a_row_begin[a]];   // one DMD row per layer (checked by the host)
+        m = max(m, static_cast<uint32_t>(cnt_tile[(static_cast<size_t>(k) * P.res_y + row) * P.res_x + c]));
+    }
+    rows[g] = m;
+}
+
+__global__ void __launch_bounds__(kThreads)
+inside_group_pack_kernel(const uint32_t* __restrict__ rows, const uint32_t* __restrict__ first, uint2* __restrict__ grp,
+                         size_t n_groups) {
+    const size_t g = static_cast<size_t>(blockIdx.x) * kThreads + threadIdx.x;
+    if (g < n_groups) grp[g] = make_uint2(first[g], rows[g]);
+}
+
+// lanes with cnt[lane] != 0 -> list (positions from an exclusive scan of the flags)
+__global__ void __launch_bounds__(kThreads)
+inside_flag_kernel(const uint32_t* __restrict__ cnt, uint32_t* __restrict__ flagged, uint64_t n) {
+    const uint64_t i = static_cast<uint64_t>(blockIdx.x) * kThreads + threadIdx.x;
+    if (i < n) flagged[i] = cnt[i] != 0 ? 1u : 0u;
+}
+
+__global__ void __launch_bounds__(kThreads)
+inside_list_kernel(const uint32_t* __restrict__ flagged, const uint32_t* __restrict__ pos, uint64_t n,
+                   uint32_t* __restrict__ list) {
+    const uint64_t i = static_cast<uint64_t>(blockIdx.x) * kThreads + threadIdx.x;
+    if (i < n && flagged[i]) list[pos[i]] = static_cast<uint32_t>(i);
 }
 
 __global__ void widen_kernel(const uint32_t* __restrict__ in, uint64_t* __restrict__ out, uint64_t n) {
@@ -116,11 +223,17 @@ __global__ void __launch_bounds__(kThreads)
 inside_pass_kernel(const __grid_constant__ SceneParams P, const uint32_t* __restrict__ off,
                    const float4* __restrict__ seg, const float* __restrict__ t_lo, const float* __restrict__ in,
                    float* __restrict__ out, size_t n_vox, const uint32_t* __restrict__ active_pixels,
-                   uint64_t n_active, float ray_weight, const int* __restrict__ gate) {
+                   uint64_t n_active, float ray_weight, const int* __restrict__ gate,
+                   const uint32_t* __restrict__ odd_lanes, uint32_t n_odd) {
     if (*gate != 0) return;
-    const uint64_t j = static_cast<uint64_t>(blockIdx.x) * kThreads + threadIdx.x;
-    if (j >= n_active) return;
-    const uint64_t lane = __ldg(active_pixels) + j;  // the pixel list is base + j (planar check)
+    // one thread per odd lane of the scene; the ones that are part of this call (the pixel list is base + j,
+    // verified by the planar check) do the work
+    const uint64_t t = static_cast<uint64_t>(blockIdx.x) * kThreads + threadIdx.x;
+    if (t >= n_odd) return;
+    const uint64_t lane = __ldg(odd_lanes + t);
+    const uint64_t base = __ldg(active_pixels);
+    if (lane < base || lane - base >= n_active) return;
+    const uint64_t j = lane - base;
     const uint32_t r0 = __ldg(off + lane), r1 = __ldg(off + lane + 1);
     if (r0 == r1) return;
     float em = 0.f;
@@ -154,6 +267,221 @@ inside_pass_kernel(const __grid_constant__ SceneParams P, const uint32_t* __rest
     if (kMode == 1) out[j] += acc * ray_weight;
 }
 
+// ---- tile lanes -------------------------------------------------------------------------------------------
+// Built like the jittered planar kernels (planarj_kernels.cu): a CTA owns [tile_h + 2][tile_w + 2][2 planes][32 layers]
+// floats of shared memory for a range of angles, a warp takes one (angle, column) group and its 32 lanes are the
+// 32 voxel layers of the block, every lane marching ITS OWN records (neighbouring layers meet the target in
+// nearly the same places, so the warp stays together).  lane = layer = bank: the red.shared.add of a deposit never
+// meets a bank conflict; a tile is flushed once with red.global.add.v4.f32.  The table rows of a group are
+// [record][lane], so a warp reads one coalesced kilobyte per record row; groups without records cost one 8-byte
+// header.  (A first version kept the records in per-lane lists: 32 scattered 32-byte loads per row, 9 long-
+// scoreboard stalls per issue, slower than the per-lane kernel - session r02w.)
+constexpr int kTThreads = 1024;
+constexpr int kTWarps = kTThreads / 32;
+constexpr float kLog2e = 1.4426950408889634f;
+
+struct InsideTilePlan {
+    const int* tile_off;     // [n_tiles][n_patterns + 1]
+    const int* tile_clo;     // [n_tiles][n_patterns]
+    const int* zl;           // film layer of active layer a
+    const int* a_row_begin;  // CSR of the DMD rows of active layer a (exactly one row per layer here)
+    const int* a_rows;
+    int tiles_x, tiles_y, tile_w, tile_h;
+    int nz, nz_pad, groups;
+};
+
+// kMode 0 (forward): in = active_data; planes = plane A, plane B at + n_vox.
+// kMode 1 (adjoint): planes = the two gradient planes; out = gT [angle of the call][column][active layer] +=.
+template <int kMode>
+__global__ void __launch_bounds__(kTThreads, 1)
+inside_tile_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ InsideTilePlan Z,
+                   const uint2* __restrict__ grp, const float4* __restrict__ table, const float* __restrict__ in,
+                   float* __restrict__ out, float* __restrict__ planes, size_t n_vox,
+                   const uint32_t* __restrict__ active_pixels, uint64_t n_active, float ray_weight,
+                   const int* __restrict__ gate) {
+    extern __shared__ __align__(16) float tile[];
+    __shared__ int touched;
+    if (*gate != 0) return;
+    const int tile_id = blockIdx.x, blk = blockIdx.y, group = blockIdx.z;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int x0 = (tile_id % Z.tiles_x) * Z.tile_w, y0 = (tile_id / Z.tiles_x) * Z.tile_h;
+    const int w = min(Z.tile_w, P.res[0] - x0), h = min(Z.tile_h, P.res[1] - y0);
+    const int pitch = Z.tile_w + 2;                        // voxels per tile row, rim included
+    const int tile_floats = (Z.tile_h + 2) * pitch * 64;   // [y][x][plane][layer lane]
+    const int n_blk = Z.nz_pad >> 5;
+    const int a = blk * 32 + lane;
+    const size_t layer_elems = static_cast<size_t>(P.res[0]) * P.res[1];
+    const int z_mine = a < Z.nz ? __ldg(Z.zl + a) : -1;
+    const int row = a < Z.nz ? __ldg(Z.a_rows + __ldg(Z.a_row_begin + a)) : -1;
+    const bool vec = ((x0 | w | P.res[0]) & 3) == 0 && (reinterpret_cast<uintptr_t>(planes) & 15) == 0 && (n_vox & 3) == 0;
+
+    int k0, nk;
+    call_angles(P, active_pixels, n_active, k0, nk);
+    const int ka = k0 + static_cast<int>(static_cast<long long>(nk) * group / Z.groups);
+    const int kb = k0 + static_cast<int>(static_cast<long long>(nk) * (group + 1) / Z.groups);
+    const int* __restrict__ off = Z.tile_off + static_cast<size_t>(tile_id) * (P.n_patterns + 1);
+    const int* __restrict__ clo = Z.tile_clo + static_cast<size_t>(tile_id) * P.n_patterns;
+    const int g_begin = __ldg(off + ka), g_end = __ldg(off + kb);
+
+    // ---- does any group of this CTA hold records?  (most tiles lie outside the target or above / below it)
+    if (threadIdx.x == 0) touched = 0;
+    __syncthreads();
+    {
+        int k = ka;
+        bool any = false;
+        for (int g = g_begin + static_cast<int>(threadIdx.x); g < g_end && !any; g += kTThreads) {
+            while (__ldg(off + k + 1) <= g) ++k;
+            const int c = __ldg(clo + k) + (g - __ldg(off + k));
+            any = __ldg(grp + (static_cast<size_t>(k) * P.res_x + c) * n_blk + blk).y != 0;
+        }
+        if (any) touched = 1;
+    }
+    __syncthreads();
+    if (!touched) return;
+
+    if (kMode == 0) {
+        for (int i = threadIdx.x; i < tile_floats; i += kTThreads) tile[i] = 0.f;
+    } else if (z_mine >= 0) {
+        // stage both gradient planes: lane = layer, a warp takes 4 voxels of a row at a time
+        for (int pl = 0; pl < 2; ++pl) {
+            const float* src = planes + pl * n_vox + z_mine * layer_elems;
+            if (vec) {
+                const int w4 = w >> 2;
+                for (int i = warp; i < h * w4; i += kTWarps) {
+                    const int yy = i / w4, xx = (i - yy * w4) << 2;
+                    const float4 v = __ldg(reinterpret_cast<const float4*>(src + static_cast<size_t>(y0 + yy) * P.res[0] + x0 + xx));
+                    float* d = tile + (((yy + 1) * pitch + xx + 1) * 2 + pl) * 32 + lane;
+                    d[0] = v.x; d[64] = v.y; d[128] = v.z; d[192] = v.w;
+                }
+            } else {
+                for (int i = warp; i < h * w; i += kTWarps) {
+                    const int yy = i / w, xx = i - yy * w;
+                    tile[(((yy + 1) * pitch + xx + 1) * 2 + pl) * 32 + lane] =
+                        __ldg(src + static_cast<size_t>(y0 + yy) * P.res[0] + x0 + xx);
+                }
+            }
+        }
+    }
+    __syncthreads();
+
+    const float sig = P.sigma_t * kLog2e;
+    const float vsx = (P.bmax[0] - P.bmin[0]) / static_cast<float>(P.res[0]);
+    const float vsy = (P.bmax[1] - P.bmin[1]) / static_cast<float>(P.res[1]);
+    const float rvx = 1.f / vsx, rvy = 1.f / vsy;
+    const float xl = P.bmin[0] + static_cast<float>(x0) * vsx, xh = P.bmin[0] + static_cast<float>(x0 + w) * vsx;
+    const float yl = P.bmin[1] + static_cast<float>(y0) * vsy, yh = P.bmin[1] + static_cast<float>(y0 + h) * vsy;
+    const uint32_t tile_s = static_cast<uint32_t>(__cvta_generic_to_shared(tile));
+    const int sxb = 4 * 64, syb = 4 * 64 * pitch;
+
+    int k = ka;
+    for (int g = g_begin + warp; g < g_end; g += kTWarps) {
+        while (__ldg(off + k + 1) <= g) ++k;
+        const int c = __ldg(clo + k) + (g - __ldg(off + k));
+        const uint2 hd = __ldg(grp + (static_cast<size_t>(k) * P.res_x + c) * n_blk + blk);
+        if (hd.y == 0) continue;
+        float em = 1.f;
+        if (kMode == 0) em = row >= 0 ? __ldg(in + active_index(P, k - k0, row, c)) * ray_weight : 0.f;
+        float acc = 0.f;
+        for (unsigned i = 0; i < hd.y; ++i) {
+            const size_t slot = ((static_cast<size_t>(hd.x) + i) << 5) + lane;
+            const float4 eb = __ldg(table + 2 * slot + 1);
+            bool live = eb.x != 0.f && em != 0.f;
+            if (!__any_sync(0xffffffffu, live)) continue;
+            float4 ea = make_float4(0.f, 0.f, 1.f, 0.f);
+            if (live) ea = __ldg(table + 2 * slot);
+            // ---- clip the record to the tile
+            float t0 = 0.f, t1 = fabsf(eb.x);
+            const bool mx = fabsf(ea.z) > 1e-8f, my = fabsf(ea.w) > 1e-8f;
+            const float rdx = rcp_approx(ea.z), rdy = rcp_approx(ea.w);
+            if (mx) {
+                const float ta = (xl - ea.x) * rdx, tb = (xh - ea.x) * rdx;
+                t0 = fmaxf(t0, fminf(ta, tb));
+                t1 = fminf(t1, fmaxf(ta, tb));
+            } else if (ea.x < xl || ea.x >= xh) {
+                live = false;
+            }
+            if (my) {
+                const float ta = (yl - ea.y) * rdy, tb = (yh - ea.y) * rdy;
+                t0 = fmaxf(t0, fminf(ta, tb));
+                t1 = fminf(t1, fmaxf(ta, tb));
+            } else if (ea.y < yl || ea.y >= yh) {
+                live = false;
+            }
+            live = live && t0 < t1;
+            if (!live) continue;
+            // entry voxel by truncation then clip (sensor.py:345-346), tile-local
+            const float gx = fmaf(ea.z, t0, ea.x), gy = fmaf(ea.w, t0, ea.y);
+            const int ix = min(max(__float2int_rz((gx - P.bmin[0]) * rvx) - x0, 0), w - 1);
+            const int iy = min(max(__float2int_rz((gy - P.bmin[1]) * rvy) - y0, 0), h - 1);
+            // optical depths relative to the entry into the tile (see planarz_kernels.cu)
+            const float u1 = sig * (t1 - t0);
+            float ux = INFINITY, uy = INFINITY, ax = 0.f, ay = 0.f;
+            int sx = 0, sy = 0;
+            if (mx) {
+                const float inv = sig * rdx;
+                const bool pos = ea.z > 0.f;
+                sx = pos ? sxb : -sxb;
+                ax = fabsf(vsx * inv);
+                ux = (fmaf(static_cast<float>(x0 + ix + (pos ? 1 : 0)), vsx, P.bmin[0]) - gx) * inv;
+            }
+            if (my) {
+                const float inv = sig * rdy;
+                const bool pos = ea.w > 0.f;
+                sy = pos ? syb : -syb;
+                ay = fabsf(vsy * inv);
+                uy = (fmaf(static_cast<float>(y0 + iy + (pos ? 1 : 0)), vsy, P.bmin[1]) - gy) * inv;
+            }
+            uint32_t addr = tile_s + 4u * static_cast<uint32_t>((((iy + 1) * pitch + ix + 1) * 2 + (eb.x < 0.f ? 1 : 0)) * 32 + lane);
+            const float wgt = eb.y * ex2_approx(-sig * t0) * em;
+            float e_prev = 1.f, part = 0.f;
+            for (;;) {
+                const float un = fminf(ux, uy);
+                const bool px = ux <= uy;
+                const float e_out = ex2_approx(-fminf(un, u1));
+                const float de = e_prev - e_out;
+                if (kMode == 1) {
+                    float v;
+                    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+                    part = fmaf(v, de, part);
+                } else {
+                    asm volatile("red.shared.add.f32 [%0], %1;" ::"r"(addr), "f"(wgt * de) : "memory");
+                }
+                if (!(un < u1)) break;
+                e_prev = e_out;
+                addr += px ? sx : sy;
+                if (px) ux += ax; else uy += ay;
+            }
+            acc = fmaf(part, wgt, acc);
+        }
+        if (kMode == 1 && acc != 0.f)
+            atomicAdd(out + (static_cast<size_t>(k - k0) * P.res_x + c) * Z.nz_pad + a, acc * ray_weight);
+    }
+    if (kMode == 1) return;
+    __syncthreads();
+    if (z_mine < 0) return;
+
+    // ---- flush: lane = layer; every lane adds 4 voxels of a row of its own layer and plane with one red.global.add.v4
+    for (int pl = 0; pl < 2; ++pl) {
+        float* dst = planes + pl * n_vox + z_mine * layer_elems;
+        if (vec) {
+            const int w4 = w >> 2;
+            for (int i = warp; i < h * w4; i += kTWarps) {
+                const int yy = i / w4, xx = (i - yy * w4) << 2;
+                const float* src = tile + (((yy + 1) * pitch + xx + 1) * 2 + pl) * 32 + lane;
+                const float v0 = src[0], v1 = src[64], v2 = src[128], v3 = src[192];
+                if (v0 != 0.f || v1 != 0.f || v2 != 0.f || v3 != 0.f)
+                    red_add_v4(dst + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx), v0, v1, v2, v3);
+            }
+        } else {
+            for (int i = warp; i < h * w; i += kTWarps) {
+                const int yy = i / w, xx = i - yy * w;
+                const float v = tile[(((yy + 1) * pitch + xx + 1) * 2 + pl) * 32 + lane];
+                if (v != 0.f) atomicAdd(dst + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx), v);
+            }
+        }
+    }
+}
+
 __global__ void __launch_bounds__(kThreads)
 inside_combine_kernel(const float* __restrict__ outside, const float* __restrict__ inside, float2* __restrict__ film,
                       size_t n_vox, const int* __restrict__ gate) {
@@ -180,71 +508,159 @@ unsigned blocks_for(uint64_t n) { return static_cast<unsigned>((n + kThreads - 1
 }  // namespace
 
 void inside_release(InsideHost& H) {
-    if (H.off) cudaFree(H.off);
-    if (H.seg) cudaFree(H.seg);
-    if (H.t_lo) cudaFree(H.t_lo);
-    if (H.planes) cudaFree(H.planes);
+    void* ptrs[] = {H.off, H.seg, H.t_lo, H.odd_lanes, H.planes, H.grp, H.table, H.mask, H.tile_off, H.tile_clo};
+    for (void* q : ptrs)
+        if (q) cudaFree(q);
     H = InsideHost{};
 }
 
 // P: the full scene (target mesh attached, surface_aware = 1).  One-off set-up; synchronises.
-cudaError_t inside_build(const SceneParams& P, const SceneParams& P1, InsideHost& H) {
+cudaError_t inside_build(const SceneParams& P, const SceneParams& P1, const PlanarHost& base, const PlanarZHost& Zh,
+                         bool allow_tiles, InsideHost& H) {
     inside_release(H);
     const uint64_t n_lanes = static_cast<uint64_t>(P.n_patterns) * P.res_x * P.res_y;
     const size_t n_vox = static_cast<size_t>(P.res[0]) * P.res[1] * P.res[2];
-    uint32_t* cnt = nullptr;
+    if (n_lanes >= (1ull << 32)) return cudaErrorNotSupported;
+    const char* env = std::getenv("DRTVAM_INSIDE_TILES");
+    const bool tiles = allow_tiles && Zh.valid && Zh.rows_max == 1 && Zh.nz > 0 && !(env && std::atoi(env) == 0);
+    TileInfo TI{Zh.row_a, Zh.zl, Zh.nz_pad, tiles ? 1 : 0};
+    const int n_blk = tiles ? Zh.nz_pad / 32 : 0;
+    const size_t n_groups = static_cast<size_t>(P.n_patterns) * P.res_x * n_blk;
+    const size_t mask_words = tiles ? (static_cast<size_t>(P.n_patterns) * P.res_x * Zh.nz_pad) >> 5 : 0;
+
+    uint32_t *cnt = nullptr, *flagged = nullptr, *pos = nullptr, *rows = nullptr, *first = nullptr;
+    uint8_t* cnt_tile = nullptr;
     int* flag = nullptr;
     uint64_t *wide = nullptr, *off = nullptr;
     void* tmp = nullptr;
     size_t tmp_bytes = 0;
-    cudaError_t e = cudaSuccess;
     auto cleanup = [&]() {
-        if (cnt) cudaFree(cnt);
-        if (flag) cudaFree(flag);
-        if (wide) cudaFree(wide);
-        if (off) cudaFree(off);
-        if (tmp) cudaFree(tmp);
+        void* ptrs[] = {cnt, flagged, pos, rows, first, cnt_tile, flag, wide, off, tmp};
+        for (void* q : ptrs)
+            if (q) cudaFree(q);
+    };
+    auto scan32 = [&](const uint32_t* in, uint32_t* out, size_t n) -> cudaError_t {
+        size_t need = 0;
+        IN_TRY(cub::DeviceScan::ExclusiveSum(nullptr, need, in, out, n));
+        if (need > tmp_bytes) {
+            if (tmp) cudaFree(tmp);
+            tmp = nullptr;
+            IN_TRY(cudaMalloc(&tmp, need));
+            tmp_bytes = need;
+        }
+        IN_TRY(cub::DeviceScan::ExclusiveSum(tmp, need, in, out, n));
+        count_launch();
+        return cudaSuccess;
     };
     auto run = [&]() -> cudaError_t {
-        IN_TRY(cudaMalloc(&cnt, sizeof(uint32_t) * n_lanes));
+        IN_TRY(cudaMalloc(&cnt, sizeof(uint32_t) * (n_lanes + 1)));
+        IN_TRY(cudaMalloc(&cnt_tile, n_lanes));
         IN_TRY(cudaMalloc(&wide, sizeof(uint64_t) * (n_lanes + 1)));
         IN_TRY(cudaMalloc(&off, sizeof(uint64_t) * (n_lanes + 1)));
+        IN_TRY(cudaMemset(cnt + n_lanes, 0, sizeof(uint32_t)));
         IN_TRY(cudaMemset(wide + n_lanes, 0, sizeof(uint64_t)));
         IN_TRY(cudaMalloc(&flag, sizeof(int)));
         IN_TRY(cudaMemset(flag, 0, sizeof(int)));
-        inside_trace_kernel<false><<<blocks_for(n_lanes), kThreads>>>(P, P1, n_lanes, cnt, nullptr, nullptr, nullptr,
-                                                                     flag);
+        inside_trace_kernel<false><<<blocks_for(n_lanes), kThreads>>>(P, P1, n_lanes, TI, cnt, cnt_tile, nullptr, nullptr,
+                                                                     nullptr, nullptr, nullptr, nullptr, flag);
         count_launch();
-        widen_kernel<<<blocks_for(n_lanes), kThreads>>>(cnt, wide, n_lanes);
-        count_launch();
-        IN_TRY(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, wide, off, n_lanes + 1));
-        IN_TRY(cudaMalloc(&tmp, tmp_bytes));
-        IN_TRY(cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, wide, off, n_lanes + 1));
-        count_launch();
-        uint64_t total = 0;
-        IN_TRY(cudaMemcpy(&total, off + n_lanes, sizeof(total), cudaMemcpyDeviceToHost));
         int bad = 0;
         IN_TRY(cudaMemcpy(&bad, flag, sizeof(bad), cudaMemcpyDeviceToHost));
         if (bad) return cudaErrorNotSupported;
+        // ---- odd lanes: offsets of their record lists, and the list of the lanes themselves
+        widen_kernel<<<blocks_for(n_lanes), kThreads>>>(cnt, wide, n_lanes);
+        count_launch();
+        size_t need = 0;
+        IN_TRY(cub::DeviceScan::ExclusiveSum(nullptr, need, wide, off, n_lanes + 1));
+        IN_TRY(cudaMalloc(&tmp, need));
+        tmp_bytes = need;
+        IN_TRY(cub::DeviceScan::ExclusiveSum(tmp, need, wide, off, n_lanes + 1));
+        count_launch();
+        uint64_t total = 0;
+        IN_TRY(cudaMemcpy(&total, off + n_lanes, sizeof(total), cudaMemcpyDeviceToHost));
+        if (total >= (1ull << 32)) return cudaErrorMemoryAllocation;
         H.n_rec = total;
+        IN_TRY(cudaMalloc(&flagged, sizeof(uint32_t) * (n_lanes + 1)));
+        IN_TRY(cudaMalloc(&pos, sizeof(uint32_t) * (n_lanes + 1)));
+        IN_TRY(cudaMemset(flagged + n_lanes, 0, sizeof(uint32_t)));
+        inside_flag_kernel<<<blocks_for(n_lanes), kThreads>>>(cnt, flagged, n_lanes);
+        count_launch();
+        IN_TRY(scan32(flagged, pos, n_lanes + 1));
+        IN_TRY(cudaMemcpy(&H.n_odd, pos + n_lanes, sizeof(uint32_t), cudaMemcpyDeviceToHost));
+        IN_TRY(cudaMalloc(&H.odd_lanes, sizeof(uint32_t) * std::max<uint32_t>(H.n_odd, 1u)));
+        if (H.n_odd) {
+            inside_list_kernel<<<blocks_for(n_lanes), kThreads>>>(flagged, pos, n_lanes, H.odd_lanes);
+            count_launch();
+        }
+        // ---- tile lanes: rows per group, first row of every group
+        if (tiles) {
+            IN_TRY(cudaMalloc(&rows, sizeof(uint32_t) * (n_groups + 1)));
+            IN_TRY(cudaMalloc(&first, sizeof(uint32_t) * (n_groups + 1)));
+            IN_TRY(cudaMemset(rows + n_groups, 0, sizeof(uint32_t)));
+            inside_group_rows_kernel<<<blocks_for(n_groups), kThreads>>>(P, Zh.a_row_begin, Zh.a_rows, Zh.nz, n_blk, cnt_tile,
+                                                                       rows, n_groups);
+            count_launch();
+            IN_TRY(scan32(rows, first, n_groups + 1));
+            uint32_t n_rows = 0;
+            IN_TRY(cudaMemcpy(&n_rows, first + n_groups, sizeof(uint32_t), cudaMemcpyDeviceToHost));
+            H.n_rows = n_rows;
+        }
+        size_t free_b = 0, all_b = 0;
+        IN_TRY(cudaMemGetInfo(&free_b, &all_b));
+        if (total * 40 + H.n_rows * 32 * 32 > free_b / 2) return cudaErrorMemoryAllocation;
         if (total) {
-            size_t free_b = 0, all_b = 0;
-            IN_TRY(cudaMemGetInfo(&free_b, &all_b));
-            if (total * 40 > free_b / 2 || total >= (1ull << 32)) return cudaErrorMemoryAllocation;
             IN_TRY(cudaMalloc(&H.seg, sizeof(float4) * 2 * total));
             IN_TRY(cudaMalloc(&H.t_lo, sizeof(float) * total));
-            inside_trace_kernel<true><<<blocks_for(n_lanes), kThreads>>>(P, P1, n_lanes, nullptr, off, H.seg, H.t_lo,
-                                                                        flag);
+        }
+        if (tiles) {
+            IN_TRY(cudaMalloc(&H.grp, sizeof(uint2) * n_groups));
+            inside_group_pack_kernel<<<blocks_for(n_groups), kThreads>>>(rows, first, H.grp, n_groups);
+            count_launch();
+            IN_TRY(cudaMalloc(&H.table, sizeof(float4) * 2 * 32 * std::max<uint64_t>(H.n_rows, 1)));
+            IN_TRY(cudaMemset(H.table, 0, sizeof(float4) * 2 * 32 * std::max<uint64_t>(H.n_rows, 1)));
+            IN_TRY(cudaMalloc(&H.mask, sizeof(uint32_t) * std::max<size_t>(mask_words, 1)));
+            IN_TRY(cudaMemset(H.mask, 0, sizeof(uint32_t) * std::max<size_t>(mask_words, 1)));
+        }
+        if (total || H.n_rows) {
+            inside_trace_kernel<true><<<blocks_for(n_lanes), kThreads>>>(P, P1, n_lanes, TI, cnt, cnt_tile, off, H.seg, H.t_lo,
+                                                                        H.grp, H.table, H.mask, flag);
             count_launch();
         }
         IN_TRY(cudaMalloc(&H.off, sizeof(uint32_t) * (n_lanes + 1)));
         narrow_kernel<<<blocks_for(n_lanes + 1), kThreads>>>(off, H.off, n_lanes + 1);
         count_launch();
         IN_TRY(cudaMalloc(&H.planes, sizeof(float) * 2 * n_vox));
+        if (tiles && H.n_rows) {
+            // the largest xy tile whose [h + 2][w + 2][2 planes][32 layers] float slab fits 227 KB
+            const int np = P1.n_patterns, rx = P1.res[0], ry = P1.res[1];
+            const int area = (227 * 1024 / 4) / 64;
+            const int side = static_cast<int>(std::floor(std::sqrt(static_cast<double>(area)))) - 2;
+            const int tw_max = std::max(4, side & ~3);
+            H.tiles_x = (rx + tw_max - 1) / tw_max;
+            H.tile_w = (((rx + H.tiles_x - 1) / H.tiles_x) + 3) & ~3;
+            H.tiles_x = (rx + H.tile_w - 1) / H.tile_w;
+            const int th_max = std::max(1, area / (H.tile_w + 2) - 2);
+            H.tiles_y = (ry + th_max - 1) / th_max;
+            H.tile_h = (ry + H.tiles_y - 1) / H.tiles_y;
+            H.smem_bytes = sizeof(float) * static_cast<size_t>(H.tile_h + 2) * (H.tile_w + 2) * 64;
+            const int n_tiles = H.tiles_x * H.tiles_y;
+            IN_TRY(cudaFuncSetAttribute(inside_tile_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        static_cast<int>(H.smem_bytes)));
+            IN_TRY(cudaFuncSetAttribute(inside_tile_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        static_cast<int>(H.smem_bytes)));
+            IN_TRY(cudaMalloc(&H.tile_off, sizeof(int) * static_cast<size_t>(n_tiles) * (np + 1)));
+            IN_TRY(cudaMalloc(&H.tile_clo, sizeof(int) * static_cast<size_t>(n_tiles) * np));
+            // a record follows the centre ray of its (angle, column) up to the re-spawn offsets of its crossings
+            // (under a micrometre each): one pixel of margin
+            const float margin = std::fmax(P1.pixel_x, P1.pixel_y);
+            IN_TRY(planar_tile_ranges(P1, base.seg_a, base.seg_b, H.tiles_x, H.tiles_y, H.tile_w, H.tile_h, H.tile_off,
+                                      H.tile_clo, margin));
+            H.tiles = true;
+        }
         IN_TRY(cudaDeviceSynchronize());
         return cudaGetLastError();
     };
-    e = run();
+    const cudaError_t e = run();
     cleanup();
     if (e != cudaSuccess) {
         inside_release(H);
@@ -260,14 +676,31 @@ cudaError_t inside_forward_begin(InsideHost& H, cudaStream_t stream) {
     return cudaMemsetAsync(H.planes, 0, sizeof(float) * 2 * H.n_vox, stream);
 }
 
+static InsideTilePlan tile_plan(const InsideHost& H, const PlanarZHost& Zh) {
+    InsideTilePlan Z{};
+    Z.tile_off = H.tile_off; Z.tile_clo = H.tile_clo;
+    Z.zl = Zh.zl; Z.a_row_begin = Zh.a_row_begin; Z.a_rows = Zh.a_rows;
+    Z.tiles_x = H.tiles_x; Z.tiles_y = H.tiles_y; Z.tile_w = H.tile_w; Z.tile_h = H.tile_h;
+    Z.nz = Zh.nz; Z.nz_pad = Zh.nz_pad;
+    Z.groups = 4;   // the tiles over the target hold all the work: four CTAs each
+    return Z;
+}
+
 // Forward, part 2: the records into the planes, then both planes into the two-channel film.
-cudaError_t inside_forward_finish(const SceneParams& P1, InsideHost& H, const int* gate, const float* active_data,
-                                  const uint32_t* active_pixels, uint64_t n_active, float ray_weight, float* film,
-                                  cudaStream_t stream) {
-    if (H.n_rec) {
-        inside_pass_kernel<0><<<blocks_for(n_active), kThreads, 0, stream>>>(P1, H.off, H.seg, H.t_lo,
-                                                                           active_data, H.planes, H.n_vox, active_pixels, n_active,
-                                                                           ray_weight, gate);
+cudaError_t inside_forward_finish(const SceneParams& P1, InsideHost& H, const PlanarZHost& Zh, const int* gate,
+                                  const float* active_data, const uint32_t* active_pixels, uint64_t n_active,
+                                  float ray_weight, float* film, cudaStream_t stream) {
+    if (H.tiles) {
+        const InsideTilePlan Z = tile_plan(H, Zh);
+        const dim3 grid(H.tiles_x * H.tiles_y, Zh.nz_pad / 32, Z.groups);
+        inside_tile_kernel<0><<<grid, kTThreads, H.smem_bytes, stream>>>(P1, Z, H.grp, H.table, active_data, nullptr, H.planes,
+                                                                        H.n_vox, active_pixels, n_active, ray_weight, gate);
+        count_launch();
+    }
+    if (H.n_odd) {
+        inside_pass_kernel<0><<<blocks_for(H.n_odd), kThreads, 0, stream>>>(P1, H.off, H.seg, H.t_lo, active_data, H.planes,
+                                                                          H.n_vox, active_pixels, n_active, ray_weight, gate,
+                                                                          H.odd_lanes, H.n_odd);
         count_launch();
     }
     inside_combine_kernel<<<blocks_for(H.n_vox), kThreads, 0, stream>>>(H.planes, H.planes + H.n_vox,
@@ -284,13 +717,27 @@ cudaError_t inside_adjoint_begin(InsideHost& H, const float* dL, cudaStream_t st
     return cudaGetLastError();
 }
 
-// Adjoint, part 2 (after the planar adjoint has written grad): adds the gather over the inside records.
+// Adjoint of the tile lanes: between the gather of the layer-parallel adjoint (whose values for these lanes have
+// just been cleared) and its unpack.
+cudaError_t inside_adjoint_tiles(const SceneParams& P1, InsideHost& H, const PlanarZHost& Zh, const int* gate,
+                                 const uint32_t* active_pixels, uint64_t n_active, float ray_weight, float* gT,
+                                 cudaStream_t stream) {
+    if (!H.tiles) return cudaSuccess;
+    const InsideTilePlan Z = tile_plan(H, Zh);
+    const dim3 grid(H.tiles_x * H.tiles_y, Zh.nz_pad / 32, Z.groups);
+    inside_tile_kernel<1><<<grid, kTThreads, H.smem_bytes, stream>>>(P1, Z, H.grp, H.table, nullptr, gT, H.planes, H.n_vox,
+                                                                    active_pixels, n_active, ray_weight, gate);
+    count_launch();
+    return cudaGetLastError();
+}
+
+// Adjoint, part 2 (after the planar adjoint has written grad): adds the gather over the records of the odd lanes.
 cudaError_t inside_adjoint_finish(const SceneParams& P1, InsideHost& H, const int* gate, const uint32_t* active_pixels,
                                   uint64_t n_active, float ray_weight, float* grad, cudaStream_t stream) {
-    if (!H.n_rec) return cudaSuccess;
-    inside_pass_kernel<1><<<blocks_for(n_active), kThreads, 0, stream>>>(P1, H.off, H.seg, H.t_lo, H.planes,
-                                                                       grad, H.n_vox, active_pixels, n_active, ray_weight,
-                                                                       gate);
+    if (!H.n_odd) return cudaSuccess;
+    inside_pass_kernel<1><<<blocks_for(H.n_odd), kThreads, 0, stream>>>(P1, H.off, H.seg, H.t_lo, H.planes, grad, H.n_vox,
+                                                                      active_pixels, n_active, ray_weight, gate,
+                                                                      H.odd_lanes, H.n_odd);
     count_launch();
     return cudaGetLastError();
 }

@@ -143,9 +143,12 @@ cudaError_t launch_planarj_adjoint(const SceneParams& P, const SceneParams& Pw, 
                                    uint32_t spp, uint32_t seed, float ray_weight, float* grad, cudaStream_t stream);
 cudaError_t planarg_build(const SceneParams& P, const PlanarHost& base, const PlanarZHost& Zh, PlanarGHost& G);
 void planarg_release(PlanarGHost& G);
+// `lane_mask` (may be null): bit ((angle * res_x + column) * nz_pad + active layer) set = the lane is not this
+// kernel's (the tile lanes of a surface-aware scene, inside_kernels.cu); its pattern value is cleared after the repack
 cudaError_t launch_planarg_forward(const SceneParams& P, PlanarZHost& H, PlanarGHost& G, const int* gate,
                                    const float* active_data, const uint32_t* active_pixels, uint64_t n_active,
-                                   float ray_weight, float* film, bool fresh, cudaStream_t stream);
+                                   float ray_weight, float* film, bool fresh, cudaStream_t stream,
+                                   const uint32_t* lane_mask = nullptr);
 // the same forward on the static scratch of the library image: no allocation (planarz_kernels.cu)
 size_t planarg_noalloc_capacity();   // floats: angles of the call x res_x x padded layers must fit
 cudaError_t launch_planarg_forward_noalloc(const SceneParams& P, const PlanarZHost& H, const PlanarGHost& G, int device,
@@ -156,9 +159,12 @@ void planarz_release(PlanarZHost& H);
 cudaError_t launch_planarz_forward(const SceneParams& P, PlanarZHost& H, const int* gate, const float* active_data,
                                    const uint32_t* active_pixels, uint64_t n_active, float ray_weight, float* film,
                                    cudaStream_t stream);
+struct InsideHost;
+// `inside` (may be null): a surface-aware scene whose tile lanes are cleared in the repacked gradient and then
+// receive the gather over their own records (inside_adjoint_tiles) before the unpack
 cudaError_t launch_planarz_adjoint(const SceneParams& P, PlanarZHost& H, const int* gate, const float* dL,
                                    const uint32_t* active_pixels, uint64_t n_active, float ray_weight, float* grad,
-                                   cudaStream_t stream);
+                                   cudaStream_t stream, InsideHost* inside = nullptr);
 
 // target mesh + surface-aware sub-voxel volumes (mesh_kernels.cu)
 struct MeshHost {
@@ -178,20 +184,46 @@ cudaError_t launch_mul(const float* a, const float* b, float* out, size_t n, cud
 // inside-target segment records: the surface-aware film on top of the planar kernels (inside_kernels.cu)
 struct InsideHost {
     bool valid = false;
+    // ODD lanes (a frozen DDA axis, a crossing that leaves the lane's layer ...): per-lane record lists, walked by
+    // one thread per lane with global atomics; the planar kernels deposit the lane's unsplit segment and a
+    // NEGATIVE record cancels its tail
     uint32_t* off = nullptr;    // [lanes + 1] first record of every lane of the full pixel grid
     float4* seg = nullptr;      // [n_rec][2] {origin, length}, {direction, throughput at the origin}
     float* t_lo = nullptr;      // [n_rec] > 0: walk the record from here on only (the negative record)
     uint64_t n_rec = 0;
+    uint32_t* odd_lanes = nullptr;  // the lanes that have such records
+    uint32_t n_odd = 0;
     float* planes = nullptr;    // [2][n_vox] plane A (outside channel), plane B (inside channel)
     size_t n_vox = 0;
+    // TILE lanes (all other lanes that meet the target): masked out of the planar kernels altogether; all their
+    // sub-segments, head included, sit in a table ordered [angle][column][32-layer block][record][layer lane]
+    // and are marched by a shared-memory tile kernel
+    bool tiles = false;
+    uint2* grp = nullptr;       // [angle][column][block] {first record row of the group, record rows}
+    float4* table = nullptr;    // [rows][32 lanes][2] {ox, oy, dx, dy}, {+-length (sign: plane B), throughput, -, -}
+    uint64_t n_rows = 0;
+    uint64_t n_tile_rec = 0;    // records in the table (statistics)
+    uint32_t* mask = nullptr;   // bit ((angle * res_x + column) * nz_pad + active layer): a tile lane
+    int* tile_off = nullptr;
+    int* tile_clo = nullptr;
+    int tiles_x = 0, tiles_y = 0, tile_w = 0, tile_h = 0;
+    size_t smem_bytes = 0;
 };
-cudaError_t inside_build(const SceneParams& P, const SceneParams& P1, InsideHost& H);
+// `allow_tiles`: the deterministic forward / adjoint of this scene run on the patch-gather and layer-parallel
+// kernels, which can mask lanes (no z window, one DMD row per layer)
+cudaError_t inside_build(const SceneParams& P, const SceneParams& P1, const PlanarHost& base, const PlanarZHost& Zh,
+                         bool allow_tiles, InsideHost& H);
 void inside_release(InsideHost& H);
 cudaError_t inside_forward_begin(InsideHost& H, cudaStream_t stream);
-cudaError_t inside_forward_finish(const SceneParams& P1, InsideHost& H, const int* gate, const float* active_data,
-                                  const uint32_t* active_pixels, uint64_t n_active, float ray_weight, float* film,
-                                  cudaStream_t stream);
+cudaError_t inside_forward_finish(const SceneParams& P1, InsideHost& H, const PlanarZHost& Zh, const int* gate,
+                                  const float* active_data, const uint32_t* active_pixels, uint64_t n_active,
+                                  float ray_weight, float* film, cudaStream_t stream);
 cudaError_t inside_adjoint_begin(InsideHost& H, const float* dL, cudaStream_t stream);
+// the tile lanes' part of the adjoint: adds to gT ([angle of the call][column][active layer], the repacked gradient
+// of the layer-parallel adjoint) between its gather and its unpack
+cudaError_t inside_adjoint_tiles(const SceneParams& P1, InsideHost& H, const PlanarZHost& Zh, const int* gate,
+                                 const uint32_t* active_pixels, uint64_t n_active, float ray_weight, float* gT,
+                                 cudaStream_t stream);
 cudaError_t inside_adjoint_finish(const SceneParams& P1, InsideHost& H, const int* gate, const uint32_t* active_pixels,
                                   uint64_t n_active, float ray_weight, float* grad, cudaStream_t stream);
 

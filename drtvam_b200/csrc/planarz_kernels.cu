@@ -101,6 +101,27 @@ zunpack_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
     }
 }
 
+// t [kk][col][a] = 0 where the lane (k0 + kk, col, a) is marked: lanes that other kernels serve (the tile lanes
+// of a surface-aware scene, inside_kernels.cu), in the repacked patterns before the forward pass and in the
+// repacked gradient after the gather
+__global__ void __launch_bounds__(256)
+zmask_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ PlanarZPlan Z, float* __restrict__ t,
+             const uint32_t* __restrict__ mask, const uint32_t* __restrict__ active_pixels, uint64_t n_active,
+             const int* __restrict__ gate) {
+    if (*gate != 0) return;
+    int k0, nk;
+    call_angles(P, active_pixels, n_active, k0, nk);
+    const size_t words_per_angle = (static_cast<size_t>(P.res_x) * Z.nz_pad) >> 5;   // nz_pad is a multiple of 32
+    const size_t wi = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x;
+    if (wi >= words_per_angle * nk) return;
+    uint32_t m = __ldg(mask + static_cast<size_t>(k0) * words_per_angle + wi);
+    while (m) {
+        const int b = __ffs(m) - 1;
+        m &= m - 1;
+        t[(wi << 5) + b] = 0.f;
+    }
+}
+
 // tile[addr .. addr + kL) += em[0..kL) * de, atomically with respect to the other warps of the CTA.
 template <int kL>
 __device__ __forceinline__ void z_scatter(uint32_t addr, const float (&em)[kL], float de) {
@@ -1403,6 +1424,16 @@ static cudaError_t z_scratch(PlanarZHost& H, size_t bytes) {
     return cudaSuccess;
 }
 
+static cudaError_t launch_zmask(const SceneParams& P, PlanarZHost& H, const uint32_t* mask, const uint32_t* active_pixels,
+                                uint64_t n_active, const int* gate, cudaStream_t stream) {
+    const size_t nk = n_active / (static_cast<uint64_t>(P.res_x) * P.n_rows);
+    const size_t words = ((static_cast<size_t>(P.res_x) * H.nz_pad) >> 5) * nk;
+    zmask_kernel<<<static_cast<unsigned>((words + 255) / 256), 256, 0, stream>>>(P, H.sub[0].plan, H.scratch, mask,
+                                                                              active_pixels, n_active, gate);
+    count_launch();
+    return cudaGetLastError();
+}
+
 // Angle groups of one sub-plan: enough CTAs for two waves of the 148 SMs.  The gather (adjoint) kernel runs one
 // 1024-thread CTA per SM, so a grid just past a multiple of 148 pays a whole extra wave (the 1-layer tail of C2:
 // 100 tiles x 3 groups = 300 CTAs = 3 waves for 2.03 waves of work); there the group count is raised to the one
@@ -1471,12 +1502,16 @@ cudaError_t launch_planarz_forward(const SceneParams& P, PlanarZHost& H, const i
 
 cudaError_t launch_planarz_adjoint(const SceneParams& P, PlanarZHost& H, const int* gate, const float* dL,
                                    const uint32_t* active_pixels, uint64_t n_active, float ray_weight, float* grad,
-                                   cudaStream_t stream) {
+                                   cudaStream_t stream, InsideHost* inside) {
     const int nk = static_cast<int>(n_active / (static_cast<uint64_t>(P.res_x) * P.n_rows));
     const size_t bytes = sizeof(float) * static_cast<size_t>(nk) * P.res_x * H.nz_pad;
     PZ_TRY(z_scratch(H, bytes));
     PZ_TRY(cudaMemsetAsync(H.scratch, 0, bytes, stream));
     PZ_TRY(z_launch<kGather>(P, H, dL, H.scratch, active_pixels, n_active, ray_weight, gate, stream));
+    if (inside && inside->tiles) {
+        PZ_TRY(launch_zmask(P, H, inside->mask, active_pixels, n_active, gate, stream));
+        PZ_TRY(inside_adjoint_tiles(P, *inside, H, gate, active_pixels, n_active, ray_weight, H.scratch, stream));
+    }
     const dim3 ugrid((P.res_x + 31) / 32, (P.n_rows + 31) / 32, nk);
     zunpack_kernel<<<ugrid, 256, 0, stream>>>(P, H.sub[0].plan, H.scratch, grad, gate);
     count_launch();
@@ -1601,13 +1636,15 @@ cudaError_t planarg_build(const SceneParams& P, const PlanarHost& base, const Pl
 
 cudaError_t launch_planarg_forward(const SceneParams& P, PlanarZHost& H, PlanarGHost& G, const int* gate,
                                    const float* active_data, const uint32_t* active_pixels, uint64_t n_active,
-                                   float ray_weight, float* film, bool fresh, cudaStream_t stream) {
+                                   float ray_weight, float* film, bool fresh, cudaStream_t stream,
+                                   const uint32_t* lane_mask) {
     const int nk = static_cast<int>(n_active / (static_cast<uint64_t>(P.res_x) * P.n_rows));
     PZ_TRY(z_scratch(H, sizeof(float) * static_cast<size_t>(nk) * P.res_x * H.nz_pad));
     const dim3 pgrid((P.res_x + 31) / 32, H.nz_pad / 32, nk);
     zpack_kernel<<<pgrid, 256, 0, stream>>>(P, H.sub[0].plan, active_data, H.scratch, nk, gate);
     count_launch();
     PZ_TRY(cudaGetLastError());
+    if (lane_mask) PZ_TRY(launch_zmask(P, H, lane_mask, active_pixels, n_active, gate, stream));
     const PlanarZPlan& Z = G.plan;
     const int regions = ((Z.tiles_x + kGWarpsX - 1) / kGWarpsX) * ((Z.tiles_y + kGWarpsY - 1) / kGWarpsY);
     constexpr int threads = 32 * kGWarpsX * kGWarpsY;
