@@ -190,6 +190,31 @@ inside_group_pack_kernel(const uint32_t* __restrict__ rows, const uint32_t* __re
     if (g < n_groups) grp[g] = make_uint2(first[g], rows[g]);
 }
 
+// rbox[r] = bounding box (xmin, ymin, xmax, ymax) of the records of table row r: one warp per row.  The rows of a
+// group are the consecutive sub-segments of its lanes - head, first stretch inside the target, ... - so a row is
+// short and a tile reads only the rows that reach it.
+__global__ void __launch_bounds__(kThreads)
+inside_row_box_kernel(const float4* __restrict__ table, uint64_t n_rows, float4* __restrict__ rbox) {
+    const uint64_t r = (static_cast<uint64_t>(blockIdx.x) * kThreads + threadIdx.x) >> 5;
+    if (r >= n_rows) return;
+    const int lane = threadIdx.x & 31;
+    const float4 ea = table[2 * ((r << 5) + lane)], eb = table[2 * ((r << 5) + lane) + 1];
+    float x0 = INFINITY, y0 = INFINITY, x1 = -INFINITY, y1 = -INFINITY;
+    if (eb.x != 0.f) {
+        const float t = fabsf(eb.x);
+        const float ex = fmaf(ea.z, t, ea.x), ey = fmaf(ea.w, t, ea.y);
+        x0 = fminf(ea.x, ex); x1 = fmaxf(ea.x, ex);
+        y0 = fminf(ea.y, ey); y1 = fmaxf(ea.y, ey);
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        x0 = fminf(x0, __shfl_xor_sync(0xffffffffu, x0, o));
+        y0 = fminf(y0, __shfl_xor_sync(0xffffffffu, y0, o));
+        x1 = fmaxf(x1, __shfl_xor_sync(0xffffffffu, x1, o));
+        y1 = fmaxf(y1, __shfl_xor_sync(0xffffffffu, y1, o));
+    }
+    if (lane == 0) rbox[r] = make_float4(x0, y0, x1, y1);
+}
+
 // lanes with cnt[lane] != 0 -> list (positions from an exclusive scan of the flags)
 __global__ void __launch_bounds__(kThreads)
 inside_flag_kernel(const uint32_t* __restrict__ cnt, uint32_t* __restrict__ flagged, uint64_t n) {
@@ -295,8 +320,8 @@ struct InsideTilePlan {
 template <int kMode>
 __global__ void __launch_bounds__(kTThreads, 1)
 inside_tile_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ InsideTilePlan Z,
-                   const uint2* __restrict__ grp, const float4* __restrict__ table, const float* __restrict__ in,
-                   float* __restrict__ out, float* __restrict__ planes, size_t n_vox,
+                   const uint2* __restrict__ grp, const float4* __restrict__ table, const float4* __restrict__ rbox,
+                   const float* __restrict__ in, float* __restrict__ out, float* __restrict__ planes, size_t n_vox,
                    const uint32_t* __restrict__ active_pixels, uint64_t n_active, float ray_weight,
                    const int* __restrict__ gate) {
     extern __shared__ __align__(16) float tile[];
@@ -383,6 +408,8 @@ inside_tile_kernel(const __grid_constant__ SceneParams P, const __grid_constant_
         if (kMode == 0) em = row >= 0 ? __ldg(in + active_index(P, k - k0, row, c)) * ray_weight : 0.f;
         float acc = 0.f;
         for (unsigned i = 0; i < hd.y; ++i) {
+            const float4 box = __ldg(rbox + hd.x + i);   // does any record of the row reach this tile?
+            if (box.x > xh + vsx || box.z < xl - vsx || box.y > yh + vsy || box.w < yl - vsy) continue;
             const size_t slot = ((static_cast<size_t>(hd.x) + i) << 5) + lane;
             const float4 eb = __ldg(table + 2 * slot + 1);
             bool live = eb.x != 0.f && em != 0.f;
@@ -508,7 +535,7 @@ unsigned blocks_for(uint64_t n) { return static_cast<unsigned>((n + kThreads - 1
 }  // namespace
 
 void inside_release(InsideHost& H) {
-    void* ptrs[] = {H.off, H.seg, H.t_lo, H.odd_lanes, H.planes, H.grp, H.table, H.mask, H.tile_off, H.tile_clo};
+    void* ptrs[] = {H.off, H.seg, H.t_lo, H.odd_lanes, H.planes, H.grp, H.table, H.rbox, H.mask, H.tile_off, H.tile_clo};
     for (void* q : ptrs)
         if (q) cudaFree(q);
     H = InsideHost{};
@@ -626,6 +653,13 @@ cudaError_t inside_build(const SceneParams& P, const SceneParams& P1, const Plan
                                                                         H.grp, H.table, H.mask, flag);
             count_launch();
         }
+        if (tiles) {
+            IN_TRY(cudaMalloc(&H.rbox, sizeof(float4) * std::max<uint64_t>(H.n_rows, 1)));
+            if (H.n_rows) {
+                inside_row_box_kernel<<<blocks_for(H.n_rows * 32), kThreads>>>(H.table, H.n_rows, H.rbox);
+                count_launch();
+            }
+        }
         IN_TRY(cudaMalloc(&H.off, sizeof(uint32_t) * (n_lanes + 1)));
         narrow_kernel<<<blocks_for(n_lanes + 1), kThreads>>>(off, H.off, n_lanes + 1);
         count_launch();
@@ -693,7 +727,7 @@ cudaError_t inside_forward_finish(const SceneParams& P1, InsideHost& H, const Pl
     if (H.tiles) {
         const InsideTilePlan Z = tile_plan(H, Zh);
         const dim3 grid(H.tiles_x * H.tiles_y, Zh.nz_pad / 32, Z.groups);
-        inside_tile_kernel<0><<<grid, kTThreads, H.smem_bytes, stream>>>(P1, Z, H.grp, H.table, active_data, nullptr, H.planes,
+        inside_tile_kernel<0><<<grid, kTThreads, H.smem_bytes, stream>>>(P1, Z, H.grp, H.table, H.rbox, active_data, nullptr, H.planes,
                                                                         H.n_vox, active_pixels, n_active, ray_weight, gate);
         count_launch();
     }
@@ -725,7 +759,7 @@ cudaError_t inside_adjoint_tiles(const SceneParams& P1, InsideHost& H, const Pla
     if (!H.tiles) return cudaSuccess;
     const InsideTilePlan Z = tile_plan(H, Zh);
     const dim3 grid(H.tiles_x * H.tiles_y, Zh.nz_pad / 32, Z.groups);
-    inside_tile_kernel<1><<<grid, kTThreads, H.smem_bytes, stream>>>(P1, Z, H.grp, H.table, nullptr, gT, H.planes, H.n_vox,
+    inside_tile_kernel<1><<<grid, kTThreads, H.smem_bytes, stream>>>(P1, Z, H.grp, H.table, H.rbox, nullptr, gT, H.planes, H.n_vox,
                                                                     active_pixels, n_active, ray_weight, gate);
     count_launch();
     return cudaGetLastError();
