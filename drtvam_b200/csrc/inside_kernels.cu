@@ -85,13 +85,17 @@ inside_trace_kernel(const __grid_constant__ SceneParams P, const __grid_constant
 
     bool as_tile = false, as_odd = false;
     size_t trow = 0;   // first table row of the lane's group
+    uint32_t n_mine = 0, n_rows_g = 0;
     if (kFill) {
         as_tile = cnt_tile[lane] != 0;
         as_odd = cnt_old[lane] != 0;
         if (!as_tile && !as_odd) return;
         if (as_tile) {
             const size_t g = (static_cast<size_t>(k) * P.res_x + c) * (TI.nz_pad >> 5) + (a >> 5);
-            trow = __ldg(grp + g).x;
+            const uint2 hd = __ldg(grp + g);
+            trow = hd.x;
+            n_rows_g = hd.y;
+            n_mine = cnt_tile[lane];
             const size_t m = (static_cast<size_t>(k) * P.res_x + c) * TI.nz_pad + a;
             atomicOr(mask + (m >> 5), 1u << (m & 31));
         }
@@ -111,7 +115,10 @@ inside_trace_kernel(const __grid_constant__ SceneParams P, const __grid_constant
     };
     auto emit_tile = [&](const Ray& r, float maxt, float w0, bool inside) {
         if (kFill && as_tile) {
-            const size_t slot = ((trow + n_tile) << 5) + (a & 31);
+            // the LAST record of a lane (its tail, the longest) goes to the last row of the group whatever the
+            // number of crossings before it, so that the tails of the 32 lanes are marched together
+            const uint32_t trow_i = n_tile + 1 == n_mine ? n_rows_g - 1 : n_tile;
+            const size_t slot = ((trow + trow_i) << 5) + (a & 31);
             table[2 * slot] = make_float4(r.ox, r.oy, r.dx, r.dy);
             table[2 * slot + 1] = make_float4(inside ? -maxt : maxt, w0, 0.f, 0.f);
         }
@@ -190,29 +197,37 @@ inside_group_pack_kernel(const uint32_t* __restrict__ rows, const uint32_t* __re
     if (g < n_groups) grp[g] = make_uint2(first[g], rows[g]);
 }
 
-// rbox[r] = bounding box (xmin, ymin, xmax, ymax) of the records of table row r: one warp per row.  The rows of a
-// group are the consecutive sub-segments of its lanes - head, first stretch inside the target, ... - so a row is
-// short and a tile reads only the rows that reach it.
+// rbox[r] = (smin, smax): the stretch of table row r along the centre ray of its (angle, column) - all records of
+// a group lie on that line up to the sub-micrometre re-spawn offsets - as s = (p - o_c) . d_c over the end points of
+// its 32 records.  One warp per group.  The rows of a group are the consecutive sub-segments of its lanes - head,
+// first stretch inside the target, ... - so a row is short, and a tile reads only the rows whose stretch meets
+// the stretch of the centre ray inside the tile.
 __global__ void __launch_bounds__(kThreads)
-inside_row_box_kernel(const float4* __restrict__ table, uint64_t n_rows, float4* __restrict__ rbox) {
-    const uint64_t r = (static_cast<uint64_t>(blockIdx.x) * kThreads + threadIdx.x) >> 5;
-    if (r >= n_rows) return;
+inside_row_range_kernel(const float4* __restrict__ seg_a, const uint2* __restrict__ grp, int n_blk,
+                        const float4* __restrict__ table, size_t n_groups, float2* __restrict__ rbox) {
+    const size_t g = (static_cast<size_t>(blockIdx.x) * kThreads + threadIdx.x) >> 5;
+    if (g >= n_groups) return;
+    const uint2 hd = grp[g];
+    if (hd.y == 0) return;
     const int lane = threadIdx.x & 31;
-    const float4 ea = table[2 * ((r << 5) + lane)], eb = table[2 * ((r << 5) + lane) + 1];
-    float x0 = INFINITY, y0 = INFINITY, x1 = -INFINITY, y1 = -INFINITY;
-    if (eb.x != 0.f) {
-        const float t = fabsf(eb.x);
-        const float ex = fmaf(ea.z, t, ea.x), ey = fmaf(ea.w, t, ea.y);
-        x0 = fminf(ea.x, ex); x1 = fmaxf(ea.x, ex);
-        y0 = fminf(ea.y, ey); y1 = fmaxf(ea.y, ey);
+    const float4 c = seg_a[g / n_blk];   // (ox, oy, dx, dy) of the centre ray, unit direction
+    for (uint32_t i = 0; i < hd.y; ++i) {
+        const size_t slot = ((static_cast<size_t>(hd.x) + i) << 5) + lane;
+        const float4 ea = table[2 * slot], eb = table[2 * slot + 1];
+        float s0 = INFINITY, s1 = -INFINITY;
+        if (eb.x != 0.f) {
+            const float t = fabsf(eb.x);
+            const float sa = (ea.x - c.x) * c.z + (ea.y - c.y) * c.w;
+            const float sb = (fmaf(ea.z, t, ea.x) - c.x) * c.z + (fmaf(ea.w, t, ea.y) - c.y) * c.w;
+            s0 = fminf(sa, sb);
+            s1 = fmaxf(sa, sb);
+        }
+        for (int o = 16; o > 0; o >>= 1) {
+            s0 = fminf(s0, __shfl_xor_sync(0xffffffffu, s0, o));
+            s1 = fmaxf(s1, __shfl_xor_sync(0xffffffffu, s1, o));
+        }
+        if (lane == 0) rbox[hd.x + i] = make_float2(s0, s1);
     }
-    for (int o = 16; o > 0; o >>= 1) {
-        x0 = fminf(x0, __shfl_xor_sync(0xffffffffu, x0, o));
-        y0 = fminf(y0, __shfl_xor_sync(0xffffffffu, y0, o));
-        x1 = fmaxf(x1, __shfl_xor_sync(0xffffffffu, x1, o));
-        y1 = fmaxf(y1, __shfl_xor_sync(0xffffffffu, y1, o));
-    }
-    if (lane == 0) rbox[r] = make_float4(x0, y0, x1, y1);
 }
 
 // lanes with cnt[lane] != 0 -> list (positions from an exclusive scan of the flags)
@@ -306,6 +321,7 @@ constexpr int kTWarps = kTThreads / 32;
 constexpr float kLog2e = 1.4426950408889634f;
 
 struct InsideTilePlan {
+    const float4* seg_a;     // centre rays of the (angle, column) pairs (planar.cuh)
     const int* tile_off;     // [n_tiles][n_patterns + 1]
     const int* tile_clo;     // [n_tiles][n_patterns]
     const int* zl;           // film layer of active layer a
@@ -320,7 +336,7 @@ struct InsideTilePlan {
 template <int kMode>
 __global__ void __launch_bounds__(kTThreads, 1)
 inside_tile_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ InsideTilePlan Z,
-                   const uint2* __restrict__ grp, const float4* __restrict__ table, const float4* __restrict__ rbox,
+                   const uint2* __restrict__ grp, const float4* __restrict__ table, const float2* __restrict__ rbox,
                    const float* __restrict__ in, float* __restrict__ out, float* __restrict__ planes, size_t n_vox,
                    const uint32_t* __restrict__ active_pixels, uint64_t n_active, float ray_weight,
                    const int* __restrict__ gate) {
@@ -399,17 +415,54 @@ inside_tile_kernel(const __grid_constant__ SceneParams P, const __grid_constant_
     const int sxb = 4 * 64, syb = 4 * 64 * pitch;
 
     int k = ka;
+    // The header of a group - (angle, column) from the range tables, its table rows, its centre ray, the lane's
+    // pattern value - is a chain of dependent loads; the chain of the NEXT group is issued before the current one
+    // is marched, so that a warp does not sit out the whole chain between two groups.
+    int kn = ka, cn = 0;
+    uint2 hdn = make_uint2(0u, 0u);
+    float4 csn = make_float4(0.f, 0.f, 1.f, 0.f);
+    float emn = 0.f;
+    auto fetch = [&](int g) {
+        hdn = make_uint2(0u, 0u);
+        if (g >= g_end) return;
+        while (__ldg(off + kn + 1) <= g) ++kn;
+        cn = __ldg(clo + kn) + (g - __ldg(off + kn));
+        hdn = __ldg(grp + (static_cast<size_t>(kn) * P.res_x + cn) * n_blk + blk);
+        csn = __ldg(Z.seg_a + static_cast<size_t>(kn) * P.res_x + cn);
+        emn = 1.f;
+        if (kMode == 0) emn = row >= 0 ? __ldg(in + active_index(P, kn - k0, row, cn)) * ray_weight : 0.f;
+    };
+    fetch(g_begin + warp);
     for (int g = g_begin + warp; g < g_end; g += kTWarps) {
-        while (__ldg(off + k + 1) <= g) ++k;
-        const int c = __ldg(clo + k) + (g - __ldg(off + k));
-        const uint2 hd = __ldg(grp + (static_cast<size_t>(k) * P.res_x + c) * n_blk + blk);
+        const int c = cn;
+        k = kn;
+        const uint2 hd = hdn;
+        const float4 cs = csn;
+        const float em = emn;
+        fetch(g + kTWarps);
         if (hd.y == 0) continue;
-        float em = 1.f;
-        if (kMode == 0) em = row >= 0 ? __ldg(in + active_index(P, k - k0, row, c)) * ray_weight : 0.f;
         float acc = 0.f;
+        // the stretch of the centre ray of (k, c) inside the tile, one voxel of margin
+        float T0 = 0.f, T1 = 0.f;
+        if (!clip_to_tile(P, cs, INFINITY, x0, y0, w, h, T0, T1, fmaxf(vsx, vsy))) continue;
+        // which rows reach this tile?  One coalesced load of (up to 32) row stretches, one ballot.
+        unsigned reach = 0xffffffffu;
+        if (hd.y <= 32) {
+            bool r = false;
+            if (static_cast<unsigned>(lane) < hd.y) {
+                const float2 rs = __ldg(rbox + hd.x + lane);
+                r = !(rs.x > T1 || rs.y < T0);
+            }
+            reach = __ballot_sync(0xffffffffu, r);
+            if (reach == 0) continue;
+        }
         for (unsigned i = 0; i < hd.y; ++i) {
-            const float4 box = __ldg(rbox + hd.x + i);   // does any record of the row reach this tile?
-            if (box.x > xh + vsx || box.z < xl - vsx || box.y > yh + vsy || box.w < yl - vsy) continue;
+            if (hd.y <= 32) {
+                if (!((reach >> i) & 1u)) continue;
+            } else {
+                const float2 rs = __ldg(rbox + hd.x + i);
+                if (rs.x > T1 || rs.y < T0) continue;
+            }
             const size_t slot = ((static_cast<size_t>(hd.x) + i) << 5) + lane;
             const float4 eb = __ldg(table + 2 * slot + 1);
             bool live = eb.x != 0.f && em != 0.f;
@@ -654,9 +707,10 @@ cudaError_t inside_build(const SceneParams& P, const SceneParams& P1, const Plan
             count_launch();
         }
         if (tiles) {
-            IN_TRY(cudaMalloc(&H.rbox, sizeof(float4) * std::max<uint64_t>(H.n_rows, 1)));
+            IN_TRY(cudaMalloc(&H.rbox, sizeof(float2) * std::max<uint64_t>(H.n_rows, 1)));
             if (H.n_rows) {
-                inside_row_box_kernel<<<blocks_for(H.n_rows * 32), kThreads>>>(H.table, H.n_rows, H.rbox);
+                inside_row_range_kernel<<<blocks_for(n_groups * 32), kThreads>>>(base.seg_a, H.grp, n_blk, H.table, n_groups,
+                                                                               H.rbox);
                 count_launch();
             }
         }
@@ -689,6 +743,7 @@ cudaError_t inside_build(const SceneParams& P, const SceneParams& P1, const Plan
             const float margin = std::fmax(P1.pixel_x, P1.pixel_y);
             IN_TRY(planar_tile_ranges(P1, base.seg_a, base.seg_b, H.tiles_x, H.tiles_y, H.tile_w, H.tile_h, H.tile_off,
                                       H.tile_clo, margin));
+            H.seg_a = base.seg_a;
             H.tiles = true;
         }
         IN_TRY(cudaDeviceSynchronize());
@@ -712,6 +767,7 @@ cudaError_t inside_forward_begin(InsideHost& H, cudaStream_t stream) {
 
 static InsideTilePlan tile_plan(const InsideHost& H, const PlanarZHost& Zh) {
     InsideTilePlan Z{};
+    Z.seg_a = H.seg_a;
     Z.tile_off = H.tile_off; Z.tile_clo = H.tile_clo;
     Z.zl = Zh.zl; Z.a_row_begin = Zh.a_row_begin; Z.a_rows = Zh.a_rows;
     Z.tiles_x = H.tiles_x; Z.tiles_y = H.tiles_y; Z.tile_w = H.tile_w; Z.tile_h = H.tile_h;
