@@ -77,6 +77,8 @@ struct PlanarZSub {      // a run of z-blocks that all hold 32 * lanes_l active 
     // `offset` on, the n deposit factors of its voxels with the step direction in the lowest mantissa bit
     float4* vhead = nullptr;
     float* vde = nullptr;
+    int* v_off = nullptr;     // prefix tables of the kept (non-empty) entries
+    int* v_ebase = nullptr;
     size_t smem_bytes = 0;
     int n_blocks = 0;
 };

@@ -46,8 +46,10 @@ struct PlanarZPlan {
     const int* tile_clo;     // [n_tiles][n_patterns]
     const int* tile_ebase;   // [n_tiles + 1] first walk entry of every tile
     const float4* entries;   // 2 x float4 per (tile, angle, column): the clipped walk, ready to march
-    const float4* vhead;     // visit lists of the adjoint: head per entry ...
+    const float4* vhead;     // visit lists of the adjoint: head per KEPT entry (.w = angle * res_x + column) ...
     const float* vde;        // ... and the deposit factors of its voxels
+    const int* v_off;        // [n_tiles][n_patterns + 1] prefix of the kept entries of a tile, per angle
+    const int* v_ebase;      // [n_tiles] kept entries before the tile
     const int* zl;           // [nz_pad] film layer of active layer a (-1 = padding)
     const int* a_row_begin;  // [nz + 1] CSR over a_rows: DMD rows that deposit in active layer a
     const int* a_rows;

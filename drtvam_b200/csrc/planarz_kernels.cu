@@ -620,6 +620,44 @@ vfill_kernel(const float4* __restrict__ entries, const int* __restrict__ voff, i
     vhead[e] = make_float4(e0.x, __uint_as_float(packed), __int_as_float(off), 0.f);
 }
 
+// ---- dropping the entries that visit nothing ---------------------------------------------------------------
+// planar_tile_ranges gives ONE column range per (tile, angle); behind a refracting box two ray families cross a
+// tile and the range spans everything between them, so at C4 most entries of a tile are empty.  The heads are
+// compacted to the entries with visits (keep -> exclusive scan -> copy); a kept head carries its
+// angle * res_x + column in .w, and the per-(tile, angle) prefix table is rewritten for the kept entries, so the
+// gather kernel walks a dense list and needs no range tables to find (angle, column).
+__global__ void __launch_bounds__(256)
+vkeep_kernel(const int* __restrict__ count, int total, int* __restrict__ keep) {
+    const int e = blockIdx.x * 256 + threadIdx.x;
+    if (e <= total) keep[e] = (e < total && count[e] > 0) ? 1 : 0;
+}
+
+__global__ void __launch_bounds__(256)
+vcompact_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ PlanarZPlan Z, const int* __restrict__ keep,
+                const int* __restrict__ kpos, int total, const float4* __restrict__ vhead, float4* __restrict__ vhead_c) {
+    const int e = blockIdx.x * 256 + threadIdx.x;
+    if (e >= total || !keep[e]) return;
+    int tile_id, k, c;
+    locate_entry(P, Z, e, tile_id, k, c);
+    float4 h = vhead[e];
+    h.w = __int_as_float(k * P.res_x + c);
+    vhead_c[kpos[e]] = h;
+}
+
+// v_off[t][k] = kept entries of tile t before angle k; v_ebase[t] = kept entries before tile t
+__global__ void __launch_bounds__(256)
+vremap_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ PlanarZPlan Z, const int* __restrict__ kpos,
+              int* __restrict__ v_off, int* __restrict__ v_ebase) {
+    const int n_tiles = Z.tiles_x * Z.tiles_y, np1 = P.n_patterns + 1;
+    const long long i = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x;
+    if (i >= static_cast<long long>(n_tiles) * np1) return;
+    const int t = static_cast<int>(i / np1), k = static_cast<int>(i - static_cast<long long>(t) * np1);
+    const int eb = __ldg(Z.tile_ebase + t);
+    const int first = kpos[eb];
+    v_off[i] = kpos[eb + __ldg(Z.tile_off + i)] - first;
+    if (k == 0) v_ebase[t] = first;
+}
+
 // in = dL (film layout), out = gT.  Same CTA / tile / z-block structure as planarz_kernel<kGather>.
 template <int kL>
 __global__ void __launch_bounds__(kZThreads, 1)
@@ -655,15 +693,13 @@ planarv_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
     call_angles(P, active_pixels, n_active, k0, nk);
     const int ka = k0 + static_cast<int>(static_cast<long long>(nk) * group / Z.groups);
     const int kb = k0 + static_cast<int>(static_cast<long long>(nk) * (group + 1) / Z.groups);
-    const int* __restrict__ off = Z.tile_off + static_cast<size_t>(tile_id) * (P.n_patterns + 1);
-    const int* __restrict__ clo = Z.tile_clo + static_cast<size_t>(tile_id) * P.n_patterns;
-    const size_t ebase = static_cast<size_t>(__ldg(Z.tile_ebase + tile_id));
+    const int* __restrict__ off = Z.v_off + static_cast<size_t>(tile_id) * (P.n_patterns + 1);
+    const size_t ebase = static_cast<size_t>(__ldg(Z.v_ebase + tile_id));
     const float4* __restrict__ vhead = Z.vhead + ebase;
     const uint32_t tile_s = static_cast<uint32_t>(__cvta_generic_to_shared(tile)) + 4u * kL * lane;
     const int sxb = 4 * kVox, syb = 4 * kVox * tw;
 
     const int f_base = __ldg(off + ka), total = __ldg(off + kb) - f_base;
-    int k = ka;
     // the head and the list of the NEXT entry are fetched while the current one is walked
     float4 head = make_float4(0.f, 0.f, 0.f, 0.f);
     float d_lo = 0.f, d_hi = 0.f;
@@ -686,10 +722,8 @@ planarv_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
         const unsigned packed = __float_as_uint(hd.y);
         const int n = (packed >> 16) & 0x7f;
         if (n == 0) continue;
-        const int g = f + f_base;
-        while (__ldg(off + k + 1) <= g) ++k;
-        const int c = __ldg(clo + k) + (g - __ldg(off + k));
-        const size_t tbase = (static_cast<size_t>(k - k0) * P.res_x + c) * Z.nz_pad + a_base + lane;
+        // angle * res_x + column of the entry, relative to the first angle of the call
+        const size_t tbase = (static_cast<size_t>(__float_as_int(hd.w)) - static_cast<size_t>(k0) * P.res_x) * Z.nz_pad + a_base + lane;
         const int sx = (packed & (1u << 30)) ? -sxb : sxb, sy = (packed & (1u << 31)) ? -syb : syb;
         uint32_t addr = tile_s + static_cast<uint32_t>((packed & 0xffffu) * (4 * kVox));
         float acc[kL];
@@ -1210,7 +1244,7 @@ planarg_mma_kernel(const __grid_constant__ SceneParams P, const __grid_constant_
 
 void planarz_release(PlanarZHost& H) {
     for (PlanarZSub& S : H.sub) {
-        void* ptrs[] = {S.tile_off, S.tile_clo, S.tile_ebase, S.entries, S.vhead, S.vde};
+        void* ptrs[] = {S.tile_off, S.tile_clo, S.tile_ebase, S.entries, S.vhead, S.vde, S.v_off, S.v_ebase};
         for (void* p : ptrs)
             if (p) cudaFree(p);
     }
@@ -1318,7 +1352,30 @@ static cudaError_t z_build_sub(const SceneParams& P, const PlanarHost& base, con
             if (too_long) {   // a walk of more than kVisitMax voxels: this sub-plan keeps the DDA kernel
                 cudaFree(S.vhead); cudaFree(S.vde);
                 S.vhead = nullptr; S.vde = nullptr;
+                return cudaSuccess;
             }
+            // compact the heads to the entries with visits (`count` becomes the keep flags, `voff` their positions)
+            vkeep_kernel<<<(n1 + 255) / 256, 256>>>(count, static_cast<int>(total), count);
+            count_launch();
+            PZ_TRY(cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, count, voff, n1));
+            count_launch();
+            int kept = 0;
+            PZ_TRY(cudaMemcpy(&kept, voff + total, sizeof(int), cudaMemcpyDeviceToHost));
+            float4* vhead_c = nullptr;
+            PZ_TRY(cudaMalloc(&vhead_c, sizeof(float4) * static_cast<size_t>(std::max(kept, 1))));
+            vcompact_kernel<<<static_cast<unsigned>((total + 255) / 256), 256>>>(P, Z, count, voff, static_cast<int>(total),
+                                                                                 S.vhead, vhead_c);
+            count_launch();
+            PZ_TRY(cudaMalloc(&S.v_off, sizeof(int) * static_cast<size_t>(n_tiles) * (np + 1)));
+            PZ_TRY(cudaMalloc(&S.v_ebase, sizeof(int) * n_tiles));
+            const long long cells = static_cast<long long>(n_tiles) * (np + 1);
+            vremap_kernel<<<static_cast<unsigned>((cells + 255) / 256), 256>>>(P, Z, voff, S.v_off, S.v_ebase);
+            count_launch();
+            PZ_TRY(cudaDeviceSynchronize());
+            cudaFree(S.vhead);
+            S.vhead = vhead_c;
+            if (std::getenv("DRTVAM_DEBUG"))
+                fprintf(stderr, "[drtvam] visit lists (kL %d): %d of %lld entries kept, %d visits\n", kL, kept, total, visits);
             return cudaSuccess;
         };
         const cudaError_t ve = run();
@@ -1331,7 +1388,7 @@ static cudaError_t z_build_sub(const SceneParams& P, const PlanarHost& base, con
             if (S.vde) cudaFree(S.vde);
             S.vhead = nullptr; S.vde = nullptr;
         }
-        Z.vhead = S.vhead; Z.vde = S.vde;
+        Z.vhead = S.vhead; Z.vde = S.vde; Z.v_off = S.v_off; Z.v_ebase = S.v_ebase;
     }
     if (kL == 1) return z_set_smem<1>(S.smem_bytes);
     if (kL == 2) return z_set_smem<2>(S.smem_bytes);
