@@ -61,6 +61,10 @@ cudaError_t launch_planar_adjoint(const SceneParams& P, PlanarHost& H, const flo
 // per-(tile, angle) first crossing column and prefix sums of the crossing-column counts
 cudaError_t planar_tile_ranges(const SceneParams& P, const float4* seg_a, const float2* seg_b, int tiles_x, int tiles_y,
                                int tile_w, int tile_h, int* tile_off_dev, int* tile_clo_dev, float margin = 0.f);
+// per-tile column lists instead of ranges (exact where a range would span the gap between two ray families)
+cudaError_t planar_tile_lists(const SceneParams& P, const float4* seg_a, const float2* seg_b, int tiles_x, int tiles_y,
+                              int tile_w, int tile_h, int* tile_off_dev, int* tile_ebase_dev, int** list_dev,
+                              long long* n_entries, float margin = 0.f);
 // mode 0: deposit the frozen-axis rays into the film; mode 1: write their pattern gradients
 cudaError_t launch_planar_frozen(const SceneParams& P, PlanarHost& H, int mode, const float* in, float* out,
                                  const uint32_t* active_pixels, uint64_t n_active, float ray_weight,
@@ -118,7 +122,8 @@ struct PlanarJHost {
     bool valid = false;
     int tiles_x = 0, tiles_y = 0, tile_w = 0, tile_h = 0;
     int* tile_off = nullptr;       // [n_tiles][n_patterns + 1] prefix of the (conservative) column counts
-    int* tile_clo = nullptr;       // [n_tiles][n_patterns]
+    int* tile_clo = nullptr;       // the column list: angle * res_x + column of every (tile, angle, column) entry
+    int* tile_ebase = nullptr;     // [n_tiles + 1] first entry of every tile in the list
     void* table = nullptr;         // per-lane segment table of the current angle chunk (forward passes)
     size_t table_bytes = 0;
     void* table_adj = nullptr;     // the same for adjoint passes

@@ -43,7 +43,7 @@ struct PlanarZPlan {
     const float2* seg_b;
     const SegmentD* seg_d;   // the same segments in double precision (set-up kernels only)
     const int* tile_off;     // [n_tiles][n_patterns + 1] prefix of per-angle column counts
-    const int* tile_clo;     // [n_tiles][n_patterns]
+    const int* tile_clo;     // [n_tiles][n_patterns]; the jittered kernels: list of angle * res_x + column per entry
     const int* tile_ebase;   // [n_tiles + 1] first walk entry of every tile
     const float4* entries;   // 2 x float4 per (tile, angle, column): the clipped walk, ready to march
     const float4* vhead;     // visit lists of the adjoint: head per KEPT entry (.w = angle * res_x + column) ...

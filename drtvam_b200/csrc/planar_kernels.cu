@@ -112,6 +112,42 @@ __global__ void planar_ranges_kernel(const __grid_constant__ SceneParams P, cons
     cnt[i] = hi >= lo ? hi - lo + 1 : 0;
 }
 
+// The same question per column instead of per range: kFill = false counts, kFill = true writes angle * res_x + column
+// of every column of angle k whose centre ray (or, with a margin, one of its two neighbours') crosses the tile.
+// One column range per (tile, angle) is enough for a single family of rays; behind a refracting box two families
+// cross a tile and the range spans everything between them (most of it empty).
+template <bool kFill>
+__global__ void planar_lists_kernel(const __grid_constant__ SceneParams P, const PlanarPlan L, const int* __restrict__ off,
+                                    const int* __restrict__ ebase, int* __restrict__ cnt, int* __restrict__ list,
+                                    float margin) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n_tiles = L.tiles_x * L.tiles_y;
+    if (i >= n_tiles * P.n_patterns) return;
+    const int tile = i / P.n_patterns, k = i - tile * P.n_patterns;
+    const int x0 = (tile % L.tiles_x) * L.tile_w, y0 = (tile / L.tiles_x) * L.tile_h;
+    const int w = min(L.tile_w, P.res[0] - x0), h = min(L.tile_h, P.res[1] - y0);
+    int n = 0;
+    int* dst = kFill ? list + ebase[tile] + off[tile * (P.n_patterns + 1) + k] : nullptr;
+    bool prev = false, cur = false;   // column c - 1, column c
+    auto crosses = [&](int c) {
+        if (c >= P.res_x) return false;
+        const float2 b = L.seg_b[k * P.res_x + c];
+        float t0, t1;
+        return b.y != 0.f && clip_to_tile(P, L.seg_a[k * P.res_x + c], b.x, x0, y0, w, h, t0, t1, margin);
+    };
+    cur = crosses(0);
+    for (int c = 0; c < P.res_x; ++c) {
+        const bool next = crosses(c + 1);
+        if (cur || (margin > 0.f && (prev || next))) {
+            if (kFill) dst[n] = k * P.res_x + c;
+            ++n;
+        }
+        prev = cur;
+        cur = next;
+    }
+    if (!kFill) cnt[i] = n;
+}
+
 // gate[0] != 0  <=>  active_pixels is not the dense layout the planar kernels index implicitly - DMD rows
 // [row_begin, row_begin + n_rows) of consecutive whole patterns, every column, in order - i.e. the planar
 // kernels must stand down and the general tracer runs instead.
@@ -376,6 +412,43 @@ cudaError_t planar_tile_ranges(const SceneParams& P, const float4* seg_a, const 
         off[t * (np + 1) + np] = acc;
     }
     return cudaMemcpy(tile_off_dev, off.data(), sizeof(int) * off.size(), cudaMemcpyHostToDevice);
+}
+
+// Per-tile column LISTS: off[t][k] = entries of tile t before angle k, ebase[t] = entries before tile t,
+// *list_dev (allocated here) = angle * res_x + column of every entry.
+cudaError_t planar_tile_lists(const SceneParams& P, const float4* seg_a, const float2* seg_b, int tiles_x, int tiles_y,
+                              int tile_w, int tile_h, int* tile_off_dev, int* tile_ebase_dev, int** list_dev,
+                              long long* n_entries, float margin) {
+    const int n_tiles = tiles_x * tiles_y, np = P.n_patterns;
+    PlanarPlan L{};
+    L.seg_a = seg_a; L.seg_b = seg_b;
+    L.tiles_x = tiles_x; L.tiles_y = tiles_y; L.tile_w = tile_w; L.tile_h = tile_h;
+    int* cnt_dev = nullptr;
+    PL_TRY(cudaMalloc(&cnt_dev, sizeof(int) * n_tiles * np));
+    planar_lists_kernel<false><<<(n_tiles * np + 127) / 128, 128>>>(P, L, nullptr, nullptr, cnt_dev, nullptr, margin);
+    count_launch();
+    std::vector<int> cnt(static_cast<size_t>(n_tiles) * np), off(static_cast<size_t>(n_tiles) * (np + 1)), ebase(n_tiles + 1);
+    cudaError_t e = cudaMemcpy(cnt.data(), cnt_dev, sizeof(int) * cnt.size(), cudaMemcpyDeviceToHost);
+    cudaFree(cnt_dev);
+    PL_TRY(e);
+    long long total = 0;
+    for (int t = 0; t < n_tiles; ++t) {
+        int acc = 0;
+        for (int k = 0; k < np; ++k) { off[t * (np + 1) + k] = acc; acc += cnt[t * np + k]; }
+        off[t * (np + 1) + np] = acc;
+        ebase[t] = static_cast<int>(total);
+        total += acc;
+    }
+    if (total >= (1ll << 31)) return cudaErrorInvalidValue;
+    ebase[n_tiles] = static_cast<int>(total);
+    PL_TRY(cudaMemcpy(tile_off_dev, off.data(), sizeof(int) * off.size(), cudaMemcpyHostToDevice));
+    PL_TRY(cudaMemcpy(tile_ebase_dev, ebase.data(), sizeof(int) * ebase.size(), cudaMemcpyHostToDevice));
+    PL_TRY(cudaMalloc(list_dev, sizeof(int) * static_cast<size_t>(std::max<long long>(total, 1))));
+    planar_lists_kernel<true><<<(n_tiles * np + 127) / 128, 128>>>(P, L, tile_off_dev, tile_ebase_dev, nullptr, *list_dev,
+                                                                 margin);
+    count_launch();
+    *n_entries = total;
+    return cudaDeviceSynchronize();
 }
 
 // Builds the segment table, the layer -> rows CSR and the per-tile column

@@ -222,7 +222,7 @@ planarj_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
     const int ka = kfirst + static_cast<int>(static_cast<long long>(Ly.nkc) * group / Z.groups);
     const int kb = kfirst + static_cast<int>(static_cast<long long>(Ly.nkc) * (group + 1) / Z.groups);
     const int* __restrict__ off = Z.tile_off + static_cast<size_t>(tile_id) * (P.n_patterns + 1);
-    const int* __restrict__ clo = Z.tile_clo + static_cast<size_t>(tile_id) * P.n_patterns;
+    const int* __restrict__ lst = Z.tile_clo + __ldg(Z.tile_ebase + tile_id);   // angle * res_x + column per entry
 
     const float sig = P.sigma_t * kLog2e;
     const float vsx = (P.bmax[0] - P.bmin[0]) / static_cast<float>(P.res[0]);
@@ -241,8 +241,9 @@ planarj_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
     for (int f = warp; f < tasks; f += kJWarps) {
         const int g = f / Ly.items + f_base;
         const int q = f - (g - f_base) * Ly.items;
-        while (__ldg(off + k + 1) <= g) ++k;
-        const int c = __ldg(clo + k) + (g - __ldg(off + k));
+        const int kc = __ldg(lst + g);
+        k = kc / P.res_x;
+        const int c = kc - k * P.res_x;
         // < 2^31 slots per chunk (planarj_pass): 32-bit index arithmetic
         const unsigned slot = ((static_cast<unsigned>(k - kfirst) * slots_kc + (static_cast<unsigned>(c) * Ly.n_blk + blk) * Ly.items + q) << 5) + lane;
         const float4 eb = __ldg(T.b + slot);
@@ -390,7 +391,7 @@ junpack_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
     } while (0)
 
 void planarj_release(PlanarJHost& J) {
-    void* ptrs[] = {J.tile_off, J.tile_clo, J.table, J.table_adj, J.gT};
+    void* ptrs[] = {J.tile_off, J.tile_clo, J.tile_ebase, J.table, J.table_adj, J.gT};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     J = PlanarJHost();
@@ -415,10 +416,13 @@ cudaError_t planarj_build(const SceneParams& P, const PlanarHost& base, const Pl
     J.smem_bytes = sizeof(float) * static_cast<size_t>(J.tile_h + 2) * (J.tile_w + 2) * 32;
     const int n_tiles = J.tiles_x * J.tiles_y;
     PJ_TRY(cudaMalloc(&J.tile_off, sizeof(int) * static_cast<size_t>(n_tiles) * (np + 1)));
-    PJ_TRY(cudaMalloc(&J.tile_clo, sizeof(int) * static_cast<size_t>(n_tiles) * np));
+    PJ_TRY(cudaMalloc(&J.tile_ebase, sizeof(int) * (n_tiles + 1)));
     const float margin = 1.5f * std::fmax(P.pixel_x, P.pixel_y);
-    PJ_TRY(planar_tile_ranges(P, base.seg_a, base.seg_b, J.tiles_x, J.tiles_y, J.tile_w, J.tile_h, J.tile_off, J.tile_clo,
-                              margin));
+    // column LISTS, not ranges: behind a refracting box the range of a (tile, angle) spans the gap between the two
+    // ray families that cross the tile, and every column in it costs a table read and a clip per item
+    long long n_entries = 0;
+    PJ_TRY(planar_tile_lists(P, base.seg_a, base.seg_b, J.tiles_x, J.tiles_y, J.tile_w, J.tile_h, J.tile_off, J.tile_ebase,
+                             &J.tile_clo, &n_entries, margin));
     PJ_TRY(cudaFuncSetAttribute(planarj_kernel<kScatter>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 static_cast<int>(J.smem_bytes)));
     PJ_TRY(cudaFuncSetAttribute(planarj_kernel<kGather>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -477,7 +481,7 @@ static cudaError_t planarj_pass(const SceneParams& P, const SceneParams& Pw, Pla
     Z.zl = Zh.zl; Z.a_row_begin = Zh.a_row_begin; Z.a_rows = Zh.a_rows; Z.row_a = Zh.row_a;
     Z.nz = Zh.nz; Z.nz_pad = Zh.nz_pad;
     Z.tiles_x = J.tiles_x; Z.tiles_y = J.tiles_y; Z.tile_w = J.tile_w; Z.tile_h = J.tile_h;
-    Z.tile_off = J.tile_off; Z.tile_clo = J.tile_clo;
+    Z.tile_off = J.tile_off; Z.tile_clo = J.tile_clo; Z.tile_ebase = J.tile_ebase;
     Z.lanes_l = 1;
     const long long ctas = static_cast<long long>(J.tiles_x) * J.tiles_y * Ly.n_blk;
 
