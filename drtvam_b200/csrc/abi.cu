@@ -456,6 +456,13 @@ int drtvam_scene_stat(DrtvamScene* s, int32_t which, uint64_t* value) {
         case 1: *value = s->zplan.valid ? static_cast<uint64_t>(s->zplan.nz) : 0; break;
         case 2: *value = s->inside.valid ? s->inside.n_rec + s->inside.n_rows * 32 : 0; break;
         case 3: *value = tables ? static_cast<uint64_t>(s->gplan.pairs) * 68u : 0; break;
+        case 4: {
+            unsigned n = 0;
+            if (s->jplan.valid && s->jplan.wmax)
+                CUDA_TRY(cudaMemcpy(&n, s->jplan.wmax + 1, sizeof(n), cudaMemcpyDeviceToHost));
+            *value = n;
+            break;
+        }
         default: return fail(DRTVAM_E_INVALID, "unknown statistic %d", which);
     }
     return DRTVAM_OK;

@@ -131,6 +131,8 @@ struct PlanarJHost {
     float* gT = nullptr;           // adjoint: per-lane gradients in table order
     size_t gT_bytes = 0;
     size_t smem_bytes = 0;
+    unsigned* wmax = nullptr;      // [0] largest |weight x pattern value| of the current forward table (float bits),
+                                   // [1] fixed-point tile words that came close to overflow (never seen)
     // the table still holds the geometry of the last forward pass (same pixels, seed, spp, weight)
     bool cache_valid = false;
     uint32_t cache_seed = 0, cache_spp = 0;

@@ -23,6 +23,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
+#include <cstring>
 #include <vector>
 
 #include "kernels.h"
@@ -57,6 +58,14 @@ __device__ __forceinline__ uint32_t sampler_stream(const SceneParams& P, size_t 
     return static_cast<uint32_t>(g * spp + smp);
 }
 
+// wmax[0] = largest |weight x pattern value| of the table of a forward pass, as the bits of a non-negative float
+// (ordered like unsigned integers): the scale of the fixed-point tile of planarj_kernel.  The plain read first
+// keeps all but the first few thousand lanes off the atomic.
+__device__ __forceinline__ void note_weight(unsigned* wmax, float v) {
+    const unsigned b = __float_as_uint(fabsf(v));
+    if (b < 0x7f800000u && b > *reinterpret_cast<volatile unsigned*>(wmax)) atomicMax(wmax, b);
+}
+
 // One thread per table slot.  kScatter: in = active_data, out = film (only lanes walked here touch it).
 // kGather: in = dL, gT = per-slot gradient (lanes walked here write theirs, every other slot is zeroed).
 // kRefresh (forward only): the geometry in the table is that of this very call - same pixels, seed and
@@ -68,7 +77,7 @@ jtable_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Sce
               const __grid_constant__ PlanarZPlan Z, const int* __restrict__ layer_a, const JLayout Ly,
               const float* __restrict__ in, float* __restrict__ out, float* __restrict__ gT,
               const uint32_t* __restrict__ active_pixels, uint64_t n_active, uint32_t spp, uint32_t seed,
-              float ray_weight, JTable T, const int* __restrict__ gate) {
+              float ray_weight, JTable T, const int* __restrict__ gate, unsigned* __restrict__ wmax) {
     if (*gate != 0) return;
     const size_t t = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x;
     const size_t total = static_cast<size_t>(Ly.nkc) * P.res_x * Ly.n_blk * Ly.items * 32;
@@ -105,6 +114,7 @@ jtable_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Sce
         if (kMode == kScatter) em = __ldg(in + j);
         if (kRefresh && state >= 0) {
             T.b[t].w = em;
+            note_weight(wmax, T.b[t].y * em);
             return;
         }
         // the gate has verified the layout, so the pixel index follows from (angle, row, column)
@@ -161,6 +171,7 @@ jtable_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Sce
     if (kRefresh) return;
     T.a[t] = ea;
     T.b[t] = eb;
+    if (kMode == kScatter && __float_as_int(eb.z) >= 0) note_weight(wmax, eb.y * eb.w);
     if (kMode == kGather) gT[t] = g_here;
 }
 
@@ -175,11 +186,21 @@ jtable_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Sce
 // Walk of one lane: optical depths relative to the tile entry; each trip deposits the current voxel up
 // to min(next boundary, tile exit) and steps across the nearer boundary, so the last voxel needs no
 // code of its own and the loop carries no step counters: 17 instructions per visit instead of 27.
-template <int kMode>
+//
+// kInt (forward only): the tile holds 32-bit FIXED-POINT sums and a deposit is one red.shared.add.s32 - a native
+// shared-memory atomic, fire and forget - instead of the LDS + FADD + ATOMS.CAST.SPIN loop that red.shared.add.f32
+// compiles to, which a warp has to wait out (37 % of the stall samples of the march, profiles/r02zf_*).  The scale
+// is chosen per CTA from the largest |weight x pattern value| of the table (wmax, written by jtable_kernel) so that
+// 64 times the deposits a voxel can receive from 4 columns per angle and item still fit 31 bits; integer addition is
+// exact, and a deposit is rounded to nearest at 2^-25 / (angles x items) of the largest possible one - far below
+// fp32's own rounding of a sum of that many terms.  A word whose magnitude passes 2^30 at the flush is counted
+// in wmax[1] (drtvam_scene_stat): never seen, a tripwire for rays focused 16 times denser than assumed.
+template <int kMode, bool kInt>
 __global__ void __launch_bounds__(kJThreads, 1)
 planarj_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ PlanarZPlan Z, const JLayout Ly,
                const JTable T, const float* __restrict__ in, float* __restrict__ out,
-               const uint32_t* __restrict__ active_pixels, uint64_t n_active, const int* __restrict__ gate) {
+               const uint32_t* __restrict__ active_pixels, uint64_t n_active, const int* __restrict__ gate,
+               unsigned* __restrict__ wmax) {
     extern __shared__ __align__(16) float tile[];
     if (*gate != 0) return;
     const int tile_id = blockIdx.x, blk = blockIdx.y, group = blockIdx.z;
@@ -233,6 +254,16 @@ planarj_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
     const float yl = P.bmin[1] + static_cast<float>(y0) * vsy, yh = P.bmin[1] + static_cast<float>(y0 + h) * vsy;
     const uint32_t tile_s = static_cast<uint32_t>(__cvta_generic_to_shared(tile));
     const int sxb = 4 * 32, syb = 4 * 32 * pitch;
+    // fixed-point scale of this CTA's tile: 2^25 / (angles x items x largest deposit)
+    float fx_scale = 0.f, fx_inv = 0.f;
+    if (kInt) {
+        const float de_max = 1.f - ex2_approx(-sig * (vsx + vsy));     // no chord through a voxel is longer
+        const float d_max = __uint_as_float(*reinterpret_cast<volatile unsigned*>(wmax)) * de_max;
+        if (d_max > 0.f) {
+            fx_scale = 33554432.f / (static_cast<float>(max(kb - ka, 1)) * static_cast<float>(Ly.items) * d_max);
+            fx_inv = 1.f / fx_scale;
+        }
+    }
 
     const int f_base = __ldg(off + ka);
     const int tasks = (__ldg(off + kb) - f_base) * Ly.items;   // < 2^31: checked by planarj_pass
@@ -300,6 +331,7 @@ planarj_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
             }
             uint32_t addr = tile_s + 4u * static_cast<uint32_t>(((iy + 1) * pitch + ix + 1) * 32 + lyr);
             wgt *= ex2_approx(-sig * t0);
+            if (kInt) wgt *= fx_scale;
             float e_prev = 1.f;
             // one trip: deposit the current voxel up to min(next boundary, tile exit), step across the
             // nearer boundary.  Unrolled by two so that the carried 2^-u needs no register move.
@@ -312,6 +344,8 @@ planarj_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
                     float v;
                     asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
                     acc = fmaf(v, de, acc);
+                } else if (kInt) {
+                    asm volatile("red.shared.add.s32 [%0], %1;" ::"r"(addr), "r"(__float2int_rn(wgt * de)) : "memory");
                 } else {
                     asm volatile("red.shared.add.f32 [%0], %1;" ::"r"(addr), "f"(wgt * de) : "memory");
                 }
@@ -338,14 +372,25 @@ planarj_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
         for (int i = warp; i < h * w4; i += kJWarps) {
             const int yy = i / w4, xx = (i - yy * w4) << 2;
             const float* src = tile + ((yy + 1) * pitch + xx + 1) * 32 + lane;
-            const float v0 = src[0], v1 = src[32], v2 = src[64], v3 = src[96];
+            float v0 = src[0], v1 = src[32], v2 = src[64], v3 = src[96];
+            if (kInt) {
+                const int i0 = __float_as_int(v0), i1 = __float_as_int(v1), i2 = __float_as_int(v2), i3 = __float_as_int(v3);
+                if (max(max(abs(i0), abs(i1)), max(abs(i2), abs(i3))) > (1 << 30)) atomicAdd(wmax + 1, 1u);
+                v0 = static_cast<float>(i0) * fx_inv; v1 = static_cast<float>(i1) * fx_inv;
+                v2 = static_cast<float>(i2) * fx_inv; v3 = static_cast<float>(i3) * fx_inv;
+            }
             if (v0 != 0.f || v1 != 0.f || v2 != 0.f || v3 != 0.f)
                 red_add_v4(dst + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx), v0, v1, v2, v3);
         }
     } else {
         for (int i = warp; i < h * w; i += kJWarps) {
             const int yy = i / w, xx = i - yy * w;
-            const float v = tile[((yy + 1) * pitch + xx + 1) * 32 + lane];
+            float v = tile[((yy + 1) * pitch + xx + 1) * 32 + lane];
+            if (kInt) {
+                const int iv = __float_as_int(v);
+                if (abs(iv) > (1 << 30)) atomicAdd(wmax + 1, 1u);
+                v = static_cast<float>(iv) * fx_inv;
+            }
             if (v != 0.f) atomicAdd(dst + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx), v);
         }
     }
@@ -391,7 +436,7 @@ junpack_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
     } while (0)
 
 void planarj_release(PlanarJHost& J) {
-    void* ptrs[] = {J.tile_off, J.tile_clo, J.tile_ebase, J.table, J.table_adj, J.gT};
+    void* ptrs[] = {J.tile_off, J.tile_clo, J.tile_ebase, J.table, J.table_adj, J.gT, J.wmax};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     J = PlanarJHost();
@@ -423,10 +468,14 @@ cudaError_t planarj_build(const SceneParams& P, const PlanarHost& base, const Pl
     long long n_entries = 0;
     PJ_TRY(planar_tile_lists(P, base.seg_a, base.seg_b, J.tiles_x, J.tiles_y, J.tile_w, J.tile_h, J.tile_off, J.tile_ebase,
                              &J.tile_clo, &n_entries, margin));
-    PJ_TRY(cudaFuncSetAttribute(planarj_kernel<kScatter>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    PJ_TRY(cudaFuncSetAttribute(planarj_kernel<kScatter, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 static_cast<int>(J.smem_bytes)));
-    PJ_TRY(cudaFuncSetAttribute(planarj_kernel<kGather>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    PJ_TRY(cudaFuncSetAttribute(planarj_kernel<kScatter, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 static_cast<int>(J.smem_bytes)));
+    PJ_TRY(cudaFuncSetAttribute(planarj_kernel<kGather, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                static_cast<int>(J.smem_bytes)));
+    PJ_TRY(cudaMalloc(&J.wmax, 2 * sizeof(unsigned)));
+    PJ_TRY(cudaMemset(J.wmax, 0, 2 * sizeof(unsigned)));
     J.valid = true;
     return cudaSuccess;
 }
@@ -495,12 +544,13 @@ static cudaError_t planarj_pass(const SceneParams& P, const SceneParams& Pw, Pla
         Ly.nkc = std::min(chunk, nk - kc);
         const size_t slots = slots_per_angle * Ly.nkc;
         const unsigned tblocks = static_cast<unsigned>((slots + 255) / 256);
+        if (kMode == kScatter) PJ_TRY(cudaMemsetAsync(J.wmax, 0, sizeof(unsigned), stream));   // the weight maximum of this table
         if (reuse)
             jtable_kernel<kScatter, true><<<tblocks, 256, 0, stream>>>(P, Pw, Z, Zh.layer_a, Ly, in, out, J.gT, active_pixels,
-                                                                      n_active, spp, seed, ray_weight, T, gate);
+                                                                      n_active, spp, seed, ray_weight, T, gate, J.wmax);
         else
             jtable_kernel<kMode, false><<<tblocks, 256, 0, stream>>>(P, Pw, Z, Zh.layer_a, Ly, in, out, J.gT, active_pixels,
-                                                                    n_active, spp, seed, ray_weight, T, gate);
+                                                                    n_active, spp, seed, ray_weight, T, gate, J.wmax);
         count_launch();
         PJ_TRY(cudaGetLastError());
         // enough CTAs for two waves of the 148 SMs: the tile flush is a red.global, so angle groups are free
@@ -508,8 +558,18 @@ static cudaError_t planarj_pass(const SceneParams& P, const SceneParams& Pw, Pla
         groups = std::max<long long>(1, std::min<long long>(groups, std::max(1, Ly.nkc / 4)));
         Z.groups = static_cast<int>(groups);
         const dim3 grid(J.tiles_x * J.tiles_y, Ly.n_blk, Z.groups);
-        planarj_kernel<kMode><<<grid, kJThreads, J.smem_bytes, stream>>>(P, Z, Ly, T, in, kMode == kGather ? J.gT : out,
-                                                                        active_pixels, n_active, gate);
+        // DRTVAM_JITTER_ATOMICS=float keeps the fp32 compare-and-swap tile (A/B measurements)
+        static const bool fixed_point = !(std::getenv("DRTVAM_JITTER_ATOMICS") &&
+                                          std::strcmp(std::getenv("DRTVAM_JITTER_ATOMICS"), "float") == 0);
+        if (kMode == kGather)
+            planarj_kernel<kGather, false><<<grid, kJThreads, J.smem_bytes, stream>>>(P, Z, Ly, T, in, J.gT, active_pixels,
+                                                                                     n_active, gate, J.wmax);
+        else if (fixed_point)
+            planarj_kernel<kScatter, true><<<grid, kJThreads, J.smem_bytes, stream>>>(P, Z, Ly, T, in, out, active_pixels,
+                                                                                     n_active, gate, J.wmax);
+        else
+            planarj_kernel<kScatter, false><<<grid, kJThreads, J.smem_bytes, stream>>>(P, Z, Ly, T, in, out, active_pixels,
+                                                                                      n_active, gate, J.wmax);
         count_launch();
         PJ_TRY(cudaGetLastError());
         if (kMode == kGather) {

@@ -225,7 +225,9 @@ int drtvam_scene_force_general(DrtvamScene *scene, int32_t on);
  *   0 = (4x4 patch, segment) coefficient pairs of the patch-gather forward (0 = tables not in use),
  *   1 = voxel layers that receive dose from the DMD rows of this handle (inside the z window),
  *   2 = target-crossing records of a surface-aware deterministic scene,
- *   3 = bytes of the coefficient table of the patch-gather forward (64 B of coefficients + 4 B ray index per pair). */
+ *   3 = bytes of the coefficient table of the patch-gather forward (64 B of coefficients + 4 B ray index per pair),
+ *   4 = fixed-point tile words of the jittered forward kernels that came within a factor 2 of overflow since the
+ *       scene was created (synchronises; 0 unless rays are focused 16 times denser than the scale assumes). */
 int drtvam_scene_stat(DrtvamScene *scene, int32_t which, uint64_t *value);
 
 /* A p : VolumeIntegrator.render (volume.py:18-56).  dose has

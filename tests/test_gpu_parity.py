@@ -444,6 +444,10 @@ def test_jittered_planar_matches_general_and_oracle(name, workdir):
         rays = pix.size * spp
         assert_jitter_parity(f_fast, f_ref, max(8, rays // 5000), 3 * n, TOL, what=f"{name} spp {spp} dose vs f32 oracle")
         assert_jitter_parity(a_fast, a_ref, max(8, rays // 5000), 1, TOL, what=f"{name} spp {spp} grad vs f32 oracle")
+    # the fixed-point tiles of the forward kernels never came near overflow (drtvam_scene_stat 4)
+    n_over = C.c_uint64(1)
+    _lib.check(fast.lib.drtvam_scene_stat(fast.h, 4, C.byref(n_over)))
+    assert n_over.value == 0
 
 
 def test_jittered_planar_rectangular_grid(workdir):
