@@ -460,7 +460,10 @@ int drtvam_scene_stat(DrtvamScene* s, int32_t which, uint64_t* value) {
             unsigned n = 0;
             if (s->jplan.valid && s->jplan.wmax)
                 CUDA_TRY(cudaMemcpy(&n, s->jplan.wmax + 1, sizeof(n), cudaMemcpyDeviceToHost));
-            *value = n;
+            unsigned m = 0;
+            if (s->inside.valid && s->inside.stat)
+                CUDA_TRY(cudaMemcpy(&m, s->inside.stat + 2, sizeof(m), cudaMemcpyDeviceToHost));
+            *value = static_cast<uint64_t>(n) + m;
             break;
         }
         default: return fail(DRTVAM_E_INVALID, "unknown statistic %d", which);

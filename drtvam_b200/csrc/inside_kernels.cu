@@ -29,6 +29,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
+#include <cstring>
 
 #include <cub/device/device_scan.cuh>
 
@@ -204,16 +205,19 @@ inside_group_pack_kernel(const uint32_t* __restrict__ rows, const uint32_t* __re
 // the stretch of the centre ray inside the tile.
 __global__ void __launch_bounds__(kThreads)
 inside_row_range_kernel(const float4* __restrict__ seg_a, const uint2* __restrict__ grp, int n_blk,
-                        const float4* __restrict__ table, size_t n_groups, float2* __restrict__ rbox) {
+                        const float4* __restrict__ table, size_t n_groups, float2* __restrict__ rbox,
+                        unsigned* __restrict__ stat) {
     const size_t g = (static_cast<size_t>(blockIdx.x) * kThreads + threadIdx.x) >> 5;
     if (g >= n_groups) return;
     const uint2 hd = grp[g];
     if (hd.y == 0) return;
     const int lane = threadIdx.x & 31;
     const float4 c = seg_a[g / n_blk];   // (ox, oy, dx, dy) of the centre ray, unit direction
+    float wm = 0.f;
     for (uint32_t i = 0; i < hd.y; ++i) {
         const size_t slot = ((static_cast<size_t>(hd.x) + i) << 5) + lane;
         const float4 ea = table[2 * slot], eb = table[2 * slot + 1];
+        if (eb.x != 0.f && isfinite(eb.y)) wm = fmaxf(wm, fabsf(eb.y));
         float s0 = INFINITY, s1 = -INFINITY;
         if (eb.x != 0.f) {
             const float t = fabsf(eb.x);
@@ -228,6 +232,22 @@ inside_row_range_kernel(const float4* __restrict__ seg_a, const uint2* __restric
         }
         if (lane == 0) rbox[hd.x + i] = make_float2(s0, s1);
     }
+    // stat[0] = largest throughput of the table (bits of a non-negative float order like unsigned integers)
+    for (int o = 16; o > 0; o >>= 1) wm = fmaxf(wm, __shfl_xor_sync(0xffffffffu, wm, o));
+    if (lane == 0 && __float_as_uint(wm) > *reinterpret_cast<volatile unsigned*>(stat)) atomicMax(stat, __float_as_uint(wm));
+}
+
+// stat[1] = largest |pattern value| of a forward call: with stat[0] the scale of the fixed-point tiles
+__global__ void __launch_bounds__(kThreads)
+inside_absmax_kernel(const float* __restrict__ v, uint64_t n, unsigned* __restrict__ stat) {
+    float m = 0.f;
+    for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * kThreads + threadIdx.x; i < n; i += static_cast<uint64_t>(gridDim.x) * kThreads) {
+        const float a = fabsf(__ldg(v + i));
+        if (a < INFINITY) m = fmaxf(m, a);
+    }
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0 && __float_as_uint(m) > *reinterpret_cast<volatile unsigned*>(stat + 1))
+        atomicMax(stat + 1, __float_as_uint(m));
 }
 
 // lanes with cnt[lane] != 0 -> list (positions from an exclusive scan of the flags)
@@ -333,13 +353,16 @@ struct InsideTilePlan {
 
 // kMode 0 (forward): in = active_data; planes = plane A, plane B at + n_vox.
 // kMode 1 (adjoint): planes = the two gradient planes; out = gT [angle of the call][column][active layer] +=.
-template <int kMode>
+// kInt (forward): the tile holds fixed-point sums and a deposit is one native red.shared.add.s32, as in the jittered
+// kernels (planarj_kernels.cu); scale from stat[0] x stat[1] (largest throughput of the table x largest |pattern
+// value| of the call), stat[2] counts words that came within a factor 2 of overflow.
+template <int kMode, bool kInt>
 __global__ void __launch_bounds__(kTThreads, 1)
 inside_tile_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ InsideTilePlan Z,
                    const uint2* __restrict__ grp, const float4* __restrict__ table, const float2* __restrict__ rbox,
                    const float* __restrict__ in, float* __restrict__ out, float* __restrict__ planes, size_t n_vox,
                    const uint32_t* __restrict__ active_pixels, uint64_t n_active, float ray_weight,
-                   const int* __restrict__ gate) {
+                   const int* __restrict__ gate, unsigned* __restrict__ stat) {
     extern __shared__ __align__(16) float tile[];
     __shared__ int touched;
     if (*gate != 0) return;
@@ -413,6 +436,15 @@ inside_tile_kernel(const __grid_constant__ SceneParams P, const __grid_constant_
     const float yl = P.bmin[1] + static_cast<float>(y0) * vsy, yh = P.bmin[1] + static_cast<float>(y0 + h) * vsy;
     const uint32_t tile_s = static_cast<uint32_t>(__cvta_generic_to_shared(tile));
     const int sxb = 4 * 64, syb = 4 * 64 * pitch;
+    // fixed-point scale: 2^25 / (angles of this CTA x 2 records that can share a voxel x largest deposit)
+    float fx_scale = 1.f, fx_inv = 1.f;
+    if (kInt) {
+        const float de_max = 1.f - ex2_approx(-sig * (vsx + vsy));
+        const float d_max = __uint_as_float(*reinterpret_cast<volatile unsigned*>(stat)) *
+                            __uint_as_float(*reinterpret_cast<volatile unsigned*>(stat + 1)) * fabsf(ray_weight) * de_max;
+        fx_scale = d_max > 0.f ? 33554432.f / (2.f * static_cast<float>(max(kb - ka, 1)) * d_max) : 0.f;
+        fx_inv = fx_scale > 0.f ? 1.f / fx_scale : 0.f;
+    }
 
     int k = ka;
     // (issuing the header chain of the NEXT group before the current one is marched was measured: 98.5 instead
@@ -498,7 +530,7 @@ inside_tile_kernel(const __grid_constant__ SceneParams P, const __grid_constant_
                 uy = (fmaf(static_cast<float>(y0 + iy + (pos ? 1 : 0)), vsy, P.bmin[1]) - gy) * inv;
             }
             uint32_t addr = tile_s + 4u * static_cast<uint32_t>((((iy + 1) * pitch + ix + 1) * 2 + (eb.x < 0.f ? 1 : 0)) * 32 + lane);
-            const float wgt = eb.y * ex2_approx(-sig * t0) * em;
+            const float wgt = eb.y * ex2_approx(-sig * t0) * em * (kInt ? fx_scale : 1.f);
             float e_prev = 1.f, part = 0.f;
             for (;;) {
                 const float un = fminf(ux, uy);
@@ -509,6 +541,8 @@ inside_tile_kernel(const __grid_constant__ SceneParams P, const __grid_constant_
                     float v;
                     asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
                     part = fmaf(v, de, part);
+                } else if (kInt) {
+                    asm volatile("red.shared.add.s32 [%0], %1;" ::"r"(addr), "r"(__float2int_rn(wgt * de)) : "memory");
                 } else {
                     asm volatile("red.shared.add.f32 [%0], %1;" ::"r"(addr), "f"(wgt * de) : "memory");
                 }
@@ -534,14 +568,25 @@ inside_tile_kernel(const __grid_constant__ SceneParams P, const __grid_constant_
             for (int i = warp; i < h * w4; i += kTWarps) {
                 const int yy = i / w4, xx = (i - yy * w4) << 2;
                 const float* src = tile + (((yy + 1) * pitch + xx + 1) * 2 + pl) * 32 + lane;
-                const float v0 = src[0], v1 = src[64], v2 = src[128], v3 = src[192];
+                float v0 = src[0], v1 = src[64], v2 = src[128], v3 = src[192];
+                if (kInt) {
+                    const int i0 = __float_as_int(v0), i1 = __float_as_int(v1), i2 = __float_as_int(v2), i3 = __float_as_int(v3);
+                    if (max(max(abs(i0), abs(i1)), max(abs(i2), abs(i3))) > (1 << 30)) atomicAdd(stat + 2, 1u);
+                    v0 = static_cast<float>(i0) * fx_inv; v1 = static_cast<float>(i1) * fx_inv;
+                    v2 = static_cast<float>(i2) * fx_inv; v3 = static_cast<float>(i3) * fx_inv;
+                }
                 if (v0 != 0.f || v1 != 0.f || v2 != 0.f || v3 != 0.f)
                     red_add_v4(dst + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx), v0, v1, v2, v3);
             }
         } else {
             for (int i = warp; i < h * w; i += kTWarps) {
                 const int yy = i / w, xx = i - yy * w;
-                const float v = tile[(((yy + 1) * pitch + xx + 1) * 2 + pl) * 32 + lane];
+                float v = tile[(((yy + 1) * pitch + xx + 1) * 2 + pl) * 32 + lane];
+                if (kInt) {
+                    const int iv = __float_as_int(v);
+                    if (abs(iv) > (1 << 30)) atomicAdd(stat + 2, 1u);
+                    v = static_cast<float>(iv) * fx_inv;
+                }
                 if (v != 0.f) atomicAdd(dst + static_cast<size_t>(y0 + yy) * P.res[0] + (x0 + xx), v);
             }
         }
@@ -574,7 +619,7 @@ unsigned blocks_for(uint64_t n) { return static_cast<unsigned>((n + kThreads - 1
 }  // namespace
 
 void inside_release(InsideHost& H) {
-    void* ptrs[] = {H.off, H.seg, H.t_lo, H.odd_lanes, H.planes, H.grp, H.table, H.rbox, H.mask, H.tile_off, H.tile_clo};
+    void* ptrs[] = {H.off, H.seg, H.t_lo, H.odd_lanes, H.planes, H.grp, H.table, H.rbox, H.stat, H.mask, H.tile_off, H.tile_clo};
     for (void* q : ptrs)
         if (q) cudaFree(q);
     H = InsideHost{};
@@ -694,9 +739,11 @@ cudaError_t inside_build(const SceneParams& P, const SceneParams& P1, const Plan
         }
         if (tiles) {
             IN_TRY(cudaMalloc(&H.rbox, sizeof(float2) * std::max<uint64_t>(H.n_rows, 1)));
+            IN_TRY(cudaMalloc(&H.stat, 4 * sizeof(unsigned)));
+            IN_TRY(cudaMemset(H.stat, 0, 4 * sizeof(unsigned)));
             if (H.n_rows) {
                 inside_row_range_kernel<<<blocks_for(n_groups * 32), kThreads>>>(base.seg_a, H.grp, n_blk, H.table, n_groups,
-                                                                               H.rbox);
+                                                                               H.rbox, H.stat);
                 count_launch();
             }
         }
@@ -718,10 +765,12 @@ cudaError_t inside_build(const SceneParams& P, const SceneParams& P1, const Plan
             H.tile_h = (ry + H.tiles_y - 1) / H.tiles_y;
             H.smem_bytes = sizeof(float) * static_cast<size_t>(H.tile_h + 2) * (H.tile_w + 2) * 64;
             const int n_tiles = H.tiles_x * H.tiles_y;
-            IN_TRY(cudaFuncSetAttribute(inside_tile_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        static_cast<int>(H.smem_bytes)));
-            IN_TRY(cudaFuncSetAttribute(inside_tile_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        static_cast<int>(H.smem_bytes)));
+            IN_TRY((cudaFuncSetAttribute(inside_tile_kernel<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>(H.smem_bytes))));
+            IN_TRY((cudaFuncSetAttribute(inside_tile_kernel<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>(H.smem_bytes))));
+            IN_TRY((cudaFuncSetAttribute(inside_tile_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>(H.smem_bytes))));
             IN_TRY(cudaMalloc(&H.tile_off, sizeof(int) * static_cast<size_t>(n_tiles) * (np + 1)));
             IN_TRY(cudaMalloc(&H.tile_clo, sizeof(int) * static_cast<size_t>(n_tiles) * np));
             // a record follows the centre ray of its (angle, column) up to the re-spawn offsets of its crossings
@@ -769,8 +818,20 @@ cudaError_t inside_forward_finish(const SceneParams& P1, InsideHost& H, const Pl
     if (H.tiles) {
         const InsideTilePlan Z = tile_plan(H, Zh);
         const dim3 grid(H.tiles_x * H.tiles_y, Zh.nz_pad / 32, Z.groups);
-        inside_tile_kernel<0><<<grid, kTThreads, H.smem_bytes, stream>>>(P1, Z, H.grp, H.table, H.rbox, active_data, nullptr, H.planes,
-                                                                        H.n_vox, active_pixels, n_active, ray_weight, gate);
+        static const bool fixed_point = !(std::getenv("DRTVAM_JITTER_ATOMICS") &&
+                                          std::strcmp(std::getenv("DRTVAM_JITTER_ATOMICS"), "float") == 0);
+        if (fixed_point) {
+            IN_TRY(cudaMemsetAsync(H.stat + 1, 0, sizeof(unsigned), stream));
+            inside_absmax_kernel<<<148 * 8, kThreads, 0, stream>>>(active_data, n_active, H.stat);
+            count_launch();
+            inside_tile_kernel<0, true><<<grid, kTThreads, H.smem_bytes, stream>>>(P1, Z, H.grp, H.table, H.rbox, active_data,
+                                                                                  nullptr, H.planes, H.n_vox, active_pixels,
+                                                                                  n_active, ray_weight, gate, H.stat);
+        } else {
+            inside_tile_kernel<0, false><<<grid, kTThreads, H.smem_bytes, stream>>>(P1, Z, H.grp, H.table, H.rbox, active_data,
+                                                                                   nullptr, H.planes, H.n_vox, active_pixels,
+                                                                                   n_active, ray_weight, gate, H.stat);
+        }
         count_launch();
     }
     if (H.n_odd) {
@@ -801,8 +862,9 @@ cudaError_t inside_adjoint_tiles(const SceneParams& P1, InsideHost& H, const Pla
     if (!H.tiles) return cudaSuccess;
     const InsideTilePlan Z = tile_plan(H, Zh);
     const dim3 grid(H.tiles_x * H.tiles_y, Zh.nz_pad / 32, Z.groups);
-    inside_tile_kernel<1><<<grid, kTThreads, H.smem_bytes, stream>>>(P1, Z, H.grp, H.table, H.rbox, nullptr, gT, H.planes, H.n_vox,
-                                                                    active_pixels, n_active, ray_weight, gate);
+    inside_tile_kernel<1, false><<<grid, kTThreads, H.smem_bytes, stream>>>(P1, Z, H.grp, H.table, H.rbox, nullptr, gT, H.planes,
+                                                                           H.n_vox, active_pixels, n_active, ray_weight, gate,
+                                                                           H.stat);
     count_launch();
     return cudaGetLastError();
 }

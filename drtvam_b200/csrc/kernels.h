@@ -212,6 +212,7 @@ struct InsideHost {
     float4* table = nullptr;    // [rows][32 lanes][2] {ox, oy, dx, dy}, {+-length (sign: plane B), throughput, -, -}
     float2* rbox = nullptr;     // [rows] stretch of the row along the centre ray of its (angle, column)
     const float4* seg_a = nullptr;  // the centre rays (owned by the planar plan)
+    unsigned* stat = nullptr;   // fixed-point scale inputs and the near-overflow counter of the forward tile kernel
     uint64_t n_rows = 0;
     uint64_t n_tile_rec = 0;    // records in the table (statistics)
     uint32_t* mask = nullptr;   // bit ((angle * res_x + column) * nz_pad + active layer): a tile lane

@@ -107,6 +107,10 @@ def test_full_size_shard_matches_oracle(name, surface_aware, k0, workdir):
     print(f"{name} surface_aware={surface_aware} angles [{k0},{k0 + SHARD}): forward {e_f:.2e} adjoint {e_a:.2e}")
     record("full_size_shard", config=name, surface_aware=surface_aware, angles=f"[{k0},{k0 + SHARD})", forward_rel_l2=e_f,
            adjoint_rel_l2=e_a, edge_voxels_flagged=flagged_f, edge_rays_flagged=flagged_a, oracle="f64")
+    # the fixed-point tiles of the record kernel (surface-aware) never came near overflow
+    n_over = C.c_uint64(1)
+    _lib.check(h.lib.drtvam_scene_stat(h.h, 4, C.byref(n_over)))
+    assert n_over.value == 0
     h.close()
     assert e_f < TOL and e_a < TOL
 
