@@ -403,9 +403,11 @@ inside_tile_kernel(const __grid_constant__ SceneParams P, const __grid_constant_
     __syncthreads();
     if (!touched) return;
 
-    if (kMode == 0) {
-        for (int i = threadIdx.x; i < tile_floats; i += kTThreads) tile[i] = 0.f;
-    } else if (z_mine >= 0) {
+    // (the adjoint too: the last step of a walk may land in the rim or in a padding layer, which the staging
+    // below does not write - a stale NaN there would survive the multiplication by a zero factor)
+    for (int i = threadIdx.x; i < tile_floats; i += kTThreads) tile[i] = 0.f;
+    __syncthreads();
+    if (kMode == 1 && z_mine >= 0) {
         // stage both gradient planes: lane = layer, a warp takes 4 voxels of a row at a time
         for (int pl = 0; pl < 2; ++pl) {
             const float* src = planes + pl * n_vox + z_mine * layer_elems;

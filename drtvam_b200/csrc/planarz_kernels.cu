@@ -886,6 +886,16 @@ constexpr size_t g_smem_bytes(int kL) {
     return (sizeof(float) * 2 * g_buf_floats(kL) + 2 * sizeof(uint64_t)) * kGWarpsX * kGWarpsY;
 }
 
+// 16-byte asynchronous copies (LDGSTS): one warp instruction moves a 512-byte line, lane by lane
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(static_cast<uint32_t>(__cvta_generic_to_shared(smem))),
+                 "l"(gmem)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
 // TMA bulk copy (one instruction of one thread moves a whole line) completing on an mbarrier
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
@@ -1084,7 +1094,11 @@ constexpr size_t gm_smem_bytes(int NT) {
     return (sizeof(float) * 2 * gm_buf_floats(NT) + 2 * sizeof(uint64_t)) * kGWarpsX * kGWarpsY;
 }
 
-template <int NT>
+// kTma = false (default since r02zt): the chunk is staged with 16-byte cp.async instead of bulk copies.  A bulk
+// copy is a uniform-datapath instruction: the eight lanes that each fetch one gathered line are serialised by the
+// compiler into an ELECT loop of 9 instructions per line, 26 % of the kernel's instructions and 30 % of its stall
+// samples (profiles/r02zs_*); with LDGSTS one warp instruction moves a whole 512-byte line.
+template <int NT, bool kTma>
 __global__ void __launch_bounds__(32 * kGWarpsX * kGWarpsY, 2)
 planarg_mma_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ PlanarZPlan Z,
                    const float4* __restrict__ coef, const int* __restrict__ ray, const float* __restrict__ in,
@@ -1106,7 +1120,7 @@ planarg_mma_kernel(const __grid_constant__ SceneParams P, const __grid_constant_
     const int a_base = a_begin + blockIdx.y * kLayers;
     float* buf = g_smem + warp * (2 * kBuf);
     uint64_t* bars = reinterpret_cast<uint64_t*>(g_smem + kGWarpsX * kGWarpsY * 2 * kBuf) + 2 * warp;
-    if (lane == 0) {
+    if (kTma && lane == 0) {
         mbar_init(bars, 1);
         mbar_init(bars + 1, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -1137,12 +1151,30 @@ planarg_mma_kernel(const __grid_constant__ SceneParams P, const __grid_constant_
         uint64_t* bar = bars + (c & 1);
         const int g = g0 + c * kGChunk;
         const int n_here = min(kGChunk, g1 - g);
-        const bool wants = lane < kGChunk && (rl >> 24) != 0;
-        const unsigned lines = __popc(__ballot_sync(0xffffffffu, wants));
-        if (lane == 0) mbar_expect_tx(bar, lines * (4u * kLayers) + 64u * n_here);
-        __syncwarp();
-        if (wants) bulk_g2s(b + lane * kLine, xb + static_cast<size_t>(rl & 0xffffff) * Z.nz_pad, 4u * kLayers, bar);
-        if (lane == kGChunk) bulk_g2s(b + kGChunk * kLine, coef + 4 * static_cast<size_t>(g), 64u * n_here, bar);
+        if constexpr (kTma) {
+            const bool wants = lane < kGChunk && (rl >> 24) != 0;
+            const unsigned lines = __popc(__ballot_sync(0xffffffffu, wants));
+            if (lane == 0) mbar_expect_tx(bar, lines * (4u * kLayers) + 64u * n_here);
+            __syncwarp();
+            if (wants) bulk_g2s(b + lane * kLine, xb + static_cast<size_t>(rl & 0xffffff) * Z.nz_pad, 4u * kLayers, bar);
+            if (lane == kGChunk) bulk_g2s(b + kGChunk * kLine, coef + 4 * static_cast<size_t>(g), 64u * n_here, bar);
+        } else {
+            // every lane has finished reading this buffer (chunk c - 2) before it is overwritten
+            __syncwarp();
+            constexpr int kPieces = kLayers / 4;          // 16-byte pieces of a line: 32, 16 or 8
+            constexpr int kLinesPerPass = 32 / kPieces;   // lines one warp instruction covers
+            const int piece = lane % kPieces;
+#pragma unroll
+            for (int p = 0; p < kGChunk / kLinesPerPass; ++p) {
+                const int j = p * kLinesPerPass + lane / kPieces;
+                const int rj = __shfl_sync(0xffffffffu, rl, j);   // every lane holds the ray word of pair lane & 7
+                if ((rj >> 24) != 0)
+                    cp_async16(b + j * kLine + 4 * piece, xb + static_cast<size_t>(rj & 0xffffff) * Z.nz_pad + 4 * piece);
+            }
+            if (lane < 4 * n_here)
+                cp_async16(b + kGChunk * kLine + 4 * lane, reinterpret_cast<const float*>(coef + 4 * static_cast<size_t>(g)) + 4 * lane);
+            cp_async_commit();
+        }
         if (lane < kGChunk) reinterpret_cast<int*>(b)[kGChunk * kLine + kGChunk * 16 + lane] = rl;
     };
 
@@ -1154,8 +1186,11 @@ planarg_mma_kernel(const __grid_constant__ SceneParams P, const __grid_constant_
         if (c + 1 < n_chunks) {
             issue(c + 1, rl_next);
             rl_next = load_rays(c + 2);
+            if constexpr (!kTma) cp_async_wait<1>();
+        } else if constexpr (!kTma) {
+            cp_async_wait<0>();
         }
-        mbar_wait(bars + (c & 1), (c >> 1) & 1);
+        if constexpr (kTma) mbar_wait(bars + (c & 1), (c >> 1) & 1);
         __syncwarp();
         const float* b = buf + (c & 1) * kBuf;
         const int n_here = min(kGChunk, g1 - (g0 + c * kGChunk));
@@ -1577,8 +1612,10 @@ cudaError_t launch_planarz_adjoint(const SceneParams& P, PlanarZHost& H, const i
 
 template <int kL>
 static cudaError_t g_set_smem() {
-    PZ_TRY(cudaFuncSetAttribute(planarg_mma_kernel<4 * kL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                static_cast<int>(gm_smem_bytes(4 * kL))));
+    PZ_TRY((cudaFuncSetAttribute(planarg_mma_kernel<4 * kL, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 static_cast<int>(gm_smem_bytes(4 * kL)))));
+    PZ_TRY((cudaFuncSetAttribute(planarg_mma_kernel<4 * kL, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 static_cast<int>(gm_smem_bytes(4 * kL)))));
     return cudaFuncSetAttribute(planarg_kernel<kL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 static_cast<int>(g_smem_bytes(kL)));
 }
@@ -1691,6 +1728,15 @@ cudaError_t planarg_build(const SceneParams& P, const PlanarHost& base, const Pl
     return cudaSuccess;
 }
 
+// DRTVAM_PLANAR_STAGING=tma stages the chunks of the tensor-core patch gather with bulk copies (A/B measurements)
+static const bool mma_tma = std::getenv("DRTVAM_PLANAR_STAGING") && std::strcmp(std::getenv("DRTVAM_PLANAR_STAGING"), "tma") == 0;
+
+template <int NT, class... Args>
+static void launch_mma(bool tma, dim3 grid, int threads, cudaStream_t stream, Args... args) {
+    if (tma) planarg_mma_kernel<NT, true><<<grid, threads, gm_smem_bytes(NT), stream>>>(args...);
+    else planarg_mma_kernel<NT, false><<<grid, threads, gm_smem_bytes(NT), stream>>>(args...);
+}
+
 cudaError_t launch_planarg_forward(const SceneParams& P, PlanarZHost& H, PlanarGHost& G, const int* gate,
                                    const float* active_data, const uint32_t* active_pixels, uint64_t n_active,
                                    float ray_weight, float* film, bool fresh, cudaStream_t stream,
@@ -1713,13 +1759,13 @@ cudaError_t launch_planarg_forward(const SceneParams& P, PlanarZHost& H, PlanarG
         const int kL = S.plan.lanes_l, a_begin = S.plan.a_begin;
         if (use_mma) {
             if (kL == 1)
-                planarg_mma_kernel<4><<<grid, threads, gm_smem_bytes(4), stream>>>(P, Z, G.coef, G.ray, H.scratch, film,
+                launch_mma<4>(mma_tma, grid, threads, stream, P, Z, G.coef, G.ray, H.scratch, film,
                                                                                   active_pixels, n_active, ray_weight, gate, a_begin, fresh ? 1 : 0);
             else if (kL == 2)
-                planarg_mma_kernel<8><<<grid, threads, gm_smem_bytes(8), stream>>>(P, Z, G.coef, G.ray, H.scratch, film,
+                launch_mma<8>(mma_tma, grid, threads, stream, P, Z, G.coef, G.ray, H.scratch, film,
                                                                                   active_pixels, n_active, ray_weight, gate, a_begin, fresh ? 1 : 0);
             else
-                planarg_mma_kernel<16><<<grid, threads, gm_smem_bytes(16), stream>>>(P, Z, G.coef, G.ray, H.scratch, film,
+                launch_mma<16>(mma_tma, grid, threads, stream, P, Z, G.coef, G.ray, H.scratch, film,
                                                                                     active_pixels, n_active, ray_weight, gate, a_begin, fresh ? 1 : 0);
         } else if (kL == 1)
             planarg_kernel<1><<<grid, threads, g_smem_bytes(1), stream>>>(P, Z, G.coef, G.ray, H.scratch, film,
@@ -1787,13 +1833,13 @@ cudaError_t launch_planarg_forward_noalloc(const SceneParams& P, const PlanarZHo
         const dim3 grid(regions, S.n_blocks);
         const int kL = S.plan.lanes_l, a_begin = S.plan.a_begin;
         if (kL == 1)
-            planarg_mma_kernel<4><<<grid, threads, gm_smem_bytes(4), stream>>>(P, Z, G.coef, G.ray, scratch, film, active_pixels,
+            launch_mma<4>(mma_tma, grid, threads, stream, P, Z, G.coef, G.ray, scratch, film, active_pixels,
                                                                               n_active, ray_weight, gate, a_begin, fresh ? 1 : 0);
         else if (kL == 2)
-            planarg_mma_kernel<8><<<grid, threads, gm_smem_bytes(8), stream>>>(P, Z, G.coef, G.ray, scratch, film, active_pixels,
+            launch_mma<8>(mma_tma, grid, threads, stream, P, Z, G.coef, G.ray, scratch, film, active_pixels,
                                                                               n_active, ray_weight, gate, a_begin, fresh ? 1 : 0);
         else
-            planarg_mma_kernel<16><<<grid, threads, gm_smem_bytes(16), stream>>>(P, Z, G.coef, G.ray, scratch, film, active_pixels,
+            launch_mma<16>(mma_tma, grid, threads, stream, P, Z, G.coef, G.ray, scratch, film, active_pixels,
                                                                                 n_active, ray_weight, gate, a_begin, fresh ? 1 : 0);
         count_launch();
         PZ_TRY(cudaGetLastError());
