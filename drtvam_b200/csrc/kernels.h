@@ -98,6 +98,7 @@ struct PlanarZHost {
     int* row_a = nullptr;
     int* layer_a = nullptr;    // [res_z] active layer of film layer z, -1 = no DMD row deposits there (or outside the z window)
     int* row_ri = nullptr;     // [res_y] position of DMD row r among the rows of its layer
+    unsigned* pmax = nullptr;  // largest |pattern value| of the current forward call (bits of a float): fp16 scale
     float* scratch = nullptr;  // [angles][columns][active layers] repack of patterns / gradients
     size_t scratch_bytes = 0;
 };
@@ -110,6 +111,8 @@ struct PlanarGHost {
     int* tile_clo = nullptr;
     int* tile_ebase = nullptr;
     float4* coef = nullptr;    // [pairs][4] float4 = 16 coefficients, voxel (yy, xx) at 4 * yy + xx
+    uint32_t* coef_h = nullptr;   // the same as {hi, lo} fp16 pairs of coefficient / coef_inv_scale (planarg_h16_kernel)
+    float coef_inv_scale = 1.f;
     int* ray = nullptr;        // [pairs] k * res_x + c
     long long pairs = 0;       // after the pairs that touch nothing are dropped
     long long candidates = 0;  // before

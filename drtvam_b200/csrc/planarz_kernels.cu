@@ -30,6 +30,7 @@
 #include <mutex>
 #include <vector>
 
+#include <cuda_fp16.h>
 #include <cub/device/device_scan.cuh>
 
 #include "expm.cuh"
@@ -99,6 +100,74 @@ zunpack_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ Pl
         const int r = P.row_begin + r0 + j, c = c0 + tx;
         if (r < P.row_begin + P.n_rows && c < P.res_x) grad[active_index(P, kk, r, c)] = tr[tx][j];
     }
+}
+
+// ---- split fp16 operands of the patch gather (planarg_h16_kernel) -----------------------------------------
+// x ~ hi + lo with hi = fp16(x), lo = fp16(x - hi): 22 bits of x when x is scaled into fp16's normal range.
+__device__ __forceinline__ uint32_t pack_split_h16(float x) {
+    const __half hi = __float2half_rn(x);
+    const __half lo = __float2half_rn(x - __half2float(hi));
+    return static_cast<uint32_t>(__half_as_ushort(hi)) | (static_cast<uint32_t>(__half_as_ushort(lo)) << 16);
+}
+
+// power of two that brings values of magnitude <= m into [1024, 2048) (m = 0: 1)
+__host__ __device__ __forceinline__ float h16_scale(float m) {
+    if (!(m > 0.f) || !isfinite(m)) return 1.f;
+    int e;
+    frexpf(m, &e);   // m = f 2^e, f in [0.5, 1)
+    return ldexpf(1.f, 11 - e);
+}
+
+// pmax[0] = largest |v[i]| as the bits of a non-negative float
+__global__ void __launch_bounds__(256)
+absmax_kernel(const float* __restrict__ v, size_t n, unsigned* __restrict__ pmax, const int* __restrict__ gate) {
+    if (gate && *gate != 0) return;
+    float m = 0.f;
+    for (size_t i = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x; i < n; i += static_cast<size_t>(gridDim.x) * 256) {
+        const float a = fabsf(__ldg(v + i));
+        if (a < INFINITY) m = fmaxf(m, a);
+    }
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0 && __float_as_uint(m) > *reinterpret_cast<volatile unsigned*>(pmax)) atomicMax(pmax, __float_as_uint(m));
+}
+
+// active_data [kk][row][col]  ->  pT [kk][col][a] as {hi, lo} fp16 pairs of (sum over the rows of layer a) x scale,
+// scale = h16_scale(rows_max x largest |pattern value| of the call)
+__global__ void __launch_bounds__(256)
+zpack_h16_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ PlanarZPlan Z,
+                 const float* __restrict__ active_data, uint32_t* __restrict__ pT, const unsigned* __restrict__ pmax,
+                 float rows_max, const int* __restrict__ gate) {
+    __shared__ float tr[32][33];
+    if (*gate != 0) return;
+    const float scale = h16_scale(__uint_as_float(__ldg(pmax)) * rows_max);
+    const int kk = blockIdx.z;
+    const int c0 = blockIdx.x * 32, a0 = blockIdx.y * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+    for (int j = ty; j < 32; j += 8) {
+        const int a = a0 + j, c = c0 + tx;
+        float v = 0.f;
+        if (a < Z.nz && c < P.res_x) {
+            const int rb = __ldg(Z.a_row_begin + a), re = __ldg(Z.a_row_begin + a + 1);
+            for (int ri = rb; ri < re; ++ri) {
+                const int r = __ldg(Z.a_rows + ri);
+                v += __ldg(active_data + active_index(P, kk, r, c));
+            }
+        }
+        tr[j][tx] = v;
+    }
+    __syncthreads();
+    for (int j = ty; j < 32; j += 8) {
+        const int c = c0 + j, a = a0 + tx;
+        if (c < P.res_x && a < Z.nz_pad)
+            pT[(static_cast<size_t>(kk) * P.res_x + c) * Z.nz_pad + a] = pack_split_h16(tr[tx][j] * scale);
+    }
+}
+
+// coef_h[i] = {hi, lo} fp16 pair of coef[i] x scale
+__global__ void __launch_bounds__(256)
+gcoef_h16_kernel(const float* __restrict__ coef, size_t n, float scale, uint32_t* __restrict__ coef_h) {
+    const size_t i = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x;
+    if (i < n) coef_h[i] = pack_split_h16(coef[i] * scale);
 }
 
 // t [kk][col][a] = 0 where the lane (k0 + kk, col, a) is marked: lanes that other kernels serve (the tile lanes
@@ -1269,6 +1338,160 @@ planarg_mma_kernel(const __grid_constant__ SceneParams P, const __grid_constant_
     }
 }
 
+// ---- the patch gather in split fp16 --------------------------------------------------------------------------
+// The 3xTF32 kernel above is bound by the tensor pipe (54 % busy at a third of its instructions; an m16n8k8 tf32
+// HMMA occupies the pipe for ~8 cycles per SM sub-partition, profiles/r02zs_*).  fp16 runs at twice the rate, and a
+// pair of fp16 numbers holds x to 22 bits once x is scaled into fp16's normal range - which both operands allow:
+// the coefficient table is static (scaled once, planarg_build) and the patterns of a call are scaled by a power of
+// two from their largest magnitude (absmax_kernel -> zpack_h16_kernel).  So the same three products
+//     hi.hi + lo.hi + hi.lo     (the dropped lo.lo term is 2^-22 relative)
+// run as mma.sync.m16n8k8 .f16 with fp32 accumulators, and both operands arrive ALREADY split ({hi, lo} packed in
+// the 32 bits an fp32 value took, so tables and staging keep their size): a fragment register is one PRMT of two
+// staged words instead of a mask, a subtraction and a select per value.
+// Fragment layout (PTX ISA, m16n8k8 .f16): with g = lane / 4, q = lane % 4
+//   A (16 x 8):  a0 = {A[g][2q], A[g][2q+1]}   a1 = {A[g+8][2q], A[g+8][2q+1]}
+//   B ( 8 x 8):  b0 = {B[2q][g], B[2q+1][g]}
+//   C (16 x 8):  as for tf32
+__device__ __forceinline__ void mma_h16(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t b0) {
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a0), "r"(a1), "r"(b0));
+}
+
+template <int NT>
+__global__ void __launch_bounds__(32 * kGWarpsX * kGWarpsY, 2)
+planarg_h16_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ PlanarZPlan Z,
+                   const uint32_t* __restrict__ coef, const int* __restrict__ ray, const uint32_t* __restrict__ in,
+                   float* __restrict__ out, const uint32_t* __restrict__ active_pixels, uint64_t n_active,
+                   float ray_weight, const int* __restrict__ gate, int a_begin, int fresh,
+                   const unsigned* __restrict__ pmax, float rows_max, float coef_inv_scale) {
+    extern __shared__ __align__(16) float g_smem[];
+    if (*gate != 0) return;
+    constexpr int kLayers = 8 * NT, kLine = gm_line(NT), kBuf = gm_buf_floats(NT);
+    static_assert(kGChunk == 8, "one chunk is one k-step of the m16n8k8 product");
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int regions_x = (Z.tiles_x + kGWarpsX - 1) / kGWarpsX;
+    const int px = (blockIdx.x % regions_x) * kGWarpsX + (warp % kGWarpsX);
+    const int py = (blockIdx.x / regions_x) * kGWarpsY + (warp / kGWarpsX);
+    if (px >= Z.tiles_x || py >= Z.tiles_y) return;
+    const int tile_id = py * Z.tiles_x + px;
+    const int a_base = a_begin + blockIdx.y * kLayers;
+    uint32_t* buf = reinterpret_cast<uint32_t*>(g_smem) + warp * (2 * kBuf);
+    // a line that is never fetched (a pair that touches nothing) enters with zero coefficients: what it holds must
+    // be finite, so the buffers start as zeros (afterwards they only ever hold staged fp16 pairs)
+    for (int i = lane; i < 2 * kBuf; i += 32) buf[i] = 0u;
+    __syncwarp();
+
+    int k0, nk;
+    call_angles(P, active_pixels, n_active, k0, nk);
+    const int* __restrict__ off = Z.tile_off + static_cast<size_t>(tile_id) * (P.n_patterns + 1);
+    const int ebase = __ldg(Z.tile_ebase + tile_id);
+    const int g0 = ebase + __ldg(off + k0), g1 = ebase + __ldg(off + k0 + nk);
+    const uint32_t* __restrict__ xb = in + a_base - static_cast<long long>(k0) * P.res_x * Z.nz_pad;
+    const int n_chunks = (g1 - g0 + kGChunk - 1) / kGChunk;
+
+    float acc[NT][4];
+#pragma unroll
+    for (int t = 0; t < NT; ++t)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) acc[t][i] = 0.f;
+
+    auto load_rays = [&](int c) {
+        const int g = g0 + c * kGChunk + (lane & (kGChunk - 1));
+        return (c < n_chunks && g < g1) ? __ldg(ray + g) : 0;
+    };
+    auto issue = [&](int c, int rl) {
+        uint32_t* b = buf + (c & 1) * kBuf;
+        const int g = g0 + c * kGChunk;
+        const int n_here = min(kGChunk, g1 - g);
+        __syncwarp();   // every lane has finished reading this buffer (chunk c - 2)
+        constexpr int kPieces = kLayers / 4;          // 16-byte pieces of a line: 32, 16 or 8
+        constexpr int kLinesPerPass = 32 / kPieces;   // lines one warp instruction covers
+        const int piece = lane % kPieces;
+#pragma unroll
+        for (int p = 0; p < kGChunk / kLinesPerPass; ++p) {
+            const int j = p * kLinesPerPass + lane / kPieces;
+            const int rj = __shfl_sync(0xffffffffu, rl, j);   // every lane holds the ray word of pair lane & 7
+            if ((rj >> 24) != 0)
+                cp_async16(b + j * kLine + 4 * piece, xb + static_cast<size_t>(rj & 0xffffff) * Z.nz_pad + 4 * piece);
+        }
+        if (lane < 4 * n_here) cp_async16(b + kGChunk * kLine + 4 * lane, coef + 16 * static_cast<size_t>(g) + 4 * lane);
+        cp_async_commit();
+        if (lane < kGChunk) reinterpret_cast<int*>(b)[kGChunk * kLine + kGChunk * 16 + lane] = rl;
+    };
+
+    const int gq = lane >> 2, q = lane & 3;
+    int rl_next = load_rays(0);
+    if (n_chunks > 0) issue(0, rl_next);
+    rl_next = load_rays(1);
+    for (int c = 0; c < n_chunks; ++c) {
+        if (c + 1 < n_chunks) {
+            issue(c + 1, rl_next);
+            rl_next = load_rays(c + 2);
+            cp_async_wait<1>();
+        } else {
+            cp_async_wait<0>();
+        }
+        __syncwarp();
+        const uint32_t* b = buf + (c & 1) * kBuf;
+        const int n_here = min(kGChunk, g1 - (g0 + c * kGChunk));
+        const int* rw = reinterpret_cast<const int*>(b) + kGChunk * kLine + kGChunk * 16;
+        // this lane's two k indices are the pairs 2q and 2q + 1 of the chunk; pairs beyond the end of the list and
+        // pairs that touch nothing (their line is not fetched) enter with zero coefficients
+        const bool v0 = 2 * q < n_here && (rw[2 * q] >> 24) != 0, v1 = 2 * q + 1 < n_here && (rw[2 * q + 1] >> 24) != 0;
+        const uint32_t* cf = b + kGChunk * kLine;
+        const uint32_t u00 = v0 ? cf[16 * (2 * q) + gq] : 0u, u01 = v1 ? cf[16 * (2 * q + 1) + gq] : 0u;
+        const uint32_t u10 = v0 ? cf[16 * (2 * q) + gq + 8] : 0u, u11 = v1 ? cf[16 * (2 * q + 1) + gq + 8] : 0u;
+        const uint32_t a0h = __byte_perm(u00, u01, 0x5410), a0l = __byte_perm(u00, u01, 0x7632);
+        const uint32_t a1h = __byte_perm(u10, u11, 0x5410), a1l = __byte_perm(u10, u11, 0x7632);
+        const uint32_t* x0 = b + (2 * q) * kLine + gq * NT;       // layers NT * gq + t of pair 2q
+        const uint32_t* x1 = b + (2 * q + 1) * kLine + gq * NT;   // ... of pair 2q + 1
+#pragma unroll
+        for (int t4 = 0; t4 < NT / 4; ++t4) {
+            const uint4 xa = *reinterpret_cast<const uint4*>(x0 + 4 * t4);
+            const uint4 xc = *reinterpret_cast<const uint4*>(x1 + 4 * t4);
+            const uint32_t ba[4] = {xa.x, xa.y, xa.z, xa.w}, bc[4] = {xc.x, xc.y, xc.z, xc.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const uint32_t bh = __byte_perm(ba[i], bc[i], 0x5410), bl = __byte_perm(ba[i], bc[i], 0x7632);
+                mma_h16(acc[4 * t4 + i], a0h, a1h, bh);
+                mma_h16(acc[4 * t4 + i], a0l, a1l, bh);
+                mma_h16(acc[4 * t4 + i], a0h, a1h, bl);
+            }
+        }
+        __syncwarp();  // the buffer is refilled by the issue of the next iteration
+    }
+
+    // undo the two scalings (powers of two: exact)
+    const float wscale = ray_weight * coef_inv_scale / h16_scale(__uint_as_float(__ldg(pmax)) * rows_max);
+    // lane (g, q) holds voxels g and g + 8 of the patch (row g / 4 resp. g / 4 + 2, column g % 4) for the
+    // layers NT * 2q + t and NT * (2q + 1) + t; the four lanes of consecutive g write 16 contiguous bytes
+    const int x0v = px * kPatch, y0v = py * kPatch;
+    const size_t layer_elems = static_cast<size_t>(P.res[0]) * P.res[1];
+    const int xx = x0v + (gq & 3), yy0 = y0v + (gq >> 2), yy1 = yy0 + 2;
+    if (xx < P.res[0]) {
+#pragma unroll
+        for (int t = 0; t < NT; ++t) {
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int z = __ldg(Z.zl + a_base + NT * (2 * q + h) + t);
+                if (z < 0) continue;
+                float* o = out + z * layer_elems + xx;
+                if (yy0 < P.res[1]) {
+                    const float v = acc[t][h] * wscale;
+                    float* d = o + static_cast<size_t>(yy0) * P.res[0];
+                    if (fresh) *d = v; else if (v != 0.f) *d += v;
+                }
+                if (yy1 < P.res[1]) {
+                    const float v = acc[t][2 + h] * wscale;
+                    float* d = o + static_cast<size_t>(yy1) * P.res[0];
+                    if (fresh) *d = v; else if (v != 0.f) *d += v;
+                }
+            }
+        }
+    }
+}
+
 }  // namespace
 
 #define PZ_TRY(expr)                      \
@@ -1283,7 +1506,7 @@ void planarz_release(PlanarZHost& H) {
         for (void* p : ptrs)
             if (p) cudaFree(p);
     }
-    void* ptrs[] = {H.zl, H.a_row_begin, H.a_rows, H.row_a, H.layer_a, H.row_ri, H.scratch};
+    void* ptrs[] = {H.zl, H.a_row_begin, H.a_rows, H.row_a, H.layer_a, H.row_ri, H.scratch, H.pmax};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     H = PlanarZHost();
@@ -1616,12 +1839,14 @@ static cudaError_t g_set_smem() {
                                  static_cast<int>(gm_smem_bytes(4 * kL)))));
     PZ_TRY((cudaFuncSetAttribute(planarg_mma_kernel<4 * kL, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  static_cast<int>(gm_smem_bytes(4 * kL)))));
+    PZ_TRY(cudaFuncSetAttribute(planarg_h16_kernel<4 * kL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                static_cast<int>(gm_smem_bytes(4 * kL))));
     return cudaFuncSetAttribute(planarg_kernel<kL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 static_cast<int>(g_smem_bytes(kL)));
 }
 
 void planarg_release(PlanarGHost& G) {
-    void* ptrs[] = {G.tile_off, G.tile_clo, G.tile_ebase, G.coef, G.ray};
+    void* ptrs[] = {G.tile_off, G.tile_clo, G.tile_ebase, G.coef, G.ray, G.coef_h};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     G = PlanarGHost();
@@ -1725,6 +1950,36 @@ cudaError_t planarg_build(const SceneParams& P, const PlanarHost& base, const Pl
     PZ_TRY(cudaDeviceSynchronize());
     G.pairs = total;
     G.valid = true;
+    // the same table as {hi, lo} fp16 pairs of the coefficients scaled into fp16's range (planarg_h16_kernel);
+    // left out (the tf32 kernel then serves) when it does not fit comfortably
+    if (total > 0) {
+        size_t free_b = 0, total_b = 0;
+        PZ_TRY(cudaMemGetInfo(&free_b, &total_b));
+        const size_t n = 16 * static_cast<size_t>(total);
+        unsigned* cmax = nullptr;
+        if (sizeof(uint32_t) * n < free_b / 4 && cudaMalloc(&cmax, sizeof(unsigned)) == cudaSuccess) {
+            unsigned bits = 0;
+            cudaError_t e = cudaMemset(cmax, 0, sizeof(unsigned));
+            if (e == cudaSuccess) {
+                absmax_kernel<<<148 * 8, 256>>>(reinterpret_cast<const float*>(G.coef), n, cmax, nullptr);
+                count_launch();
+                e = cudaMemcpy(&bits, cmax, sizeof(bits), cudaMemcpyDeviceToHost);
+            }
+            cudaFree(cmax);
+            float cm;
+            std::memcpy(&cm, &bits, sizeof(cm));
+            if (e == cudaSuccess && cm > 0.f && cudaMalloc(&G.coef_h, sizeof(uint32_t) * n) == cudaSuccess) {
+                const float sc = h16_scale(cm);
+                gcoef_h16_kernel<<<static_cast<unsigned>((n + 255) / 256), 256>>>(reinterpret_cast<const float*>(G.coef), n, sc,
+                                                                                  G.coef_h);
+                count_launch();
+                G.coef_inv_scale = 1.f / sc;
+                PZ_TRY(cudaDeviceSynchronize());
+            } else {
+                cudaGetLastError();
+            }
+        }
+    }
     return cudaSuccess;
 }
 
@@ -1744,13 +1999,48 @@ cudaError_t launch_planarg_forward(const SceneParams& P, PlanarZHost& H, PlanarG
     const int nk = static_cast<int>(n_active / (static_cast<uint64_t>(P.res_x) * P.n_rows));
     PZ_TRY(z_scratch(H, sizeof(float) * static_cast<size_t>(nk) * P.res_x * H.nz_pad));
     const dim3 pgrid((P.res_x + 31) / 32, H.nz_pad / 32, nk);
+    const PlanarZPlan& Z = G.plan;
+    const int regions = ((Z.tiles_x + kGWarpsX - 1) / kGWarpsX) * ((Z.tiles_y + kGWarpsY - 1) / kGWarpsY);
+    constexpr int threads = 32 * kGWarpsX * kGWarpsY;
+    // DRTVAM_PLANAR_FORWARD = tf32 | ffma keep the 3xTF32 tensor-core kernel / the FMA-pipe kernel (A/B measurements)
+    static const bool use_h16 = std::getenv("DRTVAM_PLANAR_FORWARD") == nullptr;
+    if (use_h16 && G.coef_h != nullptr) {
+        if (H.pmax == nullptr) PZ_TRY(cudaMalloc(&H.pmax, sizeof(unsigned)));
+        const float rows_max = static_cast<float>(std::max(1, H.rows_max));
+        PZ_TRY(cudaMemsetAsync(H.pmax, 0, sizeof(unsigned), stream));
+        absmax_kernel<<<148 * 8, 256, 0, stream>>>(active_data, n_active, H.pmax, gate);
+        count_launch();
+        zpack_h16_kernel<<<pgrid, 256, 0, stream>>>(P, H.sub[0].plan, active_data, reinterpret_cast<uint32_t*>(H.scratch), H.pmax,
+                                                    rows_max, gate);
+        count_launch();
+        PZ_TRY(cudaGetLastError());
+        if (lane_mask) PZ_TRY(launch_zmask(P, H, lane_mask, active_pixels, n_active, gate, stream));
+        const uint32_t* xin = reinterpret_cast<const uint32_t*>(H.scratch);
+        for (int i = 0; i < H.n_sub; ++i) {
+            const PlanarZSub& S = H.sub[i];
+            const dim3 grid(regions, S.n_blocks);
+            const int kL = S.plan.lanes_l, a_begin = S.plan.a_begin;
+            if (kL == 1)
+                planarg_h16_kernel<4><<<grid, threads, gm_smem_bytes(4), stream>>>(P, Z, G.coef_h, G.ray, xin, film, active_pixels,
+                                                                                  n_active, ray_weight, gate, a_begin, fresh ? 1 : 0,
+                                                                                  H.pmax, rows_max, G.coef_inv_scale);
+            else if (kL == 2)
+                planarg_h16_kernel<8><<<grid, threads, gm_smem_bytes(8), stream>>>(P, Z, G.coef_h, G.ray, xin, film, active_pixels,
+                                                                                  n_active, ray_weight, gate, a_begin, fresh ? 1 : 0,
+                                                                                  H.pmax, rows_max, G.coef_inv_scale);
+            else
+                planarg_h16_kernel<16><<<grid, threads, gm_smem_bytes(16), stream>>>(P, Z, G.coef_h, G.ray, xin, film, active_pixels,
+                                                                                    n_active, ray_weight, gate, a_begin, fresh ? 1 : 0,
+                                                                                    H.pmax, rows_max, G.coef_inv_scale);
+            count_launch();
+            PZ_TRY(cudaGetLastError());
+        }
+        return cudaSuccess;
+    }
     zpack_kernel<<<pgrid, 256, 0, stream>>>(P, H.sub[0].plan, active_data, H.scratch, nk, gate);
     count_launch();
     PZ_TRY(cudaGetLastError());
     if (lane_mask) PZ_TRY(launch_zmask(P, H, lane_mask, active_pixels, n_active, gate, stream));
-    const PlanarZPlan& Z = G.plan;
-    const int regions = ((Z.tiles_x + kGWarpsX - 1) / kGWarpsX) * ((Z.tiles_y + kGWarpsY - 1) / kGWarpsY);
-    constexpr int threads = 32 * kGWarpsX * kGWarpsY;
     // DRTVAM_PLANAR_FORWARD=ffma keeps the products on the FMA pipe (A/B measurements)
     static const bool use_mma = !(std::getenv("DRTVAM_PLANAR_FORWARD") && std::strcmp(std::getenv("DRTVAM_PLANAR_FORWARD"), "ffma") == 0);
     for (int i = 0; i < H.n_sub; ++i) {
