@@ -1451,6 +1451,8 @@ planarg_h16_kernel(const __grid_constant__ SceneParams P, const __grid_constant_
             const uint4 xa = *reinterpret_cast<const uint4*>(x0 + 4 * t4);
             const uint4 xc = *reinterpret_cast<const uint4*>(x1 + 4 * t4);
             const uint32_t ba[4] = {xa.x, xa.y, xa.z, xa.w}, bc[4] = {xc.x, xc.y, xc.z, xc.w};
+            // (product-major order over the four tiles - the three products of a tile four HMMAs apart - was
+            // measured: no difference, r02zx)
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 const uint32_t bh = __byte_perm(ba[i], bc[i], 0x5410), bl = __byte_perm(ba[i], bc[i], 0x7632);
@@ -1518,10 +1520,11 @@ static void z_tile_dims(int rx, int ry, int kL, int& tw, int& th) {
     const int max_floats = (227 * 1024) / 4;
     const int area = max_floats / (kZLaneStride * kL);
     int side = static_cast<int>(std::floor(std::sqrt(static_cast<double>(area))));
+    side = std::min(side, 32);   // a walk crosses at most w + h - 1 voxels: the visit lists of the adjoint hold 64
     int tw_max = std::max(4, side & ~3);
     int tiles_x = (rx + tw_max - 1) / tw_max;
     tw = (((rx + tiles_x - 1) / tiles_x) + 3) & ~3;
-    int th_max = std::max(1, area / tw);
+    int th_max = std::max(1, std::min(area / tw, 64 - tw));
     int tiles_y = (ry + th_max - 1) / th_max;
     th = (ry + tiles_y - 1) / tiles_y;
 }
