@@ -1400,24 +1400,34 @@ planarg_h16_kernel(const __grid_constant__ SceneParams P, const __grid_constant_
         const int g = g0 + c * kGChunk + (lane & (kGChunk - 1));
         return (c < n_chunks && g < g1) ? __ldg(ray + g) : 0;
     };
+    // Address arithmetic of the staging, hoisted: per line the loop pays a shuffle, a mask, one 32-bit multiply, a
+    // compare, one wide add and the copy (the first version re-derived 64-bit addresses and re-read kernel
+    // parameters for every line: 124 of the 269 instructions of a chunk were integer work, profiles/r02zw_*).
+    constexpr int kPieces = kLayers / 4;          // 16-byte pieces of a line: 32, 16 or 8
+    constexpr int kLinesPerPass = 32 / kPieces;   // lines one warp instruction covers
+    const uint32_t nzp4 = static_cast<uint32_t>(Z.nz_pad) * 4u;                    // bytes between two pattern lines
+    const char* const xsrc = reinterpret_cast<const char*>(xb) + 16 * (lane % kPieces);
+    const uint32_t sdst0 = static_cast<uint32_t>(__cvta_generic_to_shared(buf)) + 4u * ((lane / kPieces) * kLine) + 16u * (lane % kPieces);
+    const char* const csrc = reinterpret_cast<const char*>(coef + 16 * static_cast<size_t>(g0)) + 16 * lane;
+    const uint32_t cdst0 = static_cast<uint32_t>(__cvta_generic_to_shared(buf)) + 4u * (kGChunk * kLine) + 16u * lane;
+    const uint32_t rdst0 = static_cast<uint32_t>(__cvta_generic_to_shared(buf)) + 4u * (kGChunk * kLine + kGChunk * 16 + lane);
     auto issue = [&](int c, int rl) {
-        uint32_t* b = buf + (c & 1) * kBuf;
-        const int g = g0 + c * kGChunk;
-        const int n_here = min(kGChunk, g1 - g);
+        const uint32_t bsel = (c & 1) ? 4u * kBuf : 0u;
+        const int n_here = min(kGChunk, g1 - (g0 + c * kGChunk));
         __syncwarp();   // every lane has finished reading this buffer (chunk c - 2)
-        constexpr int kPieces = kLayers / 4;          // 16-byte pieces of a line: 32, 16 or 8
-        constexpr int kLinesPerPass = 32 / kPieces;   // lines one warp instruction covers
-        const int piece = lane % kPieces;
 #pragma unroll
         for (int p = 0; p < kGChunk / kLinesPerPass; ++p) {
-            const int j = p * kLinesPerPass + lane / kPieces;
-            const int rj = __shfl_sync(0xffffffffu, rl, j);   // every lane holds the ray word of pair lane & 7
-            if ((rj >> 24) != 0)
-                cp_async16(b + j * kLine + 4 * piece, xb + static_cast<size_t>(rj & 0xffffff) * Z.nz_pad + 4 * piece);
+            const unsigned rj = static_cast<unsigned>(__shfl_sync(0xffffffffu, rl, p * kLinesPerPass + lane / kPieces));
+            if (rj >= 0x1000000u)   // a non-empty row mask: the line is needed
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sdst0 + bsel + 4u * (p * kLinesPerPass * kLine)),
+                             "l"(xsrc + static_cast<size_t>((rj & 0xffffffu) * nzp4))
+                             : "memory");
         }
-        if (lane < 4 * n_here) cp_async16(b + kGChunk * kLine + 4 * lane, coef + 16 * static_cast<size_t>(g) + 4 * lane);
+        if (lane < 4 * n_here)
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(cdst0 + bsel), "l"(csrc + static_cast<size_t>(c) * (64 * kGChunk))
+                         : "memory");
         cp_async_commit();
-        if (lane < kGChunk) reinterpret_cast<int*>(b)[kGChunk * kLine + kGChunk * 16 + lane] = rl;
+        if (lane < kGChunk) asm volatile("st.shared.b32 [%0], %1;" ::"r"(rdst0 + bsel), "r"(rl) : "memory");
     };
 
     const int gq = lane >> 2, q = lane & 3;
