@@ -176,6 +176,9 @@ class ClockSampler:
 # mma.sync.aligned.m16n8k8 tf32 (SASS HMMA), 8 warps per SM x 16 accumulator tiles: dense TFLOP/s measured by
 # tools/microbench.py on this pool's B200 (profiles/r02g_microbench.json)
 MMA_SYNC_TF32_PEAK = 276.0
+# mma.sync.aligned.m16n8k16 f16 -> f32 (SASS HMMA.16816.F32): the same issue rate, twice the flops per instruction
+# (profiles/r03d_microbench.json)
+MMA_SYNC_F16_K16_PEAK = 555.0
 
 
 def measured_peaks():
@@ -634,22 +637,28 @@ def main():
         "evidence": "profiles/ (ncu --set full details and launch lists of this round, named r02*)",
     }
     if on_tensor:
-        # the dominant kernel is a block-sparse x dense product on the tensor pipe (ncu: tensor pipe 54 %, the
-        # busiest unit; profiles/r02i_planarg_mma_planarz_ncu_details.txt).  Dense-equivalent flops of one pass:
-        # 3 products (tf32 head/tail split) x pairs x 16 voxels x layers x 2.
-        flops = 3.0 * pairs * 16.0 * layers * 2.0
+        # the dominant kernel is a block-sparse x dense product on the tensor pipe (ncu: the tensor pipe is the
+        # busiest unit; profiles/r02i_*, r03b_*).  Dense-equivalent flops of one pass = products x pairs x 16 voxels x
+        # layers x 2: the split-fp16 kernel issues all four products of its {hi, lo} operands as two m16n8k16
+        # instructions per tile, the 3xTF32 kernel (DRTVAM_PLANAR_FORWARD=tf32) three m16n8k8 products.
+        h16 = os.environ.get("DRTVAM_PLANAR_FORWARD", "") == ""
+        products, mma_peak = (4.0, MMA_SYNC_F16_K16_PEAK) if h16 else (3.0, MMA_SYNC_TF32_PEAK)
+        flops = products * pairs * 16.0 * layers * 2.0
         tf = flops / (fwd_ms * 1e-3) * 1e-12
         roofline.update({
-            "bound": "tensor", "achieved": tf, "peak": MMA_SYNC_TF32_PEAK, "unit": "TFLOP/s",
-            "frac": tf / MMA_SYNC_TF32_PEAK,
-            "peak_source": "measured on this pool's B200 for the instruction the kernel issues (mma.sync.m16n8k8 tf32 "
-                           "-> SASS HMMA, csrc/microbench.cu, profiles/r02g_microbench.json); MEASURED_PEAKS.json only "
-                           "holds the cuBLAS bf16 tcgen05 figure, which this gathered 16x8x8 product cannot be fed into "
-                           "(DESIGN.md section 5)",
+            "kernel": "forward projection A p: absmax + zpack_h16 + planarg_h16_kernel (patch gather as mma.sync m16n8k16 "
+                      "f16 on {hi, lo} fp16 splits of both operands)" if h16 else roofline["kernel"],
+            "bound": "tensor", "achieved": tf, "peak": mma_peak, "unit": "TFLOP/s",
+            "frac": tf / mma_peak,
+            "peak_source": "measured on this pool's B200 for the instruction the kernel issues (mma.sync m16n8k16 f16 -> "
+                           "SASS HMMA.16816.F32, or m16n8k8 tf32; csrc/microbench.cu, profiles/r03d_microbench.json); "
+                           "MEASURED_PEAKS.json only holds the cuBLAS bf16 tcgen05 figure, which this gathered 16x8xK "
+                           "product cannot be fed into (DESIGN.md section 5)",
             "flops_per_launch": flops, "coefficient_pairs": pairs, "layers": layers,
             "useful_flops_per_launch": 2.0 * visits,
-            "note": "achieved = dense-equivalent tf32 flops of one forward pass / CUDA-event time of the pass; 80 % "
-                    "of them multiply zeros of the block-sparse coefficient blocks (useful = 2 flops per voxel visit). "
+            "note": "achieved = dense-equivalent flops of one forward pass / CUDA-event time of the pass; 80 % "
+                    "of them multiply zeros of the block-sparse coefficient blocks and the operand split multiplies "
+                    "them by 4 (useful = 2 flops per voxel visit). "
                     "frac_hbm = algorithmic HBM bytes (pattern values + pixel indices read, dose written) / time "
                     "against the measured copy peak; frac_atomic = voxel visits/s against the measured rate of the "
                     "shared-memory read-add-write the scatter form would need (accumulators live in registers here, so "

@@ -155,9 +155,92 @@ __global__ void mma_tf32_kernel(float* out, int iters) {
     if (acc == 123.456f) out[0] = acc;
 }
 
+// The same for mma.sync.aligned.m16n8k8 f16 with fp32 accumulators (SASS HMMA.1688.F32), the instruction of the
+// split-fp16 patch gather (planarg_h16_kernel).
+template <int kIlp>
+__global__ void mma_f16_kernel(float* out, int iters) {
+    float c[kIlp][4];
+#pragma unroll
+    for (int i = 0; i < kIlp; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) c[i][j] = 0.f;
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t a0 = 0x3c003800u + (lane & 7), a1 = 0x38003c00u + (lane & 3), b0 = 0x34003400u + (lane & 1);
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int i = 0; i < kIlp; ++i)
+            asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%0,%1,%2,%3};"
+                         : "+f"(c[i][0]), "+f"(c[i][1]), "+f"(c[i][2]), "+f"(c[i][3])
+                         : "r"(a0), "r"(a1), "r"(b0));
+    }
+    float acc = 0.f;
+#pragma unroll
+    for (int i = 0; i < kIlp; ++i) acc += c[i][0] + c[i][1] + c[i][2] + c[i][3];
+    if (acc == 123.456f) out[0] = acc;
+}
+
+// mma.sync.aligned.m16n8k16 f16 with fp32 accumulators (SASS HMMA.16816.F32): twice the flops per instruction
+template <int kIlp>
+__global__ void mma_f16k16_kernel(float* out, int iters) {
+    float c[kIlp][4];
+#pragma unroll
+    for (int i = 0; i < kIlp; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) c[i][j] = 0.f;
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t a0 = 0x3c003800u + (lane & 7), a1 = 0x38003c00u + (lane & 3), b0 = 0x34003400u + (lane & 1);
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int i = 0; i < kIlp; ++i)
+            asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                         : "+f"(c[i][0]), "+f"(c[i][1]), "+f"(c[i][2]), "+f"(c[i][3])
+                         : "r"(a0), "r"(a1), "r"(a1), "r"(a0), "r"(b0), "r"(b0));
+    }
+    float acc = 0.f;
+#pragma unroll
+    for (int i = 0; i < kIlp; ++i) acc += c[i][0] + c[i][1] + c[i][2] + c[i][3];
+    if (acc == 123.456f) out[0] = acc;
+}
+
 }  // namespace
 
 extern "C" {
+
+// mma.sync m16n8k16 f16 -> f32: dense TFLOP/s (2 * 16 * 8 * 16 flop per instruction and warp)
+double drtvam_mb_mma_f16k16(float* out, int ilp, int iters, int blocks, int threads) {
+    cudaEvent_t a, b;
+    cudaEventCreate(&a); cudaEventCreate(&b);
+    for (int rep = 0; rep < 2; ++rep) {
+        cudaEventRecord(a);
+        if (ilp == 1) mma_f16k16_kernel<1><<<blocks, threads>>>(out, iters);
+        else if (ilp == 4) mma_f16k16_kernel<4><<<blocks, threads>>>(out, iters);
+        else mma_f16k16_kernel<16><<<blocks, threads>>>(out, iters);
+        cudaEventRecord(b);
+    }
+    if (cudaGetLastError() != cudaSuccess) return -1.0;
+    const float ms = time_launches(a, b);
+    cudaEventDestroy(a); cudaEventDestroy(b);
+    const double mmas = static_cast<double>(blocks) * (threads / 32) * iters * (ilp > 4 ? 16 : ilp);
+    return mmas * 4096.0 / (ms * 1e-3) * 1e-12;
+}
+
+// mma.sync m16n8k8 f16 -> f32: dense TFLOP/s (2 * 16 * 8 * 8 flop per instruction and warp)
+double drtvam_mb_mma_f16(float* out, int ilp, int iters, int blocks, int threads) {
+    cudaEvent_t a, b;
+    cudaEventCreate(&a); cudaEventCreate(&b);
+    for (int rep = 0; rep < 2; ++rep) {
+        cudaEventRecord(a);
+        if (ilp == 1) mma_f16_kernel<1><<<blocks, threads>>>(out, iters);
+        else if (ilp == 4) mma_f16_kernel<4><<<blocks, threads>>>(out, iters);
+        else mma_f16_kernel<16><<<blocks, threads>>>(out, iters);
+        cudaEventRecord(b);
+    }
+    if (cudaGetLastError() != cudaSuccess) return -1.0;
+    const float ms = time_launches(a, b);
+    cudaEventDestroy(a); cudaEventDestroy(b);
+    const double mmas = static_cast<double>(blocks) * (threads / 32) * iters * (ilp > 4 ? 16 : ilp);
+    return mmas * 2048.0 / (ms * 1e-3) * 1e-12;
+}
 
 // mma.sync m16n8k8 tf32: returns dense TFLOP/s (2 * 16 * 8 * 8 flop per instruction and warp)
 double drtvam_mb_mma_tf32(float* out, int ilp, int iters, int blocks, int threads) {

@@ -1358,6 +1358,15 @@ __device__ __forceinline__ void mma_h16(float (&c)[4], uint32_t a0, uint32_t a1,
                  : "r"(a0), "r"(a1), "r"(b0));
 }
 
+__device__ __forceinline__ void mma_h16k16(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
+                                           uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+constexpr bool kK16 = true;   // false: three m16n8k8 products per tile (measured slower)
+
 template <int NT>
 __global__ void __launch_bounds__(32 * kGWarpsX * kGWarpsY, 2)
 planarg_h16_kernel(const __grid_constant__ SceneParams P, const __grid_constant__ PlanarZPlan Z,
@@ -1466,9 +1475,17 @@ planarg_h16_kernel(const __grid_constant__ SceneParams P, const __grid_constant_
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 const uint32_t bh = __byte_perm(ba[i], bc[i], 0x5410), bl = __byte_perm(ba[i], bc[i], 0x7632);
-                mma_h16(acc[4 * t4 + i], a0h, a1h, bh);
-                mma_h16(acc[4 * t4 + i], a0l, a1l, bh);
-                mma_h16(acc[4 * t4 + i], a0h, a1h, bl);
+                if (kK16) {
+                    // [a_hi | a_lo] (16 x 16) times [b_hi ; b_hi], then times [b_lo ; b_lo]: all four products of
+                    // the split operands in two m16n8k16 instructions (k = 0..7: the hi parts of the eight pairs,
+                    // k = 8..15: their lo parts)
+                    mma_h16k16(acc[4 * t4 + i], a0h, a1h, a0l, a1l, bh, bh);
+                    mma_h16k16(acc[4 * t4 + i], a0h, a1h, a0l, a1l, bl, bl);
+                } else {
+                    mma_h16(acc[4 * t4 + i], a0h, a1h, bh);
+                    mma_h16(acc[4 * t4 + i], a0l, a1l, bh);
+                    mma_h16(acc[4 * t4 + i], a0h, a1h, bl);
+                }
             }
         }
         __syncwarp();  // the buffer is refilled by the issue of the next iteration

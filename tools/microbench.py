@@ -52,6 +52,19 @@ def main():
         for ilp in (1, 4, 16):
             t = lib.drtvam_mb_mma_tf32(o.data_ptr(), ilp, 4096, 148, threads)
             out[f"mma_sync_tf32_m16n8k8_w{threads // 32}_ilp{ilp}_TFLOPs"] = round(t, 1)
+    # the instruction of the split-fp16 patch gather: mma.sync m16n8k8 f16 with fp32 accumulators
+    lib.drtvam_mb_mma_f16.restype = C.c_double
+    lib.drtvam_mb_mma_f16.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int]
+    for threads in (128, 256, 512):
+        for ilp in (1, 4, 16):
+            t = lib.drtvam_mb_mma_f16(o.data_ptr(), ilp, 4096, 148, threads)
+            out[f"mma_sync_f16_m16n8k8_w{threads // 32}_ilp{ilp}_TFLOPs"] = round(t, 1)
+    lib.drtvam_mb_mma_f16k16.restype = C.c_double
+    lib.drtvam_mb_mma_f16k16.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int]
+    for threads in (128, 256, 512):
+        for ilp in (1, 4, 16):
+            t = lib.drtvam_mb_mma_f16k16(o.data_ptr(), ilp, 4096, 148, threads)
+            out[f"mma_sync_f16_m16n8k16_w{threads // 32}_ilp{ilp}_TFLOPs"] = round(t, 1)
     torch.cuda.synchronize()
     print(json.dumps(out))
 
