@@ -190,8 +190,17 @@ class VolumeIntegrator(TVAMIntegrator):
                                    device=scene.emitters()[0].active_data.device, dtype=torch.float32)
             return self._project(scene, sensor, seed, spp, tangent.reshape(-1))
 
-    def render_backward(self, scene, params, grad_in, sensor=0, seed: int = 0, spp: int = 0):
-        """Adjoint A^T grad_in; returns d loss / d projector.active_data."""
+    def render_backward(self, scene, params, grad_in, sensor=0, seed: int = 0, spp: int = 0, host_out=None, blocks: int = 1,
+                        wait: bool = True):
+        """Adjoint A^T grad_in; returns d loss / d projector.active_data.
+
+        `host_out` (a pinned host tensor of the gradient's length; no counterpart in the reference, whose
+        gradients stay Dr.Jit arrays): the gradient is also copied there on the scene's copy stream - with
+        `blocks` > 1 in blocks of angles, the copy of a block running under the adjoint of the next one (measured
+        at C2: the four smaller adjoint calls cost more than the overlap saves, 21.5 against 20.0 ms per step
+        end to end, so one block is the default and the copy overlaps whatever the caller launches next).  The caller's stream
+        waits for the copies before it goes on, unless `wait` is false (the caller then waits for
+        `scene.copy_stream()` itself before it reads `host_out`)."""
         _check_emitters(scene)
         sensor = _sensor_of(scene, sensor)
         projector = scene.emitters()[0]
@@ -208,12 +217,37 @@ class VolumeIntegrator(TVAMIntegrator):
         lib = _lib.load()
         ev = self._event_pair('adjoint')
         _lib.check(lib.drtvam_scene_set_inv_volume(handle, inv_tensor.data_ptr() if inv_tensor is not None else None))
+        main = torch.cuda.current_stream(g.device)
+        n = pixels.numel()
+        hw = projector.res[0] * projector.res[1]
+        rows = getattr(scene, '_z_rows', None)
+        per_pattern = hw if rows is None else (rows[1] - rows[0]) * projector.res[0]
+        nk = n // per_pattern if per_pattern and n % per_pattern == 0 else 0
+        # lanes that draw samples are numbered through the whole call: those calls are not cut into blocks
+        draws = not (self.regular_sampling and not self.sample_time and projector.kind == 'collimated'
+                     and float(scene.medium.get('albedo', 0.0)) == 0.0 and sensor.kind == 'dda')
+        stream_out = (host_out is not None and host_out.is_pinned() and host_out.numel() == n and nk > 1
+                      and blocks > 1 and not draws)
+        blocks = max(1, min(int(blocks), nk)) if stream_out else 1
+        bounds = [per_pattern * (nk * b // blocks) for b in range(blocks + 1)] if stream_out else [0, n]
+        copy = scene.copy_stream() if host_out is not None else None
         try:
-            _lib.check(lib.drtvam_adjoint(handle, g.data_ptr(), pixels.data_ptr(), pixels.numel(), spp,
-                                          seed & 0xFFFFFFFF, inv_scalar, out.data_ptr(),
-                                          torch.cuda.current_stream(g.device).cuda_stream))
+            for b in range(blocks):
+                lo, hi = bounds[b], bounds[b + 1]
+                _lib.check(lib.drtvam_adjoint(handle, g.data_ptr(), pixels[lo:hi].data_ptr(), hi - lo, spp,
+                                              seed & 0xFFFFFFFF, inv_scalar, out[lo:hi].data_ptr(), main.cuda_stream))
+                if host_out is not None:
+                    done = torch.cuda.Event()
+                    done.record(main)
+                    with torch.cuda.stream(copy):
+                        copy.wait_event(done)
+                        host_out.reshape(-1)[lo:hi].copy_(out[lo:hi], non_blocking=True)
         finally:
             lib.drtvam_scene_set_inv_volume(handle, None)
+        if host_out is not None:
+            out.record_stream(copy)
+            if wait:
+                main.wait_stream(copy)
         if ev is not None:
             ev[1].record()
         return out

@@ -250,3 +250,27 @@ def test_streamed_render_equals_plain_render(regular, workdir):
     # pageable memory: one upload, same result
     streamed = integ.render(scene, sensor, seed=3, spp=2, host_patterns=host.clone())
     assert rel_l2(streamed.cpu().numpy(), plain.cpu().numpy()) < 1e-6
+
+
+@pytest.mark.parametrize("regular", [True, False])
+def test_streamed_gradient_download_equals_plain_adjoint(regular, workdir):
+    """render_backward(host_out=...) runs the adjoint in blocks of projection angles and copies the gradient
+    of a block to the host under the adjoint of the next one (A^T g is block-diagonal in the angles).  Same
+    gradient as one call; jittered configurations are not cut (their lanes are numbered through the whole
+    call) but still deliver the host copy."""
+    scene, integ, sensor, d, _ = build("C3", workdir, 48, n_patterns=10, device="cuda", regular_sampling=regular)
+    n = scene.projector.active_size()
+    g = torch.randn(scene.film_shape(sensor), generator=torch.Generator().manual_seed(7)).cuda()
+    plain = integ.render_backward(scene, None, g, sensor, seed=3, spp=2).clone()
+    for blocks in (1, 3, 10, 64):
+        host = torch.full((n,), float("nan")).pin_memory()
+        out = integ.render_backward(scene, None, g, sensor, seed=3, spp=2, host_out=host, blocks=blocks)
+        torch.cuda.current_stream().synchronize()
+        assert rel_l2(out.cpu().numpy(), plain.cpu().numpy()) < 1e-5
+        assert torch.equal(host, out.cpu())
+    # wait=False: the caller waits for the scene's copy stream itself
+    host = torch.full((n,), float("nan")).pin_memory()
+    out = integ.render_backward(scene, None, g, sensor, seed=3, spp=2, host_out=host, wait=False)
+    torch.cuda.current_stream().wait_stream(scene.copy_stream())
+    torch.cuda.current_stream().synchronize()
+    assert torch.equal(host, out.cpu())
