@@ -342,8 +342,9 @@ constexpr float kLog2e = 1.4426950408889634f;
 
 struct InsideTilePlan {
     const float4* seg_a;     // centre rays of the (angle, column) pairs (planar.cuh)
-    const int* tile_off;     // [n_tiles][n_patterns + 1]
-    const int* tile_clo;     // [n_tiles][n_patterns]
+    const int* tile_off;     // [n_tiles][n_patterns + 1] prefix of the entries of a tile, per angle
+    const int* tile_clo;     // the column list: angle * res_x + column of every entry (planar_tile_lists)
+    const int* tile_ebase;   // [n_tiles + 1] first entry of every tile
     const int* zl;           // film layer of active layer a
     const int* a_row_begin;  // CSR of the DMD rows of active layer a (exactly one row per layer here)
     const int* a_rows;
@@ -384,7 +385,7 @@ inside_tile_kernel(const __grid_constant__ SceneParams P, const __grid_constant_
     const int ka = k0 + static_cast<int>(static_cast<long long>(nk) * group / Z.groups);
     const int kb = k0 + static_cast<int>(static_cast<long long>(nk) * (group + 1) / Z.groups);
     const int* __restrict__ off = Z.tile_off + static_cast<size_t>(tile_id) * (P.n_patterns + 1);
-    const int* __restrict__ clo = Z.tile_clo + static_cast<size_t>(tile_id) * P.n_patterns;
+    const int* __restrict__ lst = Z.tile_clo + __ldg(Z.tile_ebase + tile_id);
     const int g_begin = __ldg(off + ka), g_end = __ldg(off + kb);
 
     // ---- does any group of this CTA hold records?  (most tiles lie outside the target or above / below it)
@@ -394,9 +395,7 @@ inside_tile_kernel(const __grid_constant__ SceneParams P, const __grid_constant_
         int k = ka;
         bool any = false;
         for (int g = g_begin + static_cast<int>(threadIdx.x); g < g_end && !any; g += kTThreads) {
-            while (__ldg(off + k + 1) <= g) ++k;
-            const int c = __ldg(clo + k) + (g - __ldg(off + k));
-            any = __ldg(grp + (static_cast<size_t>(k) * P.res_x + c) * n_blk + blk).y != 0;
+            any = __ldg(grp + static_cast<size_t>(__ldg(lst + g)) * n_blk + blk).y != 0;
         }
         if (any) touched = 1;
     }
@@ -452,9 +451,10 @@ inside_tile_kernel(const __grid_constant__ SceneParams P, const __grid_constant_
     // (issuing the header chain of the NEXT group before the current one is marched was measured: 98.5 instead
     // of 96.8 ms per C4 step, session r02zj - the registers it holds cost more than the latency it hides)
     for (int g = g_begin + warp; g < g_end; g += kTWarps) {
-        while (__ldg(off + k + 1) <= g) ++k;
-        const int c = __ldg(clo + k) + (g - __ldg(off + k));
-        const uint2 hd = __ldg(grp + (static_cast<size_t>(k) * P.res_x + c) * n_blk + blk);
+        const int kc = __ldg(lst + g);
+        k = kc / P.res_x;
+        const int c = kc - k * P.res_x;
+        const uint2 hd = __ldg(grp + static_cast<size_t>(kc) * n_blk + blk);
         if (hd.y == 0) continue;
         float em = 1.f;
         if (kMode == 0) em = row >= 0 ? __ldg(in + active_index(P, k - k0, row, c)) * ray_weight : 0.f;
@@ -621,7 +621,7 @@ unsigned blocks_for(uint64_t n) { return static_cast<unsigned>((n + kThreads - 1
 }  // namespace
 
 void inside_release(InsideHost& H) {
-    void* ptrs[] = {H.off, H.seg, H.t_lo, H.odd_lanes, H.planes, H.grp, H.table, H.rbox, H.stat, H.mask, H.tile_off, H.tile_clo};
+    void* ptrs[] = {H.off, H.seg, H.t_lo, H.odd_lanes, H.planes, H.grp, H.table, H.rbox, H.stat, H.mask, H.tile_off, H.tile_clo, H.tile_ebase};
     for (void* q : ptrs)
         if (q) cudaFree(q);
     H = InsideHost{};
@@ -774,12 +774,15 @@ cudaError_t inside_build(const SceneParams& P, const SceneParams& P1, const Plan
             IN_TRY((cudaFuncSetAttribute(inside_tile_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          static_cast<int>(H.smem_bytes))));
             IN_TRY(cudaMalloc(&H.tile_off, sizeof(int) * static_cast<size_t>(n_tiles) * (np + 1)));
-            IN_TRY(cudaMalloc(&H.tile_clo, sizeof(int) * static_cast<size_t>(n_tiles) * np));
+            IN_TRY(cudaMalloc(&H.tile_ebase, sizeof(int) * (n_tiles + 1)));
             // a record follows the centre ray of its (angle, column) up to the re-spawn offsets of its crossings
             // (under a micrometre each): one pixel of margin
             const float margin = std::fmax(P1.pixel_x, P1.pixel_y);
-            IN_TRY(planar_tile_ranges(P1, base.seg_a, base.seg_b, H.tiles_x, H.tiles_y, H.tile_w, H.tile_h, H.tile_off,
-                                      H.tile_clo, margin));
+            // column lists, not ranges: behind the refracting box the range of a (tile, angle) spans the gap between
+            // the two ray families that cross the tile (60 % of the groups a CTA looked at missed its tile, r03m)
+            long long n_entries = 0;
+            IN_TRY(planar_tile_lists(P1, base.seg_a, base.seg_b, H.tiles_x, H.tiles_y, H.tile_w, H.tile_h, H.tile_off,
+                                     H.tile_ebase, &H.tile_clo, &n_entries, margin));
             H.seg_a = base.seg_a;
             H.tiles = true;
         }
@@ -805,7 +808,7 @@ cudaError_t inside_forward_begin(InsideHost& H, cudaStream_t stream) {
 static InsideTilePlan tile_plan(const InsideHost& H, const PlanarZHost& Zh) {
     InsideTilePlan Z{};
     Z.seg_a = H.seg_a;
-    Z.tile_off = H.tile_off; Z.tile_clo = H.tile_clo;
+    Z.tile_off = H.tile_off; Z.tile_clo = H.tile_clo; Z.tile_ebase = H.tile_ebase;
     Z.zl = Zh.zl; Z.a_row_begin = Zh.a_row_begin; Z.a_rows = Zh.a_rows;
     Z.tiles_x = H.tiles_x; Z.tiles_y = H.tiles_y; Z.tile_w = H.tile_w; Z.tile_h = H.tile_h;
     Z.nz = Zh.nz; Z.nz_pad = Zh.nz_pad;

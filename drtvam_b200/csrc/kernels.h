@@ -219,8 +219,9 @@ struct InsideHost {
     uint64_t n_rows = 0;
     uint64_t n_tile_rec = 0;    // records in the table (statistics)
     uint32_t* mask = nullptr;   // bit ((angle * res_x + column) * nz_pad + active layer): a tile lane
-    int* tile_off = nullptr;
+    int* tile_off = nullptr;    // per-tile column lists (planar_tile_lists)
     int* tile_clo = nullptr;
+    int* tile_ebase = nullptr;
     int tiles_x = 0, tiles_y = 0, tile_w = 0, tile_h = 0;
     size_t smem_bytes = 0;
 };
