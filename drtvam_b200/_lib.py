@@ -11,7 +11,7 @@ import os
 from . import build as _build
 
 MAX_SURFACES = 8
-ABI_VERSION = 12
+ABI_VERSION = 13
 
 
 class DrtvamSurface(C.Structure):
@@ -81,6 +81,8 @@ SYMBOLS = {
     "drtvam_adjoint_host": (C.c_int, [_vp, _vp, _vp, _u64, _u32, _u32, _f32, _vp]),
     "drtvam_thresholded_loss": (C.c_int, [C.c_int, _vp, _vp, _f32, _vp, _u64, _f32, _f32, _f32, _f32, _f32, _i32, _f32,
                                           _vp, _vp, _vp]),
+    "drtvam_thresholded_loss_sa": (C.c_int, [C.c_int, _vp, _vp, _f32, _vp, _u64, _f32, _f32, _f32, _f32, _f32, _i32, _f32,
+                                             _vp, _vp, _vp]),
     "drtvam_lbfgs_history": (C.c_int, [C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, _u64, _i32, _vp]),
     "drtvam_lbfgs_direction": (C.c_int, [C.c_int, _vp, _i32, _u64, _vp, _i32, _vp, _vp]),
     "drtvam_lbfgs_combine": (C.c_int, [C.c_int, _vp, _i32, _vp, _u64, _vp, _vp]),

@@ -951,6 +951,22 @@ int drtvam_thresholded_loss(int device, const float* dose, const float* dose_b, 
     return DRTVAM_OK;
 }
 
+int drtvam_thresholded_loss_sa(int device, const float* dose, const float* dose_b, float alpha, const float* target,
+                               uint64_t n_voxels, float tl, float tu, float weight_object, float weight_void,
+                               float weight_limit, int32_t K, float grad_scale, float* grad, double* loss_out,
+                               void* stream) {
+    if (!dose || !target || !loss_out) return fail(DRTVAM_E_INVALID, "NULL buffer");
+    if (K < 1 || K > 8) return fail(DRTVAM_E_INVALID, "exponent K = %d outside [1, 8]", K);
+    if (!(tl < tu))  // loss.py:114-115
+        return fail(DRTVAM_E_INVALID, "[ThresholdedLoss] Lower threshold (%g) must be smaller than upper threshold (%g)",
+                    tl, tu);
+    DeviceGuard guard(device);
+    if (!guard.ok) return fail(DRTVAM_E_CUDA, "cudaSetDevice(%d) failed", device);
+    CUDA_TRY(launch_thresholded_loss_sa(dose, dose_b, alpha, target, n_voxels, tl, tu, weight_object, weight_void,
+                                        weight_limit, K, grad_scale, grad, loss_out, static_cast<cudaStream_t>(stream)));
+    return DRTVAM_OK;
+}
+
 // ---- LinearLBFGS on the device (lbfgs.py:146-275) ---------------------------------------------------
 #define LB_GUARD(dev)                                                                 \
     DeviceGuard guard(dev);                                                           \

@@ -254,6 +254,10 @@ cudaError_t launch_corner(const SceneParams& P, const uint32_t* active_pixels, u
 cudaError_t launch_thresholded_loss(const float* x, const float* x_b, float alpha, const float* target, size_t n,
                                     float tl, float tu, float w_obj, float w_void, float w_lim, int K, float grad_scale,
                                     float* grad, double* loss_out, cudaStream_t stream);
+// the same for a surface-aware (two-channel) film and target; n_vox voxels, 2 n_vox floats per array
+cudaError_t launch_thresholded_loss_sa(const float* x, const float* x_b, float alpha, const float* target, size_t n_vox,
+                                    float tl, float tu, float w_obj, float w_void, float w_lim, int K, float grad_scale,
+                                    float* grad, double* loss_out, cudaStream_t stream);
 
 
 // LinearLBFGS on the device (lbfgs_kernels.cu)

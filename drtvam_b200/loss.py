@@ -40,14 +40,17 @@ class _FusedThresholded(torch.autograd.Function):
     def forward(ctx, x, dx, alpha, target, loss):
         from . import _lib
         lib = _lib.load()
-        n = x.numel()
+        # surface-aware: two channels per voxel, the loss is per VOXEL (Loss.__call__, loss.py:44-53)
+        two = target.dim() == 4 and target.shape[-1] == 2 and x.shape == target.shape
+        n = x.numel() // 2 if two else x.numel()
         n_mean = loss.dose_count if (loss.dose_allsum is not None and loss.dose_count) else n
         need_grad = x.requires_grad and torch.is_grad_enabled()
         ctx.has_grad = bool(x.requires_grad)
         grad = torch.empty_like(x) if x.requires_grad else None
         out = torch.empty(1, device=x.device, dtype=torch.float64)
         mean = loss.reduction is torch.mean
-        _lib.check(lib.drtvam_thresholded_loss(
+        fn = lib.drtvam_thresholded_loss_sa if two else lib.drtvam_thresholded_loss
+        _lib.check(fn(
             x.device.index or 0, x.data_ptr(), dx.data_ptr() if dx is not None else None, float(alpha),
             target.data_ptr(), n, float(loss.tl), float(loss.tu), float(loss.weight_object), float(loss.weight_void),
             float(loss.weight_limit), int(loss.K), (1.0 / n_mean) if mean else 1.0,
@@ -203,9 +206,11 @@ class ThresholdedLoss(Loss):
             return False
         if x.shape != target.shape and not (x.dim() == target.dim() + 1 and x.shape[-1] == 1):
             return False
-        if target.shape == x.shape and x.shape[-1] == 2 and x.dim() == 4:
-            return False  # surface-aware two-channel volumes take the generic path
         return float(self.K).is_integer() and 1 <= int(self.K) <= 8
+
+    @staticmethod
+    def _two_channel(x, target):
+        return target.shape == x.shape and x.dim() == 4 and x.shape[-1] == 2
 
     def armijo_sweep(self, x, dx, target, direction, first, count, sums, skip=None):
         """One stage of the Armijo back-tracking search (lbfgs.py:256-266), trials [first, first + count), in
@@ -213,8 +218,8 @@ class ThresholdedLoss(Loss):
         at x + 2^-k dx, summed over ranks when the dose is z-slab sharded.  Returns (scale, pattern_term) -
         the reference evaluates the pattern term on the DIRECTION (lbfgs.py:260) - or None when this
         volume pair cannot take the fused path.  `skip`: device float, non-zero = search already over."""
-        if not (self._fusable(x, target) and self._fusable(dx, target)) or int(self.K) > 4:
-            return None
+        if not (self._fusable(x, target) and self._fusable(dx, target)) or int(self.K) > 4 or self._two_channel(x, target):
+            return None   # (surface-aware volumes: the trials go one by one through drtvam_thresholded_loss_sa)
         from . import _lib
         lib = _lib.load()
         _lib.check(lib.drtvam_armijo_losses(

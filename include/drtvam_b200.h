@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define DRTVAM_ABI_VERSION 12
+#define DRTVAM_ABI_VERSION 13
 #define DRTVAM_MAX_SURFACES 8
 #define DRTVAM_MAX_MESH_SURFACES 4
 
@@ -307,6 +307,15 @@ int drtvam_thresholded_loss(int device, const float *dose, const float *dose_b, 
                             uint64_t n, float tl, float tu, float weight_object, float weight_void,
                             float weight_limit, int32_t K, float grad_scale, float *grad, double *loss_out,
                             void *stream);
+
+/* The same loss on a SURFACE-AWARE film (two channels per voxel: dose deposited inside / outside the target,
+ * film.py:17-21) against the two-channel target of sub-voxel volumes (sensor.py:53-110): per voxel
+ * w_in eval_in(dose[0]) + w_out eval_out(dose[1]) with w = target / (target[0] + target[1]), the weighting of
+ * Loss.__call__ (loss.py:44-53).  n_voxels voxels; dose, dose_b, target and grad hold 2 n_voxels floats. */
+int drtvam_thresholded_loss_sa(int device, const float *dose, const float *dose_b, float alpha, const float *target,
+                               uint64_t n_voxels, float tl, float tu, float weight_object, float weight_void,
+                               float weight_limit, int32_t K, float grad_scale, float *grad, double *loss_out,
+                               void *stream);
 
 /* ---- LinearLBFGS on the device (lbfgs.py:146-275) --------------------------
  * All buffers are DEVICE buffers of fp32 pattern vectors of n elements unless stated; nothing below

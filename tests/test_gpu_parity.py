@@ -556,3 +556,42 @@ def test_fused_thresholded_loss_matches_torch(K, reduction):
         lazy = fused(LazyAxpy(x.detach(), dx, 0.5), target, torch.zeros(3, device="cuda"))
         generic = super(ThresholdedLoss, fused).__call__(x.detach() + 0.5 * dx, target, torch.zeros(3, device="cuda"))
     assert abs(float(lazy) - float(generic)) < 1e-5 * abs(float(generic))
+
+
+@pytest.mark.parametrize("reduction", ["sum", "mean"])
+@pytest.mark.parametrize("K", [1, 2, 3])
+def test_fused_surface_aware_loss_matches_torch(K, reduction):
+    """Loss.__call__ on a surface-aware (two-channel) film, loss.py:44-53: w_in eval_in(x[..., 0]) +
+    w_out eval_out(x[..., 1]) with w = target / target.sum(-1); the fused CUDA loss
+    (drtvam_thresholded_loss_sa) against the same formula in fp64 and against the generic torch path,
+    value, gradient and the lazy Armijo form."""
+    from drtvam_b200.loss import LazyAxpy, Loss, ThresholdedLoss
+    g = torch.Generator(device="cuda").manual_seed(6)
+    shape = (19, 23, 29, 2)
+    x = (torch.rand(shape, device="cuda", generator=g) * 1.6).requires_grad_(True)
+    dx = torch.randn(shape, device="cuda", generator=g) * 0.1
+    frac = torch.rand(shape[:-1], device="cuda", generator=g)
+    frac = torch.where(frac < 0.3, torch.zeros_like(frac), torch.where(frac > 0.7, torch.ones_like(frac), frac))
+    vol = 0.02 + 0.01 * torch.rand(shape[:-1], device="cuda", generator=g)      # sub-voxel volumes, not normalised
+    target = torch.stack([frac * vol, (1 - frac) * vol], -1).contiguous()
+    props = {"K": K, "tl": 0.85, "tu": 0.93, "weight_object": 1.5, "weight_void": 0.7, "weight_limit": 2.0,
+             "reduction": reduction}
+    fused = ThresholdedLoss(props)
+    zero = torch.zeros(3, device="cuda")
+    loss = fused(x, target, zero)
+    loss.backward()
+    xd = x.detach().double().requires_grad_(True)
+    t = target.double()
+    w = t / t.sum(-1, keepdim=True)
+    inside = props["weight_object"] * torch.clamp_min(props["tu"] - xd[..., 0], 0) ** K + \
+        props["weight_limit"] * torch.clamp_min(xd[..., 0] - 1.0, 0) ** K
+    outside = props["weight_void"] * torch.clamp_min(xd[..., 1] - props["tl"], 0) ** K
+    ref = w[..., 0] * inside + w[..., 1] * outside
+    ref = ref.sum() if reduction == "sum" else ref.mean()
+    ref.backward()
+    assert abs(float(loss) - float(ref)) < 2e-6 * abs(float(ref))
+    assert rel_l2(x.grad.cpu().numpy(), xd.grad.cpu().numpy()) < 1e-6
+    with torch.no_grad():
+        lazy = fused(LazyAxpy(x.detach(), dx, 0.5), target, zero)
+        generic = Loss.__call__(fused, x.detach() + 0.5 * dx, target, zero)
+    assert abs(float(lazy) - float(generic)) < 1e-5 * abs(float(generic))
