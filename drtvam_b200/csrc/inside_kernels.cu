@@ -812,7 +812,9 @@ static InsideTilePlan tile_plan(const InsideHost& H, const PlanarZHost& Zh) {
     Z.zl = Zh.zl; Z.a_row_begin = Zh.a_row_begin; Z.a_rows = Zh.a_rows;
     Z.tiles_x = H.tiles_x; Z.tiles_y = H.tiles_y; Z.tile_w = H.tile_w; Z.tile_h = H.tile_h;
     Z.nz = Zh.nz; Z.nz_pad = Zh.nz_pad;
-    Z.groups = 4;   // the tiles over the target hold all the work: four CTAs each
+    // the tiles over the target hold all the work: several CTAs (angle groups) each
+    static const int groups = std::getenv("DRTVAM_INSIDE_GROUPS") ? std::max(1, std::atoi(std::getenv("DRTVAM_INSIDE_GROUPS"))) : 4;
+    Z.groups = groups;
     return Z;
 }
 

@@ -258,6 +258,10 @@ class Scene:
         self.rank, self.world_size, self.group = rank, world_size, group
         n_full = p.active_pixels.numel()
         self._full_active_pixels = p.active_pixels     # the unsharded list: gather_patterns / final pattern export
+        # a surface-aware film keeps the angle partition: its tile kernel (csrc/inside_kernels.cu) needs the whole
+        # layer range of the handle, and with it the angle shards are 3 x faster than slabs on the per-lane records
+        if partition == "auto" and sensor is not None and getattr(sensor.film(), "surface_aware", False):
+            partition = "angle"
         if partition in ("auto", "zslab") and world_size > 1 and integrator is not None:
             rz = int(sensor.resolution()[2])
             A, S = grid if grid is not None else (slab_grid(world_size, rz) if partition == "auto" else (1, world_size))
