@@ -531,7 +531,8 @@ int drtvam_scene_set_z_window(DrtvamScene* s, int32_t z_begin, int32_t z_end, in
     }
     if (s->P.surface_aware) return fail(DRTVAM_E_INVALID, "a z window is not supported with a surface-aware film");
     if (int rc = ensure_planar(s)) return rc;
-    if (!s->planar_ok)
+    // (a scattering medium is planar only in its first segments: the scattered ones leave their layers)
+    if (!s->planar_ok || s->hybrid)
         return fail(DRTVAM_E_INVALID, "a z window needs a planar scene (collimated projector, rotation about z, "
                                       "vertical vial walls, no scattering): shard by projection angle instead");
     const std::vector<int>& rl = s->planar.row_layer;

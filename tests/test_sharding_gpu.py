@@ -131,6 +131,14 @@ def test_sampler_index_makes_angle_shards_reproduce_the_full_run(workdir):
     _lib.check(h.lib.drtvam_scene_set_sampler_index(h.h, None))
     # without the index the second shard draws other samples
     assert rel_l2(h.adjoint(g, pix[3 * hw:], 4, 3), a_full[3 * hw:]) > 1e-3
+    # a scattering medium is planar only in its first segments (plan 4): scattered rays leave their layers, so it
+    # must refuse a z window and be sharded by angle
+    assert h.lib.drtvam_scene_plan(h.h, pix.size, 4) == 4
+    assert h.lib.drtvam_scene_set_z_window(h.h, 0, 16, None, None) == -1
+    assert b"shard by projection angle" in h.lib.drtvam_last_error()
+    from drtvam_b200.parallel import zslab_shard
+    scene_g, integ_g, sensor_g, _, _ = build("C5", workdir, 32, n_patterns=8, spp=4, device="cuda")
+    assert zslab_shard(scene_g, 0, 2, integ_g, sensor_g) is None
 
 
 def test_pinned_pixel_list(workdir):
