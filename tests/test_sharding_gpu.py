@@ -239,6 +239,18 @@ def test_nccl_entry_points_single_rank(workdir):
     _lib.check(h.lib.drtvam_comm_destroy(h.h))
 
 
+def test_streamed_render_of_a_scattering_scene(workdir):
+    """The same for the scattering hybrid (plan 4): every block runs the planar per-lane kernels for its first
+    segments and the tracer for the rest, both on the lanes' positions in the whole wavefront."""
+    scene, integ, sensor, d, _ = build("C5", workdir, 48, n_patterns=10, device="cuda", spp=2)
+    n = scene.projector.active_size()
+    host = (torch.rand(n, generator=torch.Generator().manual_seed(5)) - 0.2).pin_memory()
+    scene.projector.active_data = host.cuda()
+    plain = integ.render(scene, sensor, seed=3, spp=2).clone()
+    streamed = integ.render(scene, sensor, seed=3, spp=2, host_patterns=host, blocks=3)
+    assert rel_l2(streamed.cpu().numpy(), plain.cpu().numpy()) < 1e-5
+
+
 @pytest.mark.parametrize("regular", [True, False])
 def test_streamed_render_equals_plain_render(regular, workdir):
     """render(host_patterns=...) uploads the patterns in blocks of projection angles under the projection of
