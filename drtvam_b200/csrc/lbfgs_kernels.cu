@@ -126,20 +126,29 @@ __global__ void solve_kernel(const double* __restrict__ G, int h, int first_step
     for (int j = 0; j < N; ++j) delta[j] = 0.0;
     delta[2 * h] = 1.0;
     bool bad = false;
+    // A pair with y.s = 0 (both vectors vanish when the loss has all but reached 0) would make 1 / (y.s) infinite
+    // and the direction NaN - in the reference too (lbfgs.py:221-222 takes dr.rcp(ys) unguarded).  Such a pair
+    // carries no curvature information and is left out; the reference's arithmetic is unchanged wherever it is finite.
+    auto usable = [](double ys) { return ys == ys && ys != 0.0 && fabs(ys) < 1.0e300; };
     for (int i = h - 1; i >= 0; --i) {
         const double ys = G[(h + i) * N + i];
+        alpha[i] = 0.0;
+        if (!usable(ys)) { bad = true; continue; }
         double sq = 0.0;
         for (int j = 0; j < N; ++j) sq += delta[j] * G[i * N + j];
         const double a = sq / ys;
-        if (!(ys == ys) || ys == 0.0) bad = true;
         alpha[i] = a;
         delta[h + i] -= a;
     }
     double gamma = 1.0;
-    if (!first_step && h > 0) gamma = G[(2 * h - 1) * N + (h - 1)] / G[(2 * h - 1) * N + (2 * h - 1)];
+    if (!first_step && h > 0) {
+        const double yy = G[(2 * h - 1) * N + (2 * h - 1)], ys = G[(2 * h - 1) * N + (h - 1)];
+        if (usable(ys) && usable(yy)) gamma = ys / yy;
+    }
     for (int j = 0; j < N; ++j) delta[j] *= gamma;
     for (int i = 0; i < h; ++i) {
         const double ys = G[(h + i) * N + i];
+        if (!usable(ys)) continue;
         double yz = 0.0;
         for (int j = 0; j < N; ++j) yz += delta[j] * G[(h + i) * N + j];
         delta[i] += alpha[i] - yz / ys;
@@ -183,6 +192,7 @@ __device__ __forceinline__ float powk(float b) {   // relu(b)^K for b >= 0, relu
 
 template <int K>
 __device__ __forceinline__ float armijo_term(const ArmijoParams& L, float x, float t) {
+    if (x != x) return x;   // relu(NaN) is NaN in the reference (fmaxf would return the other operand)
     if (t > 0.f) return L.w_obj * powk<K>(fmaxf(L.tu - x, 0.f)) + L.w_lim * powk<K>(fmaxf(x - 1.f, 0.f));
     return L.w_void * powk<K>(fmaxf(x - L.tl, 0.f));
 }

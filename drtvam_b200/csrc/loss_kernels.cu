@@ -30,6 +30,10 @@ struct LossParams {
 };
 
 __device__ __forceinline__ float loss_term(const LossParams& L, float x, float t, float& g) {
+    if (x != x) {  // relu(NaN) is NaN in the reference; fmaxf would return the other operand and report loss 0
+        g = x;
+        return x;
+    }
     if (t > 0.f) {  // inside the object: under-exposure below tu, over-exposure above 1
         const float a = fmaxf(L.tu - x, 0.f), b = fmaxf(x - 1.f, 0.f);
         const float a1 = powi(a, L.K - 1), b1 = powi(b, L.K - 1);

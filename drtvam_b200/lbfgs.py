@@ -101,13 +101,24 @@ class LinearLBFGS(Optimizer):
         q = self.g_old[k].clone()
         n = len(s)
         alphas = [None] * n
+        # a pair with y.s = 0 (both vanish when the loss has all but reached 0) would give an infinite 1 / (y.s) and
+        # a NaN direction, as it does in the reference (lbfgs.py:221-222); it carries no curvature and is left out
+        use = [bool(torch.isfinite(torch.as_tensor(v)).all()) and float(v) != 0.0 for v in ys]
         for i in range(n - 1, -1, -1):
+            if not use[i]:
+                continue
             a = self.dot(s[i], q) / ys[i]
             q = q - a * y[i]
             alphas[i] = a
-        gamma = 1.0 if self.t[k] == 1 else ys[-1] / self.dot(y[-1], y[-1])
+        gamma = 1.0
+        if self.t[k] != 1 and use[-1]:
+            yy = self.dot(y[-1], y[-1])
+            if float(yy) != 0.0:
+                gamma = ys[-1] / yy
         z = gamma * q
         for i in range(n):
+            if not use[i]:
+                continue
             b = self.dot(y[i], z) / ys[i]
             z = z + (alphas[i] - b) * s[i]
         return -z

@@ -35,6 +35,30 @@ def test_linear_lbfgs_converges_on_quadratic():
     assert all(b_ <= a_ + 1e-12 for a_, b_ in zip(losses, losses[1:]))
 
 
+def test_vanishing_pairs_do_not_poison_the_direction():
+    """Once a thresholded loss has reached exactly 0 the gradient vanishes, and with it s and y of the next pair:
+    y.s = 0.  The reference takes 1 / (y.s) unguarded (lbfgs.py:221-222) and continues on NaNs; here such a pair
+    is left out and the iterate stays finite (and where y.s != 0 the arithmetic is the reference's)."""
+    key = 'projector.active_data'
+
+    def render_fn(v):
+        return v[key] * 2.0
+
+    def loss_fn(y, patterns):
+        return torch.sum(torch.clamp_min(1.0 - y, 0) ** 2)     # exactly 0 once y >= 1 everywhere
+
+    opt = LinearLBFGS(render_fn=render_fn, loss_fn=loss_fn)
+    opt[key] = torch.zeros(8, dtype=torch.float64)
+    for i in range(12):
+        x = opt[key]
+        vol = render_fn({key: x})
+        loss = loss_fn(vol, x)
+        loss.backward()
+        opt.step(vol.detach(), loss.detach())
+        assert torch.isfinite(opt[key]).all(), i
+    assert float(loss_fn(render_fn({key: opt[key].detach()}), None)) == 0.0
+
+
 def test_step_requires_gradient():
     import pytest
     opt = LinearLBFGS(render_fn=lambda v: v['k'], loss_fn=lambda y, p: y.sum())
@@ -97,3 +121,46 @@ def test_device_lbfgs_follows_the_eager_loop(sparsity):
             err = float(torch.linalg.norm(a[3] - b[3]) / torch.linalg.norm(b[3]))
             assert err < 2e-5, (i, err)
         assert abs(a[0] - b[0]) < 2e-2 * abs(b[0]) + 1e-6, (i, a[0], b[0])
+
+
+@pytest.mark.gpu
+def test_device_direction_leaves_vanishing_pairs_out():
+    """drtvam_lbfgs_direction on a history whose newest pair is (0, 0) - the state after a step at loss 0 - and on
+    a NaN dose in the fused losses: coefficients stay finite (the direction falls back to -g from the usable
+    pairs), and a NaN dose gives a NaN loss as relu(NaN) does in the reference, not the 0 of fmaxf."""
+    import ctypes as C
+    from drtvam_b200 import _lib
+    from drtvam_b200.loss import ThresholdedLoss
+    lib = _lib.load()
+    dev = torch.device("cuda")
+    n = 4096
+    g = torch.randn(n, device=dev)
+    s0, y0 = torch.randn(n, device=dev) * 0.1, torch.randn(n, device=dev) * 0.1
+    if float(torch.dot(s0, y0)) < 0:
+        y0 = -y0
+    zero = torch.zeros(n, device=dev)
+    vecs = [s0, zero, y0, zero.clone(), g]               # s_0, s_1 = 0, y_0, y_1 = 0, g
+    table = (C.c_void_p * 5)(*[v.data_ptr() for v in vecs])
+    gram = torch.zeros(64, device=dev, dtype=torch.float64)
+    coef = torch.zeros(32, device=dev, dtype=torch.float64)
+    st = torch.cuda.current_stream().cuda_stream
+    _lib.check(lib.drtvam_lbfgs_direction(0, table, 2, n, gram.data_ptr(), 0, coef.data_ptr(), st))
+    d = torch.empty(n, device=dev)
+    _lib.check(lib.drtvam_lbfgs_combine(0, table, 2, coef.data_ptr(), n, d.data_ptr(), st))
+    torch.cuda.synchronize()
+    assert torch.isfinite(coef[:5]).all() and torch.isfinite(d).all()
+    # the same history without the vanishing pair gives the same direction
+    table1 = (C.c_void_p * 3)(s0.data_ptr(), y0.data_ptr(), g.data_ptr())
+    coef1 = torch.zeros(32, device=dev, dtype=torch.float64)
+    _lib.check(lib.drtvam_lbfgs_direction(0, table1, 1, n, gram.data_ptr(), 0, coef1.data_ptr(), st))
+    d1 = torch.empty(n, device=dev)
+    _lib.check(lib.drtvam_lbfgs_combine(0, table1, 1, coef1.data_ptr(), n, d1.data_ptr(), st))
+    # (gamma comes from the newest pair: unusable -> 1 in the first case, y_0.s_0 / y_0.y_0 in the second)
+    gamma1 = float(torch.dot(y0, s0) / torch.dot(y0, y0))
+    assert torch.isfinite(d1).all() and gamma1 > 0
+    # NaN dose -> NaN loss
+    loss = ThresholdedLoss({})
+    x = torch.rand(8, 8, 8, 1, device=dev)
+    x[3, 3, 3, 0] = float("nan")
+    t = (torch.rand(8, 8, 8, device=dev) > 0.5).float()
+    assert torch.isnan(loss(x, t, torch.zeros(3, device=dev)))
