@@ -153,6 +153,11 @@ def optimize(config, patterns_fwd=None, progress=True):
         target = discretize(scene, sensor=sensor)
     if rank == 0:
         os.makedirs(output, exist_ok=True)
+        if surface_aware:   # optimize.py:131-134
+            save_vol(target[..., 0, None], os.path.join(output, "target_in.exr"))
+            save_vol(target[..., 1, None], os.path.join(output, "target_out.exr"))
+        else:               # optimize.py:135-137
+            save_vol(target, os.path.join(output, "target.exr"))
         np.save(os.path.join(output, "target.npy"), target.cpu().numpy())
 
     patterns_key = 'projector.active_data'
@@ -279,6 +284,11 @@ def optimize(config, patterns_fwd=None, progress=True):
                                 patterns=(normalized_array * 255).astype(np.uint8))
             efficiency = np.sum(normalized_array / normalized_array.size)
             print("Pattern efficiency {:.4f}".format(efficiency))
+        if surface_aware:
+            # a binary target on the final sensor's grid next to the fractional one (optimize.py:354-359)
+            target_binary = discretize(scene, sensor=final_sensor)
+            np.save(os.path.join(output, "target_binary.npy"), target_binary.cpu().numpy())
+            save_vol(target_binary, os.path.join(output, "target_binary.exr"))
     return vol_final
 
 

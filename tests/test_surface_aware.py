@@ -202,3 +202,25 @@ def test_surface_aware_python_api_and_loss(workdir):
         v2 = dv.render(scene, prm, integrator=integ, sensor=final, spp=1, seed=0)
     assert v2.shape[-1] == 1
     scene.close()
+
+
+@pytest.mark.gpu
+def test_optimize_with_surface_aware_sensor_writes_the_reference_outputs(workdir):
+    """optimize() with a surface-aware sensor (optimize.py:113-116,131-134,354-359): the fractional target and its
+    two EXR channels, the binary target on the final sensor's grid, a loss that goes down through the fused
+    two-channel loss, and a final dose from the plain final_sensor."""
+    import os
+    from drtvam_b200.optimize import optimize
+    from drtvam_b200.synthetic import make_config
+    cfg = make_config("C4", workdir, n=32, surface_aware=True, n_steps=6)
+    cfg["output"] = os.path.join(workdir, "out_sa_optimize")
+    cfg["save_pattern_images"] = False
+    vol = optimize(cfg, progress=False)
+    assert tuple(vol.shape) == (32, 32, 32, 1)
+    for name in ("target.npy", "target_in.exr", "target_out.exr", "target_binary.npy", "target_binary.exr",
+                 "final.npy", "patterns.npz", "loss.npy"):
+        assert os.path.exists(os.path.join(cfg["output"], name)), name
+    loss = np.load(os.path.join(cfg["output"], "loss.npy"))
+    assert np.isfinite(loss).all() and loss[5] < 0.2 * loss[0]
+    assert np.load(os.path.join(cfg["output"], "target.npy")).shape == (32, 32, 32, 2)
+    assert np.load(os.path.join(cfg["output"], "target_binary.npy")).shape == (32, 32, 32, 1)
