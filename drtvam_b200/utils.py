@@ -180,11 +180,41 @@ def write_ply(path, verts, tris):
         f.write(rec.tobytes())
 
 
+def load_obj(path):
+    """Wavefront OBJ as Mitsuba's `obj` shape plugin reads it for this path (optimize.py:41 passes the file
+    extension on as the shape type): `v x y z` vertices and `f` faces, whose entries may be `i`, `i/t`, `i//n`
+    or `i/t/n`, 1-based or negative (relative to the vertices read so far); polygons are fan-triangulated.
+    Returns (vertices float64 [n, 3], triangles int64 [m, 3])."""
+    verts, tris = [], []
+    with open(path, "r") as f:
+        for line in f:
+            parts = line.split()
+            if not parts or parts[0].startswith("#"):
+                continue
+            if parts[0] == "v":
+                verts.append([float(x) for x in parts[1:4]])
+            elif parts[0] == "f":
+                idx = []
+                for token in parts[1:]:
+                    i = int(token.split("/")[0])
+                    idx.append(i - 1 if i > 0 else len(verts) + i)
+                for j in range(1, len(idx) - 1):
+                    tris.append([idx[0], idx[j], idx[j + 1]])
+    if not verts or not tris:
+        raise ValueError(f"'{path}' holds no triangles")
+    v, t = np.asarray(verts, np.float64), np.asarray(tris, np.int64)
+    if t.min() < 0 or t.max() >= len(v):
+        raise ValueError(f"'{path}': face index out of range")
+    return v, t
+
+
 def load_mesh(path):
     ext = os.path.splitext(path)[1][1:].lower()
-    if ext != "ply":
-        raise ValueError(f"Unsupported extension: '{ext}', only PLY meshes are supported.")
-    return load_ply(path)
+    if ext == "ply":
+        return load_ply(path)
+    if ext == "obj":
+        return load_obj(path)
+    raise ValueError(f"Unsupported extension: '{ext}', only PLY and OBJ meshes are supported.")
 
 
 def _uniform_sphere(u1, u2):
