@@ -166,6 +166,17 @@ __global__ void planar_check_pixels_kernel(const uint32_t* __restrict__ active_p
 
 
 // Rays of the deterministic table whose walk has a frozen axis (sensor.py:359):
+// one visit of a gather walk: the weight and the (not yet consumed) gathered value
+struct FrozenVisit {
+    static constexpr bool kRecordOnly = false;
+    const float* dL;
+    float w = 0.f, v = 0.f;
+    __device__ __forceinline__ void visit(size_t idx, float wt) {
+        w = wt;
+        v = __ldg(dL + idx);
+    }
+};
+
 // one thread per (listed (angle, column), DMD row), general walk.
 // kMode 0: in = active_data, out = film.  kMode 1: in = dL, out = pattern_grad (written, not added).
 template <int kMode>
@@ -186,9 +197,35 @@ planar_frozen_kernel(const __grid_constant__ SceneParams P, const int* __restric
     rng.seed(0u, 0u);  // never consumed: deterministic configuration
     const Ray ray = generate_ray(P, __ldg(active_pixels + j), rng);
     if (kMode == 1) {
-        GatherSink g{in};
-        trace_lane<false>(P, ray, rng, g);
-        out[j] = g.acc * ray_weight;
+        // one medium segment (the scene is planar): record it, then walk it with 8 gathers in flight - walked with
+        // one dependent load per voxel this kernel took 0.31 ms for the 2 400 lanes of C2 (profiles/r04c_*)
+        RecordSink rec;
+        rec.seg = ray;
+        trace_lane<false>(P, ray, rng, rec);
+        float acc = 0.f;
+        DdaWalk W;
+        if (rec.count > 1) {   // not a planar lane after all: the plain walk
+            Sampler rng2;
+            rng2.seed(0u, 0u);
+            GatherSink g{in};
+            trace_lane<false>(P, ray, rng2, g);
+            acc = g.acc;
+        } else if (rec.count == 1 && W.begin(P, rec.seg, rec.tmax, rec.w0, false)) {
+            bool walking = true;
+            while (walking) {
+                float w[8], v[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    FrozenVisit one{in};
+                    if (walking) walking = W.step(one);
+                    w[i] = one.w;
+                    v[i] = one.v;
+                }
+#pragma unroll
+                for (int i = 0; i < 8; ++i) acc = fmaf(w[i], v[i], acc);
+            }
+        }
+        out[j] = acc * ray_weight;
     } else {
         const float em = __ldg(in + j) * ray_weight;
         if (em == 0.f) return;
