@@ -24,6 +24,23 @@ def test_angle_ranges_balance():
     assert abs(sum(counts[a0:a1]) - sum(counts[b0:b1])) <= 50
 
 
+def test_slab_grid_keeps_a_slab_one_block_of_layers():
+    """parallel.slab_grid: (angle groups, z-slabs) with A * S = world size; a slab is one mostly-full block of
+    96..128 layers, the rest of the ranks become angle groups, and where no such cut exists the scene is sharded
+    by angle alone (the grids measured in DESIGN.md section 7)."""
+    from drtvam_b200.parallel import slab_grid
+    assert slab_grid(1, 400) == (1, 1)
+    assert slab_grid(2, 400) == (2, 1)       # two slabs of 200 layers would be three blocks each
+    assert slab_grid(4, 400) == (1, 4)
+    assert slab_grid(8, 400) == (2, 4)
+    assert slab_grid(8, 128) == (8, 1)       # one block already
+    assert slab_grid(2, 256) == (1, 2)
+    for world in (1, 2, 3, 4, 6, 8):
+        for layers in (50, 128, 200, 256, 400, 512, 1000):
+            a, s_ = slab_grid(world, layers)
+            assert a * s_ == world and (s_ == 1 or 96 <= layers // s_ <= 128)
+
+
 def test_shard_bounds_cover_everything():
     per = 12
     pix = torch.cat([torch.arange(k * per, k * per + (k % 3 + 1) * 3) for k in range(7)]).to(torch.int32)
