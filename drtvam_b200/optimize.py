@@ -18,6 +18,7 @@ from . import parallel
 from .geometry import geometries
 from .integrators import CornerIntegrator, RadonIntegrator, VolumeIntegrator
 from .lbfgs import LinearLBFGS
+from .optimizers import SGD, Adam
 from .loss import losses
 from .scene import load_dict, render, traverse
 from .transform import ScalarTransform4f
@@ -176,8 +177,8 @@ def optimize(config, patterns_fwd=None, progress=True):
         config['optimizer'] = {'type': 'lbfgs'}
     opt_cfg = dict(config['optimizer'])
     optim_type = opt_cfg.pop('type')
-    if optim_type != 'lbfgs':
-        raise NotImplementedError(f"optimizer '{optim_type}': only the linear L-BFGS of the reference CLI default is built")
+    if optim_type not in ('lbfgs', 'adam', 'sgd'):
+        raise ValueError(f"Unknown optimizer type: '{optim_type}'")
 
     if world > 1:
         scene.shard(rank, world)
@@ -198,8 +199,15 @@ def optimize(config, patterns_fwd=None, progress=True):
         loss_fn2.armijo_sweep = lambda x, dx, direction, *a: loss_fn.armijo_sweep(x, dx, target, direction, *a)
 
     consensus = parallel.make_consensus(None, world) if world > 1 else None
-    opt = LinearLBFGS(loss_fn=loss_fn2, render_fn=render_fn, dot=parallel.make_dot(None, world) if world > 1 else None,
-                      allsum=parallel.make_sum(None, world) if world > 1 else None, consensus=consensus, **opt_cfg)
+    if optim_type == 'adam':      # optimize.py:205-208
+        if world > 1 and opt_cfg.get('uniform', False):
+            raise NotImplementedError("Adam(uniform=True) on a sharded pattern vector")
+        opt = Adam(**opt_cfg)
+    elif optim_type == 'sgd':
+        opt = SGD(**opt_cfg)
+    else:
+        opt = LinearLBFGS(loss_fn=loss_fn2, render_fn=render_fn, dot=parallel.make_dot(None, world) if world > 1 else None,
+                          allsum=parallel.make_sum(None, world) if world > 1 else None, consensus=consensus, **opt_cfg)
     opt[patterns_key] = params[patterns_key]
     n_steps = config.get('n_steps', 40)
     loss_hist = np.zeros(n_steps)
@@ -249,7 +257,10 @@ def optimize(config, patterns_fwd=None, progress=True):
             if loss_hist[i] == 0.0:
                 print("Converged")
                 break
-            opt.step(vol.detach(), loss.detach())
+            if optim_type == 'lbfgs':
+                opt.step(vol.detach(), loss.detach())
+            else:
+                opt.step()
             # clamp patterns (optimize.py:320)
             opt[patterns_key] = torch.clamp_min(opt[patterns_key].detach(), 0)
             ev[2].record()
