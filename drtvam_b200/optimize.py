@@ -228,6 +228,26 @@ def optimize(config, patterns_fwd=None, progress=True):
             raise NotImplementedError("forward mode runs on one GPU")
         params[patterns_key] = flat
         params.update()
+    elif "psf_analysis" in config:
+        # optimize.py:245-264: project a handful of single pixels (a sparse pixel list: the general tracer)
+        if world > 1:
+            raise NotImplementedError("psf_analysis runs on one GPU")
+        print("\nPSF analysis enabled.")
+        entries = config["psf_analysis"]
+        print("Number of traced pixels:", len(entries))
+        xres, yres = config["projector"]["resx"], config["projector"]["resy"]
+        pixels, data = [], []
+        for entry in entries:
+            assert entry["x"] < xres, "Invalid entry in psf_analysis: x out of bounds. Please check the configuration file."
+            assert entry["y"] < yres, "Invalid entry in psf_analysis: y out of bounds. Please check the configuration file."
+            assert entry["index_pattern"] < config["projector"]["n_patterns"], \
+                "Invalid entry in psf_analysis: index_pattern out of bounds. Please check the configuration file."
+            pixels.append(xres * yres * entry["index_pattern"] + xres * entry["y"] + entry["x"])
+            data.append(float(entry["intensity"]))
+        dev = scene.projector.active_data.device
+        params['projector.active_pixels'] = torch.tensor(pixels, dtype=torch.int64, device=dev).to(torch.int32)
+        params['projector.active_data'] = torch.tensor(data, dtype=torch.float32, device=dev)
+        params.update()
     else:
         if rank == 0:
             print("Optimizing patterns...")

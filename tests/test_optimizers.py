@@ -1,6 +1,7 @@
 """Adam / SGD of the pattern vector: Mitsuba's update rules (mi.ad.Adam / mi.ad.SGD, which the reference builds
 from config['optimizer'] at optimize.py:205-209), checked against the formulas written out by hand, and one
 GPU optimisation per optimizer through optimize()."""
+import copy
 import math
 import os
 
@@ -73,3 +74,26 @@ def test_first_order_optimizers_through_optimize(optimizer, workdir):
     with pytest.raises(ValueError):
         cfg["optimizer"] = {"type": "newton"}
         optimize(cfg, progress=False)
+
+
+@pytest.mark.gpu
+def test_psf_analysis_projects_the_listed_pixels(workdir):
+    """optimize.py:245-264: with a `psf_analysis` list in the config nothing is optimised; the listed single
+    pixels are projected at their intensities (a sparse pixel list, so the general tracer) and the result is
+    linear in them."""
+    from drtvam_b200.optimize import optimize
+    from drtvam_b200.synthetic import make_config
+    cfg = make_config("C3", workdir, n=32)
+    cfg["save_pattern_images"] = False
+    entries = [{"x": 16, "y": 16, "index_pattern": 0, "intensity": 1.0},
+               {"x": 10, "y": 20, "index_pattern": 8, "intensity": 2.0}]
+    vols = []
+    for k, sub in enumerate((entries, entries[:1], entries[1:])):
+        c = copy.deepcopy(cfg)          # load_scene pops the sensor's scale keys, as the reference does
+        c.update(psf_analysis=sub, output=os.path.join(workdir, f"out_psf{k}"))
+        vols.append(optimize(c, progress=False).cpu().numpy())
+        pat = np.load(os.path.join(c["output"], "patterns.npz"))["patterns"]
+        assert np.count_nonzero(pat) == len(sub)
+    assert pat[8, 20, 10] == 2.0
+    assert vols[0].sum() > 0 and np.count_nonzero(vols[1]) < 0.05 * vols[1].size      # one thin beam
+    assert np.allclose(vols[0], vols[1] + vols[2], rtol=0, atol=1e-6 * vols[0].max())
